@@ -1,0 +1,71 @@
+// common.cuh - shared device helpers.  Compiled with -fmad=false: every a*b+c below is two
+// roundings exactly like the reference's unfused torch ops; explicit __fmaf_rn marks the places
+// where ATen itself fuses (vector norm).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "../../include/pbhc_b200.h"
+
+namespace pbhc {
+
+void set_error(const char* fmt, ...);
+int check_launch(const char* what);
+
+struct Q4 { float x, y, z, w; };  // xyzw
+struct V3 { float x, y, z; };
+
+__device__ __forceinline__ float clip01(float v) { return fminf(fmaxf(v, 0.0f), 1.0f); }
+
+// torch.linalg.vector_norm over 3 contiguous floats on CPU = sqrt(fma(z,z,fma(y,y,x*x)))
+// (probed against torch 2.11; see DESIGN.md "arithmetic parity").
+__device__ __forceinline__ float norm3(float x, float y, float z) {
+  return sqrtf(__fmaf_rn(z, z, __fmaf_rn(y, y, x * x)));
+}
+__device__ __forceinline__ float norm2(float x, float y) { return sqrtf(__fmaf_rn(y, y, x * x)); }
+
+// slerp, isaac_utils/rotations.py:210-232 (not renormalised)
+__device__ __forceinline__ Q4 slerp(Q4 a, Q4 b, float t) {
+  float c = ((a.x * b.x + a.y * b.y) + a.z * b.z) + a.w * b.w;
+  if (c < 0.0f) { b.x = -b.x; b.y = -b.y; b.z = -b.z; b.w = -b.w; }
+  c = fabsf(c);
+  float h = acosf(c);
+  float s = sqrtf(1.0f - c * c);
+  float ra = sinf((1.0f - t) * h) / s;
+  float rb = sinf(t * h) / s;
+  Q4 q = {ra * a.x + rb * b.x, ra * a.y + rb * b.y, ra * a.z + rb * b.z, ra * a.w + rb * b.w};
+  if (fabsf(s) < 0.001f) q = {0.5f * a.x + 0.5f * b.x, 0.5f * a.y + 0.5f * b.y, 0.5f * a.z + 0.5f * b.z, 0.5f * a.w + 0.5f * b.w};
+  if (fabsf(c) >= 1.0f) q = a;
+  return q;
+}
+
+// quat_mul (w_last), rotations.py:414-441 - the 8-multiplication form, association order kept
+__device__ __forceinline__ Q4 quat_mul(Q4 a, Q4 b) {
+  float ww = (a.z + a.x) * (b.x + b.y);
+  float yy = (a.w - a.y) * (b.w + b.z);
+  float zz = (a.w + a.y) * (b.w - b.z);
+  float xx = ww + yy + zz;
+  float qq = 0.5f * (xx + (a.z - a.x) * (b.x - b.y));
+  Q4 r;
+  r.w = qq - ww + (a.z - a.y) * (b.y - b.z);
+  r.x = qq - xx + (a.x + a.w) * (b.x + b.w);
+  r.y = qq - yy + (a.w - a.x) * (b.y + b.z);
+  r.z = qq - zz + (a.z + a.y) * (b.w - b.x);
+  return r;
+}
+__device__ __forceinline__ Q4 quat_conj(Q4 a) { return {-a.x, -a.y, -a.z, a.w}; }
+
+// my_quat_rotate / quat_rotate (rotations.py:83-99, 244-253): a + b + c ; inverse: a - b + c
+__device__ __forceinline__ V3 quat_rotate_impl(Q4 q, V3 v, bool inverse) {
+  float s = 2.0f * (q.w * q.w) - 1.0f;
+  V3 a = {v.x * s, v.y * s, v.z * s};
+  V3 cr = {q.y * v.z - q.z * v.y, q.z * v.x - q.x * v.z, q.x * v.y - q.y * v.x};
+  V3 b = {cr.x * q.w * 2.0f, cr.y * q.w * 2.0f, cr.z * q.w * 2.0f};
+  float d = (q.x * v.x + q.y * v.y) + q.z * v.z;  // bmm [1,3]x[3,1]
+  V3 c = {q.x * d * 2.0f, q.y * d * 2.0f, q.z * d * 2.0f};
+  if (inverse) return {a.x - b.x + c.x, a.y - b.y + c.y, a.z - b.z + c.z};
+  return {a.x + b.x + c.x, a.y + b.y + c.y, a.z + b.z + c.z};
+}
+__device__ __forceinline__ V3 quat_rotate(Q4 q, V3 v) { return quat_rotate_impl(q, v, false); }
+__device__ __forceinline__ V3 quat_rotate_inverse(Q4 q, V3 v) { return quat_rotate_impl(q, v, true); }
+
+}  // namespace pbhc
