@@ -347,3 +347,29 @@ def get_motion_state(tab, motion_ids, motion_times, offset=None):
     })
     out["_f0l"], out["_f1l"], out["_blend"] = f0, f1, blend
     return out
+
+
+# --------------------------------------------------------------------------------------
+# GAE                                            agents/ppo/ppo.py:338-355, mh_ppo/mh_ppo.py:376-395
+# --------------------------------------------------------------------------------------
+
+
+def gae(values, rewards, dones, last_values, gamma, lam, vec_reward):
+    """values/rewards [T,N,R], dones [T,N,1] bool, last_values [N,R] -> (returns, normalised advantages [T,N,1]).
+    vec_reward=True is MHPPO (advantages summed over the R heads before normalising)."""
+    returns = torch.zeros_like(values)
+    T = returns.shape[0]
+    advantage = 0
+    for step in reversed(range(T)):
+        next_values = last_values if step == T - 1 else values[step + 1]
+        nt = 1.0 - dones[step].float()
+        delta = rewards[step] + nt * gamma * next_values - values[step]
+        advantage = delta + nt * gamma * lam * advantage
+        returns[step] = advantage + values[step]
+    adv = returns - values
+    if vec_reward:
+        adv = adv.sum(dim=-1)
+        adv = (adv - adv.mean()) / (adv.std() + 1e-8)
+        return returns, adv.unsqueeze(-1)
+    adv = (adv - adv.mean()) / (adv.std() + 1e-8)
+    return returns, adv

@@ -39,7 +39,7 @@ class Tree(C.Structure):
 
 _lib = None
 
-EXPORTS = ["pbhc_abi_version", "pbhc_last_error", "pbhc_lookup", "pbhc_fk", "pbhc_gae", "pbhc_adv_normalize"]
+EXPORTS = ["pbhc_abi_version", "pbhc_last_error", "pbhc_lookup", "pbhc_fk", "pbhc_gae", "pbhc_adv_normalize", "pbhc_clip_prepare"]
 
 
 def lib():
@@ -62,6 +62,10 @@ def lib():
                            C.c_float, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
     L.pbhc_adv_normalize.restype = C.c_int
     L.pbhc_adv_normalize.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]
+    L.pbhc_clip_prepare.restype = C.c_int
+    L.pbhc_clip_prepare.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32,
+                                    C.c_int32, C.c_int32, C.c_float, C.POINTER(C.c_double), C.c_int32, C.c_void_p,
+                                    C.c_void_p, C.c_int32, C.c_void_p]
     if L.pbhc_abi_version() != 1:
         raise PbhcError("ABI version mismatch")
     _lib = L

@@ -138,3 +138,58 @@ class Humanoid_Batch:
                                       _lib.ptr(trans, torch.float32), n, _lib.ptr(pos), _lib.ptr(mat), _lib.ptr(quat),
                                       _lib.stream_ptr(dev)))
         return pos, mat, quat
+
+    def clip_kinematics(self, pose_aa, trans, dt, contact=None):
+        """FK + filtered velocities + dof_pos/dof_vel of one clip, packed as table records
+        [T, rec_stride] (layout: include/pbhc_b200.h).  pose_aa [T,J,3], trans [T,3] CUDA fp32."""
+        from .motion_lib import gaussian_weights, record_stride
+        J, Jb = self.num_bodies_augment, self.num_bodies
+        D = Jb - 1
+        T = pose_aa.shape[0]
+        dev = pose_aa.device
+        Cm = 0 if contact is None else contact.shape[1]
+        stride = record_stride(J, D, Cm)
+        pose_aa = pose_aa.contiguous()
+        pos, _, quat = self.fk(pose_aa, trans, want_mat=False, want_quat=True)
+        radius, w = gaussian_weights()
+        w_c = (C.c_double * len(w))(*w.tolist())
+        scratch = torch.empty(T, J, 6, device=dev, dtype=torch.float32)
+        records = torch.empty(T, stride, device=dev, dtype=torch.float32)
+        _lib.check(_lib.lib().pbhc_clip_prepare(_lib.ptr(pos), _lib.ptr(quat), _lib.ptr(pose_aa),
+                                                None if contact is None else _lib.ptr(contact.contiguous()), T, J, Jb, D, Cm,
+                                                dt, w_c, radius, _lib.ptr(scratch), _lib.ptr(records), stride,
+                                                _lib.stream_ptr(dev)))
+        return records
+
+    def fk_batch(self, pose, trans, convert_to_mat=True, return_full=False, dt=1 / 30):
+        """torch_humanoid_batch.py:168-226: same keys.  pose [B,T,J,3] axis-angle, trans [B,T,3] (CUDA)."""
+        if not convert_to_mat:
+            raise NotImplementedError("fk_batch(convert_to_mat=False) is not part of the B200 path")
+        if not pose.is_cuda:
+            raise _lib.PbhcError("fk_batch needs CUDA tensors (there is no CPU fallback)")
+        J, Jb = self.num_bodies_augment, self.num_bodies
+        B, T = pose.shape[:2]
+        p = pose[..., :J, :].to(torch.float32).reshape(B * T, J, 3)
+        t = trans.to(torch.float32).reshape(B * T, 3)
+        pos, mat, quat = self.fk(p, t)
+        pos, mat, quat = pos.view(B, T, J, 3), mat.view(B, T, J, 3, 3), quat.view(B, T, J, 4)
+        r = AttrDict()
+        ext = len(self.extend_config) > 0
+        if return_full:
+            recs = torch.stack([self.clip_kinematics(p.view(B, T, J, 3)[b], t.view(B, T, 3)[b], dt) for b in range(B)])
+            vel = recs[..., 7 * J:10 * J].reshape(B, T, J, 3)
+            ang = recs[..., 10 * J:13 * J].reshape(B, T, J, 3)
+            if ext:
+                r.global_velocity_extend, r.global_angular_velocity_extend = vel, ang
+        if ext:
+            r.global_translation_extend, r.global_rotation_mat_extend, r.global_rotation_extend = pos, mat, quat
+        nb = Jb if ext else J
+        r.global_translation, r.global_rotation_mat, r.global_rotation = pos[..., :nb, :], mat[..., :nb, :, :], quat[..., :nb, :]
+        if return_full:
+            D = Jb - 1
+            r.global_velocity, r.global_angular_velocity = vel[..., :nb, :], ang[..., :nb, :]
+            r.global_root_velocity, r.global_root_angular_velocity = vel[..., 0, :], ang[..., 0, :]
+            r.dof_pos = recs[..., 13 * J:13 * J + D]
+            r.dof_vels = recs[..., 13 * J + D:13 * J + 2 * D]
+            r.fps = int(1 / dt)
+        return r

@@ -1,0 +1,243 @@
+"""MotionLibRobot / MotionLibRobotWJX drop-ins (reference: humanoidverse/utils/motion_lib/
+motion_lib_base.py:42-522, motion_lib_robot.py:3-7, motion_lib_robot_WJX.py).
+
+Same constructor, methods, attributes and get_motion_state() dict; underneath ONE packed device
+table holds every UNIQUE sampled clip once (the reference concatenates one copy per env,
+motion_lib_base.py:356-372) and the sm_100a kernels pbhc_fk / pbhc_clip_prepare / pbhc_lookup do
+the work.  No CPU fallback: construction requires a CUDA device.
+"""
+import ctypes as C
+import glob
+import os
+import os.path as osp
+import random
+
+import numpy as np
+import torch
+
+from . import _lib
+from .fk import Humanoid_Batch, _cfg_get
+
+GAUSS_SIGMA, GAUSS_TRUNCATE = 2.0, 4.0
+
+
+def gaussian_weights(sigma=GAUSS_SIGMA, truncate=GAUSS_TRUNCATE):
+    """scipy.ndimage._gaussian_kernel1d(sigma, 0, radius) with radius = int(truncate*sigma + 0.5)."""
+    radius = int(truncate * float(sigma) + 0.5)
+    x = np.arange(-radius, radius + 1)
+    phi = np.exp(-0.5 / (sigma * sigma) * x ** 2)
+    return radius, phi / phi.sum()
+
+
+def record_stride(J, D, Cm):
+    return (13 * J + 2 * D + Cm + 3) // 4 * 4
+
+
+class MotionLibRobot:
+    def __init__(self, motion_lib_cfg, num_envs, device):
+        self.m_cfg = motion_lib_cfg
+        self._sim_fps = 1 / _cfg_get(motion_lib_cfg, "step_dt", 1 / 50)
+        self.num_envs = num_envs
+        self._device = torch.device(device)
+        if self._device.type != "cuda":
+            raise _lib.PbhcError("pbhc_b200.MotionLibRobot needs a CUDA device (there is no CPU fallback)")
+        _lib.lib()
+        self.has_action = False
+        self.has_contact_mask = None
+        self._contact_size = 0
+        self.mesh_parsers = Humanoid_Batch(motion_lib_cfg)
+        self.num_joints = self.mesh_parsers.num_bodies  # len(skeleton_tree.node_names), motion_lib_base.py:286
+        self.load_data(_cfg_get(motion_lib_cfg, "motion_file"))
+        self.setup_constants()
+
+    # ---- motion_lib_base.py:63-105 -----------------------------------------------------------
+    def load_data(self, motion_file):
+        import joblib
+        if isinstance(motion_file, dict):
+            self._motion_data_load = motion_file
+            values, keys = list(motion_file.values()), list(motion_file.keys())
+        elif osp.isfile(motion_file):
+            self._motion_data_load = joblib.load(motion_file)
+            values, keys = list(self._motion_data_load.values()), list(self._motion_data_load.keys())
+        else:
+            files = glob.glob(osp.join(motion_file, "*.pkl"))
+            values, keys = files, files
+            self._motion_data_load = joblib.load(files[0])
+        self._motion_data_list = np.empty(len(values), dtype=object)
+        for i, v in enumerate(values):
+            self._motion_data_list[i] = v
+        self._motion_data_keys = np.array(keys)
+        self._num_unique_motions = len(values)
+
+    def setup_constants(self):
+        dev = self._device
+        self._curr_motion_ids = None
+        self._termination_history = torch.zeros(self._num_unique_motions, device=dev)
+        self._success_rate = torch.zeros(self._num_unique_motions, device=dev)
+        self._sampling_history = torch.zeros(self._num_unique_motions, device=dev)
+        self._sampling_prob = torch.ones(self._num_unique_motions, device=dev) / self._num_unique_motions
+
+    # ---- motion_lib_base.py:261-391, 403-472 --------------------------------------------------
+    def _clip_arrays(self, entry, max_len):
+        if not isinstance(entry, dict):
+            key = entry.split("/")[-1].split(".")[0]
+            import joblib
+            entry = joblib.load(entry)[key]
+        seq_len = entry["root_trans_offset"].shape[0]
+        if max_len == -1 or seq_len < max_len:
+            start, end = 0, seq_len
+        else:
+            start = random.randint(0, seq_len - max_len)
+            end = start + max_len
+        out = dict(trans=np.asarray(entry["root_trans_offset"])[start:end], pose_aa=np.asarray(entry["pose_aa"])[start:end],
+                   fps=entry["fps"], contact=None)
+        if "action" in entry:
+            self.has_action = True
+        if "contact_mask" in entry:
+            cm = np.asarray(entry["contact_mask"])
+            assert cm.ndim == 2 and cm.shape[0] == seq_len
+            if cm.shape[1] != 2:
+                raise ValueError(f"Contact mask shape {cm.shape} is not supported")
+            self._contact_size = cm.shape[1]
+            self.has_contact_mask = "point"
+            out["contact"] = cm[start:end]
+        return out
+
+    def load_motions(self, random_sample=True, start_idx=0, max_len=-1, target_heading=None, sampling_prob=None):
+        if target_heading is not None:
+            raise NotImplementedError("target_heading re-basing is not part of the B200 path")
+        dev = self._device
+        n_load = self.num_envs
+        if random_sample:
+            prob = self._sampling_prob if sampling_prob is None else sampling_prob
+            sample_idxes = torch.multinomial(prob, num_samples=n_load, replacement=True).to(dev)
+        else:
+            sample_idxes = torch.remainder(torch.arange(n_load) + start_idx, self._num_unique_motions).to(dev)
+        self._curr_motion_ids = sample_idxes
+        idx_host = sample_idxes.cpu().numpy()
+        self.curr_motion_keys = self._motion_data_keys[idx_host]
+        # unique clips only (a random crop makes every sample its own clip)
+        if max_len == -1:
+            uniq, clip_of_motion = np.unique(idx_host, return_inverse=True)
+        else:
+            uniq, clip_of_motion = idx_host, np.arange(n_load)
+        clips = [self._clip_arrays(self._motion_data_list[u], max_len) for u in uniq]
+        self._build_table(clips)
+        com = torch.as_tensor(clip_of_motion, dtype=torch.int64, device=dev)
+        self._clip_of_motion = com.to(torch.int32).contiguous()
+        # per-loaded-motion tables, as the reference exposes them
+        self._motion_lengths = self._clip_length[com]
+        self._motion_fps = self._clip_fps[com]
+        self._motion_dt = self._clip_dt[com]
+        self._motion_num_frames = self._clip_num_frames.to(torch.int64)[com]
+        self._motion_bodies = torch.zeros(n_load, 17, device=dev)
+        self._num_motions = n_load
+        shifted = self._motion_num_frames.roll(1)
+        shifted[0] = 0
+        self.length_starts = shifted.cumsum(0)  # reference layout (one copy per env); informational
+        self.motion_ids = torch.arange(n_load, dtype=torch.long, device=dev)
+        self.num_bodies = self.num_joints
+        return clips
+
+    def _build_table(self, clips):
+        dev = self._device
+        hb = self.mesh_parsers
+        J, Jb, D = hb.num_bodies_augment, hb.num_bodies, hb.num_bodies - 1
+        Cm = self._contact_size if self.has_contact_mask else 0
+        stride = record_stride(J, D, Cm)
+        nf = [int(c["pose_aa"].shape[0]) for c in clips]
+        total = int(sum(nf))
+        records = torch.empty(total, stride, device=dev, dtype=torch.float32)
+        radius, w = gaussian_weights()
+        w_c = (C.c_double * len(w))(*w.tolist())
+        L, st = _lib.lib(), _lib.stream_ptr(dev)
+        fps_l, dt_l, len_l = [], [], []
+        row = 0
+        for c, T in zip(clips, nf):
+            dt = 1 / c["fps"]
+            pose = torch.as_tensor(np.ascontiguousarray(c["pose_aa"][:, :J]), dtype=torch.float32).to(dev)
+            trans = torch.as_tensor(np.ascontiguousarray(c["trans"]), dtype=torch.float32).to(dev)
+            pos, _, quat = hb.fk(pose, trans, want_mat=False, want_quat=True)
+            contact = None
+            if Cm:
+                contact = torch.as_tensor(np.ascontiguousarray(c["contact"]), dtype=torch.float32).to(dev)
+            scratch = torch.empty(T, J, 6, device=dev, dtype=torch.float32)
+            _lib.check(L.pbhc_clip_prepare(_lib.ptr(pos), _lib.ptr(quat), _lib.ptr(pose), _lib.ptr(contact), T, J, Jb, D,
+                                           Cm, dt, w_c, radius, _lib.ptr(scratch), records[row:row + T].data_ptr(), stride, st))
+            fps = int(1 / dt)  # torch_humanoid_batch.py:225
+            fps_l.append(fps)
+            dt_l.append(1.0 / fps)
+            len_l.append(1.0 / fps * (T - 1))
+            row += T
+        self._records = records
+        self._rec_stride = stride
+        self._clip_num_frames = torch.tensor(nf, dtype=torch.int32, device=dev)
+        starts = np.concatenate([[0], np.cumsum(nf)[:-1]]).astype(np.int64)
+        self._clip_frame_start = torch.as_tensor(starts, device=dev)
+        self._clip_length = torch.tensor(len_l, dtype=torch.float32, device=dev)
+        self._clip_dt = torch.tensor(dt_l, dtype=torch.float32, device=dev)
+        self._clip_fps = torch.tensor(fps_l, dtype=torch.float32, device=dev)
+        self._desc = _lib.TableDesc(records.data_ptr(), self._clip_num_frames.data_ptr(), self._clip_frame_start.data_ptr(),
+                                    self._clip_length.data_ptr(), self._clip_dt.data_ptr(), total, len(nf), J, Jb, D, Cm, stride)
+        self._dims = (J, Jb, D, Cm)
+
+    # ---- small accessors (motion_lib_base.py:474-501) ------------------------------------------
+    def num_motions(self):
+        return self._num_motions
+
+    def get_total_length(self):
+        return sum(self._motion_lengths)
+
+    def get_motion_num_steps(self, motion_ids=None):
+        if motion_ids is None:
+            return (self._motion_num_frames * self._sim_fps / self._motion_fps).ceil().int()
+        return (self._motion_num_frames[motion_ids] * self._sim_fps / self._motion_fps).ceil().int()
+
+    def sample_time(self, motion_ids, truncate_time=None):
+        phase = torch.rand(motion_ids.shape, device=self._device)
+        motion_len = self._motion_lengths[motion_ids]
+        if truncate_time is not None:
+            assert truncate_time >= 0.0
+            motion_len -= truncate_time
+        return phase * motion_len
+
+    def get_motion_length(self, motion_ids=None):
+        if motion_ids is None:
+            return self._motion_lengths
+        return self._motion_lengths[motion_ids]
+
+    # ---- motion_lib_base.py:123-259 -------------------------------------------------------------
+    def get_motion_state(self, motion_ids, motion_times, offset=None, with_indices=False):
+        J, Jb, D, Cm = self._dims
+        dev = self._device
+        shape = tuple(motion_ids.shape)
+        n = int(np.prod(shape)) if len(shape) else 1
+        ids = motion_ids.to(device=dev, dtype=torch.int64).contiguous()
+        times = motion_times.to(device=dev, dtype=torch.float32).contiguous()
+        off = None if offset is None else offset.to(device=dev, dtype=torch.float32).contiguous()
+        f = lambda *s: torch.empty(shape + s, device=dev, dtype=torch.float32)
+        res = {"root_pos": f(3), "root_rot": f(4), "dof_pos": f(D), "root_vel": f(3), "root_ang_vel": f(3),
+               "dof_vel": f(D), "motion_aa": f(3 * Jb), "motion_bodies": f(17), "rg_pos": f(Jb, 3), "rb_rot": f(Jb, 4),
+               "body_vel": f(Jb, 3), "body_ang_vel": f(Jb, 3), "rg_pos_t": f(J, 3), "rg_rot_t": f(J, 4),
+               "body_vel_t": f(J, 3), "body_ang_vel_t": f(J, 3)}
+        if Cm:
+            res["contact_mask"] = f(Cm)
+        extra = {}
+        if with_indices:
+            extra = {"f0l": torch.empty(shape, device=dev, dtype=torch.int64),
+                     "f1l": torch.empty(shape, device=dev, dtype=torch.int64), "blend": f()}
+        out = _lib.LookupOut()
+        for k in _lib.LOOKUP_FIELDS:
+            t = res.get(k, extra.get(k))
+            setattr(out, k, None if t is None else t.data_ptr())
+        _lib.check(_lib.lib().pbhc_lookup(C.byref(self._desc), self._clip_of_motion.data_ptr(), ids.data_ptr(),
+                                          times.data_ptr(), None if off is None else off.data_ptr(), n, C.byref(out),
+                                          _lib.stream_ptr(dev)))
+        res["dof_vel"] = res["dof_vel"].view(shape[0], -1) if len(shape) else res["dof_vel"]  # :246
+        if Cm:  # the reference puts contact_mask first (:231-238); dict order is not part of the contract
+            pass
+        res.update({"_" + k: v for k, v in extra.items()})
+        return res
+
+
+MotionLibRobotWJX = MotionLibRobot  # the single-clip "FakeCat" variant (motion_lib_robot_WJX.py) needs no special case here
