@@ -21,6 +21,8 @@ __device__ __forceinline__ float clip01(float v) { return fminf(fmaxf(v, 0.0f), 
 __device__ __forceinline__ float norm3(float x, float y, float z) {
   return sqrtf(__fmaf_rn(z, z, __fmaf_rn(y, y, x * x)));
 }
+// ... but over 4 contiguous floats ATen's vectorised path gives the plain sequential sum (probed).
+__device__ __forceinline__ float norm4(float x, float y, float z, float w) { return sqrtf(((x * x + y * y) + z * z) + w * w); }
 __device__ __forceinline__ float norm2(float x, float y) { return sqrtf(__fmaf_rn(y, y, x * x)); }
 
 // slerp, isaac_utils/rotations.py:210-232 (not renormalised)

@@ -33,7 +33,7 @@ __global__ void clip_raw_vel_kernel(const float* __restrict__ pos, const float* 
     const float* a = quat + ((int64_t)(t + 1) * J + j) * 4;
     const float* b = quat + ((int64_t)t * J + j) * 4;
     Q4 m = quat_mul({a[0], a[1], a[2], a[3]}, quat_conj({b[0], b[1], b[2], b[3]}));
-    float n = sqrtf(__fmaf_rn(m.w, m.w, __fmaf_rn(m.z, m.z, __fmaf_rn(m.y, m.y, m.x * m.x))));
+    float n = norm4(m.x, m.y, m.z, m.w);
     n = fmaxf(n, 1e-9f);
     dq = {m.x / n, m.y / n, m.z / n, m.w / n};
   }

@@ -142,6 +142,12 @@ class Humanoid_Batch:
     def clip_kinematics(self, pose_aa, trans, dt, contact=None):
         """FK + filtered velocities + dof_pos/dof_vel of one clip, packed as table records
         [T, rec_stride] (layout: include/pbhc_b200.h).  pose_aa [T,J,3], trans [T,3] CUDA fp32."""
+        pose_aa = pose_aa.contiguous()
+        pos, _, quat = self.fk(pose_aa, trans, want_mat=False, want_quat=True)
+        return self.pack_clip(pos, quat, pose_aa, dt, contact)
+
+    def pack_clip(self, pos, quat, pose_aa, dt, contact=None):
+        """pbhc_clip_prepare: world pos [T,J,3] / quat xyzw [T,J,4] (FK output) + pose_aa -> records."""
         from .motion_lib import gaussian_weights, record_stride
         J, Jb = self.num_bodies_augment, self.num_bodies
         D = Jb - 1
@@ -149,13 +155,12 @@ class Humanoid_Batch:
         dev = pose_aa.device
         Cm = 0 if contact is None else contact.shape[1]
         stride = record_stride(J, D, Cm)
-        pose_aa = pose_aa.contiguous()
-        pos, _, quat = self.fk(pose_aa, trans, want_mat=False, want_quat=True)
         radius, w = gaussian_weights()
         w_c = (C.c_double * len(w))(*w.tolist())
         scratch = torch.empty(T, J, 6, device=dev, dtype=torch.float32)
         records = torch.empty(T, stride, device=dev, dtype=torch.float32)
-        _lib.check(_lib.lib().pbhc_clip_prepare(_lib.ptr(pos), _lib.ptr(quat), _lib.ptr(pose_aa),
+        _lib.check(_lib.lib().pbhc_clip_prepare(_lib.ptr(pos.contiguous()), _lib.ptr(quat.contiguous()),
+                                                _lib.ptr(pose_aa.contiguous()),
                                                 None if contact is None else _lib.ptr(contact.contiguous()), T, J, Jb, D, Cm,
                                                 dt, w_c, radius, _lib.ptr(scratch), _lib.ptr(records), stride,
                                                 _lib.stream_ptr(dev)))

@@ -233,7 +233,7 @@ class MotionLibRobot:
         _lib.check(_lib.lib().pbhc_lookup(C.byref(self._desc), self._clip_of_motion.data_ptr(), ids.data_ptr(),
                                           times.data_ptr(), None if off is None else off.data_ptr(), n, C.byref(out),
                                           _lib.stream_ptr(dev)))
-        res["dof_vel"] = res["dof_vel"].view(shape[0], -1) if len(shape) else res["dof_vel"]  # :246
+        res["dof_vel"] = res["dof_vel"].reshape(shape[0], int(np.prod(shape[1:])) * D) if len(shape) else res["dof_vel"]  # :246
         if Cm:  # the reference puts contact_mask first (:231-238); dict order is not part of the contract
             pass
         res.update({"_" + k: v for k, v in extra.items()})

@@ -1,0 +1,75 @@
+#!/usr/bin/env python
+"""Per-kernel timing on one GPU (CUDA events, L2 flushed by working sets larger than L2):
+python tools/microbench.py [--envs 65536] [--iters 20].  Prints one JSON line per kernel with achieved
+algorithmic GB/s (SURVEY.md 8d byte figures).  Development aid; bench.py is the contract."""
+import argparse
+import json
+import os
+import sys
+import tempfile
+
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+
+def timeit(fn, iters, warmup=3):
+    for _ in range(warmup):
+        fn()
+    torch.cuda.synchronize()
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(iters + 1)]
+    ev[0].record()
+    for i in range(iters):
+        fn()
+        ev[i + 1].record()
+    torch.cuda.synchronize()
+    ts = sorted(ev[i].elapsed_time(ev[i + 1]) for i in range(iters))
+    return ts[len(ts) // 2]
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--envs", type=int, default=65536)
+    ap.add_argument("--iters", type=int, default=20)
+    a = ap.parse_args()
+    from tests._util import product_cfg
+    from pbhc_b200.motion_lib import MotionLibRobot
+    from pbhc_b200.gae import compute_returns
+    dev = "cuda:0"
+    n = a.envs
+    peak = 6548.8
+    for tag, names in (("23", ["Horse-stance_pose", "Bruce_Lee_pose", "Charleston_dance", "Hooks_punch",
+                               "Horse-stance_punch", "Roundhouse_kick", "Side_kick"]), ("29", ["g1_29dof_clip"])):
+        ml = MotionLibRobot(product_cfg(tag, tempfile.mkdtemp(), names), n, dev)
+        ml.load_motions(random_sample=False)
+        J, Jb, D, Cm = ml._dims
+        ids = torch.randint(0, n, (n,), device=dev)
+        t = torch.rand(n, device=dev) * ml._motion_lengths[ids]
+        off = torch.randn(n, 3, device=dev)
+        ms = timeit(lambda: ml.get_motion_state(ids, t, off), a.iters)
+        rec = 13 * J + 2 * D + Cm
+        outf = 3 + 4 + D + 3 + 3 + D + 3 * Jb + 17 + 13 * Jb + 13 * J + Cm
+        byt = 24 + 2 * rec * 4 + outf * 4
+        print(json.dumps(dict(kernel=f"lookup_{tag}", n=n, ms=ms, bytes_per_unit=byt, gbs=byt * n / ms / 1e6,
+                              frac=byt * n / ms / 1e6 / peak)))
+        pose = torch.randn(n, J, 3, device=dev) * 0.5
+        trans = torch.randn(n, 3, device=dev)
+        hb = ml.mesh_parsers
+        ms = timeit(lambda: hb.fk(pose, trans), a.iters)
+        byt = J * 12 + 12 + J * (12 + 16 + 36)
+        print(json.dumps(dict(kernel=f"fk_{tag}", n=n, ms=ms, bytes_per_unit=byt, gbs=byt * n / ms / 1e6,
+                              frac=byt * n / ms / 1e6 / peak)))
+    for R, N in ((1, n * 4), (21, n)):
+        T = 24
+        v, r = torch.randn(T, N, R, device=dev), torch.randn(T, N, R, device=dev)
+        d = torch.rand(T, N, 1, device=dev) < 0.02
+        lv = torch.randn(N, R, device=dev)
+        ms = timeit(lambda: compute_returns(v, r, d, lv, 0.99, 0.95), a.iters)
+        byt = T * R * 12 + T + R * 4 + T * 4 + T * 8
+        print(json.dumps(dict(kernel=f"gae_R{R}", n=N, ms=ms, bytes_per_unit=byt, gbs=byt * N / ms / 1e6,
+                              frac=byt * N / ms / 1e6 / peak)))
+
+
+if __name__ == "__main__":
+    main()
