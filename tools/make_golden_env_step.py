@@ -1,0 +1,113 @@
+"""env stage of tools/make_golden.py: drive the UNMODIFIED reference LeggedRobotMotionTracking (on
+oracle/ref_env.FakeSim) for a few steps on seeded synthetic simulator state and dump, per step, every
+input of `_post_physics_step` and every output / mutated buffer -> tests/golden/ref_env_<case>.npz.
+"""
+import os
+
+import numpy as np
+import torch
+
+from oracle import ref_env as E, ref_loader as R, synth
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+GOLD = os.path.join(ROOT, "tests", "golden")
+
+
+def _np(x):
+    if torch.is_tensor(x):
+        return x.detach().cpu().numpy().copy()
+    return np.asarray(x)
+
+
+def env_state(env):
+    """every persistent per-env / scalar buffer the hot path reads or writes."""
+    s = dict(
+        episode_length_buf=env.episode_length_buf, motion_start_times=env.motion_start_times, motion_len=env.motion_len,
+        motion_ids=env.motion_ids, actions=env.actions, last_actions=env.last_actions, last_dof_pos=env.last_dof_pos,
+        last_dof_vel=env.last_dof_vel, last_contacts=env.last_contacts.float(), feet_air_time=env.feet_air_time,
+        kp_scale=env._kp_scale, kd_scale=env._kd_scale, rfi_lim_scale=env._rfi_lim_scale, rao_scale=env._rao_scale,
+        action_delay_idx=env.action_delay_idx, default_dof_pos=env.default_dof_pos,
+        base_com_bias=env.simulator._base_com_bias, link_mass_scale=env.simulator._link_mass_scale,
+        friction_coeffs=env.simulator.friction_coeffs, env_origins=env.env_origins,
+        average_episode_length=np.float64(env.average_episode_length), reward_penalty_scale=np.float64(env.reward_penalty_scale),
+        motion_far_threshold=np.float64(env.terminate_when_motion_far_threshold),
+        soft_dof_pos=np.float64(env.soft_dof_pos_curriculum_value), soft_dof_vel=np.float64(env.soft_dof_vel_curriculum_value),
+        soft_torque=np.float64(env.soft_torque_curriculum_value), rew_buf=env.rew_buf, reset_buf=env.reset_buf,
+        time_out_buf=env.time_out_buf, dof_state=env.simulator.dof_state, root_state=env.simulator.all_root_states,
+        end_time_ratio_buf=env.end_time_ratio_buf)
+    for k, v in env.history_handler.history.items():
+        s["hist_" + k] = v
+    for k, v in env.episode_sums.items():
+        s["epsum_" + k] = v
+    for k, v in env.config.rewards.reward_tracking_sigma.items():
+        s["sigma_" + k] = np.float64(v)
+    for k, v in getattr(env, "_reward_error_ema", {}).items():
+        s["ema_" + k] = np.float64(v)
+    return {k: _np(v) for k, v in s.items()}
+
+
+def run_case(name, n_envs, n_steps, obs, seed, overrides=None):
+    ov = {"domain_rand.push_robots": False}
+    ov.update(overrides or {})
+    cfg = E.build_config(n_envs, R.example_motion("Horse-stance_pose"), obs=obs, overrides=ov)
+    env, ns = E.make_env(cfg, seed=seed)
+    sim = env.simulator
+    gen = torch.Generator().manual_seed(seed)
+    N, D, Jb = n_envs, env.num_dof, env.num_bodies
+    # spread the envs over the clip and put a few near its end so motion_end fires
+    env.motion_start_times[:] = torch.rand(N, generator=gen) * env.motion_len
+    env.motion_start_times[:3] = env.motion_len[:3] - torch.tensor([0.01, 0.03, 0.05])
+    env.episode_length_buf[:] = torch.randint(0, 50, (N,), generator=gen)
+    env.episode_length_buf[:3] = 0
+    # privileged DR tensors that the critic observes
+    sim._base_com_bias[:] = (torch.rand(N, 3, generator=gen) - 0.5) * 0.1
+    sim._link_mass_scale[:] = 0.9 + 0.2 * torch.rand(N, sim._link_mass_scale.shape[1], generator=gen)
+    sim.friction_coeffs[:] = 0.2 + torch.rand(N, 1, 1, generator=gen)
+    env._kp_scale[:] = 0.9 + 0.2 * torch.rand(N, D, generator=gen)
+    env._kd_scale[:] = 0.9 + 0.2 * torch.rand(N, D, generator=gen)
+    out = {"meta_n_envs": N, "meta_n_steps": n_steps, "meta_obs": obs, "meta_dt": env.dt,
+           "meta_reward_names": np.array(env.reward_names), "meta_reward_scales": np.array([env.reward_scales[k] for k in env.reward_names]),
+           "meta_termination_scale": np.float64(env.reward_scales["termination"]),
+           "meta_history_keys": np.array(list(env.history_handler.history.keys()))}
+    for k, v in env_state(env).items():
+        out["init_" + k] = v
+    for step in range(n_steps):
+        actions = synth.synth_actions(N, D, gen)
+        env._pre_physics_step(actions)
+        env._physics_step()
+        t = (env.episode_length_buf + 2) * env.dt + env.motion_start_times
+        ref = env._motion_lib.get_motion_state(env.motion_ids, t, offset=env.env_origins)
+        body, root, dof, cf = synth.synth_sim_state(ref, Jb, gen)
+        sim.set_state(body, root, dof, cf)
+        p = f"s{step}_"
+        out.update({p + "in_body_state": _np(body), p + "in_root_state": _np(root), p + "in_dof_state": _np(dof),
+                    p + "in_contact_forces": _np(cf), p + "in_actions": _np(env.actions), p + "in_torques": _np(env.torques)})
+        env._post_physics_step()
+        for k, v in env.obs_buf_dict.items():
+            out[p + "obs_" + k] = _np(v)
+        for k, v in env_state(env).items():
+            out[p + "out_" + k] = v
+        for k, v in env.log_dict.items():
+            out[p + "log_" + k] = _np(v).astype(np.float64)
+        out[p + "extras_ref_body_pos_extend"] = _np(env.extras["ref_body_pos_extend"])
+        out[p + "extras_ref_body_rot_extend"] = _np(env.extras["ref_body_rot_extend"])
+        out[p + "dbg_dif_global_body_pos"] = _np(env.dif_global_body_pos)
+        out[p + "dbg_ref_motion_phase"] = _np(env._ref_motion_phase)
+        out[p + "dbg_base_ang_vel"] = _np(env.base_ang_vel)
+        out[p + "dbg_projected_gravity"] = _np(env.projected_gravity)
+    np.savez_compressed(os.path.join(GOLD, f"ref_env_{name}.npz"), **out)
+    return env
+
+
+ZERO_NOISE = {f"obs.noise_scales.{k}": 0.0 for k in ("base_ang_vel", "projected_gravity", "dof_pos", "dof_vel")}
+
+
+def run(ns=None):
+    # obs=main ships uniform observation noise (helpers.py:152, torch.rand_like): parity runs set the four
+    # non-zero noise scales to 0 exactly like the reference's own obs/motion_tracking/benchmark.yaml does.
+    run_case("mt23_main", 48, 6, "motion_tracking/main", 11, ZERO_NOISE)
+    run_case("mt23_bench", 32, 3, "motion_tracking/benchmark", 12)
+
+
+if __name__ == "__main__":
+    run()
