@@ -278,7 +278,10 @@ class MotionTable:
     """Concatenation of clips exactly as load_motions lays them out (motion_lib_base.py:342-384):
     per-clip num_frames / length / dt / fps and length_starts = cumsum(roll(num_frames))."""
 
-    def __init__(self, clips, num_bodies):
+    def __init__(self, clips, num_bodies, motion_to_clip=None):
+        """motion_to_clip (optional, [num_motions] long): the reference holds one copy of its clip per sampled
+        motion; with this indirection the oracle stores each unique clip once - same values, same indices
+        relative to the clip start."""
         self.num_bodies = num_bodies
         cat = lambda k: torch.cat([getattr(c, k) for c in clips], dim=0).float()
         self.pos, self.rot, self.vel, self.ang_vel = cat("pos"), cat("rot"), cat("vel"), cat("ang_vel")
@@ -293,6 +296,10 @@ class MotionTable:
         shifted = self.num_frames.roll(1)
         shifted[0] = 0
         self.starts = shifted.cumsum(0)
+        if motion_to_clip is not None:
+            m = torch.as_tensor(motion_to_clip, dtype=torch.long)
+            self.num_frames, self.fps, self.dt = self.num_frames[m], self.fps[m], self.dt[m]
+            self.length, self.starts = self.length[m], self.starts[m]
 
 
 def calc_frame_blend(time, length, num_frames, dt):

@@ -1,0 +1,204 @@
+"""TrackSpec: everything the fused tracking step needs from the reference's composed config
+(`env.config` of `+exp=motion_tracking`, humanoidverse/config/**), flattened into plain Python values.
+
+It is the host-side equivalent of what LeggedRobotBase.__init__/_prepare_reward_function/_init_buffers,
+BaseTask._setup_robot_body_indices, LeggedRobotMotionTracking._init_tracking_config/_init_motion_extend
+and HistoryHandler.__init__ derive from the config (legged_robot_base.py:28-233, base_task.py:172-205,
+motion_tracking.py:203-247, history_handler.py:12-27).  Pure Python, no torch, no CUDA.
+"""
+import math
+
+# reward terms implemented by csrc/track.cu, in enum order (ids are part of the C ABI)
+REWARD_IDS = {name: i for i, name in enumerate([
+    "teleop_contact_mask", "teleop_max_joint_position", "teleop_body_position_extend", "teleop_vr_3point",
+    "teleop_body_position_feet", "teleop_body_rotation_extend", "teleop_body_ang_velocity_extend",
+    "teleop_body_velocity_extend", "teleop_joint_position", "teleop_joint_velocity", "penalty_torques",
+    "penalty_action_rate", "feet_air_time", "penalty_feet_contact_forces", "penalty_stumble", "penalty_slippage",
+    "limits_dof_pos", "limits_dof_vel", "limits_torque", "collision", "penalty_dof_vel", "penalty_dof_acc",
+    "foot_slip_penalty", "alive", "penalty_orientation", "teleop_contact_mask_v2"])}
+
+# adaptive-sigma slots (config.rewards.reward_tracking_sigma keys), in enum order
+SIGMA_IDS = {name: i for i, name in enumerate([
+    "teleop_max_joint_pos", "teleop_upper_body_pos", "teleop_lower_body_pos", "teleop_vr_3point_pos",
+    "teleop_feet_pos", "teleop_body_rot", "teleop_body_vel", "teleop_body_ang_vel", "teleop_joint_pos",
+    "teleop_joint_vel"])}
+
+# observation sources (getters `_get_obs_<key>`), enum order; dims as functions of (D, J, L)
+OBS_SRC = ["base_lin_vel", "base_ang_vel", "projected_gravity", "dof_pos", "dof_vel", "actions", "ref_motion_phase",
+           "dif_local_rigid_body_pos", "local_ref_rigid_body_pos", "dr_base_com", "dr_link_mass", "dr_kp", "dr_kd",
+           "dr_friction", "dr_ctrl_delay", "local_ref_rigid_body_vel", "global_ref_rigid_body_vel", "dif_joint_angles",
+           "dif_joint_velocities", "base_pos_z"]
+OBS_SRC_IDS = {k: i for i, k in enumerate(OBS_SRC)}
+
+
+def obs_src_dim(key, D, J, L):
+    return {"base_lin_vel": 3, "base_ang_vel": 3, "projected_gravity": 3, "dof_pos": D, "dof_vel": D, "actions": D,
+            "ref_motion_phase": 1, "dif_local_rigid_body_pos": 3 * J, "local_ref_rigid_body_pos": 3 * J, "dr_base_com": 3,
+            "dr_link_mass": L, "dr_kp": D, "dr_kd": D, "dr_friction": 1, "dr_ctrl_delay": 1,
+            "local_ref_rigid_body_vel": 3 * J, "global_ref_rigid_body_vel": 3 * J, "dif_joint_angles": D,
+            "dif_joint_velocities": D, "base_pos_z": 1}[key]
+
+
+def _get(cfg, path, default=None):
+    node = cfg
+    for k in path.split("."):
+        if node is None:
+            return default
+        if isinstance(node, dict):
+            node = node.get(k, None)
+        else:
+            node = getattr(node, k, None)
+    return default if node is None else node
+
+
+class TrackSpec:
+    """see module docstring.  Build with TrackSpec.from_config(env_config)."""
+
+    @classmethod
+    def from_config(cls, cfg):
+        s = cls()
+        robot, rw, obs, dr = _get(cfg, "robot"), _get(cfg, "rewards"), _get(cfg, "obs"), _get(cfg, "domain_rand")
+        s.body_names = list(_get(robot, "body_names"))
+        s.dof_names = list(_get(robot, "dof_names"))
+        s.Jb, s.D = len(s.body_names), len(s.dof_names)
+        ext = list(_get(robot, "motion.extend_config", []) or [])
+        s.ext_parent = [s.body_names.index(_get(e, "parent_name")) for e in ext]
+        s.ext_pos = [[float(v) for v in _get(e, "pos")] for e in ext]
+        s.ext_rot_wxyz = [[float(v) for v in _get(e, "rot")] for e in ext]
+        s.body_list = s.body_names + [_get(e, "joint_name") for e in ext]  # simulator._body_list after _init_motion_extend
+        s.J = len(s.body_list)
+        s.dt = _get(cfg, "simulator.config.sim.control_decimation") * (1.0 / _get(cfg, "simulator.config.sim.fps"))
+        s.max_episode_length = math.ceil(_get(cfg, "max_episode_length_s") / s.dt)  # base_task.py:39
+        s.max_episode_length_s = float(_get(cfg, "max_episode_length_s"))
+        # body index sets (base_task.py:172-184, motion_tracking.py:203-211)
+        s.feet_ids = [i for i, n in enumerate(s.body_names) if _get(robot, "foot_name") in n]
+        pen = []
+        for name in _get(robot, "penalize_contacts_on", []) or []:
+            pen.extend(i for i, n in enumerate(s.body_names) if name in n)
+        s.penalised_ids = pen
+        s.vr3_ids = [s.body_list.index(n) for n in _get(robot, "motion.motion_tracking_link", [])]
+        s.lower_ids = [s.body_list.index(n) for n in _get(robot, "motion.lower_body_link", [])]
+        s.upper_ids = [s.body_list.index(n) for n in _get(robot, "motion.upper_body_link", [])]
+        s.default_joint_angles = [float(_get(robot, "init_state.default_joint_angles")[n]) for n in s.dof_names]
+        s.hard_dof_lo = [float(v) for v in _get(robot, "dof_pos_lower_limit_list")]
+        s.hard_dof_hi = [float(v) for v in _get(robot, "dof_pos_upper_limit_list")]
+        s.dof_vel_limit = [float(v) for v in _get(robot, "dof_vel_limit_list")]
+        s.torque_limit = [float(v) for v in _get(robot, "dof_effort_limit_list")]
+        s._from_rewards(cfg, rw)
+        s._from_termination(cfg)
+        s._from_obs(cfg, obs, dr)
+        s.dr = dict(randomize_pd_gain=bool(_get(dr, "randomize_pd_gain", False)), kp_range=list(_get(dr, "kp_range", [1, 1])),
+                    kd_range=list(_get(dr, "kd_range", [1, 1])), randomize_rfi_lim=bool(_get(dr, "randomize_rfi_lim", False)),
+                    rfi_lim_range=list(_get(dr, "rfi_lim_range", [1, 1])), use_rao=bool(_get(dr, "use_rao", False)),
+                    rao_lim=float(_get(dr, "rao_lim", 0.0)), randomize_ctrl_delay=bool(_get(dr, "randomize_ctrl_delay", False)),
+                    ctrl_delay_step_range=list(_get(dr, "ctrl_delay_step_range", [0, 0])))
+        s.noise_to_initial_level = float(_get(cfg, "noise_to_initial_level", 0))
+        s.init_noise_scale = {k: float(v) for k, v in dict(_get(cfg, "init_noise_scale", {}) or {}).items()}
+        s.use_vec_reward = bool(_get(cfg, "use_vec_reward", False))
+        s.clip_observations = float(_get(cfg, "normalization.clip_observations"))
+        return s
+
+    # ---- rewards (legged_robot_base.py:167-233) --------------------------------------------------------
+    def _from_rewards(self, cfg, rw):
+        self.reward_names, self.reward_scales = [], []
+        self.termination_scale = None
+        for name, scale in dict(_get(rw, "reward_scales")).items():
+            if scale == 0:
+                continue
+            scale = scale * self.dt
+            if name == "termination":
+                self.termination_scale = scale
+                continue
+            if name not in REWARD_IDS:
+                raise NotImplementedError(f"reward term '{name}' is not implemented by the B200 tracking step")
+            self.reward_names.append(name)
+            self.reward_scales.append(scale)
+        self.episode_sum_names = [n for n, sc in dict(_get(rw, "reward_scales")).items() if sc != 0]
+        self.only_positive_rewards = bool(_get(rw, "only_positive_rewards", False))
+        pen_names = set(_get(rw, "reward_penalty_reward_names", []) or [])
+        self.penalty_curriculum = bool(_get(rw, "reward_penalty_curriculum", False))
+        self.reward_is_penalty = [bool(self.penalty_curriculum and n in pen_names) for n in self.reward_names]
+        self.penalty = dict(initial=float(_get(rw, "reward_initial_penalty_scale", 1.0)), lo=float(_get(rw, "reward_min_penalty_scale", 0.0)),
+                            hi=float(_get(rw, "reward_max_penalty_scale", 1.0)), down=float(_get(rw, "reward_penalty_level_down_threshold", 0)),
+                            up=float(_get(rw, "reward_penalty_level_up_threshold", 0)), degree=float(_get(rw, "reward_penalty_degree", 0)))
+        self.num_compute_average_epl = float(_get(rw, "num_compute_average_epl"))
+        self.sigma0 = {k: float(v) for k, v in dict(_get(rw, "reward_tracking_sigma", {}) or {}).items()}
+        ad = _get(rw, "adaptive_tracking_sigma")
+        self.adaptive = dict(enable=bool(_get(ad, "enable", False)), alpha=float(_get(ad, "alpha", 0.0)),
+                             scale=float(_get(ad, "scale", 1.0)), type=str(_get(ad, "type", "origin")))
+        self.w_lower = float(_get(rw, "teleop_body_pos_lowerbody_weight", 1.0))
+        self.w_upper = float(_get(rw, "teleop_body_pos_upperbody_weight", 1.0))
+        self.desired_feet_air_time = float(_get(rw, "desired_feet_air_time", 0.0))
+        self.max_contact_force = float(_get(rw, "locomotion_max_contact_force", 0.0))
+        lim = _get(rw, "reward_limit")
+        cur = _get(lim, "reward_limits_curriculum")
+        self.soft_dof_pos_limit = float(_get(lim, "soft_dof_pos_limit"))
+        self.soft_dof_vel_limit = float(_get(lim, "soft_dof_vel_limit"))
+        self.soft_torque_limit = float(_get(lim, "soft_torque_limit"))
+        self.limit_cur = {}
+        for k in ("dof_pos", "dof_vel", "torque"):
+            self.limit_cur[k] = dict(enable=bool(_get(cur, f"soft_{k}_curriculum", False)),
+                                     initial=float(_get(cur, f"soft_{k}_initial_limit", 1.0)), lo=float(_get(cur, f"soft_{k}_min_limit", 0)),
+                                     hi=float(_get(cur, f"soft_{k}_max_limit", 1)), degree=float(_get(cur, f"soft_{k}_curriculum_degree", 0)),
+                                     down=float(_get(cur, f"soft_{k}_curriculum_level_down_threshold", 0)),
+                                     up=float(_get(cur, f"soft_{k}_curriculum_level_up_threshold", 0)))
+
+    # ---- termination (legged_robot_base.py:408-489, motion_tracking.py:330-358) -------------------------
+    def _from_termination(self, cfg):
+        t = _get(cfg, "termination")
+        unsupported = ["terminate_by_contact", "terminate_by_low_height", "terminate_when_dof_far",
+                       "terminate_when_close_to_dof_pos_limit", "terminate_when_close_to_dof_vel_limit",
+                       "terminate_when_close_to_torque_limit"]
+        for k in unsupported:
+            if _get(t, k, False):
+                raise NotImplementedError(f"termination '{k}' is not implemented by the B200 tracking step")
+        self.term_gravity = bool(_get(t, "terminate_by_gravity", False))
+        self.term_motion_far = bool(_get(t, "terminate_when_motion_far", False))
+        self.term_motion_end = bool(_get(t, "terminate_when_motion_end", False))
+        self.term_gravity_thr = float(_get(cfg, "termination_scales.termination_gravity", 0.0))
+        tc = _get(cfg, "termination_curriculum")
+        self.far_cur = dict(enable=bool(self.term_motion_far and _get(tc, "terminate_when_motion_far_curriculum", False)),
+                            initial=float(_get(tc, "terminate_when_motion_far_initial_threshold", 0)),
+                            hi=float(_get(tc, "terminate_when_motion_far_threshold_max", 0)),
+                            lo=float(_get(tc, "terminate_when_motion_far_threshold_min", 0)),
+                            degree=float(_get(tc, "terminate_when_motion_far_curriculum_degree", 0)),
+                            down=float(_get(tc, "terminate_when_motion_far_curriculum_level_down_threshold", 0)),
+                            up=float(_get(tc, "terminate_when_motion_far_curriculum_level_up_threshold", 0)))
+        self.motion_far_threshold0 = (self.far_cur["initial"] if self.far_cur["enable"]
+                                      else float(_get(cfg, "termination_scales.termination_motion_far_threshold", 0)))
+
+    # ---- observations + history (legged_robot_base.py:763-793, helpers.py:128-152, history_handler.py) ---
+    def _from_obs(self, cfg, obs, dr):
+        D, J = self.D, self.J
+        self.L = len(_get(dr, "randomize_link_body_names", []) or [])
+        self.obs_scales = {k: float(v) for k, v in dict(_get(obs, "obs_scales")).items()}
+        self.noise_scales = {k: float(v) for k, v in dict(_get(obs, "noise_scales")).items()}
+        aux = {a: dict(c) for a, c in dict(_get(obs, "obs_auxiliary", {}) or {}).items()}
+        self.obs_aux = aux
+        self.hist_len = {}
+        for a, c in aux.items():  # history_handler.py:18-24 (insertion order of first appearance)
+            for k, n in c.items():
+                self.hist_len[k] = max(self.hist_len.get(k, 0), int(n))
+        self.hist_keys = list(self.hist_len.keys())
+        self.hist_dim = {k: obs_src_dim(k, D, J, self.L) for k in self.hist_keys}
+        self.obs_groups = {}
+        for g, keys in dict(_get(obs, "obs_dict")).items():
+            segs, off = [], 0
+            for key in sorted(keys):
+                if key.endswith("_raw"):
+                    raise NotImplementedError("'_raw' observation keys are not implemented by the B200 tracking step")
+                if key in aux:
+                    for hk in sorted(aux[key].keys()):
+                        n = int(aux[key][hk]) * self.hist_dim[hk]
+                        segs.append(dict(kind="hist", key=hk, len=int(aux[key][hk]), dim=self.hist_dim[hk], off=off,
+                                         scale=self.obs_scales[key]))
+                        off += n
+                else:
+                    n = obs_src_dim(key, D, J, self.L)
+                    segs.append(dict(kind="src", key=key, dim=n, off=off, scale=self.obs_scales[key],
+                                     noise=self.noise_scales[key]))
+                    off += n
+            self.obs_groups[g] = dict(segs=segs, dim=off)
+        self.add_noise_curriculum = bool(_get(obs, "add_noise_currculum", False))
+        if self.add_noise_curriculum:
+            raise NotImplementedError("observation-noise curriculum is not implemented by the B200 tracking step")

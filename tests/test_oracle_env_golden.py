@@ -1,0 +1,64 @@
+"""Pins oracle/pbhc_oracle_env.py (the CPU restatement of the motion_tracking env step) against golden
+fixtures produced by the UNMODIFIED reference env (tools/make_golden_env_step.py).  CPU only."""
+import json
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import pbhc_oracle as O, pbhc_oracle_env as OE
+from pbhc_b200.spec import TrackSpec
+from tests._util import gold, oracle_clip
+
+INJECT = ("motion_start_times", "kp_scale", "kd_scale", "rfi_lim_scale", "rao_scale", "action_delay_idx")
+SCALARS = ("average_episode_length", "reward_penalty_scale", "motion_far_threshold", "soft_dof_pos", "soft_dof_vel", "soft_torque")
+
+
+def load_case(name):
+    g = gold(f"ref_env_{name}.npz")
+    spec = TrackSpec.from_config(json.loads(str(g["meta_config_json"])))
+    N = int(g["meta_n_envs"])
+    tab = O.MotionTable([oracle_clip("23", "Horse-stance_pose")], spec.Jb, motion_to_clip=[0] * N)
+    return g, spec, N, tab
+
+
+def state_from(g, prefix, spec):
+    S = {}
+    for k in g:
+        if k.startswith(prefix):
+            v = g[k]
+            S[k[len(prefix):]] = torch.from_numpy(v) if v.ndim else float(v)
+    for k in ("dof_state", "root_state"):
+        S.pop(k, None)
+    return S
+
+
+@pytest.mark.parametrize("case", ["mt23_main", "mt23_bench"])
+def test_env_step_oracle_matches_reference(case):
+    g, spec, N, tab = load_case(case)
+    S = state_from(g, "init_", spec)
+    for step in range(int(g["meta_n_steps"])):
+        p = f"s{step}_"
+        inp = {k: torch.from_numpy(g[p + "in_" + k].copy()) for k in
+               ("body_state", "root_state", "dof_state", "contact_forces", "actions", "torques")}
+        inject = {k: torch.from_numpy(g[p + "out_" + k]) for k in INJECT}
+        obs, log, extras = OE.step(spec, tab, S, inp, inject)
+        for gname, v in obs.items():
+            assert np.array_equal(v.numpy(), g[p + "obs_" + gname]), (step, gname)
+        for k in g:
+            if not k.startswith(p + "out_"):
+                continue
+            name = k[len(p) + 4:]
+            if name == "dof_state":
+                assert np.array_equal(inp["dof_state"].reshape(-1, 2).numpy(), g[k]), (step, name)
+            elif name == "root_state":
+                assert np.array_equal(inp["root_state"].numpy(), g[k]), (step, name)
+            elif name in SCALARS or name.startswith("sigma_") or name.startswith("ema_"):
+                assert float(S[name]) == float(g[k]), (step, name, float(S[name]), float(g[k]))
+            else:
+                mine = S[name].numpy() if name != "last_contacts" else S[name].float().numpy()
+                assert np.array_equal(mine.astype(g[k].dtype), g[k]), (step, name)
+        for k, v in log.items():
+            assert np.float64(np.float32(float(v))) == np.float64(np.float32(g[p + "log_" + k])), (step, k, float(v), float(g[p + "log_" + k]))
+        assert np.array_equal(extras["ref_body_pos_extend"].numpy(), g[p + "extras_ref_body_pos_extend"])
+        assert np.array_equal(extras["ref_body_rot_extend"].numpy(), g[p + "extras_ref_body_rot_extend"])

@@ -50,6 +50,11 @@ def run_case(name, n_envs, n_steps, obs, seed, overrides=None):
     ov = {"domain_rand.push_robots": False}
     ov.update(overrides or {})
     cfg = E.build_config(n_envs, R.example_motion("Horse-stance_pose"), obs=obs, overrides=ov)
+    import copy, json
+    cj = copy.deepcopy(cfg)  # before the env mutates it (reward_scales *= dt, adaptive sigmas)
+    cj["robot"]["motion"]["motion_file"] = "Horse-stance_pose"
+    cj["robot"]["motion"]["asset"]["assetRoot"] = "description/robots/g1/"
+    cfg_json = json.dumps(cj)
     env, ns = E.make_env(cfg, seed=seed)
     sim = env.simulator
     gen = torch.Generator().manual_seed(seed)
@@ -65,7 +70,7 @@ def run_case(name, n_envs, n_steps, obs, seed, overrides=None):
     sim.friction_coeffs[:] = 0.2 + torch.rand(N, 1, 1, generator=gen)
     env._kp_scale[:] = 0.9 + 0.2 * torch.rand(N, D, generator=gen)
     env._kd_scale[:] = 0.9 + 0.2 * torch.rand(N, D, generator=gen)
-    out = {"meta_n_envs": N, "meta_n_steps": n_steps, "meta_obs": obs, "meta_dt": env.dt,
+    out = {"meta_config_json": cfg_json, "meta_n_envs": N, "meta_n_steps": n_steps, "meta_obs": obs, "meta_dt": env.dt,
            "meta_reward_names": np.array(env.reward_names), "meta_reward_scales": np.array([env.reward_scales[k] for k in env.reward_names]),
            "meta_termination_scale": np.float64(env.reward_scales["termination"]),
            "meta_history_keys": np.array(list(env.history_handler.history.keys()))}
