@@ -115,6 +115,164 @@ int pbhc_clip_prepare(const float* pos, const float* quat, const float* pose_aa,
                       const double* gauss_weights_host, int32_t radius, float* scratch,
                       float* records, int32_t rec_stride, void* stream);
 
+/* ---- K3: fused motion-tracking env step (lookup + diffs + termination + rewards + reset + observations +
+ * history), i.e. everything LeggedRobotBase._post_physics_step does between refresh_sim_tensors and
+ * extras["to_log"] for LeggedRobotMotionTracking (envs/legged_base_task/legged_robot_base.py:297-338,
+ * envs/motion_tracking/motion_tracking.py:330-358, 548-747, 1030-1328; utils/helpers.py:128-152;
+ * envs/env_utils/history_handler.py:33-48).  One launch per step, no host synchronisation: scalars the
+ * reference keeps on the host (adaptive sigmas, curricula, average episode length) live in `scalars`
+ * (device doubles) and are advanced by pbhc_track_finalize from per-step reductions. */
+#define PBHC_MAX_DOF 32
+#define PBHC_MAX_REWARDS 32
+#define PBHC_MAX_EXT 4
+#define PBHC_MAX_FEET 4
+#define PBHC_MAX_OBS_GROUPS 4
+#define PBHC_MAX_HIST_KEYS 8
+#define PBHC_NUM_OBS_SRC 20
+#define PBHC_NUM_SIGMA 10
+#define PBHC_ENVF_STRIDE 8   /* env_f32 row: start_time, motion_len, air_time[2], last_contact[2], end_time_ratio, pad */
+
+/* layout of `scalars` (device double[PBHC_SCALARS]) */
+#define PBHC_S_SIGMA 0        /* [10] reward_tracking_sigma, enum order of pbhc_b200/spec.py SIGMA_IDS */
+#define PBHC_S_EMA 10         /* [10] _reward_error_ema */
+#define PBHC_S_AVG_EPL 20     /* average_episode_length (an fp32 value) */
+#define PBHC_S_PENALTY 21     /* reward_penalty_scale */
+#define PBHC_S_FAR_THR 22     /* terminate_when_motion_far_threshold */
+#define PBHC_S_SOFT_DOF_POS 23
+#define PBHC_S_SOFT_DOF_VEL 24
+#define PBHC_S_SOFT_TORQUE 25
+#define PBHC_S_PUSH_COUNT 26  /* history pushes so far (ring-buffer head = -count mod H) */
+#define PBHC_S_LOG 32         /* [32] log_dict values of the last step, see PBHC_L_* */
+#define PBHC_SCALARS 64
+/* layout of `acc` (device double[PBHC_ACC]): per-step sums over envs; all-reduce across ranks before finalize */
+#define PBHC_A_SIGMA_ERR 0    /* [10] sum over envs of each adaptive-sigma error term */
+#define PBHC_A_UPPER_NORM 10  /* sum of |dif_pos| over upper bodies and envs (then lower, vr3, joint) */
+#define PBHC_A_LOWER_NORM 11
+#define PBHC_A_VR3_NORM 12
+#define PBHC_A_JOINT_NORM 13
+#define PBHC_A_TERM_GRAVITY 14
+#define PBHC_A_TERM_FAR 15
+#define PBHC_A_TERM_TIMEOUT 16
+#define PBHC_A_TERM_MOTION_END 17
+#define PBHC_A_RESET 18       /* number of envs reset this step */
+#define PBHC_A_RESET_EPLEN 19 /* sum of their episode lengths */
+#define PBHC_A_ETR_SUM 20     /* sum / sum of squares of end_time_ratio_buf over all envs */
+#define PBHC_A_ETR_SQ 21
+#define PBHC_A_NUM_ENVS 22
+#define PBHC_ACC 32
+#define PBHC_L_UPPER 0
+#define PBHC_L_LOWER 1
+#define PBHC_L_VR3 2
+#define PBHC_L_JOINT 3
+#define PBHC_L_TERM_GRAVITY 4
+#define PBHC_L_TERM_FAR 5
+#define PBHC_L_TERM_TIMEOUT 6
+#define PBHC_L_TERM_MOTION_END 7
+#define PBHC_L_ETR_MEAN 8
+#define PBHC_L_ETR_STD 9
+#define PBHC_L_FAR_THR 10     /* values logged BEFORE this step's curriculum update, like the reference */
+#define PBHC_L_PENALTY 11
+#define PBHC_L_AVG_EPL 12
+#define PBHC_L_SOFT_DOF_POS 13
+#define PBHC_L_SOFT_DOF_VEL 14
+#define PBHC_L_SOFT_TORQUE 15
+
+typedef struct { int32_t enable; double lo, hi, degree, down, up; } PbhcCurriculum;
+
+typedef struct {
+  int32_t J, Jb, D, L, n_ext, n_feet;
+  int32_t ext_parent[PBHC_MAX_EXT];
+  float ext_pos[PBHC_MAX_EXT][3];
+  float ext_rot_xyzw[PBHC_MAX_EXT][4];
+  int32_t feet_ids[PBHC_MAX_FEET];
+  uint64_t upper_mask, lower_mask, vr3_mask, penalised_mask; /* bit j = body j of the extended list */
+  float dt;
+  int64_t max_episode_length;
+  /* rewards (ids: pbhc_b200/spec.py REWARD_IDS) */
+  int32_t n_rewards, use_vec_reward, only_positive_rewards, has_termination;
+  int32_t reward_id[PBHC_MAX_REWARDS];
+  float reward_scale[PBHC_MAX_REWARDS];
+  int32_t reward_is_penalty[PBHC_MAX_REWARDS];
+  float termination_scale;
+  float w_lower, w_upper, desired_feet_air_time, max_contact_force;
+  float hard_lo[PBHC_MAX_DOF], hard_hi[PBHC_MAX_DOF], soft_lo[PBHC_MAX_DOF], soft_hi[PBHC_MAX_DOF];
+  float vel_limit[PBHC_MAX_DOF], torque_limit[PBHC_MAX_DOF];
+  float soft_dof_vel_limit, soft_torque_limit;
+  /* termination */
+  int32_t term_gravity, term_motion_far, term_motion_end;
+  float term_gravity_thr;
+  /* adaptive sigma: type 0 = origin, 1 = mean, 2 = scale */
+  int32_t adaptive_enable, adaptive_type;
+  double adaptive_alpha, adaptive_scale;
+  PbhcCurriculum cur_penalty, cur_far, cur_dof_pos, cur_dof_vel, cur_torque;
+  double num_compute_average_epl;
+  /* observations: feature vector = the PBHC_NUM_OBS_SRC sources (scaled) followed by the history in logical
+   * (newest-first) order; each obs group is a gather `obs[i] = clip(feat[map[i]] * mul[i])` */
+  int32_t n_groups;
+  int32_t group_dim[PBHC_MAX_OBS_GROUPS];
+  const int32_t* group_map[PBHC_MAX_OBS_GROUPS]; /* device */
+  const float* group_mul[PBHC_MAX_OBS_GROUPS];   /* device */
+  float obs_scale[PBHC_NUM_OBS_SRC], obs_noise[PBHC_NUM_OBS_SRC];
+  float clip_obs;
+  int32_t n_hist_keys, hist_row; /* hist_row = sum_k len_k*dim_k floats per env */
+  int32_t hist_src[PBHC_MAX_HIST_KEYS], hist_len[PBHC_MAX_HIST_KEYS], hist_dim[PBHC_MAX_HIST_KEYS];
+  /* episodic domain randomisation at reset (legged_robot_base.py:599-635) when values are not injected */
+  int32_t randomize_pd_gain, randomize_rfi_lim, use_rao, randomize_ctrl_delay, delay_lo, delay_hi;
+  float kp_lo, kp_hi, kd_lo, kd_hi, rfi_lo, rfi_hi, rao_lim;
+  uint64_t seed;
+  float reset_noise[6];   /* dof_pos, dof_vel, root_pos, root_rot [rad], root_vel, root_ang_vel; 0 = reference default */
+  uint32_t src_used_mask; /* bit k: observation source k is referenced by a group or a history key */
+  int32_t n_upper, n_lower, n_vr3; /* popcounts of the masks (log means) */
+  int32_t n_episode_sums; /* n_rewards (+1 with termination): row width of episode_sums */
+} PbhcTrackCfg;
+
+typedef struct {
+  /* simulator state (borrowed; dof_state / root_state / actions are WRITTEN for envs that reset) */
+  const float* body_state; int64_t body_env_stride; /* [N, >=Jb, 13], floats between envs */
+  float* root_state;            /* [N,13] */
+  float* dof_state;             /* [N,D,2] */
+  const float* contact_forces;  /* [N,Jb,3] */
+  float* actions;               /* [N,D] clipped actions of this step */
+  const float* torques;         /* [N,D] */
+  const float* env_origins;     /* [N,3] */
+  const int64_t* motion_ids;    /* [N] */
+  const int32_t* clip_of_motion;/* nullable */
+  const float* default_dof_pos; int64_t default_dof_stride; /* [N,D] (stride D) or [D] (stride 0) */
+  const float* base_com_bias;   /* [N,3] */
+  const float* link_mass_scale; /* [N,L] */
+  const float* friction;        /* [N] */
+  /* persistent env state */
+  int64_t* episode_length_buf;  /* [N] */
+  float* env_f32;               /* [N,PBHC_ENVF_STRIDE] */
+  float* last_actions; float* last_dof_pos; float* last_dof_vel; /* [N,D] */
+  float* kp_scale; float* kd_scale; float* rfi_lim_scale; float* rao_scale; /* [N,D] */
+  int64_t* action_delay_idx;    /* [N] */
+  float* hist;                  /* [N,hist_row] ring buffers, key-major */
+  float* episode_sums;          /* [N,n_episode_sums] */
+  double* scalars;              /* [PBHC_SCALARS] */
+  /* outputs */
+  float* obs[PBHC_MAX_OBS_GROUPS]; /* [N,group_dim] */
+  float* rew_buf;               /* [N,n_rewards+1] (vec) or [N] */
+  int64_t* reset_buf;           /* [N] */
+  uint8_t* time_out_buf;        /* [N] */
+  float* ref_body_pos_extend;   /* [N,J,3] nullable */
+  float* ref_body_rot_extend;   /* [N,J,4] nullable */
+  float* last_episode_sums;     /* [N,n_episode_sums]: episode sums of envs reset this step (rows of others untouched) */
+  double* partials;             /* [max_blocks,PBHC_ACC] scratch */
+  double* acc;                  /* [PBHC_ACC] */
+  /* values the reference draws with torch RNG at resets; NULL = in-kernel Philox */
+  const float* inject_start_times; const float* inject_kp; const float* inject_kd; const float* inject_rfi;
+  const float* inject_rao; const int64_t* inject_delay;
+} PbhcTrackIO;
+
+/* number of rows `partials` must have */
+int pbhc_track_max_blocks(void);
+/* main kernel + deterministic reduction of the per-block partial sums into io->acc */
+int pbhc_track_step(const PbhcTrackCfg* cfg, const PbhcTableDesc* tab, const PbhcTrackIO* io, int64_t n_envs, void* stream);
+/* advances `scalars` from `acc` (adaptive sigma, average episode length, curricula, log values);
+ * call after pbhc_track_step (and after all-reducing acc when envs are sharded over ranks) */
+int pbhc_track_finalize(const PbhcTrackCfg* cfg, const double* acc, double* scalars, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

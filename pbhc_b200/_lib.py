@@ -39,7 +39,8 @@ class Tree(C.Structure):
 
 _lib = None
 
-EXPORTS = ["pbhc_abi_version", "pbhc_last_error", "pbhc_lookup", "pbhc_fk", "pbhc_gae", "pbhc_adv_normalize", "pbhc_clip_prepare"]
+EXPORTS = ["pbhc_abi_version", "pbhc_last_error", "pbhc_lookup", "pbhc_fk", "pbhc_gae", "pbhc_adv_normalize", "pbhc_clip_prepare",
+           "pbhc_track_max_blocks", "pbhc_track_step", "pbhc_track_finalize"]
 
 
 def lib():
@@ -66,6 +67,7 @@ def lib():
     L.pbhc_clip_prepare.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32,
                                     C.c_int32, C.c_int32, C.c_float, C.POINTER(C.c_double), C.c_int32, C.c_void_p,
                                     C.c_void_p, C.c_int32, C.c_void_p]
+    bind_track(L)
     if L.pbhc_abi_version() != 1:
         raise PbhcError("ABI version mismatch")
     _lib = L
@@ -92,3 +94,73 @@ def ptr(t, dtype=None):
 
 def stream_ptr(device=None):
     return torch.cuda.current_stream(device).cuda_stream
+
+
+# ---- K3 structs (mirror include/pbhc_b200.h exactly) ------------------------------------------------
+MAX_DOF, MAX_REWARDS, MAX_EXT, MAX_FEET, MAX_OBS_GROUPS, MAX_HIST_KEYS = 32, 32, 4, 4, 4, 8
+NUM_OBS_SRC, NUM_SIGMA, ENVF_STRIDE, SCALARS, ACC = 20, 10, 8, 64, 32
+S_SIGMA, S_EMA, S_AVG_EPL, S_PENALTY, S_FAR_THR, S_SOFT_DOF_POS, S_SOFT_DOF_VEL, S_SOFT_TORQUE, S_PUSH_COUNT, S_LOG = 0, 10, 20, 21, 22, 23, 24, 25, 26, 32
+LOG_NAMES = ["upper_body_diff_norm", "lower_body_diff_norm", "vr_3point_diff_norm", "joint_pos_diff_norm",
+             "terminate_by_gravity", "terminate_by_motion_far", "terminate_by_time_out", "terminate_by_motion_end",
+             "end_time_ratio", "end_time_ratio_std", "terminate_when_motion_far_threshold", "penalty_scale",
+             "average_episode_length", "soft_dof_pos_curriculum_value", "soft_dof_vel_curriculum_value",
+             "soft_torque_curriculum_value"]
+
+
+class Curriculum(C.Structure):
+    _fields_ = [("enable", C.c_int32), ("lo", C.c_double), ("hi", C.c_double), ("degree", C.c_double),
+                ("down", C.c_double), ("up", C.c_double)]
+
+
+class TrackCfg(C.Structure):
+    _fields_ = [
+        ("J", C.c_int32), ("Jb", C.c_int32), ("D", C.c_int32), ("L", C.c_int32), ("n_ext", C.c_int32), ("n_feet", C.c_int32),
+        ("ext_parent", C.c_int32 * MAX_EXT), ("ext_pos", (C.c_float * 3) * MAX_EXT), ("ext_rot_xyzw", (C.c_float * 4) * MAX_EXT),
+        ("feet_ids", C.c_int32 * MAX_FEET),
+        ("upper_mask", C.c_uint64), ("lower_mask", C.c_uint64), ("vr3_mask", C.c_uint64), ("penalised_mask", C.c_uint64),
+        ("dt", C.c_float), ("max_episode_length", C.c_int64),
+        ("n_rewards", C.c_int32), ("use_vec_reward", C.c_int32), ("only_positive_rewards", C.c_int32), ("has_termination", C.c_int32),
+        ("reward_id", C.c_int32 * MAX_REWARDS), ("reward_scale", C.c_float * MAX_REWARDS), ("reward_is_penalty", C.c_int32 * MAX_REWARDS),
+        ("termination_scale", C.c_float),
+        ("w_lower", C.c_float), ("w_upper", C.c_float), ("desired_feet_air_time", C.c_float), ("max_contact_force", C.c_float),
+        ("hard_lo", C.c_float * MAX_DOF), ("hard_hi", C.c_float * MAX_DOF), ("soft_lo", C.c_float * MAX_DOF), ("soft_hi", C.c_float * MAX_DOF),
+        ("vel_limit", C.c_float * MAX_DOF), ("torque_limit", C.c_float * MAX_DOF),
+        ("soft_dof_vel_limit", C.c_float), ("soft_torque_limit", C.c_float),
+        ("term_gravity", C.c_int32), ("term_motion_far", C.c_int32), ("term_motion_end", C.c_int32), ("term_gravity_thr", C.c_float),
+        ("adaptive_enable", C.c_int32), ("adaptive_type", C.c_int32), ("adaptive_alpha", C.c_double), ("adaptive_scale", C.c_double),
+        ("cur_penalty", Curriculum), ("cur_far", Curriculum), ("cur_dof_pos", Curriculum), ("cur_dof_vel", Curriculum), ("cur_torque", Curriculum),
+        ("num_compute_average_epl", C.c_double),
+        ("n_groups", C.c_int32), ("group_dim", C.c_int32 * MAX_OBS_GROUPS),
+        ("group_map", C.c_void_p * MAX_OBS_GROUPS), ("group_mul", C.c_void_p * MAX_OBS_GROUPS),
+        ("obs_scale", C.c_float * NUM_OBS_SRC), ("obs_noise", C.c_float * NUM_OBS_SRC), ("clip_obs", C.c_float),
+        ("n_hist_keys", C.c_int32), ("hist_row", C.c_int32),
+        ("hist_src", C.c_int32 * MAX_HIST_KEYS), ("hist_len", C.c_int32 * MAX_HIST_KEYS), ("hist_dim", C.c_int32 * MAX_HIST_KEYS),
+        ("randomize_pd_gain", C.c_int32), ("randomize_rfi_lim", C.c_int32), ("use_rao", C.c_int32), ("randomize_ctrl_delay", C.c_int32),
+        ("delay_lo", C.c_int32), ("delay_hi", C.c_int32),
+        ("kp_lo", C.c_float), ("kp_hi", C.c_float), ("kd_lo", C.c_float), ("kd_hi", C.c_float), ("rfi_lo", C.c_float), ("rfi_hi", C.c_float),
+        ("rao_lim", C.c_float),
+        ("seed", C.c_uint64), ("reset_noise", C.c_float * 6), ("src_used_mask", C.c_uint32),
+        ("n_upper", C.c_int32), ("n_lower", C.c_int32), ("n_vr3", C.c_int32), ("n_episode_sums", C.c_int32)]
+
+
+TRACK_IO_FIELDS = [
+    "body_state", "body_env_stride", "root_state", "dof_state", "contact_forces", "actions", "torques", "env_origins",
+    "motion_ids", "clip_of_motion", "default_dof_pos", "default_dof_stride", "base_com_bias", "link_mass_scale", "friction",
+    "episode_length_buf", "env_f32", "last_actions", "last_dof_pos", "last_dof_vel", "kp_scale", "kd_scale",
+    "rfi_lim_scale", "rao_scale", "action_delay_idx", "hist", "episode_sums", "scalars"]
+
+
+class TrackIO(C.Structure):
+    _fields_ = ([(k, C.c_int64 if k.endswith("_stride") else C.c_void_p) for k in TRACK_IO_FIELDS]
+                + [("obs", C.c_void_p * MAX_OBS_GROUPS)]
+                + [(k, C.c_void_p) for k in ("rew_buf", "reset_buf", "time_out_buf", "ref_body_pos_extend", "ref_body_rot_extend",
+                                             "last_episode_sums", "partials", "acc", "inject_start_times", "inject_kp",
+                                             "inject_kd", "inject_rfi", "inject_rao", "inject_delay")])
+
+
+def bind_track(L):
+    L.pbhc_track_max_blocks.restype = C.c_int
+    L.pbhc_track_step.restype = C.c_int
+    L.pbhc_track_step.argtypes = [C.POINTER(TrackCfg), C.POINTER(TableDesc), C.POINTER(TrackIO), C.c_int64, C.c_void_p]
+    L.pbhc_track_finalize.restype = C.c_int
+    L.pbhc_track_finalize.argtypes = [C.POINTER(TrackCfg), C.c_void_p, C.c_void_p, C.c_void_p]

@@ -4,6 +4,7 @@
 // scattered into the reference's output dict layout.
 // Reference: utils/motion_lib/motion_lib_base.py:123-259, 503-513; isaac_utils/rotations.py:210-232.
 #include "common.cuh"
+#include "table.cuh"
 
 namespace pbhc {
 
@@ -16,29 +17,6 @@ struct LookupParams {
   const float* offset;
   int64_t n;
 };
-
-struct FrameBlend { int64_t f0, f1; float blend; };
-
-// motion_lib_base.py:503-513 with torch's promotions: (num_frames-1) and idx0 are int64 -> fp32
-__device__ __forceinline__ FrameBlend frame_blend(const PbhcTableDesc& tab, int clip, float time) {
-  int nf = tab.clip_num_frames[clip];
-  float len = tab.clip_length[clip];
-  float dt = tab.clip_dt[clip];
-  float phase = clip01(time / len);
-  if (time < 0.0f) time = 0.0f;
-  int64_t idx0 = (int64_t)(phase * (float)(nf - 1));
-  int64_t idx1 = min(idx0 + 1, (int64_t)(nf - 1));
-  float blend = clip01((time - (float)idx0 * dt) / dt);
-  int64_t start = tab.clip_frame_start[clip];
-  return {idx0 + start, idx1 + start, blend};
-}
-
-__device__ __forceinline__ int resolve_clip(const PbhcTableDesc& tab, const int32_t* clip_of_motion, int64_t mid) {
-  int64_t c = clip_of_motion ? (int64_t)clip_of_motion[mid] : mid;
-  if (c < 0) c = 0;
-  if (c >= tab.num_clips) c = tab.num_clips - 1;
-  return (int)c;
-}
 
 __device__ __forceinline__ void emit3(float* ext, float* base, float* root, int64_t q, int J, int Jb, int idx, float v) {
   if (ext) ext[q * (3 * J) + idx] = v;
