@@ -142,8 +142,8 @@ int pbhc_clip_prepare(const float* pos, const float* quat, const float* pose_aa,
 #define PBHC_S_SOFT_DOF_VEL 24
 #define PBHC_S_SOFT_TORQUE 25
 #define PBHC_S_PUSH_COUNT 26  /* history pushes so far (ring-buffer head = -count mod H) */
-#define PBHC_S_LOG 32         /* [32] log_dict values of the last step, see PBHC_L_* */
-#define PBHC_SCALARS 64
+#define PBHC_S_LOG 32         /* [48] log_dict values of the last step, see PBHC_L_* */
+#define PBHC_SCALARS 96
 /* layout of `acc` (device double[PBHC_ACC]): per-step sums over envs; all-reduce across ranks before finalize */
 #define PBHC_A_SIGMA_ERR 0    /* [10] sum over envs of each adaptive-sigma error term */
 #define PBHC_A_UPPER_NORM 10  /* sum of |dif_pos| over upper bodies and envs (then lower, vr3, joint) */
@@ -176,6 +176,8 @@ int pbhc_clip_prepare(const float* pos, const float* quat, const float* pose_aa,
 #define PBHC_L_SOFT_DOF_POS 13
 #define PBHC_L_SOFT_DOF_VEL 14
 #define PBHC_L_SOFT_TORQUE 15
+#define PBHC_L_ADP_SIGMA 16    /* [10] sigma / [10] ema as logged by _log_motion_tracking_info: BEFORE this step's update */
+#define PBHC_L_ERROR_EMA 26
 
 typedef struct { int32_t enable; double lo, hi, degree, down, up; } PbhcCurriculum;
 

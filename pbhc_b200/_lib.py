@@ -98,7 +98,8 @@ def stream_ptr(device=None):
 
 # ---- K3 structs (mirror include/pbhc_b200.h exactly) ------------------------------------------------
 MAX_DOF, MAX_REWARDS, MAX_EXT, MAX_FEET, MAX_OBS_GROUPS, MAX_HIST_KEYS = 32, 32, 4, 4, 4, 8
-NUM_OBS_SRC, NUM_SIGMA, ENVF_STRIDE, SCALARS, ACC = 20, 10, 8, 64, 32
+NUM_OBS_SRC, NUM_SIGMA, ENVF_STRIDE, SCALARS, ACC = 20, 10, 8, 96, 32
+L_ADP_SIGMA, L_ERROR_EMA = 16, 26
 S_SIGMA, S_EMA, S_AVG_EPL, S_PENALTY, S_FAR_THR, S_SOFT_DOF_POS, S_SOFT_DOF_VEL, S_SOFT_TORQUE, S_PUSH_COUNT, S_LOG = 0, 10, 20, 21, 22, 23, 24, 25, 26, 32
 LOG_NAMES = ["upper_body_diff_norm", "lower_body_diff_norm", "vr_3point_diff_norm", "joint_pos_diff_norm",
              "terminate_by_gravity", "terminate_by_motion_far", "terminate_by_time_out", "terminate_by_motion_end",

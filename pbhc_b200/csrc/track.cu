@@ -552,6 +552,7 @@ __global__ void track_finalize_kernel(const __grid_constant__ PbhcTrackCfg c, co
   L[PBHC_L_SOFT_DOF_POS] = (double)(float)S[PBHC_S_SOFT_DOF_POS];
   L[PBHC_L_SOFT_DOF_VEL] = (double)(float)S[PBHC_S_SOFT_DOF_VEL];
   L[PBHC_L_SOFT_TORQUE] = (double)(float)S[PBHC_S_SOFT_TORQUE];
+  for (int k = 0; k < PBHC_NUM_SIGMA; ++k) { L[PBHC_L_ADP_SIGMA + k] = S[PBHC_S_SIGMA + k]; L[PBHC_L_ERROR_EMA + k] = S[PBHC_S_EMA + k]; }
   if (c.adaptive_enable) {
     uint32_t active = 0;
     for (int i = 0; i < c.n_rewards; ++i) {

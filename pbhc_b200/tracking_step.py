@@ -116,9 +116,10 @@ class TrackingStep:
     def log_dict(self):
         vals = self.scalars[_lib.S_LOG:_lib.S_LOG + len(_lib.LOG_NAMES)].float()
         d = {n: vals[i] for i, n in enumerate(_lib.LOG_NAMES)}
-        sig = self.scalars[_lib.S_SIGMA:_lib.S_SIGMA + _lib.NUM_SIGMA].float()
-        ema = self.scalars[_lib.S_EMA:_lib.S_EMA + _lib.NUM_SIGMA].float()
-        for name, i in SIGMA_IDS.items():
+        b = _lib.S_LOG
+        sig = self.scalars[b + _lib.L_ADP_SIGMA:b + _lib.L_ADP_SIGMA + _lib.NUM_SIGMA].float()
+        ema = self.scalars[b + _lib.L_ERROR_EMA:b + _lib.L_ERROR_EMA + _lib.NUM_SIGMA].float()
+        for name, i in SIGMA_IDS.items():  # logged before the step's update, like _log_motion_tracking_info
             d["adp_sigma_" + name], d["error_ema_" + name] = sig[i], ema[i]
         return d
 
@@ -126,3 +127,149 @@ class TrackingStep:
         """config.rewards.reward_tracking_sigma as the reference mutates it (synchronises)."""
         sig = self.scalars[_lib.S_SIGMA:_lib.S_SIGMA + _lib.NUM_SIGMA].cpu().tolist()
         return {name: sig[i] for name, i in SIGMA_IDS.items()}
+
+    # ---- PbhcTrackCfg from the spec ---------------------------------------------------------------------
+    def _build_cfg(self, seed):
+        s, dev = self.spec, self.device
+        c = _lib.TrackCfg()
+        c.J, c.Jb, c.D, c.L, c.n_ext, c.n_feet = s.J, s.Jb, s.D, s.L, s.J - s.Jb, len(s.feet_ids)
+        for i, p in enumerate(s.ext_parent):
+            c.ext_parent[i] = p
+            for k in range(3):
+                c.ext_pos[i][k] = s.ext_pos[i][k]
+            w, x, y, z = s.ext_rot_wxyz[i]
+            for k, v in enumerate((x, y, z, w)):
+                c.ext_rot_xyzw[i][k] = v
+        for i, f in enumerate(s.feet_ids):
+            c.feet_ids[i] = f
+        c.upper_mask, c.lower_mask, c.vr3_mask = _mask(s.upper_ids), _mask(s.lower_ids), _mask(s.vr3_ids)
+        c.penalised_mask = _mask(s.penalised_ids)
+        c.n_upper, c.n_lower, c.n_vr3 = len(s.upper_ids), len(s.lower_ids), len(s.vr3_ids)
+        c.dt, c.max_episode_length = s.dt, int(s.max_episode_length)
+        c.n_rewards, c.use_vec_reward = len(s.reward_names), int(s.use_vec_reward)
+        c.only_positive_rewards, c.has_termination = int(s.only_positive_rewards), int(s.termination_scale is not None)
+        for i, n in enumerate(s.reward_names):
+            c.reward_id[i], c.reward_scale[i], c.reward_is_penalty[i] = REWARD_IDS[n], s.reward_scales[i], int(s.reward_is_penalty[i])
+        c.termination_scale = s.termination_scale or 0.0
+        c.w_lower, c.w_upper = s.w_lower, s.w_upper
+        c.desired_feet_air_time, c.max_contact_force = s.desired_feet_air_time, s.max_contact_force
+        # soft limits exactly as the simulator derives them in fp32 (isaacgym.py:373-385)
+        lo, hi = torch.tensor(s.hard_dof_lo), torch.tensor(s.hard_dof_hi)
+        m, r = (lo + hi) / 2, hi - lo
+        slo, shi = m - 0.5 * r * s.soft_dof_pos_limit, m + 0.5 * r * s.soft_dof_pos_limit
+        for d in range(s.D):
+            c.hard_lo[d], c.hard_hi[d], c.soft_lo[d], c.soft_hi[d] = float(lo[d]), float(hi[d]), float(slo[d]), float(shi[d])
+            c.vel_limit[d], c.torque_limit[d] = s.dof_vel_limit[d], s.torque_limit[d]
+        c.soft_dof_vel_limit, c.soft_torque_limit = s.soft_dof_vel_limit, s.soft_torque_limit
+        c.term_gravity, c.term_motion_far, c.term_motion_end = int(s.term_gravity), int(s.term_motion_far), int(s.term_motion_end)
+        c.term_gravity_thr = s.term_gravity_thr
+        a = s.adaptive
+        c.adaptive_enable, c.adaptive_type = int(a["enable"]), {"origin": 0, "mean": 1, "scale": 2}[a["type"]]
+        c.adaptive_alpha, c.adaptive_scale = a["alpha"], a["scale"]
+
+        def cur(d, enable):
+            return _lib.Curriculum(int(enable), d["lo"], d["hi"], d["degree"], d["down"], d["up"])
+        c.cur_penalty = cur(s.penalty, s.penalty_curriculum)
+        c.cur_far = cur(s.far_cur, s.far_cur["enable"])
+        c.cur_dof_pos = cur(s.limit_cur["dof_pos"], s.limit_cur["dof_pos"]["enable"])
+        c.cur_dof_vel = cur(s.limit_cur["dof_vel"], s.limit_cur["dof_vel"]["enable"])
+        c.cur_torque = cur(s.limit_cur["torque"], s.limit_cur["torque"]["enable"])
+        c.num_compute_average_epl = s.num_compute_average_epl
+        # observation gather maps over the feature vector [sources | history (logical order)]
+        src_off, off = {}, 0
+        for k in OBS_SRC:
+            src_off[k] = off
+            off += obs_src_dim(k, s.D, s.J, s.L)
+        hist_off, hbase = off, {}
+        for k, b in zip(s.hist_keys, self._hist_base):
+            hbase[k] = hist_off + b
+        used = 0
+        self._maps = []
+        c.n_groups = len(s.obs_groups)
+        for g, (name, grp) in enumerate(s.obs_groups.items()):
+            idx, mul = [], []
+            for seg in grp["segs"]:
+                if seg["kind"] == "src":
+                    used |= 1 << OBS_SRC_IDS[seg["key"]]
+                    idx += list(range(src_off[seg["key"]], src_off[seg["key"]] + seg["dim"]))
+                    mul += [1.0] * seg["dim"]  # the source scale is folded into the feature
+                    if seg["noise"] != 0:
+                        raise NotImplementedError("observation noise: use noise scale 0 (obs/motion_tracking/benchmark.yaml) for now")
+                else:
+                    n = seg["len"] * seg["dim"]
+                    idx += list(range(hbase[seg["key"]], hbase[seg["key"]] + n))
+                    mul += [seg["scale"]] * n
+            tm = torch.tensor(idx, dtype=torch.int32, device=dev)
+            tf = torch.tensor(mul, dtype=torch.float32, device=dev)
+            self._maps.append((tm, tf))
+            c.group_dim[g], c.group_map[g], c.group_mul[g] = grp["dim"], tm.data_ptr(), tf.data_ptr()
+        for i, k in enumerate(OBS_SRC):
+            c.obs_scale[i] = s.obs_scales.get(k, 1.0)
+            c.obs_noise[i] = 0.0
+        c.clip_obs = s.clip_observations
+        c.n_hist_keys, c.hist_row = len(s.hist_keys), self.hist_row
+        for i, k in enumerate(s.hist_keys):
+            used |= 1 << OBS_SRC_IDS[k]
+            c.hist_src[i], c.hist_len[i], c.hist_dim[i] = OBS_SRC_IDS[k], s.hist_len[k], s.hist_dim[k]
+        c.src_used_mask = used
+        dr = s.dr
+        c.randomize_pd_gain, c.randomize_rfi_lim = int(dr["randomize_pd_gain"]), int(dr["randomize_rfi_lim"])
+        c.use_rao, c.randomize_ctrl_delay = int(dr["use_rao"]), int(dr["randomize_ctrl_delay"])
+        c.delay_lo, c.delay_hi = int(dr["ctrl_delay_step_range"][0]), int(dr["ctrl_delay_step_range"][1])
+        c.kp_lo, c.kp_hi, c.kd_lo, c.kd_hi = dr["kp_range"][0], dr["kp_range"][1], dr["kd_range"][0], dr["kd_range"][1]
+        c.rfi_lo, c.rfi_hi, c.rao_lim = dr["rfi_lim_range"][0], dr["rfi_lim_range"][1], dr["rao_lim"]
+        c.seed = int(seed)
+        lvl, ns = s.noise_to_initial_level, s.init_noise_scale
+        vals = [ns.get("dof_pos", 0) * lvl, ns.get("dof_vel", 0) * lvl, ns.get("root_pos", 0) * lvl,
+                ns.get("root_rot", 0) * 3.14 / 180 * lvl, ns.get("root_vel", 0) * lvl, ns.get("root_ang_vel", 0) * lvl]
+        for i, v in enumerate(vals):
+            c.reset_noise[i] = v
+        c.n_episode_sums = self.n_sums
+        self._cfg = c
+
+    # ---- one env step -----------------------------------------------------------------------------------
+    def step(self, sim, actions, torques, env_origins, motion_ids, inject=None, group=None):
+        """sim: object with Isaac-Gym-layout CUDA tensors (simulator/isaacgym/isaacgym.py:596-618):
+        _rigid_body_state [N*bodies,13] or [N,bodies,13], all_root_states [N,13], dof_state [N*D,2],
+        contact_forces [N,Jb,3], _base_com_bias [N,3], _link_mass_scale [N,L], friction_coeffs [N,1,1].
+        actions [N,D] (zeroed in place for envs that reset) and torques [N,D] are this step's clipped actions /
+        last applied torques.  Returns (obs_buf_dict, rew_buf, reset_buf, extras) like LeggedRobotBase.step."""
+        io, p, s = self._io, _lib.ptr, self.spec
+        body = sim._rigid_body_state
+        io.body_state, io.body_env_stride = p(body, torch.float32), body.numel() // self.N
+        io.root_state, io.dof_state = p(sim.all_root_states, torch.float32), p(sim.dof_state, torch.float32)
+        io.contact_forces = p(sim.contact_forces, torch.float32)
+        io.actions, io.torques = p(actions, torch.float32), p(torques, torch.float32)
+        io.env_origins, io.motion_ids = p(env_origins, torch.float32), p(motion_ids, torch.int64)
+        io.clip_of_motion = self.lib._clip_of_motion.data_ptr()
+        io.default_dof_pos, io.default_dof_stride = p(self.default_dof_pos), s.D
+        io.base_com_bias = p(sim._base_com_bias, torch.float32)
+        io.link_mass_scale = p(sim._link_mass_scale, torch.float32) if s.L else None
+        io.friction = p(sim.friction_coeffs, torch.float32)
+        io.episode_length_buf, io.env_f32 = p(self.episode_length_buf), p(self.env_f32)
+        io.last_actions, io.last_dof_pos, io.last_dof_vel = p(self.last_actions), p(self.last_dof_pos), p(self.last_dof_vel)
+        io.kp_scale, io.kd_scale = p(self._kp_scale), p(self._kd_scale)
+        io.rfi_lim_scale, io.rao_scale = p(self._rfi_lim_scale), p(self._rao_scale)
+        io.action_delay_idx, io.hist, io.episode_sums = p(self.action_delay_idx), p(self.hist), p(self._episode_sums)
+        io.scalars = p(self.scalars)
+        for g, name in enumerate(s.obs_groups):
+            io.obs[g] = p(self.obs_buf_dict[name])
+        io.rew_buf, io.reset_buf = p(self.rew_buf), p(self.reset_buf)
+        io.time_out_buf = self.time_out_buf.data_ptr()
+        io.ref_body_pos_extend, io.ref_body_rot_extend = p(self.ref_body_pos_extend), p(self.ref_body_rot_extend)
+        io.last_episode_sums, io.partials, io.acc = p(self.last_episode_sums), p(self.partials), p(self.acc)
+        inj = inject or {}
+        io.inject_start_times = p(inj.get("motion_start_times"))
+        io.inject_kp, io.inject_kd = p(inj.get("kp_scale")), p(inj.get("kd_scale"))
+        io.inject_rfi, io.inject_rao = p(inj.get("rfi_lim_scale")), p(inj.get("rao_scale"))
+        io.inject_delay = p(inj.get("action_delay_idx"))
+        self._keep = (actions, torques, env_origins, motion_ids, inj)
+        st = _lib.stream_ptr(self.device)
+        _lib.check(self._L.pbhc_track_step(C.byref(self._cfg), C.byref(self.lib._desc), C.byref(io), self.N, st))
+        if group is not None or (torch.distributed.is_available() and torch.distributed.is_initialized()
+                                 and torch.distributed.get_world_size() > 1):
+            torch.distributed.all_reduce(self.acc, group=group)  # the only cross-rank exchange of the step (SURVEY 8e)
+        _lib.check(self._L.pbhc_track_finalize(C.byref(self._cfg), p(self.acc), p(self.scalars), st))
+        self.extras = {"time_outs": self.time_out_buf, "ref_body_pos_extend": self.ref_body_pos_extend,
+                       "ref_body_rot_extend": self.ref_body_rot_extend, "to_log": None}
+        return self.obs_buf_dict, self.rew_buf, self.reset_buf, self.extras

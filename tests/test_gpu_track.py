@@ -1,0 +1,125 @@
+"""GPU parity of the fused tracking step (K3, csrc/track.cu through the C ABI) against golden fixtures of the
+UNMODIFIED reference env (tests/golden/ref_env_*.npz) and, at larger sizes, against the CPU oracle
+(oracle/pbhc_oracle_env.py).  Masks / indices bit-exact; fp32 within 1e-5 rel / 1e-6 abs."""
+import json
+import types
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import pbhc_oracle as O, pbhc_oracle_env as OE, synth
+from pbhc_b200 import _lib
+from pbhc_b200.spec import TrackSpec, SIGMA_IDS
+from tests._util import gold, oracle_clip, product_cfg, assert_close
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+INJECT = ("motion_start_times", "kp_scale", "kd_scale", "rfi_lim_scale", "rao_scale", "action_delay_idx")
+NAMES = ["Horse-stance_pose"]
+
+
+def make_step(spec, N, tmp_path, clip_names=NAMES, exact=True):
+    from pbhc_b200.motion_lib import MotionLibRobot
+    from pbhc_b200.tracking_step import TrackingStep
+    from tests.test_gpu_parity import _install_exact_table
+    ml = MotionLibRobot(product_cfg("23", str(tmp_path), clip_names), N, DEV)
+    ml.load_motions(random_sample=False)
+    if exact:
+        _install_exact_table(ml, [oracle_clip("23", n) for n in clip_names])
+    return TrackingStep(spec, ml, N, DEV), ml
+
+
+def make_sim(N, Jb, D, L):
+    z = lambda *s: torch.zeros(*s, device=DEV)
+    return types.SimpleNamespace(_rigid_body_state=z(N * Jb, 13), all_root_states=z(N, 13), dof_state=z(N * D, 2),
+                                 contact_forces=z(N, Jb, 3), _base_com_bias=z(N, 3), _link_mass_scale=z(N, L),
+                                 friction_coeffs=z(N, 1, 1))
+
+
+def load_state(ts, S, spec):
+    """oracle / golden state dict -> TrackingStep buffers (history is key-major, logical order at push count 0)."""
+    t = lambda k: torch.as_tensor(np.asarray(S[k])).to(DEV)
+    ts.episode_length_buf.copy_(t("episode_length_buf"))
+    ts.env_f32[:, 0], ts.env_f32[:, 1] = t("motion_start_times"), t("motion_len")
+    ts.env_f32[:, 2:4], ts.env_f32[:, 4:6] = t("feet_air_time"), t("last_contacts").float()
+    ts.env_f32[:, 6] = t("end_time_ratio_buf")
+    for a, k in ((ts.last_actions, "last_actions"), (ts.last_dof_pos, "last_dof_pos"), (ts.last_dof_vel, "last_dof_vel"),
+                 (ts._kp_scale, "kp_scale"), (ts._kd_scale, "kd_scale"), (ts._rfi_lim_scale, "rfi_lim_scale"),
+                 (ts._rao_scale, "rao_scale"), (ts.action_delay_idx, "action_delay_idx"), (ts.default_dof_pos, "default_dof_pos")):
+        a.copy_(t(k))
+    for k, base in zip(spec.hist_keys, ts._hist_base):
+        n = spec.hist_len[k] * spec.hist_dim[k]
+        ts.hist[:, base:base + n] = t("hist_" + k).reshape(ts.N, -1)
+    for i, name in enumerate(ts._sum_names):
+        ts._episode_sums[:, i] = t("epsum_" + name)
+
+
+def compare_state(ts, G, spec, tag):
+    """G: dict of expected (reference / oracle) post-step buffers."""
+    e = lambda k: np.asarray(G[k])
+    assert np.array_equal(ts.episode_length_buf.cpu().numpy(), e("episode_length_buf")), tag
+    assert np.array_equal(ts.reset_buf.cpu().numpy(), e("reset_buf")), tag
+    assert np.array_equal(ts.time_out_buf.cpu().numpy(), e("time_out_buf")), tag
+    assert np.array_equal(ts.action_delay_idx.cpu().numpy(), e("action_delay_idx")), tag
+    assert_close(ts.rew_buf.cpu(), e("rew_buf"), what=f"{tag} rew_buf")
+    for name, mine in (("motion_start_times", ts.motion_start_times), ("motion_len", ts.motion_len),
+                       ("feet_air_time", ts.feet_air_time), ("end_time_ratio_buf", ts.end_time_ratio_buf),
+                       ("last_actions", ts.last_actions), ("last_dof_pos", ts.last_dof_pos), ("last_dof_vel", ts.last_dof_vel),
+                       ("kp_scale", ts._kp_scale), ("kd_scale", ts._kd_scale), ("rfi_lim_scale", ts._rfi_lim_scale),
+                       ("rao_scale", ts._rao_scale)):
+        assert_close(mine.cpu(), e(name), what=f"{tag} {name}")
+    assert np.array_equal(ts.last_contacts.cpu().numpy(), e("last_contacts").astype(np.float32)), tag
+    for k in spec.hist_keys:
+        assert_close(ts.history_handler.query(k).cpu(), e("hist_" + k), what=f"{tag} hist_{k}")
+    for name, v in ts.episode_sums.items():
+        assert_close(v.cpu(), e("epsum_" + name), what=f"{tag} epsum_{name}")
+    sc = ts.scalars.cpu().numpy()
+    for name, i in SIGMA_IDS.items():
+        assert abs(sc[_lib.S_SIGMA + i] - float(G["sigma_" + name])) <= 1e-6 * abs(float(G["sigma_" + name])), (tag, name)
+        assert abs(sc[_lib.S_EMA + i] - float(G["ema_" + name])) <= 1e-6 * abs(float(G["ema_" + name])), (tag, name)
+    for name, i in (("average_episode_length", _lib.S_AVG_EPL), ("reward_penalty_scale", _lib.S_PENALTY),
+                    ("motion_far_threshold", _lib.S_FAR_THR), ("soft_dof_pos", _lib.S_SOFT_DOF_POS),
+                    ("soft_dof_vel", _lib.S_SOFT_DOF_VEL), ("soft_torque", _lib.S_SOFT_TORQUE)):
+        assert abs(sc[i] - float(G[name])) <= 1e-6 * abs(float(G[name])) + 1e-12, (tag, name, sc[i], float(G[name]))
+
+
+@pytest.mark.parametrize("case", ["mt23_main", "mt23_bench"])
+def test_track_step_matches_reference_golden(case, tmp_path):
+    g = gold(f"ref_env_{case}.npz")
+    spec = TrackSpec.from_config(json.loads(str(g["meta_config_json"])))
+    N = int(g["meta_n_envs"])
+    ts, ml = make_step(spec, N, tmp_path)
+    sim = make_sim(N, spec.Jb, spec.D, spec.L)
+    init = {k[5:]: g[k] for k in g if k.startswith("init_")}
+    load_state(ts, init, spec)
+    sim._base_com_bias.copy_(torch.from_numpy(init["base_com_bias"]))
+    sim._link_mass_scale.copy_(torch.from_numpy(init["link_mass_scale"]))
+    sim.friction_coeffs.copy_(torch.from_numpy(init["friction_coeffs"]))
+    origins = torch.from_numpy(init["env_origins"]).to(DEV)
+    mids = torch.from_numpy(init["motion_ids"]).to(DEV)
+    for step in range(int(g["meta_n_steps"])):
+        p = f"s{step}_"
+        sim._rigid_body_state.copy_(torch.from_numpy(g[p + "in_body_state"]).reshape(-1, 13))
+        sim.all_root_states.copy_(torch.from_numpy(g[p + "in_root_state"]))
+        sim.dof_state.copy_(torch.from_numpy(g[p + "in_dof_state"]).reshape(-1, 2))
+        sim.contact_forces.copy_(torch.from_numpy(g[p + "in_contact_forces"]))
+        actions = torch.from_numpy(g[p + "in_actions"]).to(DEV).contiguous()
+        torques = torch.from_numpy(g[p + "in_torques"]).to(DEV).contiguous()
+        inject = {k: torch.from_numpy(g[p + "out_" + k]).to(DEV).contiguous() for k in INJECT}
+        obs, rew, reset, extras = ts.step(sim, actions, torques, origins, mids, inject=inject)
+        torch.cuda.synchronize()
+        tag = f"{case} step {step}"
+        for name, v in obs.items():
+            assert_close(v.cpu(), g[p + "obs_" + name], what=f"{tag} obs {name}")
+        G = {k[len(p) + 4:]: g[k] for k in g if k.startswith(p + "out_")}
+        compare_state(ts, G, spec, tag)
+        assert_close(actions.cpu(), g[p + "out_actions"], what=f"{tag} actions")
+        assert_close(sim.dof_state.cpu(), g[p + "out_dof_state"], what=f"{tag} dof_state")
+        assert_close(sim.all_root_states.cpu(), g[p + "out_root_state"], what=f"{tag} root_state")
+        assert_close(extras["ref_body_pos_extend"].cpu(), g[p + "extras_ref_body_pos_extend"], what=f"{tag} ref pos")
+        assert_close(extras["ref_body_rot_extend"].cpu(), g[p + "extras_ref_body_rot_extend"], what=f"{tag} ref rot")
+        log = ts.log_dict
+        for k in g:
+            if k.startswith(p + "log_") and k[len(p) + 4:] in log:
+                assert_close(log[k[len(p) + 4:]].cpu(), np.float32(g[k]), rtol=1e-5, atol=1e-6, what=f"{tag} log {k}")
