@@ -1,0 +1,78 @@
+"""Product-side fixtures built only from committed files under tests/golden/ (no /root/reference, no oracle/):
+a synthesised G1 MJCF, a joblib motion file and the motion_lib_cfg / env config the drop-in classes take.
+Used by tests, smoke() and bench.py."""
+import json
+import os
+
+import numpy as np
+
+GOLD = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests", "golden")
+
+
+def gold(name):
+    return dict(np.load(os.path.join(GOLD, name), allow_pickle=False))
+
+
+def tree_json(tag):
+    with open(os.path.join(GOLD, f"g1_{tag}dof_tree.json")) as f:
+        return json.load(f)
+
+
+def motion_npz(name):
+    return gold(f"motion_{name}.npz")
+
+
+def env_config(case="mt23_main"):
+    """the composed reference env config (hydra `env.config`) saved with the golden env fixture."""
+    return json.loads(str(gold(f"ref_env_{case}.npz")["meta_config_json"]))
+
+
+EXTEND = [dict(joint_name="left_hand_link", parent_name="left_elbow_link", pos=[0.25, 0.0, 0.0], rot=[1.0, 0.0, 0.0, 0.0]),
+          dict(joint_name="right_hand_link", parent_name="right_elbow_link", pos=[0.25, 0.0, 0.0], rot=[1.0, 0.0, 0.0, 0.0]),
+          dict(joint_name="head_link", parent_name="torso_link", pos=[0.0, 0.0, 0.42], rot=[1.0, 0.0, 0.0, 0.0])]
+
+
+def write_mjcf(tag, path):
+    """Synthesises an MJCF with the kinematic constants of tests/golden/g1_<tag>dof_tree.json (bodies in
+    DFS order, one hinge per non-root body, a free joint on the root, one motor per hinge)."""
+    import xml.etree.ElementTree as ET
+    t = tree_json(tag)
+    nb = t["num_bodies"]
+    root = ET.Element("mujoco", model=f"g1_{tag}")
+    world = ET.SubElement(root, "worldbody")
+    act = ET.SubElement(root, "actuator")
+    nodes = []
+    fmt = lambda v: " ".join(repr(float(np.float32(x))) for x in v)
+    for i in range(nb):
+        parent = world if t["parents"][i] < 0 else nodes[t["parents"][i]]
+        b = ET.SubElement(parent, "body", name=t["names"][i], pos=fmt(t["offsets"][i]), quat=fmt(t["local_rot_wxyz"][i]))
+        nodes.append(b)
+        if i == 0:
+            ET.SubElement(b, "joint", name="floating_base_joint", type="free")
+        else:
+            jn = t["names"][i].replace("_link", "_joint")
+            ET.SubElement(b, "joint", name=jn, type="hinge", axis=" ".join(str(int(a)) for a in t["dof_axis"][i - 1]),
+                          range=" ".join(repr(float(x)) for x in t["joints_range"][i - 1]))
+            ET.SubElement(act, "motor", name=jn, joint=jn)
+    ET.ElementTree(root).write(path)
+    return path
+
+
+def product_cfg(tag, tmpdir, motion_names):
+    """motion_lib_cfg for pbhc_b200.MotionLibRobot built only from committed fixtures."""
+    import joblib
+    from pbhc_b200.fk import AttrDict
+    os.makedirs(tmpdir, exist_ok=True)
+    write_mjcf(tag, os.path.join(tmpdir, f"g1_{tag}.xml"))
+    data = {}
+    for nm in motion_names:
+        m = motion_npz(nm)
+        e = dict(root_trans_offset=m["root_trans_offset"], pose_aa=m["pose_aa"], dof=m["dof"], root_rot=m["root_rot"],
+                 fps=int(m["fps"]))
+        if "contact_mask" in m:
+            e["contact_mask"] = m["contact_mask"]
+        data[nm] = e
+    pkl = os.path.join(tmpdir, f"motions_{tag}_{len(motion_names)}.pkl")
+    joblib.dump(data, pkl)
+    return AttrDict(asset=AttrDict(assetRoot=str(tmpdir), assetFileName=f"g1_{tag}.xml"), motion_file=pkl,
+                    extend_config=[AttrDict(e) for e in EXTEND], step_dt=0.02)

@@ -1,6 +1,7 @@
-"""TEST INFRASTRUCTURE ONLY - seeded synthetic simulator state (SURVEY.md 8d input table).  Pure torch on
-CPU, no reference import: used by the golden generator, the parity tests, smoke() and bench.py's
-cpu_baseline leg so that the CPU oracle and the GPU path see identical bits."""
+"""Seeded synthetic simulator state (SURVEY.md 8d input table) - the stand-in for the external physics.
+Pure torch, device-agnostic (tensors follow `ref`'s device and the generator's), no oracle / reference import:
+used by the golden generator, the parity tests, smoke() and bench.py so that the CPU oracle and the GPU path
+see identical bits."""
 import math
 
 import torch

@@ -228,12 +228,13 @@ class TrackingStep:
         self._cfg = c
 
     # ---- one env step -----------------------------------------------------------------------------------
-    def step(self, sim, actions, torques, env_origins, motion_ids, inject=None, group=None):
-        """sim: object with Isaac-Gym-layout CUDA tensors (simulator/isaacgym/isaacgym.py:596-618):
+    def bind(self, sim, actions, torques, env_origins, motion_ids, inject=None):
+        """Records the device pointers of this step's borrowed tensors in the PbhcTrackIO block (no launch).
+        sim: object with Isaac-Gym-layout CUDA tensors (simulator/isaacgym/isaacgym.py:596-618):
         _rigid_body_state [N*bodies,13] or [N,bodies,13], all_root_states [N,13], dof_state [N*D,2],
         contact_forces [N,Jb,3], _base_com_bias [N,3], _link_mass_scale [N,L], friction_coeffs [N,1,1].
         actions [N,D] (zeroed in place for envs that reset) and torques [N,D] are this step's clipped actions /
-        last applied torques.  Returns (obs_buf_dict, rew_buf, reset_buf, extras) like LeggedRobotBase.step."""
+        last applied torques."""
         io, p, s = self._io, _lib.ptr, self.spec
         body = sim._rigid_body_state
         io.body_state, io.body_env_stride = p(body, torch.float32), body.numel() // self.N
@@ -263,13 +264,28 @@ class TrackingStep:
         io.inject_kp, io.inject_kd = p(inj.get("kp_scale")), p(inj.get("kd_scale"))
         io.inject_rfi, io.inject_rao = p(inj.get("rfi_lim_scale")), p(inj.get("rao_scale"))
         io.inject_delay = p(inj.get("action_delay_idx"))
-        self._keep = (actions, torques, env_origins, motion_ids, inj)
-        st = _lib.stream_ptr(self.device)
-        _lib.check(self._L.pbhc_track_step(C.byref(self._cfg), C.byref(self.lib._desc), C.byref(io), self.N, st))
-        if group is not None or (torch.distributed.is_available() and torch.distributed.is_initialized()
-                                 and torch.distributed.get_world_size() > 1):
-            torch.distributed.all_reduce(self.acc, group=group)  # the only cross-rank exchange of the step
-        _lib.check(self._L.pbhc_track_finalize(C.byref(self._cfg), p(self.acc), p(self.scalars), st))
+        self._keep = (sim, actions, torques, env_origins, motion_ids, inj)
+
+    def launch(self):
+        """pbhc_track_step on the current stream with the pointers of the last bind(): the fused kernel + the
+        deterministic reduction of its per-block sums into `acc`."""
+        _lib.check(self._L.pbhc_track_step(C.byref(self._cfg), C.byref(self.lib._desc), C.byref(self._io), self.N,
+                                           _lib.stream_ptr(self.device)))
+
+    def finalize(self, group=None):
+        """all-reduce of `acc` when envs are sharded over ranks (the only cross-rank exchange of the step),
+        then pbhc_track_finalize advances the device scalars (adaptive sigma, curricula, log values)."""
+        dist = torch.distributed
+        if group is not None or (dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1):
+            dist.all_reduce(self.acc, group=group)
+        _lib.check(self._L.pbhc_track_finalize(C.byref(self._cfg), _lib.ptr(self.acc), _lib.ptr(self.scalars),
+                                               _lib.stream_ptr(self.device)))
+
+    def step(self, sim, actions, torques, env_origins, motion_ids, inject=None, group=None):
+        """Returns (obs_buf_dict, rew_buf, reset_buf, extras) like LeggedRobotBase.step (see bind() for the inputs)."""
+        self.bind(sim, actions, torques, env_origins, motion_ids, inject)
+        self.launch()
+        self.finalize(group)
         self.extras = {"time_outs": self.time_out_buf, "ref_body_pos_extend": self.ref_body_pos_extend,
                        "ref_body_rot_extend": self.ref_body_rot_extend, "to_log": None}
         return self.obs_buf_dict, self.rew_buf, self.reset_buf, self.extras

@@ -1,0 +1,127 @@
+"""The benchmark workload: config A/B of SURVEY.md 8 (G1 23-DoF `+exp=motion_tracking +obs=motion_tracking/main
++rewards=motion_tracking/main`, single clip Horse-stance_pose, synthetic simulator state) assembled from the
+committed fixtures only.  Shared by bench.py, __graft_entry__.smoke() and the GPU tests so they all drive the
+product through the same calls.  Nothing here imports oracle/ or /root/reference.
+"""
+import types
+
+import torch
+
+from . import synth
+from .fixtures import env_config, product_cfg
+from .spec import TrackSpec
+
+CLIP = "Horse-stance_pose"
+CASE = "mt23_main"  # obs=motion_tracking/main with the four observation-noise scales set to 0 (= benchmark.yaml's choice)
+
+
+def step_bytes(spec, contact_size=2):
+    """Algorithmic HBM bytes of ONE fused env step (SURVEY.md 8d row "Fused tracked env-step"), recomputed from
+    the live config.  The motion table is excluded when it is a single L2-resident clip."""
+    D, J, Jb, L = spec.D, spec.J, spec.Jb, spec.L
+    n_sums = len(spec.reward_names) + (1 if spec.termination_scale is not None else 0)
+    hist_step = sum(spec.hist_dim[k] for k in spec.hist_keys)
+    hist_all = sum(spec.hist_dim[k] * spec.hist_len[k] for k in spec.hist_keys)
+    reads = dict(body_state=Jb * 13 * 4, root_state=13 * 4, dof_state=D * 2 * 4, contact_forces=Jb * 3 * 4,
+                 actions_last_actions_last_dof_vel_torques=4 * D * 4,
+                 per_env_scalars=8 + 8 + 4 + 4 + 12,            # episode_length, motion_id, start time, motion_len, origin
+                 stateful_reward_state=4 * contact_size * 2,    # feet_air_time, last_contacts
+                 privileged_dr=12 + L * 4 + 2 * D * 4 + 4 + 8,  # com bias, link mass, kp, kd, friction, ctrl delay
+                 default_dof_pos=D * 4, history=hist_all * 4, episode_sums=n_sums * 4)
+    rew_w = (len(spec.reward_names) + 1) * 4 if spec.use_vec_reward else 4
+    writes = dict(obs=sum(g["dim"] for g in spec.obs_groups.values()) * 4, rew_buf=rew_w, reset_timeout=8 + 1,
+                  episode_sums=n_sums * 4, history_push=hist_step * 4,
+                  last_state=3 * D * 4 + 8 + 4 * 4 * 2 + 24,     # last_actions/dof_pos/dof_vel, episode_length, air/contacts, times
+                  extras_ref=J * 7 * 4)
+    return sum(reads.values()) + sum(writes.values()), reads, writes
+
+
+def fk_bytes(J):
+    """K2 per pose: pose_aa + trans in; positions, xyzw quaternions and 3x3 matrices out."""
+    return J * 12 + 12 + J * (12 + 16 + 36)
+
+
+class Workload:
+    """Everything one rank needs to run env steps on `device` for `n_envs` environments."""
+
+    def __init__(self, n_envs, device, tmpdir, seed=0, case=CASE, clip=CLIP):
+        from .motion_lib import MotionLibRobot
+        from .tracking_step import TrackingStep
+        self.N, self.device = int(n_envs), torch.device(device)
+        self.spec = spec = TrackSpec.from_config(env_config(case))
+        self.lib = MotionLibRobot(product_cfg("23", tmpdir, [clip]), self.N, self.device)
+        self.lib.load_motions(random_sample=False)
+        self.ts = TrackingStep(spec, self.lib, self.N, self.device, seed=seed)
+        self.host = self.make_inputs(seed)
+        dev = self.device
+        h = self.host
+        self.sim = types.SimpleNamespace(
+            _rigid_body_state=h["body_state"].reshape(-1, 13).to(dev), all_root_states=h["root_state"].to(dev),
+            dof_state=h["dof_state"].reshape(-1, 2).to(dev), contact_forces=h["contact_forces"].to(dev),
+            _base_com_bias=h["base_com_bias"].to(dev), _link_mass_scale=h["link_mass_scale"].to(dev),
+            friction_coeffs=h["friction_coeffs"].to(dev))
+        self.actions, self.torques = h["actions"].to(dev), h["torques"].to(dev)
+        self.env_origins, self.motion_ids = h["env_origins"].to(dev), h["motion_ids"].to(dev)
+        self.pose_aa, self.trans = h["pose_aa"].to(dev), h["trans"].to(dev)
+        self.load_env_state(h)
+        self.ts.bind(self.sim, self.actions, self.torques, self.env_origins, self.motion_ids)
+
+    # ---- seeded synthetic inputs (CPU tensors: the CPU oracle consumes the very same bits) -------------------
+    def make_inputs(self, seed):
+        N, spec, dev = self.N, self.spec, self.device
+        D, Jb, J = spec.D, spec.Jb, spec.J
+        gen = torch.Generator().manual_seed(seed)
+        mlen = float(self.lib._motion_lengths[0])
+        h = {}
+        h["motion_ids"] = torch.arange(N, dtype=torch.int64)
+        h["motion_len"] = torch.full((N,), mlen)
+        h["motion_start_times"] = torch.rand(N, generator=gen) * mlen
+        h["episode_length_buf"] = torch.randint(0, 50, (N,), generator=gen)
+        side = int(N ** 0.5) + 1  # env origins on a grid, spacing 5 m (base_task.py:136-142)
+        idx = torch.arange(N)
+        h["env_origins"] = torch.stack([(idx // side).float() * 5.0, (idx % side).float() * 5.0, torch.zeros(N)], dim=1)
+        t = (h["episode_length_buf"] + 2) * spec.dt + h["motion_start_times"]
+        ref = self.lib.get_motion_state(h["motion_ids"].to(dev), t.to(dev), h["env_origins"].to(dev))
+        ref = {k: v.cpu() for k, v in ref.items()}
+        body, root, dof, cf = synth.synth_sim_state(ref, Jb, gen, feet=tuple(spec.feet_ids))
+        h.update(body_state=body, root_state=root, dof_state=dof, contact_forces=cf)
+        h["actions"] = synth.synth_actions(N, D, gen)
+        lim = torch.tensor(spec.torque_limit)
+        h["torques"] = torch.maximum(torch.minimum(torch.randn(N, D, generator=gen) * 20.0, lim), -lim)
+        h["base_com_bias"] = (torch.rand(N, 3, generator=gen) - 0.5) * 0.1
+        h["link_mass_scale"] = 0.9 + 0.2 * torch.rand(N, spec.L, generator=gen)
+        h["friction_coeffs"] = 0.2 + torch.rand(N, 1, 1, generator=gen)
+        h["kp_scale"] = 0.9 + 0.2 * torch.rand(N, D, generator=gen)
+        h["kd_scale"] = 0.9 + 0.2 * torch.rand(N, D, generator=gen)
+        h["last_actions"] = synth.synth_actions(N, D, gen)
+        h["last_dof_vel"] = dof[..., 1] + torch.randn(N, D, generator=gen) * 0.1
+        # FK input of the step: the reference pose of each env's current frame (fk_batch(B=N, T=1), BASELINE configs[0])
+        h["pose_aa"] = torch.randn(N, J, 3, generator=gen) * 0.3
+        h["trans"] = root[:, :3].clone()
+        return h
+
+    def load_env_state(self, h):
+        ts = self.ts
+        ts.episode_length_buf.copy_(h["episode_length_buf"])
+        ts.env_f32.zero_()
+        ts.env_f32[:, 0].copy_(h["motion_start_times"])
+        ts.env_f32[:, 1].copy_(h["motion_len"])
+        ts._kp_scale.copy_(h["kp_scale"])
+        ts._kd_scale.copy_(h["kd_scale"])
+        ts.last_actions.copy_(h["last_actions"])
+        ts.last_dof_vel.copy_(h["last_dof_vel"])
+
+    # ---- the step ------------------------------------------------------------------------------------------
+    def fk(self):
+        """K2 on the N per-env poses: positions + xyzw quaternions + rotation matrices."""
+        return self.lib.mesh_parsers.fk(self.pose_aa, self.trans, want_mat=True, want_quat=True)
+
+    def step(self, with_fk=True):
+        """one tracked env step: [K2 FK] + fused lookup/diff/termination/reward/reset/obs/history kernel + finalize."""
+        if with_fk:
+            self.fk_out = self.fk()
+        self.ts.launch()
+        self.ts.finalize()
+        return self.ts.obs_buf_dict, self.ts.rew_buf, self.ts.reset_buf
+
+    LAUNCHES_PER_STEP = {"fk": 1, "track": 2, "finalize": 1}

@@ -7,28 +7,15 @@ import torch
 
 from oracle import pbhc_oracle as O
 
-GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+from pbhc_b200.fixtures import GOLD, gold, tree_json, motion_npz, write_mjcf, product_cfg, EXTEND, env_config  # noqa: F401
 
 # north_star tolerance: fp32 within 1e-5 relative / 1e-6 absolute
 RTOL, ATOL = 1e-5, 1e-6
 
 
-def gold(name):
-    return dict(np.load(os.path.join(GOLD, name), allow_pickle=False))
-
-
-def tree_json(tag):
-    with open(os.path.join(GOLD, f"g1_{tag}dof_tree.json")) as f:
-        return json.load(f)
-
-
 def oracle_tree(tag):
     t = tree_json(tag)
     return O.make_tree(t["names"], t["parents"], t["offsets"], t["local_rot_wxyz"], t["num_bodies"], t["dof_axis"])
-
-
-def motion_npz(name):
-    return gold(f"motion_{name}.npz")
 
 
 def oracle_clip(tag, name):
@@ -50,54 +37,69 @@ def assert_close(a, b, rtol=RTOL, atol=ATOL, what=""):
                              f"at flat {int(i)} (got {a.flatten()[i]:.8g}, want {b.flatten()[i]:.8g})")
 
 
-# ---- product-side fixtures (no /root/reference at run time) ---------------------------------------
-
-EXTEND = [dict(joint_name="left_hand_link", parent_name="left_elbow_link", pos=[0.25, 0.0, 0.0], rot=[1.0, 0.0, 0.0, 0.0]),
-          dict(joint_name="right_hand_link", parent_name="right_elbow_link", pos=[0.25, 0.0, 0.0], rot=[1.0, 0.0, 0.0, 0.0]),
-          dict(joint_name="head_link", parent_name="torso_link", pos=[0.0, 0.0, 0.42], rot=[1.0, 0.0, 0.0, 0.0])]
-
-
-def write_mjcf(tag, path):
-    """Synthesises an MJCF with the kinematic constants of tests/golden/g1_<tag>dof_tree.json (bodies in
-    DFS order, one hinge per non-root body, a free joint on the root, one motor per hinge)."""
-    import xml.etree.ElementTree as ET
-    t = tree_json(tag)
-    nb = t["num_bodies"]
-    root = ET.Element("mujoco", model=f"g1_{tag}")
-    world = ET.SubElement(root, "worldbody")
-    act = ET.SubElement(root, "actuator")
-    nodes = []
-    fmt = lambda v: " ".join(repr(float(np.float32(x))) for x in v)
-    for i in range(nb):
-        parent = world if t["parents"][i] < 0 else nodes[t["parents"][i]]
-        b = ET.SubElement(parent, "body", name=t["names"][i], pos=fmt(t["offsets"][i]), quat=fmt(t["local_rot_wxyz"][i]))
-        nodes.append(b)
-        if i == 0:
-            ET.SubElement(b, "joint", name="floating_base_joint", type="free")
-        else:
-            jn = t["names"][i].replace("_link", "_joint")
-            ET.SubElement(b, "joint", name=jn, type="hinge", axis=" ".join(str(int(a)) for a in t["dof_axis"][i - 1]),
-                          range=" ".join(repr(float(x)) for x in t["joints_range"][i - 1]))
-            ET.SubElement(act, "motor", name=jn, joint=jn)
-    ET.ElementTree(root).write(path)
-    return path
+def install_exact_table(ml, clips):
+    """Overwrite the GPU-built records with the oracle's (reference-exact) per-frame arrays so that the kernels are
+    compared on bit-identical inputs (slerp has hard branches that a last-ulp table difference can flip)."""
+    J, Jb, D, Cm = ml._dims
+    rows = []
+    for c in clips:
+        parts = [c.rot.reshape(c.num_frames, -1), c.pos.reshape(c.num_frames, -1), c.vel.reshape(c.num_frames, -1),
+                 c.ang_vel.reshape(c.num_frames, -1), c.dof_pos, c.dof_vel]
+        if Cm:
+            parts.append(c.contact)
+        r = torch.cat(parts, dim=1)
+        rows.append(torch.nn.functional.pad(r, (0, ml._rec_stride - r.shape[1])))
+    rec = torch.cat(rows).float()
+    assert rec.shape == ml._records.shape
+    ml._records.copy_(rec.to(ml._records.device))
 
 
-def product_cfg(tag, tmpdir, motion_names):
-    """motion_lib_cfg for pbhc_b200.MotionLibRobot built only from committed fixtures."""
-    import joblib
-    from pbhc_b200.fk import AttrDict
-    os.makedirs(tmpdir, exist_ok=True)
-    write_mjcf(tag, os.path.join(tmpdir, f"g1_{tag}.xml"))
-    data = {}
-    for nm in motion_names:
-        m = motion_npz(nm)
-        e = dict(root_trans_offset=m["root_trans_offset"], pose_aa=m["pose_aa"], dof=m["dof"], root_rot=m["root_rot"],
-                 fps=int(m["fps"]))
-        if "contact_mask" in m:
-            e["contact_mask"] = m["contact_mask"]
-        data[nm] = e
-    pkl = os.path.join(tmpdir, f"motions_{tag}_{len(motion_names)}.pkl")
-    joblib.dump(data, pkl)
-    return AttrDict(asset=AttrDict(assetRoot=str(tmpdir), assetFileName=f"g1_{tag}.xml"), motion_file=pkl,
-                    extend_config=[AttrDict(e) for e in EXTEND], step_dt=0.02)
+def oracle_env_from_workload(wl, clip_tag="23"):
+    """(tab, S, inp) for oracle.pbhc_oracle_env.step holding the same bits as a pbhc_b200.workload.Workload."""
+    from oracle import pbhc_oracle_env as OE
+    from pbhc_b200.workload import CLIP
+    spec, h, N = wl.spec, wl.host, wl.N
+    tab = O.MotionTable([oracle_clip(clip_tag, CLIP)], spec.Jb)
+    S = OE.new_state(spec, N, env_origins=h["env_origins"].clone())
+    S["motion_ids"] = torch.zeros(N, dtype=torch.long)
+    for k in ("motion_len", "motion_start_times", "episode_length_buf", "kp_scale", "kd_scale", "last_actions", "last_dof_vel",
+              "base_com_bias", "link_mass_scale", "friction_coeffs"):
+        S[k] = h[k].clone()
+    inp = {k: h[k].clone() for k in ("body_state", "root_state", "dof_state", "contact_forces", "actions", "torques")}
+    return tab, S, inp
+
+
+def check_workload_step_against_oracle(wl, n_steps=2, seed=5):
+    """Runs n_steps of the fused GPU step and of the CPU oracle on the same inputs (start times drawn at resets are
+    injected into both) and compares observations, rewards, masks and per-env state."""
+    from oracle import pbhc_oracle_env as OE
+    from pbhc_b200.workload import CLIP
+    spec, ts, N = wl.spec, wl.ts, wl.N
+    install_exact_table(wl.lib, [oracle_clip("23", CLIP)])
+    tab, S, inp = oracle_env_from_workload(wl)
+    gen = torch.Generator().manual_seed(seed)
+    dev = wl.device
+    for step in range(n_steps):
+        start = torch.rand(N, generator=gen) * float(tab.length[0])
+        inj_o = {"motion_start_times": start}
+        inj_g = {"motion_start_times": start.to(dev)}
+        obs_o, log_o, _ = OE.step(spec, tab, S, inp, inject=inj_o)
+        ts.bind(wl.sim, wl.actions, wl.torques, wl.env_origins, wl.motion_ids, inject=inj_g)
+        ts.launch()
+        ts.finalize()
+        torch.cuda.synchronize()
+        tag = f"workload step {step}"
+        assert torch.equal(ts.reset_buf.cpu(), S["reset_buf"]), tag + " reset_buf"
+        assert torch.equal(ts.time_out_buf.cpu(), S["time_out_buf"]), tag + " time_out_buf"
+        assert torch.equal(ts.episode_length_buf.cpu(), S["episode_length_buf"]), tag + " episode_length_buf"
+        assert_close(ts.rew_buf.cpu(), S["rew_buf"], what=tag + " rew_buf")
+        for name, v in ts.obs_buf_dict.items():
+            assert_close(v.cpu(), obs_o[name], what=f"{tag} obs {name}")
+        assert_close(ts.motion_start_times.cpu(), S["motion_start_times"], what=tag + " start times")
+        assert_close(wl.sim.dof_state.cpu().view(N, -1, 2), inp["dof_state"], what=tag + " dof_state")
+        assert_close(wl.sim.all_root_states.cpu(), inp["root_state"], what=tag + " root_state")
+        for name, v in ts.episode_sums.items():
+            assert_close(v.cpu(), S["epsum_" + name], what=f"{tag} epsum_{name}")
+        # the oracle's `actions` of the next step = this step's actions (zeroed for envs that reset)
+        inp["actions"] = S["actions"].clone()
+    return int(S["reset_buf"].sum())

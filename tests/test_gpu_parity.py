@@ -25,21 +25,7 @@ def _lib_with(tag, names, tmp_path, n):
     return ml
 
 
-def _install_exact_table(ml, clips):
-    """Overwrite the GPU-built records with the oracle's (reference-exact) per-frame arrays so that the
-    lookup kernel is compared on bit-identical inputs."""
-    J, Jb, D, Cm = ml._dims
-    rows = []
-    for c in clips:
-        parts = [c.rot.reshape(c.num_frames, -1), c.pos.reshape(c.num_frames, -1), c.vel.reshape(c.num_frames, -1),
-                 c.ang_vel.reshape(c.num_frames, -1), c.dof_pos, c.dof_vel]
-        if Cm:
-            parts.append(c.contact)
-        r = torch.cat(parts, dim=1)
-        rows.append(torch.nn.functional.pad(r, (0, ml._rec_stride - r.shape[1])))
-    rec = torch.cat(rows).float()
-    assert rec.shape == ml._records.shape
-    ml._records.copy_(rec.to(DEV))
+from tests._util import install_exact_table as _install_exact_table  # noqa: E402
 
 
 @pytest.mark.parametrize("tag,name", [("23", "Horse-stance_pose"), ("29", "g1_29dof_clip")])

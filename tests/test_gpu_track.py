@@ -8,7 +8,8 @@ import numpy as np
 import pytest
 import torch
 
-from oracle import pbhc_oracle as O, pbhc_oracle_env as OE, synth
+from oracle import pbhc_oracle as O, pbhc_oracle_env as OE
+from pbhc_b200 import synth
 from pbhc_b200 import _lib
 from pbhc_b200.spec import TrackSpec, SIGMA_IDS
 from tests._util import gold, oracle_clip, product_cfg, assert_close
@@ -123,3 +124,14 @@ def test_track_step_matches_reference_golden(case, tmp_path):
         for k in g:
             if k.startswith(p + "log_") and k[len(p) + 4:] in log:
                 assert_close(log[k[len(p) + 4:]].cpu(), np.float32(g[k]), rtol=1e-5, atol=1e-6, what=f"{tag} log {k}")
+
+
+@pytest.mark.parametrize("n_envs", [1, 37, 4096])
+def test_workload_step_vs_oracle(n_envs, tmp_path):
+    """the bench workload itself (ragged and default-training sizes) against the CPU oracle, incl. resets."""
+    from pbhc_b200.workload import Workload
+    from tests._util import check_workload_step_against_oracle
+    wl = Workload(n_envs, DEV, str(tmp_path), seed=3)
+    n_reset = check_workload_step_against_oracle(wl, n_steps=3)
+    if n_envs >= 4096:
+        assert n_reset > 0

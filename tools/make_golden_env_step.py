@@ -7,7 +7,8 @@ import os
 import numpy as np
 import torch
 
-from oracle import ref_env as E, ref_loader as R, synth
+from oracle import ref_env as E, ref_loader as R
+from pbhc_b200 import synth
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 GOLD = os.path.join(ROOT, "tests", "golden")
