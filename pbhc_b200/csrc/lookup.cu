@@ -87,7 +87,8 @@ extern "C" int pbhc_lookup(const PbhcTableDesc* tab, const int32_t* clip_of_moti
                            const float* motion_times, const float* offset, int64_t n, const PbhcLookupOut* out,
                            void* stream) {
   using namespace pbhc;
-  if (!tab || !out || !motion_ids || !motion_times || n < 0) { set_error("pbhc_lookup: null argument"); return PBHC_E_BADARG; }
+  if (!tab || !out || n < 0) { set_error("pbhc_lookup: null argument"); return PBHC_E_BADARG; }
+  if (n > 0 && (!motion_ids || !motion_times)) { set_error("pbhc_lookup: null motion_ids / motion_times"); return PBHC_E_BADARG; }
   if (!tab->records || tab->num_clips <= 0 || tab->num_joints <= 0 || tab->num_bodies > tab->num_joints) {
     set_error("pbhc_lookup: bad table descriptor"); return PBHC_E_BADARG;
   }

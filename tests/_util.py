@@ -80,9 +80,13 @@ def check_workload_step_against_oracle(wl, n_steps=2, seed=5):
     gen = torch.Generator().manual_seed(seed)
     dev = wl.device
     for step in range(n_steps):
-        start = torch.rand(N, generator=gen) * float(tab.length[0])
-        inj_o = {"motion_start_times": start}
-        inj_g = {"motion_start_times": start.to(dev)}
+        D, dr = spec.D, spec.dr
+        u = lambda lo, hi: lo + (hi - lo) * torch.rand(N, D, generator=gen)
+        inj_o = {"motion_start_times": torch.rand(N, generator=gen) * float(tab.length[0]),
+                 "kp_scale": u(*dr["kp_range"]), "kd_scale": u(*dr["kd_range"]), "rfi_lim_scale": u(*dr["rfi_lim_range"]),
+                 "rao_scale": u(-dr["rao_lim"], dr["rao_lim"]),
+                 "action_delay_idx": torch.randint(dr["ctrl_delay_step_range"][0], dr["ctrl_delay_step_range"][1] + 1, (N,), generator=gen)}
+        inj_g = {k: v.to(dev).contiguous() for k, v in inj_o.items()}
         obs_o, log_o, _ = OE.step(spec, tab, S, inp, inject=inj_o)
         ts.bind(wl.sim, wl.actions, wl.torques, wl.env_origins, wl.motion_ids, inject=inj_g)
         ts.launch()
