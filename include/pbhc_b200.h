@@ -14,7 +14,7 @@
 extern "C" {
 #endif
 
-#define PBHC_ABI_VERSION 1
+#define PBHC_ABI_VERSION 2
 #define PBHC_OK 0
 #define PBHC_E_BADARG (-1)
 #define PBHC_E_ALIGN (-2)
@@ -22,6 +22,9 @@ extern "C" {
 #define PBHC_E_CUDA (-4)
 
 int pbhc_abi_version(void);
+/* sizeof of an ABI struct, for bindings to verify their mirror: 0 PbhcTableDesc, 1 PbhcLookupOut, 2 PbhcTree,
+ * 3 PbhcTrackCfg, 4 PbhcTrackIO, 5 PbhcHistDst, 6 PbhcCurriculum; -1 for an unknown id */
+int64_t pbhc_struct_size(int32_t which);
 const char* pbhc_last_error(void);
 
 /* ---- packed motion table (replaces the 11 concatenated tensors of
@@ -128,6 +131,7 @@ int pbhc_clip_prepare(const float* pos, const float* quat, const float* pose_aa,
 #define PBHC_MAX_FEET 4
 #define PBHC_MAX_OBS_GROUPS 4
 #define PBHC_MAX_HIST_KEYS 8
+#define PBHC_MAX_HIST_DST 16
 #define PBHC_NUM_OBS_SRC 20
 #define PBHC_NUM_SIGMA 10
 #define PBHC_ENVF_STRIDE 8   /* env_f32 row: start_time, motion_len, air_time[2], last_contact[2], end_time_ratio, pad */
@@ -180,6 +184,8 @@ int pbhc_clip_prepare(const float* pos, const float* quat, const float* pose_aa,
 #define PBHC_L_ERROR_EMA 26
 
 typedef struct { int32_t enable; double lo, hi, degree, down, up; } PbhcCurriculum;
+/* history key `key` (index into hist_src) appears in obs group `group` at `offset`, newest `len` slots, scaled by mul */
+typedef struct { int32_t key, group, offset, len; float mul; } PbhcHistDst;
 
 typedef struct {
   int32_t J, Jb, D, L, n_ext, n_feet;
@@ -208,12 +214,15 @@ typedef struct {
   double adaptive_alpha, adaptive_scale;
   PbhcCurriculum cur_penalty, cur_far, cur_dof_pos, cur_dof_vel, cur_torque;
   double num_compute_average_epl;
-  /* observations: feature vector = the PBHC_NUM_OBS_SRC sources (scaled) followed by the history in logical
-   * (newest-first) order; each obs group is a gather `obs[i] = clip(feat[map[i]] * mul[i])` */
+  /* observations (legged_robot_base.py:763-793, helpers.py:128-152): every obs group is a row of contiguous
+   * segments; a segment is either one observation source (scaled by obs_scale[src]) or the newest `len` slots of one
+   * history key (times `mul`, the obs scale of the history key of the group).  src_dst[k][g] = offset of source k in
+   * group g (-1: absent).  Rows are clipped to +-clip_obs after assembly. */
   int32_t n_groups;
   int32_t group_dim[PBHC_MAX_OBS_GROUPS];
-  const int32_t* group_map[PBHC_MAX_OBS_GROUPS]; /* device */
-  const float* group_mul[PBHC_MAX_OBS_GROUPS];   /* device */
+  int32_t src_dst[PBHC_NUM_OBS_SRC][PBHC_MAX_OBS_GROUPS];
+  int32_t n_hist_dst;
+  PbhcHistDst hist_dst[PBHC_MAX_HIST_DST];
   float obs_scale[PBHC_NUM_OBS_SRC], obs_noise[PBHC_NUM_OBS_SRC];
   float clip_obs;
   int32_t n_hist_keys, hist_row; /* hist_row = sum_k len_k*dim_k floats per env */

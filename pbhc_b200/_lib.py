@@ -9,6 +9,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libpbhc_b200.so")
 
 c_f32p = C.c_void_p
+ABI_VERSION = 2
 MAX_JOINTS = 40
 
 
@@ -39,7 +40,7 @@ class Tree(C.Structure):
 
 _lib = None
 
-EXPORTS = ["pbhc_abi_version", "pbhc_last_error", "pbhc_lookup", "pbhc_fk", "pbhc_gae", "pbhc_adv_normalize", "pbhc_clip_prepare",
+EXPORTS = ["pbhc_abi_version", "pbhc_struct_size", "pbhc_last_error", "pbhc_lookup", "pbhc_fk", "pbhc_gae", "pbhc_adv_normalize", "pbhc_clip_prepare",
            "pbhc_track_max_blocks", "pbhc_track_step", "pbhc_track_finalize"]
 
 
@@ -68,8 +69,13 @@ def lib():
                                     C.c_int32, C.c_int32, C.c_float, C.POINTER(C.c_double), C.c_int32, C.c_void_p,
                                     C.c_void_p, C.c_int32, C.c_void_p]
     bind_track(L)
-    if L.pbhc_abi_version() != 1:
+    if L.pbhc_abi_version() != ABI_VERSION:
         raise PbhcError("ABI version mismatch")
+    L.pbhc_struct_size.restype = C.c_int64
+    L.pbhc_struct_size.argtypes = [C.c_int32]
+    for i, t in enumerate((TableDesc, LookupOut, Tree, TrackCfg, TrackIO, HistDst, Curriculum)):
+        if L.pbhc_struct_size(i) != C.sizeof(t):
+            raise PbhcError(f"ABI struct {t.__name__}: library {L.pbhc_struct_size(i)} B, binding {C.sizeof(t)} B")
     _lib = L
     return L
 
@@ -97,7 +103,7 @@ def stream_ptr(device=None):
 
 
 # ---- K3 structs (mirror include/pbhc_b200.h exactly) ------------------------------------------------
-MAX_DOF, MAX_REWARDS, MAX_EXT, MAX_FEET, MAX_OBS_GROUPS, MAX_HIST_KEYS = 32, 32, 4, 4, 4, 8
+MAX_DOF, MAX_REWARDS, MAX_EXT, MAX_FEET, MAX_OBS_GROUPS, MAX_HIST_KEYS, MAX_HIST_DST = 32, 32, 4, 4, 4, 8, 16
 NUM_OBS_SRC, NUM_SIGMA, ENVF_STRIDE, SCALARS, ACC = 20, 10, 8, 96, 32
 L_ADP_SIGMA, L_ERROR_EMA = 16, 26
 S_SIGMA, S_EMA, S_AVG_EPL, S_PENALTY, S_FAR_THR, S_SOFT_DOF_POS, S_SOFT_DOF_VEL, S_SOFT_TORQUE, S_PUSH_COUNT, S_LOG = 0, 10, 20, 21, 22, 23, 24, 25, 26, 32
@@ -111,6 +117,10 @@ LOG_NAMES = ["upper_body_diff_norm", "lower_body_diff_norm", "vr_3point_diff_nor
 class Curriculum(C.Structure):
     _fields_ = [("enable", C.c_int32), ("lo", C.c_double), ("hi", C.c_double), ("degree", C.c_double),
                 ("down", C.c_double), ("up", C.c_double)]
+
+
+class HistDst(C.Structure):
+    _fields_ = [("key", C.c_int32), ("group", C.c_int32), ("offset", C.c_int32), ("len", C.c_int32), ("mul", C.c_float)]
 
 
 class TrackCfg(C.Structure):
@@ -132,7 +142,7 @@ class TrackCfg(C.Structure):
         ("cur_penalty", Curriculum), ("cur_far", Curriculum), ("cur_dof_pos", Curriculum), ("cur_dof_vel", Curriculum), ("cur_torque", Curriculum),
         ("num_compute_average_epl", C.c_double),
         ("n_groups", C.c_int32), ("group_dim", C.c_int32 * MAX_OBS_GROUPS),
-        ("group_map", C.c_void_p * MAX_OBS_GROUPS), ("group_mul", C.c_void_p * MAX_OBS_GROUPS),
+        ("src_dst", (C.c_int32 * MAX_OBS_GROUPS) * NUM_OBS_SRC), ("n_hist_dst", C.c_int32), ("hist_dst", HistDst * MAX_HIST_DST),
         ("obs_scale", C.c_float * NUM_OBS_SRC), ("obs_noise", C.c_float * NUM_OBS_SRC), ("clip_obs", C.c_float),
         ("n_hist_keys", C.c_int32), ("hist_row", C.c_int32),
         ("hist_src", C.c_int32 * MAX_HIST_KEYS), ("hist_len", C.c_int32 * MAX_HIST_KEYS), ("hist_dim", C.c_int32 * MAX_HIST_KEYS),

@@ -26,3 +26,15 @@ int check_launch(const char* what) {
 
 extern "C" int pbhc_abi_version(void) { return PBHC_ABI_VERSION; }
 extern "C" const char* pbhc_last_error(void) { return pbhc::g_err; }
+extern "C" int64_t pbhc_struct_size(int32_t which) {
+  switch (which) {
+    case 0: return sizeof(PbhcTableDesc);
+    case 1: return sizeof(PbhcLookupOut);
+    case 2: return sizeof(PbhcTree);
+    case 3: return sizeof(PbhcTrackCfg);
+    case 4: return sizeof(PbhcTrackIO);
+    case 5: return sizeof(PbhcHistDst);
+    case 6: return sizeof(PbhcCurriculum);
+    default: return -1;
+  }
+}

@@ -1,9 +1,17 @@
-// track.cu - K3: the fused motion-tracking env step.  One warp owns one env per iteration of a
-// persistent grid-stride loop: lanes run over bodies (J <= 64), dofs (D <= 32) and flat record /
-// observation elements; everything per-env is staged once in per-warp shared memory (sim body state,
-// the lerped/slerped reference record, the scaled observation features + history) so that every global
-// access is a coalesced run of contiguous floats.  Cross-env sums (adaptive-sigma errors, log means,
-// reset statistics) are accumulated per block and reduced deterministically - no atomics, no host sync.
+// track.cu - K3: the fused motion-tracking env step (lookup + differences + termination + rewards + reset +
+// observations + history) as ONE persistent kernel.
+//
+// Mapping.  One warp owns one env per iteration of a grid-stride loop; lanes run over bodies (J <= 64), dofs
+// (D <= 32), reward terms and flat row elements.  Work that is scalar per env (frame index / blend, root-frame
+// velocities, heading quaternion) is hoisted into a "pre" phase where lane i computes it for the i-th env of the
+// warp's next 32 envs, so its cost is amortised over the lanes instead of being replicated 32x.  The observation
+// rows are assembled in per-warp shared memory in their final layout (each producer writes its value to every
+// group that contains it, the history ring is scattered in with a per-launch map) and leave with 128/64-bit
+// coalesced stores; simulator state enters with 128-bit loads.  The 16 per-env sums share one transposing
+// butterfly (16 shuffles instead of 80) whose per-value summation order equals the plain xor butterfly's.
+// Cross-env sums (adaptive-sigma errors, log means, reset statistics) are accumulated per lane in fp64 registers
+// and reduced deterministically - no atomics, no host sync.  Lane-indexed configuration lives in shared memory.
+// Arithmetic is the reference's unfused fp32 op sequence (-fmad=false): see DESIGN.md "arithmetic parity".
 // Reference: legged_robot_base.py:297-338, 346-380, 408-489, 715-793, 944-1087; motion_tracking.py:330-358,
 // 548-747, 1030-1328; helpers.py:128-152; history_handler.py:33-48 (paths under humanoidverse/envs|utils).
 #include "common.cuh"
@@ -11,17 +19,11 @@
 
 namespace pbhc {
 
-constexpr int kTW = 8;              // warps (envs in flight) per block
-constexpr int kTrackMaxBlocks = 148 * 4;
-
-struct TrackParams {
-  PbhcTrackCfg c;
-  PbhcTableDesc tab;
-  PbhcTrackIO io;
-  int64_t n;
-  int sm_body, sm_ref, sm_cf, sm_feat, sm_per_warp;  // per-warp shared-memory offsets (floats)
-  int src_off[PBHC_NUM_OBS_SRC + 1];                 // feature offsets of the observation sources; [last] = history
-};
+constexpr int kTW = 8;                      // warps (envs in flight) per block
+constexpr int kTrackMaxBlocks = 148 * 8;
+constexpr int kPre = 22;                    // per-env values of the pre phase
+constexpr int kRv = 48;                     // per-env scalar table (see enum Rv)
+constexpr int kMaxHistDstPerKey = 4;
 
 enum ObsSrc { S_BASE_LIN_VEL, S_BASE_ANG_VEL, S_PROJ_GRAV, S_DOF_POS, S_DOF_VEL, S_ACTIONS, S_PHASE, S_DIF_LOCAL,
               S_LOCAL_REF, S_DR_COM, S_DR_MASS, S_DR_KP, S_DR_KD, S_DR_FRICTION, S_DR_DELAY, S_LOCAL_REF_VEL,
@@ -31,6 +33,15 @@ enum RewardId { R_CONTACT_MASK, R_MAX_JOINT_POS, R_BODY_POS_EXT, R_VR3, R_FEET_P
                 R_STUMBLE, R_SLIPPAGE, R_LIM_DOF_POS, R_LIM_DOF_VEL, R_LIM_TORQUE, R_COLLISION, R_DOF_VEL, R_DOF_ACC,
                 R_FOOT_SLIP, R_ALIVE, R_ORIENTATION, R_CONTACT_MASK_V2 };
 enum SigmaId { G_MAX_JOINT, G_UPPER, G_LOWER, G_VR3, G_FEET, G_ROT, G_VEL, G_ANG_VEL, G_JOINT_POS, G_JOINT_VEL };
+// per-env scalar table `rv`: slots 0..22 are laid out like `acc` (PBHC_A_*), the rest are raw reward values
+enum Rv { V_SIGMA_ERR = 0, V_UP_N = 10, V_LO_N, V_VR_N, V_JOINT_N, V_T_GRAV, V_T_FAR, V_T_OUT, V_T_END, V_RESET, V_RESET_EPLEN,
+          V_ETR, V_ETR_SQ, V_ONE, V_CONTACT = 24, V_CONTACT_V2, V_TQ2, V_DACT2, V_DV2, V_ACC2, V_ORIENT, V_ALIVE, V_AIR, V_FORCE,
+          V_STUMBLE, V_SLIP, V_FSLIP, V_LIM_POS, V_LIM_VEL, V_LIM_TQ, V_COLLIDE };
+enum RewardKind { K_RAW, K_EXP, K_EXP2 };
+// pre-phase values (per env)
+enum Pre { P_F0, P_F1, P_BLEND, P_PHASE, P_HZ, P_HW, P_RPX, P_RPY, P_RPZ, P_BLV, P_BAV = P_BLV + 3, P_PG = P_BAV + 3,
+           P_CLIP = P_PG + 3, P_GRAVN, P_ORIENT };
+static_assert(P_ORIENT + 1 <= kPre, "pre table too small");
 
 __host__ __device__ inline int src_dim(int k, int D, int J, int L) {
   switch (k) {
@@ -42,6 +53,21 @@ __host__ __device__ inline int src_dim(int k, int D, int J, int L) {
   }
 }
 
+struct TrackParams {
+  PbhcTrackCfg c;
+  PbhcTableDesc tab;
+  PbhcTrackIO io;
+  int64_t n;
+  int row_off[PBHC_MAX_OBS_GROUPS + 1];  // smem offsets of the obs rows; [n_groups] = history push staging
+  int rows_len;                          // floats of `rows` (obs rows + push staging)
+  int push_len;                          // floats pushed into the history per step
+  int push_off[PBHC_MAX_HIST_KEYS];      // offset of key k inside the push staging
+  int hist_base[PBHC_MAX_HIST_KEYS];     // offset of key k inside the global history row
+  int sm_body, sm_cf, sm_rows, sm_rv, sm_pre, sm_per_warp;  // per-warp shared-memory offsets (floats)
+  int hist_any_mul;                      // some history destination has mul != 1
+  int n_hdst_max;                        // max destinations of one history element
+};
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
@@ -51,6 +77,24 @@ __device__ __forceinline__ float warp_max(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
   return v;
+}
+
+// Sums 16 per-lane values across the warp with 16 shuffles.  Round r keeps, in each lane, the half of the values
+// selected by one lane bit and adds the partner's copy of them; after the xor-16/8/4/2 rounds every lane holds one
+// value index ((lane >> 1) & 15), the xor-1 round completes it.  For each value the additions are the same pairs in
+// the same order as the plain xor butterfly (16, 8, 4, 2, 1), so the results are bit-identical to warp_sum().
+__device__ __forceinline__ float warp_sum16(float (&v)[16], int lane) {
+#pragma unroll
+  for (int half = 8, bit = 16; half >= 1; half >>= 1, bit >>= 1) {
+    const bool upper = (lane & bit) != 0;
+#pragma unroll
+    for (int i = 0; i < half; ++i) {
+      const float send = upper ? v[i] : v[i + half];
+      const float keep = upper ? v[i + half] : v[i];
+      v[i] = keep + __shfl_xor_sync(0xffffffffu, send, bit);
+    }
+  }
+  return v[0] + __shfl_xor_sync(0xffffffffu, v[0], 1);
 }
 
 // Philox4x32-10 (counter-based; one call per (env, step, stream))
@@ -87,439 +131,644 @@ __device__ __forceinline__ Q4 heading_quat_inv(Q4 q) {
   return {0.0f / n, 0.0f / n, sz / n, w / n};
 }
 
-struct Sums {  // per-lane partial sums over bodies, reduced across the warp afterwards
-  float up_sq, lo_sq, vr_sq, feet_sq, rot_sq, vel_sq, ang_sq, up_n, lo_n, vr_n, collide;
-  int far;
+// my_quat_rotate(q, v) for q = (0, 0, z, w) - the heading quaternion.  Same expression tree as quat_rotate_impl with
+// the terms that multiply q.x = q.y = 0 dropped: they are exact zeros, so only the sign of a zero result can differ.
+__device__ __forceinline__ V3 quat_rotate_z(float qz, float qw, V3 v) {
+  const float s = 2.0f * (qw * qw) - 1.0f;
+  const V3 a = {v.x * s, v.y * s, v.z * s};
+  const V3 b = {(0.0f - qz * v.y) * qw * 2.0f, (qz * v.x) * qw * 2.0f, 0.0f};
+  const float d = qz * v.z;
+  return {a.x + b.x, a.y + b.y, a.z + qz * d * 2.0f};
+}
+
+// block-level tables (built once per block from the launch parameters)
+struct BlockTables {
+  double scal[PBHC_SCALARS];
+  double acc[kTW][PBHC_ACC];
+  float lim_lo[PBHC_MAX_DOF], lim_hi[PBHC_MAX_DOF], lim_vel[PBHC_MAX_DOF], lim_tq[PBHC_MAX_DOF];
+  float r_scale[PBHC_MAX_REWARDS], r_pen[PBHC_MAX_REWARDS], r_sigma[PBHC_MAX_REWARDS];
+  int r_kind[PBHC_MAX_REWARDS], r_arg[PBHC_MAX_REWARDS];
+  float sum_div[16];                 // divisor applied to the k-th value of the 16-way reduction
+  int sum_slot[16];                  // rv slot of the k-th value
+  int sdst[PBHC_NUM_OBS_SRC][8];     // smem row offset of source k in each obs group [0..3] / the push staging [4] (-1: none)
+  float obs_scale[PBHC_NUM_OBS_SRC];
+  int hist_head_w[PBHC_MAX_HIST_KEYS];
 };
 
-__global__ void __launch_bounds__(kTW * 32) track_kernel(const __grid_constant__ TrackParams P) {
-  extern __shared__ float smem[];
-  __shared__ double sm_scal[PBHC_SCALARS];
-  __shared__ double sm_acc[kTW][PBHC_ACC];
+// k-th value of the 16-way reduction
+enum Sum16 { U_UP_SQ, U_LO_SQ, U_VR_SQ, U_FEET_SQ, U_ROT_SQ, U_VEL_SQ, U_ANG_SQ, U_UP_N, U_LO_N, U_VR_N, U_DJA2, U_DJV2, U_TQ2,
+             U_DACT2, U_DV2, U_ACC2 };
+
+__device__ void build_tables(const TrackParams& P, BlockTables& T, int* hmap, int* pmap) {
+  const PbhcTrackCfg& c = P.c;
+  const int tid = threadIdx.x, nt = blockDim.x;
+  for (int i = tid; i < PBHC_SCALARS; i += nt) T.scal[i] = P.io.scalars[i];
+  for (int i = tid; i < kTW * PBHC_ACC; i += nt) (&T.acc[0][0])[i] = 0.0;
+  __syncthreads();
+  const uint64_t push_count = (uint64_t)T.scal[PBHC_S_PUSH_COUNT];
+  if (tid < c.D) {  // soft limits of this launch (legged_robot_base.py:974-1002); the curriculum values are launch constants
+    float lo = c.soft_lo[tid], hi = c.soft_hi[tid];
+    if (c.cur_dof_pos.enable) {
+      const float m = (c.hard_lo[tid] + c.hard_hi[tid]) / 2.0f, r = c.hard_hi[tid] - c.hard_lo[tid];
+      const float cv = (float)T.scal[PBHC_S_SOFT_DOF_POS];
+      lo = m - 0.5f * r * cv; hi = m + 0.5f * r * cv;
+    }
+    T.lim_lo[tid] = lo; T.lim_hi[tid] = hi;
+    const float vs = c.cur_dof_vel.enable ? (float)T.scal[PBHC_S_SOFT_DOF_VEL] : c.soft_dof_vel_limit;
+    T.lim_vel[tid] = c.vel_limit[tid] * vs;
+    T.lim_tq[tid] = c.torque_limit[tid] * (c.cur_torque.enable ? (float)T.scal[PBHC_S_SOFT_TORQUE] : c.soft_torque_limit);
+  }
+  if (tid < PBHC_MAX_REWARDS) {
+    int kind = K_RAW, arg = V_ONE;
+    float sig = 1.0f;
+    if (tid < c.n_rewards) {
+      switch (c.reward_id[tid]) {
+        case R_CONTACT_MASK: arg = V_CONTACT; break;
+        case R_CONTACT_MASK_V2: arg = V_CONTACT_V2; break;
+        case R_MAX_JOINT_POS: kind = K_EXP; arg = G_MAX_JOINT; break;
+        case R_BODY_POS_EXT: kind = K_EXP2; arg = G_LOWER; break;
+        case R_VR3: kind = K_EXP; arg = G_VR3; break;
+        case R_FEET_POS: kind = K_EXP; arg = G_FEET; break;
+        case R_BODY_ROT: kind = K_EXP; arg = G_ROT; break;
+        case R_BODY_ANG_VEL: kind = K_EXP; arg = G_ANG_VEL; break;
+        case R_BODY_VEL: kind = K_EXP; arg = G_VEL; break;
+        case R_JOINT_POS: kind = K_EXP; arg = G_JOINT_POS; break;
+        case R_JOINT_VEL: kind = K_EXP; arg = G_JOINT_VEL; break;
+        case R_TORQUES: arg = V_TQ2; break;
+        case R_ACTION_RATE: arg = V_DACT2; break;
+        case R_DOF_VEL: arg = V_DV2; break;
+        case R_DOF_ACC: arg = V_ACC2; break;
+        case R_ORIENTATION: arg = V_ORIENT; break;
+        case R_ALIVE: arg = V_ALIVE; break;
+        case R_FEET_AIR_TIME: arg = V_AIR; break;
+        case R_FEET_FORCES: arg = V_FORCE; break;
+        case R_STUMBLE: arg = V_STUMBLE; break;
+        case R_SLIPPAGE: arg = V_SLIP; break;
+        case R_FOOT_SLIP: arg = V_FSLIP; break;
+        case R_LIM_DOF_POS: arg = V_LIM_POS; break;
+        case R_LIM_DOF_VEL: arg = V_LIM_VEL; break;
+        case R_LIM_TORQUE: arg = V_LIM_TQ; break;
+        case R_COLLISION: arg = V_COLLIDE; break;
+        default: break;
+      }
+      if (kind != K_RAW) sig = (float)T.scal[PBHC_S_SIGMA + arg];
+    }
+    T.r_kind[tid] = kind; T.r_arg[tid] = arg; T.r_sigma[tid] = sig;
+    T.r_scale[tid] = tid < c.n_rewards ? c.reward_scale[tid] : 0.0f;
+    T.r_pen[tid] = (tid < c.n_rewards && c.reward_is_penalty[tid]) ? (float)T.scal[PBHC_S_PENALTY] : 1.0f;
+  }
+  if (tid < 16) {
+    float div = 1.0f; int slot = 0;
+    switch (tid) {
+      case U_UP_SQ: div = (float)c.n_upper; slot = V_SIGMA_ERR + G_UPPER; break;
+      case U_LO_SQ: div = (float)c.n_lower; slot = V_SIGMA_ERR + G_LOWER; break;
+      case U_VR_SQ: div = (float)c.n_vr3; slot = V_SIGMA_ERR + G_VR3; break;
+      case U_FEET_SQ: div = (float)c.n_feet; slot = V_SIGMA_ERR + G_FEET; break;
+      case U_ROT_SQ: div = (float)c.J; slot = V_SIGMA_ERR + G_ROT; break;
+      case U_VEL_SQ: div = (float)c.J; slot = V_SIGMA_ERR + G_VEL; break;
+      case U_ANG_SQ: div = (float)c.J; slot = V_SIGMA_ERR + G_ANG_VEL; break;
+      case U_UP_N: slot = V_UP_N; break;
+      case U_LO_N: slot = V_LO_N; break;
+      case U_VR_N: slot = V_VR_N; break;
+      case U_DJA2: div = (float)c.D; slot = V_SIGMA_ERR + G_JOINT_POS; break;
+      case U_DJV2: div = (float)c.D; slot = V_SIGMA_ERR + G_JOINT_VEL; break;
+      case U_TQ2: slot = V_TQ2; break;
+      case U_DACT2: slot = V_DACT2; break;
+      case U_DV2: slot = V_DV2; break;
+      default: slot = V_ACC2; break;
+    }
+    T.sum_div[tid] = div; T.sum_slot[tid] = slot;
+  }
+  for (int i = tid; i < PBHC_NUM_OBS_SRC * 8; i += nt) {
+    const int k = i >> 3, g = i & 7;
+    int off = -1;
+    if (g < PBHC_MAX_OBS_GROUPS) { if (g < c.n_groups && c.src_dst[k][g] >= 0) off = P.row_off[g] + c.src_dst[k][g]; }
+    else if (g == PBHC_MAX_OBS_GROUPS) for (int h = 0; h < c.n_hist_keys; ++h) if (c.hist_src[h] == k) off = P.row_off[c.n_groups] + P.push_off[h];
+    T.sdst[k][g] = off;
+  }
+  if (tid < PBHC_NUM_OBS_SRC) T.obs_scale[tid] = c.obs_scale[tid];
+  // history ring: physical slot of logical slot s of key k is (head_k + s) % len_k, head_k = -push_count mod len_k
+  // (HistoryHandler keeps newest-first order, history_handler.py:40-48).  hmap[d][i]: smem destination of physical
+  // element i of the global history row in the d-th obs segment that shows it; pmap[i]: physical element that
+  // receives push element i.
+  if (tid < c.n_hist_keys) {
+    const int len = c.hist_len[tid];
+    T.hist_head_w[tid] = (int)((len - ((push_count + 1) % len)) % len);
+  }
+  for (int i = tid; i < c.hist_row; i += nt) {
+    int k = 0;
+    while (k + 1 < c.n_hist_keys && i >= P.hist_base[k + 1]) ++k;
+    const int len = c.hist_len[k], dim = c.hist_dim[k];
+    const int r = i - P.hist_base[k], ps = r / dim, cc = r - ps * dim;
+    const int head = (int)((len - (push_count % len)) % len);
+    const int s = (ps - head + len) % len;  // logical slot
+    int nd = 0;
+    for (int e = 0; e < c.n_hist_dst && nd < kMaxHistDstPerKey; ++e) {
+      const PbhcHistDst& h = c.hist_dst[e];
+      if (h.key != k) continue;
+      hmap[nd * c.hist_row + i] = s < h.len ? ((P.row_off[h.group] + h.offset + s * dim + cc) | (e << 24)) : -1;
+      ++nd;
+    }
+    for (; nd < P.n_hdst_max; ++nd) hmap[nd * c.hist_row + i] = -1;
+  }
+  __syncthreads();
+  for (int i = tid; i < P.push_len; i += nt) {
+    int k = 0;
+    while (k + 1 < c.n_hist_keys && i >= P.push_off[k + 1]) ++k;
+    pmap[i] = P.hist_base[k] + T.hist_head_w[k] * c.hist_dim[k] + (i - P.push_off[k]);
+  }
+  __syncthreads();
+}
+
+// writes `v` of element `e` of one observation source into every row that shows it (sd = T.sdst[source])
+__device__ __forceinline__ void put1(const int* sd, float* rows, int e, float v) {
+  const int4 d = *reinterpret_cast<const int4*>(sd);
+  const int push = sd[4];
+  if (d.x >= 0) rows[d.x + e] = v;
+  if (d.y >= 0) rows[d.y + e] = v;
+  if (d.z >= 0) rows[d.z + e] = v;
+  if (d.w >= 0) rows[d.w + e] = v;
+  if (push >= 0) rows[push + e] = v;
+}
+__device__ __forceinline__ void put3(const int* sd, float* rows, int e, float x, float y, float z) {
+  const int4 d = *reinterpret_cast<const int4*>(sd);
+  const int push = sd[4];
+  if (d.x >= 0) { rows[d.x + e] = x; rows[d.x + e + 1] = y; rows[d.x + e + 2] = z; }
+  if (d.y >= 0) { rows[d.y + e] = x; rows[d.y + e + 1] = y; rows[d.y + e + 2] = z; }
+  if (d.z >= 0) { rows[d.z + e] = x; rows[d.z + e + 1] = y; rows[d.z + e + 2] = z; }
+  if (d.w >= 0) { rows[d.w + e] = x; rows[d.w + e + 1] = y; rows[d.w + e + 2] = z; }
+  if (push >= 0) { rows[push + e] = x; rows[push + e + 1] = y; rows[push + e + 2] = z; }
+}
+
+// global -> shared copy of `count` floats with the widest vector the row alignment allows (vec = 4, 2 or 1)
+__device__ __forceinline__ void warp_load(float* dst, const float* src, int count, int vec, int lane) {
+  if (vec == 4) {
+    const float4* s = reinterpret_cast<const float4*>(src);
+    float4* d = reinterpret_cast<float4*>(dst);
+    for (int i = lane; i < (count >> 2); i += 32) d[i] = s[i];
+    for (int i = (count & ~3) + lane; i < count; i += 32) dst[i] = src[i];
+  } else if (vec == 2) {
+    const float2* s = reinterpret_cast<const float2*>(src);
+    float2* d = reinterpret_cast<float2*>(dst);
+    for (int i = lane; i < (count >> 1); i += 32) d[i] = s[i];
+    if ((count & 1) && lane == 0) dst[count - 1] = src[count - 1];
+  } else {
+    for (int i = lane; i < count; i += 32) dst[i] = src[i];
+  }
+}
+
+// shared -> global copy of one observation row, clipped to +-clip (legged_robot_base.py:326-328)
+__device__ __forceinline__ void warp_store_clipped(float* dst, const float* src, int count, int vec, float clip, int lane) {
+  if (vec == 4) {
+    const float4* s = reinterpret_cast<const float4*>(src);
+    float4* d = reinterpret_cast<float4*>(dst);
+    for (int i = lane; i < (count >> 2); i += 32) {
+      float4 v = s[i];
+      v.x = fminf(fmaxf(v.x, -clip), clip); v.y = fminf(fmaxf(v.y, -clip), clip);
+      v.z = fminf(fmaxf(v.z, -clip), clip); v.w = fminf(fmaxf(v.w, -clip), clip);
+      d[i] = v;
+    }
+  } else if (vec == 2) {
+    const float2* s = reinterpret_cast<const float2*>(src);
+    float2* d = reinterpret_cast<float2*>(dst);
+    for (int i = lane; i < (count >> 1); i += 32) {
+      float2 v = s[i];
+      v.x = fminf(fmaxf(v.x, -clip), clip); v.y = fminf(fmaxf(v.y, -clip), clip);
+      d[i] = v;
+    }
+  } else {
+    for (int i = lane; i < count; i += 32) dst[i] = fminf(fmaxf(src[i], -clip), clip);
+  }
+}
+
+__host__ __device__ inline int vec_of(int64_t row_floats, const void* base) {
+  const uintptr_t a = (uintptr_t)base;
+  if ((row_floats & 3) == 0 && (a & 15) == 0) return 4;
+  if ((row_floats & 1) == 0 && (a & 7) == 0) return 2;
+  return 1;
+}
+
+__device__ __forceinline__ int up4(int v) { return (v + 3) & ~3; }
+
+__global__ void __launch_bounds__(kTW * 32, 3) track_kernel(const __grid_constant__ TrackParams P) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  BlockTables& T = *reinterpret_cast<BlockTables*>(smem_raw);
   const PbhcTrackCfg& c = P.c;
   const PbhcTrackIO& io = P.io;
   const PbhcTableDesc& tab = P.tab;
+  int* hmap = reinterpret_cast<int*>(smem_raw + ((sizeof(BlockTables) + 15) & ~size_t(15)));
+  int* pmap = hmap + up4(P.n_hdst_max * c.hist_row);
+  float* wbase = reinterpret_cast<float*>(pmap + up4(P.push_len));
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int J = c.J, Jb = c.Jb, D = c.D, L = c.L, Cm = tab.contact_size;
-  float* sm_body = smem + warp * P.sm_per_warp + P.sm_body;
-  float* sm_ref = smem + warp * P.sm_per_warp + P.sm_ref;
-  float* sm_cf = smem + warp * P.sm_per_warp + P.sm_cf;
-  float* feat = smem + warp * P.sm_per_warp + P.sm_feat;
-  for (int i = threadIdx.x; i < PBHC_SCALARS; i += blockDim.x) sm_scal[i] = io.scalars[i];
-  for (int i = threadIdx.x; i < kTW * PBHC_ACC; i += blockDim.x) (&sm_acc[0][0])[i] = 0.0;
-  __syncthreads();
-  double* acc = sm_acc[warp];
-  const float far_thr = (float)sm_scal[PBHC_S_FAR_THR];
-  const float penalty_scale = (float)sm_scal[PBHC_S_PENALTY];
-  const uint64_t push_count = (uint64_t)sm_scal[PBHC_S_PUSH_COUNT];
-  const int e_pos = 4 * J, e_vel = 7 * J, e_ang = 10 * J, e_dp = 13 * J, e_dv = e_dp + D, e_c = e_dv + D, e_end = e_c + Cm;
-  const int hist_off = P.src_off[PBHC_NUM_OBS_SRC];
+  float* sm_body = wbase + warp * P.sm_per_warp + P.sm_body;
+  float* sm_cf = wbase + warp * P.sm_per_warp + P.sm_cf;
+  float* rows = wbase + warp * P.sm_per_warp + P.sm_rows;
+  float* rv = wbase + warp * P.sm_per_warp + P.sm_rv;
+  float* pre = wbase + warp * P.sm_per_warp + P.sm_pre;
+  build_tables(P, T, hmap, pmap);
 
-  for (int64_t n = (int64_t)blockIdx.x * kTW + warp; n < P.n; n += (int64_t)gridDim.x * kTW) {
+  const float far_thr = (float)T.scal[PBHC_S_FAR_THR];
+  const uint32_t push_count = (uint32_t)(uint64_t)T.scal[PBHC_S_PUSH_COUNT];
+  const int e_pos = 4 * J, e_vel = 7 * J, e_ang = 10 * J, e_dp = 13 * J, e_dv = e_dp + D, e_c = e_dv + D;
+  const int body_vec = vec_of(io.body_env_stride, io.body_state) == 4 && ((Jb * 13) & 3) == 0 ? 4
+                       : (vec_of(io.body_env_stride, io.body_state) >= 2 && ((Jb * 13) & 1) == 0 ? 2 : 1);
+  const int cf_vec = vec_of(Jb * 3, io.contact_forces);
+  const int hist_vec = c.hist_row > 0 ? vec_of(c.hist_row, io.hist) : 1;
+  uint64_t feet_mask = 0;
+  for (int f = 0; f < c.n_feet; ++f) feet_mask |= 1ull << c.feet_ids[f];
+  const int my_foot = lane < c.n_feet ? (lane == 0 ? c.feet_ids[0] : c.feet_ids[1]) : 0;
+  const bool ld = lane < D;
+  const float lim_lo = ld ? T.lim_lo[lane] : 0.f, lim_hi = ld ? T.lim_hi[lane] : 0.f;
+  const float lim_v = ld ? T.lim_vel[lane] : 0.f, lim_t = ld ? T.lim_tq[lane] : 0.f;
+  double acc_reg = 0.0;
+
+  const int64_t stride = (int64_t)gridDim.x * kTW;
+  for (int64_t chunk = (int64_t)blockIdx.x * kTW + warp; chunk < P.n; chunk += 32 * stride) {
+    // ---- pre phase: lane i = i-th env of this chunk (legged_robot_base.py:346-353, motion_tracking.py:548-558, 678-739) ----
     __syncwarp();
-    // ---- A. per-env scalars ------------------------------------------------------------------
-    int64_t ep = io.episode_length_buf[n] + 1;  // legged_robot_base.py:299
-    const int64_t last_ep = ep;
-    float* envf = io.env_f32 + n * PBHC_ENVF_STRIDE;
-    float start = envf[0], mlen = envf[1];
-    float air[PBHC_MAX_FEET], last_c[PBHC_MAX_FEET];
-#pragma unroll
-    for (int f = 0; f < 2; ++f) { air[f] = envf[2 + f]; last_c[f] = envf[4 + f]; }
-    float etr = envf[6];
-    const int clip = resolve_clip(tab, io.clip_of_motion, io.motion_ids[n]);
-    const float t = (float)(ep + 1) * c.dt + start;  // kick_motion_res, motion_tracking.py:554
-    const FrameBlend fb = frame_blend(tab, clip, t);
-    const float b = fb.blend, omb = 1.0f - b;
-    const float* r0 = tab.records + fb.f0 * tab.rec_stride;
-    const float* r1 = tab.records + fb.f1 * tab.rec_stride;
-    const float org[3] = {io.env_origins[n * 3], io.env_origins[n * 3 + 1], io.env_origins[n * 3 + 2]};
-    // ---- C. stage sim body state, contact forces, reference record, history ------------------
     {
-      const float* g = io.body_state + n * io.body_env_stride;
-      for (int i = lane; i < Jb * 13; i += 32) sm_body[i] = g[i];
-      const float* gc = io.contact_forces + n * (Jb * 3);
-      for (int i = lane; i < Jb * 3; i += 32) sm_cf[i] = gc[i];
-      for (int j = lane; j < J; j += 32) {
-        const float4 a = __ldg(reinterpret_cast<const float4*>(r0) + j);
-        const float4 d = __ldg(reinterpret_cast<const float4*>(r1) + j);
-        const Q4 s = slerp({a.x, a.y, a.z, a.w}, {d.x, d.y, d.z, d.w}, b);
-        sm_ref[4 * j] = s.x; sm_ref[4 * j + 1] = s.y; sm_ref[4 * j + 2] = s.z; sm_ref[4 * j + 3] = s.w;
-      }
-#pragma unroll 4
-      for (int e = e_pos + lane; e < e_end; e += 32) {
-        float v = omb * __ldg(r0 + e) + b * __ldg(r1 + e);
-        if (e < e_vel) v = v + org[(e - e_pos) % 3];
-        sm_ref[e] = v;
-      }
-      // history, rotated into logical (newest-first) order
-      const float* gh = io.hist + n * c.hist_row;
-      int base = 0;
-      for (int k = 0; k < c.n_hist_keys; ++k) {
-        const int len = c.hist_len[k], dim = c.hist_dim[k];
-        const int head = (int)((len - (push_count % len)) % len);
-        for (int i = lane; i < len * dim; i += 32) {
-          const int s = i / dim, cc = i - s * dim;
-          int ps = head + s; if (ps >= len) ps -= len;
-          feat[hist_off + base + i] = gh[base + ps * dim + cc];
-        }
-        base += len * dim;
+      const int64_t m = chunk + (int64_t)lane * stride;
+      if (m < P.n) {
+        const int64_t ep = io.episode_length_buf[m] + 1;  // legged_robot_base.py:299
+        const float start = io.env_f32[m * PBHC_ENVF_STRIDE];
+        const int clip = resolve_clip(tab, io.clip_of_motion, io.motion_ids[m]);
+        const float t = (float)(ep + 1) * c.dt + start;  // kick_motion_res, motion_tracking.py:554
+        const FrameBlend fb = frame_blend(tab, clip, t);
+        const float* root = io.root_state + m * 13;
+        const Q4 rq = {root[3], root[4], root[5], root[6]};
+        const V3 blv = quat_rotate_inverse(rq, {root[7], root[8], root[9]});
+        const V3 bav = quat_rotate_inverse(rq, {root[10], root[11], root[12]});
+        const V3 pg = quat_rotate_inverse(rq, {0.0f, 0.0f, -1.0f});
+        const Q4 hinv = heading_quat_inv(rq);
+        pre[P_F0 * 32 + lane] = __int_as_float((int)fb.f0);
+        pre[P_F1 * 32 + lane] = __int_as_float((int)fb.f1);
+        pre[P_BLEND * 32 + lane] = fb.blend;
+        pre[P_PHASE * 32 + lane] = t / tab.clip_length[clip];  // motion_tracking.py:738-739
+        pre[P_HZ * 32 + lane] = hinv.z; pre[P_HW * 32 + lane] = hinv.w;
+        pre[P_RPX * 32 + lane] = root[0]; pre[P_RPY * 32 + lane] = root[1]; pre[P_RPZ * 32 + lane] = root[2];
+        pre[(P_BLV + 0) * 32 + lane] = blv.x; pre[(P_BLV + 1) * 32 + lane] = blv.y; pre[(P_BLV + 2) * 32 + lane] = blv.z;
+        pre[(P_BAV + 0) * 32 + lane] = bav.x; pre[(P_BAV + 1) * 32 + lane] = bav.y; pre[(P_BAV + 2) * 32 + lane] = bav.z;
+        pre[(P_PG + 0) * 32 + lane] = pg.x; pre[(P_PG + 1) * 32 + lane] = pg.y; pre[(P_PG + 2) * 32 + lane] = pg.z;
+        pre[P_CLIP * 32 + lane] = __int_as_float(clip);
+        pre[P_GRAVN * 32 + lane] = norm2(pg.x, pg.y);
+        pre[P_ORIENT * 32 + lane] = pg.x * pg.x + pg.y * pg.y;
       }
     }
     __syncwarp();
-    // ---- D. root quantities (legged_robot_base.py:346-353) -----------------------------------
-    float* root = io.root_state + n * 13;
-    const V3 rp = {root[0], root[1], root[2]};
-    const Q4 rq = {root[3], root[4], root[5], root[6]};
-    const V3 blv = quat_rotate_inverse(rq, {root[7], root[8], root[9]});
-    const V3 bav = quat_rotate_inverse(rq, {root[10], root[11], root[12]});
-    const V3 pg = quat_rotate_inverse(rq, {0.0f, 0.0f, -1.0f});
-    const Q4 hinv = heading_quat_inv(rq);
-    // ---- E. bodies: extended state, differences, heading-frame features ----------------------
-    Sums s = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
-    uint64_t feet_mask = 0;
-    for (int f = 0; f < c.n_feet; ++f) feet_mask |= 1ull << c.feet_ids[f];
-    for (int j = lane; j < J; j += 32) {
-      V3 p, v, w; Q4 q;
-      if (j < Jb) {
-        const float* bs = sm_body + j * 13;
-        p = {bs[0], bs[1], bs[2]}; q = {bs[3], bs[4], bs[5], bs[6]}; v = {bs[7], bs[8], bs[9]}; w = {bs[10], bs[11], bs[12]};
-      } else {  // motion_tracking.py:619-643
-        const int x = j - Jb;
-        const float* bs = sm_body + c.ext_parent[x] * 13;
-        const Q4 qp = {bs[3], bs[4], bs[5], bs[6]};
-        const V3 off = {c.ext_pos[x][0], c.ext_pos[x][1], c.ext_pos[x][2]};
-        const Q4 qe = {c.ext_rot_xyzw[x][0], c.ext_rot_xyzw[x][1], c.ext_rot_xyzw[x][2], c.ext_rot_xyzw[x][3]};
-        const V3 r = quat_rotate(qe, quat_rotate(qp, off));
-        p = {r.x + bs[0], r.y + bs[1], r.z + bs[2]};
-        q = quat_mul(qp, qe);
-        w = {bs[10], bs[11], bs[12]};
-        v = {bs[7] + (w.y * off.z - w.z * off.y), bs[8] + (w.z * off.x - w.x * off.z), bs[9] + (w.x * off.y - w.y * off.x)};
-      }
-      const float* rr = sm_ref + 4 * j;
-      const float* rpz = sm_ref + e_pos + 3 * j;
-      const float* rv = sm_ref + e_vel + 3 * j;
-      const float* rw = sm_ref + e_ang + 3 * j;
-      const V3 dp = {rpz[0] - p.x, rpz[1] - p.y, rpz[2] - p.z};
-      const float dq0 = rr[0] - q.x, dq1 = rr[1] - q.y, dq2 = rr[2] - q.z, dq3 = rr[3] - q.w;
-      const V3 dv = {rv[0] - v.x, rv[1] - v.y, rv[2] - v.z};
-      const V3 dw = {rw[0] - w.x, rw[1] - w.y, rw[2] - w.z};
-      const float m_pos = ((dp.x * dp.x + dp.y * dp.y) + dp.z * dp.z) / 3.0f;
-      const float nrm = norm3(dp.x, dp.y, dp.z);
-      const uint64_t bit = 1ull << j;
-      if (c.upper_mask & bit) { s.up_sq += m_pos; s.up_n += nrm; }
-      if (c.lower_mask & bit) { s.lo_sq += m_pos; s.lo_n += nrm; }
-      if (c.vr3_mask & bit) { s.vr_sq += m_pos; s.vr_n += nrm; }
-      if (feet_mask & bit) s.feet_sq += m_pos;
-      s.rot_sq += (((dq0 * dq0 + dq1 * dq1) + dq2 * dq2) + dq3 * dq3) / 4.0f;
-      s.vel_sq += ((dv.x * dv.x + dv.y * dv.y) + dv.z * dv.z) / 3.0f;
-      s.ang_sq += ((dw.x * dw.x + dw.y * dw.y) + dw.z * dw.z) / 3.0f;
-      if (nrm > far_thr) s.far = 1;
-      if (j < Jb && (c.penalised_mask & bit)) {
-        const float* fc = sm_cf + 3 * j;
-        if (norm3(fc[0], fc[1], fc[2]) > 0.1f) s.collide += 1.0f;
-      }
-      const V3 dl = quat_rotate(hinv, dp);  // motion_tracking.py:694-697
-      float* f0 = feat + P.src_off[S_DIF_LOCAL] + 3 * j;
-      const float sc0 = c.obs_scale[S_DIF_LOCAL];
-      f0[0] = dl.x * sc0; f0[1] = dl.y * sc0; f0[2] = dl.z * sc0;
-      const V3 lr = quat_rotate(hinv, {rpz[0] - rp.x, rpz[1] - rp.y, rpz[2] - rp.z});  // :705-707
-      float* f1 = feat + P.src_off[S_LOCAL_REF] + 3 * j;
-      const float sc1 = c.obs_scale[S_LOCAL_REF];
-      f1[0] = lr.x * sc1; f1[1] = lr.y * sc1; f1[2] = lr.z * sc1;
-      if (c.src_used_mask & ((1u << S_LOCAL_REF_VEL) | (1u << S_GLOBAL_REF_VEL))) {
-        const V3 lv = quat_rotate(hinv, {rv[0], rv[1], rv[2]});
-        float* f2 = feat + P.src_off[S_LOCAL_REF_VEL] + 3 * j;
-        float* f3 = feat + P.src_off[S_GLOBAL_REF_VEL] + 3 * j;
-        const float sc2 = c.obs_scale[S_LOCAL_REF_VEL], sc3 = c.obs_scale[S_GLOBAL_REF_VEL];
-        f2[0] = lv.x * sc2; f2[1] = lv.y * sc2; f2[2] = lv.z * sc2;
-        f3[0] = rv[0] * sc3; f3[1] = rv[1] * sc3; f3[2] = rv[2] * sc3;
-      }
-    }
-    s.up_sq = warp_sum(s.up_sq); s.lo_sq = warp_sum(s.lo_sq); s.vr_sq = warp_sum(s.vr_sq); s.feet_sq = warp_sum(s.feet_sq);
-    s.rot_sq = warp_sum(s.rot_sq); s.vel_sq = warp_sum(s.vel_sq); s.ang_sq = warp_sum(s.ang_sq);
-    s.up_n = warp_sum(s.up_n); s.lo_n = warp_sum(s.lo_n); s.vr_n = warp_sum(s.vr_n); s.collide = warp_sum(s.collide);
-    const bool far = __any_sync(0xffffffffu, s.far);
-    // ---- F. dofs (lane = dof) ---------------------------------------------------------------------
-    const bool ld = lane < D;
-    float dpos = 0.f, dvel = 0.f, act = 0.f, tq = 0.f, lact = 0.f, ldv = 0.f, ddef = 0.f;
-    if (ld) {
-      const float2 ds = reinterpret_cast<const float2*>(io.dof_state)[n * D + lane];
-      dpos = ds.x; dvel = ds.y;
-      act = io.actions[n * D + lane]; tq = io.torques[n * D + lane];
-      lact = io.last_actions[n * D + lane]; ldv = io.last_dof_vel[n * D + lane];
-      ddef = io.default_dof_pos[n * io.default_dof_stride + lane];
-    }
-    const float dja = ld ? sm_ref[e_dp + lane] - dpos : 0.f;   // motion_tracking.py:661-665
-    const float djv = ld ? sm_ref[e_dv + lane] - dvel : 0.f;
-    const float max_dja = warp_max(fabsf(dja));
-    const float sum_dja2 = warp_sum(dja * dja);
-    const float sum_djv2 = warp_sum(djv * djv);
-    const float sum_tq2 = warp_sum(tq * tq);
-    const float dact = lact - act;
-    const float sum_dact2 = warp_sum(dact * dact);
-    const float sum_dv2 = warp_sum(dvel * dvel);
-    const float dacc = (ldv - dvel) / c.dt;
-    const float sum_acc2 = warp_sum(ld ? dacc * dacc : 0.f);
-    float lim_pos = 0.f, lim_vel = 0.f, lim_tq = 0.f;
-    if (ld) {
-      float lo = c.soft_lo[lane], hi = c.soft_hi[lane];
-      if (c.cur_dof_pos.enable) {  // legged_robot_base.py:977-981
-        const float m = (c.hard_lo[lane] + c.hard_hi[lane]) / 2.0f, r = c.hard_hi[lane] - c.hard_lo[lane];
-        const float cv = (float)sm_scal[PBHC_S_SOFT_DOF_POS];
-        lo = m - 0.5f * r * cv; hi = m + 0.5f * r * cv;
-      }
-      lim_pos = -fminf(dpos - lo, 0.0f) + fmaxf(dpos - hi, 0.0f);
-      const float vs = c.cur_dof_vel.enable ? (float)sm_scal[PBHC_S_SOFT_DOF_VEL] : c.soft_dof_vel_limit;
-      lim_vel = fminf(fmaxf(fabsf(dvel) - c.vel_limit[lane] * vs, 0.0f), 1.0f);
-      if (c.cur_torque.enable) lim_tq = fminf(fmaxf(fabsf(tq) - c.torque_limit[lane] * (float)sm_scal[PBHC_S_SOFT_TORQUE], 0.0f), 1.0f);
-      else lim_tq = fmaxf(fabsf(tq) - c.torque_limit[lane] * c.soft_torque_limit, 0.0f);
-    }
-    lim_pos = warp_sum(lim_pos); lim_vel = warp_sum(lim_vel); lim_tq = warp_sum(lim_tq);
-    // ---- G. feet (uniform across lanes) -------------------------------------------------------------
-    float contacts[PBHC_MAX_FEET], filt[PBHC_MAX_FEET];
-    float r_air = 0.f, r_force = 0.f, r_slip = 0.f, r_fslip = 0.f, cm_err = 0.f;
-    bool stumble = false;
-    for (int f = 0; f < c.n_feet; ++f) {
-      const float* fc = sm_cf + 3 * c.feet_ids[f];
-      const float* bs = sm_body + 13 * c.feet_ids[f];
-      const float fn = norm3(fc[0], fc[1], fc[2]);
-      contacts[f] = fn > 1.0f ? 1.0f : 0.0f;                                  // legged_robot_base.py:352-353
-      filt[f] = (contacts[f] != 0.0f || last_c[f] != 0.0f) ? 1.0f : 0.0f;
-      if (Cm) cm_err += fabsf(filt[f] - sm_ref[e_c + f]);
-      // feet_air_time, motion_tracking.py:1307-1319 (uses last_contacts of the previous step)
-      const bool cz = fc[2] > 1.0f;
-      const bool fz = cz || last_c[f] != 0.0f;
-      const float first = (air[f] > 0.0f && fz) ? 1.0f : 0.0f;
-      air[f] += c.dt;
-      r_air += (air[f] - c.desired_feet_air_time) * first;
-      air[f] *= fz ? 0.0f : 1.0f;
-      r_force += fmaxf(fn - c.max_contact_force, 0.0f);                        // :1321-1323
-      if (norm2(fc[0], fc[1]) > 5.0f * fabsf(fc[2])) stumble = true;           // :1325-1328
-      r_slip += norm3(bs[7], bs[8], bs[9]) * (fn > 1.0f ? 1.0f : 0.0f);        // legged_robot_base.py:1004-1010
-      r_fslip += (fn > 1.0f ? 1.0f : 0.0f) * norm2(bs[7], bs[8]);              // :1012-1017
-    }
-    // ---- H. termination (legged_robot_base.py:408-489, motion_tracking.py:330-358) ---------------------
-    const bool t_grav = c.term_gravity && norm2(pg.x, pg.y) > c.term_gravity_thr;
-    const bool t_far = c.term_motion_far && far;
-    const bool t_out = ep > c.max_episode_length;
-    const bool t_end = c.term_motion_end && ((float)ep * c.dt + start > mlen);
-    const bool time_out = t_out || t_end;
-    const bool reset = t_grav || t_far || time_out;
-    // ---- I. rewards (lane = reward term) ----------------------------------------------------------------
-    const float e_up = s.up_sq / (float)c.n_upper, e_lo = s.lo_sq / (float)c.n_lower, e_vr = s.vr_sq / (float)c.n_vr3;
-    const float e_feet = s.feet_sq / (float)c.n_feet, e_rot = s.rot_sq / (float)J, e_vel2 = s.vel_sq / (float)J, e_ang2 = s.ang_sq / (float)J;
-    const float e_jp = sum_dja2 / (float)D, e_jv = sum_djv2 / (float)D;
-    float rew = 0.0f;
-    if (lane < c.n_rewards) {
-      const double* sg = sm_scal + PBHC_S_SIGMA;
-      float r = 0.0f;
-      switch (c.reward_id[lane]) {
-        case R_CONTACT_MASK: r = 1.0f - cm_err / (float)c.n_feet; break;
-        case R_CONTACT_MASK_V2: r = 0.5f - cm_err / (float)c.n_feet; break;
-        case R_MAX_JOINT_POS: r = expf(-max_dja / (float)sg[G_MAX_JOINT]); break;
-        case R_BODY_POS_EXT: r = expf(-e_lo / (float)sg[G_LOWER]) * c.w_lower + expf(-e_up / (float)sg[G_UPPER]) * c.w_upper; break;
-        case R_VR3: r = expf(-e_vr / (float)sg[G_VR3]); break;
-        case R_FEET_POS: r = expf(-e_feet / (float)sg[G_FEET]); break;
-        case R_BODY_ROT: r = expf(-e_rot / (float)sg[G_ROT]); break;
-        case R_BODY_ANG_VEL: r = expf(-e_ang2 / (float)sg[G_ANG_VEL]); break;
-        case R_BODY_VEL: r = expf(-e_vel2 / (float)sg[G_VEL]); break;
-        case R_JOINT_POS: r = expf(-e_jp / (float)sg[G_JOINT_POS]); break;
-        case R_JOINT_VEL: r = expf(-e_jv / (float)sg[G_JOINT_VEL]); break;
-        case R_TORQUES: r = sum_tq2; break;
-        case R_ACTION_RATE: r = sum_dact2; break;
-        case R_DOF_VEL: r = sum_dv2; break;
-        case R_DOF_ACC: r = sum_acc2; break;
-        case R_ORIENTATION: r = pg.x * pg.x + pg.y * pg.y; break;
-        case R_ALIVE: r = 1.0f; break;
-        case R_FEET_AIR_TIME: r = r_air; break;
-        case R_FEET_FORCES: r = r_force; break;
-        case R_STUMBLE: r = stumble ? 1.0f : 0.0f; break;
-        case R_SLIPPAGE: r = r_slip; break;
-        case R_FOOT_SLIP: r = r_fslip; break;
-        case R_LIM_DOF_POS: r = lim_pos; break;
-        case R_LIM_DOF_VEL: r = lim_vel; break;
-        case R_LIM_TORQUE: r = lim_tq; break;
-        case R_COLLISION: r = s.collide; break;
-        default: break;
-      }
-      rew = r * c.reward_scale[lane];
-      if (c.reward_is_penalty[lane]) rew *= penalty_scale;
-    }
-    const float term_rew = c.has_termination ? ((reset && !time_out) ? 1.0f : 0.0f) * c.termination_scale : 0.0f;
-    {
-      const int R = c.n_rewards;
-      float* es = io.episode_sums + n * c.n_episode_sums;
-      if (c.use_vec_reward) {
-        float v = rew;
-        if (c.only_positive_rewards) v = fmaxf(v, 0.0f);
-        if (lane == R - 1) v += term_rew;  // the reference's stale loop index, legged_robot_base.py:744
-        if (lane < R) io.rew_buf[n * (R + 1) + lane] = v;
-        if (lane == R) io.rew_buf[n * (R + 1) + R] = 0.0f;
-      } else {
-        float tot = warp_sum(lane < R ? rew : 0.0f);
-        if (c.only_positive_rewards) tot = fmaxf(tot, 0.0f);
-        if (lane == 0) io.rew_buf[n] = tot + term_rew;
-      }
-      float ev = 0.0f;
-      if (lane < c.n_episode_sums) ev = es[lane] + (lane < R ? rew : term_rew);
-      if (reset) {  // extras["episode"], legged_robot_base.py:509-513
-        if (lane < c.n_episode_sums) io.last_episode_sums[n * c.n_episode_sums + lane] = ev;
-        ev = 0.0f;
-      }
-      if (lane < c.n_episode_sums) es[lane] = ev;
-    }
-    if (lane == 0) {
-      acc[PBHC_A_SIGMA_ERR + G_MAX_JOINT] += max_dja; acc[PBHC_A_SIGMA_ERR + G_UPPER] += e_up;
-      acc[PBHC_A_SIGMA_ERR + G_LOWER] += e_lo; acc[PBHC_A_SIGMA_ERR + G_VR3] += e_vr;
-      acc[PBHC_A_SIGMA_ERR + G_FEET] += e_feet; acc[PBHC_A_SIGMA_ERR + G_ROT] += e_rot;
-      acc[PBHC_A_SIGMA_ERR + G_VEL] += e_vel2; acc[PBHC_A_SIGMA_ERR + G_ANG_VEL] += e_ang2;
-      acc[PBHC_A_SIGMA_ERR + G_JOINT_POS] += e_jp; acc[PBHC_A_SIGMA_ERR + G_JOINT_VEL] += e_jv;
-      acc[PBHC_A_UPPER_NORM] += s.up_n; acc[PBHC_A_LOWER_NORM] += s.lo_n; acc[PBHC_A_VR3_NORM] += s.vr_n;
-      acc[PBHC_A_JOINT_NORM] += sqrtf(sum_dja2);
-      acc[PBHC_A_TERM_GRAVITY] += t_grav; acc[PBHC_A_TERM_FAR] += t_far;
-      acc[PBHC_A_TERM_TIMEOUT] += time_out; acc[PBHC_A_TERM_MOTION_END] += t_end;
-      acc[PBHC_A_NUM_ENVS] += 1.0;
-    }
-    // ---- J. reset (legged_robot_base.py:491-516, 647-686, 587-635; motion_tracking.py:274-296, 369-384, 445-543) --
-    float kp = 1.f, kd = 1.f, delay_f;
-    if (ld) { kp = io.kp_scale[n * D + lane]; kd = io.kd_scale[n * D + lane]; }
-    int64_t delay = io.action_delay_idx[n];
-    const float phase = t / tab.clip_length[clip];  // motion_tracking.py:738-739 (stale for envs that reset, like the reference)
-    if (reset) {
-      const Rng rng = {make_uint2((uint32_t)c.seed, (uint32_t)(c.seed >> 32)), (uint32_t)n, (uint32_t)(n >> 32), (uint32_t)push_count};
-      act = 0.0f;
-      if (ld) io.actions[n * D + lane] = 0.0f;
-      for (int f = 0; f < c.n_feet; ++f) { air[f] = 0.0f; contacts[f] = 0.0f; filt[f] = 0.0f; }
-      for (int i = lane; i < c.hist_row; i += 32) { feat[hist_off + i] = 0.0f; io.hist[n * c.hist_row + i] = 0.0f; }
-      if (lane == 0) { acc[PBHC_A_RESET] += 1.0; acc[PBHC_A_RESET_EPLEN] += (double)last_ep; }
-      ep = 0;
-      if (ld) {  // _episodic_domain_randomization
-        if (c.randomize_pd_gain) {
-          kp = io.inject_kp ? io.inject_kp[n * D + lane] : (c.kp_hi - c.kp_lo) * rng.uniform(16 + lane) + c.kp_lo;
-          kd = io.inject_kd ? io.inject_kd[n * D + lane] : (c.kd_hi - c.kd_lo) * rng.uniform(48 + lane) + c.kd_lo;
-          io.kp_scale[n * D + lane] = kp; io.kd_scale[n * D + lane] = kd;
-        }
-        if (c.randomize_rfi_lim)
-          io.rfi_lim_scale[n * D + lane] = io.inject_rfi ? io.inject_rfi[n * D + lane] : (c.rfi_hi - c.rfi_lo) * rng.uniform(80 + lane) + c.rfi_lo;
-        if (c.use_rao)
-          io.rao_scale[n * D + lane] = io.inject_rao ? io.inject_rao[n * D + lane] : (c.rao_lim - (-c.rao_lim)) * rng.uniform(112 + lane) + (-c.rao_lim);
-      }
-      if (c.randomize_ctrl_delay) {
-        delay = io.inject_delay ? io.inject_delay[n] : c.delay_lo + (int64_t)(rng.draw(1).x % (uint32_t)(c.delay_hi - c.delay_lo + 1));
-        if (lane == 0) io.action_delay_idx[n] = delay;
-      }
-      etr = ((float)last_ep * c.dt + start) / mlen;                       // motion_tracking.py:281-282
-      mlen = tab.clip_length[clip];                                       // _resample_motion_times
-      start = io.inject_start_times ? io.inject_start_times[n] : rng.uniform(0) * mlen;
-      // _reset_dofs / _reset_root_states from the motion state at the new time
-      const FrameBlend f2 = frame_blend(tab, clip, (float)(ep + 1) * c.dt + start);
-      const float b2 = f2.blend, omb2 = 1.0f - b2;
-      const float* q0 = tab.records + f2.f0 * tab.rec_stride;
-      const float* q1 = tab.records + f2.f1 * tab.rec_stride;
-      if (ld) {
-        dpos = omb2 * q0[e_dp + lane] + b2 * q1[e_dp + lane];
-        dvel = omb2 * q0[e_dv + lane] + b2 * q1[e_dv + lane];
-        if (c.reset_noise[0] != 0.0f) dpos = dpos + rng.normal(144 + lane) * c.reset_noise[0];
-        if (c.reset_noise[1] != 0.0f) dvel = dvel + rng.normal(176 + lane) * c.reset_noise[1];
-        reinterpret_cast<float2*>(io.dof_state)[n * D + lane] = make_float2(dpos, dvel);
-      }
-      if (lane < 13) {
-        float v;
-        if (lane >= 3 && lane < 7) {
-          const float4 a = reinterpret_cast<const float4*>(q0)[0], d4 = reinterpret_cast<const float4*>(q1)[0];
-          const Q4 rr = slerp({a.x, a.y, a.z, a.w}, {d4.x, d4.y, d4.z, d4.w}, b2);
-          Q4 nq = {0.0f, 0.0f, 0.0f, 1.0f};  // small_random_quaternions(n, 0)
-          if (c.reset_noise[3] != 0.0f) {
-            V3 ax = {rng.normal(2), rng.normal(3), rng.normal(4)};
-            const float an = norm3(ax.x, ax.y, ax.z);
-            const float ang = c.reset_noise[3] * rng.uniform(5);
-            const float sh = sinf(ang / 2.0f);
-            nq = {sh * (ax.x / an), sh * (ax.y / an), sh * (ax.z / an), cosf(ang / 2.0f)};
+    for (int e = 0; e < 32; ++e) {
+      const int64_t n = chunk + (int64_t)e * stride;
+      if (n >= P.n) break;
+      __syncwarp();
+      // ---- A. per-env scalars + staging of the simulator state --------------------------------------------
+      int64_t ep = io.episode_length_buf[n] + 1;
+      const int64_t last_ep = ep;
+      float* envf = io.env_f32 + n * PBHC_ENVF_STRIDE;
+      const float4 ef0 = reinterpret_cast<const float4*>(envf)[0];  // start, motion_len, air_time[2]
+      const float4 ef1 = reinterpret_cast<const float4*>(envf)[1];  // last_contacts[2], end_time_ratio, pad
+      float start = ef0.x, mlen = ef0.y, etr = ef1.z;
+      warp_load(sm_body, io.body_state + n * io.body_env_stride, Jb * 13, body_vec, lane);
+      warp_load(sm_cf, io.contact_forces + n * (Jb * 3), Jb * 3, cf_vec, lane);
+      const int clip = __float_as_int(pre[P_CLIP * 32 + e]);
+      const float b = pre[P_BLEND * 32 + e], omb = 1.0f - b;
+      const float* r0 = tab.records + (int64_t)__float_as_int(pre[P_F0 * 32 + e]) * tab.rec_stride;
+      const float* r1 = tab.records + (int64_t)__float_as_int(pre[P_F1 * 32 + e]) * tab.rec_stride;
+      const float hz = pre[P_HZ * 32 + e], hw = pre[P_HW * 32 + e];
+      const V3 rp = {pre[P_RPX * 32 + e], pre[P_RPY * 32 + e], pre[P_RPZ * 32 + e]};
+      const float org[3] = {io.env_origins[n * 3], io.env_origins[n * 3 + 1], io.env_origins[n * 3 + 2]};
+      // history ring -> its places in the observation rows (HistoryHandler.query, history_handler.py:46-48)
+      if (c.hist_row > 0) {
+        const float* gh = io.hist + n * c.hist_row;
+        for (int i = lane; i < c.hist_row; i += 32) {
+          const float v = gh[i];
+          for (int d = 0; d < P.n_hdst_max; ++d) {
+            const int m = hmap[d * c.hist_row + i];
+            if (m >= 0) rows[m & 0xffffff] = P.hist_any_mul ? v * c.hist_dst[m >> 24].mul : v;
           }
-          const Q4 o = quat_mul(nq, rr);
-          v = lane == 3 ? o.x : (lane == 4 ? o.y : (lane == 5 ? o.z : o.w));
-        } else {
-          const int e = lane < 3 ? e_pos + lane : (lane < 10 ? e_vel + (lane - 7) : e_ang + (lane - 10));
-          v = omb2 * q0[e] + b2 * q1[e];
-          if (lane < 3) v = v + org[lane];
-          const float ns = lane < 3 ? c.reset_noise[2] : (lane < 10 ? c.reset_noise[4] : c.reset_noise[5]);
-          if (ns != 0.0f) v = v + rng.normal(8 + lane) * ns;
         }
-        root[lane] = v;
       }
-    }
-    delay_f = (float)delay;
-    // ---- K. observation features, groups, history push, state write-back -----------------------------------
-    {
-      const float* sc = c.obs_scale;
-      if (lane < 3) {
-        const float l3 = lane == 0 ? blv.x : (lane == 1 ? blv.y : blv.z);
-        const float a3 = lane == 0 ? bav.x : (lane == 1 ? bav.y : bav.z);
-        const float g3 = lane == 0 ? pg.x : (lane == 1 ? pg.y : pg.z);
-        feat[P.src_off[S_BASE_LIN_VEL] + lane] = l3 * sc[S_BASE_LIN_VEL];
-        feat[P.src_off[S_BASE_ANG_VEL] + lane] = a3 * sc[S_BASE_ANG_VEL];
-        feat[P.src_off[S_PROJ_GRAV] + lane] = g3 * sc[S_PROJ_GRAV];
-        feat[P.src_off[S_DR_COM] + lane] = io.base_com_bias[n * 3 + lane] * sc[S_DR_COM];
+      __syncwarp();
+      // ---- B. bodies: reference (lerp / slerp of the two frames), extended state, differences, heading-frame features
+      float sums[16];
+#pragma unroll
+      for (int i = 0; i < 16; ++i) sums[i] = 0.0f;
+      int far = 0, n_collide = 0;
+      for (int j0 = 0; j0 < J; j0 += 32) {
+        const int j = j0 + lane;
+        bool collide = false;
+        if (j < J) {
+          V3 p, v, w; Q4 q;
+          if (j < Jb) {
+            const float* bs = sm_body + j * 13;
+            p = {bs[0], bs[1], bs[2]}; q = {bs[3], bs[4], bs[5], bs[6]}; v = {bs[7], bs[8], bs[9]}; w = {bs[10], bs[11], bs[12]};
+          } else {  // motion_tracking.py:619-643
+            const int x = j - Jb;
+            const float* bs = sm_body + c.ext_parent[x] * 13;
+            const Q4 qp = {bs[3], bs[4], bs[5], bs[6]};
+            const V3 off = {c.ext_pos[x][0], c.ext_pos[x][1], c.ext_pos[x][2]};
+            const Q4 qe = {c.ext_rot_xyzw[x][0], c.ext_rot_xyzw[x][1], c.ext_rot_xyzw[x][2], c.ext_rot_xyzw[x][3]};
+            const V3 r = quat_rotate(qe, quat_rotate(qp, off));
+            p = {r.x + bs[0], r.y + bs[1], r.z + bs[2]};
+            q = quat_mul(qp, qe);
+            w = {bs[10], bs[11], bs[12]};
+            v = {bs[7] + (w.y * off.z - w.z * off.y), bs[8] + (w.z * off.x - w.x * off.z), bs[9] + (w.x * off.y - w.y * off.x)};
+          }
+          const float4 qa = __ldg(reinterpret_cast<const float4*>(r0) + j);
+          const float4 qb = __ldg(reinterpret_cast<const float4*>(r1) + j);
+          const Q4 rr = slerp({qa.x, qa.y, qa.z, qa.w}, {qb.x, qb.y, qb.z, qb.w}, b);
+          float rpz[3], rvv[3], rw[3];
+#pragma unroll
+          for (int k = 0; k < 3; ++k) {
+            rpz[k] = (omb * __ldg(r0 + e_pos + 3 * j + k) + b * __ldg(r1 + e_pos + 3 * j + k)) + org[k];
+            rvv[k] = omb * __ldg(r0 + e_vel + 3 * j + k) + b * __ldg(r1 + e_vel + 3 * j + k);
+            rw[k] = omb * __ldg(r0 + e_ang + 3 * j + k) + b * __ldg(r1 + e_ang + 3 * j + k);
+          }
+          if (io.ref_body_pos_extend) {
+            float* o = io.ref_body_pos_extend + n * (3 * J) + 3 * j;
+            o[0] = rpz[0]; o[1] = rpz[1]; o[2] = rpz[2];
+          }
+          if (io.ref_body_rot_extend) reinterpret_cast<float4*>(io.ref_body_rot_extend)[n * J + j] = make_float4(rr.x, rr.y, rr.z, rr.w);
+          const V3 dp = {rpz[0] - p.x, rpz[1] - p.y, rpz[2] - p.z};
+          const float dq0 = rr.x - q.x, dq1 = rr.y - q.y, dq2 = rr.z - q.z, dq3 = rr.w - q.w;
+          const V3 dv = {rvv[0] - v.x, rvv[1] - v.y, rvv[2] - v.z};
+          const V3 dw = {rw[0] - w.x, rw[1] - w.y, rw[2] - w.z};
+          const float m_pos = ((dp.x * dp.x + dp.y * dp.y) + dp.z * dp.z) / 3.0f;
+          const float nrm = norm3(dp.x, dp.y, dp.z);
+          const uint64_t bit = 1ull << j;
+          if (c.upper_mask & bit) { sums[U_UP_SQ] += m_pos; sums[U_UP_N] += nrm; }
+          if (c.lower_mask & bit) { sums[U_LO_SQ] += m_pos; sums[U_LO_N] += nrm; }
+          if (c.vr3_mask & bit) { sums[U_VR_SQ] += m_pos; sums[U_VR_N] += nrm; }
+          if (feet_mask & bit) sums[U_FEET_SQ] += m_pos;
+          sums[U_ROT_SQ] += (((dq0 * dq0 + dq1 * dq1) + dq2 * dq2) + dq3 * dq3) / 4.0f;
+          sums[U_VEL_SQ] += ((dv.x * dv.x + dv.y * dv.y) + dv.z * dv.z) / 3.0f;
+          sums[U_ANG_SQ] += ((dw.x * dw.x + dw.y * dw.y) + dw.z * dw.z) / 3.0f;
+          if (nrm > far_thr) far = 1;
+          if (j < Jb && (c.penalised_mask & bit)) {
+            const float* fc = sm_cf + 3 * j;
+            collide = norm3(fc[0], fc[1], fc[2]) > 0.1f;
+          }
+          const V3 dl = quat_rotate_z(hz, hw, dp);  // motion_tracking.py:694-697
+          const float sc0 = T.obs_scale[S_DIF_LOCAL];
+          put3(T.sdst[S_DIF_LOCAL], rows, 3 * j, dl.x * sc0, dl.y * sc0, dl.z * sc0);
+          const V3 lr = quat_rotate_z(hz, hw, {rpz[0] - rp.x, rpz[1] - rp.y, rpz[2] - rp.z});  // :705-707
+          const float sc1 = T.obs_scale[S_LOCAL_REF];
+          put3(T.sdst[S_LOCAL_REF], rows, 3 * j, lr.x * sc1, lr.y * sc1, lr.z * sc1);
+          if (c.src_used_mask & ((1u << S_LOCAL_REF_VEL) | (1u << S_GLOBAL_REF_VEL))) {
+            const V3 lv = quat_rotate_z(hz, hw, {rvv[0], rvv[1], rvv[2]});
+            const float sc2 = T.obs_scale[S_LOCAL_REF_VEL], sc3 = T.obs_scale[S_GLOBAL_REF_VEL];
+            put3(T.sdst[S_LOCAL_REF_VEL], rows, 3 * j, lv.x * sc2, lv.y * sc2, lv.z * sc2);
+            put3(T.sdst[S_GLOBAL_REF_VEL], rows, 3 * j, rvv[0] * sc3, rvv[1] * sc3, rvv[2] * sc3);
+          }
+        }
+        n_collide += __popc(__ballot_sync(0xffffffffu, collide));
+      }
+      const bool any_far = __any_sync(0xffffffffu, far);
+      // ---- C. dofs (lane = dof) ---------------------------------------------------------------------------
+      float dpos = 0.f, dvel = 0.f, act = 0.f, tq = 0.f, lact = 0.f, ldv = 0.f, ddef = 0.f, kp = 1.f, kd = 1.f;
+      float dja = 0.f, djv = 0.f;
+      if (ld) {
+        const float2 ds = reinterpret_cast<const float2*>(io.dof_state)[n * D + lane];
+        dpos = ds.x; dvel = ds.y;
+        act = io.actions[n * D + lane]; tq = io.torques[n * D + lane];
+        lact = io.last_actions[n * D + lane]; ldv = io.last_dof_vel[n * D + lane];
+        ddef = io.default_dof_pos[n * io.default_dof_stride + lane];
+        kp = io.kp_scale[n * D + lane]; kd = io.kd_scale[n * D + lane];
+        dja = (omb * __ldg(r0 + e_dp + lane) + b * __ldg(r1 + e_dp + lane)) - dpos;   // motion_tracking.py:661-665
+        djv = (omb * __ldg(r0 + e_dv + lane) + b * __ldg(r1 + e_dv + lane)) - dvel;
+      }
+      const float max_dja = warp_max(fabsf(dja));
+      sums[U_DJA2] = dja * dja; sums[U_DJV2] = djv * djv; sums[U_TQ2] = tq * tq;
+      const float dact = lact - act;
+      sums[U_DACT2] = dact * dact; sums[U_DV2] = dvel * dvel;
+      const float dacc = (ldv - dvel) / c.dt;
+      sums[U_ACC2] = ld ? dacc * dacc : 0.f;
+      float l_pos = 0.f, l_vel = 0.f, l_tq = 0.f;
+      if (ld) {  // legged_robot_base.py:974-1002
+        l_pos = -fminf(dpos - lim_lo, 0.0f) + fmaxf(dpos - lim_hi, 0.0f);
+        l_vel = fminf(fmaxf(fabsf(dvel) - lim_v, 0.0f), 1.0f);
+        l_tq = c.cur_torque.enable ? fminf(fmaxf(fabsf(tq) - lim_t, 0.0f), 1.0f) : fmaxf(fabsf(tq) - lim_t, 0.0f);
+      }
+      l_pos = warp_sum(l_pos); l_vel = warp_sum(l_vel); l_tq = warp_sum(l_tq);
+      {
+        const float tot = warp_sum16(sums, lane);
+        const int idx = (lane >> 1) & 15;
+        rv[T.sum_slot[idx]] = tot / T.sum_div[idx];
+        if (idx == U_DJA2) rv[V_JOINT_N] = sqrtf(tot);
+      }
+      // ---- D. feet (lane = foot): contacts, feet_air_time, contact-force / slip terms -----------------------------
+      float x_air = 0.f, x_force = 0.f, x_slip = 0.f, x_fslip = 0.f, x_cm = 0.f, contact_f = 0.f, air_f = 0.f;
+      bool x_stumble = false;
+      if (lane < c.n_feet) {
+        const float* fc = sm_cf + 3 * my_foot;
+        const float* bs = sm_body + 13 * my_foot;
+        const float last_c = lane == 0 ? ef1.x : ef1.y;
+        air_f = lane == 0 ? ef0.z : ef0.w;
+        const float fn = norm3(fc[0], fc[1], fc[2]);
+        contact_f = fn > 1.0f ? 1.0f : 0.0f;                                   // legged_robot_base.py:352-353
+        const float filt = (contact_f != 0.0f || last_c != 0.0f) ? 1.0f : 0.0f;
+        if (Cm) x_cm = fabsf(filt - (omb * __ldg(r0 + e_c + lane) + b * __ldg(r1 + e_c + lane)));
+        // feet_air_time, motion_tracking.py:1307-1319 (uses last_contacts of the previous step)
+        const bool fz = fc[2] > 1.0f || last_c != 0.0f;
+        const float first = (air_f > 0.0f && fz) ? 1.0f : 0.0f;
+        air_f += c.dt;
+        x_air = (air_f - c.desired_feet_air_time) * first;
+        air_f *= fz ? 0.0f : 1.0f;
+        x_force = fmaxf(fn - c.max_contact_force, 0.0f);                        // :1321-1323
+        x_stumble = norm2(fc[0], fc[1]) > 5.0f * fabsf(fc[2]);                  // :1325-1328
+        x_slip = norm3(bs[7], bs[8], bs[9]) * (fn > 1.0f ? 1.0f : 0.0f);        // legged_robot_base.py:1004-1010
+        x_fslip = (fn > 1.0f ? 1.0f : 0.0f) * norm2(bs[7], bs[8]);              // :1012-1017
+      }
+      x_air += __shfl_xor_sync(0xffffffffu, x_air, 1); x_force += __shfl_xor_sync(0xffffffffu, x_force, 1);
+      x_slip += __shfl_xor_sync(0xffffffffu, x_slip, 1); x_fslip += __shfl_xor_sync(0xffffffffu, x_fslip, 1);
+      x_cm += __shfl_xor_sync(0xffffffffu, x_cm, 1);
+      const bool stumble = __any_sync(0xffffffffu, x_stumble);
+      float air1 = __shfl_sync(0xffffffffu, air_f, 1), contact1 = __shfl_sync(0xffffffffu, contact_f, 1);  // lane 0 packs the state
+      // ---- E. termination (legged_robot_base.py:408-489, motion_tracking.py:330-358) -------------------------------
+      const bool t_grav = c.term_gravity && pre[P_GRAVN * 32 + e] > c.term_gravity_thr;
+      const bool t_far = c.term_motion_far && any_far;
+      const bool t_out = ep > c.max_episode_length;
+      const bool t_end = c.term_motion_end && ((float)ep * c.dt + start > mlen);
+      const bool time_out = t_out || t_end;
+      const bool reset = t_grav || t_far || time_out;
+      if (lane == 0) {
+        rv[V_SIGMA_ERR + G_MAX_JOINT] = max_dja;
+        rv[V_T_GRAV] = t_grav; rv[V_T_FAR] = t_far; rv[V_T_OUT] = time_out; rv[V_T_END] = t_end;
+        rv[V_RESET] = reset; rv[V_ONE] = 1.0f; rv[V_ALIVE] = 1.0f;
+        rv[V_CONTACT] = 1.0f - x_cm / (float)c.n_feet; rv[V_CONTACT_V2] = 0.5f - x_cm / (float)c.n_feet;
+        rv[V_ORIENT] = pre[P_ORIENT * 32 + e];
+        rv[V_AIR] = x_air; rv[V_FORCE] = x_force; rv[V_STUMBLE] = stumble ? 1.0f : 0.0f; rv[V_SLIP] = x_slip; rv[V_FSLIP] = x_fslip;
+        rv[V_LIM_POS] = l_pos; rv[V_LIM_VEL] = l_vel; rv[V_LIM_TQ] = l_tq; rv[V_COLLIDE] = (float)n_collide;
+      }
+      __syncwarp();
+      // ---- F. rewards (lane = reward term; legged_robot_base.py:715-761) ------------------------------------------
+      float rew = 0.0f;
+      if (lane < c.n_rewards) {
+        const int kind = T.r_kind[lane];
+        float r = rv[T.r_arg[lane]];
+        if (kind != K_RAW) {
+          r = expf(-r / T.r_sigma[lane]);
+          if (kind == K_EXP2)  // teleop_body_position_extend, motion_tracking.py:1177-1199
+            r = r * c.w_lower + expf(-rv[V_SIGMA_ERR + G_UPPER] / (float)T.scal[PBHC_S_SIGMA + G_UPPER]) * c.w_upper;
+        }
+        rew = r * T.r_scale[lane] * T.r_pen[lane];
+      }
+      const float term_rew = c.has_termination ? ((reset && !time_out) ? 1.0f : 0.0f) * c.termination_scale : 0.0f;
+      {
+        const int R = c.n_rewards;
+        float* es = io.episode_sums + n * c.n_episode_sums;
+        if (c.use_vec_reward) {
+          float v = rew;
+          if (c.only_positive_rewards) v = fmaxf(v, 0.0f);
+          if (lane == R - 1) v += term_rew;  // the reference's stale loop index, legged_robot_base.py:744
+          if (lane < R) io.rew_buf[n * (R + 1) + lane] = v;
+          if (lane == R) io.rew_buf[n * (R + 1) + R] = 0.0f;
+        } else {
+          float tot = warp_sum(lane < R ? rew : 0.0f);
+          if (c.only_positive_rewards) tot = fmaxf(tot, 0.0f);
+          if (lane == 0) io.rew_buf[n] = tot + term_rew;
+        }
+        float ev = 0.0f;
+        if (lane < c.n_episode_sums) ev = es[lane] + (lane < R ? rew : term_rew);
+        if (reset) {  // extras["episode"], legged_robot_base.py:509-513
+          if (lane < c.n_episode_sums) io.last_episode_sums[n * c.n_episode_sums + lane] = ev;
+          ev = 0.0f;
+        }
+        if (lane < c.n_episode_sums) es[lane] = ev;
+      }
+      // ---- G. reset (legged_robot_base.py:491-516, 647-686, 587-635; motion_tracking.py:274-296, 369-384, 445-543) ----
+      int64_t delay = io.action_delay_idx[n];
+      float air0 = air_f, contact0 = contact_f;  // meaningful in lane 0
+      if (reset) {
+        const Rng rng = {make_uint2((uint32_t)c.seed, (uint32_t)(c.seed >> 32)), (uint32_t)n, (uint32_t)(n >> 32), push_count};
+        act = 0.0f;
+        if (ld) io.actions[n * D + lane] = 0.0f;
+        air0 = 0.0f; air1 = 0.0f; contact0 = 0.0f; contact1 = 0.0f;
+        if (c.hist_row > 0) {  // HistoryHandler.reset: zero rows (and what the observation rows already took from them)
+          for (int i = lane; i < c.hist_row; i += 32) {
+            io.hist[n * c.hist_row + i] = 0.0f;
+            for (int d = 0; d < P.n_hdst_max; ++d) {
+              const int m = hmap[d * c.hist_row + i];
+              if (m >= 0) rows[m & 0xffffff] = 0.0f;
+            }
+          }
+        }
+        ep = 0;
+        if (ld) {  // _episodic_domain_randomization
+          if (c.randomize_pd_gain) {
+            kp = io.inject_kp ? io.inject_kp[n * D + lane] : (c.kp_hi - c.kp_lo) * rng.uniform(16 + lane) + c.kp_lo;
+            kd = io.inject_kd ? io.inject_kd[n * D + lane] : (c.kd_hi - c.kd_lo) * rng.uniform(48 + lane) + c.kd_lo;
+            io.kp_scale[n * D + lane] = kp; io.kd_scale[n * D + lane] = kd;
+          }
+          if (c.randomize_rfi_lim)
+            io.rfi_lim_scale[n * D + lane] = io.inject_rfi ? io.inject_rfi[n * D + lane] : (c.rfi_hi - c.rfi_lo) * rng.uniform(80 + lane) + c.rfi_lo;
+          if (c.use_rao)
+            io.rao_scale[n * D + lane] = io.inject_rao ? io.inject_rao[n * D + lane] : (c.rao_lim - (-c.rao_lim)) * rng.uniform(112 + lane) + (-c.rao_lim);
+        }
+        if (c.randomize_ctrl_delay) {
+          delay = io.inject_delay ? io.inject_delay[n] : c.delay_lo + (int64_t)(rng.draw(1).x % (uint32_t)(c.delay_hi - c.delay_lo + 1));
+          if (lane == 0) io.action_delay_idx[n] = delay;
+        }
+        etr = ((float)last_ep * c.dt + start) / mlen;                       // motion_tracking.py:281-282
+        mlen = tab.clip_length[clip];                                       // _resample_motion_times
+        start = io.inject_start_times ? io.inject_start_times[n] : rng.uniform(0) * mlen;
+        // _reset_dofs / _reset_root_states from the motion state at the new time
+        const FrameBlend f2 = frame_blend(tab, clip, (float)(ep + 1) * c.dt + start);
+        const float b2 = f2.blend, omb2 = 1.0f - b2;
+        const float* q0 = tab.records + f2.f0 * tab.rec_stride;
+        const float* q1 = tab.records + f2.f1 * tab.rec_stride;
+        if (ld) {
+          dpos = omb2 * q0[e_dp + lane] + b2 * q1[e_dp + lane];
+          dvel = omb2 * q0[e_dv + lane] + b2 * q1[e_dv + lane];
+          if (c.reset_noise[0] != 0.0f) dpos = dpos + rng.normal(144 + lane) * c.reset_noise[0];
+          if (c.reset_noise[1] != 0.0f) dvel = dvel + rng.normal(176 + lane) * c.reset_noise[1];
+          reinterpret_cast<float2*>(io.dof_state)[n * D + lane] = make_float2(dpos, dvel);
+        }
+        if (lane < 13) {
+          float v;
+          if (lane >= 3 && lane < 7) {
+            const float4 a = reinterpret_cast<const float4*>(q0)[0], d4 = reinterpret_cast<const float4*>(q1)[0];
+            const Q4 rr = slerp({a.x, a.y, a.z, a.w}, {d4.x, d4.y, d4.z, d4.w}, b2);
+            Q4 nq = {0.0f, 0.0f, 0.0f, 1.0f};  // small_random_quaternions(n, 0)
+            if (c.reset_noise[3] != 0.0f) {
+              V3 ax = {rng.normal(2), rng.normal(3), rng.normal(4)};
+              const float an = norm3(ax.x, ax.y, ax.z);
+              const float ang = c.reset_noise[3] * rng.uniform(5);
+              const float sh = sinf(ang / 2.0f);
+              nq = {sh * (ax.x / an), sh * (ax.y / an), sh * (ax.z / an), cosf(ang / 2.0f)};
+            }
+            const Q4 o = quat_mul(nq, rr);
+            v = lane == 3 ? o.x : (lane == 4 ? o.y : (lane == 5 ? o.z : o.w));
+          } else {
+            const int el = lane < 3 ? e_pos + lane : (lane < 10 ? e_vel + (lane - 7) : e_ang + (lane - 10));
+            v = omb2 * q0[el] + b2 * q1[el];
+            if (lane < 3) v = v + org[lane];
+            const float ns = lane < 3 ? c.reset_noise[2] : (lane < 10 ? c.reset_noise[4] : c.reset_noise[5]);
+            if (ns != 0.0f) v = v + rng.normal(8 + lane) * ns;
+          }
+          io.root_state[n * 13 + lane] = v;
+        }
+      }
+      // ---- H. observation features into the rows (legged_robot_base.py:763-793, 1114-1215; motion_tracking.py:944-1015)
+      if (lane < 16) {
+        int k, ce = 0;
+        float val;
+        if (lane < 9) { k = lane / 3; ce = lane - 3 * k; val = pre[(P_BLV + lane) * 32 + e]; }
+        else if (lane < 12) { k = S_DR_COM; ce = lane - 9; val = io.base_com_bias[n * 3 + ce]; }
+        else if (lane == 12) { k = S_PHASE; val = pre[P_PHASE * 32 + e]; }   // stale for envs that reset, like the reference
+        else if (lane == 13) { k = S_DR_FRICTION; val = io.friction[n]; }
+        else if (lane == 14) { k = S_DR_DELAY; val = (float)delay; }
+        else { k = S_BASE_POS_Z; val = rp.z; }
+        put1(T.sdst[k], rows, ce, val * T.obs_scale[k]);
       }
       if (ld) {
-        feat[P.src_off[S_DOF_POS] + lane] = (dpos - ddef) * sc[S_DOF_POS];
-        feat[P.src_off[S_DOF_VEL] + lane] = dvel * sc[S_DOF_VEL];
-        feat[P.src_off[S_ACTIONS] + lane] = act * sc[S_ACTIONS];
-        feat[P.src_off[S_DR_KP] + lane] = kp * sc[S_DR_KP];
-        feat[P.src_off[S_DR_KD] + lane] = kd * sc[S_DR_KD];
-        feat[P.src_off[S_DIF_JOINT] + lane] = dja * sc[S_DIF_JOINT];
-        feat[P.src_off[S_DIF_JOINT_VEL] + lane] = djv * sc[S_DIF_JOINT_VEL];
+        put1(T.sdst[S_DOF_POS], rows, lane, (dpos - ddef) * T.obs_scale[S_DOF_POS]);
+        put1(T.sdst[S_DOF_VEL], rows, lane, dvel * T.obs_scale[S_DOF_VEL]);
+        put1(T.sdst[S_ACTIONS], rows, lane, act * T.obs_scale[S_ACTIONS]);
+        put1(T.sdst[S_DR_KP], rows, lane, kp * T.obs_scale[S_DR_KP]);
+        put1(T.sdst[S_DR_KD], rows, lane, kd * T.obs_scale[S_DR_KD]);
+        if (c.src_used_mask & ((1u << S_DIF_JOINT) | (1u << S_DIF_JOINT_VEL))) {
+          put1(T.sdst[S_DIF_JOINT], rows, lane, dja * T.obs_scale[S_DIF_JOINT]);
+          put1(T.sdst[S_DIF_JOINT_VEL], rows, lane, djv * T.obs_scale[S_DIF_JOINT_VEL]);
+        }
       }
-      for (int i = lane; i < L; i += 32) feat[P.src_off[S_DR_MASS] + i] = io.link_mass_scale[n * L + i] * sc[S_DR_MASS];
+      for (int i = lane; i < L; i += 32) put1(T.sdst[S_DR_MASS], rows, i, io.link_mass_scale[n * L + i] * T.obs_scale[S_DR_MASS]);
+      if (lane == 0) { rv[V_ETR] = etr; }
+      __syncwarp();
+      // ---- I. rows -> global (clipped), history push, state write-back -----------------------------------------------
+      for (int g = 0; g < c.n_groups; ++g) {
+        const int dim = c.group_dim[g];
+        warp_store_clipped(io.obs[g] + n * dim, rows + P.row_off[g], dim, vec_of(dim, io.obs[g]), c.clip_obs, lane);
+      }
+      if (P.push_len > 0) {  // HistoryHandler.add (history_handler.py:40-44) as a ring-buffer push: one slot per key is written
+        float* gh = io.hist + n * c.hist_row;
+        const float* ps = rows + P.row_off[c.n_groups];
+        for (int i = lane; i < P.push_len; i += 32) gh[pmap[i]] = ps[i];
+      }
+      if (ld) {  // _post_compute_observations_callback, legged_robot_base.py:398-405
+        io.last_actions[n * D + lane] = act;
+        io.last_dof_pos[n * D + lane] = dpos;
+        io.last_dof_vel[n * D + lane] = dvel;
+      }
       if (lane == 0) {
-        feat[P.src_off[S_PHASE]] = phase * sc[S_PHASE];
-        feat[P.src_off[S_DR_FRICTION]] = io.friction[n] * sc[S_DR_FRICTION];
-        feat[P.src_off[S_DR_DELAY]] = delay_f * sc[S_DR_DELAY];
-        feat[P.src_off[S_BASE_POS_Z]] = rp.z * sc[S_BASE_POS_Z];
+        reinterpret_cast<float4*>(envf)[0] = make_float4(start, mlen, air0, c.n_feet > 1 ? air1 : 0.0f);
+        reinterpret_cast<float4*>(envf)[1] = make_float4(contact0, c.n_feet > 1 ? contact1 : 0.0f, etr, ef1.w);
+        io.episode_length_buf[n] = ep;
+        io.reset_buf[n] = reset ? 1 : 0;
+        io.time_out_buf[n] = time_out ? 1 : 0;
       }
-    }
-    __syncwarp();
-    for (int g = 0; g < c.n_groups; ++g) {
-      const int dim = c.group_dim[g];
-      const int32_t* map = c.group_map[g];
-      const float* mul = c.group_mul[g];
-      float* o = io.obs[g] + n * dim;
-      for (int i = lane; i < dim; i += 32) {
-        const float v = feat[__ldg(map + i)] * __ldg(mul + i);
-        o[i] = fminf(fmaxf(v, -c.clip_obs), c.clip_obs);
+      if (lane < 23) {  // per-lane fp64 accumulation of the cross-env sums (slot = lane, layout PBHC_A_*)
+        double a = (double)rv[lane];
+        if (lane == V_RESET_EPLEN) a = reset ? (double)last_ep : 0.0;
+        if (lane == V_ETR_SQ) { const double x = (double)rv[V_ETR]; a = x * x; }
+        acc_reg += a;
       }
-    }
-    {  // HistoryHandler.add (history_handler.py:40-44) as a ring-buffer push: one slot per key is written
-      float* gh = io.hist + n * c.hist_row;
-      int base = 0;
-      for (int k = 0; k < c.n_hist_keys; ++k) {
-        const int len = c.hist_len[k], dim = c.hist_dim[k];
-        const int head = (int)((len - ((push_count + 1) % len)) % len);
-        const float* src = feat + P.src_off[c.hist_src[k]];
-        for (int i = lane; i < dim; i += 32) gh[base + head * dim + i] = src[i];
-        base += len * dim;
-      }
-    }
-    if (io.ref_body_pos_extend) for (int i = lane; i < 3 * J; i += 32) io.ref_body_pos_extend[n * (3 * J) + i] = sm_ref[e_pos + i];
-    if (io.ref_body_rot_extend) for (int i = lane; i < 4 * J; i += 32) io.ref_body_rot_extend[n * (4 * J) + i] = sm_ref[i];
-    if (ld) {  // _post_compute_observations_callback, legged_robot_base.py:398-405
-      io.last_actions[n * D + lane] = act;
-      io.last_dof_pos[n * D + lane] = dpos;
-      io.last_dof_vel[n * D + lane] = dvel;
-    }
-    if (lane == 0) {
-      envf[0] = start; envf[1] = mlen; envf[6] = etr;
-      for (int f = 0; f < 2; ++f) { envf[2 + f] = f < c.n_feet ? air[f] : 0.0f; envf[4 + f] = f < c.n_feet ? contacts[f] : 0.0f; }
-      io.episode_length_buf[n] = ep;
-      io.reset_buf[n] = reset ? 1 : 0;
-      io.time_out_buf[n] = time_out ? 1 : 0;
-      acc[PBHC_A_ETR_SUM] += (double)etr; acc[PBHC_A_ETR_SQ] += (double)etr * (double)etr;
     }
   }
+  T.acc[warp][lane] = lane < 23 ? acc_reg : 0.0;
   __syncthreads();
   if (threadIdx.x < PBHC_ACC) {
     double v = 0.0;
-    for (int w = 0; w < kTW; ++w) v += sm_acc[w][threadIdx.x];
+    for (int w = 0; w < kTW; ++w) v += T.acc[w][threadIdx.x];
     io.partials[(int64_t)blockIdx.x * PBHC_ACC + threadIdx.x] = v;
   }
 }
@@ -607,6 +856,7 @@ __global__ void track_finalize_kernel(const __grid_constant__ PbhcTrackCfg c, co
   S[PBHC_S_PUSH_COUNT] += 1.0;
 }
 
+
 static int g_track_blocks_per_sm = 0;
 
 }  // namespace pbhc
@@ -618,8 +868,10 @@ extern "C" int pbhc_track_step(const PbhcTrackCfg* cfg, const PbhcTableDesc* tab
   if (!cfg || !tab || !io || n < 0) { set_error("pbhc_track_step: null argument"); return PBHC_E_BADARG; }
   const PbhcTrackCfg& c = *cfg;
   if (c.J <= 0 || c.J > 64 || c.Jb > c.J || c.D <= 0 || c.D > PBHC_MAX_DOF || c.n_ext != c.J - c.Jb || c.n_ext > PBHC_MAX_EXT ||
-      c.n_feet < 0 || c.n_feet > 2 || c.n_rewards < 0 || c.n_rewards >= 32 || c.n_episode_sums > 32 || c.n_groups > PBHC_MAX_OBS_GROUPS ||
-      c.n_hist_keys > PBHC_MAX_HIST_KEYS || c.J != tab->num_joints || c.Jb != tab->num_bodies || c.D != tab->num_dof) {
+      c.n_feet < 0 || c.n_feet > 2 || c.n_rewards < 0 || c.n_rewards >= 32 || c.n_episode_sums > 32 || c.n_groups < 0 ||
+      c.n_groups > PBHC_MAX_OBS_GROUPS || c.n_hist_keys < 0 || c.n_hist_keys > PBHC_MAX_HIST_KEYS || c.n_hist_dst < 0 ||
+      c.n_hist_dst > PBHC_MAX_HIST_DST || c.J != tab->num_joints || c.Jb != tab->num_bodies || c.D != tab->num_dof ||
+      tab->total_frames > 0x7fffffffLL) {
     set_error("pbhc_track_step: configuration outside the supported envelope (J<=64, D<=32, feet<=2, rewards<32)"); return PBHC_E_RANGE;
   }
   const void* need[] = {io->body_state, io->root_state, io->dof_state, io->contact_forces, io->actions, io->torques, io->env_origins,
@@ -629,30 +881,56 @@ extern "C" int pbhc_track_step(const PbhcTrackCfg* cfg, const PbhcTableDesc* tab
                         io->last_episode_sums, io->partials, io->acc};
   for (const void* p : need) if (!p) { set_error("pbhc_track_step: a required PbhcTrackIO pointer is NULL"); return PBHC_E_BADARG; }
   if ((c.L > 0 && !io->link_mass_scale) || (c.hist_row > 0 && !io->hist)) { set_error("pbhc_track_step: NULL link_mass_scale / hist"); return PBHC_E_BADARG; }
-  for (int g = 0; g < c.n_groups; ++g) if (!io->obs[g] || !c.group_map[g] || !c.group_mul[g]) { set_error("pbhc_track_step: NULL obs group %d", g); return PBHC_E_BADARG; }
-  if (((uintptr_t)tab->records & 15) || ((uintptr_t)io->dof_state & 7)) { set_error("pbhc_track_step: records must be 16-B, dof_state 8-B aligned"); return PBHC_E_ALIGN; }
-  if (n == 0) return PBHC_OK;
+  for (int g = 0; g < c.n_groups; ++g) if (!io->obs[g] || c.group_dim[g] <= 0) { set_error("pbhc_track_step: NULL / empty obs group %d", g); return PBHC_E_BADARG; }
+  if (((uintptr_t)tab->records & 15) || ((uintptr_t)io->dof_state & 7) || ((uintptr_t)io->env_f32 & 15) ||
+      (io->ref_body_rot_extend && ((uintptr_t)io->ref_body_rot_extend & 15))) {
+    set_error("pbhc_track_step: records / env_f32 / ref_body_rot_extend must be 16-B, dof_state 8-B aligned"); return PBHC_E_ALIGN;
+  }
   TrackParams P;
   P.c = c; P.tab = *tab; P.io = *io; P.n = n;
+  // history layout: global row = keys back to back ([len_k, dim_k] each); push staging = one slot per key
+  int hrow = 0, push = 0;
+  for (int k = 0; k < PBHC_MAX_HIST_KEYS; ++k) { P.hist_base[k] = hrow; P.push_off[k] = push; if (k < c.n_hist_keys) { hrow += c.hist_len[k] * c.hist_dim[k]; push += c.hist_dim[k]; } }
+  if (hrow != c.hist_row) { set_error("pbhc_track_step: hist_row %d != sum len*dim %d", c.hist_row, hrow); return PBHC_E_BADARG; }
+  P.push_len = push;
+  auto up4h = [](int v) { return (v + 3) & ~3; };
   int off = 0;
-  for (int k = 0; k < PBHC_NUM_OBS_SRC; ++k) { P.src_off[k] = off; off += src_dim(k, c.D, c.J, c.L); }
-  P.src_off[PBHC_NUM_OBS_SRC] = off;
-  const int feat_len = off + c.hist_row;
-  auto up4 = [](int v) { return (v + 3) & ~3; };
+  for (int g = 0; g < PBHC_MAX_OBS_GROUPS; ++g) { P.row_off[g] = off; if (g < c.n_groups) off += up4h(c.group_dim[g]); }
+  P.row_off[c.n_groups] = off;
+  P.rows_len = off + up4h(push);
+  // validate the destination tables against the row sizes
+  for (int k = 0; k < PBHC_NUM_OBS_SRC; ++k)
+    for (int g = 0; g < c.n_groups; ++g)
+      if (c.src_dst[k][g] >= 0 && c.src_dst[k][g] + src_dim(k, c.D, c.J, c.L) > c.group_dim[g]) { set_error("pbhc_track_step: src_dst[%d][%d] out of range", k, g); return PBHC_E_RANGE; }
+  int per_key[PBHC_MAX_HIST_KEYS] = {0};
+  P.hist_any_mul = 0; P.n_hdst_max = 0;
+  for (int e = 0; e < c.n_hist_dst; ++e) {
+    const PbhcHistDst& h = c.hist_dst[e];
+    if (h.key < 0 || h.key >= c.n_hist_keys || h.group < 0 || h.group >= c.n_groups || h.len < 0 || h.len > c.hist_len[h.key] ||
+        h.offset < 0 || h.offset + h.len * c.hist_dim[h.key] > c.group_dim[h.group]) { set_error("pbhc_track_step: hist_dst[%d] out of range", e); return PBHC_E_RANGE; }
+    if (++per_key[h.key] > kMaxHistDstPerKey) { set_error("pbhc_track_step: a history key appears in more than %d segments", kMaxHistDstPerKey); return PBHC_E_RANGE; }
+    if (per_key[h.key] > P.n_hdst_max) P.n_hdst_max = per_key[h.key];
+    if (h.mul != 1.0f) P.hist_any_mul = 1;
+  }
+  for (int k = 0; k < c.n_hist_keys; ++k) if (c.hist_len[k] <= 0 || c.hist_dim[k] != src_dim(c.hist_src[k], c.D, c.J, c.L)) { set_error("pbhc_track_step: bad history key %d", k); return PBHC_E_BADARG; }
+  if (n == 0) return PBHC_OK;
   P.sm_body = 0;
-  P.sm_ref = up4(c.Jb * 13);
-  P.sm_cf = P.sm_ref + up4(tab->rec_stride);
-  P.sm_feat = P.sm_cf + up4(c.Jb * 3);
-  P.sm_per_warp = P.sm_feat + up4(feat_len) + 1;  // +1: odd stride between warps
-  const size_t shmem = (size_t)kTW * P.sm_per_warp * sizeof(float);
-  if (shmem > 200 * 1024) { set_error("pbhc_track_step: shared memory %zu B too large", shmem); return PBHC_E_RANGE; }
+  P.sm_cf = up4h(c.Jb * 13);
+  P.sm_rows = P.sm_cf + up4h(c.Jb * 3);
+  P.sm_rv = P.sm_rows + up4h(P.rows_len);
+  P.sm_pre = P.sm_rv + kRv;
+  P.sm_per_warp = P.sm_pre + kPre * 32;
+  const size_t shmem = ((sizeof(BlockTables) + 15) & ~size_t(15)) + sizeof(int) * (up4h(P.n_hdst_max * c.hist_row) + up4h(push)) +
+                       (size_t)kTW * P.sm_per_warp * sizeof(float);
+  if (shmem > 220 * 1024) { set_error("pbhc_track_step: shared memory %zu B too large", shmem); return PBHC_E_RANGE; }
   static thread_local size_t configured = 0;
-  if (shmem > configured) {
+  if (shmem > configured || g_track_blocks_per_sm == 0) {
     if (cudaFuncSetAttribute(track_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shmem) != cudaSuccess) return check_launch("pbhc_track_step(attr)");
+    (void)cudaFuncSetAttribute(track_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
     configured = shmem;
     int per_sm = 0;
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, track_kernel, kTW * 32, shmem);
-    g_track_blocks_per_sm = per_sm < 1 ? 1 : (per_sm > 4 ? 4 : per_sm);
+    g_track_blocks_per_sm = per_sm < 1 ? 1 : (per_sm > 8 ? 8 : per_sm);
   }
   int64_t blocks = (n + kTW - 1) / kTW;
   const int64_t cap = 148LL * g_track_blocks_per_sm;

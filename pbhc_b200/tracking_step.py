@@ -175,34 +175,28 @@ class TrackingStep:
         c.cur_dof_vel = cur(s.limit_cur["dof_vel"], s.limit_cur["dof_vel"]["enable"])
         c.cur_torque = cur(s.limit_cur["torque"], s.limit_cur["torque"]["enable"])
         c.num_compute_average_epl = s.num_compute_average_epl
-        # observation gather maps over the feature vector [sources | history (logical order)]
-        src_off, off = {}, 0
-        for k in OBS_SRC:
-            src_off[k] = off
-            off += obs_src_dim(k, s.D, s.J, s.L)
-        hist_off, hbase = off, {}
-        for k, b in zip(s.hist_keys, self._hist_base):
-            hbase[k] = hist_off + b
+        # observation rows: where each source / history key sits in each group (include/pbhc_b200.h)
         used = 0
-        self._maps = []
         c.n_groups = len(s.obs_groups)
+        for k in range(len(OBS_SRC)):
+            for g in range(_lib.MAX_OBS_GROUPS):
+                c.src_dst[k][g] = -1
+        n_hd = 0
         for g, (name, grp) in enumerate(s.obs_groups.items()):
-            idx, mul = [], []
+            c.group_dim[g] = grp["dim"]
             for seg in grp["segs"]:
                 if seg["kind"] == "src":
-                    used |= 1 << OBS_SRC_IDS[seg["key"]]
-                    idx += list(range(src_off[seg["key"]], src_off[seg["key"]] + seg["dim"]))
-                    mul += [1.0] * seg["dim"]  # the source scale is folded into the feature
+                    k = OBS_SRC_IDS[seg["key"]]
+                    used |= 1 << k
+                    c.src_dst[k][g] = seg["off"]  # the source scale is applied by the producer
                     if seg["noise"] != 0:
                         raise NotImplementedError("observation noise: use noise scale 0 (obs/motion_tracking/benchmark.yaml) for now")
                 else:
-                    n = seg["len"] * seg["dim"]
-                    idx += list(range(hbase[seg["key"]], hbase[seg["key"]] + n))
-                    mul += [seg["scale"]] * n
-            tm = torch.tensor(idx, dtype=torch.int32, device=dev)
-            tf = torch.tensor(mul, dtype=torch.float32, device=dev)
-            self._maps.append((tm, tf))
-            c.group_dim[g], c.group_map[g], c.group_mul[g] = grp["dim"], tm.data_ptr(), tf.data_ptr()
+                    if n_hd >= _lib.MAX_HIST_DST:
+                        raise NotImplementedError("too many history segments in the observation groups")
+                    c.hist_dst[n_hd] = _lib.HistDst(s.hist_keys.index(seg["key"]), g, seg["off"], seg["len"], seg["scale"])
+                    n_hd += 1
+        c.n_hist_dst = n_hd
         for i, k in enumerate(OBS_SRC):
             c.obs_scale[i] = s.obs_scales.get(k, 1.0)
             c.obs_noise[i] = 0.0
