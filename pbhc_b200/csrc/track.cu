@@ -22,6 +22,7 @@ namespace pbhc {
 constexpr int kTW = 8;                      // warps (envs in flight) per block
 constexpr int kTrackMaxBlocks = 148 * 8;
 constexpr int kPre = 22;                    // per-env values of the pre phase
+constexpr int kChunk = 16;                  // envs per pre phase (lanes used by it)
 constexpr int kRv = 48;                     // per-env scalar table (see enum Rv)
 constexpr int kMaxHistDstPerKey = 4;
 
@@ -263,13 +264,15 @@ __device__ void build_tables(const TrackParams& P, BlockTables& T, int* hmap, in
     const int head = (int)((len - (push_count % len)) % len);
     const int s = (ps - head + len) % len;  // logical slot
     int nd = 0;
+    const int H = c.hist_row;
     for (int e = 0; e < c.n_hist_dst && nd < kMaxHistDstPerKey; ++e) {
       const PbhcHistDst& h = c.hist_dst[e];
       if (h.key != k) continue;
-      hmap[nd * c.hist_row + i] = s < h.len ? ((P.row_off[h.group] + h.offset + s * dim + cc) | (e << 24)) : -1;
+      const int m = s < h.len ? ((P.row_off[h.group] + h.offset + s * dim + cc) | (P.hist_any_mul ? (e << 24) : 0)) : -1;
+      hmap[nd < 2 ? 2 * i + nd : nd * H + i] = m;
       ++nd;
     }
-    for (; nd < P.n_hdst_max; ++nd) hmap[nd * c.hist_row + i] = -1;
+    for (; nd < (P.n_hdst_max < 2 ? 2 : P.n_hdst_max); ++nd) hmap[nd < 2 ? 2 * i + nd : nd * H + i] = -1;
   }
   __syncthreads();
   for (int i = tid; i < P.push_len; i += nt) {
@@ -341,6 +344,42 @@ __device__ __forceinline__ void warp_store_clipped(float* dst, const float* src,
   }
 }
 
+
+// Scatters one env's history ring (global, physical slot order) into the observation rows.  hmap holds, per physical
+// element, its first two destinations interleaved ({m0, m1}, -1 = none) followed by planes for destinations 2, 3.
+__device__ __forceinline__ void hist_scatter(const float* gh, float* rows, const int* hmap, const PbhcTrackCfg& c, int n_dst,
+                                             int any_mul, int vec, int lane, bool zero) {
+  const int H = c.hist_row;
+  if (!any_mul && vec == 4) {
+    const float4* g4 = reinterpret_cast<const float4*>(gh);
+    const int4* m4 = reinterpret_cast<const int4*>(hmap);
+    for (int i = lane; i < (H >> 2); i += 32) {
+      const float4 v = zero ? make_float4(0.f, 0.f, 0.f, 0.f) : g4[i];
+      const int4 a = m4[2 * i], b = m4[2 * i + 1];  // {m0,m1} of elements 4i, 4i+1 | 4i+2, 4i+3
+      if (a.x >= 0) rows[a.x] = v.x;
+      if (a.y >= 0) rows[a.y] = v.x;
+      if (a.z >= 0) rows[a.z] = v.y;
+      if (a.w >= 0) rows[a.w] = v.y;
+      if (b.x >= 0) rows[b.x] = v.z;
+      if (b.y >= 0) rows[b.y] = v.z;
+      if (b.z >= 0) rows[b.z] = v.w;
+      if (b.w >= 0) rows[b.w] = v.w;
+    }
+  } else {
+    for (int i = lane; i < H; i += 32) {
+      const float v = zero ? 0.0f : gh[i];
+      const int m0 = hmap[2 * i], m1 = hmap[2 * i + 1];
+      if (m0 >= 0) rows[m0 & 0xffffff] = any_mul ? v * c.hist_dst[m0 >> 24].mul : v;
+      if (m1 >= 0) rows[m1 & 0xffffff] = any_mul ? v * c.hist_dst[m1 >> 24].mul : v;
+    }
+  }
+  for (int d = 2; d < n_dst; ++d)
+    for (int i = lane; i < H; i += 32) {
+      const int m = hmap[d * H + i];
+      if (m >= 0) rows[m & 0xffffff] = zero ? 0.0f : (any_mul ? gh[i] * c.hist_dst[m >> 24].mul : gh[i]);
+    }
+}
+
 __host__ __device__ inline int vec_of(int64_t row_floats, const void* base) {
   const uintptr_t a = (uintptr_t)base;
   if ((row_floats & 3) == 0 && (a & 15) == 0) return 4;
@@ -357,7 +396,7 @@ __global__ void __launch_bounds__(kTW * 32, 3) track_kernel(const __grid_constan
   const PbhcTrackIO& io = P.io;
   const PbhcTableDesc& tab = P.tab;
   int* hmap = reinterpret_cast<int*>(smem_raw + ((sizeof(BlockTables) + 15) & ~size_t(15)));
-  int* pmap = hmap + up4(P.n_hdst_max * c.hist_row);
+  int* pmap = hmap + up4((P.n_hdst_max < 2 ? 2 : P.n_hdst_max) * c.hist_row);
   float* wbase = reinterpret_cast<float*>(pmap + up4(P.push_len));
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int J = c.J, Jb = c.Jb, D = c.D, L = c.L, Cm = tab.contact_size;
@@ -384,12 +423,12 @@ __global__ void __launch_bounds__(kTW * 32, 3) track_kernel(const __grid_constan
   double acc_reg = 0.0;
 
   const int64_t stride = (int64_t)gridDim.x * kTW;
-  for (int64_t chunk = (int64_t)blockIdx.x * kTW + warp; chunk < P.n; chunk += 32 * stride) {
+  for (int64_t chunk = (int64_t)blockIdx.x * kTW + warp; chunk < P.n; chunk += kChunk * stride) {
     // ---- pre phase: lane i = i-th env of this chunk (legged_robot_base.py:346-353, motion_tracking.py:548-558, 678-739) ----
     __syncwarp();
     {
       const int64_t m = chunk + (int64_t)lane * stride;
-      if (m < P.n) {
+      if (lane < kChunk && m < P.n) {
         const int64_t ep = io.episode_length_buf[m] + 1;  // legged_robot_base.py:299
         const float start = io.env_f32[m * PBHC_ENVF_STRIDE];
         const int clip = resolve_clip(tab, io.clip_of_motion, io.motion_ids[m]);
@@ -401,22 +440,22 @@ __global__ void __launch_bounds__(kTW * 32, 3) track_kernel(const __grid_constan
         const V3 bav = quat_rotate_inverse(rq, {root[10], root[11], root[12]});
         const V3 pg = quat_rotate_inverse(rq, {0.0f, 0.0f, -1.0f});
         const Q4 hinv = heading_quat_inv(rq);
-        pre[P_F0 * 32 + lane] = __int_as_float((int)fb.f0);
-        pre[P_F1 * 32 + lane] = __int_as_float((int)fb.f1);
-        pre[P_BLEND * 32 + lane] = fb.blend;
-        pre[P_PHASE * 32 + lane] = t / tab.clip_length[clip];  // motion_tracking.py:738-739
-        pre[P_HZ * 32 + lane] = hinv.z; pre[P_HW * 32 + lane] = hinv.w;
-        pre[P_RPX * 32 + lane] = root[0]; pre[P_RPY * 32 + lane] = root[1]; pre[P_RPZ * 32 + lane] = root[2];
-        pre[(P_BLV + 0) * 32 + lane] = blv.x; pre[(P_BLV + 1) * 32 + lane] = blv.y; pre[(P_BLV + 2) * 32 + lane] = blv.z;
-        pre[(P_BAV + 0) * 32 + lane] = bav.x; pre[(P_BAV + 1) * 32 + lane] = bav.y; pre[(P_BAV + 2) * 32 + lane] = bav.z;
-        pre[(P_PG + 0) * 32 + lane] = pg.x; pre[(P_PG + 1) * 32 + lane] = pg.y; pre[(P_PG + 2) * 32 + lane] = pg.z;
-        pre[P_CLIP * 32 + lane] = __int_as_float(clip);
-        pre[P_GRAVN * 32 + lane] = norm2(pg.x, pg.y);
-        pre[P_ORIENT * 32 + lane] = pg.x * pg.x + pg.y * pg.y;
+        pre[(P_F0) * kChunk + lane] = __int_as_float((int)fb.f0);
+        pre[(P_F1) * kChunk + lane] = __int_as_float((int)fb.f1);
+        pre[(P_BLEND) * kChunk + lane] = fb.blend;
+        pre[(P_PHASE) * kChunk + lane] = t / tab.clip_length[clip];  // motion_tracking.py:738-739
+        pre[(P_HZ) * kChunk + lane] = hinv.z; pre[(P_HW) * kChunk + lane] = hinv.w;
+        pre[(P_RPX) * kChunk + lane] = root[0]; pre[(P_RPY) * kChunk + lane] = root[1]; pre[(P_RPZ) * kChunk + lane] = root[2];
+        pre[(P_BLV + 0) * kChunk + lane] = blv.x; pre[(P_BLV + 1) * kChunk + lane] = blv.y; pre[(P_BLV + 2) * kChunk + lane] = blv.z;
+        pre[(P_BAV + 0) * kChunk + lane] = bav.x; pre[(P_BAV + 1) * kChunk + lane] = bav.y; pre[(P_BAV + 2) * kChunk + lane] = bav.z;
+        pre[(P_PG + 0) * kChunk + lane] = pg.x; pre[(P_PG + 1) * kChunk + lane] = pg.y; pre[(P_PG + 2) * kChunk + lane] = pg.z;
+        pre[(P_CLIP) * kChunk + lane] = __int_as_float(clip);
+        pre[(P_GRAVN) * kChunk + lane] = norm2(pg.x, pg.y);
+        pre[(P_ORIENT) * kChunk + lane] = pg.x * pg.x + pg.y * pg.y;
       }
     }
     __syncwarp();
-    for (int e = 0; e < 32; ++e) {
+    for (int e = 0; e < kChunk; ++e) {
       const int64_t n = chunk + (int64_t)e * stride;
       if (n >= P.n) break;
       __syncwarp();
@@ -429,24 +468,15 @@ __global__ void __launch_bounds__(kTW * 32, 3) track_kernel(const __grid_constan
       float start = ef0.x, mlen = ef0.y, etr = ef1.z;
       warp_load(sm_body, io.body_state + n * io.body_env_stride, Jb * 13, body_vec, lane);
       warp_load(sm_cf, io.contact_forces + n * (Jb * 3), Jb * 3, cf_vec, lane);
-      const int clip = __float_as_int(pre[P_CLIP * 32 + e]);
-      const float b = pre[P_BLEND * 32 + e], omb = 1.0f - b;
-      const float* r0 = tab.records + (int64_t)__float_as_int(pre[P_F0 * 32 + e]) * tab.rec_stride;
-      const float* r1 = tab.records + (int64_t)__float_as_int(pre[P_F1 * 32 + e]) * tab.rec_stride;
-      const float hz = pre[P_HZ * 32 + e], hw = pre[P_HW * 32 + e];
-      const V3 rp = {pre[P_RPX * 32 + e], pre[P_RPY * 32 + e], pre[P_RPZ * 32 + e]};
+      const int clip = __float_as_int(pre[(P_CLIP) * kChunk + e]);
+      const float b = pre[(P_BLEND) * kChunk + e], omb = 1.0f - b;
+      const float* r0 = tab.records + (int64_t)__float_as_int(pre[(P_F0) * kChunk + e]) * tab.rec_stride;
+      const float* r1 = tab.records + (int64_t)__float_as_int(pre[(P_F1) * kChunk + e]) * tab.rec_stride;
+      const float hz = pre[(P_HZ) * kChunk + e], hw = pre[(P_HW) * kChunk + e];
+      const V3 rp = {pre[(P_RPX) * kChunk + e], pre[(P_RPY) * kChunk + e], pre[(P_RPZ) * kChunk + e]};
       const float org[3] = {io.env_origins[n * 3], io.env_origins[n * 3 + 1], io.env_origins[n * 3 + 2]};
       // history ring -> its places in the observation rows (HistoryHandler.query, history_handler.py:46-48)
-      if (c.hist_row > 0) {
-        const float* gh = io.hist + n * c.hist_row;
-        for (int i = lane; i < c.hist_row; i += 32) {
-          const float v = gh[i];
-          for (int d = 0; d < P.n_hdst_max; ++d) {
-            const int m = hmap[d * c.hist_row + i];
-            if (m >= 0) rows[m & 0xffffff] = P.hist_any_mul ? v * c.hist_dst[m >> 24].mul : v;
-          }
-        }
-      }
+      if (c.hist_row > 0) hist_scatter(io.hist + n * c.hist_row, rows, hmap, c, P.n_hdst_max, P.hist_any_mul, hist_vec, lane, false);
       __syncwarp();
       // ---- B. bodies: reference (lerp / slerp of the two frames), extended state, differences, heading-frame features
       float sums[16];
@@ -584,7 +614,7 @@ __global__ void __launch_bounds__(kTW * 32, 3) track_kernel(const __grid_constan
       const bool stumble = __any_sync(0xffffffffu, x_stumble);
       float air1 = __shfl_sync(0xffffffffu, air_f, 1), contact1 = __shfl_sync(0xffffffffu, contact_f, 1);  // lane 0 packs the state
       // ---- E. termination (legged_robot_base.py:408-489, motion_tracking.py:330-358) -------------------------------
-      const bool t_grav = c.term_gravity && pre[P_GRAVN * 32 + e] > c.term_gravity_thr;
+      const bool t_grav = c.term_gravity && pre[(P_GRAVN) * kChunk + e] > c.term_gravity_thr;
       const bool t_far = c.term_motion_far && any_far;
       const bool t_out = ep > c.max_episode_length;
       const bool t_end = c.term_motion_end && ((float)ep * c.dt + start > mlen);
@@ -595,7 +625,7 @@ __global__ void __launch_bounds__(kTW * 32, 3) track_kernel(const __grid_constan
         rv[V_T_GRAV] = t_grav; rv[V_T_FAR] = t_far; rv[V_T_OUT] = time_out; rv[V_T_END] = t_end;
         rv[V_RESET] = reset; rv[V_ONE] = 1.0f; rv[V_ALIVE] = 1.0f;
         rv[V_CONTACT] = 1.0f - x_cm / (float)c.n_feet; rv[V_CONTACT_V2] = 0.5f - x_cm / (float)c.n_feet;
-        rv[V_ORIENT] = pre[P_ORIENT * 32 + e];
+        rv[V_ORIENT] = pre[(P_ORIENT) * kChunk + e];
         rv[V_AIR] = x_air; rv[V_FORCE] = x_force; rv[V_STUMBLE] = stumble ? 1.0f : 0.0f; rv[V_SLIP] = x_slip; rv[V_FSLIP] = x_fslip;
         rv[V_LIM_POS] = l_pos; rv[V_LIM_VEL] = l_vel; rv[V_LIM_TQ] = l_tq; rv[V_COLLIDE] = (float)n_collide;
       }
@@ -643,14 +673,9 @@ __global__ void __launch_bounds__(kTW * 32, 3) track_kernel(const __grid_constan
         act = 0.0f;
         if (ld) io.actions[n * D + lane] = 0.0f;
         air0 = 0.0f; air1 = 0.0f; contact0 = 0.0f; contact1 = 0.0f;
-        if (c.hist_row > 0) {  // HistoryHandler.reset: zero rows (and what the observation rows already took from them)
-          for (int i = lane; i < c.hist_row; i += 32) {
-            io.hist[n * c.hist_row + i] = 0.0f;
-            for (int d = 0; d < P.n_hdst_max; ++d) {
-              const int m = hmap[d * c.hist_row + i];
-              if (m >= 0) rows[m & 0xffffff] = 0.0f;
-            }
-          }
+        if (c.hist_row > 0) {  // HistoryHandler.reset: zero the ring (and what the observation rows already took from it)
+          for (int i = lane; i < c.hist_row; i += 32) io.hist[n * c.hist_row + i] = 0.0f;
+          hist_scatter(io.hist + n * c.hist_row, rows, hmap, c, P.n_hdst_max, P.hist_any_mul, hist_vec, lane, true);
         }
         ep = 0;
         if (ld) {  // _episodic_domain_randomization
@@ -712,9 +737,9 @@ __global__ void __launch_bounds__(kTW * 32, 3) track_kernel(const __grid_constan
       if (lane < 16) {
         int k, ce = 0;
         float val;
-        if (lane < 9) { k = lane / 3; ce = lane - 3 * k; val = pre[(P_BLV + lane) * 32 + e]; }
+        if (lane < 9) { k = lane / 3; ce = lane - 3 * k; val = pre[(P_BLV + lane) * kChunk + e]; }
         else if (lane < 12) { k = S_DR_COM; ce = lane - 9; val = io.base_com_bias[n * 3 + ce]; }
-        else if (lane == 12) { k = S_PHASE; val = pre[P_PHASE * 32 + e]; }   // stale for envs that reset, like the reference
+        else if (lane == 12) { k = S_PHASE; val = pre[(P_PHASE) * kChunk + e]; }   // stale for envs that reset, like the reference
         else if (lane == 13) { k = S_DR_FRICTION; val = io.friction[n]; }
         else if (lane == 14) { k = S_DR_DELAY; val = (float)delay; }
         else { k = S_BASE_POS_Z; val = rp.z; }
@@ -919,8 +944,8 @@ extern "C" int pbhc_track_step(const PbhcTrackCfg* cfg, const PbhcTableDesc* tab
   P.sm_rows = P.sm_cf + up4h(c.Jb * 3);
   P.sm_rv = P.sm_rows + up4h(P.rows_len);
   P.sm_pre = P.sm_rv + kRv;
-  P.sm_per_warp = P.sm_pre + kPre * 32;
-  const size_t shmem = ((sizeof(BlockTables) + 15) & ~size_t(15)) + sizeof(int) * (up4h(P.n_hdst_max * c.hist_row) + up4h(push)) +
+  P.sm_per_warp = P.sm_pre + kPre * kChunk;
+  const size_t shmem = ((sizeof(BlockTables) + 15) & ~size_t(15)) + sizeof(int) * (up4h((P.n_hdst_max < 2 ? 2 : P.n_hdst_max) * c.hist_row) + up4h(push)) +
                        (size_t)kTW * P.sm_per_warp * sizeof(float);
   if (shmem > 220 * 1024) { set_error("pbhc_track_step: shared memory %zu B too large", shmem); return PBHC_E_RANGE; }
   static thread_local size_t configured = 0;
