@@ -65,6 +65,11 @@ struct TrackParams {
   int push_off[PBHC_MAX_HIST_KEYS];      // offset of key k inside the push staging
   int hist_base[PBHC_MAX_HIST_KEYS];     // offset of key k inside the global history row
   int sm_body, sm_cf, sm_rows, sm_rv, sm_pre, sm_per_warp;  // per-warp shared-memory offsets (floats)
+  int o_hmap, o_pmap, o_warp, warp_bytes;                    // byte offsets inside the dynamic shared memory
+  int ob_body, ob_cf, ob_rows, ob_rv, ob_pre;                // byte offsets of the per-warp regions
+  int e_pos, e_vel, e_ang, e_dp, e_dv, e_c;                  // float offsets inside a table record
+  int body_vec, cf_vec, hist_vec, obs_vec[PBHC_MAX_OBS_GROUPS];  // widest vector access each row alignment allows
+  int dump;                                                  // float offset (in `rows`) of the scratch region absent destinations write to
   int hist_any_mul;                      // some history destination has mul != 1
   int n_hdst_max;                        // max destinations of one history element
 };
@@ -242,7 +247,7 @@ __device__ void build_tables(const TrackParams& P, BlockTables& T, int* hmap, in
   }
   for (int i = tid; i < PBHC_NUM_OBS_SRC * 8; i += nt) {
     const int k = i >> 3, g = i & 7;
-    int off = -1;
+    int off = P.dump;  // absent destination: the scratch region
     if (g < PBHC_MAX_OBS_GROUPS) { if (g < c.n_groups && c.src_dst[k][g] >= 0) off = P.row_off[g] + c.src_dst[k][g]; }
     else if (g == PBHC_MAX_OBS_GROUPS) for (int h = 0; h < c.n_hist_keys; ++h) if (c.hist_src[h] == k) off = P.row_off[c.n_groups] + P.push_off[h];
     T.sdst[k][g] = off;
@@ -268,11 +273,11 @@ __device__ void build_tables(const TrackParams& P, BlockTables& T, int* hmap, in
     for (int e = 0; e < c.n_hist_dst && nd < kMaxHistDstPerKey; ++e) {
       const PbhcHistDst& h = c.hist_dst[e];
       if (h.key != k) continue;
-      const int m = s < h.len ? ((P.row_off[h.group] + h.offset + s * dim + cc) | (P.hist_any_mul ? (e << 24) : 0)) : -1;
+      const int m = s < h.len ? ((P.row_off[h.group] + h.offset + s * dim + cc) | (P.hist_any_mul ? (e << 24) : 0)) : P.dump + (i & 63);
       hmap[nd < 2 ? 2 * i + nd : nd * H + i] = m;
       ++nd;
     }
-    for (; nd < (P.n_hdst_max < 2 ? 2 : P.n_hdst_max); ++nd) hmap[nd < 2 ? 2 * i + nd : nd * H + i] = -1;
+    for (; nd < (P.n_hdst_max < 2 ? 2 : P.n_hdst_max); ++nd) hmap[nd < 2 ? 2 * i + nd : nd * H + i] = P.dump + (i & 63);
   }
   __syncthreads();
   for (int i = tid; i < P.push_len; i += nt) {
@@ -283,24 +288,23 @@ __device__ void build_tables(const TrackParams& P, BlockTables& T, int* hmap, in
   __syncthreads();
 }
 
-// writes `v` of element `e` of one observation source into every row that shows it (sd = T.sdst[source])
+// writes `v` of element `e` of one observation source into every row that shows it (sd = T.sdst[source]); absent
+// destinations point at the per-warp scratch region, so the stores are unconditional
 __device__ __forceinline__ void put1(const int* sd, float* rows, int e, float v) {
   const int4 d = *reinterpret_cast<const int4*>(sd);
   const int push = sd[4];
-  if (d.x >= 0) rows[d.x + e] = v;
-  if (d.y >= 0) rows[d.y + e] = v;
-  if (d.z >= 0) rows[d.z + e] = v;
-  if (d.w >= 0) rows[d.w + e] = v;
-  if (push >= 0) rows[push + e] = v;
+  float* r = rows + e;
+  r[d.x] = v; r[d.y] = v; r[d.z] = v; r[d.w] = v; r[push] = v;
 }
 __device__ __forceinline__ void put3(const int* sd, float* rows, int e, float x, float y, float z) {
   const int4 d = *reinterpret_cast<const int4*>(sd);
   const int push = sd[4];
-  if (d.x >= 0) { rows[d.x + e] = x; rows[d.x + e + 1] = y; rows[d.x + e + 2] = z; }
-  if (d.y >= 0) { rows[d.y + e] = x; rows[d.y + e + 1] = y; rows[d.y + e + 2] = z; }
-  if (d.z >= 0) { rows[d.z + e] = x; rows[d.z + e + 1] = y; rows[d.z + e + 2] = z; }
-  if (d.w >= 0) { rows[d.w + e] = x; rows[d.w + e + 1] = y; rows[d.w + e + 2] = z; }
-  if (push >= 0) { rows[push + e] = x; rows[push + e + 1] = y; rows[push + e + 2] = z; }
+  float* r = rows + e;
+  r[d.x] = x; r[d.x + 1] = y; r[d.x + 2] = z;
+  r[d.y] = x; r[d.y + 1] = y; r[d.y + 2] = z;
+  r[d.z] = x; r[d.z + 1] = y; r[d.z + 2] = z;
+  r[d.w] = x; r[d.w + 1] = y; r[d.w + 2] = z;
+  r[push] = x; r[push + 1] = y; r[push + 2] = z;
 }
 
 // global -> shared copy of `count` floats with the widest vector the row alignment allows (vec = 4, 2 or 1)
@@ -355,15 +359,9 @@ __device__ __forceinline__ void hist_scatter(const float* gh, float* rows, const
     const int4* m4 = reinterpret_cast<const int4*>(hmap);
     for (int i = lane; i < (H >> 2); i += 32) {
       const float4 v = zero ? make_float4(0.f, 0.f, 0.f, 0.f) : g4[i];
-      const int4 a = m4[2 * i], b = m4[2 * i + 1];  // {m0,m1} of elements 4i, 4i+1 | 4i+2, 4i+3
-      if (a.x >= 0) rows[a.x] = v.x;
-      if (a.y >= 0) rows[a.y] = v.x;
-      if (a.z >= 0) rows[a.z] = v.y;
-      if (a.w >= 0) rows[a.w] = v.y;
-      if (b.x >= 0) rows[b.x] = v.z;
-      if (b.y >= 0) rows[b.y] = v.z;
-      if (b.z >= 0) rows[b.z] = v.w;
-      if (b.w >= 0) rows[b.w] = v.w;
+      const int4 a = m4[2 * i], b = m4[2 * i + 1];  // {m0,m1} of elements 4i, 4i+1 | 4i+2, 4i+3 (absent -> scratch)
+      rows[a.x] = v.x; rows[a.y] = v.x; rows[a.z] = v.y; rows[a.w] = v.y;
+      rows[b.x] = v.z; rows[b.y] = v.z; rows[b.z] = v.w; rows[b.w] = v.w;
     }
   } else {
     for (int i = lane; i < H; i += 32) {
@@ -395,25 +393,22 @@ __global__ void __launch_bounds__(kTW * 32, 3) track_kernel(const __grid_constan
   const PbhcTrackCfg& c = P.c;
   const PbhcTrackIO& io = P.io;
   const PbhcTableDesc& tab = P.tab;
-  int* hmap = reinterpret_cast<int*>(smem_raw + ((sizeof(BlockTables) + 15) & ~size_t(15)));
-  int* pmap = hmap + up4((P.n_hdst_max < 2 ? 2 : P.n_hdst_max) * c.hist_row);
-  float* wbase = reinterpret_cast<float*>(pmap + up4(P.push_len));
+  int* hmap = reinterpret_cast<int*>(smem_raw + P.o_hmap);
+  int* pmap = reinterpret_cast<int*>(smem_raw + P.o_pmap);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int J = c.J, Jb = c.Jb, D = c.D, L = c.L, Cm = tab.contact_size;
-  float* sm_body = wbase + warp * P.sm_per_warp + P.sm_body;
-  float* sm_cf = wbase + warp * P.sm_per_warp + P.sm_cf;
-  float* rows = wbase + warp * P.sm_per_warp + P.sm_rows;
-  float* rv = wbase + warp * P.sm_per_warp + P.sm_rv;
-  float* pre = wbase + warp * P.sm_per_warp + P.sm_pre;
+  unsigned char* wp = smem_raw + P.o_warp + warp * P.warp_bytes;
+  float* sm_body = reinterpret_cast<float*>(wp + P.ob_body);
+  float* sm_cf = reinterpret_cast<float*>(wp + P.ob_cf);
+  float* rows = reinterpret_cast<float*>(wp + P.ob_rows);
+  float* rv = reinterpret_cast<float*>(wp + P.ob_rv);
+  float* pre = reinterpret_cast<float*>(wp + P.ob_pre);
   build_tables(P, T, hmap, pmap);
 
   const float far_thr = (float)T.scal[PBHC_S_FAR_THR];
   const uint32_t push_count = (uint32_t)(uint64_t)T.scal[PBHC_S_PUSH_COUNT];
-  const int e_pos = 4 * J, e_vel = 7 * J, e_ang = 10 * J, e_dp = 13 * J, e_dv = e_dp + D, e_c = e_dv + D;
-  const int body_vec = vec_of(io.body_env_stride, io.body_state) == 4 && ((Jb * 13) & 3) == 0 ? 4
-                       : (vec_of(io.body_env_stride, io.body_state) >= 2 && ((Jb * 13) & 1) == 0 ? 2 : 1);
-  const int cf_vec = vec_of(Jb * 3, io.contact_forces);
-  const int hist_vec = c.hist_row > 0 ? vec_of(c.hist_row, io.hist) : 1;
+  const int e_pos = P.e_pos, e_vel = P.e_vel, e_ang = P.e_ang, e_dp = P.e_dp, e_dv = P.e_dv, e_c = P.e_c;
+  const int body_vec = P.body_vec, cf_vec = P.cf_vec, hist_vec = P.hist_vec;
   uint64_t feet_mask = 0;
   for (int f = 0; f < c.n_feet; ++f) feet_mask |= 1ull << c.feet_ids[f];
   const int my_foot = lane < c.n_feet ? (lane == 0 ? c.feet_ids[0] : c.feet_ids[1]) : 0;
@@ -422,13 +417,13 @@ __global__ void __launch_bounds__(kTW * 32, 3) track_kernel(const __grid_constan
   const float lim_v = ld ? T.lim_vel[lane] : 0.f, lim_t = ld ? T.lim_tq[lane] : 0.f;
   double acc_reg = 0.0;
 
-  const int64_t stride = (int64_t)gridDim.x * kTW;
-  for (int64_t chunk = (int64_t)blockIdx.x * kTW + warp; chunk < P.n; chunk += kChunk * stride) {
+  const int stride = (int)gridDim.x * kTW, n_envs = (int)P.n;  // P.n < 2^31 / kChunk (checked by the launcher): 32-bit env ids
+  for (int chunk = (int)blockIdx.x * kTW + warp; chunk < n_envs; chunk += kChunk * stride) {
     // ---- pre phase: lane i = i-th env of this chunk (legged_robot_base.py:346-353, motion_tracking.py:548-558, 678-739) ----
     __syncwarp();
     {
-      const int64_t m = chunk + (int64_t)lane * stride;
-      if (lane < kChunk && m < P.n) {
+      const int64_t m = chunk + lane * stride;
+      if (lane < kChunk && m < n_envs) {
         const int64_t ep = io.episode_length_buf[m] + 1;  // legged_robot_base.py:299
         const float start = io.env_f32[m * PBHC_ENVF_STRIDE];
         const int clip = resolve_clip(tab, io.clip_of_motion, io.motion_ids[m]);
@@ -456,8 +451,9 @@ __global__ void __launch_bounds__(kTW * 32, 3) track_kernel(const __grid_constan
     }
     __syncwarp();
     for (int e = 0; e < kChunk; ++e) {
-      const int64_t n = chunk + (int64_t)e * stride;
-      if (n >= P.n) break;
+      const int n32 = chunk + e * stride;
+      if (n32 >= n_envs) break;
+      const int64_t n = n32;  // sign-extended 32-bit: every n * row_size below is one IMAD.WIDE
       __syncwarp();
       // ---- A. per-env scalars + staging of the simulator state --------------------------------------------
       int64_t ep = io.episode_length_buf[n] + 1;
@@ -762,7 +758,7 @@ __global__ void __launch_bounds__(kTW * 32, 3) track_kernel(const __grid_constan
       // ---- I. rows -> global (clipped), history push, state write-back -----------------------------------------------
       for (int g = 0; g < c.n_groups; ++g) {
         const int dim = c.group_dim[g];
-        warp_store_clipped(io.obs[g] + n * dim, rows + P.row_off[g], dim, vec_of(dim, io.obs[g]), c.clip_obs, lane);
+        warp_store_clipped(io.obs[g] + n * dim, rows + P.row_off[g], dim, P.obs_vec[g], c.clip_obs, lane);
       }
       if (P.push_len > 0) {  // HistoryHandler.add (history_handler.py:40-44) as a ring-buffer push: one slot per key is written
         float* gh = io.hist + n * c.hist_row;
@@ -939,14 +935,29 @@ extern "C" int pbhc_track_step(const PbhcTrackCfg* cfg, const PbhcTableDesc* tab
   }
   for (int k = 0; k < c.n_hist_keys; ++k) if (c.hist_len[k] <= 0 || c.hist_dim[k] != src_dim(c.hist_src[k], c.D, c.J, c.L)) { set_error("pbhc_track_step: bad history key %d", k); return PBHC_E_BADARG; }
   if (n == 0) return PBHC_OK;
+  P.dump = P.rows_len;                                   // scratch for absent destinations: one source wide
+  const int dump_len = up4h(3 * c.J + 4);
   P.sm_body = 0;
   P.sm_cf = up4h(c.Jb * 13);
   P.sm_rows = P.sm_cf + up4h(c.Jb * 3);
-  P.sm_rv = P.sm_rows + up4h(P.rows_len);
+  P.sm_rv = P.sm_rows + up4h(P.rows_len) + dump_len;
   P.sm_pre = P.sm_rv + kRv;
   P.sm_per_warp = P.sm_pre + kPre * kChunk;
-  const size_t shmem = ((sizeof(BlockTables) + 15) & ~size_t(15)) + sizeof(int) * (up4h((P.n_hdst_max < 2 ? 2 : P.n_hdst_max) * c.hist_row) + up4h(push)) +
-                       (size_t)kTW * P.sm_per_warp * sizeof(float);
+  P.o_hmap = (int)((sizeof(BlockTables) + 15) & ~size_t(15));
+  P.o_pmap = P.o_hmap + 4 * up4h((P.n_hdst_max < 2 ? 2 : P.n_hdst_max) * c.hist_row);
+  P.o_warp = P.o_pmap + 4 * up4h(push);
+  P.warp_bytes = 4 * P.sm_per_warp;
+  P.ob_body = 4 * P.sm_body; P.ob_cf = 4 * P.sm_cf; P.ob_rows = 4 * P.sm_rows; P.ob_rv = 4 * P.sm_rv; P.ob_pre = 4 * P.sm_pre;
+  P.e_pos = 4 * c.J; P.e_vel = 7 * c.J; P.e_ang = 10 * c.J; P.e_dp = 13 * c.J; P.e_dv = P.e_dp + c.D; P.e_c = P.e_dv + c.D;
+  {
+    const int bv = vec_of(io->body_env_stride, io->body_state);
+    P.body_vec = (bv == 4 && ((c.Jb * 13) & 3) == 0) ? 4 : ((bv >= 2 && ((c.Jb * 13) & 1) == 0) ? 2 : 1);
+    P.cf_vec = vec_of(c.Jb * 3, io->contact_forces);
+    P.hist_vec = c.hist_row > 0 ? vec_of(c.hist_row, io->hist) : 1;
+    for (int g = 0; g < PBHC_MAX_OBS_GROUPS; ++g) P.obs_vec[g] = g < c.n_groups ? vec_of(c.group_dim[g], io->obs[g]) : 1;
+  }
+  if (n > 0x7fffffffLL / (kChunk * 2)) { set_error("pbhc_track_step: too many envs for one launch"); return PBHC_E_RANGE; }
+  const size_t shmem = (size_t)P.o_warp + (size_t)kTW * P.warp_bytes;
   if (shmem > 220 * 1024) { set_error("pbhc_track_step: shared memory %zu B too large", shmem); return PBHC_E_RANGE; }
   static thread_local size_t configured = 0;
   if (shmem > configured || g_track_blocks_per_sm == 0) {
