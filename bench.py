@@ -275,7 +275,7 @@ def run_b200_arm(a):
     for i in range(Kk):
         ev[i][0].record()
         if with_fk:
-            wl.fk_out = wl.fk()
+            wl.fk()
         ev[i][1].record()
         ts.launch()
         ev[i][2].record()

@@ -7,8 +7,8 @@
 
 namespace pbhc {
 
-constexpr int kChunk = 4;         // joints per staging chunk
-constexpr int kFkWarps = 4;
+constexpr int kChunk = 3;         // joints per staging chunk
+constexpr int kFkWarps = 1;         // one warp per block: 15 blocks (= pose tiles) fit an SM, 65536 poses are a single wave
 constexpr int kMaxSlots = 8;
 constexpr int kStageRow = kChunk * 16 + 1;  // odd stride -> conflict-free per-thread rows
 constexpr int kInRow = kChunk * 3 + 1;
@@ -66,20 +66,28 @@ __device__ __forceinline__ void mat_to_quat_xyzw(const M3& R, float* q) {
   q[0] = c[1] / d; q[1] = c[2] / d; q[2] = c[3] / d; q[3] = c[0] / d;
 }
 
-// copy rows: global [pose][row_len] segment (col0 .. col0+ncol) <-> smem [lane][stride]
-__device__ __forceinline__ void fill_rows(float* sm, int stride, const float* g, int64_t row_len, int col0, int ncol, int npose, int lane) {
-  const int total = npose * ncol;
-  for (int f = lane; f < total; f += 32) {
-    const int t = f / ncol, c = f - t * ncol;
-    sm[t * stride + c] = __ldg(g + t * row_len + col0 + c);
+// Row staging between global memory ([pose][row_len], poses of a warp are contiguous) and shared memory
+// ([lane = pose][odd stride], conflict-free for the per-thread compute).  The copies run pose-major: for each pose the
+// lanes cover the chunk's columns, so the per-lane shared / global offsets are loop invariants and an iteration is
+// one LDS/LDG + one STG/STS (no integer division in the loop).
+__device__ __forceinline__ void fill_rows(float* sm, int stride, const float* g, int row_len, int col0, int ncol, int npose, int lane) {
+  if (lane < ncol) {
+    const float* gp = g + col0 + lane;
+    float* sp = sm + lane;
+#pragma unroll 4
+    for (int t = 0; t < npose; ++t) sp[t * stride] = __ldg(gp + t * row_len);
   }
 }
-__device__ __forceinline__ void flush_rows(const float* sm, int stride, int sm_col0, int sm_jstride, int ncomp, float* g, int64_t row_len, int col0, int nj, int npose, int lane) {
-  const int ncol = nj * ncomp, total = npose * ncol;
-  for (int f = lane; f < total; f += 32) {
-    const int t = f / ncol, c = f - t * ncol;
-    const int jj = c / ncomp, cc = c - jj * ncomp;
-    g[t * row_len + col0 + c] = sm[t * stride + jj * sm_jstride + sm_col0 + cc];
+template <int NCOMP>
+__device__ __forceinline__ void flush_rows(const float* sm, int stride, int sm_col0, int sm_jstride, float* g, int row_len, int col0,
+                                           int nj, int npose, int lane) {
+  const int ncol = nj * NCOMP;
+  for (int c = lane; c < ncol; c += 32) {
+    const int jj = c / NCOMP, cc = c - jj * NCOMP;
+    const float* sp = sm + jj * sm_jstride + sm_col0 + cc;
+    float* gp = g + col0 + c;
+#pragma unroll 4
+    for (int t = 0; t < npose; ++t) gp[t * row_len] = sp[t * stride];
   }
 }
 
@@ -152,9 +160,9 @@ __global__ void __launch_bounds__(kFkWarps * 32) fk_kernel(const __grid_constant
       }
     }
     __syncwarp();
-    flush_rows(sm_out, kStageRow, 0, 16, 3, pos + p0 * (3 * J), 3 * J, 3 * j0, nj, npose, lane);
-    if (rotmat) flush_rows(sm_out, kStageRow, 3, 16, 9, rotmat + p0 * (9 * J), 9 * J, 9 * j0, nj, npose, lane);
-    if (quat) flush_rows(sm_out, kStageRow, 12, 16, 4, quat + p0 * (4 * J), 4 * J, 4 * j0, nj, npose, lane);
+    flush_rows<3>(sm_out, kStageRow, 0, 16, pos + p0 * (3 * J), 3 * J, 3 * j0, nj, npose, lane);
+    if (rotmat) flush_rows<9>(sm_out, kStageRow, 3, 16, rotmat + p0 * (9 * J), 9 * J, 9 * j0, nj, npose, lane);
+    if (quat) flush_rows<4>(sm_out, kStageRow, 12, 16, quat + p0 * (4 * J), 4 * J, 4 * j0, nj, npose, lane);
   }
 }
 
@@ -190,6 +198,11 @@ extern "C" int pbhc_fk(const PbhcTree* tree, const float* pose_aa, const float* 
   if (n == 0) return PBHC_OK;
   const size_t shmem = (size_t)kFkWarps * (32 * kInRow + 32 * kStageRow + P.n_slots * 12 * 32) * sizeof(float);
   static thread_local size_t configured = 0;
+  static thread_local bool carved = false;
+  if (!carved) {  // shared memory bounds the resident warps: ask for the largest carve-out
+    (void)cudaFuncSetAttribute(fk_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    carved = true;
+  }
   if (shmem > 48 * 1024 && shmem > configured) {
     if (cudaFuncSetAttribute(fk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shmem) != cudaSuccess) return check_launch("pbhc_fk(attr)");
     configured = shmem;

@@ -124,16 +124,20 @@ class Humanoid_Batch:
         self._c_tree = _lib.Tree(len(parents), self._c_parents, self._c_offsets, self._c_lrot)
 
     # ------------------------------------------------------------------------------------------
-    def fk(self, pose_aa, trans, want_mat=True, want_quat=True):
-        """pose_aa [n,J,3], trans [n,3] CUDA fp32 -> (pos [n,J,3], rotmat [n,J,3,3] | None, quat_xyzw [n,J,4] | None)."""
+    def fk(self, pose_aa, trans, want_mat=True, want_quat=True, out=None):
+        """pose_aa [n,J,3], trans [n,3] CUDA fp32 -> (pos [n,J,3], rotmat [n,J,3,3] | None, quat_xyzw [n,J,4] | None).
+        `out` = a previous result tuple to overwrite instead of allocating."""
         J = self.num_bodies_augment
         n = pose_aa.shape[0]
         pose_aa = pose_aa.contiguous()
         trans = trans.contiguous()
         dev = pose_aa.device
-        pos = torch.empty(n, J, 3, device=dev, dtype=torch.float32)
-        mat = torch.empty(n, J, 3, 3, device=dev, dtype=torch.float32) if want_mat else None
-        quat = torch.empty(n, J, 4, device=dev, dtype=torch.float32) if want_quat else None
+        if out is not None:
+            pos, mat, quat = out
+        else:
+            pos = torch.empty(n, J, 3, device=dev, dtype=torch.float32)
+            mat = torch.empty(n, J, 3, 3, device=dev, dtype=torch.float32) if want_mat else None
+            quat = torch.empty(n, J, 4, device=dev, dtype=torch.float32) if want_quat else None
         _lib.check(_lib.lib().pbhc_fk(C.byref(self._c_tree), _lib.ptr(pose_aa, torch.float32),
                                       _lib.ptr(trans, torch.float32), n, _lib.ptr(pos), _lib.ptr(mat), _lib.ptr(quat),
                                       _lib.stream_ptr(dev)))

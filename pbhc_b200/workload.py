@@ -114,12 +114,13 @@ class Workload:
     # ---- the step ------------------------------------------------------------------------------------------
     def fk(self):
         """K2 on the N per-env poses: positions + xyzw quaternions + rotation matrices."""
-        return self.lib.mesh_parsers.fk(self.pose_aa, self.trans, want_mat=True, want_quat=True)
+        self.fk_out = self.lib.mesh_parsers.fk(self.pose_aa, self.trans, want_mat=True, want_quat=True, out=getattr(self, "fk_out", None))
+        return self.fk_out
 
     def step(self, with_fk=True):
         """one tracked env step: [K2 FK] + fused lookup/diff/termination/reward/reset/obs/history kernel + finalize."""
         if with_fk:
-            self.fk_out = self.fk()
+            self.fk()
         self.ts.launch()
         self.ts.finalize()
         return self.ts.obs_buf_dict, self.ts.rew_buf, self.ts.reset_buf
