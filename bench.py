@@ -265,7 +265,7 @@ def run_b200_arm(a):
     if world > 1:
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
     total_ms = float(ms.item())
-    resets = float(ts.acc[_lib_index("A_RESET")].item()) / N
+    resets = float(ts.acc[_lib_index("A_RESET")].item()) / (N * world)
 
     # ---- per-kernel pass: the dominant kernel (pbhc_track_step = fused kernel + its 1-block reduction) and K2, eager,
     # CUDA events on the launching stream around each launch ----------------------------------------------------------
@@ -293,9 +293,7 @@ def run_b200_arm(a):
     sampler.mark("load_end")
     sampler.stop()
     if rank != 0:
-        if world > 1:
-            dist.destroy_process_group()
-        return 0
+        return _finish(torch, dist, world, graph)
 
     peak, peak_src = peaks()
     bytes_step, reads, writes = step_bytes(wl.spec)
@@ -328,8 +326,19 @@ def run_b200_arm(a):
                                           f"reference torch path (torch {r['torch']}, {r['cores']} threads), FK {'in' if with_fk else 'not in'} step",
                                 "ms_per_step": r["ms_per_step"]}
     print(json.dumps(line), flush=True)
+    return _finish(torch, dist, world, graph)
+
+
+def _finish(torch, dist, world, graph):
+    """Leaves without tearing NCCL down: destroy_process_group() after a CUDA graph captured a collective can block
+    forever (seen on the 2-GPU box); every rank drains its stream, meets at a barrier and exits."""
+    torch.cuda.synchronize()
     if world > 1:
-        dist.destroy_process_group()
+        dist.barrier()
+        torch.cuda.synchronize()
+        sys.stdout.flush()
+        sys.stderr.flush()
+        os._exit(0)
     return 0
 
 

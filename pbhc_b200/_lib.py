@@ -6,7 +6,7 @@ import os
 import torch  # noqa: F401  (loads libcudart.so.12 so the library resolves against torch's runtime)
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libpbhc_b200.so")
+LIB_PATH = os.environ.get("PBHC_B200_LIB") or os.path.join(_HERE, "libpbhc_b200.so")  # override: development A/B builds
 
 c_f32p = C.c_void_p
 ABI_VERSION = 2

@@ -23,7 +23,7 @@ constexpr int kTW = 8;                      // warps (envs in flight) per block
 constexpr int kTrackMaxBlocks = 148 * 8;
 constexpr int kPre = 22;                    // per-env values of the pre phase
 constexpr int kChunk = 16;                  // envs per pre phase (lanes used by it)
-constexpr int kRv = 48;                     // per-env scalar table (see enum Rv)
+constexpr int kRv = 56;                     // per-env scalar table (see enum Rv)
 constexpr int kMaxHistDstPerKey = 4;
 
 enum ObsSrc { S_BASE_LIN_VEL, S_BASE_ANG_VEL, S_PROJ_GRAV, S_DOF_POS, S_DOF_VEL, S_ACTIONS, S_PHASE, S_DIF_LOCAL,
@@ -37,7 +37,7 @@ enum SigmaId { G_MAX_JOINT, G_UPPER, G_LOWER, G_VR3, G_FEET, G_ROT, G_VEL, G_ANG
 // per-env scalar table `rv`: slots 0..22 are laid out like `acc` (PBHC_A_*), the rest are raw reward values
 enum Rv { V_SIGMA_ERR = 0, V_UP_N = 10, V_LO_N, V_VR_N, V_JOINT_N, V_T_GRAV, V_T_FAR, V_T_OUT, V_T_END, V_RESET, V_RESET_EPLEN,
           V_ETR, V_ETR_SQ, V_ONE, V_CONTACT = 24, V_CONTACT_V2, V_TQ2, V_DACT2, V_DV2, V_ACC2, V_ORIENT, V_ALIVE, V_AIR, V_FORCE,
-          V_STUMBLE, V_SLIP, V_FSLIP, V_LIM_POS, V_LIM_VEL, V_LIM_TQ, V_COLLIDE };
+          V_STUMBLE, V_SLIP, V_FSLIP, V_LIM_POS, V_LIM_VEL, V_LIM_TQ, V_COLLIDE, V_ENVF = 44 /* 8 floats */, V_EP = 52 /* int64 */ };
 enum RewardKind { K_RAW, K_EXP, K_EXP2 };
 // pre-phase values (per env)
 enum Pre { P_F0, P_F1, P_BLEND, P_PHASE, P_HZ, P_HW, P_RPX, P_RPY, P_RPZ, P_BLV, P_BAV = P_BLV + 3, P_PG = P_BAV + 3,
@@ -156,7 +156,7 @@ struct BlockTables {
   int r_kind[PBHC_MAX_REWARDS], r_arg[PBHC_MAX_REWARDS];
   float sum_div[16];                 // divisor applied to the k-th value of the 16-way reduction
   int sum_slot[16];                  // rv slot of the k-th value
-  int sdst[PBHC_NUM_OBS_SRC][8];     // smem row offset of source k in each obs group [0..3] / the push staging [4] (-1: none)
+  int sdst[PBHC_NUM_OBS_SRC][8];     // {count, smem row offsets of source k in the obs groups that show it and in the push staging}
   float obs_scale[PBHC_NUM_OBS_SRC];
   int hist_head_w[PBHC_MAX_HIST_KEYS];
 };
@@ -245,6 +245,15 @@ __device__ void build_tables(const TrackParams& P, BlockTables& T, int* hmap, in
     }
     T.sum_div[tid] = div; T.sum_slot[tid] = slot;
   }
+#if F_PUT
+  if (tid < PBHC_NUM_OBS_SRC) {  // {count, valid destinations...} of source tid
+    int cnt = 0;
+    for (int g = 0; g < c.n_groups; ++g) if (c.src_dst[tid][g] >= 0) T.sdst[tid][++cnt] = P.row_off[g] + c.src_dst[tid][g];
+    for (int h = 0; h < c.n_hist_keys; ++h) if (c.hist_src[h] == tid) { T.sdst[tid][++cnt] = P.row_off[c.n_groups] + P.push_off[h]; break; }
+    T.sdst[tid][0] = cnt;
+    for (int i = cnt + 1; i < 8; ++i) T.sdst[tid][i] = P.dump;
+  }
+#else
   for (int i = tid; i < PBHC_NUM_OBS_SRC * 8; i += nt) {
     const int k = i >> 3, g = i & 7;
     int off = P.dump;  // absent destination: the scratch region
@@ -252,6 +261,7 @@ __device__ void build_tables(const TrackParams& P, BlockTables& T, int* hmap, in
     else if (g == PBHC_MAX_OBS_GROUPS) for (int h = 0; h < c.n_hist_keys; ++h) if (c.hist_src[h] == k) off = P.row_off[c.n_groups] + P.push_off[h];
     T.sdst[k][g] = off;
   }
+#endif
   if (tid < PBHC_NUM_OBS_SRC) T.obs_scale[tid] = c.obs_scale[tid];
   // history ring: physical slot of logical slot s of key k is (head_k + s) % len_k, head_k = -push_count mod len_k
   // (HistoryHandler keeps newest-first order, history_handler.py:40-48).  hmap[d][i]: smem destination of physical
@@ -288,8 +298,37 @@ __device__ void build_tables(const TrackParams& P, BlockTables& T, int* hmap, in
   __syncthreads();
 }
 
-// writes `v` of element `e` of one observation source into every row that shows it (sd = T.sdst[source]); absent
-// destinations point at the per-warp scratch region, so the stores are unconditional
+// Two measured alternatives are kept behind macros (B200, 65536 envs, track kernel alone): the kernel is bound by
+// instruction issue, not by LSU wavefronts, so the variants with fewer instructions win even though they make more
+// shared-memory wavefronts.  F_PUT=1: only valid destinations are stored (predicated)            -> 0.356 ms vs 0.345 ms
+//                            F_HIST=1: scalar conflict-free history scatter instead of 128-bit loads -> 0.358 ms vs 0.345 ms
+#ifndef F_PUT
+#define F_PUT 0
+#endif
+#ifndef F_HIST
+#define F_HIST 0
+#endif
+#if F_PUT
+// writes `v` of element `e` of one observation source into every row that shows it.  sd = T.sdst[source] =
+// {count, dst0, dst1, ...}: only the valid destinations (count is the same for every lane and env: uniform branches)
+__device__ __forceinline__ void put1(const int* sd, float* rows, int e, float v) {
+  const int4 d = *reinterpret_cast<const int4*>(sd);
+  float* r = rows + e;
+  if (d.x > 0) r[d.y] = v;
+  if (d.x > 1) r[d.z] = v;
+  if (d.x > 2) r[d.w] = v;
+  if (d.x > 3) { r[sd[4]] = v; if (d.x > 4) r[sd[5]] = v; }
+}
+__device__ __forceinline__ void put3(const int* sd, float* rows, int e, float x, float y, float z) {
+  const int4 d = *reinterpret_cast<const int4*>(sd);
+  float* r = rows + e;
+  if (d.x > 0) { r[d.y] = x; r[d.y + 1] = y; r[d.y + 2] = z; }
+  if (d.x > 1) { r[d.z] = x; r[d.z + 1] = y; r[d.z + 2] = z; }
+  if (d.x > 2) { r[d.w] = x; r[d.w + 1] = y; r[d.w + 2] = z; }
+  for (int i = 3; i < d.x; ++i) { const int o = sd[i + 1]; r[o] = x; r[o + 1] = y; r[o + 2] = z; }
+}
+
+#else
 __device__ __forceinline__ void put1(const int* sd, float* rows, int e, float v) {
   const int4 d = *reinterpret_cast<const int4*>(sd);
   const int push = sd[4];
@@ -307,6 +346,7 @@ __device__ __forceinline__ void put3(const int* sd, float* rows, int e, float x,
   r[push] = x; r[push + 1] = y; r[push + 2] = z;
 }
 
+#endif
 // global -> shared copy of `count` floats with the widest vector the row alignment allows (vec = 4, 2 or 1)
 __device__ __forceinline__ void warp_load(float* dst, const float* src, int count, int vec, int lane) {
   if (vec == 4) {
@@ -354,12 +394,31 @@ __device__ __forceinline__ void warp_store_clipped(float* dst, const float* src,
 __device__ __forceinline__ void hist_scatter(const float* gh, float* rows, const int* hmap, const PbhcTrackCfg& c, int n_dst,
                                              int any_mul, int vec, int lane, bool zero) {
   const int H = c.hist_row;
+#if F_HIST
+  (void)vec;  // consecutive lanes take consecutive elements: coalesced loads, conflict-free shared stores
+  const int2* m2 = reinterpret_cast<const int2*>(hmap);
+  if (!any_mul) {
+#pragma unroll 4
+    for (int i = lane; i < H; i += 32) {
+      const float v = zero ? 0.0f : gh[i];
+      const int2 m = m2[i];  // absent destinations point at the scratch region
+      rows[m.x] = v; rows[m.y] = v;
+    }
+  } else {
+    for (int i = lane; i < H; i += 32) {
+      const float v = zero ? 0.0f : gh[i];
+      const int2 m = m2[i];
+      rows[m.x & 0xffffff] = v * c.hist_dst[m.x >> 24].mul;
+      rows[m.y & 0xffffff] = v * c.hist_dst[m.y >> 24].mul;
+    }
+  }
+#else
   if (!any_mul && vec == 4) {
     const float4* g4 = reinterpret_cast<const float4*>(gh);
     const int4* m4 = reinterpret_cast<const int4*>(hmap);
     for (int i = lane; i < (H >> 2); i += 32) {
       const float4 v = zero ? make_float4(0.f, 0.f, 0.f, 0.f) : g4[i];
-      const int4 a = m4[2 * i], b = m4[2 * i + 1];  // {m0,m1} of elements 4i, 4i+1 | 4i+2, 4i+3 (absent -> scratch)
+      const int4 a = m4[2 * i], b = m4[2 * i + 1];
       rows[a.x] = v.x; rows[a.y] = v.x; rows[a.z] = v.y; rows[a.w] = v.y;
       rows[b.x] = v.z; rows[b.y] = v.z; rows[b.z] = v.w; rows[b.w] = v.w;
     }
@@ -367,10 +426,11 @@ __device__ __forceinline__ void hist_scatter(const float* gh, float* rows, const
     for (int i = lane; i < H; i += 32) {
       const float v = zero ? 0.0f : gh[i];
       const int m0 = hmap[2 * i], m1 = hmap[2 * i + 1];
-      if (m0 >= 0) rows[m0 & 0xffffff] = any_mul ? v * c.hist_dst[m0 >> 24].mul : v;
-      if (m1 >= 0) rows[m1 & 0xffffff] = any_mul ? v * c.hist_dst[m1 >> 24].mul : v;
+      rows[m0 & 0xffffff] = any_mul ? v * c.hist_dst[m0 >> 24].mul : v;
+      rows[m1 & 0xffffff] = any_mul ? v * c.hist_dst[m1 >> 24].mul : v;
     }
   }
+#endif
   for (int d = 2; d < n_dst; ++d)
     for (int i = lane; i < H; i += 32) {
       const int m = hmap[d * H + i];
@@ -456,14 +516,14 @@ __global__ void __launch_bounds__(kTW * 32, 3) track_kernel(const __grid_constan
       const int64_t n = n32;  // sign-extended 32-bit: every n * row_size below is one IMAD.WIDE
       __syncwarp();
       // ---- A. per-env scalars + staging of the simulator state --------------------------------------------
-      int64_t ep = io.episode_length_buf[n] + 1;
-      const int64_t last_ep = ep;
-      float* envf = io.env_f32 + n * PBHC_ENVF_STRIDE;
-      const float4 ef0 = reinterpret_cast<const float4*>(envf)[0];  // start, motion_len, air_time[2]
-      const float4 ef1 = reinterpret_cast<const float4*>(envf)[1];  // last_contacts[2], end_time_ratio, pad
-      float start = ef0.x, mlen = ef0.y, etr = ef1.z;
       warp_load(sm_body, io.body_state + n * io.body_env_stride, Jb * 13, body_vec, lane);
       warp_load(sm_cf, io.contact_forces + n * (Jb * 3), Jb * 3, cf_vec, lane);
+      if (lane == 0) {  // per-env scalars: loaded with the first wave of loads, parked in shared memory until phases D-G
+        const float4* ge = reinterpret_cast<const float4*>(io.env_f32 + n * PBHC_ENVF_STRIDE);
+        *reinterpret_cast<float4*>(rv + V_ENVF) = ge[0];
+        *reinterpret_cast<float4*>(rv + V_ENVF + 4) = ge[1];
+        *reinterpret_cast<long long*>(rv + V_EP) = io.episode_length_buf[n];
+      }
       const int clip = __float_as_int(pre[(P_CLIP) * kChunk + e]);
       const float b = pre[(P_BLEND) * kChunk + e], omb = 1.0f - b;
       const float* r0 = tab.records + (int64_t)__float_as_int(pre[(P_F0) * kChunk + e]) * tab.rec_stride;
@@ -575,6 +635,25 @@ __global__ void __launch_bounds__(kTW * 32, 3) track_kernel(const __grid_constan
         l_tq = c.cur_torque.enable ? fminf(fmaxf(fabsf(tq) - lim_t, 0.0f), 1.0f) : fmaxf(fabsf(tq) - lim_t, 0.0f);
       }
       l_pos = warp_sum(l_pos); l_vel = warp_sum(l_vel); l_tq = warp_sum(l_tq);
+      // dof-wise observation features and the last_* state are written now (values of an env that does not reset) so
+      // that nothing of this phase stays live across the next ones; the rare reset branch overwrites them
+      auto emit_dof = [&](float p_, float v_, float a_, float kp_, float kd_, float def_) {
+        put1(T.sdst[S_DOF_POS], rows, lane, (p_ - def_) * T.obs_scale[S_DOF_POS]);
+        put1(T.sdst[S_DOF_VEL], rows, lane, v_ * T.obs_scale[S_DOF_VEL]);
+        put1(T.sdst[S_ACTIONS], rows, lane, a_ * T.obs_scale[S_ACTIONS]);
+        put1(T.sdst[S_DR_KP], rows, lane, kp_ * T.obs_scale[S_DR_KP]);
+        put1(T.sdst[S_DR_KD], rows, lane, kd_ * T.obs_scale[S_DR_KD]);
+        io.last_actions[n * D + lane] = a_;   // _post_compute_observations_callback, legged_robot_base.py:398-405
+        io.last_dof_pos[n * D + lane] = p_;
+        io.last_dof_vel[n * D + lane] = v_;
+      };
+      if (ld) {
+        emit_dof(dpos, dvel, act, kp, kd, ddef);
+        if (c.src_used_mask & ((1u << S_DIF_JOINT) | (1u << S_DIF_JOINT_VEL))) {
+          put1(T.sdst[S_DIF_JOINT], rows, lane, dja * T.obs_scale[S_DIF_JOINT]);
+          put1(T.sdst[S_DIF_JOINT_VEL], rows, lane, djv * T.obs_scale[S_DIF_JOINT_VEL]);
+        }
+      }
       {
         const float tot = warp_sum16(sums, lane);
         const int idx = (lane >> 1) & 15;
@@ -582,6 +661,14 @@ __global__ void __launch_bounds__(kTW * 32, 3) track_kernel(const __grid_constan
         if (idx == U_DJA2) rv[V_JOINT_N] = sqrtf(tot);
       }
       // ---- D. feet (lane = foot): contacts, feet_air_time, contact-force / slip terms -----------------------------
+      // (the per-env scalars were parked in shared memory at the top of the iteration: nothing of them stays in registers
+      // across the body / dof phases)
+      int64_t ep = *reinterpret_cast<const long long*>(rv + V_EP) + 1;
+      const int64_t last_ep = ep;
+      float* envf = io.env_f32 + n * PBHC_ENVF_STRIDE;
+      const float4 ef0 = *reinterpret_cast<const float4*>(rv + V_ENVF);      // start, motion_len, air_time[2]
+      const float4 ef1 = *reinterpret_cast<const float4*>(rv + V_ENVF + 4);  // last_contacts[2], end_time_ratio, pad
+      float start = ef0.x, mlen = ef0.y, etr = ef1.z;
       float x_air = 0.f, x_force = 0.f, x_slip = 0.f, x_fslip = 0.f, x_cm = 0.f, contact_f = 0.f, air_f = 0.f;
       bool x_stumble = false;
       if (lane < c.n_feet) {
@@ -666,7 +753,6 @@ __global__ void __launch_bounds__(kTW * 32, 3) track_kernel(const __grid_constan
       float air0 = air_f, contact0 = contact_f;  // meaningful in lane 0
       if (reset) {
         const Rng rng = {make_uint2((uint32_t)c.seed, (uint32_t)(c.seed >> 32)), (uint32_t)n, (uint32_t)(n >> 32), push_count};
-        act = 0.0f;
         if (ld) io.actions[n * D + lane] = 0.0f;
         air0 = 0.0f; air1 = 0.0f; contact0 = 0.0f; contact1 = 0.0f;
         if (c.hist_row > 0) {  // HistoryHandler.reset: zero the ring (and what the observation rows already took from it)
@@ -674,11 +760,13 @@ __global__ void __launch_bounds__(kTW * 32, 3) track_kernel(const __grid_constan
           hist_scatter(io.hist + n * c.hist_row, rows, hmap, c, P.n_hdst_max, P.hist_any_mul, hist_vec, lane, true);
         }
         ep = 0;
+        float kp2 = 1.f, kd2 = 1.f, dpos2 = 0.f, dvel2 = 0.f;  // (nothing of the dof phase is kept live for this rare branch)
         if (ld) {  // _episodic_domain_randomization
+          kp2 = io.kp_scale[n * D + lane]; kd2 = io.kd_scale[n * D + lane];
           if (c.randomize_pd_gain) {
-            kp = io.inject_kp ? io.inject_kp[n * D + lane] : (c.kp_hi - c.kp_lo) * rng.uniform(16 + lane) + c.kp_lo;
-            kd = io.inject_kd ? io.inject_kd[n * D + lane] : (c.kd_hi - c.kd_lo) * rng.uniform(48 + lane) + c.kd_lo;
-            io.kp_scale[n * D + lane] = kp; io.kd_scale[n * D + lane] = kd;
+            kp2 = io.inject_kp ? io.inject_kp[n * D + lane] : (c.kp_hi - c.kp_lo) * rng.uniform(16 + lane) + c.kp_lo;
+            kd2 = io.inject_kd ? io.inject_kd[n * D + lane] : (c.kd_hi - c.kd_lo) * rng.uniform(48 + lane) + c.kd_lo;
+            io.kp_scale[n * D + lane] = kp2; io.kd_scale[n * D + lane] = kd2;
           }
           if (c.randomize_rfi_lim)
             io.rfi_lim_scale[n * D + lane] = io.inject_rfi ? io.inject_rfi[n * D + lane] : (c.rfi_hi - c.rfi_lo) * rng.uniform(80 + lane) + c.rfi_lo;
@@ -698,11 +786,11 @@ __global__ void __launch_bounds__(kTW * 32, 3) track_kernel(const __grid_constan
         const float* q0 = tab.records + f2.f0 * tab.rec_stride;
         const float* q1 = tab.records + f2.f1 * tab.rec_stride;
         if (ld) {
-          dpos = omb2 * q0[e_dp + lane] + b2 * q1[e_dp + lane];
-          dvel = omb2 * q0[e_dv + lane] + b2 * q1[e_dv + lane];
-          if (c.reset_noise[0] != 0.0f) dpos = dpos + rng.normal(144 + lane) * c.reset_noise[0];
-          if (c.reset_noise[1] != 0.0f) dvel = dvel + rng.normal(176 + lane) * c.reset_noise[1];
-          reinterpret_cast<float2*>(io.dof_state)[n * D + lane] = make_float2(dpos, dvel);
+          dpos2 = omb2 * q0[e_dp + lane] + b2 * q1[e_dp + lane];
+          dvel2 = omb2 * q0[e_dv + lane] + b2 * q1[e_dv + lane];
+          if (c.reset_noise[0] != 0.0f) dpos2 = dpos2 + rng.normal(144 + lane) * c.reset_noise[0];
+          if (c.reset_noise[1] != 0.0f) dvel2 = dvel2 + rng.normal(176 + lane) * c.reset_noise[1];
+          reinterpret_cast<float2*>(io.dof_state)[n * D + lane] = make_float2(dpos2, dvel2);
         }
         if (lane < 13) {
           float v;
@@ -728,6 +816,7 @@ __global__ void __launch_bounds__(kTW * 32, 3) track_kernel(const __grid_constan
           }
           io.root_state[n * 13 + lane] = v;
         }
+        if (ld) emit_dof(dpos2, dvel2, 0.0f, kp2, kd2, io.default_dof_pos[n * io.default_dof_stride + lane]);
       }
       // ---- H. observation features into the rows (legged_robot_base.py:763-793, 1114-1215; motion_tracking.py:944-1015)
       if (lane < 16) {
@@ -741,17 +830,6 @@ __global__ void __launch_bounds__(kTW * 32, 3) track_kernel(const __grid_constan
         else { k = S_BASE_POS_Z; val = rp.z; }
         put1(T.sdst[k], rows, ce, val * T.obs_scale[k]);
       }
-      if (ld) {
-        put1(T.sdst[S_DOF_POS], rows, lane, (dpos - ddef) * T.obs_scale[S_DOF_POS]);
-        put1(T.sdst[S_DOF_VEL], rows, lane, dvel * T.obs_scale[S_DOF_VEL]);
-        put1(T.sdst[S_ACTIONS], rows, lane, act * T.obs_scale[S_ACTIONS]);
-        put1(T.sdst[S_DR_KP], rows, lane, kp * T.obs_scale[S_DR_KP]);
-        put1(T.sdst[S_DR_KD], rows, lane, kd * T.obs_scale[S_DR_KD]);
-        if (c.src_used_mask & ((1u << S_DIF_JOINT) | (1u << S_DIF_JOINT_VEL))) {
-          put1(T.sdst[S_DIF_JOINT], rows, lane, dja * T.obs_scale[S_DIF_JOINT]);
-          put1(T.sdst[S_DIF_JOINT_VEL], rows, lane, djv * T.obs_scale[S_DIF_JOINT_VEL]);
-        }
-      }
       for (int i = lane; i < L; i += 32) put1(T.sdst[S_DR_MASS], rows, i, io.link_mass_scale[n * L + i] * T.obs_scale[S_DR_MASS]);
       if (lane == 0) { rv[V_ETR] = etr; }
       __syncwarp();
@@ -764,11 +842,6 @@ __global__ void __launch_bounds__(kTW * 32, 3) track_kernel(const __grid_constan
         float* gh = io.hist + n * c.hist_row;
         const float* ps = rows + P.row_off[c.n_groups];
         for (int i = lane; i < P.push_len; i += 32) gh[pmap[i]] = ps[i];
-      }
-      if (ld) {  // _post_compute_observations_callback, legged_robot_base.py:398-405
-        io.last_actions[n * D + lane] = act;
-        io.last_dof_pos[n * D + lane] = dpos;
-        io.last_dof_vel[n * D + lane] = dvel;
       }
       if (lane == 0) {
         reinterpret_cast<float4*>(envf)[0] = make_float4(start, mlen, air0, c.n_feet > 1 ? air1 : 0.0f);
