@@ -357,45 +357,40 @@ def ncu_traffic():
 
 
 def e2e_pass(torch, dist, wl, K, with_fk, world, dev):
-    """The same step through the public API with HOST buffers: every step copies the simulator state and actions from
-    pinned host memory to the device, runs the step, and reads observations / rewards / reset flags back to pinned
-    host memory."""
-    ts, h = wl.ts, wl.host
+    """The same step through the public host-buffer API (pbhc_b200.tracking_step.HostStep): every step copies the
+    simulator state and actions from pinned host memory to the device, runs the step, and reads observations /
+    rewards / reset flags back to pinned host memory (chunked so that copies and kernels overlap)."""
+    from pbhc_b200.tracking_step import HostStep
+    h = wl.host
     pin = lambda t: t.contiguous().pin_memory()
-    src = [(pin(h["body_state"].reshape(-1, 13)), wl.sim._rigid_body_state), (pin(h["root_state"]), wl.sim.all_root_states),
-           (pin(h["dof_state"].reshape(-1, 2)), wl.sim.dof_state), (pin(h["contact_forces"]), wl.sim.contact_forces),
-           (pin(h["actions"]), wl.actions), (pin(h["torques"]), wl.torques)]
+    host_in = {k: pin(h[k]) for k in ("body_state", "root_state", "dof_state", "contact_forces", "actions", "torques")}
+    extra = None
     if with_fk:
-        src += [(pin(h["pose_aa"]), wl.pose_aa), (pin(h["trans"]), wl.trans)]
-    outs = list(ts.obs_buf_dict.values()) + [ts.rew_buf, ts.reset_buf, ts.time_out_buf]
-    dst = [(o, torch.empty(o.shape, dtype=o.dtype).pin_memory()) for o in outs]
-    h2d = sum(s.numel() * s.element_size() for s, _ in src)
-    d2h = sum(o.numel() * o.element_size() for o, _ in dst)
+        wl.fk()
+        pos, mat, quat = wl.fk_out
+        hb = wl.lib.mesh_parsers
 
-    def one():
-        for s, d in src:
-            d.copy_(s, non_blocking=True)
-        wl.step(with_fk)
-        for o, hbuf in dst:
-            hbuf.copy_(o, non_blocking=True)
-        torch.cuda.synchronize()  # the caller owns the results on the host before the next step starts
-
+        def fk_range(lo, hi):
+            hb.fk(wl.pose_aa[lo:hi], wl.trans[lo:hi], out=(pos[lo:hi], mat[lo:hi], quat[lo:hi]))
+        extra = (fk_range, [(pin(h["pose_aa"]), wl.pose_aa), (pin(h["trans"]), wl.trans)])
+    hs = HostStep(wl.ts, wl.sim, wl.actions, wl.torques, wl.env_origins, wl.motion_ids, host_in, extra=extra, chunks=8)
     for _ in range(3):
-        one()
+        hs.step()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize()
     e0.record()
     for _ in range(K):
-        one()
+        hs.step()
     e1.record()
     torch.cuda.synchronize()
     ms = torch.tensor([e0.elapsed_time(e1)], device=dev, dtype=torch.float64)
     if world > 1:
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-    return {"value": wl.N * world * K / (float(ms.item()) * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d * world,
-            "d2h_bytes_per_step": d2h * world, "steps": K, "ms_per_step": float(ms.item()) / K}
+    return {"value": wl.N * world * K / (float(ms.item()) * 1e-3), "unit": UNIT, "h2d_bytes_per_step": hs.h2d_bytes * world,
+            "d2h_bytes_per_step": hs.d2h_bytes * world, "steps": K, "ms_per_step": float(ms.item()) / K,
+            "api": "pbhc_b200.tracking_step.HostStep (8 env chunks pipelined over 3 streams)"}
 
 
 def main():

@@ -14,7 +14,7 @@
 extern "C" {
 #endif
 
-#define PBHC_ABI_VERSION 2
+#define PBHC_ABI_VERSION 3
 #define PBHC_OK 0
 #define PBHC_E_BADARG (-1)
 #define PBHC_E_ALIGN (-2)
@@ -274,6 +274,7 @@ typedef struct {
   /* values the reference draws with torch RNG at resets; NULL = in-kernel Philox */
   const float* inject_start_times; const float* inject_kp; const float* inject_kd; const float* inject_rfi;
   const float* inject_rao; const int64_t* inject_delay;
+  int64_t env_offset;           /* global id of env 0 of this call (keys the in-kernel RNG when a step is launched in chunks) */
 } PbhcTrackIO;
 
 /* number of rows `partials` must have */

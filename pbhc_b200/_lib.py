@@ -9,7 +9,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("PBHC_B200_LIB") or os.path.join(_HERE, "libpbhc_b200.so")  # override: development A/B builds
 
 c_f32p = C.c_void_p
-ABI_VERSION = 2
+ABI_VERSION = 3
 MAX_JOINTS = 40
 
 
@@ -166,7 +166,8 @@ class TrackIO(C.Structure):
                 + [("obs", C.c_void_p * MAX_OBS_GROUPS)]
                 + [(k, C.c_void_p) for k in ("rew_buf", "reset_buf", "time_out_buf", "ref_body_pos_extend", "ref_body_rot_extend",
                                              "last_episode_sums", "partials", "acc", "inject_start_times", "inject_kp",
-                                             "inject_kd", "inject_rfi", "inject_rao", "inject_delay")])
+                                             "inject_kd", "inject_rfi", "inject_rao", "inject_delay")]
+                + [("env_offset", C.c_int64)])
 
 
 def bind_track(L):

@@ -752,7 +752,7 @@ __global__ void __launch_bounds__(kTW * 32, 3) track_kernel(const __grid_constan
       int64_t delay = io.action_delay_idx[n];
       float air0 = air_f, contact0 = contact_f;  // meaningful in lane 0
       if (reset) {
-        const Rng rng = {make_uint2((uint32_t)c.seed, (uint32_t)(c.seed >> 32)), (uint32_t)n, (uint32_t)(n >> 32), push_count};
+        const Rng rng = {make_uint2((uint32_t)c.seed, (uint32_t)(c.seed >> 32)), (uint32_t)(n + io.env_offset), (uint32_t)((uint64_t)(n + io.env_offset) >> 32), push_count};
         if (ld) io.actions[n * D + lane] = 0.0f;
         air0 = 0.0f; air1 = 0.0f; contact0 = 0.0f; contact1 = 0.0f;
         if (c.hist_row > 0) {  // HistoryHandler.reset: zero the ring (and what the observation rows already took from it)

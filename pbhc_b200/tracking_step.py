@@ -283,3 +283,101 @@ class TrackingStep:
         self.extras = {"time_outs": self.time_out_buf, "ref_body_pos_extend": self.ref_body_pos_extend,
                        "ref_body_rot_extend": self.ref_body_rot_extend, "to_log": None}
         return self.obs_buf_dict, self.rew_buf, self.reset_buf, self.extras
+
+    # ---- chunked launches and the host-buffer pipeline --------------------------------------------------------
+    def _row_bytes(self):
+        """bytes per env of every per-env pointer of PbhcTrackIO (what a launch on envs [lo, hi) offsets)."""
+        s, io = self.spec, self._io
+        D, J, Jb, L = s.D, s.J, s.Jb, s.L
+        rew = (len(s.reward_names) + 1) * 4 if s.use_vec_reward else 4
+        rb = dict(body_state=io.body_env_stride * 4, root_state=52, dof_state=D * 8, contact_forces=Jb * 12, actions=D * 4, torques=D * 4,
+                  env_origins=12, motion_ids=8, default_dof_pos=io.default_dof_stride * 4, base_com_bias=12, link_mass_scale=L * 4,
+                  friction=4, episode_length_buf=8, env_f32=_lib.ENVF_STRIDE * 4, last_actions=D * 4, last_dof_pos=D * 4,
+                  last_dof_vel=D * 4, kp_scale=D * 4, kd_scale=D * 4, rfi_lim_scale=D * 4, rao_scale=D * 4, action_delay_idx=8,
+                  hist=self.hist_row * 4, episode_sums=self.n_sums * 4, rew_buf=rew, reset_buf=8, time_out_buf=1,
+                  ref_body_pos_extend=J * 12, ref_body_rot_extend=J * 16, last_episode_sums=self.n_sums * 4,
+                  inject_start_times=4, inject_kp=D * 4, inject_kd=D * 4, inject_rfi=D * 4, inject_rao=D * 4, inject_delay=8)
+        return rb
+
+    def launch_range(self, lo, hi, acc):
+        """pbhc_track_step on envs [lo, hi) of the last bind(), per-step sums into `acc` (a [PBHC_ACC] fp64 tensor).
+        Used to pipeline a step in chunks; sum the chunk `acc`s into self.acc before finalize()."""
+        io = _lib.TrackIO.from_buffer_copy(self._io)
+        for name, nbytes in self._row_bytes().items():
+            v = getattr(io, name)
+            if v:
+                setattr(io, name, v + lo * nbytes)
+        for g, name in enumerate(self.spec.obs_groups):
+            io.obs[g] = self._io.obs[g] + lo * self.obs_buf_dict[name].shape[1] * 4
+        io.acc, io.env_offset = _lib.ptr(acc, torch.float64), self._io.env_offset + lo
+        _lib.check(self._L.pbhc_track_step(C.byref(self._cfg), C.byref(self.lib._desc), C.byref(io), hi - lo,
+                                           _lib.stream_ptr(self.device)))
+
+
+class HostStep:
+    """The step for callers whose simulator state lives in HOST memory (pinned): `step()` copies the inputs of this step
+    to the device, runs the fused step and copies observations / rewards / reset flags back, pipelined over `chunks`
+    ranges of envs on three streams so that the host->device copy of chunk k+1, the kernels of chunk k and the
+    device->host copy of chunk k-1 overlap (PCIe is full duplex).  Returns when the results are on the host."""
+
+    def __init__(self, tracking_step, sim, actions, torques, env_origins, motion_ids, host_in, extra=None, chunks=8):
+        """host_in: dict name -> pinned CPU tensor for body_state / root_state / dof_state / contact_forces / actions /
+        torques, shaped like the device tensors; extra: optional (fn(lo, hi), [(host, device), ...]) run per chunk before
+        the tracking kernel (the benchmark uses it for K2 on the same envs)."""
+        ts = self.ts = tracking_step
+        self.N, self.dev = ts.N, ts.device
+        ts.bind(sim, actions, torques, env_origins, motion_ids)
+        self.pairs = [(host_in["body_state"], sim._rigid_body_state.view(self.N, -1)), (host_in["root_state"], sim.all_root_states),
+                      (host_in["dof_state"], sim.dof_state.view(self.N, -1)), (host_in["contact_forces"], sim.contact_forces.view(self.N, -1)),
+                      (host_in["actions"], actions), (host_in["torques"], torques)]
+        self.pairs = [(h.view(self.N, -1), d) for h, d in self.pairs]
+        self.extra_fn = None
+        if extra is not None:
+            self.extra_fn = extra[0]
+            self.pairs += [(h.view(self.N, -1), d.view(self.N, -1)) for h, d in extra[1]]
+        outs = list(ts.obs_buf_dict.values()) + [ts.rew_buf.view(self.N, -1), ts.reset_buf.view(self.N, 1), ts.time_out_buf.view(self.N, 1)]
+        self.outs = [(o, torch.empty(o.shape, dtype=o.dtype).pin_memory()) for o in outs]
+        for h, _ in self.pairs:
+            if not h.is_pinned():
+                raise _lib.PbhcError("HostStep needs pinned host tensors")
+        c = max(1, min(int(chunks), self.N // 4 or 1))
+        step = -(-self.N // c)
+        step = (step + 3) // 4 * 4  # chunk starts on multiples of 4 envs keep every row 16-byte aligned
+        self.ranges = [(lo, min(lo + step, self.N)) for lo in range(0, self.N, step)]
+        self.s_in, self.s_k, self.s_out = (torch.cuda.Stream(self.dev) for _ in range(3))
+        self.acc = torch.zeros(len(self.ranges), _lib.ACC, device=self.dev, dtype=torch.float64)
+        self.h2d_bytes = sum(h.numel() * h.element_size() for h, _ in self.pairs)
+        self.d2h_bytes = sum(o.numel() * o.element_size() for o, _ in self.outs)
+
+    @property
+    def host_out(self):
+        names = list(self.ts.obs_buf_dict.keys()) + ["rew_buf", "reset_buf", "time_out_buf"]
+        return {n: h for n, (_, h) in zip(names, self.outs)}
+
+    def step(self):
+        ts = self.ts
+        cur = torch.cuda.current_stream(self.dev)
+        for s in (self.s_in, self.s_k, self.s_out):
+            s.wait_stream(cur)
+        for k, (lo, hi) in enumerate(self.ranges):
+            with torch.cuda.stream(self.s_in):
+                for h, d in self.pairs:
+                    d[lo:hi].copy_(h[lo:hi], non_blocking=True)
+                ev_in = self.s_in.record_event()
+            with torch.cuda.stream(self.s_k):
+                self.s_k.wait_event(ev_in)
+                if self.extra_fn is not None:
+                    self.extra_fn(lo, hi)
+                ts.launch_range(lo, hi, self.acc[k])
+                ev_k = self.s_k.record_event()
+            with torch.cuda.stream(self.s_out):
+                self.s_out.wait_event(ev_k)
+                for o, h in self.outs:
+                    h[lo:hi].copy_(o[lo:hi], non_blocking=True)
+        with torch.cuda.stream(self.s_k):
+            torch.sum(self.acc, dim=0, out=ts.acc)
+            ts.finalize()
+        cur.wait_stream(self.s_k)
+        cur.wait_stream(self.s_out)
+        cur.synchronize()  # the caller owns the results on the host when step() returns
+        return self.host_out

@@ -135,3 +135,34 @@ def test_workload_step_vs_oracle(n_envs, tmp_path):
     n_reset = check_workload_step_against_oracle(wl, n_steps=3)
     if n_envs >= 4096:
         assert n_reset > 0
+
+
+def test_host_step_chunked_pipeline_equals_single_launch(tmp_path):
+    """HostStep (host buffers, 5 ragged env chunks on 3 streams) gives bit-identical per-env results to one launch;
+    in-kernel reset draws are keyed by the global env id, so they do not depend on the chunking either."""
+    from pbhc_b200.workload import Workload
+    from pbhc_b200.tracking_step import HostStep
+    n = 1003
+    a = Workload(n, DEV, str(tmp_path / "a"), seed=7)
+    b = Workload(n, DEV, str(tmp_path / "b"), seed=7)
+    pin = lambda t: t.contiguous().pin_memory()
+    host_in = {k: pin(b.host[k]) for k in ("body_state", "root_state", "dof_state", "contact_forces", "actions", "torques")}
+    hs = HostStep(b.ts, b.sim, b.actions, b.torques, b.env_origins, b.motion_ids, host_in, chunks=5)
+    assert len(hs.ranges) >= 4 and hs.ranges[-1][1] == n
+    for step in range(3):
+        a.sim._rigid_body_state.copy_(a.host["body_state"].reshape(-1, 13))  # what the host step re-uploads every step
+        a.sim.all_root_states.copy_(a.host["root_state"])
+        a.sim.dof_state.copy_(a.host["dof_state"].reshape(-1, 2))
+        a.actions.copy_(a.host["actions"])
+        a.step(with_fk=False)
+        out = hs.step()
+        torch.cuda.synchronize()
+        for name, v in a.ts.obs_buf_dict.items():
+            assert torch.equal(v.cpu(), out[name]), (step, name)
+        assert torch.equal(a.ts.rew_buf.cpu().view(n, -1), out["rew_buf"])
+        assert torch.equal(a.ts.reset_buf.cpu().view(n, 1), out["reset_buf"])
+        assert torch.equal(a.ts.time_out_buf.cpu().view(n, 1), out["time_out_buf"])
+        assert torch.equal(a.ts.env_f32.cpu(), b.ts.env_f32.cpu())
+        assert torch.equal(a.ts.hist.cpu(), b.ts.hist.cpu())
+        assert torch.allclose(a.ts.scalars.cpu(), b.ts.scalars.cpu(), rtol=1e-12, atol=0)
+    assert int(a.ts.reset_buf.sum()) > 0
