@@ -157,7 +157,8 @@ struct BlockTables {
   float sum_div[16];                 // divisor applied to the k-th value of the 16-way reduction
   int sum_slot[16];                  // rv slot of the k-th value
   int sdst[PBHC_NUM_OBS_SRC][8];     // {count, smem row offsets of source k in the obs groups that show it and in the push staging}
-  float obs_scale[PBHC_NUM_OBS_SRC];
+  float obs_scale[PBHC_NUM_OBS_SRC], obs_noise[PBHC_NUM_OBS_SRC];
+  uint32_t noise_mask;               // bit k: source k carries observation noise
   int hist_head_w[PBHC_MAX_HIST_KEYS];
 };
 
@@ -262,7 +263,12 @@ __device__ void build_tables(const TrackParams& P, BlockTables& T, int* hmap, in
     T.sdst[k][g] = off;
   }
 #endif
-  if (tid < PBHC_NUM_OBS_SRC) T.obs_scale[tid] = c.obs_scale[tid];
+  if (tid < PBHC_NUM_OBS_SRC) { T.obs_scale[tid] = c.obs_scale[tid]; T.obs_noise[tid] = c.obs_noise[tid]; }
+  if (tid == 0) {
+    uint32_t m = 0;
+    for (int k = 0; k < PBHC_NUM_OBS_SRC; ++k) if (c.obs_noise[k] != 0.0f) m |= 1u << k;
+    T.noise_mask = m;
+  }
   // history ring: physical slot of logical slot s of key k is (head_k + s) % len_k, head_k = -push_count mod len_k
   // (HistoryHandler keeps newest-first order, history_handler.py:40-48).  hmap[d][i]: smem destination of physical
   // element i of the global history row in the d-th obs segment that shows it; pmap[i]: physical element that
@@ -347,6 +353,38 @@ __device__ __forceinline__ void put3(const int* sd, float* rows, int e, float x,
 }
 
 #endif
+// One element (three for emit3) of observation source k to every row that shows it: (value + U(-1,1)*noise) * scale with an
+// independent draw per destination, like parse_observation() does per obs group and for the history (helpers.py:128-152;
+// torch.rand_like there, Philox keyed by (seed, env, step, source, element) here).  Noise-free sources take the plain path.
+struct NoiseKey { uint64_t seed; int64_t env; uint32_t step; };
+__device__ __forceinline__ float noisy(float raw, uint32_t bits, float ns, float sc) { return (raw + (u01(bits) * 2.0f - 1.0f) * ns) * sc; }
+__device__ __noinline__ void emit_noisy(const BlockTables& T, float* rows, int k, int e, float raw, const NoiseKey& nk) {
+  const Rng rng = {make_uint2((uint32_t)nk.seed, (uint32_t)(nk.seed >> 32)), (uint32_t)nk.env, (uint32_t)((uint64_t)nk.env >> 32), nk.step};
+  const uint32_t st = 4096u + ((uint32_t)k * 256u + (uint32_t)e) * 2u;
+  const uint4 a = rng.draw(st);
+  const uint32_t b = rng.draw(st + 1u).x;
+  const float ns = T.obs_noise[k], sc = T.obs_scale[k];
+  const int* sd = T.sdst[k];
+  float* r = rows + e;
+#if F_PUT
+  const uint32_t bits[5] = {a.x, a.y, a.z, a.w, b};
+  for (int i = 0; i < sd[0]; ++i) r[sd[i + 1]] = noisy(raw, bits[i], ns, sc);
+#else
+  r[sd[0]] = noisy(raw, a.x, ns, sc); r[sd[1]] = noisy(raw, a.y, ns, sc); r[sd[2]] = noisy(raw, a.z, ns, sc);
+  r[sd[3]] = noisy(raw, a.w, ns, sc); r[sd[4]] = noisy(raw, b, ns, sc);
+#endif
+}
+template <bool kNoise>
+__device__ __forceinline__ void emit1(const BlockTables& T, float* rows, int k, int e, float raw, const NoiseKey& nk) {
+  if (kNoise && (T.noise_mask & (1u << k))) emit_noisy(T, rows, k, e, raw, nk);
+  else put1(T.sdst[k], rows, e, raw * T.obs_scale[k]);
+}
+template <bool kNoise>
+__device__ __forceinline__ void emit3(const BlockTables& T, float* rows, int k, int e, float x, float y, float z, const NoiseKey& nk) {
+  if (kNoise && (T.noise_mask & (1u << k))) { emit_noisy(T, rows, k, e, x, nk); emit_noisy(T, rows, k, e + 1, y, nk); emit_noisy(T, rows, k, e + 2, z, nk); }
+  else { const float sc = T.obs_scale[k]; put3(T.sdst[k], rows, e, x * sc, y * sc, z * sc); }
+}
+
 // global -> shared copy of `count` floats with the widest vector the row alignment allows (vec = 4, 2 or 1)
 __device__ __forceinline__ void warp_load(float* dst, const float* src, int count, int vec, int lane) {
   if (vec == 4) {
@@ -447,6 +485,7 @@ __host__ __device__ inline int vec_of(int64_t row_floats, const void* base) {
 
 __device__ __forceinline__ int up4(int v) { return (v + 3) & ~3; }
 
+template <bool kNoise>
 __global__ void __launch_bounds__(kTW * 32, 3) track_kernel(const __grid_constant__ TrackParams P) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   BlockTables& T = *reinterpret_cast<BlockTables*>(smem_raw);
@@ -514,6 +553,7 @@ __global__ void __launch_bounds__(kTW * 32, 3) track_kernel(const __grid_constan
       const int n32 = chunk + e * stride;
       if (n32 >= n_envs) break;
       const int64_t n = n32;  // sign-extended 32-bit: every n * row_size below is one IMAD.WIDE
+      const NoiseKey nk = {c.seed, n + io.env_offset, push_count};
       __syncwarp();
       // ---- A. per-env scalars + staging of the simulator state --------------------------------------------
       warp_load(sm_body, io.body_state + n * io.body_env_stride, Jb * 13, body_vec, lane);
@@ -594,16 +634,13 @@ __global__ void __launch_bounds__(kTW * 32, 3) track_kernel(const __grid_constan
             collide = norm3(fc[0], fc[1], fc[2]) > 0.1f;
           }
           const V3 dl = quat_rotate_z(hz, hw, dp);  // motion_tracking.py:694-697
-          const float sc0 = T.obs_scale[S_DIF_LOCAL];
-          put3(T.sdst[S_DIF_LOCAL], rows, 3 * j, dl.x * sc0, dl.y * sc0, dl.z * sc0);
+          emit3<kNoise>(T, rows, S_DIF_LOCAL, 3 * j, dl.x, dl.y, dl.z, nk);
           const V3 lr = quat_rotate_z(hz, hw, {rpz[0] - rp.x, rpz[1] - rp.y, rpz[2] - rp.z});  // :705-707
-          const float sc1 = T.obs_scale[S_LOCAL_REF];
-          put3(T.sdst[S_LOCAL_REF], rows, 3 * j, lr.x * sc1, lr.y * sc1, lr.z * sc1);
+          emit3<kNoise>(T, rows, S_LOCAL_REF, 3 * j, lr.x, lr.y, lr.z, nk);
           if (c.src_used_mask & ((1u << S_LOCAL_REF_VEL) | (1u << S_GLOBAL_REF_VEL))) {
             const V3 lv = quat_rotate_z(hz, hw, {rvv[0], rvv[1], rvv[2]});
-            const float sc2 = T.obs_scale[S_LOCAL_REF_VEL], sc3 = T.obs_scale[S_GLOBAL_REF_VEL];
-            put3(T.sdst[S_LOCAL_REF_VEL], rows, 3 * j, lv.x * sc2, lv.y * sc2, lv.z * sc2);
-            put3(T.sdst[S_GLOBAL_REF_VEL], rows, 3 * j, rvv[0] * sc3, rvv[1] * sc3, rvv[2] * sc3);
+            emit3<kNoise>(T, rows, S_LOCAL_REF_VEL, 3 * j, lv.x, lv.y, lv.z, nk);
+            emit3<kNoise>(T, rows, S_GLOBAL_REF_VEL, 3 * j, rvv[0], rvv[1], rvv[2], nk);
           }
         }
         n_collide += __popc(__ballot_sync(0xffffffffu, collide));
@@ -638,11 +675,11 @@ __global__ void __launch_bounds__(kTW * 32, 3) track_kernel(const __grid_constan
       // dof-wise observation features and the last_* state are written now (values of an env that does not reset) so
       // that nothing of this phase stays live across the next ones; the rare reset branch overwrites them
       auto emit_dof = [&](float p_, float v_, float a_, float kp_, float kd_, float def_) {
-        put1(T.sdst[S_DOF_POS], rows, lane, (p_ - def_) * T.obs_scale[S_DOF_POS]);
-        put1(T.sdst[S_DOF_VEL], rows, lane, v_ * T.obs_scale[S_DOF_VEL]);
-        put1(T.sdst[S_ACTIONS], rows, lane, a_ * T.obs_scale[S_ACTIONS]);
-        put1(T.sdst[S_DR_KP], rows, lane, kp_ * T.obs_scale[S_DR_KP]);
-        put1(T.sdst[S_DR_KD], rows, lane, kd_ * T.obs_scale[S_DR_KD]);
+        emit1<kNoise>(T, rows, S_DOF_POS, lane, p_ - def_, nk);
+        emit1<kNoise>(T, rows, S_DOF_VEL, lane, v_, nk);
+        emit1<kNoise>(T, rows, S_ACTIONS, lane, a_, nk);
+        emit1<kNoise>(T, rows, S_DR_KP, lane, kp_, nk);
+        emit1<kNoise>(T, rows, S_DR_KD, lane, kd_, nk);
         io.last_actions[n * D + lane] = a_;   // _post_compute_observations_callback, legged_robot_base.py:398-405
         io.last_dof_pos[n * D + lane] = p_;
         io.last_dof_vel[n * D + lane] = v_;
@@ -650,8 +687,8 @@ __global__ void __launch_bounds__(kTW * 32, 3) track_kernel(const __grid_constan
       if (ld) {
         emit_dof(dpos, dvel, act, kp, kd, ddef);
         if (c.src_used_mask & ((1u << S_DIF_JOINT) | (1u << S_DIF_JOINT_VEL))) {
-          put1(T.sdst[S_DIF_JOINT], rows, lane, dja * T.obs_scale[S_DIF_JOINT]);
-          put1(T.sdst[S_DIF_JOINT_VEL], rows, lane, djv * T.obs_scale[S_DIF_JOINT_VEL]);
+          emit1<kNoise>(T, rows, S_DIF_JOINT, lane, dja, nk);
+          emit1<kNoise>(T, rows, S_DIF_JOINT_VEL, lane, djv, nk);
         }
       }
       {
@@ -828,9 +865,9 @@ __global__ void __launch_bounds__(kTW * 32, 3) track_kernel(const __grid_constan
         else if (lane == 13) { k = S_DR_FRICTION; val = io.friction[n]; }
         else if (lane == 14) { k = S_DR_DELAY; val = (float)delay; }
         else { k = S_BASE_POS_Z; val = rp.z; }
-        put1(T.sdst[k], rows, ce, val * T.obs_scale[k]);
+        emit1<kNoise>(T, rows, k, ce, val, nk);
       }
-      for (int i = lane; i < L; i += 32) put1(T.sdst[S_DR_MASS], rows, i, io.link_mass_scale[n * L + i] * T.obs_scale[S_DR_MASS]);
+      for (int i = lane; i < L; i += 32) emit1<kNoise>(T, rows, S_DR_MASS, i, io.link_mass_scale[n * L + i], nk);
       if (lane == 0) { rv[V_ETR] = etr; }
       __syncwarp();
       // ---- I. rows -> global (clipped), history push, state write-back -----------------------------------------------
@@ -867,12 +904,22 @@ __global__ void __launch_bounds__(kTW * 32, 3) track_kernel(const __grid_constan
   }
 }
 
-// deterministic reduction of the per-block partials
-__global__ void track_reduce_kernel(const double* __restrict__ partials, int n_blocks, double* __restrict__ acc) {
-  const int a = threadIdx.x;  // blockDim = PBHC_ACC
+// deterministic reduction of the per-block partials: 32 groups of threads take every 32nd block (independent loads in
+// flight instead of one serial chain), then a fixed-order sum over the groups
+__global__ void __launch_bounds__(1024) track_reduce_kernel(const double* __restrict__ partials, int n_blocks, double* __restrict__ acc) {
+  __shared__ double part[32][PBHC_ACC + 1];
+  const int a = threadIdx.x & (PBHC_ACC - 1), g = threadIdx.x / PBHC_ACC;  // blockDim = 32 * PBHC_ACC
   double v = 0.0;
-  for (int b = 0; b < n_blocks; ++b) v += partials[(int64_t)b * PBHC_ACC + a];
-  acc[a] = v;
+#pragma unroll 4
+  for (int b = g; b < n_blocks; b += 32) v += partials[(int64_t)b * PBHC_ACC + a];
+  part[g][a] = v;
+  __syncthreads();
+  if (g == 0) {
+    double t = 0.0;
+#pragma unroll
+    for (int k = 0; k < 32; ++k) t += part[k][a];
+    acc[a] = t;
+  }
 }
 
 __device__ double curriculum(double value, double avg, const PbhcCurriculum& c, double sign_down) {
@@ -1032,20 +1079,26 @@ extern "C" int pbhc_track_step(const PbhcTrackCfg* cfg, const PbhcTableDesc* tab
   if (n > 0x7fffffffLL / (kChunk * 2)) { set_error("pbhc_track_step: too many envs for one launch"); return PBHC_E_RANGE; }
   const size_t shmem = (size_t)P.o_warp + (size_t)kTW * P.warp_bytes;
   if (shmem > 220 * 1024) { set_error("pbhc_track_step: shared memory %zu B too large", shmem); return PBHC_E_RANGE; }
-  static thread_local size_t configured = 0;
-  if (shmem > configured || g_track_blocks_per_sm == 0) {
-    if (cudaFuncSetAttribute(track_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shmem) != cudaSuccess) return check_launch("pbhc_track_step(attr)");
-    (void)cudaFuncSetAttribute(track_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
-    configured = shmem;
+  bool noise = false;
+  for (int k = 0; k < PBHC_NUM_OBS_SRC; ++k) noise |= c.obs_noise[k] != 0.0f;
+  // two instantiations: the noise-free one (benchmark.yaml, evaluation) carries no Philox code in its observation stores
+  auto kern = noise ? track_kernel<true> : track_kernel<false>;
+  static thread_local size_t configured[2] = {0, 0};
+  static thread_local int per_sm_of[2] = {0, 0};
+  if (shmem > configured[noise] || per_sm_of[noise] == 0) {
+    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shmem) != cudaSuccess) return check_launch("pbhc_track_step(attr)");
+    (void)cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    configured[noise] = shmem;
     int per_sm = 0;
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, track_kernel, kTW * 32, shmem);
-    g_track_blocks_per_sm = per_sm < 1 ? 1 : (per_sm > 8 ? 8 : per_sm);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kTW * 32, shmem);
+    per_sm_of[noise] = per_sm < 1 ? 1 : (per_sm > 8 ? 8 : per_sm);
   }
+  g_track_blocks_per_sm = per_sm_of[noise];
   int64_t blocks = (n + kTW - 1) / kTW;
   const int64_t cap = 148LL * g_track_blocks_per_sm;
   if (blocks > cap) blocks = cap;
-  track_kernel<<<(unsigned)blocks, kTW * 32, shmem, (cudaStream_t)stream>>>(P);
-  track_reduce_kernel<<<1, PBHC_ACC, 0, (cudaStream_t)stream>>>(io->partials, (int)blocks, io->acc);
+  kern<<<(unsigned)blocks, kTW * 32, shmem, (cudaStream_t)stream>>>(P);
+  track_reduce_kernel<<<1, 32 * PBHC_ACC, 0, (cudaStream_t)stream>>>(io->partials, (int)blocks, io->acc);
   return check_launch("pbhc_track_step");
 }
 

@@ -22,9 +22,17 @@ def motion_npz(name):
     return gold(f"motion_{name}.npz")
 
 
-def env_config(case="mt23_main"):
-    """the composed reference env config (hydra `env.config`) saved with the golden env fixture."""
-    return json.loads(str(gold(f"ref_env_{case}.npz")["meta_config_json"]))
+MAIN_NOISE = dict(base_ang_vel=0.3, projected_gravity=0.2, dof_pos=0.01, dof_vel=1.0)  # config/obs/motion_tracking/main.yaml:81-99
+
+
+def env_config(case="mt23_main", noise=None):
+    """the composed reference env config (hydra `env.config`) saved with the golden env fixture.  The fixture was
+    recorded with every observation-noise scale at 0 (torch.rand_like cannot be replayed); `noise` = dict of
+    noise_scales to put back (MAIN_NOISE = the values obs/motion_tracking/main.yaml ships)."""
+    cfg = json.loads(str(gold(f"ref_env_{case}.npz")["meta_config_json"]))
+    if noise:
+        cfg["obs"]["noise_scales"].update(noise)
+    return cfg
 
 
 EXTEND = [dict(joint_name="left_hand_link", parent_name="left_elbow_link", pos=[0.25, 0.0, 0.0], rot=[1.0, 0.0, 0.0, 0.0]),

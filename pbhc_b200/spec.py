@@ -191,7 +191,7 @@ class TrackSpec:
                     for hk in sorted(aux[key].keys()):
                         n = int(aux[key][hk]) * self.hist_dim[hk]
                         segs.append(dict(kind="hist", key=hk, len=int(aux[key][hk]), dim=self.hist_dim[hk], off=off,
-                                         scale=self.obs_scales[key]))
+                                         scale=self.obs_scales[key], group_key=key))
                         off += n
                 else:
                     n = obs_src_dim(key, D, J, self.L)

@@ -189,9 +189,9 @@ class TrackingStep:
                     k = OBS_SRC_IDS[seg["key"]]
                     used |= 1 << k
                     c.src_dst[k][g] = seg["off"]  # the source scale is applied by the producer
-                    if seg["noise"] != 0:
-                        raise NotImplementedError("observation noise: use noise scale 0 (obs/motion_tracking/benchmark.yaml) for now")
                 else:
+                    if s.noise_scales.get(seg.get("group_key", ""), 0.0) != 0:
+                        raise NotImplementedError("noise on a whole history block (noise_scales.history_*) is not implemented")
                     if n_hd >= _lib.MAX_HIST_DST:
                         raise NotImplementedError("too many history segments in the observation groups")
                     c.hist_dst[n_hd] = _lib.HistDst(s.hist_keys.index(seg["key"]), g, seg["off"], seg["len"], seg["scale"])
@@ -199,7 +199,9 @@ class TrackingStep:
         c.n_hist_dst = n_hd
         for i, k in enumerate(OBS_SRC):
             c.obs_scale[i] = s.obs_scales.get(k, 1.0)
-            c.obs_noise[i] = 0.0
+            # helpers.py:136-152: noise_scales[key] (x1: the noise curriculum is rejected by TrackSpec); it applies to the
+            # key wherever it is shown, the pushed history element included (legged_robot_base.py:781-783)
+            c.obs_noise[i] = s.noise_scales.get(k, 0.0) if (used >> i) & 1 or k in s.hist_keys else 0.0
         c.clip_obs = s.clip_observations
         c.n_hist_keys, c.hist_row = len(s.hist_keys), self.hist_row
         for i, k in enumerate(s.hist_keys):

@@ -44,11 +44,11 @@ def fk_bytes(J):
 class Workload:
     """Everything one rank needs to run env steps on `device` for `n_envs` environments."""
 
-    def __init__(self, n_envs, device, tmpdir, seed=0, case=CASE, clip=CLIP):
+    def __init__(self, n_envs, device, tmpdir, seed=0, case=CASE, clip=CLIP, noise=None):
         from .motion_lib import MotionLibRobot
         from .tracking_step import TrackingStep
         self.N, self.device = int(n_envs), torch.device(device)
-        self.spec = spec = TrackSpec.from_config(env_config(case))
+        self.spec = spec = TrackSpec.from_config(env_config(case, noise))
         self.lib = MotionLibRobot(product_cfg("23", tmpdir, [clip]), self.N, self.device)
         self.lib.load_motions(random_sample=False)
         self.ts = TrackingStep(spec, self.lib, self.N, self.device, seed=seed)

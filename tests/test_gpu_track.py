@@ -166,3 +166,63 @@ def test_host_step_chunked_pipeline_equals_single_launch(tmp_path):
         assert torch.equal(a.ts.hist.cpu(), b.ts.hist.cpu())
         assert torch.allclose(a.ts.scalars.cpu(), b.ts.scalars.cpu(), rtol=1e-12, atol=0)
     assert int(a.ts.reset_buf.sum()) > 0
+
+
+def test_observation_noise_statistics(tmp_path):
+    """obs/motion_tracking/main.yaml noise: (value + U(-1,1)*noise_scale) * obs_scale, an independent draw per element,
+    per observation group and for the pushed history element (helpers.py:128-152).  torch.rand_like cannot be replayed,
+    so parity here is distributional: bounds, mean 0, variance 1/3, independence between groups, exact equality of the
+    noise-free columns and of everything that is not an observation, reproducibility under the seed."""
+    from pbhc_b200.fixtures import MAIN_NOISE
+    from pbhc_b200.workload import Workload
+    n = 8192
+    clean = Workload(n, DEV, str(tmp_path / "c"), seed=5)
+    noisy = Workload(n, DEV, str(tmp_path / "n"), seed=5, noise=MAIN_NOISE)
+    again = Workload(n, DEV, str(tmp_path / "a"), seed=5, noise=MAIN_NOISE)
+    other = Workload(n, DEV, str(tmp_path / "o"), seed=6, noise=MAIN_NOISE)
+    other.load_env_state(noisy.host)  # same inputs, different seed (Workload draws its inputs from the seed too)
+    for name in ("_rigid_body_state", "all_root_states", "dof_state", "contact_forces", "_base_com_bias", "_link_mass_scale", "friction_coeffs"):
+        getattr(other.sim, name).copy_(getattr(noisy.sim, name))
+    other.actions.copy_(noisy.actions); other.torques.copy_(noisy.torques); other.env_origins.copy_(noisy.env_origins)
+    for wl in (clean, noisy, again, other):
+        wl.step(with_fk=False)
+    torch.cuda.synchronize()
+    spec = noisy.spec
+    assert torch.equal(clean.ts.rew_buf, noisy.ts.rew_buf) and torch.equal(clean.ts.reset_buf, noisy.ts.reset_buf)
+    keep = ~clean.ts.reset_buf.bool()
+    units = {}
+    for g, grp in spec.obs_groups.items():
+        a, b = clean.ts.obs_buf_dict[g], noisy.ts.obs_buf_dict[g]
+        assert torch.equal(b, again.ts.obs_buf_dict[g])
+        for seg in grp["segs"]:
+            cols = slice(seg["off"], seg["off"] + (seg["dim"] if seg["kind"] == "src" else seg["len"] * seg["dim"]))
+            ns = seg.get("noise", 0.0)
+            if seg["kind"] == "src" and ns != 0:
+                u = ((b[:, cols] - a[:, cols]) / (ns * seg["scale"]))[keep].double()
+                assert u.abs().max() <= 1.0 + 1e-4
+                assert abs(u.mean().item()) < 0.02 and abs(u.var().item() - 1.0 / 3.0) < 0.02
+                lo, hi = (u < -0.5).double().mean().item(), (u > 0.5).double().mean().item()
+                assert abs(lo - 0.25) < 0.02 and abs(hi - 0.25) < 0.02
+                if u.shape[1] > 1:  # neighbouring elements are independent
+                    assert abs((u[:, 0] * u[:, 1]).mean().item()) < 0.02
+                units[(g, seg["key"])] = u
+                o = ((other.ts.obs_buf_dict[g][:, cols] - a[:, cols]) / (ns * seg["scale"]))[keep].double()
+                assert abs((o * u).mean().item()) < 0.02 and not torch.equal(o, u)
+            elif seg["kind"] == "src":
+                assert torch.equal(a[:, cols], b[:, cols]), seg["key"]
+    groups = list(spec.obs_groups)
+    shared = [k for (g, k) in units if g == groups[0] and (groups[1], k) in units]
+    assert shared
+    for k in shared:  # actor and critic see different draws
+        assert abs((units[(groups[0], k)] * units[(groups[1], k)]).mean().item()) < 0.02
+    for k in spec.hist_keys:  # the pushed history element carries its own draw
+        ns = spec.noise_scales.get(k, 0.0)
+        new_c, new_n = clean.ts.history_handler.query(k)[:, 0], noisy.ts.history_handler.query(k)[:, 0]
+        if ns == 0:
+            assert torch.equal(new_c, new_n), k
+        else:
+            u = ((new_n - new_c) / (ns * spec.obs_scales[k]))[keep].double()
+            assert u.abs().max() <= 1.0 + 1e-4 and abs(u.var().item() - 1.0 / 3.0) < 0.02
+            for g in groups:
+                if (g, k) in units:
+                    assert abs((u * units[(g, k)]).mean().item()) < 0.02
