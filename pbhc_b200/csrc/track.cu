@@ -64,6 +64,7 @@ struct TrackParams {
   int push_len;                          // floats pushed into the history per step
   int push_off[PBHC_MAX_HIST_KEYS];      // offset of key k inside the push staging
   int hist_base[PBHC_MAX_HIST_KEYS];     // offset of key k inside the global history row
+  int hist_stage;                      // 1: the history ring is staged through the (then idle) simulator-state buffer
   int sm_body, sm_cf, sm_rows, sm_rv, sm_pre, sm_per_warp;  // per-warp shared-memory offsets (floats)
   int o_hmap, o_pmap, o_warp, warp_bytes;                    // byte offsets inside the dynamic shared memory
   int ob_body, ob_cf, ob_rows, ob_rv, ob_pre;                // byte offsets of the per-warp regions
@@ -402,6 +403,24 @@ __device__ __forceinline__ void warp_load(float* dst, const float* src, int coun
   }
 }
 
+// Asynchronous global -> shared copies (LDGSTS): the warp queues the next block of input while it computes on the current
+// one, so no lane ever waits on HBM latency for the simulator state or the history ring.
+__device__ __forceinline__ void cp_async16(void* s, const void* g) { asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(s)), "l"(g) : "memory"); }
+__device__ __forceinline__ void cp_async8(void* s, const void* g) { asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"((uint32_t)__cvta_generic_to_shared(s)), "l"(g) : "memory"); }
+__device__ __forceinline__ void cp_async4(void* s, const void* g) { asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((uint32_t)__cvta_generic_to_shared(s)), "l"(g) : "memory"); }
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+__device__ __forceinline__ void warp_load_async(float* dst, const float* src, int count, int vec, int lane) {
+  if (vec == 4) {
+    for (int i = lane; i < (count >> 2); i += 32) cp_async16(dst + 4 * i, src + 4 * i);
+    for (int i = (count & ~3) + lane; i < count; i += 32) cp_async4(dst + i, src + i);
+  } else if (vec == 2) {
+    for (int i = lane; i < (count >> 1); i += 32) cp_async8(dst + 2 * i, src + 2 * i);
+    if ((count & 1) && lane == 0) cp_async4(dst + count - 1, src + count - 1);
+  } else {
+    for (int i = lane; i < count; i += 32) cp_async4(dst + i, src + i);
+  }
+}
+
 // shared -> global copy of one observation row, clipped to +-clip (legged_robot_base.py:326-328)
 __device__ __forceinline__ void warp_store_clipped(float* dst, const float* src, int count, int vec, float clip, int lane) {
   if (vec == 4) {
@@ -517,6 +536,12 @@ __global__ void __launch_bounds__(kTW * 32, 3) track_kernel(const __grid_constan
   double acc_reg = 0.0;
 
   const int stride = (int)gridDim.x * kTW, n_envs = (int)P.n;  // P.n < 2^31 / kChunk (checked by the launcher): 32-bit env ids
+  const int hist_stage = P.hist_stage;
+  auto fetch_sim_state = [&](int64_t m) {  // queue env m's rigid-body state and contact forces into the staging buffers
+    warp_load_async(sm_body, io.body_state + m * io.body_env_stride, Jb * 13, body_vec, lane);
+    warp_load_async(sm_cf, io.contact_forces + m * (Jb * 3), Jb * 3, cf_vec, lane);
+  };
+  if ((int)blockIdx.x * kTW + warp < n_envs) fetch_sim_state((int)blockIdx.x * kTW + warp);
   for (int chunk = (int)blockIdx.x * kTW + warp; chunk < n_envs; chunk += kChunk * stride) {
     // ---- pre phase: lane i = i-th env of this chunk (legged_robot_base.py:346-353, motion_tracking.py:548-558, 678-739) ----
     __syncwarp();
@@ -554,10 +579,9 @@ __global__ void __launch_bounds__(kTW * 32, 3) track_kernel(const __grid_constan
       if (n32 >= n_envs) break;
       const int64_t n = n32;  // sign-extended 32-bit: every n * row_size below is one IMAD.WIDE
       const NoiseKey nk = {c.seed, n + io.env_offset, push_count};
+      cp_async_wait();  // this env's simulator state, queued while the previous env was being written out
       __syncwarp();
-      // ---- A. per-env scalars + staging of the simulator state --------------------------------------------
-      warp_load(sm_body, io.body_state + n * io.body_env_stride, Jb * 13, body_vec, lane);
-      warp_load(sm_cf, io.contact_forces + n * (Jb * 3), Jb * 3, cf_vec, lane);
+      // ---- A. per-env scalars ------------------------------------------------------------------------------
       if (lane == 0) {  // per-env scalars: loaded with the first wave of loads, parked in shared memory until phases D-G
         const float4* ge = reinterpret_cast<const float4*>(io.env_f32 + n * PBHC_ENVF_STRIDE);
         *reinterpret_cast<float4*>(rv + V_ENVF) = ge[0];
@@ -572,7 +596,7 @@ __global__ void __launch_bounds__(kTW * 32, 3) track_kernel(const __grid_constan
       const V3 rp = {pre[(P_RPX) * kChunk + e], pre[(P_RPY) * kChunk + e], pre[(P_RPZ) * kChunk + e]};
       const float org[3] = {io.env_origins[n * 3], io.env_origins[n * 3 + 1], io.env_origins[n * 3 + 2]};
       // history ring -> its places in the observation rows (HistoryHandler.query, history_handler.py:46-48)
-      if (c.hist_row > 0) hist_scatter(io.hist + n * c.hist_row, rows, hmap, c, P.n_hdst_max, P.hist_any_mul, hist_vec, lane, false);
+      if (c.hist_row > 0 && !hist_stage) hist_scatter(io.hist + n * c.hist_row, rows, hmap, c, P.n_hdst_max, P.hist_any_mul, hist_vec, lane, false);
       __syncwarp();
       // ---- B. bodies: reference (lerp / slerp of the two frames), extended state, differences, heading-frame features
       float sums[16];
@@ -733,6 +757,10 @@ __global__ void __launch_bounds__(kTW * 32, 3) track_kernel(const __grid_constan
       x_cm += __shfl_xor_sync(0xffffffffu, x_cm, 1);
       const bool stumble = __any_sync(0xffffffffu, x_stumble);
       float air1 = __shfl_sync(0xffffffffu, air_f, 1), contact1 = __shfl_sync(0xffffffffu, contact_f, 1);  // lane 0 packs the state
+      if (hist_stage) {  // the simulator-state buffer is idle from here on: the history ring arrives in it during E-H
+        __syncwarp();
+        warp_load_async(sm_body, io.hist + n * c.hist_row, c.hist_row, hist_vec, lane);
+      }
       // ---- E. termination (legged_robot_base.py:408-489, motion_tracking.py:330-358) -------------------------------
       const bool t_grav = c.term_gravity && pre[(P_GRAVN) * kChunk + e] > c.term_gravity_thr;
       const bool t_far = c.term_motion_far && any_far;
@@ -869,7 +897,13 @@ __global__ void __launch_bounds__(kTW * 32, 3) track_kernel(const __grid_constan
       }
       for (int i = lane; i < L; i += 32) emit1<kNoise>(T, rows, S_DR_MASS, i, io.link_mass_scale[n * L + i], nk);
       if (lane == 0) { rv[V_ETR] = etr; }
+      if (hist_stage) {  // history ring -> its places in the rows (zeros are already there for an env that reset)
+        cp_async_wait();
+        __syncwarp();
+        if (!reset) hist_scatter(sm_body, rows, hmap, c, P.n_hdst_max, P.hist_any_mul, hist_vec, lane, false);
+      }
       __syncwarp();
+      if (n32 + stride < n_envs) fetch_sim_state(n + stride);
       // ---- I. rows -> global (clipped), history push, state write-back -----------------------------------------------
       for (int g = 0; g < c.n_groups; ++g) {
         const int dim = c.group_dim[g];
@@ -1067,6 +1101,7 @@ extern "C" int pbhc_track_step(const PbhcTrackCfg* cfg, const PbhcTableDesc* tab
   P.o_pmap = P.o_hmap + 4 * up4h((P.n_hdst_max < 2 ? 2 : P.n_hdst_max) * c.hist_row);
   P.o_warp = P.o_pmap + 4 * up4h(push);
   P.warp_bytes = 4 * P.sm_per_warp;
+  P.hist_stage = (c.hist_row > 0 && c.hist_row <= P.sm_rows) ? 1 : 0;
   P.ob_body = 4 * P.sm_body; P.ob_cf = 4 * P.sm_cf; P.ob_rows = 4 * P.sm_rows; P.ob_rv = 4 * P.sm_rv; P.ob_pre = 4 * P.sm_pre;
   P.e_pos = 4 * c.J; P.e_vel = 7 * c.J; P.e_ang = 10 * c.J; P.e_dp = 13 * c.J; P.e_dv = P.e_dp + c.D; P.e_c = P.e_dv + c.D;
   {
