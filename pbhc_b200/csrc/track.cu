@@ -19,7 +19,13 @@
 
 namespace pbhc {
 
-constexpr int kTW = 8;                      // warps (envs in flight) per block
+#ifndef F_TW
+#define F_TW 8   // warps (envs in flight) per block
+#endif
+#ifndef F_BPS
+#define F_BPS 3  // resident blocks per SM the register budget is sized for
+#endif
+constexpr int kTW = F_TW;
 constexpr int kTrackMaxBlocks = 148 * 8;
 constexpr int kPre = 22;                    // per-env values of the pre phase
 constexpr int kChunk = 16;                  // envs per pre phase (lanes used by it)
@@ -505,7 +511,7 @@ __host__ __device__ inline int vec_of(int64_t row_floats, const void* base) {
 __device__ __forceinline__ int up4(int v) { return (v + 3) & ~3; }
 
 template <bool kNoise>
-__global__ void __launch_bounds__(kTW * 32, 3) track_kernel(const __grid_constant__ TrackParams P) {
+__global__ void __launch_bounds__(kTW * 32, F_BPS) track_kernel(const __grid_constant__ TrackParams P) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   BlockTables& T = *reinterpret_cast<BlockTables*>(smem_raw);
   const PbhcTrackCfg& c = P.c;
