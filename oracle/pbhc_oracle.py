@@ -132,6 +132,48 @@ def get_euler_xyz_in_tensor(q):
     return torch.stack((roll, pitch, yaw), dim=-1)
 
 
+def quat_apply(a, b):
+    """utils/torch_utils.py:51-58 (xyzw): b + w*t + xyz x t, t = 2 (xyz x b)."""
+    shape = b.shape
+    a = a.reshape(-1, 4)
+    b = b.reshape(-1, 3)
+    xyz = a[:, :3]
+    t = xyz.cross(b, dim=-1) * 2
+    return (b + a[:, 3:] * t + xyz.cross(t, dim=-1)).view(shape)
+
+
+def yaw_quat(quat):
+    """utils/torch_utils.py:239-270 (w_last): yaw-only quaternion, renormalised."""
+    shape = quat.shape
+    f = quat.reshape(-1, 4)
+    qx, qy, qz, qw = f[:, 0], f[:, 1], f[:, 2], f[:, 3]
+    yaw = torch.atan2(2 * (qw * qz + qx * qy), 1 - 2 * (qy * qy + qz * qz))
+    out = torch.zeros_like(f)
+    out[:, 2] = torch.sin(yaw / 2)
+    out[:, 3] = torch.cos(yaw / 2)
+    return normalize(out).view(shape)
+
+
+def matrix_from_quat(q):
+    """utils/torch_utils.py:274-297 (w_last): rotation matrix [..., 3, 3] with 2/|q|^2."""
+    i, j, k, r = torch.unbind(q, -1)
+    two_s = 2.0 / (q * q).sum(-1)
+    o = torch.stack((1 - two_s * (j * j + k * k), two_s * (i * j - k * r), two_s * (i * k + j * r),
+                     two_s * (i * j + k * r), 1 - two_s * (i * i + k * k), two_s * (j * k - i * r),
+                     two_s * (i * k - j * r), two_s * (j * k + i * r), 1 - two_s * (i * i + j * j)), -1)
+    return o.reshape(q.shape[:-1] + (3, 3))
+
+
+def quat_to_angle(q):
+    """angle part of quat_to_angle_axis (rotations.py:185-207): 2 acos(w) wrapped by atan2(sin, cos), 0 where
+    sqrt(1 - w^2) <= 1e-5 (NaN-compare false also gives 0)."""
+    w = q[..., 3]
+    sin_theta = torch.sqrt(1 - w * w)
+    angle = 2 * torch.acos(w)
+    angle = torch.atan2(torch.sin(angle), torch.cos(angle))
+    return torch.where(torch.abs(sin_theta) > 1e-5, angle, torch.zeros_like(angle))
+
+
 # ---- WXYZ helpers used by FK (rotations.py:519-636, "FROM PHC rotation_conversions.py") ----
 
 

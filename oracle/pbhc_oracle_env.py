@@ -1,8 +1,9 @@
-"""CPU oracle for the motion_tracking env step (K3).  TEST INFRASTRUCTURE ONLY.
+"""CPU oracle for the motion_tracking / general_tracking env step (K3).  TEST INFRASTRUCTURE ONLY.
 
 A torch-fp32 (CPU) restatement of what one `_post_physics_step` of the reference's
 LeggedRobotMotionTracking does (humanoidverse/envs/legged_base_task/legged_robot_base.py:297-338 and the
-callbacks it dispatches to; envs/motion_tracking/motion_tracking.py), driven by a pbhc_b200.spec.TrackSpec
+callbacks it dispatches to; envs/motion_tracking/motion_tracking.py) or LeggedRobotGeneralTracking
+(envs/motion_tracking/general_tracking.py, spec.general) does, driven by a pbhc_b200.spec.TrackSpec
 and the oracle motion table (oracle/pbhc_oracle.py).  Each block cites the reference lines it follows.
 
 Parity pin: tests/test_oracle_env_golden.py replays tests/golden/ref_env_*.npz - inputs and outputs of the
@@ -32,6 +33,7 @@ def new_state(spec, N, env_origins=None):
         kp_scale=torch.ones(N, D), kd_scale=torch.ones(N, D), rfi_lim_scale=torch.ones(N, D), rao_scale=torch.ones(N, D),
         action_delay_idx=torch.zeros(N, dtype=torch.long), default_dof_pos=torch.tensor(spec.default_joint_angles).repeat(N, 1),
         base_com_bias=torch.zeros(N, 3), link_mass_scale=torch.ones(N, spec.L), friction_coeffs=torch.ones(N, 1, 1),
+        base_mass_scale=torch.ones(N, 1),
         env_origins=torch.zeros(N, 3) if env_origins is None else env_origins,
         rew_buf=torch.zeros(N, len(spec.reward_names) + 1) if spec.use_vec_reward else torch.zeros(N),
         reset_buf=torch.ones(N, dtype=torch.long), time_out_buf=torch.zeros(N, dtype=torch.bool),
@@ -58,8 +60,8 @@ def _update_sigma(spec, S, err, term):
     ema, sig = S["ema_" + term], S["sigma_" + term]
     if a["type"] == "scale":
         S["sigma_" + term] = min(ema * a["scale"], sig)
-    elif a["type"] == "mean":
-        S["sigma_" + term] = (min(ema, sig) + ema) / 2
+    elif a["type"] == "mean":  # general_tracking.py:985 keeps only the EMA
+        S["sigma_" + term] = ema if spec.general else (min(ema, sig) + ema) / 2
     elif a["type"] == "origin":
         S["sigma_" + term] = min(ema, sig)
 
@@ -115,7 +117,75 @@ def _pre_compute(spec, tab, S, inp):
     W["global_ref_rigid_body_vel"] = ref["body_vel_t"].reshape(N, -1)
     # phase, motion_tracking.py:738-744
     W["ref_motion_phase"] = (times / tab.length[S["motion_ids"]]).unsqueeze(1)
+    if spec.general:
+        _pre_compute_general(spec, tab, S, inp, W)
     return W
+
+
+def _future_targets(spec, tab, S, W):
+    """_get_future_motion_targets, general_tracking.py:500-565: F future reference frames per env (2-D lookup)."""
+    N, F, a = S["motion_ids"].shape[0], spec.future_num_steps, spec.anchor_index
+    steps = torch.tensor(spec.future_steps, dtype=torch.long)
+    times = S["episode_length_buf"] * spec.dt + S["motion_start_times"]
+    obs_times = steps * spec.dt + times[:, None]
+    ids = S["motion_ids"][:, None].expand(-1, F)
+    off = S["env_origins"][:, None, :].expand(-1, F, -1)
+    r = O.get_motion_state(tab, ids, obs_times, off)
+    flat_rot = r["root_rot"].reshape(N * F, 4)
+    rpy = O.get_euler_xyz_in_tensor(flat_rot)
+    roll_pitch = rpy[:, :2].reshape(N, F, 2)
+    root_vel = O.quat_rotate_inverse(flat_rot, r["root_vel"].reshape(N * F, 3)).view(N, F, 3)
+    root_ang = O.quat_rotate_inverse(flat_rot, r["root_ang_vel"].reshape(N * F, 3)).view(N, F, 3)
+    pos_t, rot_t = r["rg_pos_t"], r["rg_rot_t"]
+    J = pos_t.shape[2]
+    a_pos = pos_t[..., a, :][..., None, :].repeat(1, 1, J, 1)
+    a_rot = rot_t[..., a, :][..., None, :].repeat(1, 1, J, 1)
+    key = O.quat_apply(O.quat_conjugate(a_rot), pos_t - a_pos)[..., spec.key_ids, :].reshape(N, F, -1)
+    W["future_motion_root_height"] = r["root_pos"][..., 2:3].reshape(N, -1)
+    W["future_motion_roll_pitch"] = roll_pitch.reshape(N, -1)
+    W["future_motion_base_lin_vel"] = root_vel.reshape(N, -1)
+    W["future_motion_base_yaw_vel"] = root_ang[..., 2:3].reshape(N, -1)
+    W["future_motion_dof_pos"] = r["dof_pos"].reshape(N, -1)
+    W["future_motion_local_ref_key_body_pos"] = key.reshape(N, -1)
+    W["next_step_ref_motion"] = torch.cat((r["root_pos"][:, 0, 2:3], roll_pitch[:, 0, :], root_vel[:, 0, :], root_ang[:, 0, 2:3],
+                                           r["dof_pos"][:, 0, :], key[:, 0, :]), dim=-1)
+
+
+def _pre_compute_general(spec, tab, S, inp, W):
+    """what LeggedRobotGeneralTracking._pre_compute_observations_callback adds or changes
+    (general_tracking.py:568-805)."""
+    N, J, a = inp["root_state"].shape[0], spec.J, spec.anchor_index
+    ref, root = W["ref"], inp["root_state"]
+    if spec.future_num_steps > 0:
+        _future_targets(spec, tab, S, W)
+    W["rpy"] = O.get_euler_xyz_in_tensor(root[:, 3:7])          # legged_robot_base.py:349
+    W["roll_pitch"] = W["rpy"][:, :2]
+    # differences (:638-666): quaternion product instead of the component-wise subtraction of motion_tracking
+    W["dif_rot"] = O.quat_mul(ref["rg_rot_t"], O.quat_conjugate(W["rot_ext"]))
+    ref_root_vel_local = O.quat_rotate_inverse(ref["root_rot"].view(N, 4), ref["root_vel"].view(N, 3)).view(N, 3)
+    W["dif_root_velocity"] = ref_root_vel_local - W["base_lin_vel"]
+    # beyondmimic block (:738-803)
+    pos_ext, rot_ext = W["pos_ext"], W["rot_ext"]
+    a_pos = ref["rg_pos_t"][:, a, :][:, None, :].repeat(1, J, 1)
+    a_rot = ref["rg_rot_t"][:, a, :][:, None, :].repeat(1, J, 1)
+    ra_pos = pos_ext[:, a, :][:, None, :].repeat(1, J, 1)
+    ra_rot = rot_ext[:, a, :][:, None, :].repeat(1, J, 1)
+    delta_pos = ra_pos                      # the reference aliases: the z overwrite below also changes ra_pos (:752-753)
+    delta_pos[..., 2] = a_pos[..., 2]
+    delta_ori = O.yaw_quat(O.quat_mul(ra_rot, O.quat_conjugate(a_rot)))
+    rel_pos = delta_pos + O.quat_apply(delta_ori, ref["rg_pos_t"] - a_pos)
+    rel_rot = O.quat_mul(delta_ori, ref["rg_rot_t"])
+    W["dif_local_body_pos"] = rel_pos - pos_ext
+    W["dif_local_body_rot"] = O.quat_mul(rel_rot, O.quat_conjugate(rot_ext))
+    W["local_body_rot"] = O.matrix_from_quat(O.quat_mul(O.quat_conjugate(ra_rot), rot_ext))[..., :2]
+    W["local_body_pos"] = O.quat_apply(O.quat_conjugate(ra_rot), pos_ext - ra_pos)
+    W["anchor_ref_rot"] = O.matrix_from_quat(O.quat_mul(O.quat_conjugate(rot_ext[:, a, :]), ref["rg_rot_t"][:, a, :]))[..., :2]
+    W["anchor_ref_pos"] = O.quat_apply(O.quat_conjugate(rot_ext[:, a, :]), ref["rg_pos_t"][:, a, :] - pos_ext[:, a, :])
+    W["dif_anchor_body_pos"] = W["dif_pos"][:, a, :]
+    W["dif_anchor_pos_z"] = ref["rg_pos_t"][:, a, -1] - pos_ext[:, a, -1]
+    grav = torch.tensor([0.0, 0.0, -1.0]).repeat(N, 1)
+    W["dif_anchor_ori"] = (O.quat_rotate_inverse(ref["rg_rot_t"][:, a, :], grav)[:, 2]
+                           - O.quat_rotate_inverse(rot_ext[:, a, :], grav)[:, 2])
 
 
 def _termination(spec, S, W, log):
@@ -132,6 +202,16 @@ def _termination(spec, S, W, log):
         S["reset_buf"] |= by["motion_far"]
         if spec.far_cur["enable"]:
             log["terminate_when_motion_far_threshold"] = torch.tensor(S["motion_far_threshold"], dtype=torch.float)
+    if spec.general:  # general_tracking.py:241-255
+        if spec.term_ref_pos_z:
+            by["ref_pos_z"] = torch.abs(W["dif_anchor_pos_z"]) > spec.term_ref_pos_z_thr
+            S["reset_buf"] |= by["ref_pos_z"]
+        if spec.term_ref_ori:
+            by["ref_ori"] = W["dif_anchor_ori"].abs() > spec.term_ref_ori_thr
+            S["reset_buf"] |= by["ref_ori"]
+        if spec.term_body_z:
+            by["body_z"] = torch.any(W["dif_local_body_pos"][:, spec.body_z_ids, -1].abs() > spec.term_body_z_thr, dim=-1)
+            S["reset_buf"] |= by["body_z"]
     S["time_out_buf"] |= S["episode_length_buf"] > spec.max_episode_length
     by["time_out"] = S["time_out_buf"]
     if spec.term_motion_end:
@@ -223,6 +303,17 @@ def _rewards(spec, S, W, inp, log):
                                   else torch.sum((torch.abs(torques) - tl * spec.soft_torque_limit).clip(min=0.0), dim=1)),
         "collision": lambda: torch.sum(1.0 * (torch.norm(cf[:, spec.penalised_ids, :], dim=-1) > 0.1), dim=1),
     }
+    if spec.general:  # general_tracking.py:1116-1270
+        K, a = spec.key_ids, spec.anchor_index
+        fn.update({
+            "teleop_root_vel": lambda: track((W["dif_root_velocity"] ** 2).mean(dim=-1), "teleop_root_vel"),
+            "teleop_anchor_body_position": lambda: track((W["dif_anchor_body_pos"] ** 2).mean(dim=-1), "teleop_anchor_body_pos"),
+            "teleop_anchor_body_rotation": lambda: track(O.quat_to_angle(W["dif_rot"])[:, a] ** 2, "teleop_anchor_body_rot"),
+            "local_key_body_position": lambda: track(msq(W["dif_local_body_pos"][:, K, :]), "local_key_body_pos"),
+            "local_key_body_rotation": lambda: track((O.quat_to_angle(W["dif_local_body_rot"])[:, K] ** 2).mean(dim=-1), "local_key_body_rot"),
+            "key_body_velocity": lambda: track(msq(W["dif_vel"][:, K, :]), "key_body_vel"),
+            "key_body_ang_velocity": lambda: track(msq(W["dif_ang"][:, K, :]), "key_body_ang_vel"),
+        })
     S["rew_buf"][:] = 0.0
     i = 0
     for i, name in enumerate(spec.reward_names):
@@ -314,8 +405,12 @@ def _reset(spec, tab, S, W, inp, inject, log, last_ep_len):
     if spec.noise_to_initial_level != 0:
         raise NotImplementedError("oracle: reset noise needs injected normals (reference default noise_to_initial_level = 0)")
     dof = inp["dof_state"]
-    dof[ids, :, 0] = ref["dof_pos"][ids]
-    dof[ids, :, 1] = ref["dof_vel"][ids]
+    # general_tracking._reset_dofs (:464-483) queries the motion at episode_length*dt + start (no +1); motion_tracking's
+    # (:524-543) shares kick_motion_res() with the root reset
+    ref_d = (O.get_motion_state(tab, S["motion_ids"], S["episode_length_buf"] * spec.dt + S["motion_start_times"], offset=S["env_origins"])
+             if spec.general else ref)
+    dof[ids, :, 0] = ref_d["dof_pos"][ids]
+    dof[ids, :, 1] = ref_d["dof_vel"][ids]
     root = inp["root_state"]
     root[ids, :3] = ref["root_pos"][ids]
     ident = torch.zeros(len(ids), 4)
@@ -346,6 +441,18 @@ def _observations(spec, S, W, inp):
         "dif_joint_angles": W["dif_joint_angles"], "dif_joint_velocities": W["dif_joint_velocities"],
         "base_pos_z": inp["root_state"][:, 2:3],
     }
+    if spec.general:  # getters of general_tracking.py:879-927; root_height is a live view of the root state (:608)
+        K = spec.key_ids
+        src.update({
+            "roll_pitch": W["roll_pitch"], "local_key_body_pos": W["local_body_pos"][:, K, :].reshape(N, -1),
+            "local_key_body_rot": W["local_body_rot"][:, K, ...].reshape(N, -1), "anchor_ref_pos": W["anchor_ref_pos"].reshape(N, -1),
+            "anchor_ref_rot": W["anchor_ref_rot"].reshape(N, -1), "contact_mask": W["contacts_filt"],
+            "root_height": inp["root_state"][:, 2:3], "dr_base_mass": S["base_mass_scale"],
+        })
+        for k in ("next_step_ref_motion", "future_motion_root_height", "future_motion_roll_pitch", "future_motion_base_lin_vel",
+                  "future_motion_base_yaw_vel", "future_motion_dof_pos", "future_motion_local_ref_key_body_pos"):
+            if k in W:
+                src[k] = W[k]
     obs = {}
     for g, grp in spec.obs_groups.items():
         parts = []
@@ -382,6 +489,13 @@ def step(spec, tab, S, inp, inject=None):
     log["lower_body_diff_norm"] = dp[:, spec.lower_ids, :].norm(dim=-1).mean()
     log["vr_3point_diff_norm"] = dp[:, spec.vr3_ids, :].norm(dim=-1).mean()
     log["joint_pos_diff_norm"] = W["dif_joint_angles"].norm(dim=-1).mean()
+    if spec.general:  # general_tracking.py:303-335
+        dl = W["dif_local_body_pos"]
+        log["key_body_diff_norm"] = dp[:, spec.key_ids, :].norm(dim=-1).mean()
+        log["local_upper_body_diff_norm"] = dl[:, spec.upper_ids, :].norm(dim=-1).mean()
+        log["local_lower_body_diff_norm"] = dl[:, spec.lower_ids, :].norm(dim=-1).mean()
+        log["local_vr_3point_diff_norm"] = dl[:, spec.vr3_ids, :].norm(dim=-1).mean()
+        log["local_key_body_diff_norm"] = dl[:, spec.key_ids, :].norm(dim=-1).mean()
     _termination(spec, S, W, log)
     _rewards(spec, S, W, inp, log)
     extras = {"ref_body_pos_extend": W["ref"]["rg_pos_t"].clone(), "ref_body_rot_extend": W["ref"]["rg_rot_t"].clone()}

@@ -84,6 +84,19 @@ def build_config(num_envs, motion_file, robot="g1/g1_23dof_lock_wrist", rewards=
                 v = int(eval(m.group(1))) if m else int(v)
             dims[k] = v
     obs_c["obs_dims"] = dims
+
+    def _interp(x):  # ${obs.history_length} etc. inside the obs group (OmegaConf interpolation)
+        if isinstance(x, dict):
+            return {k: _interp(v) for k, v in x.items()}
+        if isinstance(x, list):
+            return [_interp(v) for v in x]
+        if isinstance(x, str):
+            m = re.match(r"^\$\{obs\.([A-Za-z_]+)\}$", x)
+            if m:
+                return obs_c[m.group(1)]
+        return x
+    for k in list(obs_c.keys()):
+        obs_c[k] = _interp(obs_c[k])
     for k, v in (overrides or {}).items():
         node = cfg
         ks = k.split(".")

@@ -18,7 +18,15 @@ def tree_json(tag):
         return json.load(f)
 
 
+# the multi-clip 29-DoF library of config C: three clips cut out of the one committed 29-DoF sequence (frame ranges)
+CLIPS29 = {"clip_full": (0, 520), "clip_a": (100, 300), "clip_b": (250, 500)}
+
+
 def motion_npz(name):
+    if name in CLIPS29:
+        lo, hi = CLIPS29[name]
+        m = gold("motion_g1_29dof_clip.npz")
+        return {k: (v[lo:hi] if getattr(v, "ndim", 0) else v) for k, v in m.items()}
     return gold(f"motion_{name}.npz")
 
 

@@ -15,24 +15,40 @@ REWARD_IDS = {name: i for i, name in enumerate([
     "teleop_body_velocity_extend", "teleop_joint_position", "teleop_joint_velocity", "penalty_torques",
     "penalty_action_rate", "feet_air_time", "penalty_feet_contact_forces", "penalty_stumble", "penalty_slippage",
     "limits_dof_pos", "limits_dof_vel", "limits_torque", "collision", "penalty_dof_vel", "penalty_dof_acc",
-    "foot_slip_penalty", "alive", "penalty_orientation", "teleop_contact_mask_v2"])}
+    "foot_slip_penalty", "alive", "penalty_orientation", "teleop_contact_mask_v2",
+    # general_tracking (general_tracking.py:1116-1270)
+    "teleop_root_vel", "teleop_anchor_body_position", "teleop_anchor_body_rotation", "local_key_body_position",
+    "local_key_body_rotation", "key_body_velocity", "key_body_ang_velocity"])}
 
 # adaptive-sigma slots (config.rewards.reward_tracking_sigma keys), in enum order
 SIGMA_IDS = {name: i for i, name in enumerate([
     "teleop_max_joint_pos", "teleop_upper_body_pos", "teleop_lower_body_pos", "teleop_vr_3point_pos",
     "teleop_feet_pos", "teleop_body_rot", "teleop_body_vel", "teleop_body_ang_vel", "teleop_joint_pos",
-    "teleop_joint_vel"])}
+    "teleop_joint_vel",
+    "teleop_root_vel", "teleop_anchor_body_pos", "teleop_anchor_body_rot", "local_key_body_pos", "local_key_body_rot",
+    "key_body_vel", "key_body_ang_vel"])}
 
 # observation sources (getters `_get_obs_<key>`), enum order; dims as functions of (D, J, L)
 OBS_SRC = ["base_lin_vel", "base_ang_vel", "projected_gravity", "dof_pos", "dof_vel", "actions", "ref_motion_phase",
            "dif_local_rigid_body_pos", "local_ref_rigid_body_pos", "dr_base_com", "dr_link_mass", "dr_kp", "dr_kd",
            "dr_friction", "dr_ctrl_delay", "local_ref_rigid_body_vel", "global_ref_rigid_body_vel", "dif_joint_angles",
-           "dif_joint_velocities", "base_pos_z"]
+           "dif_joint_velocities", "base_pos_z",
+           # general_tracking getters (general_tracking.py:879-927, legged_robot_base.py:1193)
+           "roll_pitch", "local_key_body_pos", "local_key_body_rot", "anchor_ref_pos", "anchor_ref_rot", "next_step_ref_motion",
+           "contact_mask", "root_height", "dr_base_mass", "future_motion_root_height", "future_motion_roll_pitch",
+           "future_motion_base_lin_vel", "future_motion_base_yaw_vel", "future_motion_dof_pos",
+           "future_motion_local_ref_key_body_pos"]
+GENERAL_ONLY_SRC = set(OBS_SRC[OBS_SRC.index("roll_pitch"):])
 OBS_SRC_IDS = {k: i for i, k in enumerate(OBS_SRC)}
 
 
-def obs_src_dim(key, D, J, L):
-    return {"base_lin_vel": 3, "base_ang_vel": 3, "projected_gravity": 3, "dof_pos": D, "dof_vel": D, "actions": D,
+def obs_src_dim(key, D, J, L, K=0, F=0):
+    """K = number of key bodies, F = future_num_steps (general_tracking only)."""
+    return {"roll_pitch": 2, "local_key_body_pos": 3 * K, "local_key_body_rot": 6 * K, "anchor_ref_pos": 3, "anchor_ref_rot": 6,
+            "next_step_ref_motion": 7 + D + 3 * K, "contact_mask": 2, "root_height": 1, "dr_base_mass": 1,
+            "future_motion_root_height": F, "future_motion_roll_pitch": 2 * F, "future_motion_base_lin_vel": 3 * F,
+            "future_motion_base_yaw_vel": F, "future_motion_dof_pos": F * D, "future_motion_local_ref_key_body_pos": F * 3 * K,
+            "base_lin_vel": 3, "base_ang_vel": 3, "projected_gravity": 3, "dof_pos": D, "dof_vel": D, "actions": D,
             "ref_motion_phase": 1, "dif_local_rigid_body_pos": 3 * J, "local_ref_rigid_body_pos": 3 * J, "dr_base_com": 3,
             "dr_link_mass": L, "dr_kp": D, "dr_kd": D, "dr_friction": 1, "dr_ctrl_delay": 1,
             "local_ref_rigid_body_vel": 3 * J, "global_ref_rigid_body_vel": 3 * J, "dif_joint_angles": D,
@@ -55,8 +71,14 @@ class TrackSpec:
     """see module docstring.  Build with TrackSpec.from_config(env_config)."""
 
     @classmethod
-    def from_config(cls, cfg):
+    def from_config(cls, cfg, env_class=None):
+        """cfg: the composed `env.config`.  env_class: "motion_tracking" (LeggedRobotMotionTracking) or "general_tracking"
+        (LeggedRobotGeneralTracking) - what hydra's `env._target_` selects; defaults to cfg["env_class"] if present."""
         s = cls()
+        s.env_class = env_class or _get(cfg, "env_class", "motion_tracking")
+        if s.env_class not in ("motion_tracking", "general_tracking"):
+            raise ValueError(f"unknown env class {s.env_class}")
+        s.general = s.env_class == "general_tracking"
         robot, rw, obs, dr = _get(cfg, "robot"), _get(cfg, "rewards"), _get(cfg, "obs"), _get(cfg, "domain_rand")
         s.body_names = list(_get(robot, "body_names"))
         s.dof_names = list(_get(robot, "dof_names"))
@@ -79,6 +101,10 @@ class TrackSpec:
         s.vr3_ids = [s.body_list.index(n) for n in _get(robot, "motion.motion_tracking_link", [])]
         s.lower_ids = [s.body_list.index(n) for n in _get(robot, "motion.lower_body_link", [])]
         s.upper_ids = [s.body_list.index(n) for n in _get(robot, "motion.upper_body_link", [])]
+        # general_tracking.py:86-98: key bodies; anchor = find_rigid_body_indice(anchor_link) + 1 (not found -> -1 -> body 0)
+        s.key_ids = [s.body_list.index(n) for n in (_get(robot, "key_bodies", []) or [])] if s.general else []
+        anchor_link = _get(robot, "motion.anchor_link", "pelvis_link")
+        s.anchor_index = (s.body_names.index(anchor_link) if anchor_link in s.body_names else -1) + 1
         s.default_joint_angles = [float(_get(robot, "init_state.default_joint_angles")[n]) for n in s.dof_names]
         s.hard_dof_lo = [float(v) for v in _get(robot, "dof_pos_lower_limit_list")]
         s.hard_dof_hi = [float(v) for v in _get(robot, "dof_pos_upper_limit_list")]
@@ -156,6 +182,15 @@ class TrackSpec:
         self.term_motion_far = bool(_get(t, "terminate_when_motion_far", False))
         self.term_motion_end = bool(_get(t, "terminate_when_motion_end", False))
         self.term_gravity_thr = float(_get(cfg, "termination_scales.termination_gravity", 0.0))
+        # general_tracking.py:241-255
+        g = self.general
+        self.term_ref_pos_z = bool(g and _get(t, "terminate_by_ref_pos_z", False))
+        self.term_ref_ori = bool(g and _get(t, "terminate_by_ref_ori", False))
+        self.term_body_z = bool(g and _get(t, "terminate_by_body_z", False))
+        self.term_ref_pos_z_thr = float(_get(cfg, "termination_scales.terminate_by_ref_pos_z_threshold", 0.25))
+        self.term_ref_ori_thr = float(_get(cfg, "termination_scales.terminate_by_ref_ori_threshold", 0.8))
+        self.term_body_z_thr = float(_get(cfg, "termination_scales.terminate_by_body_z_threshold", 0.25))
+        self.body_z_ids = [4, 10, 24, 25, 26]  # hard-coded in the reference (:253)
         tc = _get(cfg, "termination_curriculum")
         self.far_cur = dict(enable=bool(self.term_motion_far and _get(tc, "terminate_when_motion_far_curriculum", False)),
                             initial=float(_get(tc, "terminate_when_motion_far_initial_threshold", 0)),
@@ -171,6 +206,17 @@ class TrackSpec:
     def _from_obs(self, cfg, obs, dr):
         D, J = self.D, self.J
         self.L = len(_get(dr, "randomize_link_body_names", []) or [])
+        K = len(self.key_ids)
+        self.future_num_steps = int(_get(obs, "future_num_steps", 0) or 0) if self.general else 0
+        self.future_max_steps = int(_get(obs, "future_max_steps", 0) or 0)
+        F = self.future_num_steps
+        if F > 0:  # torch.linspace(1, max, F, dtype=long) (general_tracking.py:501-507), evaluated by torch itself
+            import torch
+            self.future_steps = [int(v) for v in torch.linspace(start=1, end=self.future_max_steps, steps=F, dtype=torch.long)]
+        else:
+            self.future_steps = []
+        if bool(_get(obs, "masked_dof_vel", False)):
+            raise NotImplementedError("obs.masked_dof_vel is not implemented by the B200 tracking step")
         self.obs_scales = {k: float(v) for k, v in dict(_get(obs, "obs_scales")).items()}
         self.noise_scales = {k: float(v) for k, v in dict(_get(obs, "noise_scales")).items()}
         aux = {a: dict(c) for a, c in dict(_get(obs, "obs_auxiliary", {}) or {}).items()}
@@ -180,7 +226,7 @@ class TrackSpec:
             for k, n in c.items():
                 self.hist_len[k] = max(self.hist_len.get(k, 0), int(n))
         self.hist_keys = list(self.hist_len.keys())
-        self.hist_dim = {k: obs_src_dim(k, D, J, self.L) for k in self.hist_keys}
+        self.hist_dim = {k: obs_src_dim(k, D, J, self.L, K, F) for k in self.hist_keys}
         self.obs_groups = {}
         for g, keys in dict(_get(obs, "obs_dict")).items():
             segs, off = [], 0
@@ -194,7 +240,9 @@ class TrackSpec:
                                          scale=self.obs_scales[key], group_key=key))
                         off += n
                 else:
-                    n = obs_src_dim(key, D, J, self.L)
+                    if key in GENERAL_ONLY_SRC and not self.general:
+                        raise NotImplementedError(f"observation '{key}' exists only in general_tracking")
+                    n = obs_src_dim(key, D, J, self.L, K, F)
                     segs.append(dict(kind="src", key=key, dim=n, off=off, scale=self.obs_scales[key],
                                      noise=self.noise_scales[key]))
                     off += n

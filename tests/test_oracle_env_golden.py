@@ -18,7 +18,12 @@ def load_case(name):
     g = gold(f"ref_env_{name}.npz")
     spec = TrackSpec.from_config(json.loads(str(g["meta_config_json"])))
     N = int(g["meta_n_envs"])
-    tab = O.MotionTable([oracle_clip("23", "Horse-stance_pose")], spec.Jb, motion_to_clip=[0] * N)
+    if spec.general:
+        from pbhc_b200.fixtures import CLIPS29
+        clips = [oracle_clip("29", nm) for nm in CLIPS29]
+        tab = O.MotionTable(clips, spec.Jb, motion_to_clip=[i % len(clips) for i in range(N)])  # load_motions(random_sample=False)
+    else:
+        tab = O.MotionTable([oracle_clip("23", "Horse-stance_pose")], spec.Jb, motion_to_clip=[0] * N)
     return g, spec, N, tab
 
 
@@ -33,7 +38,7 @@ def state_from(g, prefix, spec):
     return S
 
 
-@pytest.mark.parametrize("case", ["mt23_main", "mt23_bench"])
+@pytest.mark.parametrize("case", ["mt23_main", "mt23_bench", "gt29_teacher"])
 def test_env_step_oracle_matches_reference(case):
     g, spec, N, tab = load_case(case)
     S = state_from(g, "init_", spec)

@@ -30,12 +30,14 @@ def env_state(env):
         action_delay_idx=env.action_delay_idx, default_dof_pos=env.default_dof_pos,
         base_com_bias=env.simulator._base_com_bias, link_mass_scale=env.simulator._link_mass_scale,
         friction_coeffs=env.simulator.friction_coeffs, env_origins=env.env_origins,
-        average_episode_length=np.float64(env.average_episode_length), reward_penalty_scale=np.float64(env.reward_penalty_scale),
+        average_episode_length=np.float64(env.average_episode_length), reward_penalty_scale=np.float64(getattr(env, "reward_penalty_scale", 1.0)),
         motion_far_threshold=np.float64(env.terminate_when_motion_far_threshold),
-        soft_dof_pos=np.float64(env.soft_dof_pos_curriculum_value), soft_dof_vel=np.float64(env.soft_dof_vel_curriculum_value),
-        soft_torque=np.float64(env.soft_torque_curriculum_value), rew_buf=env.rew_buf, reset_buf=env.reset_buf,
+        soft_dof_pos=np.float64(getattr(env, "soft_dof_pos_curriculum_value", 1.0)), soft_dof_vel=np.float64(getattr(env, "soft_dof_vel_curriculum_value", 1.0)),
+        soft_torque=np.float64(getattr(env, "soft_torque_curriculum_value", 1.0)), rew_buf=env.rew_buf, reset_buf=env.reset_buf,
         time_out_buf=env.time_out_buf, dof_state=env.simulator.dof_state, root_state=env.simulator.all_root_states,
         end_time_ratio_buf=env.end_time_ratio_buf)
+    if hasattr(env.simulator, "_base_mass_scale"):
+        s["base_mass_scale"] = env.simulator._base_mass_scale
     for k, v in env.history_handler.history.items():
         s["hist_" + k] = v
     for k, v in env.episode_sums.items():
@@ -47,16 +49,35 @@ def env_state(env):
     return {k: _np(v) for k, v in s.items()}
 
 
-def run_case(name, n_envs, n_steps, obs, seed, overrides=None):
+def _library29(tmp="/tmp/pbhc_golden"):
+    """the 3-clip 29-DoF library of pbhc_b200.fixtures.CLIPS29 as a joblib file the reference loads."""
+    import joblib
+    from pbhc_b200.fixtures import CLIPS29, motion_npz
+    os.makedirs(tmp, exist_ok=True)
+    data = {}
+    for nm in CLIPS29:
+        m = motion_npz(nm)
+        data[nm] = dict(root_trans_offset=m["root_trans_offset"], pose_aa=m["pose_aa"], dof=m["dof"], root_rot=m["root_rot"], fps=int(m["fps"]))
+    path = os.path.join(tmp, "motions29_3.pkl")
+    joblib.dump(data, path)
+    return path
+
+
+def run_case(name, n_envs, n_steps, obs, seed, overrides=None, general=False):
     ov = {"domain_rand.push_robots": False}
     ov.update(overrides or {})
-    cfg = E.build_config(n_envs, R.example_motion("Horse-stance_pose"), obs=obs, overrides=ov)
+    if general:
+        cfg = E.build_config(n_envs, _library29(), robot="g1/g1_29dof_general", rewards="motion_tracking/general_main", obs=obs,
+                             env="general_tracking", overrides=ov)
+    else:
+        cfg = E.build_config(n_envs, R.example_motion("Horse-stance_pose"), obs=obs, overrides=ov)
     import copy, json
     cj = copy.deepcopy(cfg)  # before the env mutates it (reward_scales *= dt, adaptive sigmas)
-    cj["robot"]["motion"]["motion_file"] = "Horse-stance_pose"
+    cj["robot"]["motion"]["motion_file"] = "clips29" if general else "Horse-stance_pose"
     cj["robot"]["motion"]["asset"]["assetRoot"] = "description/robots/g1/"
+    cj["env_class"] = "general_tracking" if general else "motion_tracking"
     cfg_json = json.dumps(cj)
-    env, ns = E.make_env(cfg, seed=seed)
+    env, ns = E.make_env(cfg, env_cls="general" if general else "motion_tracking", seed=seed)
     sim = env.simulator
     gen = torch.Generator().manual_seed(seed)
     N, D, Jb = n_envs, env.num_dof, env.num_bodies
@@ -69,6 +90,8 @@ def run_case(name, n_envs, n_steps, obs, seed, overrides=None):
     sim._base_com_bias[:] = (torch.rand(N, 3, generator=gen) - 0.5) * 0.1
     sim._link_mass_scale[:] = 0.9 + 0.2 * torch.rand(N, sim._link_mass_scale.shape[1], generator=gen)
     sim.friction_coeffs[:] = 0.2 + torch.rand(N, 1, 1, generator=gen)
+    if general:
+        sim._base_mass_scale[:] = 0.9 + 0.2 * torch.rand(N, 1, generator=gen)
     env._kp_scale[:] = 0.9 + 0.2 * torch.rand(N, D, generator=gen)
     env._kd_scale[:] = 0.9 + 0.2 * torch.rand(N, D, generator=gen)
     out = {"meta_config_json": cfg_json, "meta_n_envs": N, "meta_n_steps": n_steps, "meta_obs": obs, "meta_dt": env.dt,
@@ -83,7 +106,7 @@ def run_case(name, n_envs, n_steps, obs, seed, overrides=None):
         env._physics_step()
         t = (env.episode_length_buf + 2) * env.dt + env.motion_start_times
         ref = env._motion_lib.get_motion_state(env.motion_ids, t, offset=env.env_origins)
-        body, root, dof, cf = synth.synth_sim_state(ref, Jb, gen)
+        body, root, dof, cf = synth.synth_sim_state(ref, Jb, gen, feet=tuple(int(i) for i in env.feet_indices))
         sim.set_state(body, root, dof, cf)
         p = f"s{step}_"
         out.update({p + "in_body_state": _np(body), p + "in_root_state": _np(root), p + "in_dof_state": _np(dof),
@@ -101,6 +124,11 @@ def run_case(name, n_envs, n_steps, obs, seed, overrides=None):
         out[p + "dbg_ref_motion_phase"] = _np(env._ref_motion_phase)
         out[p + "dbg_base_ang_vel"] = _np(env.base_ang_vel)
         out[p + "dbg_projected_gravity"] = _np(env.projected_gravity)
+        if general:
+            for k in ("dif_local_body_pos", "dif_local_body_rot", "dif_global_body_rot", "dif_root_velocity", "dif_anchor_pos_z", "dif_anchor_ori",
+                      "body_pos_relative_w", "_obs_local_body_pos", "_obs_local_body_rot", "_obs_anchor_ref_pos", "_obs_anchor_ref_rot",
+                      "obs_next_step_mimic_buf", "rpy"):
+                out[p + "dbg_" + k.lstrip("_")] = _np(getattr(env, k))
     np.savez_compressed(os.path.join(GOLD, f"ref_env_{name}.npz"), **out)
     return env
 
@@ -113,7 +141,17 @@ def run(ns=None):
     # non-zero noise scales to 0 exactly like the reference's own obs/motion_tracking/benchmark.yaml does.
     run_case("mt23_main", 48, 6, "motion_tracking/main", 11, ZERO_NOISE)
     run_case("mt23_bench", 32, 3, "motion_tracking/benchmark", 12)
+    run_general()
+
+
+ZERO_NOISE_C = {f"obs.noise_scales.{k}": 0.0 for k in ("base_ang_vel", "dof_pos", "dof_vel", "roll_pitch")}
+
+
+def run_general():
+    # config C: LeggedRobotGeneralTracking, G1 29-DoF, obs_ppo_teacher, rewards general_main, 3-clip library
+    run_case("gt29_teacher", 48, 6, "motion_tracking/obs_ppo_teacher", 21, ZERO_NOISE_C, general=True)
 
 
 if __name__ == "__main__":
-    run()
+    import sys
+    run_general() if "general" in sys.argv else run()
