@@ -14,7 +14,7 @@
 extern "C" {
 #endif
 
-#define PBHC_ABI_VERSION 3
+#define PBHC_ABI_VERSION 4
 #define PBHC_OK 0
 #define PBHC_E_BADARG (-1)
 #define PBHC_E_ALIGN (-2)
@@ -120,8 +120,9 @@ int pbhc_clip_prepare(const float* pos, const float* quat, const float* pose_aa,
 
 /* ---- K3: fused motion-tracking env step (lookup + diffs + termination + rewards + reset + observations +
  * history), i.e. everything LeggedRobotBase._post_physics_step does between refresh_sim_tensors and
- * extras["to_log"] for LeggedRobotMotionTracking (envs/legged_base_task/legged_robot_base.py:297-338,
- * envs/motion_tracking/motion_tracking.py:330-358, 548-747, 1030-1328; utils/helpers.py:128-152;
+ * extras["to_log"] for LeggedRobotMotionTracking or LeggedRobotGeneralTracking (envs/legged_base_task/legged_robot_base.py:297-338,
+ * envs/motion_tracking/motion_tracking.py:330-358, 548-747, 1030-1328; envs/motion_tracking/general_tracking.py:
+ * 226-262, 500-805, 1116-1270; utils/helpers.py:128-152;
  * envs/env_utils/history_handler.py:33-48).  One launch per step, no host synchronisation: scalars the
  * reference keeps on the host (adaptive sigmas, curricula, average episode length) live in `scalars`
  * (device doubles) and are advanced by pbhc_track_finalize from per-step reductions. */
@@ -132,38 +133,49 @@ int pbhc_clip_prepare(const float* pos, const float* quat, const float* pose_aa,
 #define PBHC_MAX_OBS_GROUPS 4
 #define PBHC_MAX_HIST_KEYS 8
 #define PBHC_MAX_HIST_DST 16
-#define PBHC_NUM_OBS_SRC 20
-#define PBHC_NUM_SIGMA 10
+#define PBHC_NUM_OBS_SRC 35  /* 20 shared + 15 of LeggedRobotGeneralTracking, enum order of pbhc_b200/spec.py OBS_SRC */
+#define PBHC_NUM_SIGMA 17   /* 10 + 7 of general_tracking, enum order of SIGMA_IDS */
+#define PBHC_MAX_KEY 16     /* key bodies (general_tracking) */
+#define PBHC_MAX_FUTURE 32  /* future reference steps (general_tracking) */
 #define PBHC_ENVF_STRIDE 8   /* env_f32 row: start_time, motion_len, air_time[2], last_contact[2], end_time_ratio, pad */
 
 /* layout of `scalars` (device double[PBHC_SCALARS]) */
-#define PBHC_S_SIGMA 0        /* [10] reward_tracking_sigma, enum order of pbhc_b200/spec.py SIGMA_IDS */
-#define PBHC_S_EMA 10         /* [10] _reward_error_ema */
-#define PBHC_S_AVG_EPL 20     /* average_episode_length (an fp32 value) */
-#define PBHC_S_PENALTY 21     /* reward_penalty_scale */
-#define PBHC_S_FAR_THR 22     /* terminate_when_motion_far_threshold */
-#define PBHC_S_SOFT_DOF_POS 23
-#define PBHC_S_SOFT_DOF_VEL 24
-#define PBHC_S_SOFT_TORQUE 25
-#define PBHC_S_PUSH_COUNT 26  /* history pushes so far (ring-buffer head = -count mod H) */
-#define PBHC_S_LOG 32         /* [48] log_dict values of the last step, see PBHC_L_* */
-#define PBHC_SCALARS 96
+#define PBHC_S_SIGMA 0        /* [17] reward_tracking_sigma, enum order of pbhc_b200/spec.py SIGMA_IDS */
+#define PBHC_S_EMA 17         /* [17] _reward_error_ema */
+#define PBHC_S_AVG_EPL 34     /* average_episode_length (an fp32 value) */
+#define PBHC_S_PENALTY 35     /* reward_penalty_scale */
+#define PBHC_S_FAR_THR 36     /* terminate_when_motion_far_threshold */
+#define PBHC_S_SOFT_DOF_POS 37
+#define PBHC_S_SOFT_DOF_VEL 38
+#define PBHC_S_SOFT_TORQUE 39
+#define PBHC_S_PUSH_COUNT 40  /* history pushes so far (ring-buffer head = -count mod H) */
+#define PBHC_S_LOG 48         /* [64] log_dict values of the last step, see PBHC_L_* */
+#define PBHC_SCALARS 112
 /* layout of `acc` (device double[PBHC_ACC]): per-step sums over envs; all-reduce across ranks before finalize */
-#define PBHC_A_SIGMA_ERR 0    /* [10] sum over envs of each adaptive-sigma error term */
-#define PBHC_A_UPPER_NORM 10  /* sum of |dif_pos| over upper bodies and envs (then lower, vr3, joint) */
-#define PBHC_A_LOWER_NORM 11
-#define PBHC_A_VR3_NORM 12
-#define PBHC_A_JOINT_NORM 13
-#define PBHC_A_TERM_GRAVITY 14
-#define PBHC_A_TERM_FAR 15
-#define PBHC_A_TERM_TIMEOUT 16
-#define PBHC_A_TERM_MOTION_END 17
-#define PBHC_A_RESET 18       /* number of envs reset this step */
-#define PBHC_A_RESET_EPLEN 19 /* sum of their episode lengths */
-#define PBHC_A_ETR_SUM 20     /* sum / sum of squares of end_time_ratio_buf over all envs */
-#define PBHC_A_ETR_SQ 21
-#define PBHC_A_NUM_ENVS 22
-#define PBHC_ACC 32
+#define PBHC_A_SIGMA_ERR 0    /* [17] sum over envs of each adaptive-sigma error term */
+#define PBHC_A_UPPER_NORM 17  /* sum of |dif_pos| over upper bodies and envs (then lower, vr3, joint) */
+#define PBHC_A_LOWER_NORM 18
+#define PBHC_A_VR3_NORM 19
+#define PBHC_A_JOINT_NORM 20
+#define PBHC_A_TERM_GRAVITY 21
+#define PBHC_A_TERM_FAR 22
+#define PBHC_A_TERM_TIMEOUT 23
+#define PBHC_A_TERM_MOTION_END 24
+#define PBHC_A_RESET 25       /* number of envs reset this step */
+#define PBHC_A_RESET_EPLEN 26 /* sum of their episode lengths */
+#define PBHC_A_ETR_SUM 27     /* sum / sum of squares of end_time_ratio_buf over all envs */
+#define PBHC_A_ETR_SQ 28
+#define PBHC_A_NUM_ENVS 29
+/* general_tracking only (general_tracking.py:241-255, 303-335) */
+#define PBHC_A_KEY_NORM 32        /* sum of |dif_pos| over key bodies */
+#define PBHC_A_LOCAL_UPPER_NORM 33 /* sums of |dif_local_body_pos| over upper / lower / vr3 / key bodies */
+#define PBHC_A_LOCAL_LOWER_NORM 34
+#define PBHC_A_LOCAL_VR3_NORM 35
+#define PBHC_A_LOCAL_KEY_NORM 36
+#define PBHC_A_TERM_REF_POS_Z 37
+#define PBHC_A_TERM_REF_ORI 38
+#define PBHC_A_TERM_BODY_Z 39
+#define PBHC_ACC 64
 #define PBHC_L_UPPER 0
 #define PBHC_L_LOWER 1
 #define PBHC_L_VR3 2
@@ -180,8 +192,16 @@ int pbhc_clip_prepare(const float* pos, const float* quat, const float* pose_aa,
 #define PBHC_L_SOFT_DOF_POS 13
 #define PBHC_L_SOFT_DOF_VEL 14
 #define PBHC_L_SOFT_TORQUE 15
-#define PBHC_L_ADP_SIGMA 16    /* [10] sigma / [10] ema as logged by _log_motion_tracking_info: BEFORE this step's update */
-#define PBHC_L_ERROR_EMA 26
+#define PBHC_L_ADP_SIGMA 16    /* [17] sigma / [17] ema as logged by _log_motion_tracking_info: BEFORE this step's update */
+#define PBHC_L_ERROR_EMA 33
+#define PBHC_L_KEY 50          /* general_tracking logs */
+#define PBHC_L_LOCAL_UPPER 51
+#define PBHC_L_LOCAL_LOWER 52
+#define PBHC_L_LOCAL_VR3 53
+#define PBHC_L_LOCAL_KEY 54
+#define PBHC_L_TERM_REF_POS_Z 55
+#define PBHC_L_TERM_REF_ORI 56
+#define PBHC_L_TERM_BODY_Z 57
 
 typedef struct { int32_t enable; double lo, hi, degree, down, up; } PbhcCurriculum;
 /* history key `key` (index into hist_src) appears in obs group `group` at `offset`, newest `len` slots, scaled by mul */
@@ -232,9 +252,19 @@ typedef struct {
   float kp_lo, kp_hi, kd_lo, kd_hi, rfi_lo, rfi_hi, rao_lim;
   uint64_t seed;
   float reset_noise[6];   /* dof_pos, dof_vel, root_pos, root_rot [rad], root_vel, root_ang_vel; 0 = reference default */
-  uint32_t src_used_mask; /* bit k: observation source k is referenced by a group or a history key */
+  uint64_t src_used_mask; /* bit k: observation source k is referenced by a group or a history key */
   int32_t n_upper, n_lower, n_vr3; /* popcounts of the masks (log means) */
   int32_t n_episode_sums; /* n_rewards (+1 with termination): row width of episode_sums */
+  /* LeggedRobotGeneralTracking (envs/motion_tracking/general_tracking.py); general = 0: LeggedRobotMotionTracking */
+  int32_t general;
+  int32_t anchor_index;              /* general_tracking.py:97-98; must be a simulator body (< Jb) */
+  int32_t n_key;                     /* key bodies, in config order (observation layout follows it) */
+  int32_t key_ids[PBHC_MAX_KEY];
+  uint64_t key_mask, body_z_mask;    /* body_z: the hard-coded bodies of :253 */
+  int32_t term_ref_pos_z, term_ref_ori, term_body_z;  /* :241-255 */
+  float term_ref_pos_z_thr, term_ref_ori_thr, term_body_z_thr;
+  int32_t n_future;                  /* obs.future_num_steps; future_steps = linspace(1, future_max_steps, n).long() (:501-507) */
+  int32_t future_steps[PBHC_MAX_FUTURE];
 } PbhcTrackCfg;
 
 typedef struct {
@@ -252,6 +282,7 @@ typedef struct {
   const float* base_com_bias;   /* [N,3] */
   const float* link_mass_scale; /* [N,L] */
   const float* friction;        /* [N] */
+  const float* base_mass_scale; /* [N] simulator._base_mass_scale (general_tracking privileged obs), nullable */
   /* persistent env state */
   int64_t* episode_length_buf;  /* [N] */
   float* env_f32;               /* [N,PBHC_ENVF_STRIDE] */

@@ -9,7 +9,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("PBHC_B200_LIB") or os.path.join(_HERE, "libpbhc_b200.so")  # override: development A/B builds
 
 c_f32p = C.c_void_p
-ABI_VERSION = 3
+ABI_VERSION = 4
 MAX_JOINTS = 40
 
 
@@ -104,14 +104,18 @@ def stream_ptr(device=None):
 
 # ---- K3 structs (mirror include/pbhc_b200.h exactly) ------------------------------------------------
 MAX_DOF, MAX_REWARDS, MAX_EXT, MAX_FEET, MAX_OBS_GROUPS, MAX_HIST_KEYS, MAX_HIST_DST = 32, 32, 4, 4, 4, 8, 16
-NUM_OBS_SRC, NUM_SIGMA, ENVF_STRIDE, SCALARS, ACC = 20, 10, 8, 96, 32
-L_ADP_SIGMA, L_ERROR_EMA = 16, 26
-S_SIGMA, S_EMA, S_AVG_EPL, S_PENALTY, S_FAR_THR, S_SOFT_DOF_POS, S_SOFT_DOF_VEL, S_SOFT_TORQUE, S_PUSH_COUNT, S_LOG = 0, 10, 20, 21, 22, 23, 24, 25, 26, 32
+NUM_OBS_SRC, NUM_SIGMA, ENVF_STRIDE, SCALARS, ACC, MAX_KEY, MAX_FUTURE = 35, 17, 8, 112, 64, 16, 32
+L_ADP_SIGMA, L_ERROR_EMA = 16, 33
+S_SIGMA, S_EMA, S_AVG_EPL, S_PENALTY, S_FAR_THR, S_SOFT_DOF_POS, S_SOFT_DOF_VEL, S_SOFT_TORQUE, S_PUSH_COUNT, S_LOG = 0, 17, 34, 35, 36, 37, 38, 39, 40, 48
 LOG_NAMES = ["upper_body_diff_norm", "lower_body_diff_norm", "vr_3point_diff_norm", "joint_pos_diff_norm",
              "terminate_by_gravity", "terminate_by_motion_far", "terminate_by_time_out", "terminate_by_motion_end",
              "end_time_ratio", "end_time_ratio_std", "terminate_when_motion_far_threshold", "penalty_scale",
              "average_episode_length", "soft_dof_pos_curriculum_value", "soft_dof_vel_curriculum_value",
              "soft_torque_curriculum_value"]
+# general_tracking logs: name -> PBHC_L_* index
+LOG_NAMES_GENERAL = {"key_body_diff_norm": 50, "local_upper_body_diff_norm": 51, "local_lower_body_diff_norm": 52,
+                     "local_vr_3point_diff_norm": 53, "local_key_body_diff_norm": 54, "terminate_by_ref_pos_z": 55,
+                     "terminate_by_ref_ori": 56, "terminate_by_body_z": 57}
 
 
 class Curriculum(C.Structure):
@@ -150,13 +154,19 @@ class TrackCfg(C.Structure):
         ("delay_lo", C.c_int32), ("delay_hi", C.c_int32),
         ("kp_lo", C.c_float), ("kp_hi", C.c_float), ("kd_lo", C.c_float), ("kd_hi", C.c_float), ("rfi_lo", C.c_float), ("rfi_hi", C.c_float),
         ("rao_lim", C.c_float),
-        ("seed", C.c_uint64), ("reset_noise", C.c_float * 6), ("src_used_mask", C.c_uint32),
-        ("n_upper", C.c_int32), ("n_lower", C.c_int32), ("n_vr3", C.c_int32), ("n_episode_sums", C.c_int32)]
+        ("seed", C.c_uint64), ("reset_noise", C.c_float * 6), ("src_used_mask", C.c_uint64),
+        ("n_upper", C.c_int32), ("n_lower", C.c_int32), ("n_vr3", C.c_int32), ("n_episode_sums", C.c_int32),
+        ("general", C.c_int32), ("anchor_index", C.c_int32), ("n_key", C.c_int32), ("key_ids", C.c_int32 * MAX_KEY),
+        ("key_mask", C.c_uint64), ("body_z_mask", C.c_uint64),
+        ("term_ref_pos_z", C.c_int32), ("term_ref_ori", C.c_int32), ("term_body_z", C.c_int32),
+        ("term_ref_pos_z_thr", C.c_float), ("term_ref_ori_thr", C.c_float), ("term_body_z_thr", C.c_float),
+        ("n_future", C.c_int32), ("future_steps", C.c_int32 * MAX_FUTURE)]
 
 
 TRACK_IO_FIELDS = [
     "body_state", "body_env_stride", "root_state", "dof_state", "contact_forces", "actions", "torques", "env_origins",
     "motion_ids", "clip_of_motion", "default_dof_pos", "default_dof_stride", "base_com_bias", "link_mass_scale", "friction",
+    "base_mass_scale",
     "episode_length_buf", "env_f32", "last_actions", "last_dof_pos", "last_dof_vel", "kp_scale", "kd_scale",
     "rfi_lim_scale", "rao_scale", "action_delay_idx", "hist", "episode_sums", "scalars"]
 

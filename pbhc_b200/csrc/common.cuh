@@ -70,4 +70,43 @@ __device__ __forceinline__ V3 quat_rotate_impl(Q4 q, V3 v, bool inverse) {
 __device__ __forceinline__ V3 quat_rotate(Q4 q, V3 v) { return quat_rotate_impl(q, v, false); }
 __device__ __forceinline__ V3 quat_rotate_inverse(Q4 q, V3 v) { return quat_rotate_impl(q, v, true); }
 
+// ---- helpers of LeggedRobotGeneralTracking (utils/torch_utils.py, isaac_utils/rotations.py) ----
+// quat_apply (torch_utils.py:51-58): b + w*t + xyz x t with t = 2 (xyz x b)
+__device__ __forceinline__ V3 quat_apply(Q4 a, V3 b) {
+  const V3 t = {(a.y * b.z - a.z * b.y) * 2.0f, (a.z * b.x - a.x * b.z) * 2.0f, (a.x * b.y - a.y * b.x) * 2.0f};
+  const V3 u = {a.y * t.z - a.z * t.y, a.z * t.x - a.x * t.z, a.x * t.y - a.y * t.x};
+  return {(b.x + a.w * t.x) + u.x, (b.y + a.w * t.y) + u.y, (b.z + a.w * t.z) + u.z};
+}
+// yaw_quat (torch_utils.py:239-270, w_last): (0, 0, sin(yaw/2), cos(yaw/2)) renormalised like maths.normalize
+__device__ __forceinline__ Q4 yaw_quat(Q4 q) {
+  const float yaw = atan2f(2.0f * (q.w * q.z + q.x * q.y), 1.0f - 2.0f * (q.y * q.y + q.z * q.z));
+  const float s = sinf(yaw / 2.0f), c = cosf(yaw / 2.0f);
+  const float n = fmaxf(norm4(0.0f, 0.0f, s, c), 1e-9f);
+  return {0.0f / n, 0.0f / n, s / n, c / n};
+}
+// first two columns of matrix_from_quat (torch_utils.py:274-297, w_last), row-major: m00 m01 m10 m11 m20 m21
+__device__ __forceinline__ void mat_cols2(Q4 q, float (&o)[6]) {
+  const float i = q.x, j = q.y, k = q.z, r = q.w;
+  const float two_s = 2.0f / (((i * i + j * j) + k * k) + r * r);
+  o[0] = 1.0f - two_s * (j * j + k * k); o[1] = two_s * (i * j - k * r);
+  o[2] = two_s * (i * j + k * r);        o[3] = 1.0f - two_s * (i * i + k * k);
+  o[4] = two_s * (i * k - j * r);        o[5] = two_s * (j * k + i * r);
+}
+// angle of quat_to_angle_axis (rotations.py:185-207): normalize_angle(2 acos(w)), 0 when sqrt(1 - w^2) <= 1e-5 (or NaN)
+__device__ __forceinline__ float quat_angle(Q4 q) {
+  const float st = sqrtf(1.0f - q.w * q.w);
+  const float a = 2.0f * acosf(q.w);
+  const float an = atan2f(sinf(a), cosf(a));
+  return fabsf(st) > 1e-5f ? an : 0.0f;
+}
+// roll and pitch of get_euler_xyz_in_tensor (rotations.py:368-387; copysign of maths.py:16-19)
+__device__ __forceinline__ void euler_roll_pitch(Q4 q, float& roll, float& pitch) {
+  const float sinr = 2.0f * (q.w * q.x + q.y * q.z);
+  const float cosr = ((q.w * q.w - q.x * q.x) - q.y * q.y) + q.z * q.z;
+  roll = atan2f(sinr, cosr);
+  const float sinp = 2.0f * (q.w * q.y - q.z * q.x);
+  const float sgn = sinp > 0.0f ? 1.0f : (sinp < 0.0f ? -1.0f : 0.0f);
+  pitch = fabsf(sinp) >= 1.0f ? fabsf(1.5707963267948966f) * sgn : asinf(sinp);
+}
+
 }  // namespace pbhc

@@ -27,31 +27,57 @@ namespace pbhc {
 #endif
 constexpr int kTW = F_TW;
 constexpr int kTrackMaxBlocks = 148 * 8;
-constexpr int kPre = 22;                    // per-env values of the pre phase
+constexpr int kPre = 24;                    // per-env values of the pre phase
 constexpr int kChunk = 16;                  // envs per pre phase (lanes used by it)
-constexpr int kRv = 56;                     // per-env scalar table (see enum Rv)
+constexpr int kRv = 72;                     // per-env scalar table (see enum Rv)
+constexpr int kFut = 12;                    // per-future-step values staged by the general_tracking future pass
 constexpr int kMaxHistDstPerKey = 4;
 
 enum ObsSrc { S_BASE_LIN_VEL, S_BASE_ANG_VEL, S_PROJ_GRAV, S_DOF_POS, S_DOF_VEL, S_ACTIONS, S_PHASE, S_DIF_LOCAL,
               S_LOCAL_REF, S_DR_COM, S_DR_MASS, S_DR_KP, S_DR_KD, S_DR_FRICTION, S_DR_DELAY, S_LOCAL_REF_VEL,
-              S_GLOBAL_REF_VEL, S_DIF_JOINT, S_DIF_JOINT_VEL, S_BASE_POS_Z };
+              S_GLOBAL_REF_VEL, S_DIF_JOINT, S_DIF_JOINT_VEL, S_BASE_POS_Z,
+              // LeggedRobotGeneralTracking
+              S_ROLL_PITCH, S_LKEY_POS, S_LKEY_ROT, S_ANCHOR_POS, S_ANCHOR_ROT, S_NEXT_STEP, S_CONTACT_MASK, S_ROOT_HEIGHT,
+              S_DR_BASE_MASS, S_FUT_HEIGHT, S_FUT_RP, S_FUT_LIN, S_FUT_YAW, S_FUT_DOF, S_FUT_KEY };
+static_assert(S_FUT_KEY + 1 == PBHC_NUM_OBS_SRC, "ObsSrc and PBHC_NUM_OBS_SRC disagree");
 enum RewardId { R_CONTACT_MASK, R_MAX_JOINT_POS, R_BODY_POS_EXT, R_VR3, R_FEET_POS, R_BODY_ROT, R_BODY_ANG_VEL,
                 R_BODY_VEL, R_JOINT_POS, R_JOINT_VEL, R_TORQUES, R_ACTION_RATE, R_FEET_AIR_TIME, R_FEET_FORCES,
                 R_STUMBLE, R_SLIPPAGE, R_LIM_DOF_POS, R_LIM_DOF_VEL, R_LIM_TORQUE, R_COLLISION, R_DOF_VEL, R_DOF_ACC,
-                R_FOOT_SLIP, R_ALIVE, R_ORIENTATION, R_CONTACT_MASK_V2 };
-enum SigmaId { G_MAX_JOINT, G_UPPER, G_LOWER, G_VR3, G_FEET, G_ROT, G_VEL, G_ANG_VEL, G_JOINT_POS, G_JOINT_VEL };
-// per-env scalar table `rv`: slots 0..22 are laid out like `acc` (PBHC_A_*), the rest are raw reward values
-enum Rv { V_SIGMA_ERR = 0, V_UP_N = 10, V_LO_N, V_VR_N, V_JOINT_N, V_T_GRAV, V_T_FAR, V_T_OUT, V_T_END, V_RESET, V_RESET_EPLEN,
-          V_ETR, V_ETR_SQ, V_ONE, V_CONTACT = 24, V_CONTACT_V2, V_TQ2, V_DACT2, V_DV2, V_ACC2, V_ORIENT, V_ALIVE, V_AIR, V_FORCE,
-          V_STUMBLE, V_SLIP, V_FSLIP, V_LIM_POS, V_LIM_VEL, V_LIM_TQ, V_COLLIDE, V_ENVF = 44 /* 8 floats */, V_EP = 52 /* int64 */ };
+                R_FOOT_SLIP, R_ALIVE, R_ORIENTATION, R_CONTACT_MASK_V2,
+                R_ROOT_VEL, R_ANCHOR_POS, R_ANCHOR_ROT, R_LKEY_POS, R_LKEY_ROT, R_KEY_VEL, R_KEY_ANG };
+enum SigmaId { G_MAX_JOINT, G_UPPER, G_LOWER, G_VR3, G_FEET, G_ROT, G_VEL, G_ANG_VEL, G_JOINT_POS, G_JOINT_VEL,
+               G_ROOT_VEL, G_ANCHOR_POS, G_ANCHOR_ROT, G_LKEY_POS, G_LKEY_ROT, G_KEY_VEL, G_KEY_ANG };
+static_assert(G_KEY_ANG + 1 == PBHC_NUM_SIGMA, "SigmaId and PBHC_NUM_SIGMA disagree");
+// per-env scalar table `rv`: slots 0..39 are laid out like `acc` (PBHC_A_*), the rest are raw reward values
+enum Rv { V_SIGMA_ERR = 0, V_UP_N = 17, V_LO_N, V_VR_N, V_JOINT_N, V_T_GRAV, V_T_FAR, V_T_OUT, V_T_END, V_RESET, V_RESET_EPLEN,
+          V_ETR, V_ETR_SQ, V_ONE, V_KEY_N = 32, V_LUP_N, V_LLO_N, V_LVR_N, V_LKEY_N, V_T_REFZ, V_T_ORI, V_T_BODYZ,
+          V_CONTACT = 40, V_CONTACT_V2, V_TQ2, V_DACT2, V_DV2, V_ACC2, V_ORIENT, V_ALIVE, V_AIR, V_FORCE,
+          V_STUMBLE, V_SLIP, V_FSLIP, V_LIM_POS, V_LIM_VEL, V_LIM_TQ, V_COLLIDE, V_ENVF = 60 /* 8 floats */, V_EP = 68 /* int64 */ };
+static_assert(V_UP_N == PBHC_A_UPPER_NORM && V_ONE == PBHC_A_NUM_ENVS && V_KEY_N == PBHC_A_KEY_NORM && V_T_BODYZ == PBHC_A_TERM_BODY_Z &&
+              V_RESET_EPLEN == PBHC_A_RESET_EPLEN && V_ETR_SQ == PBHC_A_ETR_SQ, "rv and acc layouts disagree");
+constexpr int kAccLo = PBHC_A_NUM_ENVS + 1;  // slots [0, kAccLo) are accumulated by lane = slot; general_tracking adds [32, 40)
 enum RewardKind { K_RAW, K_EXP, K_EXP2 };
 // pre-phase values (per env)
 enum Pre { P_F0, P_F1, P_BLEND, P_PHASE, P_HZ, P_HW, P_RPX, P_RPY, P_RPZ, P_BLV, P_BAV = P_BLV + 3, P_PG = P_BAV + 3,
-           P_CLIP = P_PG + 3, P_GRAVN, P_ORIENT };
-static_assert(P_ORIENT + 1 <= kPre, "pre table too small");
+           P_CLIP = P_PG + 3, P_GRAVN, P_ORIENT, P_ROLL, P_PITCH };
+static_assert(P_PITCH + 1 <= kPre, "pre table too small");
+// general_tracking: per-future-step values (lane s = step s) staged in the idle simulator-state buffer
+enum Fut { F_F0, F_F1, F_BLEND, F_APX, F_APY, F_APZ, F_AQX, F_AQY, F_AQZ, F_AQW };
+static_assert(F_AQW + 1 <= kFut, "future table too small");
 
-__host__ __device__ inline int src_dim(int k, int D, int J, int L) {
+__host__ __device__ inline int src_dim(int k, int D, int J, int L, int K = 0, int F = 0) {
   switch (k) {
+    case S_ROLL_PITCH: case S_CONTACT_MASK: return 2;
+    case S_LKEY_POS: return 3 * K;
+    case S_LKEY_ROT: return 6 * K;
+    case S_ANCHOR_ROT: return 6;
+    case S_NEXT_STEP: return 7 + D + 3 * K;
+    case S_ROOT_HEIGHT: case S_DR_BASE_MASS: return 1;
+    case S_FUT_HEIGHT: case S_FUT_YAW: return F;
+    case S_FUT_RP: return 2 * F;
+    case S_FUT_LIN: return 3 * F;
+    case S_FUT_DOF: return F * D;
+    case S_FUT_KEY: return F * 3 * K;
     case S_DOF_POS: case S_DOF_VEL: case S_ACTIONS: case S_DR_KP: case S_DR_KD: case S_DIF_JOINT: case S_DIF_JOINT_VEL: return D;
     case S_DIF_LOCAL: case S_LOCAL_REF: case S_LOCAL_REF_VEL: case S_GLOBAL_REF_VEL: return 3 * J;
     case S_DR_MASS: return L;
@@ -77,6 +103,8 @@ struct TrackParams {
   int e_pos, e_vel, e_ang, e_dp, e_dv, e_c;                  // float offsets inside a table record
   int body_vec, cf_vec, hist_vec, obs_vec[PBHC_MAX_OBS_GROUPS];  // widest vector access each row alignment allows
   int dump;                                                  // float offset (in `rows`) of the scratch region absent destinations write to
+  int group_direct[PBHC_MAX_OBS_GROUPS];  // 1: the group holds only future-target sources, written straight to global memory
+  int has_air_time;                      // the feet_air_time reward is active (only then the reference advances feet_air_time)
   int hist_any_mul;                      // some history destination has mul != 1
   int n_hdst_max;                        // max destinations of one history element
 };
@@ -157,27 +185,30 @@ __device__ __forceinline__ V3 quat_rotate_z(float qz, float qw, V3 v) {
 // block-level tables (built once per block from the launch parameters)
 struct BlockTables {
   double scal[PBHC_SCALARS];
-  double acc[kTW][PBHC_ACC];
   float lim_lo[PBHC_MAX_DOF], lim_hi[PBHC_MAX_DOF], lim_vel[PBHC_MAX_DOF], lim_tq[PBHC_MAX_DOF];
   float r_scale[PBHC_MAX_REWARDS], r_pen[PBHC_MAX_REWARDS], r_sigma[PBHC_MAX_REWARDS];
   int r_kind[PBHC_MAX_REWARDS], r_arg[PBHC_MAX_REWARDS];
-  float sum_div[16];                 // divisor applied to the k-th value of the 16-way reduction
-  int sum_slot[16];                  // rv slot of the k-th value
+  float sum_div[32];                 // divisor applied to the k-th value of the 16-way reduction ([16..31]: second reduction of general_tracking)
+  int sum_slot[32];                  // rv slot of the k-th value
+  signed char key_slot[64];          // general_tracking: position of body j in the key-body list (-1: not a key body)
   int sdst[PBHC_NUM_OBS_SRC][8];     // {count, smem row offsets of source k in the obs groups that show it and in the push staging}
   float obs_scale[PBHC_NUM_OBS_SRC], obs_noise[PBHC_NUM_OBS_SRC];
-  uint32_t noise_mask;               // bit k: source k carries observation noise
+  uint64_t noise_mask;               // bit k: source k carries observation noise
   int hist_head_w[PBHC_MAX_HIST_KEYS];
 };
 
 // k-th value of the 16-way reduction
 enum Sum16 { U_UP_SQ, U_LO_SQ, U_VR_SQ, U_FEET_SQ, U_ROT_SQ, U_VEL_SQ, U_ANG_SQ, U_UP_N, U_LO_N, U_VR_N, U_DJA2, U_DJV2, U_TQ2,
              U_DACT2, U_DV2, U_ACC2 };
+// general_tracking: first reduction = body sums (the dof sums U_DJA2.. keep their index in a second reduction)
+enum Sum16G { GU_UP_SQ, GU_LO_SQ, GU_VR_SQ, GU_FEET_SQ, GU_UP_N, GU_LO_N, GU_VR_N, GU_KEY_N, GU_LUP_N, GU_LLO_N, GU_LVR_N, GU_LKEY_N,
+              GU_LKEY_POS, GU_LKEY_ROT, GU_KEY_VEL, GU_KEY_ANG };
+constexpr int V_SPARE = 30;  // rv slot nobody reads
 
 __device__ void build_tables(const TrackParams& P, BlockTables& T, int* hmap, int* pmap) {
   const PbhcTrackCfg& c = P.c;
   const int tid = threadIdx.x, nt = blockDim.x;
   for (int i = tid; i < PBHC_SCALARS; i += nt) T.scal[i] = P.io.scalars[i];
-  for (int i = tid; i < kTW * PBHC_ACC; i += nt) (&T.acc[0][0])[i] = 0.0;
   __syncthreads();
   const uint64_t push_count = (uint64_t)T.scal[PBHC_S_PUSH_COUNT];
   if (tid < c.D) {  // soft limits of this launch (legged_robot_base.py:974-1002); the curriculum values are launch constants
@@ -223,6 +254,13 @@ __device__ void build_tables(const TrackParams& P, BlockTables& T, int* hmap, in
         case R_LIM_DOF_VEL: arg = V_LIM_VEL; break;
         case R_LIM_TORQUE: arg = V_LIM_TQ; break;
         case R_COLLISION: arg = V_COLLIDE; break;
+        case R_ROOT_VEL: kind = K_EXP; arg = G_ROOT_VEL; break;
+        case R_ANCHOR_POS: kind = K_EXP; arg = G_ANCHOR_POS; break;
+        case R_ANCHOR_ROT: kind = K_EXP; arg = G_ANCHOR_ROT; break;
+        case R_LKEY_POS: kind = K_EXP; arg = G_LKEY_POS; break;
+        case R_LKEY_ROT: kind = K_EXP; arg = G_LKEY_ROT; break;
+        case R_KEY_VEL: kind = K_EXP; arg = G_KEY_VEL; break;
+        case R_KEY_ANG: kind = K_EXP; arg = G_KEY_ANG; break;
         default: break;
       }
       if (kind != K_RAW) sig = (float)T.scal[PBHC_S_SIGMA + arg];
@@ -231,32 +269,62 @@ __device__ void build_tables(const TrackParams& P, BlockTables& T, int* hmap, in
     T.r_scale[tid] = tid < c.n_rewards ? c.reward_scale[tid] : 0.0f;
     T.r_pen[tid] = (tid < c.n_rewards && c.reward_is_penalty[tid]) ? (float)T.scal[PBHC_S_PENALTY] : 1.0f;
   }
-  if (tid < 16) {
-    float div = 1.0f; int slot = 0;
-    switch (tid) {
-      case U_UP_SQ: div = (float)c.n_upper; slot = V_SIGMA_ERR + G_UPPER; break;
-      case U_LO_SQ: div = (float)c.n_lower; slot = V_SIGMA_ERR + G_LOWER; break;
-      case U_VR_SQ: div = (float)c.n_vr3; slot = V_SIGMA_ERR + G_VR3; break;
-      case U_FEET_SQ: div = (float)c.n_feet; slot = V_SIGMA_ERR + G_FEET; break;
-      case U_ROT_SQ: div = (float)c.J; slot = V_SIGMA_ERR + G_ROT; break;
-      case U_VEL_SQ: div = (float)c.J; slot = V_SIGMA_ERR + G_VEL; break;
-      case U_ANG_SQ: div = (float)c.J; slot = V_SIGMA_ERR + G_ANG_VEL; break;
-      case U_UP_N: slot = V_UP_N; break;
-      case U_LO_N: slot = V_LO_N; break;
-      case U_VR_N: slot = V_VR_N; break;
-      case U_DJA2: div = (float)c.D; slot = V_SIGMA_ERR + G_JOINT_POS; break;
-      case U_DJV2: div = (float)c.D; slot = V_SIGMA_ERR + G_JOINT_VEL; break;
-      case U_TQ2: slot = V_TQ2; break;
-      case U_DACT2: slot = V_DACT2; break;
-      case U_DV2: slot = V_DV2; break;
-      default: slot = V_ACC2; break;
+  if (tid < 32) {
+    float div = 1.0f; int slot = V_SPARE;
+    const int u = tid & 15;
+    const bool dof_table = c.general ? tid >= 16 : tid < 16;   // where the dof sums are reduced
+    if (dof_table || !c.general) {
+      switch (u) {
+        case U_UP_SQ: if (!c.general) { div = (float)c.n_upper; slot = V_SIGMA_ERR + G_UPPER; } break;
+        case U_LO_SQ: if (!c.general) { div = (float)c.n_lower; slot = V_SIGMA_ERR + G_LOWER; } break;
+        case U_VR_SQ: if (!c.general) { div = (float)c.n_vr3; slot = V_SIGMA_ERR + G_VR3; } break;
+        case U_FEET_SQ: if (!c.general) { div = (float)c.n_feet; slot = V_SIGMA_ERR + G_FEET; } break;
+        case U_ROT_SQ: if (!c.general) { div = (float)c.J; slot = V_SIGMA_ERR + G_ROT; } break;
+        case U_VEL_SQ: if (!c.general) { div = (float)c.J; slot = V_SIGMA_ERR + G_VEL; } break;
+        case U_ANG_SQ: if (!c.general) { div = (float)c.J; slot = V_SIGMA_ERR + G_ANG_VEL; } break;
+        case U_UP_N: if (!c.general) slot = V_UP_N; break;
+        case U_LO_N: if (!c.general) slot = V_LO_N; break;
+        case U_VR_N: if (!c.general) slot = V_VR_N; break;
+        case U_DJA2: div = (float)c.D; slot = V_SIGMA_ERR + G_JOINT_POS; break;
+        case U_DJV2: div = (float)c.D; slot = V_SIGMA_ERR + G_JOINT_VEL; break;
+        case U_TQ2: slot = V_TQ2; break;
+        case U_DACT2: slot = V_DACT2; break;
+        case U_DV2: slot = V_DV2; break;
+        default: slot = V_ACC2; break;
+      }
+      if (!c.general && tid >= 16) { div = 1.0f; slot = V_SPARE; }
+    } else {
+      const float nk = (float)c.n_key;
+      switch (u) {
+        case GU_UP_SQ: div = (float)c.n_upper; slot = V_SIGMA_ERR + G_UPPER; break;
+        case GU_LO_SQ: div = (float)c.n_lower; slot = V_SIGMA_ERR + G_LOWER; break;
+        case GU_VR_SQ: div = (float)c.n_vr3; slot = V_SIGMA_ERR + G_VR3; break;
+        case GU_FEET_SQ: div = (float)c.n_feet; slot = V_SIGMA_ERR + G_FEET; break;
+        case GU_UP_N: slot = V_UP_N; break;
+        case GU_LO_N: slot = V_LO_N; break;
+        case GU_VR_N: slot = V_VR_N; break;
+        case GU_KEY_N: slot = V_KEY_N; break;
+        case GU_LUP_N: slot = V_LUP_N; break;
+        case GU_LLO_N: slot = V_LLO_N; break;
+        case GU_LVR_N: slot = V_LVR_N; break;
+        case GU_LKEY_N: slot = V_LKEY_N; break;
+        case GU_LKEY_POS: div = nk; slot = V_SIGMA_ERR + G_LKEY_POS; break;
+        case GU_LKEY_ROT: div = nk; slot = V_SIGMA_ERR + G_LKEY_ROT; break;
+        case GU_KEY_VEL: div = nk; slot = V_SIGMA_ERR + G_KEY_VEL; break;
+        default: div = nk; slot = V_SIGMA_ERR + G_KEY_ANG; break;
+      }
     }
     T.sum_div[tid] = div; T.sum_slot[tid] = slot;
+  }
+  if (tid < 64) {
+    int ks = -1;
+    for (int i = 0; i < c.n_key; ++i) if (c.key_ids[i] == tid) ks = i;
+    T.key_slot[tid] = (signed char)ks;
   }
 #if F_PUT
   if (tid < PBHC_NUM_OBS_SRC) {  // {count, valid destinations...} of source tid
     int cnt = 0;
-    for (int g = 0; g < c.n_groups; ++g) if (c.src_dst[tid][g] >= 0) T.sdst[tid][++cnt] = P.row_off[g] + c.src_dst[tid][g];
+    for (int g = 0; g < c.n_groups; ++g) if (c.src_dst[tid][g] >= 0 && !P.group_direct[g]) T.sdst[tid][++cnt] = P.row_off[g] + c.src_dst[tid][g];
     for (int h = 0; h < c.n_hist_keys; ++h) if (c.hist_src[h] == tid) { T.sdst[tid][++cnt] = P.row_off[c.n_groups] + P.push_off[h]; break; }
     T.sdst[tid][0] = cnt;
     for (int i = cnt + 1; i < 8; ++i) T.sdst[tid][i] = P.dump;
@@ -265,15 +333,15 @@ __device__ void build_tables(const TrackParams& P, BlockTables& T, int* hmap, in
   for (int i = tid; i < PBHC_NUM_OBS_SRC * 8; i += nt) {
     const int k = i >> 3, g = i & 7;
     int off = P.dump;  // absent destination: the scratch region
-    if (g < PBHC_MAX_OBS_GROUPS) { if (g < c.n_groups && c.src_dst[k][g] >= 0) off = P.row_off[g] + c.src_dst[k][g]; }
+    if (g < PBHC_MAX_OBS_GROUPS) { if (g < c.n_groups && c.src_dst[k][g] >= 0 && !P.group_direct[g]) off = P.row_off[g] + c.src_dst[k][g]; }
     else if (g == PBHC_MAX_OBS_GROUPS) for (int h = 0; h < c.n_hist_keys; ++h) if (c.hist_src[h] == k) off = P.row_off[c.n_groups] + P.push_off[h];
     T.sdst[k][g] = off;
   }
 #endif
   if (tid < PBHC_NUM_OBS_SRC) { T.obs_scale[tid] = c.obs_scale[tid]; T.obs_noise[tid] = c.obs_noise[tid]; }
   if (tid == 0) {
-    uint32_t m = 0;
-    for (int k = 0; k < PBHC_NUM_OBS_SRC; ++k) if (c.obs_noise[k] != 0.0f) m |= 1u << k;
+    uint64_t m = 0;
+    for (int k = 0; k < PBHC_NUM_OBS_SRC; ++k) if (c.obs_noise[k] != 0.0f) m |= 1ull << k;
     T.noise_mask = m;
   }
   // history ring: physical slot of logical slot s of key k is (head_k + s) % len_k, head_k = -push_count mod len_k
@@ -383,12 +451,12 @@ __device__ __noinline__ void emit_noisy(const BlockTables& T, float* rows, int k
 }
 template <bool kNoise>
 __device__ __forceinline__ void emit1(const BlockTables& T, float* rows, int k, int e, float raw, const NoiseKey& nk) {
-  if (kNoise && (T.noise_mask & (1u << k))) emit_noisy(T, rows, k, e, raw, nk);
+  if (kNoise && ((T.noise_mask >> k) & 1ull)) emit_noisy(T, rows, k, e, raw, nk);
   else put1(T.sdst[k], rows, e, raw * T.obs_scale[k]);
 }
 template <bool kNoise>
 __device__ __forceinline__ void emit3(const BlockTables& T, float* rows, int k, int e, float x, float y, float z, const NoiseKey& nk) {
-  if (kNoise && (T.noise_mask & (1u << k))) { emit_noisy(T, rows, k, e, x, nk); emit_noisy(T, rows, k, e + 1, y, nk); emit_noisy(T, rows, k, e + 2, z, nk); }
+  if (kNoise && ((T.noise_mask >> k) & 1ull)) { emit_noisy(T, rows, k, e, x, nk); emit_noisy(T, rows, k, e + 1, y, nk); emit_noisy(T, rows, k, e + 2, z, nk); }
   else { const float sc = T.obs_scale[k]; put3(T.sdst[k], rows, e, x * sc, y * sc, z * sc); }
 }
 
@@ -510,8 +578,8 @@ __host__ __device__ inline int vec_of(int64_t row_floats, const void* base) {
 
 __device__ __forceinline__ int up4(int v) { return (v + 3) & ~3; }
 
-template <bool kNoise>
-__global__ void __launch_bounds__(kTW * 32, F_BPS) track_kernel(const __grid_constant__ TrackParams P) {
+template <bool kNoise, bool kGeneral>
+__global__ void __launch_bounds__(kTW * 32, kGeneral ? 2 : F_BPS) track_kernel(const __grid_constant__ TrackParams P) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   BlockTables& T = *reinterpret_cast<BlockTables*>(smem_raw);
   const PbhcTrackCfg& c = P.c;
@@ -539,7 +607,7 @@ __global__ void __launch_bounds__(kTW * 32, F_BPS) track_kernel(const __grid_con
   const bool ld = lane < D;
   const float lim_lo = ld ? T.lim_lo[lane] : 0.f, lim_hi = ld ? T.lim_hi[lane] : 0.f;
   const float lim_v = ld ? T.lim_vel[lane] : 0.f, lim_t = ld ? T.lim_tq[lane] : 0.f;
-  double acc_reg = 0.0;
+  double acc_reg = 0.0, acc_reg2 = 0.0;  // slot = lane (and lane + 32 for general_tracking)
 
   const int stride = (int)gridDim.x * kTW, n_envs = (int)P.n;  // P.n < 2^31 / kChunk (checked by the launcher): 32-bit env ids
   const int hist_stage = P.hist_stage;
@@ -577,6 +645,11 @@ __global__ void __launch_bounds__(kTW * 32, F_BPS) track_kernel(const __grid_con
         pre[(P_CLIP) * kChunk + lane] = __int_as_float(clip);
         pre[(P_GRAVN) * kChunk + lane] = norm2(pg.x, pg.y);
         pre[(P_ORIENT) * kChunk + lane] = pg.x * pg.x + pg.y * pg.y;
+        if constexpr (kGeneral) {  // self.rpy, legged_robot_base.py:349
+          float roll, pitch;
+          euler_roll_pitch(rq, roll, pitch);
+          pre[(P_ROLL) * kChunk + lane] = roll; pre[(P_PITCH) * kChunk + lane] = pitch;
+        }
       }
     }
     __syncwarp();
@@ -604,11 +677,56 @@ __global__ void __launch_bounds__(kTW * 32, F_BPS) track_kernel(const __grid_con
       // history ring -> its places in the observation rows (HistoryHandler.query, history_handler.py:46-48)
       if (c.hist_row > 0 && !hist_stage) hist_scatter(io.hist + n * c.hist_row, rows, hmap, c, P.n_hdst_max, P.hist_any_mul, hist_vec, lane, false);
       __syncwarp();
+      // ---- general_tracking: anchor quantities (general_tracking.py:738-803), the same values in every lane -----------
+      Q4 g_raq = {0.f, 0.f, 0.f, 1.f}, g_dori = {0.f, 0.f, 0.f, 1.f};  // robot anchor rotation; delta_ori_w
+      V3 g_ap = {0.f, 0.f, 0.f}, g_dpos = {0.f, 0.f, 0.f};              // reference anchor position; delta_pos_w
+      bool t_refz = false, t_ori = false;
+      if constexpr (kGeneral) {
+        const int a = c.anchor_index;
+        const float* bs = sm_body + a * 13;
+        const V3 rap = {bs[0], bs[1], bs[2]};
+        g_raq = {bs[3], bs[4], bs[5], bs[6]};
+        const float4 qa = __ldg(reinterpret_cast<const float4*>(r0) + a), qb = __ldg(reinterpret_cast<const float4*>(r1) + a);
+        const Q4 ar = slerp({qa.x, qa.y, qa.z, qa.w}, {qb.x, qb.y, qb.z, qb.w}, b);
+        g_ap = {(omb * __ldg(r0 + e_pos + 3 * a) + b * __ldg(r1 + e_pos + 3 * a)) + org[0],
+                (omb * __ldg(r0 + e_pos + 3 * a + 1) + b * __ldg(r1 + e_pos + 3 * a + 1)) + org[1],
+                (omb * __ldg(r0 + e_pos + 3 * a + 2) + b * __ldg(r1 + e_pos + 3 * a + 2)) + org[2]};
+        // delta_pos_w aliases robot_anchor_pos_w_repeat in the reference (:752-753): the z overwrite is seen by
+        // _obs_local_body_pos too, so g_dpos stands for both
+        g_dpos = {rap.x, rap.y, g_ap.z};
+        g_dori = yaw_quat(quat_mul(g_raq, quat_conj(ar)));
+        float m6[6];
+        mat_cols2(quat_mul(quat_conj(g_raq), ar), m6);                                     // _obs_anchor_ref_rot (:785-792)
+        const V3 arp = quat_apply(quat_conj(g_raq), {g_ap.x - rap.x, g_ap.y - rap.y, g_ap.z - rap.z});  // _obs_anchor_ref_pos
+        if (lane < 6) {
+          const float mv = lane == 0 ? m6[0] : lane == 1 ? m6[1] : lane == 2 ? m6[2] : lane == 3 ? m6[3] : lane == 4 ? m6[4] : m6[5];
+          emit1<kNoise>(T, rows, S_ANCHOR_ROT, lane, mv, nk);
+          if (lane < 3) emit1<kNoise>(T, rows, S_ANCHOR_POS, lane, lane == 0 ? arp.x : lane == 1 ? arp.y : arp.z, nk);
+        }
+        const V3 dpa = {g_ap.x - rap.x, g_ap.y - rap.y, g_ap.z - rap.z};                   // dif_anchor_body_pos
+        const float ang = quat_angle(quat_mul(ar, quat_conj(g_raq)));                       // dif_global_body_rot[anchor]
+        // dif_root_velocity (:656-657): reference root velocity in the reference root frame minus base_lin_vel
+        const float4 ra0 = __ldg(reinterpret_cast<const float4*>(r0)), rb0 = __ldg(reinterpret_cast<const float4*>(r1));
+        const Q4 rrq = slerp({ra0.x, ra0.y, ra0.z, ra0.w}, {rb0.x, rb0.y, rb0.z, rb0.w}, b);
+        const V3 rrv = {omb * __ldg(r0 + e_vel) + b * __ldg(r1 + e_vel), omb * __ldg(r0 + e_vel + 1) + b * __ldg(r1 + e_vel + 1),
+                        omb * __ldg(r0 + e_vel + 2) + b * __ldg(r1 + e_vel + 2)};
+        const V3 rl = quat_rotate_inverse(rrq, rrv);
+        const V3 drv = {rl.x - pre[(P_BLV + 0) * kChunk + e], rl.y - pre[(P_BLV + 1) * kChunk + e], rl.z - pre[(P_BLV + 2) * kChunk + e]};
+        const float apz = g_ap.z - rap.z;                                                    // dif_anchor_pos_z (:797)
+        const float aori = quat_rotate_inverse(ar, {0.0f, 0.0f, -1.0f}).z - quat_rotate_inverse(g_raq, {0.0f, 0.0f, -1.0f}).z;
+        t_refz = c.term_ref_pos_z && fabsf(apz) > c.term_ref_pos_z_thr;                      // :241-249
+        t_ori = c.term_ref_ori && fabsf(aori) > c.term_ref_ori_thr;
+        if (lane == 0) {
+          rv[V_SIGMA_ERR + G_ANCHOR_POS] = ((dpa.x * dpa.x + dpa.y * dpa.y) + dpa.z * dpa.z) / 3.0f;
+          rv[V_SIGMA_ERR + G_ANCHOR_ROT] = ang * ang;
+          rv[V_SIGMA_ERR + G_ROOT_VEL] = ((drv.x * drv.x + drv.y * drv.y) + drv.z * drv.z) / 3.0f;
+        }
+      }
       // ---- B. bodies: reference (lerp / slerp of the two frames), extended state, differences, heading-frame features
       float sums[16];
 #pragma unroll
       for (int i = 0; i < 16; ++i) sums[i] = 0.0f;
-      int far = 0, n_collide = 0;
+      int far = 0, n_collide = 0, bodyz = 0;
       for (int j0 = 0; j0 < J; j0 += 32) {
         const int j = j0 + lane;
         bool collide = false;
@@ -651,23 +769,52 @@ __global__ void __launch_bounds__(kTW * 32, F_BPS) track_kernel(const __grid_con
           const float m_pos = ((dp.x * dp.x + dp.y * dp.y) + dp.z * dp.z) / 3.0f;
           const float nrm = norm3(dp.x, dp.y, dp.z);
           const uint64_t bit = 1ull << j;
-          if (c.upper_mask & bit) { sums[U_UP_SQ] += m_pos; sums[U_UP_N] += nrm; }
-          if (c.lower_mask & bit) { sums[U_LO_SQ] += m_pos; sums[U_LO_N] += nrm; }
-          if (c.vr3_mask & bit) { sums[U_VR_SQ] += m_pos; sums[U_VR_N] += nrm; }
-          if (feet_mask & bit) sums[U_FEET_SQ] += m_pos;
-          sums[U_ROT_SQ] += (((dq0 * dq0 + dq1 * dq1) + dq2 * dq2) + dq3 * dq3) / 4.0f;
-          sums[U_VEL_SQ] += ((dv.x * dv.x + dv.y * dv.y) + dv.z * dv.z) / 3.0f;
-          sums[U_ANG_SQ] += ((dw.x * dw.x + dw.y * dw.y) + dw.z * dw.z) / 3.0f;
+          if constexpr (!kGeneral) {
+            if (c.upper_mask & bit) { sums[U_UP_SQ] += m_pos; sums[U_UP_N] += nrm; }
+            if (c.lower_mask & bit) { sums[U_LO_SQ] += m_pos; sums[U_LO_N] += nrm; }
+            if (c.vr3_mask & bit) { sums[U_VR_SQ] += m_pos; sums[U_VR_N] += nrm; }
+            if (feet_mask & bit) sums[U_FEET_SQ] += m_pos;
+            sums[U_ROT_SQ] += (((dq0 * dq0 + dq1 * dq1) + dq2 * dq2) + dq3 * dq3) / 4.0f;
+            sums[U_VEL_SQ] += ((dv.x * dv.x + dv.y * dv.y) + dv.z * dv.z) / 3.0f;
+            sums[U_ANG_SQ] += ((dw.x * dw.x + dw.y * dw.y) + dw.z * dw.z) / 3.0f;
+          } else {  // general_tracking.py:760-783, 303-335, 1131-1222
+            const V3 rel = quat_apply(g_dori, {rpz[0] - g_ap.x, rpz[1] - g_ap.y, rpz[2] - g_ap.z});
+            const V3 dl2 = {(g_dpos.x + rel.x) - p.x, (g_dpos.y + rel.y) - p.y, (g_dpos.z + rel.z) - p.z};  // dif_local_body_pos
+            const float nl = norm3(dl2.x, dl2.y, dl2.z);
+            if (c.upper_mask & bit) { sums[GU_UP_SQ] += m_pos; sums[GU_UP_N] += nrm; sums[GU_LUP_N] += nl; }
+            if (c.lower_mask & bit) { sums[GU_LO_SQ] += m_pos; sums[GU_LO_N] += nrm; sums[GU_LLO_N] += nl; }
+            if (c.vr3_mask & bit) { sums[GU_VR_SQ] += m_pos; sums[GU_VR_N] += nrm; sums[GU_LVR_N] += nl; }
+            if (feet_mask & bit) sums[GU_FEET_SQ] += m_pos;
+            if (c.key_mask & bit) {
+              sums[GU_KEY_N] += nrm; sums[GU_LKEY_N] += nl;
+              sums[GU_LKEY_POS] += ((dl2.x * dl2.x + dl2.y * dl2.y) + dl2.z * dl2.z) / 3.0f;
+              const float la = quat_angle(quat_mul(quat_mul(g_dori, rr), quat_conj(q)));  // dif_local_body_rot
+              sums[GU_LKEY_ROT] += la * la;
+              sums[GU_KEY_VEL] += ((dv.x * dv.x + dv.y * dv.y) + dv.z * dv.z) / 3.0f;
+              sums[GU_KEY_ANG] += ((dw.x * dw.x + dw.y * dw.y) + dw.z * dw.z) / 3.0f;
+              const int ks = T.key_slot[j];
+              const V3 lp = quat_apply(quat_conj(g_raq), {p.x - g_dpos.x, p.y - g_dpos.y, p.z - g_dpos.z});  // _obs_local_body_pos
+              emit3<kNoise>(T, rows, S_LKEY_POS, 3 * ks, lp.x, lp.y, lp.z, nk);
+              float m6[6];
+              mat_cols2(quat_mul(quat_conj(g_raq), q), m6);                                  // _obs_local_body_rot
+              emit3<kNoise>(T, rows, S_LKEY_ROT, 6 * ks, m6[0], m6[1], m6[2], nk);
+              emit3<kNoise>(T, rows, S_LKEY_ROT, 6 * ks + 3, m6[3], m6[4], m6[5], nk);
+            }
+            if ((c.body_z_mask & bit) && fabsf(dl2.z) > c.term_body_z_thr) bodyz = 1;        // :251-255
+            (void)dq0; (void)dq1; (void)dq2; (void)dq3;
+          }
           if (nrm > far_thr) far = 1;
           if (j < Jb && (c.penalised_mask & bit)) {
             const float* fc = sm_cf + 3 * j;
             collide = norm3(fc[0], fc[1], fc[2]) > 0.1f;
           }
-          const V3 dl = quat_rotate_z(hz, hw, dp);  // motion_tracking.py:694-697
-          emit3<kNoise>(T, rows, S_DIF_LOCAL, 3 * j, dl.x, dl.y, dl.z, nk);
-          const V3 lr = quat_rotate_z(hz, hw, {rpz[0] - rp.x, rpz[1] - rp.y, rpz[2] - rp.z});  // :705-707
-          emit3<kNoise>(T, rows, S_LOCAL_REF, 3 * j, lr.x, lr.y, lr.z, nk);
-          if (c.src_used_mask & ((1u << S_LOCAL_REF_VEL) | (1u << S_GLOBAL_REF_VEL))) {
+          if (!kGeneral || (c.src_used_mask & ((1ull << S_DIF_LOCAL) | (1ull << S_LOCAL_REF)))) {
+            const V3 dl = quat_rotate_z(hz, hw, dp);  // motion_tracking.py:694-697
+            emit3<kNoise>(T, rows, S_DIF_LOCAL, 3 * j, dl.x, dl.y, dl.z, nk);
+            const V3 lr = quat_rotate_z(hz, hw, {rpz[0] - rp.x, rpz[1] - rp.y, rpz[2] - rp.z});  // :705-707
+            emit3<kNoise>(T, rows, S_LOCAL_REF, 3 * j, lr.x, lr.y, lr.z, nk);
+          }
+          if (c.src_used_mask & ((1ull << S_LOCAL_REF_VEL) | (1ull << S_GLOBAL_REF_VEL))) {
             const V3 lv = quat_rotate_z(hz, hw, {rvv[0], rvv[1], rvv[2]});
             emit3<kNoise>(T, rows, S_LOCAL_REF_VEL, 3 * j, lv.x, lv.y, lv.z, nk);
             emit3<kNoise>(T, rows, S_GLOBAL_REF_VEL, 3 * j, rvv[0], rvv[1], rvv[2], nk);
@@ -690,6 +837,13 @@ __global__ void __launch_bounds__(kTW * 32, F_BPS) track_kernel(const __grid_con
         djv = (omb * __ldg(r0 + e_dv + lane) + b * __ldg(r1 + e_dv + lane)) - dvel;
       }
       const float max_dja = warp_max(fabsf(dja));
+      if constexpr (kGeneral) {  // the body sums take the whole first reduction; the dof sums get their own
+        const float tot = warp_sum16(sums, lane);
+        const int idx = (lane >> 1) & 15;
+        rv[T.sum_slot[idx]] = tot / T.sum_div[idx];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) sums[i] = 0.0f;
+      }
       sums[U_DJA2] = dja * dja; sums[U_DJV2] = djv * djv; sums[U_TQ2] = tq * tq;
       const float dact = lact - act;
       sums[U_DACT2] = dact * dact; sums[U_DV2] = dvel * dvel;
@@ -716,7 +870,7 @@ __global__ void __launch_bounds__(kTW * 32, F_BPS) track_kernel(const __grid_con
       };
       if (ld) {
         emit_dof(dpos, dvel, act, kp, kd, ddef);
-        if (c.src_used_mask & ((1u << S_DIF_JOINT) | (1u << S_DIF_JOINT_VEL))) {
+        if (c.src_used_mask & ((1ull << S_DIF_JOINT) | (1ull << S_DIF_JOINT_VEL))) {
           emit1<kNoise>(T, rows, S_DIF_JOINT, lane, dja, nk);
           emit1<kNoise>(T, rows, S_DIF_JOINT_VEL, lane, djv, nk);
         }
@@ -724,7 +878,7 @@ __global__ void __launch_bounds__(kTW * 32, F_BPS) track_kernel(const __grid_con
       {
         const float tot = warp_sum16(sums, lane);
         const int idx = (lane >> 1) & 15;
-        rv[T.sum_slot[idx]] = tot / T.sum_div[idx];
+        rv[T.sum_slot[(kGeneral ? 16 : 0) + idx]] = tot / T.sum_div[(kGeneral ? 16 : 0) + idx];
         if (idx == U_DJA2) rv[V_JOINT_N] = sqrtf(tot);
       }
       // ---- D. feet (lane = foot): contacts, feet_air_time, contact-force / slip terms -----------------------------
@@ -738,6 +892,7 @@ __global__ void __launch_bounds__(kTW * 32, F_BPS) track_kernel(const __grid_con
       float start = ef0.x, mlen = ef0.y, etr = ef1.z;
       float x_air = 0.f, x_force = 0.f, x_slip = 0.f, x_fslip = 0.f, x_cm = 0.f, contact_f = 0.f, air_f = 0.f;
       bool x_stumble = false;
+      float cm_f = 0.f;  // contacts_filt of this lane's foot (general_tracking observes it)
       if (lane < c.n_feet) {
         const float* fc = sm_cf + 3 * my_foot;
         const float* bs = sm_body + 13 * my_foot;
@@ -746,13 +901,16 @@ __global__ void __launch_bounds__(kTW * 32, F_BPS) track_kernel(const __grid_con
         const float fn = norm3(fc[0], fc[1], fc[2]);
         contact_f = fn > 1.0f ? 1.0f : 0.0f;                                   // legged_robot_base.py:352-353
         const float filt = (contact_f != 0.0f || last_c != 0.0f) ? 1.0f : 0.0f;
+        cm_f = filt;
         if (Cm) x_cm = fabsf(filt - (omb * __ldg(r0 + e_c + lane) + b * __ldg(r1 + e_c + lane)));
         // feet_air_time, motion_tracking.py:1307-1319 (uses last_contacts of the previous step)
         const bool fz = fc[2] > 1.0f || last_c != 0.0f;
-        const float first = (air_f > 0.0f && fz) ? 1.0f : 0.0f;
-        air_f += c.dt;
-        x_air = (air_f - c.desired_feet_air_time) * first;
-        air_f *= fz ? 0.0f : 1.0f;
+        if (P.has_air_time) {
+          const float first = (air_f > 0.0f && fz) ? 1.0f : 0.0f;
+          air_f += c.dt;
+          x_air = (air_f - c.desired_feet_air_time) * first;
+          air_f *= fz ? 0.0f : 1.0f;
+        }
         x_force = fmaxf(fn - c.max_contact_force, 0.0f);                        // :1321-1323
         x_stumble = norm2(fc[0], fc[1]) > 5.0f * fabsf(fc[2]);                  // :1325-1328
         x_slip = norm3(bs[7], bs[8], bs[9]) * (fn > 1.0f ? 1.0f : 0.0f);        // legged_robot_base.py:1004-1010
@@ -763,6 +921,88 @@ __global__ void __launch_bounds__(kTW * 32, F_BPS) track_kernel(const __grid_con
       x_cm += __shfl_xor_sync(0xffffffffu, x_cm, 1);
       const bool stumble = __any_sync(0xffffffffu, x_stumble);
       float air1 = __shfl_sync(0xffffffffu, air_f, 1), contact1 = __shfl_sync(0xffffffffu, contact_f, 1);  // lane 0 packs the state
+      // ---- general_tracking: future reference window (_get_future_motion_targets, general_tracking.py:500-565) ------
+      if constexpr (kGeneral) {
+        if (c.n_future > 0) {
+          // value of observation source k, element el: groups made only of such sources are written straight to global
+          // memory (scaled and clipped here), any other group through its shared-memory row
+          auto emitg = [&](int k, int el, float val) {
+            const float sv = val * T.obs_scale[k];
+            for (int g = 0; g < c.n_groups; ++g) {
+              const int o = c.src_dst[k][g];
+              if (o < 0) continue;
+              if (P.group_direct[g]) io.obs[g][n * c.group_dim[g] + o + el] = fminf(fmaxf(sv, -c.clip_obs), c.clip_obs);
+              else rows[P.row_off[g] + o + el] = sv;
+            }
+          };
+          __syncwarp();  // the simulator-state buffer is idle from here on: it holds the per-step table
+          float* fut = sm_body;
+          const int F = c.n_future, K = c.n_key, a = c.anchor_index;
+          const float t0 = (float)ep * c.dt + start;                 // episode_length_buf * dt + start (:509), no +1
+          if (lane < F) {  // lane = future step: frame pair, root-frame quantities, anchor pose
+            const float ts = (float)c.future_steps[lane] * c.dt + t0;
+            const FrameBlend fb = frame_blend(tab, clip, ts);
+            const float* q0 = tab.records + fb.f0 * tab.rec_stride;
+            const float* q1 = tab.records + fb.f1 * tab.rec_stride;
+            const float bb = fb.blend, ob = 1.0f - bb;
+            const float4 a0 = __ldg(reinterpret_cast<const float4*>(q0)), a1 = __ldg(reinterpret_cast<const float4*>(q1));
+            const Q4 rq = slerp({a0.x, a0.y, a0.z, a0.w}, {a1.x, a1.y, a1.z, a1.w}, bb);
+            const V3 rvl = quat_rotate_inverse(rq, {ob * __ldg(q0 + e_vel) + bb * __ldg(q1 + e_vel), ob * __ldg(q0 + e_vel + 1) + bb * __ldg(q1 + e_vel + 1),
+                                                    ob * __ldg(q0 + e_vel + 2) + bb * __ldg(q1 + e_vel + 2)});
+            const V3 ral = quat_rotate_inverse(rq, {ob * __ldg(q0 + e_ang) + bb * __ldg(q1 + e_ang), ob * __ldg(q0 + e_ang + 1) + bb * __ldg(q1 + e_ang + 1),
+                                                    ob * __ldg(q0 + e_ang + 2) + bb * __ldg(q1 + e_ang + 2)});
+            const float rz = (ob * __ldg(q0 + e_pos + 2) + bb * __ldg(q1 + e_pos + 2)) + org[2];
+            float roll, pitch;
+            euler_roll_pitch(rq, roll, pitch);
+            const float4 b0 = __ldg(reinterpret_cast<const float4*>(q0) + a), b1 = __ldg(reinterpret_cast<const float4*>(q1) + a);
+            const Q4 aq = slerp({b0.x, b0.y, b0.z, b0.w}, {b1.x, b1.y, b1.z, b1.w}, bb);
+            fut[F_F0 * 32 + lane] = __int_as_float((int)fb.f0); fut[F_F1 * 32 + lane] = __int_as_float((int)fb.f1);
+            fut[F_BLEND * 32 + lane] = bb;
+            fut[F_APX * 32 + lane] = (ob * __ldg(q0 + e_pos + 3 * a) + bb * __ldg(q1 + e_pos + 3 * a)) + org[0];
+            fut[F_APY * 32 + lane] = (ob * __ldg(q0 + e_pos + 3 * a + 1) + bb * __ldg(q1 + e_pos + 3 * a + 1)) + org[1];
+            fut[F_APZ * 32 + lane] = (ob * __ldg(q0 + e_pos + 3 * a + 2) + bb * __ldg(q1 + e_pos + 3 * a + 2)) + org[2];
+            fut[F_AQX * 32 + lane] = aq.x; fut[F_AQY * 32 + lane] = aq.y; fut[F_AQZ * 32 + lane] = aq.z; fut[F_AQW * 32 + lane] = aq.w;
+            emitg(S_FUT_HEIGHT, lane, rz);
+            emitg(S_FUT_RP, 2 * lane, roll); emitg(S_FUT_RP, 2 * lane + 1, pitch);
+            emitg(S_FUT_LIN, 3 * lane, rvl.x); emitg(S_FUT_LIN, 3 * lane + 1, rvl.y); emitg(S_FUT_LIN, 3 * lane + 2, rvl.z);
+            emitg(S_FUT_YAW, lane, ral.z);
+            if (lane == 0) {  // obs_next_step_mimic_buf (:553-563): the step-0 slices
+              emit1<kNoise>(T, rows, S_NEXT_STEP, 0, rz, nk); emit1<kNoise>(T, rows, S_NEXT_STEP, 1, roll, nk);
+              emit1<kNoise>(T, rows, S_NEXT_STEP, 2, pitch, nk); emit3<kNoise>(T, rows, S_NEXT_STEP, 3, rvl.x, rvl.y, rvl.z, nk);
+              emit1<kNoise>(T, rows, S_NEXT_STEP, 6, ral.z, nk);
+            }
+          }
+          __syncwarp();
+          for (int s = 0; s < F; ++s) {  // dof_pos of every future step: lane = dof
+            const float* q0 = tab.records + (int64_t)__float_as_int(fut[F_F0 * 32 + s]) * tab.rec_stride;
+            const float* q1 = tab.records + (int64_t)__float_as_int(fut[F_F1 * 32 + s]) * tab.rec_stride;
+            const float bb = fut[F_BLEND * 32 + s], ob = 1.0f - bb;
+            if (ld) {
+              const float v = ob * __ldg(q0 + e_dp + lane) + bb * __ldg(q1 + e_dp + lane);
+              emitg(S_FUT_DOF, s * D + lane, v);
+              if (s == 0) emit1<kNoise>(T, rows, S_NEXT_STEP, 7 + lane, v, nk);
+            }
+          }
+          for (int s0 = 0; s0 < F; s0 += 2) {  // key bodies in the reference anchor frame: two steps per pass, lane = (step, key)
+            const int s = s0 + (lane >> 4), k = lane & 15;
+            if (s < F && k < K) {
+              const int j = c.key_ids[k];
+              const float* q0 = tab.records + (int64_t)__float_as_int(fut[F_F0 * 32 + s]) * tab.rec_stride;
+              const float* q1 = tab.records + (int64_t)__float_as_int(fut[F_F1 * 32 + s]) * tab.rec_stride;
+              const float bb = fut[F_BLEND * 32 + s], ob = 1.0f - bb;
+              const V3 d = {((ob * __ldg(q0 + e_pos + 3 * j) + bb * __ldg(q1 + e_pos + 3 * j)) + org[0]) - fut[F_APX * 32 + s],
+                            ((ob * __ldg(q0 + e_pos + 3 * j + 1) + bb * __ldg(q1 + e_pos + 3 * j + 1)) + org[1]) - fut[F_APY * 32 + s],
+                            ((ob * __ldg(q0 + e_pos + 3 * j + 2) + bb * __ldg(q1 + e_pos + 3 * j + 2)) + org[2]) - fut[F_APZ * 32 + s]};
+              const Q4 aq = {fut[F_AQX * 32 + s], fut[F_AQY * 32 + s], fut[F_AQZ * 32 + s], fut[F_AQW * 32 + s]};
+              const V3 lp = quat_apply(quat_conj(aq), d);
+              const int el = s * 3 * K + 3 * k;
+              emitg(S_FUT_KEY, el, lp.x); emitg(S_FUT_KEY, el + 1, lp.y); emitg(S_FUT_KEY, el + 2, lp.z);
+              if (s == 0) emit3<kNoise>(T, rows, S_NEXT_STEP, 7 + D + 3 * k, lp.x, lp.y, lp.z, nk);
+            }
+          }
+          __syncwarp();
+        }
+      }
       if (hist_stage) {  // the simulator-state buffer is idle from here on: the history ring arrives in it during E-H
         __syncwarp();
         warp_load_async(sm_body, io.hist + n * c.hist_row, c.hist_row, hist_vec, lane);
@@ -773,11 +1013,14 @@ __global__ void __launch_bounds__(kTW * 32, F_BPS) track_kernel(const __grid_con
       const bool t_out = ep > c.max_episode_length;
       const bool t_end = c.term_motion_end && ((float)ep * c.dt + start > mlen);
       const bool time_out = t_out || t_end;
-      const bool reset = t_grav || t_far || time_out;
+      bool t_bodyz = false;
+      if constexpr (kGeneral) t_bodyz = c.term_body_z && __any_sync(0xffffffffu, bodyz);
+      const bool reset = t_grav || t_far || time_out || t_refz || t_ori || t_bodyz;
       if (lane == 0) {
         rv[V_SIGMA_ERR + G_MAX_JOINT] = max_dja;
         rv[V_T_GRAV] = t_grav; rv[V_T_FAR] = t_far; rv[V_T_OUT] = time_out; rv[V_T_END] = t_end;
         rv[V_RESET] = reset; rv[V_ONE] = 1.0f; rv[V_ALIVE] = 1.0f;
+        if constexpr (kGeneral) { rv[V_T_REFZ] = t_refz; rv[V_T_ORI] = t_ori; rv[V_T_BODYZ] = t_bodyz; }
         rv[V_CONTACT] = 1.0f - x_cm / (float)c.n_feet; rv[V_CONTACT_V2] = 0.5f - x_cm / (float)c.n_feet;
         rv[V_ORIENT] = pre[(P_ORIENT) * kChunk + e];
         rv[V_AIR] = x_air; rv[V_FORCE] = x_force; rv[V_STUMBLE] = stumble ? 1.0f : 0.0f; rv[V_SLIP] = x_slip; rv[V_FSLIP] = x_fslip;
@@ -822,6 +1065,7 @@ __global__ void __launch_bounds__(kTW * 32, F_BPS) track_kernel(const __grid_con
       // ---- G. reset (legged_robot_base.py:491-516, 647-686, 587-635; motion_tracking.py:274-296, 369-384, 445-543) ----
       int64_t delay = io.action_delay_idx[n];
       float air0 = air_f, contact0 = contact_f;  // meaningful in lane 0
+      float root_z = rp.z;                       // simulator root height as the observations see it (live view: new value after a reset)
       if (reset) {
         const Rng rng = {make_uint2((uint32_t)c.seed, (uint32_t)(c.seed >> 32)), (uint32_t)(n + io.env_offset), (uint32_t)((uint64_t)(n + io.env_offset) >> 32), push_count};
         if (ld) io.actions[n * D + lane] = 0.0f;
@@ -857,14 +1101,25 @@ __global__ void __launch_bounds__(kTW * 32, F_BPS) track_kernel(const __grid_con
         const float* q0 = tab.records + f2.f0 * tab.rec_stride;
         const float* q1 = tab.records + f2.f1 * tab.rec_stride;
         if (ld) {
-          dpos2 = omb2 * q0[e_dp + lane] + b2 * q1[e_dp + lane];
-          dvel2 = omb2 * q0[e_dv + lane] + b2 * q1[e_dv + lane];
-          if (c.reset_noise[0] != 0.0f) dpos2 = dpos2 + rng.normal(144 + lane) * c.reset_noise[0];
-          if (c.reset_noise[1] != 0.0f) dvel2 = dvel2 + rng.normal(176 + lane) * c.reset_noise[1];
+          if constexpr (kGeneral) {  // general_tracking._reset_dofs (:464-483): motion at episode_length*dt + start (no +1), uniform noise
+            const FrameBlend f3 = frame_blend(tab, clip, (float)ep * c.dt + start);
+            const float b3 = f3.blend, omb3 = 1.0f - b3;
+            const float* p0 = tab.records + f3.f0 * tab.rec_stride;
+            const float* p1 = tab.records + f3.f1 * tab.rec_stride;
+            dpos2 = omb3 * p0[e_dp + lane] + b3 * p1[e_dp + lane];
+            dvel2 = omb3 * p0[e_dv + lane] + b3 * p1[e_dv + lane];
+            if (c.reset_noise[0] != 0.0f) dpos2 = dpos2 + rng.uniform(144 + lane) * c.reset_noise[0];
+            if (c.reset_noise[1] != 0.0f) dvel2 = dvel2 + rng.uniform(176 + lane) * c.reset_noise[1];
+          } else {
+            dpos2 = omb2 * q0[e_dp + lane] + b2 * q1[e_dp + lane];
+            dvel2 = omb2 * q0[e_dv + lane] + b2 * q1[e_dv + lane];
+            if (c.reset_noise[0] != 0.0f) dpos2 = dpos2 + rng.normal(144 + lane) * c.reset_noise[0];
+            if (c.reset_noise[1] != 0.0f) dvel2 = dvel2 + rng.normal(176 + lane) * c.reset_noise[1];
+          }
           reinterpret_cast<float2*>(io.dof_state)[n * D + lane] = make_float2(dpos2, dvel2);
         }
+        float v = 0.0f;
         if (lane < 13) {
-          float v;
           if (lane >= 3 && lane < 7) {
             const float4 a = reinterpret_cast<const float4*>(q0)[0], d4 = reinterpret_cast<const float4*>(q1)[0];
             const Q4 rr = slerp({a.x, a.y, a.z, a.w}, {d4.x, d4.y, d4.z, d4.w}, b2);
@@ -887,6 +1142,7 @@ __global__ void __launch_bounds__(kTW * 32, F_BPS) track_kernel(const __grid_con
           }
           io.root_state[n * 13 + lane] = v;
         }
+        if constexpr (kGeneral) root_z = __shfl_sync(0xffffffffu, v, 2);
         if (ld) emit_dof(dpos2, dvel2, 0.0f, kp2, kd2, io.default_dof_pos[n * io.default_dof_stride + lane]);
       }
       // ---- H. observation features into the rows (legged_robot_base.py:763-793, 1114-1215; motion_tracking.py:944-1015)
@@ -902,6 +1158,18 @@ __global__ void __launch_bounds__(kTW * 32, F_BPS) track_kernel(const __grid_con
         emit1<kNoise>(T, rows, k, ce, val, nk);
       }
       for (int i = lane; i < L; i += 32) emit1<kNoise>(T, rows, S_DR_MASS, i, io.link_mass_scale[n * L + i], nk);
+      if constexpr (kGeneral) {  // getters of general_tracking.py:879-891, legged_robot_base.py:1193
+        const float cmv = __shfl_sync(0xffffffffu, cm_f, (lane - 2) & 31);  // contacts_filt (zeroed by a reset, :664-666)
+        if (lane < 6) {
+          int k, ce = 0;
+          float val;
+          if (lane < 2) { k = S_ROLL_PITCH; ce = lane; val = pre[(P_ROLL + lane) * kChunk + e]; }  // stale for envs that reset
+          else if (lane < 4) { k = S_CONTACT_MASK; ce = lane - 2; val = reset ? 0.0f : cmv; }
+          else if (lane == 4) { k = S_ROOT_HEIGHT; val = root_z; }
+          else { k = S_DR_BASE_MASS; val = io.base_mass_scale ? io.base_mass_scale[n] : 1.0f; }
+          emit1<kNoise>(T, rows, k, ce, val, nk);
+        }
+      }
       if (lane == 0) { rv[V_ETR] = etr; }
       if (hist_stage) {  // history ring -> its places in the rows (zeros are already there for an env that reset)
         cp_async_wait();
@@ -912,6 +1180,7 @@ __global__ void __launch_bounds__(kTW * 32, F_BPS) track_kernel(const __grid_con
       if (n32 + stride < n_envs) fetch_sim_state(n + stride);
       // ---- I. rows -> global (clipped), history push, state write-back -----------------------------------------------
       for (int g = 0; g < c.n_groups; ++g) {
+        if (kGeneral && P.group_direct[g]) continue;
         const int dim = c.group_dim[g];
         warp_store_clipped(io.obs[g] + n * dim, rows + P.row_off[g], dim, P.obs_vec[g], c.clip_obs, lane);
       }
@@ -927,37 +1196,43 @@ __global__ void __launch_bounds__(kTW * 32, F_BPS) track_kernel(const __grid_con
         io.reset_buf[n] = reset ? 1 : 0;
         io.time_out_buf[n] = time_out ? 1 : 0;
       }
-      if (lane < 23) {  // per-lane fp64 accumulation of the cross-env sums (slot = lane, layout PBHC_A_*)
+      if (lane < kAccLo) {  // per-lane fp64 accumulation of the cross-env sums (slot = lane, layout PBHC_A_*)
         double a = (double)rv[lane];
         if (lane == V_RESET_EPLEN) a = reset ? (double)last_ep : 0.0;
         if (lane == V_ETR_SQ) { const double x = (double)rv[V_ETR]; a = x * x; }
         acc_reg += a;
       }
+      if constexpr (kGeneral) if (lane < 8) acc_reg2 += (double)rv[32 + lane];
     }
   }
-  T.acc[warp][lane] = lane < 23 ? acc_reg : 0.0;
+  // block partials: every warp parks its 64 sums in its (now idle) pre-phase buffer, 64 threads add them up in warp order
+  __syncwarp();
+  double* wacc = reinterpret_cast<double*>(pre);
+  wacc[lane] = lane < kAccLo ? acc_reg : 0.0;
+  wacc[32 + lane] = (kGeneral && lane < 8) ? acc_reg2 : 0.0;
   __syncthreads();
   if (threadIdx.x < PBHC_ACC) {
     double v = 0.0;
-    for (int w = 0; w < kTW; ++w) v += T.acc[w][threadIdx.x];
+    for (int w = 0; w < kTW; ++w) v += reinterpret_cast<const double*>(smem_raw + P.o_warp + w * P.warp_bytes + P.ob_pre)[threadIdx.x];
     io.partials[(int64_t)blockIdx.x * PBHC_ACC + threadIdx.x] = v;
   }
 }
 
 // deterministic reduction of the per-block partials: 32 groups of threads take every 32nd block (independent loads in
 // flight instead of one serial chain), then a fixed-order sum over the groups
+constexpr int kReduceGroups = 1024 / PBHC_ACC;
 __global__ void __launch_bounds__(1024) track_reduce_kernel(const double* __restrict__ partials, int n_blocks, double* __restrict__ acc) {
-  __shared__ double part[32][PBHC_ACC + 1];
-  const int a = threadIdx.x & (PBHC_ACC - 1), g = threadIdx.x / PBHC_ACC;  // blockDim = 32 * PBHC_ACC
+  __shared__ double part[kReduceGroups][PBHC_ACC + 1];
+  const int a = threadIdx.x & (PBHC_ACC - 1), g = threadIdx.x / PBHC_ACC;  // blockDim = kReduceGroups * PBHC_ACC
   double v = 0.0;
 #pragma unroll 4
-  for (int b = g; b < n_blocks; b += 32) v += partials[(int64_t)b * PBHC_ACC + a];
+  for (int b = g; b < n_blocks; b += kReduceGroups) v += partials[(int64_t)b * PBHC_ACC + a];
   part[g][a] = v;
   __syncthreads();
   if (g == 0) {
     double t = 0.0;
 #pragma unroll
-    for (int k = 0; k < 32; ++k) t += part[k][a];
+    for (int k = 0; k < kReduceGroups; ++k) t += part[k][a];
     acc[a] = t;
   }
 }
@@ -996,6 +1271,13 @@ __global__ void track_finalize_kernel(const __grid_constant__ PbhcTrackCfg c, co
         case R_BODY_ANG_VEL: active |= 1u << G_ANG_VEL; break;
         case R_JOINT_POS: active |= 1u << G_JOINT_POS; break;
         case R_JOINT_VEL: active |= 1u << G_JOINT_VEL; break;
+        case R_ROOT_VEL: active |= 1u << G_ROOT_VEL; break;
+        case R_ANCHOR_POS: active |= 1u << G_ANCHOR_POS; break;
+        case R_ANCHOR_ROT: active |= 1u << G_ANCHOR_ROT; break;
+        case R_LKEY_POS: active |= 1u << G_LKEY_POS; break;
+        case R_LKEY_ROT: active |= 1u << G_LKEY_ROT; break;
+        case R_KEY_VEL: active |= 1u << G_KEY_VEL; break;
+        case R_KEY_ANG: active |= 1u << G_KEY_ANG; break;
         default: break;
       }
     }
@@ -1006,7 +1288,7 @@ __global__ void track_finalize_kernel(const __grid_constant__ PbhcTrackCfg c, co
       S[PBHC_S_EMA + k] = ema;
       const double sig = S[PBHC_S_SIGMA + k];
       if (c.adaptive_type == 2) S[PBHC_S_SIGMA + k] = fmin(ema * c.adaptive_scale, sig);
-      else if (c.adaptive_type == 1) S[PBHC_S_SIGMA + k] = (fmin(ema, sig) + ema) / 2.0;
+      else if (c.adaptive_type == 1) S[PBHC_S_SIGMA + k] = c.general ? ema : (fmin(ema, sig) + ema) / 2.0;  // general_tracking.py:985
       else S[PBHC_S_SIGMA + k] = fmin(ema, sig);
     }
   }
@@ -1016,6 +1298,16 @@ __global__ void track_finalize_kernel(const __grid_constant__ PbhcTrackCfg c, co
   L[PBHC_L_JOINT] = acc[PBHC_A_JOINT_NORM] / n;
   const double resets = acc[PBHC_A_RESET];
   const float reset_mean = (float)(resets / n) + 1e-15f;
+  if (c.general) {  // general_tracking.py:303-335, 241-255
+    L[PBHC_L_KEY] = acc[PBHC_A_KEY_NORM] / (n * c.n_key);
+    L[PBHC_L_LOCAL_UPPER] = acc[PBHC_A_LOCAL_UPPER_NORM] / (n * c.n_upper);
+    L[PBHC_L_LOCAL_LOWER] = acc[PBHC_A_LOCAL_LOWER_NORM] / (n * c.n_lower);
+    L[PBHC_L_LOCAL_VR3] = acc[PBHC_A_LOCAL_VR3_NORM] / (n * c.n_vr3);
+    L[PBHC_L_LOCAL_KEY] = acc[PBHC_A_LOCAL_KEY_NORM] / (n * c.n_key);
+    L[PBHC_L_TERM_REF_POS_Z] = (double)((float)(acc[PBHC_A_TERM_REF_POS_Z] / n) / reset_mean);
+    L[PBHC_L_TERM_REF_ORI] = (double)((float)(acc[PBHC_A_TERM_REF_ORI] / n) / reset_mean);
+    L[PBHC_L_TERM_BODY_Z] = (double)((float)(acc[PBHC_A_TERM_BODY_Z] / n) / reset_mean);
+  }
   L[PBHC_L_TERM_GRAVITY] = (double)((float)(acc[PBHC_A_TERM_GRAVITY] / n) / reset_mean);
   L[PBHC_L_TERM_FAR] = (double)((float)(acc[PBHC_A_TERM_FAR] / n) / reset_mean);
   L[PBHC_L_TERM_TIMEOUT] = (double)((float)(acc[PBHC_A_TERM_TIMEOUT] / n) / reset_mean);
@@ -1067,8 +1359,34 @@ extern "C" int pbhc_track_step(const PbhcTrackCfg* cfg, const PbhcTableDesc* tab
       (io->ref_body_rot_extend && ((uintptr_t)io->ref_body_rot_extend & 15))) {
     set_error("pbhc_track_step: records / env_f32 / ref_body_rot_extend must be 16-B, dof_state 8-B aligned"); return PBHC_E_ALIGN;
   }
+  if (c.general) {
+    if (c.anchor_index < 0 || c.anchor_index >= c.Jb || c.n_key < 0 || c.n_key > PBHC_MAX_KEY || c.n_future < 0 || c.n_future > PBHC_MAX_FUTURE) {
+      set_error("pbhc_track_step: general_tracking needs anchor < Jb, <= %d key bodies, <= %d future steps", PBHC_MAX_KEY, PBHC_MAX_FUTURE); return PBHC_E_RANGE;
+    }
+    for (int i = 0; i < c.n_key; ++i) if (c.key_ids[i] < 0 || c.key_ids[i] >= c.J) { set_error("pbhc_track_step: key body %d out of range", i); return PBHC_E_RANGE; }
+    for (int k = S_FUT_HEIGHT; k <= S_FUT_KEY; ++k) if (c.obs_noise[k] != 0.0f) { set_error("pbhc_track_step: noise on future-target observations is not implemented"); return PBHC_E_RANGE; }
+    for (int r = 0; r < c.n_rewards; ++r)
+      if (c.reward_id[r] == R_BODY_ROT || c.reward_id[r] == R_BODY_VEL || c.reward_id[r] == R_BODY_ANG_VEL) {
+        set_error("pbhc_track_step: whole-body rotation / velocity rewards are not implemented for general_tracking"); return PBHC_E_RANGE;
+      }
+  } else {
+    for (int k = S_ROLL_PITCH; k < PBHC_NUM_OBS_SRC; ++k)
+      if ((c.src_used_mask >> k) & 1ull) { set_error("pbhc_track_step: observation source %d exists only in general_tracking", k); return PBHC_E_RANGE; }
+    for (int r = 0; r < c.n_rewards; ++r) if (c.reward_id[r] >= R_ROOT_VEL) { set_error("pbhc_track_step: reward %d exists only in general_tracking", c.reward_id[r]); return PBHC_E_RANGE; }
+  }
   TrackParams P;
   P.c = c; P.tab = *tab; P.io = *io; P.n = n;
+  P.has_air_time = 0;
+  for (int r = 0; r < c.n_rewards; ++r) if (c.reward_id[r] == R_FEET_AIR_TIME) P.has_air_time = 1;
+  // a group made only of future-target sources never passes through shared memory
+  for (int g = 0; g < PBHC_MAX_OBS_GROUPS; ++g) {
+    bool fut = false, other = false;
+    if (c.general && g < c.n_groups) {
+      for (int k = 0; k < PBHC_NUM_OBS_SRC; ++k) if (c.src_dst[k][g] >= 0) (k >= S_FUT_HEIGHT ? fut : other) = true;
+      for (int e = 0; e < c.n_hist_dst; ++e) if (c.hist_dst[e].group == g) other = true;
+    }
+    P.group_direct[g] = (fut && !other) ? 1 : 0;
+  }
   // history layout: global row = keys back to back ([len_k, dim_k] each); push staging = one slot per key
   int hrow = 0, push = 0;
   for (int k = 0; k < PBHC_MAX_HIST_KEYS; ++k) { P.hist_base[k] = hrow; P.push_off[k] = push; if (k < c.n_hist_keys) { hrow += c.hist_len[k] * c.hist_dim[k]; push += c.hist_dim[k]; } }
@@ -1076,13 +1394,13 @@ extern "C" int pbhc_track_step(const PbhcTrackCfg* cfg, const PbhcTableDesc* tab
   P.push_len = push;
   auto up4h = [](int v) { return (v + 3) & ~3; };
   int off = 0;
-  for (int g = 0; g < PBHC_MAX_OBS_GROUPS; ++g) { P.row_off[g] = off; if (g < c.n_groups) off += up4h(c.group_dim[g]); }
+  for (int g = 0; g < PBHC_MAX_OBS_GROUPS; ++g) { P.row_off[g] = off; if (g < c.n_groups && !P.group_direct[g]) off += up4h(c.group_dim[g]); }
   P.row_off[c.n_groups] = off;
   P.rows_len = off + up4h(push);
   // validate the destination tables against the row sizes
   for (int k = 0; k < PBHC_NUM_OBS_SRC; ++k)
     for (int g = 0; g < c.n_groups; ++g)
-      if (c.src_dst[k][g] >= 0 && c.src_dst[k][g] + src_dim(k, c.D, c.J, c.L) > c.group_dim[g]) { set_error("pbhc_track_step: src_dst[%d][%d] out of range", k, g); return PBHC_E_RANGE; }
+      if (c.src_dst[k][g] >= 0 && c.src_dst[k][g] + src_dim(k, c.D, c.J, c.L, c.n_key, c.n_future) > c.group_dim[g]) { set_error("pbhc_track_step: src_dst[%d][%d] out of range", k, g); return PBHC_E_RANGE; }
   int per_key[PBHC_MAX_HIST_KEYS] = {0};
   P.hist_any_mul = 0; P.n_hdst_max = 0;
   for (int e = 0; e < c.n_hist_dst; ++e) {
@@ -1093,7 +1411,7 @@ extern "C" int pbhc_track_step(const PbhcTrackCfg* cfg, const PbhcTableDesc* tab
     if (per_key[h.key] > P.n_hdst_max) P.n_hdst_max = per_key[h.key];
     if (h.mul != 1.0f) P.hist_any_mul = 1;
   }
-  for (int k = 0; k < c.n_hist_keys; ++k) if (c.hist_len[k] <= 0 || c.hist_dim[k] != src_dim(c.hist_src[k], c.D, c.J, c.L)) { set_error("pbhc_track_step: bad history key %d", k); return PBHC_E_BADARG; }
+  for (int k = 0; k < c.n_hist_keys; ++k) if (c.hist_len[k] <= 0 || c.hist_dim[k] != src_dim(c.hist_src[k], c.D, c.J, c.L, c.n_key, c.n_future)) { set_error("pbhc_track_step: bad history key %d", k); return PBHC_E_BADARG; }
   if (n == 0) return PBHC_OK;
   P.dump = P.rows_len;                                   // scratch for absent destinations: one source wide
   const int dump_len = up4h(3 * c.J + 4);
@@ -1123,23 +1441,25 @@ extern "C" int pbhc_track_step(const PbhcTrackCfg* cfg, const PbhcTableDesc* tab
   bool noise = false;
   for (int k = 0; k < PBHC_NUM_OBS_SRC; ++k) noise |= c.obs_noise[k] != 0.0f;
   // two instantiations: the noise-free one (benchmark.yaml, evaluation) carries no Philox code in its observation stores
-  auto kern = noise ? track_kernel<true> : track_kernel<false>;
-  static thread_local size_t configured[2] = {0, 0};
-  static thread_local int per_sm_of[2] = {0, 0};
-  if (shmem > configured[noise] || per_sm_of[noise] == 0) {
+  if (c.general && c.n_future > 0 && kFut * 32 > P.sm_rows) { set_error("pbhc_track_step: future table does not fit the staging buffer"); return PBHC_E_RANGE; }
+  const int variant = (noise ? 1 : 0) + (c.general ? 2 : 0);
+  auto kern = variant == 0 ? track_kernel<false, false> : variant == 1 ? track_kernel<true, false> : variant == 2 ? track_kernel<false, true> : track_kernel<true, true>;
+  static thread_local size_t configured[4] = {0, 0, 0, 0};
+  static thread_local int per_sm_of[4] = {0, 0, 0, 0};
+  if (shmem > configured[variant] || per_sm_of[variant] == 0) {
     if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shmem) != cudaSuccess) return check_launch("pbhc_track_step(attr)");
     (void)cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
-    configured[noise] = shmem;
+    configured[variant] = shmem;
     int per_sm = 0;
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kTW * 32, shmem);
-    per_sm_of[noise] = per_sm < 1 ? 1 : (per_sm > 8 ? 8 : per_sm);
+    per_sm_of[variant] = per_sm < 1 ? 1 : (per_sm > 8 ? 8 : per_sm);
   }
-  g_track_blocks_per_sm = per_sm_of[noise];
+  g_track_blocks_per_sm = per_sm_of[variant];
   int64_t blocks = (n + kTW - 1) / kTW;
   const int64_t cap = 148LL * g_track_blocks_per_sm;
   if (blocks > cap) blocks = cap;
   kern<<<(unsigned)blocks, kTW * 32, shmem, (cudaStream_t)stream>>>(P);
-  track_reduce_kernel<<<1, 32 * PBHC_ACC, 0, (cudaStream_t)stream>>>(io->partials, (int)blocks, io->acc);
+  track_reduce_kernel<<<1, kReduceGroups * PBHC_ACC, 0, (cudaStream_t)stream>>>(io->partials, (int)blocks, io->acc);
   return check_launch("pbhc_track_step");
 }
 

@@ -137,6 +137,11 @@ class TrackSpec:
                 continue
             if name not in REWARD_IDS:
                 raise NotImplementedError(f"reward term '{name}' is not implemented by the B200 tracking step")
+            general_only = REWARD_IDS[name] >= REWARD_IDS["teleop_root_vel"]
+            if general_only and not self.general:
+                raise NotImplementedError(f"reward term '{name}' exists only in general_tracking")
+            if self.general and name in ("teleop_body_rotation_extend", "teleop_body_velocity_extend", "teleop_body_ang_velocity_extend"):
+                raise NotImplementedError(f"reward term '{name}' is not implemented for general_tracking")
             self.reward_names.append(name)
             self.reward_scales.append(scale)
         self.episode_sum_names = [n for n, sc in dict(_get(rw, "reward_scales")).items() if sc != 0]

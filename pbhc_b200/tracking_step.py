@@ -80,7 +80,7 @@ class TrackingStep:
             if name in SIGMA_IDS:
                 init[_lib.S_SIGMA + SIGMA_IDS[name]] = v
                 init[_lib.S_EMA + SIGMA_IDS[name]] = v
-        init[_lib.S_PENALTY] = s.penalty["initial"]
+        init[_lib.S_PENALTY] = s.penalty["initial"] if s.penalty_curriculum else 1.0  # unused (never applied) without the curriculum
         init[_lib.S_FAR_THR] = s.motion_far_threshold0
         init[_lib.S_SOFT_DOF_POS] = s.limit_cur["dof_pos"]["initial"]
         init[_lib.S_SOFT_DOF_VEL] = s.limit_cur["dof_vel"]["initial"]
@@ -121,6 +121,9 @@ class TrackingStep:
         ema = self.scalars[b + _lib.L_ERROR_EMA:b + _lib.L_ERROR_EMA + _lib.NUM_SIGMA].float()
         for name, i in SIGMA_IDS.items():  # logged before the step's update, like _log_motion_tracking_info
             d["adp_sigma_" + name], d["error_ema_" + name] = sig[i], ema[i]
+        if self.spec.general:  # general_tracking.py:303-335, 241-255
+            for name, i in _lib.LOG_NAMES_GENERAL.items():
+                d[name] = self.scalars[b + i].float()
         return d
 
     def reward_tracking_sigma(self):
@@ -221,6 +224,22 @@ class TrackingStep:
         for i, v in enumerate(vals):
             c.reset_noise[i] = v
         c.n_episode_sums = self.n_sums
+        # LeggedRobotGeneralTracking extras (general_tracking.py)
+        c.general = int(s.general)
+        if s.general:
+            if len(s.key_ids) > _lib.MAX_KEY or s.future_num_steps > _lib.MAX_FUTURE:
+                raise NotImplementedError("too many key bodies / future steps for the B200 tracking step")
+            if s.anchor_index >= s.Jb:
+                raise NotImplementedError("the anchor must be a simulator body")
+            c.anchor_index, c.n_key = s.anchor_index, len(s.key_ids)
+            for i, k in enumerate(s.key_ids):
+                c.key_ids[i] = k
+            c.key_mask, c.body_z_mask = _mask(s.key_ids), _mask(s.body_z_ids)
+            c.term_ref_pos_z, c.term_ref_ori, c.term_body_z = int(s.term_ref_pos_z), int(s.term_ref_ori), int(s.term_body_z)
+            c.term_ref_pos_z_thr, c.term_ref_ori_thr, c.term_body_z_thr = s.term_ref_pos_z_thr, s.term_ref_ori_thr, s.term_body_z_thr
+            c.n_future = s.future_num_steps
+            for i, v in enumerate(s.future_steps):
+                c.future_steps[i] = v
         self._cfg = c
 
     # ---- one env step -----------------------------------------------------------------------------------
@@ -243,6 +262,8 @@ class TrackingStep:
         io.base_com_bias = p(sim._base_com_bias, torch.float32)
         io.link_mass_scale = p(sim._link_mass_scale, torch.float32) if s.L else None
         io.friction = p(sim.friction_coeffs, torch.float32)
+        bm = getattr(sim, "_base_mass_scale", None)
+        io.base_mass_scale = p(bm, torch.float32) if bm is not None else None
         io.episode_length_buf, io.env_f32 = p(self.episode_length_buf), p(self.env_f32)
         io.last_actions, io.last_dof_pos, io.last_dof_vel = p(self.last_actions), p(self.last_dof_pos), p(self.last_dof_vel)
         io.kp_scale, io.kd_scale = p(self._kp_scale), p(self._kd_scale)
@@ -294,7 +315,7 @@ class TrackingStep:
         rew = (len(s.reward_names) + 1) * 4 if s.use_vec_reward else 4
         rb = dict(body_state=io.body_env_stride * 4, root_state=52, dof_state=D * 8, contact_forces=Jb * 12, actions=D * 4, torques=D * 4,
                   env_origins=12, motion_ids=8, default_dof_pos=io.default_dof_stride * 4, base_com_bias=12, link_mass_scale=L * 4,
-                  friction=4, episode_length_buf=8, env_f32=_lib.ENVF_STRIDE * 4, last_actions=D * 4, last_dof_pos=D * 4,
+                  friction=4, base_mass_scale=4, episode_length_buf=8, env_f32=_lib.ENVF_STRIDE * 4, last_actions=D * 4, last_dof_pos=D * 4,
                   last_dof_vel=D * 4, kp_scale=D * 4, kd_scale=D * 4, rfi_lim_scale=D * 4, rao_scale=D * 4, action_delay_idx=8,
                   hist=self.hist_row * 4, episode_sums=self.n_sums * 4, rew_buf=rew, reset_buf=8, time_out_buf=1,
                   ref_body_pos_extend=J * 12, ref_body_rot_extend=J * 16, last_episode_sums=self.n_sums * 4,

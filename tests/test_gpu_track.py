@@ -20,14 +20,17 @@ INJECT = ("motion_start_times", "kp_scale", "kd_scale", "rfi_lim_scale", "rao_sc
 NAMES = ["Horse-stance_pose"]
 
 
-def make_step(spec, N, tmp_path, clip_names=NAMES, exact=True):
+def make_step(spec, N, tmp_path, clip_names=None, exact=True):
+    from pbhc_b200.fixtures import CLIPS29
     from pbhc_b200.motion_lib import MotionLibRobot
     from pbhc_b200.tracking_step import TrackingStep
     from tests.test_gpu_parity import _install_exact_table
-    ml = MotionLibRobot(product_cfg("23", str(tmp_path), clip_names), N, DEV)
+    tag = "29" if spec.general else "23"   # config C: G1 29-DoF with the 3-clip library, config A/B: 23-DoF single clip
+    clip_names = clip_names or (list(CLIPS29) if spec.general else NAMES)
+    ml = MotionLibRobot(product_cfg(tag, str(tmp_path), clip_names), N, DEV)
     ml.load_motions(random_sample=False)
     if exact:
-        _install_exact_table(ml, [oracle_clip("23", n) for n in clip_names])
+        _install_exact_table(ml, [oracle_clip(tag, n) for n in clip_names])
     return TrackingStep(spec, ml, N, DEV), ml
 
 
@@ -35,7 +38,7 @@ def make_sim(N, Jb, D, L):
     z = lambda *s: torch.zeros(*s, device=DEV)
     return types.SimpleNamespace(_rigid_body_state=z(N * Jb, 13), all_root_states=z(N, 13), dof_state=z(N * D, 2),
                                  contact_forces=z(N, Jb, 3), _base_com_bias=z(N, 3), _link_mass_scale=z(N, L),
-                                 friction_coeffs=z(N, 1, 1))
+                                 friction_coeffs=z(N, 1, 1), _base_mass_scale=torch.ones(N, 1, device=DEV))
 
 
 def load_state(ts, S, spec):
@@ -77,15 +80,18 @@ def compare_state(ts, G, spec, tag):
         assert_close(v.cpu(), e("epsum_" + name), what=f"{tag} epsum_{name}")
     sc = ts.scalars.cpu().numpy()
     for name, i in SIGMA_IDS.items():
+        if "sigma_" + name not in G:
+            continue
         assert abs(sc[_lib.S_SIGMA + i] - float(G["sigma_" + name])) <= 1e-6 * abs(float(G["sigma_" + name])), (tag, name)
-        assert abs(sc[_lib.S_EMA + i] - float(G["ema_" + name])) <= 1e-6 * abs(float(G["ema_" + name])), (tag, name)
+        if "ema_" + name in G:
+            assert abs(sc[_lib.S_EMA + i] - float(G["ema_" + name])) <= 1e-6 * abs(float(G["ema_" + name])), (tag, name)
     for name, i in (("average_episode_length", _lib.S_AVG_EPL), ("reward_penalty_scale", _lib.S_PENALTY),
                     ("motion_far_threshold", _lib.S_FAR_THR), ("soft_dof_pos", _lib.S_SOFT_DOF_POS),
                     ("soft_dof_vel", _lib.S_SOFT_DOF_VEL), ("soft_torque", _lib.S_SOFT_TORQUE)):
         assert abs(sc[i] - float(G[name])) <= 1e-6 * abs(float(G[name])) + 1e-12, (tag, name, sc[i], float(G[name]))
 
 
-@pytest.mark.parametrize("case", ["mt23_main", "mt23_bench"])
+@pytest.mark.parametrize("case", ["mt23_main", "mt23_bench", "gt29_teacher"])
 def test_track_step_matches_reference_golden(case, tmp_path):
     g = gold(f"ref_env_{case}.npz")
     spec = TrackSpec.from_config(json.loads(str(g["meta_config_json"])))
@@ -97,6 +103,8 @@ def test_track_step_matches_reference_golden(case, tmp_path):
     sim._base_com_bias.copy_(torch.from_numpy(init["base_com_bias"]))
     sim._link_mass_scale.copy_(torch.from_numpy(init["link_mass_scale"]))
     sim.friction_coeffs.copy_(torch.from_numpy(init["friction_coeffs"]))
+    if "base_mass_scale" in init:
+        sim._base_mass_scale.copy_(torch.from_numpy(init["base_mass_scale"]))
     origins = torch.from_numpy(init["env_origins"]).to(DEV)
     mids = torch.from_numpy(init["motion_ids"]).to(DEV)
     for step in range(int(g["meta_n_steps"])):
