@@ -29,7 +29,12 @@ if ROOT not in sys.path:
 
 METRIC = "tracked env-steps/s (motion lookup+FK+reward+obs)"
 UNIT = "env-steps/s"
-WORKLOAD = "G1 23-DoF motion_tracking step (obs=main, rewards=main, clip Horse-stance_pose), synthetic sim state"
+WORKLOADS = {
+    "A": "G1 23-DoF motion_tracking step (obs=main, rewards=main, clip Horse-stance_pose), synthetic sim state",
+    "C": "G1 29-DoF general_tracking step (obs=obs_ppo_teacher, rewards=general_main, 3-clip library, per-env motion ids, "
+         "20-step future window), synthetic sim state",
+}
+WORKLOAD = WORKLOADS["A"]
 
 
 def parse_args():
@@ -45,7 +50,12 @@ def parse_args():
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="CPU baseline time budget")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
-    return ap.parse_args()
+    ap.add_argument("--workload", default="A", choices=["A", "C"],
+                    help="A: BASELINE configs[0..1] (23-DoF motion_tracking, the headline); C: configs[2] (29-DoF general_tracking)")
+    a = ap.parse_args()
+    global WORKLOAD
+    WORKLOAD = WORKLOADS[a.workload]
+    return a
 
 
 def peaks():
@@ -126,7 +136,7 @@ class ClockSampler(threading.Thread):
 # CPU arm: the oracle port of the reference's torch implementation, on the host cores (the one place outside tests/
 # and smoke() that executes oracle/).
 # ---------------------------------------------------------------------------------------------------------------
-def cpu_reference(n_envs, steps, warmup, seconds=None, with_fk=True, seed=0):
+def cpu_reference(n_envs, steps, warmup, seconds=None, with_fk=True, seed=0, workload="A"):
     """Times `steps` env steps (or as many as fit in `seconds`, at least 3) of the CPU oracle on n_envs envs."""
     import torch
     from oracle import pbhc_oracle as O, pbhc_oracle_env as OE
@@ -134,17 +144,19 @@ def cpu_reference(n_envs, steps, warmup, seconds=None, with_fk=True, seed=0):
     from pbhc_b200 import synth
     from pbhc_b200.fixtures import env_config
     from pbhc_b200.spec import TrackSpec
-    from pbhc_b200.workload import CASE, CLIP
+    from pbhc_b200.fixtures import CLIPS29
+    from pbhc_b200.workload import CASE, CASE_C, CLIP
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
-    spec = TrackSpec.from_config(env_config(CASE))
-    tree = oracle_tree("23")
-    tab = O.MotionTable([oracle_clip("23", CLIP)], spec.Jb)
+    spec = TrackSpec.from_config(env_config(CASE_C if workload == "C" else CASE))
+    tag, clips = ("29", list(CLIPS29)) if spec.general else ("23", [CLIP])
+    tree = oracle_tree(tag)
     N, D, Jb, J = n_envs, spec.D, spec.Jb, spec.J
+    tab = O.MotionTable([oracle_clip(tag, c) for c in clips], spec.Jb, motion_to_clip=[i % len(clips) for i in range(N)])
     gen = torch.Generator().manual_seed(seed)
     S = OE.new_state(spec, N)
-    mlen = float(tab.length[0])
-    S["motion_ids"] = torch.zeros(N, dtype=torch.long)
+    S["motion_ids"] = torch.arange(N)
+    mlen = tab.length[S["motion_ids"]]
     S["motion_len"][:] = mlen
     S["motion_start_times"][:] = torch.rand(N, generator=gen) * mlen
     S["episode_length_buf"][:] = torch.randint(0, 50, (N,), generator=gen)
@@ -180,7 +192,7 @@ def run_reference_arm(a):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
-    r = cpu_reference(a.cpu_envs, a.steps, a.warmup, seconds=150.0, with_fk=not a.no_fk)
+    r = cpu_reference(a.cpu_envs, a.steps, a.warmup, seconds=150.0, with_fk=not a.no_fk, workload=a.workload)
     sample = (f"{r['n_envs']} envs per step (a slice of the {a.envs}-env workload), {r['steps']} timed steps after {a.warmup} warm-up; "
               "CPU oracle port of the reference torch path (oracle/pbhc_oracle_env.py, pinned bit-exact to the reference env), "
               f"torch {r['torch']} with {r['cores']} threads")
@@ -213,7 +225,8 @@ def run_b200_arm(a):
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     N, K, W, with_fk = a.envs, a.steps, max(a.warmup, 3), not a.no_fk
-    wl = Workload(N, dev, tempfile.mkdtemp(prefix=f"pbhc_bench_r{rank}_"), seed=1000 + rank)
+    from pbhc_b200.workload import CASE, CASE_C
+    wl = Workload(N, dev, tempfile.mkdtemp(prefix=f"pbhc_bench_r{rank}_"), seed=1000 + rank, case=CASE_C if a.workload == "C" else CASE)
     ts = wl.ts
     sampler = ClockSampler(torch.cuda.current_device() if os.environ.get("CUDA_VISIBLE_DEVICES") is None else local)
     sampler.start()
@@ -306,10 +319,10 @@ def run_b200_arm(a):
         "data": "synthetic",
         "config": {"workload": WORKLOAD, "envs_per_gpu": N, "envs_total": N * world, "fk_in_step": with_fk, "launch": mode,
                    "l2": f"inputs larger than L2 ({bytes_step * N / 1e6:.0f} MB touched per step per GPU vs 126 MB L2)",
-                   "parallelism": f"envs sharded over {world} GPU(s); one all-reduce of 32 doubles per step" if world > 1 else "single GPU",
+                   "parallelism": f"envs sharded over {world} GPU(s); one all-reduce of 64 doubles per step" if world > 1 else "single GPU",
                    "reset_fraction_last_step": resets},
-        "roofline": {"bound": "hbm", "kernel": "track_kernel (pbhc_track_step: fused K1+K3 + 1-block reduction)",
-                     "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": ncu_traffic(),
+        "roofline": {"bound": "hbm", "kernel": "track_kernel (pbhc_track_step: fused K1+K3 + block-partials reduction)",
+                     "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": ncu_traffic() if a.workload == "A" else None,
                      "peak_source": peak_src, "algorithmic_bytes_per_env_step": bytes_step, "kernel_ms": track_ms,
                      "envs_per_launch": N},
         "stages_ms": {"fk": fk_ms if with_fk else None, "track": track_ms, "finalize": fin_ms,
@@ -320,7 +333,7 @@ def run_b200_arm(a):
     if e2e is not None:
         line["e2e"] = e2e
     if not a.no_cpu_baseline:
-        r = cpu_reference(a.cpu_envs, 10 ** 9, 2, seconds=a.cpu_seconds, with_fk=with_fk)
+        r = cpu_reference(a.cpu_envs, 10 ** 9, 2, seconds=a.cpu_seconds, with_fk=with_fk, workload=a.workload)
         line["cpu_baseline"] = {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "port",
                                 "sample": f"{r['n_envs']} envs per step, {r['steps']} steps in ~{a.cpu_seconds:.0f} s, CPU oracle port of the "
                                           f"reference torch path (torch {r['torch']}, {r['cores']} threads), FK {'in' if with_fk else 'not in'} step",
@@ -343,7 +356,7 @@ def _finish(torch, dist, world, graph):
 
 
 def _lib_index(name):
-    return {"A_RESET": 18}[name]  # PBHC_A_RESET, include/pbhc_b200.h
+    return {"A_RESET": 25}[name]  # PBHC_A_RESET, include/pbhc_b200.h
 
 
 def ncu_traffic():

@@ -13,6 +13,7 @@ from .spec import TrackSpec
 
 CLIP = "Horse-stance_pose"
 CASE = "mt23_main"  # obs=motion_tracking/main with the four observation-noise scales set to 0 (= benchmark.yaml's choice)
+CASE_C = "gt29_teacher"  # config C of SURVEY.md 8: general_tracking, G1 29-DoF, obs_ppo_teacher, rewards general_main, 3-clip library
 
 
 def step_bytes(spec, contact_size=2):
@@ -45,11 +46,14 @@ class Workload:
     """Everything one rank needs to run env steps on `device` for `n_envs` environments."""
 
     def __init__(self, n_envs, device, tmpdir, seed=0, case=CASE, clip=CLIP, noise=None):
+        from .fixtures import CLIPS29
         from .motion_lib import MotionLibRobot
         from .tracking_step import TrackingStep
         self.N, self.device = int(n_envs), torch.device(device)
         self.spec = spec = TrackSpec.from_config(env_config(case, noise))
-        self.lib = MotionLibRobot(product_cfg("23", tmpdir, [clip]), self.N, self.device)
+        self.tag = "29" if spec.general else "23"
+        self.clips = list(CLIPS29) if spec.general else [clip]
+        self.lib = MotionLibRobot(product_cfg(self.tag, tmpdir, self.clips), self.N, self.device)
         self.lib.load_motions(random_sample=False)
         self.ts = TrackingStep(spec, self.lib, self.N, self.device, seed=seed)
         self.host = self.make_inputs(seed)
@@ -59,7 +63,7 @@ class Workload:
             _rigid_body_state=h["body_state"].reshape(-1, 13).to(dev), all_root_states=h["root_state"].to(dev),
             dof_state=h["dof_state"].reshape(-1, 2).to(dev), contact_forces=h["contact_forces"].to(dev),
             _base_com_bias=h["base_com_bias"].to(dev), _link_mass_scale=h["link_mass_scale"].to(dev),
-            friction_coeffs=h["friction_coeffs"].to(dev))
+            friction_coeffs=h["friction_coeffs"].to(dev), _base_mass_scale=h["base_mass_scale"].to(dev))
         self.actions, self.torques = h["actions"].to(dev), h["torques"].to(dev)
         self.env_origins, self.motion_ids = h["env_origins"].to(dev), h["motion_ids"].to(dev)
         self.pose_aa, self.trans = h["pose_aa"].to(dev), h["trans"].to(dev)
@@ -71,11 +75,10 @@ class Workload:
         N, spec, dev = self.N, self.spec, self.device
         D, Jb, J = spec.D, spec.Jb, spec.J
         gen = torch.Generator().manual_seed(seed)
-        mlen = float(self.lib._motion_lengths[0])
         h = {}
-        h["motion_ids"] = torch.arange(N, dtype=torch.int64)
-        h["motion_len"] = torch.full((N,), mlen)
-        h["motion_start_times"] = torch.rand(N, generator=gen) * mlen
+        h["motion_ids"] = torch.arange(N, dtype=torch.int64)  # per-env motion ids; load_motions maps id -> clip (id % num clips)
+        h["motion_len"] = self.lib.get_motion_length(h["motion_ids"].to(dev)).cpu()
+        h["motion_start_times"] = torch.rand(N, generator=gen) * h["motion_len"]
         h["episode_length_buf"] = torch.randint(0, 50, (N,), generator=gen)
         side = int(N ** 0.5) + 1  # env origins on a grid, spacing 5 m (base_task.py:136-142)
         idx = torch.arange(N)
@@ -91,6 +94,7 @@ class Workload:
         h["base_com_bias"] = (torch.rand(N, 3, generator=gen) - 0.5) * 0.1
         h["link_mass_scale"] = 0.9 + 0.2 * torch.rand(N, spec.L, generator=gen)
         h["friction_coeffs"] = 0.2 + torch.rand(N, 1, 1, generator=gen)
+        h["base_mass_scale"] = 0.9 + 0.2 * torch.rand(N, 1, generator=gen) if spec.general else torch.ones(N, 1)
         h["kp_scale"] = 0.9 + 0.2 * torch.rand(N, D, generator=gen)
         h["kd_scale"] = 0.9 + 0.2 * torch.rand(N, D, generator=gen)
         h["last_actions"] = synth.synth_actions(N, D, gen)

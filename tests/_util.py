@@ -54,16 +54,16 @@ def install_exact_table(ml, clips):
     ml._records.copy_(rec.to(ml._records.device))
 
 
-def oracle_env_from_workload(wl, clip_tag="23"):
+def oracle_env_from_workload(wl):
     """(tab, S, inp) for oracle.pbhc_oracle_env.step holding the same bits as a pbhc_b200.workload.Workload."""
     from oracle import pbhc_oracle_env as OE
-    from pbhc_b200.workload import CLIP
     spec, h, N = wl.spec, wl.host, wl.N
-    tab = O.MotionTable([oracle_clip(clip_tag, CLIP)], spec.Jb)
+    nc = len(wl.clips)
+    tab = O.MotionTable([oracle_clip(wl.tag, c) for c in wl.clips], spec.Jb, motion_to_clip=[i % nc for i in range(N)])
     S = OE.new_state(spec, N, env_origins=h["env_origins"].clone())
-    S["motion_ids"] = torch.zeros(N, dtype=torch.long)
+    S["motion_ids"] = h["motion_ids"].clone()
     for k in ("motion_len", "motion_start_times", "episode_length_buf", "kp_scale", "kd_scale", "last_actions", "last_dof_vel",
-              "base_com_bias", "link_mass_scale", "friction_coeffs"):
+              "base_com_bias", "link_mass_scale", "friction_coeffs", "base_mass_scale"):
         S[k] = h[k].clone()
     inp = {k: h[k].clone() for k in ("body_state", "root_state", "dof_state", "contact_forces", "actions", "torques")}
     return tab, S, inp
@@ -73,16 +73,15 @@ def check_workload_step_against_oracle(wl, n_steps=2, seed=5):
     """Runs n_steps of the fused GPU step and of the CPU oracle on the same inputs (start times drawn at resets are
     injected into both) and compares observations, rewards, masks and per-env state."""
     from oracle import pbhc_oracle_env as OE
-    from pbhc_b200.workload import CLIP
     spec, ts, N = wl.spec, wl.ts, wl.N
-    install_exact_table(wl.lib, [oracle_clip("23", CLIP)])
+    install_exact_table(wl.lib, [oracle_clip(wl.tag, c) for c in wl.clips])
     tab, S, inp = oracle_env_from_workload(wl)
     gen = torch.Generator().manual_seed(seed)
     dev = wl.device
     for step in range(n_steps):
         D, dr = spec.D, spec.dr
         u = lambda lo, hi: lo + (hi - lo) * torch.rand(N, D, generator=gen)
-        inj_o = {"motion_start_times": torch.rand(N, generator=gen) * float(tab.length[0]),
+        inj_o = {"motion_start_times": torch.rand(N, generator=gen) * tab.length[S["motion_ids"]],
                  "kp_scale": u(*dr["kp_range"]), "kd_scale": u(*dr["kd_range"]), "rfi_lim_scale": u(*dr["rfi_lim_range"]),
                  "rao_scale": u(-dr["rao_lim"], dr["rao_lim"]),
                  "action_delay_idx": torch.randint(dr["ctrl_delay_step_range"][0], dr["ctrl_delay_step_range"][1] + 1, (N,), generator=gen)}
@@ -98,7 +97,13 @@ def check_workload_step_against_oracle(wl, n_steps=2, seed=5):
         assert torch.equal(ts.episode_length_buf.cpu(), S["episode_length_buf"]), tag + " episode_length_buf"
         assert_close(ts.rew_buf.cpu(), S["rew_buf"], what=tag + " rew_buf")
         for name, v in ts.obs_buf_dict.items():
-            assert_close(v.cpu(), obs_o[name], what=f"{tag} obs {name}")
+            # config C at thousands of envs: reference velocities of several m/s (the 29-DoF clips) rotated by a slerp-ed
+            # quaternion - in the future targets, and in base_lin_vel after a reset wrote a slerp-ed root rotation.  CUDA's
+            # and glibc's acosf / sinf differ in the last ulp, which shows as ~1e-7 RELATIVE TO THE VECTOR NORM in components
+            # that happen to be near zero -> the absolute floor is scaled by that norm (observed worst case 1.5e-6).  The
+            # golden-fixture tests against the reference itself keep 1e-6.
+            atol = 4e-6 if spec.general else ATOL
+            assert_close(v.cpu(), obs_o[name], atol=atol, what=f"{tag} obs {name}")
         assert_close(ts.motion_start_times.cpu(), S["motion_start_times"], what=tag + " start times")
         assert_close(wl.sim.dof_state.cpu().view(N, -1, 2), inp["dof_state"], what=tag + " dof_state")
         assert_close(wl.sim.all_root_states.cpu(), inp["root_state"], what=tag + " root_state")

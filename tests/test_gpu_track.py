@@ -145,6 +145,18 @@ def test_workload_step_vs_oracle(n_envs, tmp_path):
         assert n_reset > 0
 
 
+@pytest.mark.parametrize("n_envs", [37, 4096])
+def test_workload_step_vs_oracle_general_tracking(n_envs, tmp_path):
+    """config C (general_tracking, G1 29-DoF, 3-clip library with per-env motion ids and random start times) against the
+    CPU oracle at ragged and training sizes, incl. resets and the 20-step future window."""
+    from pbhc_b200.workload import Workload, CASE_C
+    from tests._util import check_workload_step_against_oracle
+    wl = Workload(n_envs, DEV, str(tmp_path), seed=4, case=CASE_C)
+    n_reset = check_workload_step_against_oracle(wl, n_steps=3)
+    if n_envs >= 4096:
+        assert n_reset > 0
+
+
 def test_host_step_chunked_pipeline_equals_single_launch(tmp_path):
     """HostStep (host buffers, 5 ragged env chunks on 3 streams) gives bit-identical per-env results to one launch;
     in-kernel reset draws are keyed by the global env id, so they do not depend on the chunking either."""
