@@ -191,7 +191,8 @@ struct BlockTables {
   float sum_div[32];                 // divisor applied to the k-th value of the 16-way reduction ([16..31]: second reduction of general_tracking)
   int sum_slot[32];                  // rv slot of the k-th value
   signed char key_slot[64];          // general_tracking: position of body j in the key-body list (-1: not a key body)
-  int sdst[PBHC_NUM_OBS_SRC][8];     // {count, smem row offsets of source k in the obs groups that show it and in the push staging}
+  int f_g[6], f_off[6], f_row[6];    // future-target source i: its direct group (-1: none) and offset there; its smem row offset (-1: none)
+  alignas(16) int sdst[PBHC_NUM_OBS_SRC][8];     // (read as int4) {count, smem row offsets of source k in the obs groups that show it and in the push staging}
   float obs_scale[PBHC_NUM_OBS_SRC], obs_noise[PBHC_NUM_OBS_SRC];
   uint64_t noise_mask;               // bit k: source k carries observation noise
   int hist_head_w[PBHC_MAX_HIST_KEYS];
@@ -315,6 +316,16 @@ __device__ void build_tables(const TrackParams& P, BlockTables& T, int* hmap, in
       }
     }
     T.sum_div[tid] = div; T.sum_slot[tid] = slot;
+  }
+  if (tid < 6) {  // where the future-target sources go (at most one direct group and one shared-memory row each: checked by the launcher)
+    const int k = S_FUT_HEIGHT + tid;
+    int fg = -1, fo = 0, fr = -1;
+    for (int g = 0; g < c.n_groups; ++g) {
+      const int o = c.src_dst[k][g];
+      if (o < 0) continue;
+      if (P.group_direct[g]) { fg = g; fo = o; } else fr = P.row_off[g] + o;
+    }
+    T.f_g[tid] = fg; T.f_off[tid] = fo; T.f_row[tid] = fr;
   }
   if (tid < 64) {
     int ks = -1;
@@ -924,16 +935,21 @@ __global__ void __launch_bounds__(kTW * 32, kGeneral ? 2 : F_BPS) track_kernel(c
       // ---- general_tracking: future reference window (_get_future_motion_targets, general_tracking.py:500-565) ------
       if constexpr (kGeneral) {
         if (c.n_future > 0) {
-          // value of observation source k, element el: groups made only of such sources are written straight to global
-          // memory (scaled and clipped here), any other group through its shared-memory row
-          auto emitg = [&](int k, int el, float val) {
-            const float sv = val * T.obs_scale[k];
-            for (int g = 0; g < c.n_groups; ++g) {
-              const int o = c.src_dst[k][g];
-              if (o < 0) continue;
-              if (P.group_direct[g]) io.obs[g][n * c.group_dim[g] + o + el] = fminf(fmaxf(sv, -c.clip_obs), c.clip_obs);
-              else rows[P.row_off[g] + o + el] = sv;
-            }
+          // destinations of a future-target source: a group made only of such sources is written straight to global memory
+          // (scaled and clipped here), any other group through its shared-memory row
+          struct FDst { float* gp; int row; float sc; };
+          auto fdst = [&](int k) {
+            const int i = k - S_FUT_HEIGHT, g = T.f_g[i];
+            FDst d;
+            d.gp = g >= 0 ? io.obs[g] + n * c.group_dim[g] + T.f_off[i] : nullptr;
+            d.row = T.f_row[i]; d.sc = T.obs_scale[k];
+            return d;
+          };
+          const float clipv = c.clip_obs;
+          auto fput = [&](const FDst& d, int el, float val) {
+            const float sv = val * d.sc;
+            if (d.gp) d.gp[el] = fminf(fmaxf(sv, -clipv), clipv);
+            if (d.row >= 0) rows[d.row + el] = sv;
           };
           __syncwarp();  // the simulator-state buffer is idle from here on: it holds the per-step table
           float* fut = sm_body;
@@ -962,10 +978,10 @@ __global__ void __launch_bounds__(kTW * 32, kGeneral ? 2 : F_BPS) track_kernel(c
             fut[F_APY * 32 + lane] = (ob * __ldg(q0 + e_pos + 3 * a + 1) + bb * __ldg(q1 + e_pos + 3 * a + 1)) + org[1];
             fut[F_APZ * 32 + lane] = (ob * __ldg(q0 + e_pos + 3 * a + 2) + bb * __ldg(q1 + e_pos + 3 * a + 2)) + org[2];
             fut[F_AQX * 32 + lane] = aq.x; fut[F_AQY * 32 + lane] = aq.y; fut[F_AQZ * 32 + lane] = aq.z; fut[F_AQW * 32 + lane] = aq.w;
-            emitg(S_FUT_HEIGHT, lane, rz);
-            emitg(S_FUT_RP, 2 * lane, roll); emitg(S_FUT_RP, 2 * lane + 1, pitch);
-            emitg(S_FUT_LIN, 3 * lane, rvl.x); emitg(S_FUT_LIN, 3 * lane + 1, rvl.y); emitg(S_FUT_LIN, 3 * lane + 2, rvl.z);
-            emitg(S_FUT_YAW, lane, ral.z);
+            fput(fdst(S_FUT_HEIGHT), lane, rz);
+            { const FDst d = fdst(S_FUT_RP); fput(d, 2 * lane, roll); fput(d, 2 * lane + 1, pitch); }
+            { const FDst d = fdst(S_FUT_LIN); fput(d, 3 * lane, rvl.x); fput(d, 3 * lane + 1, rvl.y); fput(d, 3 * lane + 2, rvl.z); }
+            fput(fdst(S_FUT_YAW), lane, ral.z);
             if (lane == 0) {  // obs_next_step_mimic_buf (:553-563): the step-0 slices
               emit1<kNoise>(T, rows, S_NEXT_STEP, 0, rz, nk); emit1<kNoise>(T, rows, S_NEXT_STEP, 1, roll, nk);
               emit1<kNoise>(T, rows, S_NEXT_STEP, 2, pitch, nk); emit3<kNoise>(T, rows, S_NEXT_STEP, 3, rvl.x, rvl.y, rvl.z, nk);
@@ -973,13 +989,14 @@ __global__ void __launch_bounds__(kTW * 32, kGeneral ? 2 : F_BPS) track_kernel(c
             }
           }
           __syncwarp();
+          const FDst d_dof = fdst(S_FUT_DOF), d_key = fdst(S_FUT_KEY);
           for (int s = 0; s < F; ++s) {  // dof_pos of every future step: lane = dof
             const float* q0 = tab.records + (int64_t)__float_as_int(fut[F_F0 * 32 + s]) * tab.rec_stride;
             const float* q1 = tab.records + (int64_t)__float_as_int(fut[F_F1 * 32 + s]) * tab.rec_stride;
             const float bb = fut[F_BLEND * 32 + s], ob = 1.0f - bb;
             if (ld) {
               const float v = ob * __ldg(q0 + e_dp + lane) + bb * __ldg(q1 + e_dp + lane);
-              emitg(S_FUT_DOF, s * D + lane, v);
+              fput(d_dof, s * D + lane, v);
               if (s == 0) emit1<kNoise>(T, rows, S_NEXT_STEP, 7 + lane, v, nk);
             }
           }
@@ -996,7 +1013,7 @@ __global__ void __launch_bounds__(kTW * 32, kGeneral ? 2 : F_BPS) track_kernel(c
               const Q4 aq = {fut[F_AQX * 32 + s], fut[F_AQY * 32 + s], fut[F_AQZ * 32 + s], fut[F_AQW * 32 + s]};
               const V3 lp = quat_apply(quat_conj(aq), d);
               const int el = s * 3 * K + 3 * k;
-              emitg(S_FUT_KEY, el, lp.x); emitg(S_FUT_KEY, el + 1, lp.y); emitg(S_FUT_KEY, el + 2, lp.z);
+              fput(d_key, el, lp.x); fput(d_key, el + 1, lp.y); fput(d_key, el + 2, lp.z);
               if (s == 0) emit3<kNoise>(T, rows, S_NEXT_STEP, 7 + D + 3 * k, lp.x, lp.y, lp.z, nk);
             }
           }
@@ -1387,6 +1404,11 @@ extern "C" int pbhc_track_step(const PbhcTrackCfg* cfg, const PbhcTableDesc* tab
     }
     P.group_direct[g] = (fut && !other) ? 1 : 0;
   }
+  for (int k = S_FUT_HEIGHT; c.general && k <= S_FUT_KEY; ++k) {
+    int nd = 0, nr = 0;
+    for (int g = 0; g < c.n_groups; ++g) if (c.src_dst[k][g] >= 0) (P.group_direct[g] ? nd : nr)++;
+    if (nd > 1 || nr > 1) { set_error("pbhc_track_step: a future-target observation may appear in at most one pure and one mixed group"); return PBHC_E_RANGE; }
+  }
   // history layout: global row = keys back to back ([len_k, dim_k] each); push staging = one slot per key
   int hrow = 0, push = 0;
   for (int k = 0; k < PBHC_MAX_HIST_KEYS; ++k) { P.hist_base[k] = hrow; P.push_off[k] = push; if (k < c.n_hist_keys) { hrow += c.hist_len[k] * c.hist_dim[k]; push += c.hist_dim[k]; } }
@@ -1418,6 +1440,9 @@ extern "C" int pbhc_track_step(const PbhcTrackCfg* cfg, const PbhcTableDesc* tab
   P.sm_body = 0;
   P.sm_cf = up4h(c.Jb * 13);
   P.sm_rows = P.sm_cf + up4h(c.Jb * 3);
+  // general_tracking runs two blocks per SM (register-bound): there is shared memory to spare, so the staging buffer is
+  // widened to also take the (longer) history ring
+  if (c.general && c.hist_row > P.sm_rows && c.hist_row <= 1024) P.sm_rows = up4h(c.hist_row);
   P.sm_rv = P.sm_rows + up4h(P.rows_len) + dump_len;
   P.sm_pre = P.sm_rv + kRv;
   P.sm_per_warp = P.sm_pre + kPre * kChunk;
