@@ -92,11 +92,13 @@ __device__ __forceinline__ void mat_cols2(Q4 q, float (&o)[6]) {
   o[2] = two_s * (i * j + k * r);        o[3] = 1.0f - two_s * (i * i + k * k);
   o[4] = two_s * (i * k - j * r);        o[5] = two_s * (j * k + i * r);
 }
-// angle of quat_to_angle_axis (rotations.py:185-207): normalize_angle(2 acos(w)), 0 when sqrt(1 - w^2) <= 1e-5 (or NaN)
+// angle of quat_to_angle_axis (rotations.py:185-207): normalize_angle(2 acos(w)), 0 when sqrt(1 - w^2) <= 1e-5 (or NaN).
+// normalize_angle is atan2(sin a, cos a) there; for a in [0, 2 pi] that is a, or a - 2 pi above pi, which is what is
+// computed here (agrees to ~1e-7 relative; every caller squares the angle).
 __device__ __forceinline__ float quat_angle(Q4 q) {
   const float st = sqrtf(1.0f - q.w * q.w);
   const float a = 2.0f * acosf(q.w);
-  const float an = atan2f(sinf(a), cosf(a));
+  const float an = a > 3.14159265358979f ? a - 6.28318530717959f : a;
   return fabsf(st) > 1e-5f ? an : 0.0f;
 }
 // roll and pitch of get_euler_xyz_in_tensor (rotations.py:368-387; copysign of maths.py:16-19)

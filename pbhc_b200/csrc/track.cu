@@ -490,19 +490,23 @@ __device__ __forceinline__ void warp_load(float* dst, const float* src, int coun
 
 // Asynchronous global -> shared copies (LDGSTS): the warp queues the next block of input while it computes on the current
 // one, so no lane ever waits on HBM latency for the simulator state or the history ring.
-__device__ __forceinline__ void cp_async16(void* s, const void* g) { asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(s)), "l"(g) : "memory"); }
-__device__ __forceinline__ void cp_async8(void* s, const void* g) { asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"((uint32_t)__cvta_generic_to_shared(s)), "l"(g) : "memory"); }
-__device__ __forceinline__ void cp_async4(void* s, const void* g) { asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((uint32_t)__cvta_generic_to_shared(s)), "l"(g) : "memory"); }
+__device__ __forceinline__ void cp_async16(uint32_t s, const void* g) { asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(s), "l"(g) : "memory"); }
+__device__ __forceinline__ void cp_async8(uint32_t s, const void* g) { asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(s), "l"(g) : "memory"); }
+__device__ __forceinline__ void cp_async4(uint32_t s, const void* g) { asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(s), "l"(g) : "memory"); }
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 __device__ __forceinline__ void warp_load_async(float* dst, const float* src, int count, int vec, int lane) {
+  const uint32_t sd = (uint32_t)__cvta_generic_to_shared(dst);  // one address conversion per copy, byte offsets from there
+  const char* gs = reinterpret_cast<const char*>(src);
   if (vec == 4) {
-    for (int i = lane; i < (count >> 2); i += 32) cp_async16(dst + 4 * i, src + 4 * i);
-    for (int i = (count & ~3) + lane; i < count; i += 32) cp_async4(dst + i, src + i);
+    const int nb = (count >> 2) << 4;
+    for (int o = lane << 4; o < nb; o += 512) cp_async16(sd + o, gs + o);
+    for (int i = (count & ~3) + lane; i < count; i += 32) cp_async4(sd + 4 * i, gs + 4 * i);
   } else if (vec == 2) {
-    for (int i = lane; i < (count >> 1); i += 32) cp_async8(dst + 2 * i, src + 2 * i);
-    if ((count & 1) && lane == 0) cp_async4(dst + count - 1, src + count - 1);
+    const int nb = (count >> 1) << 3;
+    for (int o = lane << 3; o < nb; o += 256) cp_async8(sd + o, gs + o);
+    if ((count & 1) && lane == 0) cp_async4(sd + 4 * (count - 1), gs + 4 * (count - 1));
   } else {
-    for (int i = lane; i < count; i += 32) cp_async4(dst + i, src + i);
+    for (int o = lane << 2; o < 4 * count; o += 128) cp_async4(sd + o, gs + o);
   }
 }
 
@@ -601,11 +605,11 @@ __global__ void __launch_bounds__(kTW * 32, kGeneral ? 2 : F_BPS) track_kernel(c
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int J = c.J, Jb = c.Jb, D = c.D, L = c.L, Cm = tab.contact_size;
   unsigned char* wp = smem_raw + P.o_warp + warp * P.warp_bytes;
-  float* sm_body = reinterpret_cast<float*>(wp + P.ob_body);
+  float* rv = reinterpret_cast<float*>(wp);                       // fixed-size tables first: compile-time offsets from wp
+  float* pre = rv + kRv;
+  float* sm_body = pre + kPre * kChunk;
   float* sm_cf = reinterpret_cast<float*>(wp + P.ob_cf);
   float* rows = reinterpret_cast<float*>(wp + P.ob_rows);
-  float* rv = reinterpret_cast<float*>(wp + P.ob_rv);
-  float* pre = reinterpret_cast<float*>(wp + P.ob_pre);
   build_tables(P, T, hmap, pmap);
 
   const float far_thr = (float)T.scal[PBHC_S_FAR_THR];
@@ -1230,7 +1234,7 @@ __global__ void __launch_bounds__(kTW * 32, kGeneral ? 2 : F_BPS) track_kernel(c
   __syncthreads();
   if (threadIdx.x < PBHC_ACC) {
     double v = 0.0;
-    for (int w = 0; w < kTW; ++w) v += reinterpret_cast<const double*>(smem_raw + P.o_warp + w * P.warp_bytes + P.ob_pre)[threadIdx.x];
+    for (int w = 0; w < kTW; ++w) v += reinterpret_cast<const double*>(smem_raw + P.o_warp + w * P.warp_bytes + kRv * 4)[threadIdx.x];
     io.partials[(int64_t)blockIdx.x * PBHC_ACC + threadIdx.x] = v;
   }
 }
@@ -1437,20 +1441,23 @@ extern "C" int pbhc_track_step(const PbhcTrackCfg* cfg, const PbhcTableDesc* tab
   if (n == 0) return PBHC_OK;
   P.dump = P.rows_len;                                   // scratch for absent destinations: one source wide
   const int dump_len = up4h(3 * c.J + 4);
-  P.sm_body = 0;
-  P.sm_cf = up4h(c.Jb * 13);
-  P.sm_rows = P.sm_cf + up4h(c.Jb * 3);
+  // per-warp layout: the fixed-size tables first, so that the kernel reaches rv / pre / the staging buffer with
+  // compile-time offsets from one base register
+  P.sm_rv = 0;
+  P.sm_pre = kRv;
+  P.sm_body = kRv + kPre * kChunk;
+  P.sm_cf = P.sm_body + up4h(c.Jb * 13);
+  int stage_len = up4h(c.Jb * 13) + up4h(c.Jb * 3);  // staging buffer = body state + contact forces (+ padding)
   // general_tracking runs two blocks per SM (register-bound): there is shared memory to spare, so the staging buffer is
   // widened to also take the (longer) history ring
-  if (c.general && c.hist_row > P.sm_rows && c.hist_row <= 1024) P.sm_rows = up4h(c.hist_row);
-  P.sm_rv = P.sm_rows + up4h(P.rows_len) + dump_len;
-  P.sm_pre = P.sm_rv + kRv;
-  P.sm_per_warp = P.sm_pre + kPre * kChunk;
+  if (c.general && c.hist_row > stage_len && c.hist_row <= 1024) stage_len = up4h(c.hist_row);
+  P.sm_rows = P.sm_body + stage_len;
+  P.sm_per_warp = P.sm_rows + up4h(P.rows_len) + dump_len;
   P.o_hmap = (int)((sizeof(BlockTables) + 15) & ~size_t(15));
   P.o_pmap = P.o_hmap + 4 * up4h((P.n_hdst_max < 2 ? 2 : P.n_hdst_max) * c.hist_row);
   P.o_warp = P.o_pmap + 4 * up4h(push);
   P.warp_bytes = 4 * P.sm_per_warp;
-  P.hist_stage = (c.hist_row > 0 && c.hist_row <= P.sm_rows) ? 1 : 0;
+  P.hist_stage = (c.hist_row > 0 && c.hist_row <= stage_len) ? 1 : 0;
   P.ob_body = 4 * P.sm_body; P.ob_cf = 4 * P.sm_cf; P.ob_rows = 4 * P.sm_rows; P.ob_rv = 4 * P.sm_rv; P.ob_pre = 4 * P.sm_pre;
   P.e_pos = 4 * c.J; P.e_vel = 7 * c.J; P.e_ang = 10 * c.J; P.e_dp = 13 * c.J; P.e_dv = P.e_dp + c.D; P.e_c = P.e_dv + c.D;
   {
@@ -1466,7 +1473,7 @@ extern "C" int pbhc_track_step(const PbhcTrackCfg* cfg, const PbhcTableDesc* tab
   bool noise = false;
   for (int k = 0; k < PBHC_NUM_OBS_SRC; ++k) noise |= c.obs_noise[k] != 0.0f;
   // two instantiations: the noise-free one (benchmark.yaml, evaluation) carries no Philox code in its observation stores
-  if (c.general && c.n_future > 0 && kFut * 32 > P.sm_rows) { set_error("pbhc_track_step: future table does not fit the staging buffer"); return PBHC_E_RANGE; }
+  if (c.general && c.n_future > 0 && kFut * 32 > P.sm_rows - P.sm_body) { set_error("pbhc_track_step: future table does not fit the staging buffer"); return PBHC_E_RANGE; }
   const int variant = (noise ? 1 : 0) + (c.general ? 2 : 0);
   auto kern = variant == 0 ? track_kernel<false, false> : variant == 1 ? track_kernel<true, false> : variant == 2 ? track_kernel<false, true> : track_kernel<true, true>;
   static thread_local size_t configured[4] = {0, 0, 0, 0};
