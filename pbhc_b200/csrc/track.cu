@@ -403,7 +403,7 @@ __device__ void build_tables(const TrackParams& P, BlockTables& T, int* hmap, in
 #if F_PUT
 // writes `v` of element `e` of one observation source into every row that shows it.  sd = T.sdst[source] =
 // {count, dst0, dst1, ...}: only the valid destinations (count is the same for every lane and env: uniform branches)
-__device__ __forceinline__ void put1(const int* sd, float* rows, int e, float v) {
+__device__ __forceinline__ void put1(const int* sd, float* rows, int e, float v, bool = true) {
   const int4 d = *reinterpret_cast<const int4*>(sd);
   float* r = rows + e;
   if (d.x > 0) r[d.y] = v;
@@ -411,7 +411,7 @@ __device__ __forceinline__ void put1(const int* sd, float* rows, int e, float v)
   if (d.x > 2) r[d.w] = v;
   if (d.x > 3) { r[sd[4]] = v; if (d.x > 4) r[sd[5]] = v; }
 }
-__device__ __forceinline__ void put3(const int* sd, float* rows, int e, float x, float y, float z) {
+__device__ __forceinline__ void put3(const int* sd, float* rows, int e, float x, float y, float z, bool = true) {
   const int4 d = *reinterpret_cast<const int4*>(sd);
   float* r = rows + e;
   if (d.x > 0) { r[d.y] = x; r[d.y + 1] = y; r[d.y + 2] = z; }
@@ -421,28 +421,32 @@ __device__ __forceinline__ void put3(const int* sd, float* rows, int e, float x,
 }
 
 #else
-__device__ __forceinline__ void put1(const int* sd, float* rows, int e, float v) {
+// (wide: the config has more than two observation groups - a launch constant, so the branch is uniform)
+__device__ __forceinline__ void put1(const int* sd, float* rows, int e, float v, bool wide = true) {
   const int4 d = *reinterpret_cast<const int4*>(sd);
   const int push = sd[4];
   float* r = rows + e;
-  r[d.x] = v; r[d.y] = v; r[d.z] = v; r[d.w] = v; r[push] = v;
+  r[d.x] = v; r[d.y] = v; r[push] = v;
+  if (wide) { r[d.z] = v; r[d.w] = v; }
 }
-__device__ __forceinline__ void put3(const int* sd, float* rows, int e, float x, float y, float z) {
+__device__ __forceinline__ void put3(const int* sd, float* rows, int e, float x, float y, float z, bool wide = true) {
   const int4 d = *reinterpret_cast<const int4*>(sd);
   const int push = sd[4];
   float* r = rows + e;
   r[d.x] = x; r[d.x + 1] = y; r[d.x + 2] = z;
   r[d.y] = x; r[d.y + 1] = y; r[d.y + 2] = z;
-  r[d.z] = x; r[d.z + 1] = y; r[d.z + 2] = z;
-  r[d.w] = x; r[d.w + 1] = y; r[d.w + 2] = z;
   r[push] = x; r[push + 1] = y; r[push + 2] = z;
+  if (wide) {
+    r[d.z] = x; r[d.z + 1] = y; r[d.z + 2] = z;
+    r[d.w] = x; r[d.w + 1] = y; r[d.w + 2] = z;
+  }
 }
 
 #endif
 // One element (three for emit3) of observation source k to every row that shows it: (value + U(-1,1)*noise) * scale with an
 // independent draw per destination, like parse_observation() does per obs group and for the history (helpers.py:128-152;
 // torch.rand_like there, Philox keyed by (seed, env, step, source, element) here).  Noise-free sources take the plain path.
-struct NoiseKey { uint64_t seed; int64_t env; uint32_t step; };
+struct NoiseKey { uint64_t seed; int64_t env; uint32_t step; bool wide; };  // (+ the launch constant put1 / put3 branch on)
 __device__ __forceinline__ float noisy(float raw, uint32_t bits, float ns, float sc) { return (raw + (u01(bits) * 2.0f - 1.0f) * ns) * sc; }
 __device__ __noinline__ void emit_noisy(const BlockTables& T, float* rows, int k, int e, float raw, const NoiseKey& nk) {
   const Rng rng = {make_uint2((uint32_t)nk.seed, (uint32_t)(nk.seed >> 32)), (uint32_t)nk.env, (uint32_t)((uint64_t)nk.env >> 32), nk.step};
@@ -463,12 +467,12 @@ __device__ __noinline__ void emit_noisy(const BlockTables& T, float* rows, int k
 template <bool kNoise>
 __device__ __forceinline__ void emit1(const BlockTables& T, float* rows, int k, int e, float raw, const NoiseKey& nk) {
   if (kNoise && ((T.noise_mask >> k) & 1ull)) emit_noisy(T, rows, k, e, raw, nk);
-  else put1(T.sdst[k], rows, e, raw * T.obs_scale[k]);
+  else put1(T.sdst[k], rows, e, raw * T.obs_scale[k], nk.wide);
 }
 template <bool kNoise>
 __device__ __forceinline__ void emit3(const BlockTables& T, float* rows, int k, int e, float x, float y, float z, const NoiseKey& nk) {
   if (kNoise && ((T.noise_mask >> k) & 1ull)) { emit_noisy(T, rows, k, e, x, nk); emit_noisy(T, rows, k, e + 1, y, nk); emit_noisy(T, rows, k, e + 2, z, nk); }
-  else { const float sc = T.obs_scale[k]; put3(T.sdst[k], rows, e, x * sc, y * sc, z * sc); }
+  else { const float sc = T.obs_scale[k]; put3(T.sdst[k], rows, e, x * sc, y * sc, z * sc, nk.wide); }
 }
 
 // global -> shared copy of `count` floats with the widest vector the row alignment allows (vec = 4, 2 or 1)
@@ -672,7 +676,7 @@ __global__ void __launch_bounds__(kTW * 32, kGeneral ? 2 : F_BPS) track_kernel(c
       const int n32 = chunk + e * stride;
       if (n32 >= n_envs) break;
       const int64_t n = n32;  // sign-extended 32-bit: every n * row_size below is one IMAD.WIDE
-      const NoiseKey nk = {c.seed, n + io.env_offset, push_count};
+      const NoiseKey nk = {c.seed, n + io.env_offset, push_count, c.n_groups > 2};
       cp_async_wait();  // this env's simulator state, queued while the previous env was being written out
       __syncwarp();
       // ---- A. per-env scalars ------------------------------------------------------------------------------
