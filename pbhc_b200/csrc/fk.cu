@@ -91,7 +91,28 @@ __device__ __forceinline__ void flush_rows(const float* sm, int stride, int sm_c
   }
 }
 
-__global__ void __launch_bounds__(kFkWarps * 32) fk_kernel(const __grid_constant__ FkParams P, const float* __restrict__ pose_aa,
+// Full tiles (32 poses, kChunk joints): every lane moves one element per step - element idx = lane + 32 k of the
+// [pose][column] block, so a step stores 32 consecutive elements (runs of NC contiguous floats per pose) and no lane
+// idles; NC is a compile-time constant, the divisions are multiplications.
+template <int NC>
+__device__ __forceinline__ void fill_full(float* sm, const float* g, int row_len, int col0, int lane) {
+#pragma unroll 3
+  for (int k = 0; k < NC; ++k) {
+    const int idx = lane + 32 * k, t = idx / NC, c = idx - t * NC;
+    sm[t * kInRow + c] = __ldg(g + t * row_len + col0 + c);
+  }
+}
+template <int NCOMP>
+__device__ __forceinline__ void flush_full(const float* sm, int sm_col0, float* g, int row_len, int col0, int lane) {
+  constexpr int NC = NCOMP * kChunk;
+#pragma unroll 4
+  for (int k = 0; k < NC; ++k) {
+    const int idx = lane + 32 * k, t = idx / NC, c = idx - t * NC, jj = c / NCOMP, cc = c - jj * NCOMP;
+    g[t * row_len + col0 + c] = sm[t * kStageRow + jj * 16 + sm_col0 + cc];
+  }
+}
+
+__global__ void __launch_bounds__(kFkWarps * 32, 16) fk_kernel(const __grid_constant__ FkParams P, const float* __restrict__ pose_aa,
                                                             const float* __restrict__ trans, int64_t n, float* __restrict__ pos,
                                                             float* __restrict__ rotmat, float* __restrict__ quat) {
   extern __shared__ float smem[];
@@ -114,7 +135,9 @@ __global__ void __launch_bounds__(kFkWarps * 32) fk_kernel(const __grid_constant
   for (int j0 = 0; j0 < J; j0 += kChunk) {
     const int nj = min(kChunk, J - j0);
     __syncwarp();
-    fill_rows(sm_in, kInRow, g_in, 3 * J, 3 * j0, 3 * nj, npose, lane);
+    const bool full = npose == 32 && nj == kChunk;
+    if (full) fill_full<3 * kChunk>(sm_in, g_in, 3 * J, 3 * j0, lane);
+    else fill_rows(sm_in, kInRow, g_in, 3 * J, 3 * j0, 3 * nj, npose, lane);
     __syncwarp();
     if (live) {
       for (int jj = 0; jj < nj; ++jj) {
@@ -160,9 +183,15 @@ __global__ void __launch_bounds__(kFkWarps * 32) fk_kernel(const __grid_constant
       }
     }
     __syncwarp();
-    flush_rows<3>(sm_out, kStageRow, 0, 16, pos + p0 * (3 * J), 3 * J, 3 * j0, nj, npose, lane);
-    if (rotmat) flush_rows<9>(sm_out, kStageRow, 3, 16, rotmat + p0 * (9 * J), 9 * J, 9 * j0, nj, npose, lane);
-    if (quat) flush_rows<4>(sm_out, kStageRow, 12, 16, quat + p0 * (4 * J), 4 * J, 4 * j0, nj, npose, lane);
+    if (full) {
+      flush_full<3>(sm_out, 0, pos + p0 * (3 * J), 3 * J, 3 * j0, lane);
+      if (rotmat) flush_full<9>(sm_out, 3, rotmat + p0 * (9 * J), 9 * J, 9 * j0, lane);
+      if (quat) flush_full<4>(sm_out, 12, quat + p0 * (4 * J), 4 * J, 4 * j0, lane);
+    } else {
+      flush_rows<3>(sm_out, kStageRow, 0, 16, pos + p0 * (3 * J), 3 * J, 3 * j0, nj, npose, lane);
+      if (rotmat) flush_rows<9>(sm_out, kStageRow, 3, 16, rotmat + p0 * (9 * J), 9 * J, 9 * j0, nj, npose, lane);
+      if (quat) flush_rows<4>(sm_out, kStageRow, 12, 16, quat + p0 * (4 * J), 4 * J, 4 * j0, nj, npose, lane);
+    }
   }
 }
 
