@@ -102,6 +102,16 @@ __device__ __forceinline__ void fill_full(float* sm, const float* g, int row_len
     sm[t * kInRow + c] = __ldg(g + t * row_len + col0 + c);
   }
 }
+// the same copy queued with cp.async (LDGSTS): the next chunk's pose rows arrive while the current chunk is computed
+template <int NC>
+__device__ __forceinline__ void fill_full_async(float* sm, const float* g, int row_len, int col0, int lane) {
+  const uint32_t sd = (uint32_t)__cvta_generic_to_shared(sm);
+#pragma unroll 3
+  for (int k = 0; k < NC; ++k) {
+    const int idx = lane + 32 * k, t = idx / NC, c = idx - t * NC;
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sd + 4 * (t * kInRow + c)), "l"(g + t * row_len + col0 + c) : "memory");
+  }
+}
 template <int NCOMP>
 __device__ __forceinline__ void flush_full(const float* sm, int sm_col0, float* g, int row_len, int col0, int lane) {
   constexpr int NC = NCOMP * kChunk;
@@ -118,9 +128,9 @@ __global__ void __launch_bounds__(kFkWarps * 32, 16) fk_kernel(const __grid_cons
   extern __shared__ float smem[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int J = P.J;
-  const int per_warp = 32 * kInRow + 32 * kStageRow + P.n_slots * 12 * 32;
-  float* sm_in = smem + warp * per_warp;
-  float* sm_out = sm_in + 32 * kInRow;
+  const int per_warp = 2 * 32 * kInRow + 32 * kStageRow + P.n_slots * 12 * 32;
+  float* sm_in0 = smem + warp * per_warp;  // two input buffers (full tiles prefetch the next chunk)
+  float* sm_out = sm_in0 + 2 * 32 * kInRow;
   float* sm_slot = sm_out + 32 * kStageRow;
   const int64_t p0 = ((int64_t)blockIdx.x * kFkWarps + warp) * 32;
   if (p0 >= n) return;
@@ -132,12 +142,20 @@ __global__ void __launch_bounds__(kFkWarps * 32, 16) fk_kernel(const __grid_cons
 #pragma unroll
   for (int i = 0; i < 9; ++i) Rc.m[i] = 0.f;
 
-  for (int j0 = 0; j0 < J; j0 += kChunk) {
+  const bool tile32 = npose == 32;
+  if (tile32 && J >= kChunk) fill_full_async<3 * kChunk>(sm_in0, g_in, 3 * J, 0, lane);
+  int buf = 0;
+  for (int j0 = 0; j0 < J; j0 += kChunk, buf ^= 1) {
     const int nj = min(kChunk, J - j0);
+    float* sm_in = sm_in0 + buf * 32 * kInRow;
     __syncwarp();
-    const bool full = npose == 32 && nj == kChunk;
-    if (full) fill_full<3 * kChunk>(sm_in, g_in, 3 * J, 3 * j0, lane);
-    else fill_rows(sm_in, kInRow, g_in, 3 * J, 3 * j0, 3 * nj, npose, lane);
+    const bool full = tile32 && nj == kChunk;
+    if (full) {
+      asm volatile("cp.async.wait_all;" ::: "memory");
+      if (j0 + 2 * kChunk <= J) fill_full_async<3 * kChunk>(sm_in0 + (buf ^ 1) * 32 * kInRow, g_in, 3 * J, 3 * (j0 + kChunk), lane);
+    } else {
+      fill_rows(sm_in, kInRow, g_in, 3 * J, 3 * j0, 3 * nj, npose, lane);
+    }
     __syncwarp();
     if (live) {
       for (int jj = 0; jj < nj; ++jj) {
@@ -225,7 +243,7 @@ extern "C" int pbhc_fk(const PbhcTree* tree, const float* pose_aa, const float* 
     P.load_slot[i] = P.save_slot[p];
   }
   if (n == 0) return PBHC_OK;
-  const size_t shmem = (size_t)kFkWarps * (32 * kInRow + 32 * kStageRow + P.n_slots * 12 * 32) * sizeof(float);
+  const size_t shmem = (size_t)kFkWarps * (2 * 32 * kInRow + 32 * kStageRow + P.n_slots * 12 * 32) * sizeof(float);
   static thread_local size_t configured = 0;
   static thread_local bool carved = false;
   if (!carved) {  // shared memory bounds the resident warps: ask for the largest carve-out
