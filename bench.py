@@ -50,6 +50,7 @@ def parse_args():
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="CPU baseline time budget")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--e2e-chunks", type=int, default=4, help="env chunks of the host-buffer pipeline (HostStep)")
     ap.add_argument("--workload", default="A", choices=["A", "C"],
                     help="A: BASELINE configs[0..1] (23-DoF motion_tracking, the headline); C: configs[2] (29-DoF general_tracking)")
     a = ap.parse_args()
@@ -302,7 +303,7 @@ def run_b200_arm(a):
     # ---- end to end: host buffers in, host results out, every step ----------------------------------------------------
     e2e = None
     if not a.no_e2e:
-        e2e = e2e_pass(torch, dist, wl, min(K, 20), with_fk, world, dev)
+        e2e = e2e_pass(torch, dist, wl, min(K, 20), with_fk, world, dev, chunks=a.e2e_chunks)
     sampler.mark("load_end")
     sampler.stop()
     if rank != 0:
@@ -369,7 +370,7 @@ def ncu_traffic():
     return None
 
 
-def e2e_pass(torch, dist, wl, K, with_fk, world, dev):
+def e2e_pass(torch, dist, wl, K, with_fk, world, dev, chunks=4):
     """The same step through the public host-buffer API (pbhc_b200.tracking_step.HostStep): every step copies the
     simulator state and actions from pinned host memory to the device, runs the step, and reads observations /
     rewards / reset flags back to pinned host memory (chunked so that copies and kernels overlap)."""
@@ -386,7 +387,7 @@ def e2e_pass(torch, dist, wl, K, with_fk, world, dev):
         def fk_range(lo, hi):
             hb.fk(wl.pose_aa[lo:hi], wl.trans[lo:hi], out=(pos[lo:hi], mat[lo:hi], quat[lo:hi]))
         extra = (fk_range, [(pin(h["pose_aa"]), wl.pose_aa), (pin(h["trans"]), wl.trans)])
-    hs = HostStep(wl.ts, wl.sim, wl.actions, wl.torques, wl.env_origins, wl.motion_ids, host_in, extra=extra, chunks=8)
+    hs = HostStep(wl.ts, wl.sim, wl.actions, wl.torques, wl.env_origins, wl.motion_ids, host_in, extra=extra, chunks=chunks)
     for _ in range(3):
         hs.step()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -403,7 +404,7 @@ def e2e_pass(torch, dist, wl, K, with_fk, world, dev):
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
     return {"value": wl.N * world * K / (float(ms.item()) * 1e-3), "unit": UNIT, "h2d_bytes_per_step": hs.h2d_bytes * world,
             "d2h_bytes_per_step": hs.d2h_bytes * world, "steps": K, "ms_per_step": float(ms.item()) / K,
-            "api": "pbhc_b200.tracking_step.HostStep (8 env chunks pipelined over 3 streams)"}
+            "api": f"pbhc_b200.tracking_step.HostStep ({len(hs.ranges)} env chunks pipelined over 3 streams" + (", replayed as one CUDA graph)" if hs._graph is not None else ")")}
 
 
 def main():
