@@ -124,7 +124,7 @@ __device__ __forceinline__ void flush_full(const float* sm, int sm_col0, float* 
 
 __global__ void __launch_bounds__(kFkWarps * 32, 16) fk_kernel(const __grid_constant__ FkParams P, const float* __restrict__ pose_aa,
                                                             const float* __restrict__ trans, int64_t n, float* __restrict__ pos,
-                                                            float* __restrict__ rotmat, float* __restrict__ quat) {
+                                                            float* __restrict__ rotmat, float* __restrict__ quat, int tile) {
   extern __shared__ float smem[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int J = P.J;
@@ -132,9 +132,9 @@ __global__ void __launch_bounds__(kFkWarps * 32, 16) fk_kernel(const __grid_cons
   float* sm_in0 = smem + warp * per_warp;  // two input buffers (full tiles prefetch the next chunk)
   float* sm_out = sm_in0 + 2 * 32 * kInRow;
   float* sm_slot = sm_out + 32 * kStageRow;
-  const int64_t p0 = ((int64_t)blockIdx.x * kFkWarps + warp) * 32;
+  const int64_t p0 = ((int64_t)blockIdx.x * kFkWarps + warp) * tile;  // tile = poses per warp (32, or fewer for small batches)
   if (p0 >= n) return;
-  const int npose = (int)min((int64_t)32, n - p0);
+  const int npose = (int)min((int64_t)tile, n - p0);
   const bool live = lane < npose;
   const float* g_in = pose_aa + p0 * (3 * J);
   M3 Rc;  // world rotation of the previous joint
@@ -254,9 +254,13 @@ extern "C" int pbhc_fk(const PbhcTree* tree, const float* pose_aa, const float* 
     if (cudaFuncSetAttribute(fk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shmem) != cudaSuccess) return check_launch("pbhc_fk(attr)");
     configured = shmem;
   }
-  const int64_t per_block = (int64_t)kFkWarps * 32;
+  // small batches: with 32 poses per warp fewer warps than SMs would exist and the kernel is pure latency; narrower
+  // tiles (idle lanes) keep every SM busy and shorten the per-pose staging loops
+  int tile = 32;
+  while (tile > 8 && (n + tile - 1) / tile < 2 * 148) tile >>= 1;
+  const int64_t per_block = (int64_t)kFkWarps * tile;
   const int64_t blocks = (n + per_block - 1) / per_block;
   if (blocks > 0x7fffffffLL) { set_error("pbhc_fk: too many poses"); return PBHC_E_RANGE; }
-  fk_kernel<<<(unsigned)blocks, kFkWarps * 32, shmem, (cudaStream_t)stream>>>(P, pose_aa, trans, n, pos, rotmat, quat_xyzw);
+  fk_kernel<<<(unsigned)blocks, kFkWarps * 32, shmem, (cudaStream_t)stream>>>(P, pose_aa, trans, n, pos, rotmat, quat_xyzw, tile);
   return check_launch("pbhc_fk");
 }

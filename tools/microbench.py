@@ -38,7 +38,11 @@ def main():
     from pbhc_b200.gae import compute_returns
     dev = "cuda:0"
     n = a.envs
-    peak = 6548.8
+    peak = 6447.8
+    try:
+        peak = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"])
+    except Exception:
+        pass
     for tag, names in (("23", ["Horse-stance_pose", "Bruce_Lee_pose", "Charleston_dance", "Hooks_punch",
                                "Horse-stance_punch", "Roundhouse_kick", "Side_kick"]), ("29", ["g1_29dof_clip"])):
         ml = MotionLibRobot(product_cfg(tag, tempfile.mkdtemp(), names), n, dev)
