@@ -139,7 +139,7 @@ __device__ __forceinline__ float warp_sum16(float (&v)[16], int lane) {
 }
 
 // Philox4x32-10 (counter-based; one call per (env, step, stream))
-__device__ __forceinline__ uint4 philox(uint4 ctr, uint2 key) {
+__device__ __noinline__ uint4 philox(uint4 ctr, uint2 key) {  // cold (resets, observation noise): kept out of line so the hot loop stays small
 #pragma unroll
   for (int r = 0; r < 10; ++r) {
     const uint32_t hi0 = __umulhi(0xD2511F53u, ctr.x), lo0 = 0xD2511F53u * ctr.x;
@@ -154,7 +154,7 @@ struct Rng {
   uint2 key; uint32_t env_lo, env_hi, step;
   __device__ __forceinline__ uint4 draw(uint32_t stream) const { return philox(make_uint4(env_lo, env_hi, step, stream), key); }
   __device__ __forceinline__ float uniform(uint32_t stream) const { return u01(draw(stream).x); }
-  __device__ __forceinline__ float normal(uint32_t stream) const {
+  __device__ __noinline__ float normal(uint32_t stream) const {
     const uint4 r = draw(stream);
     const float u1 = fmaxf(u01(r.x), 1.0f / 16777216.0f), u2 = u01(r.y);
     return sqrtf(-2.0f * logf(u1)) * cosf(6.283185307179586f * u2);
@@ -503,13 +503,17 @@ __device__ __forceinline__ void warp_load_async(float* dst, const float* src, in
   const char* gs = reinterpret_cast<const char*>(src);
   if (vec == 4) {
     const int nb = (count >> 2) << 4;
+#pragma unroll 1
     for (int o = lane << 4; o < nb; o += 512) cp_async16(sd + o, gs + o);
+#pragma unroll 1
     for (int i = (count & ~3) + lane; i < count; i += 32) cp_async4(sd + 4 * i, gs + 4 * i);
   } else if (vec == 2) {
     const int nb = (count >> 1) << 3;
+#pragma unroll 1
     for (int o = lane << 3; o < nb; o += 256) cp_async8(sd + o, gs + o);
     if ((count & 1) && lane == 0) cp_async4(sd + 4 * (count - 1), gs + 4 * (count - 1));
   } else {
+#pragma unroll 1
     for (int o = lane << 2; o < 4 * count; o += 128) cp_async4(sd + o, gs + o);
   }
 }
