@@ -91,7 +91,7 @@ def compare_state(ts, G, spec, tag):
         assert abs(sc[i] - float(G[name])) <= 1e-6 * abs(float(G[name])) + 1e-12, (tag, name, sc[i], float(G[name]))
 
 
-@pytest.mark.parametrize("case", ["mt23_main", "mt23_bench", "gt29_teacher"])
+@pytest.mark.parametrize("case", ["mt23_main", "mt23_bench", "gt29_teacher", "gt29_student"])
 def test_track_step_matches_reference_golden(case, tmp_path):
     g = gold(f"ref_env_{case}.npz")
     spec = TrackSpec.from_config(json.loads(str(g["meta_config_json"])))

@@ -150,6 +150,8 @@ ZERO_NOISE_C = {f"obs.noise_scales.{k}": 0.0 for k in ("base_ang_vel", "dof_pos"
 def run_general():
     # config C: LeggedRobotGeneralTracking, G1 29-DoF, obs_ppo_teacher, rewards general_main, 3-clip library
     run_case("gt29_teacher", 48, 6, "motion_tracking/obs_ppo_teacher", 21, ZERO_NOISE_C, general=True)
+    # scripts/train/student_ue_29dof.sh: the student observations (history inside actor_obs, no key-body targets)
+    run_case("gt29_student", 32, 4, "motion_tracking/obs_ppo_student", 22, ZERO_NOISE_C, general=True)
 
 
 if __name__ == "__main__":
