@@ -23,7 +23,7 @@ extern "C" {
 
 int pbhc_abi_version(void);
 /* sizeof of an ABI struct, for bindings to verify their mirror: 0 PbhcTableDesc, 1 PbhcLookupOut, 2 PbhcTree,
- * 3 PbhcTrackCfg, 4 PbhcTrackIO, 5 PbhcHistDst, 6 PbhcCurriculum; -1 for an unknown id */
+ * 3 PbhcTrackCfg, 4 PbhcTrackIO, 5 PbhcHistDst, 6 PbhcCurriculum, 7 PbhcGatherKey; -1 for an unknown id */
 int64_t pbhc_struct_size(int32_t which);
 const char* pbhc_last_error(void);
 
@@ -105,6 +105,31 @@ int pbhc_gae(const float* rewards, const float* values, const uint8_t* dones,
 
 /* advantages = (adv - mean) / (std_unbiased + 1e-8), in place (ppo.py:354). */
 int pbhc_adv_normalize(float* adv, int64_t n, const double* stats3_global, void* stream);
+
+/* ---- RolloutStorage (agents/modules/data_utils.py:30-152) data movement, SURVEY.md 8f N3.
+ * mini_batch_generator (data_utils.py:116-152) shuffles every stored key with
+ * `buf.flatten(0, 1)[indices]`, indices = randperm(T*N): dst[r, :] = src[idx[r], :] for rows of
+ * row_bytes bytes (any dtype; src has src_rows rows, both dense).  An index outside [0, src_rows)
+ * skips the row and sets *bad_index_flag (device int32, zero it first) - torch raises IndexError
+ * there; the Python mirror checks the flag. */
+int pbhc_gather_rows(const void* src, int64_t src_rows, int64_t row_bytes, const int64_t* idx,
+                     int64_t n_rows, void* dst, int32_t* bad_index_flag, void* stream);
+
+/* The same gather for every stored key of the storage in ONE launch (the reference issues one
+ * index_select per key, 11+ per PPO update): the index tile is read once and shared by all keys. */
+#define PBHC_MAX_GATHER_KEYS 24
+typedef struct PbhcGatherKey {
+  const void* src;   /* [src_rows, row_bytes] dense */
+  void* dst;         /* [n_rows, row_bytes] dense */
+  int64_t row_bytes;
+} PbhcGatherKey;
+int pbhc_gather_keys(const PbhcGatherKey* keys, int32_t n_keys, const int64_t* idx, int64_t n_rows,
+                     int64_t src_rows, int32_t* bad_index_flag, void* stream);
+
+/* Time-out bootstrap of the stored rewards, PPO._rollout_step (agents/ppo/ppo.py:266-270):
+ * rewards[n,R] += gamma * values[n,R] * time_outs[n] (time_outs = bool bytes), in place. */
+int pbhc_timeout_bootstrap(float* rewards, const float* values, const uint8_t* time_outs,
+                           int64_t n_envs, int32_t R, float gamma, void* stream);
 
 /* ---- load-time clip preparation: FK output -> packed table records.
  * Replaces Humanoid_Batch._compute_velocity / _compute_angular_velocity / dof_pos / dof_vels

@@ -33,6 +33,13 @@ class LookupOut(C.Structure):
     _fields_ = [(k, C.c_void_p) for k in LOOKUP_FIELDS]
 
 
+class GatherKey(C.Structure):
+    _fields_ = [("src", C.c_void_p), ("dst", C.c_void_p), ("row_bytes", C.c_int64)]
+
+
+MAX_GATHER_KEYS = 24
+
+
 class Tree(C.Structure):
     _fields_ = [("num_joints", C.c_int32), ("parents", C.POINTER(C.c_int32)), ("offsets", C.POINTER(C.c_float)),
                 ("local_rot_mat", C.POINTER(C.c_float))]
@@ -41,7 +48,7 @@ class Tree(C.Structure):
 _lib = None
 
 EXPORTS = ["pbhc_abi_version", "pbhc_struct_size", "pbhc_last_error", "pbhc_lookup", "pbhc_fk", "pbhc_gae", "pbhc_adv_normalize", "pbhc_clip_prepare",
-           "pbhc_track_max_blocks", "pbhc_track_step", "pbhc_track_finalize"]
+           "pbhc_track_max_blocks", "pbhc_track_step", "pbhc_track_finalize", "pbhc_gather_rows", "pbhc_gather_keys", "pbhc_timeout_bootstrap"]
 
 
 def lib():
@@ -64,6 +71,12 @@ def lib():
                            C.c_float, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
     L.pbhc_adv_normalize.restype = C.c_int
     L.pbhc_adv_normalize.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]
+    L.pbhc_gather_rows.restype = C.c_int
+    L.pbhc_gather_rows.argtypes = [C.c_void_p, C.c_int64, C.c_int64, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]
+    L.pbhc_gather_keys.restype = C.c_int
+    L.pbhc_gather_keys.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p]
+    L.pbhc_timeout_bootstrap.restype = C.c_int
+    L.pbhc_timeout_bootstrap.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_float, C.c_void_p]
     L.pbhc_clip_prepare.restype = C.c_int
     L.pbhc_clip_prepare.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32,
                                     C.c_int32, C.c_int32, C.c_float, C.POINTER(C.c_double), C.c_int32, C.c_void_p,
@@ -73,7 +86,7 @@ def lib():
         raise PbhcError("ABI version mismatch")
     L.pbhc_struct_size.restype = C.c_int64
     L.pbhc_struct_size.argtypes = [C.c_int32]
-    for i, t in enumerate((TableDesc, LookupOut, Tree, TrackCfg, TrackIO, HistDst, Curriculum)):
+    for i, t in enumerate((TableDesc, LookupOut, Tree, TrackCfg, TrackIO, HistDst, Curriculum, GatherKey)):
         if L.pbhc_struct_size(i) != C.sizeof(t):
             raise PbhcError(f"ABI struct {t.__name__}: library {L.pbhc_struct_size(i)} B, binding {C.sizeof(t)} B")
     _lib = L

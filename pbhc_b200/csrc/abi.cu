@@ -35,6 +35,7 @@ extern "C" int64_t pbhc_struct_size(int32_t which) {
     case 4: return sizeof(PbhcTrackIO);
     case 5: return sizeof(PbhcHistDst);
     case 6: return sizeof(PbhcCurriculum);
+    case 7: return sizeof(PbhcGatherKey);
     default: return -1;
   }
 }

@@ -283,6 +283,19 @@ class TrackingStep:
         io.inject_delay = p(inj.get("action_delay_idx"))
         self._keep = (sim, actions, torques, env_origins, motion_ids, inj)
 
+    def write_obs_into(self, buffers):
+        """Redirects observation groups to caller-owned [N, dim] fp32 CUDA tensors from the next bind() on, e.g.
+        `{g: storage.slot(g, step + 1)}` so RolloutStorage.update_key (agents/ppo/ppo.py:251-252) finds the rows
+        already in place.  Groups not named keep their buffer.  Takes effect for the next launch() (the pointer block
+        of the last bind() is patched too); a HostStep / CUDA graph built earlier keeps the pointers it captured."""
+        names = list(self.spec.obs_groups)
+        for g, t in buffers.items():
+            cur = self.obs_buf_dict[g]
+            if t.shape != cur.shape or t.dtype != cur.dtype or t.device != cur.device or not t.is_contiguous():
+                raise _lib.PbhcError(f"write_obs_into: '{g}' must be a contiguous {tuple(cur.shape)} {cur.dtype} tensor on {cur.device}")
+            self.obs_buf_dict[g] = t
+            self._io.obs[names.index(g)] = _lib.ptr(t)
+
     def launch(self):
         """pbhc_track_step on the current stream with the pointers of the last bind(): the fused kernel + the
         deterministic reduction of its per-block sums into `acc`."""

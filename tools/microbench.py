@@ -73,6 +73,30 @@ def main():
         byt = T * R * 12 + T + R * 4 + T * 4 + T * 8
         print(json.dumps(dict(kernel=f"gae_R{R}", n=N, ms=ms, bytes_per_unit=byt, gbs=byt * N / ms / 1e6,
                               frac=byt * N / ms / 1e6 / peak)))
+    # RolloutStorage shuffle-gather: the keys PPO._setup_storage registers (ppo.py:124-135) at config A's
+    # widths, T = 24 steps; bytes = every stored row read once + written once + the int64 permutation.  The eager-torch
+    # line is the reference expression (one index_select + contiguous per key) on the same buffers.
+    from pbhc_b200.rollout import RolloutStorage
+    T = 24
+    for N in sorted({4096, min(n, 32768)}):
+        st = RolloutStorage(N, T, device=dev)
+        dims = dict(actor_obs=380, critic_obs=463, actions=23, rewards=1, dones=1, values=1, returns=1, advantages=1,
+                    actions_log_prob=1, action_mean=23, action_sigma=23)
+        for k, w in dims.items():
+            st.register_key(k, shape=(w,), dtype=torch.bool if k == "dones" else torch.float)
+            if k != "dones":
+                st.batch_update_data(k, torch.randn(T, N, w, device=dev))
+        row = sum(getattr(st, k)[0, 0].numel() * getattr(st, k).element_size() for k in st.stored_keys)
+        byt = 2 * row + 8
+        idx = torch.randperm(T * N, device=dev)
+        out = st.gather(idx)
+        ms = timeit(lambda: st.gather(idx, out=out, check=False), a.iters)
+        print(json.dumps(dict(kernel="rollout_gather", n=T * N, ms=ms, bytes_per_unit=byt, gbs=byt * T * N / ms / 1e6,
+                              frac=byt * T * N / ms / 1e6 / peak, launches=1)))
+        ms = timeit(lambda: {k: getattr(st, k)[:].flatten(0, 1)[idx].contiguous() for k in st.stored_keys}, a.iters)
+        print(json.dumps(dict(kernel="rollout_gather_eager_torch", n=T * N, ms=ms, bytes_per_unit=byt,
+                              gbs=byt * T * N / ms / 1e6, frac=byt * T * N / ms / 1e6 / peak, launches=len(dims))))
+        del st, out
 
 
 if __name__ == "__main__":
