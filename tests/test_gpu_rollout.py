@@ -84,7 +84,7 @@ def test_same_seed_same_batches_as_eager_torch():
             assert torch.equal(b[k], ref[k][j * mini:(j + 1) * mini])
 
 
-@pytest.mark.parametrize("T,N", [(1, 1), (3, 33), (24, 4096)])
+@pytest.mark.parametrize("T,N", [(1, 1), (3, 33), (24, 4096), (5, 40001)])
 def test_gather_all_widths_vs_oracle(T, N):
     """row widths covering the 1/4/8/16-byte vector paths, rows narrower and wider than a warp, odd strides"""
     from oracle import pbhc_oracle_rollout as OR
@@ -93,6 +93,7 @@ def test_gather_all_widths_vs_oracle(T, N):
     rng = np.random.default_rng(T * 1000 + N)
     shapes = {"w1": ((1,), "float"), "w2": ((2,), "float"), "w3": ((3,), "float"), "w4": ((4,), "float"), "w12": ((12,), "float"),
               "w31": ((31,), "float"), "w130": ((130,), "float"), "w380": ((380,), "float"), "w1540": ((1540,), "float"),
+              "w33": ((33,), "float"), "w35": ((35,), "float"), "w462": ((462,), "float"), "w463": ((463,), "float"), "l17": ((17,), "long"),
               "b1": ((1,), "bool"), "b7": ((7,), "bool"), "b16": ((16,), "bool"), "l1": ((1,), "long"), "l3": ((3,), "long"),
               "m": ((3, 5), "float")}
     if N > 1000:
