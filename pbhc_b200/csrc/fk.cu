@@ -10,7 +10,11 @@ namespace pbhc {
 constexpr int kChunk = 3;         // joints per staging chunk
 constexpr int kFkWarps = 1;         // one warp per block: 15 blocks (= pose tiles) fit an SM, 65536 poses are a single wave
 constexpr int kMaxSlots = 8;
-constexpr int kStageRow = kChunk * 16 + 1;  // odd stride -> conflict-free per-thread rows
+// output staging: one region per output array, [pose][columns of the chunk] with odd strides (conflict-free per-thread
+// rows); a region mirrors the global layout of the chunk, so the flush is a linear walk without index arithmetic
+constexpr int kPosRow = kChunk * 3, kRotRow = kChunk * 9, kQuatRow = kChunk * 4 + 1;
+constexpr int kStageRow = kPosRow + kRotRow + kQuatRow;
+static_assert((kPosRow & 1) && (kRotRow & 1) && (kQuatRow & 1), "odd shared-memory strides");
 constexpr int kInRow = kChunk * 3 + 1;
 
 struct FkParams {
@@ -29,7 +33,7 @@ __device__ __forceinline__ M3 matmul3(const M3& a, const M3& b) {
 #pragma unroll
   for (int i = 0; i < 3; ++i)
 #pragma unroll
-    for (int j = 0; j < 3; ++j) c.m[i * 3 + j] = (a.m[i * 3] * b.m[j] + a.m[i * 3 + 1] * b.m[3 + j]) + a.m[i * 3 + 2] * b.m[6 + j];
+    for (int j = 0; j < 3; ++j) c.m[i * 3 + j] = __fmaf_rn(a.m[i * 3 + 2], b.m[6 + j], __fmaf_rn(a.m[i * 3 + 1], b.m[3 + j], a.m[i * 3] * b.m[j]));
   return c;
 }
 
@@ -112,13 +116,19 @@ __device__ __forceinline__ void fill_full_async(float* sm, const float* g, int r
     asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sd + 4 * (t * kInRow + c)), "l"(g + t * row_len + col0 + c) : "memory");
   }
 }
-template <int NCOMP>
-__device__ __forceinline__ void flush_full(const float* sm, int sm_col0, float* g, int row_len, int col0, int lane) {
-  constexpr int NC = NCOMP * kChunk;
-#pragma unroll 4
-  for (int k = 0; k < NC; ++k) {
-    const int idx = lane + 32 * k, t = idx / NC, c = idx - t * NC, jj = c / NCOMP, cc = c - jj * NCOMP;
-    g[t * row_len + col0 + c] = sm[t * kStageRow + jj * 16 + sm_col0 + cc];
+// full tile (32 poses): element idx = lane + 32 k of the [pose][NC columns] block, walked with running pointers
+template <int NC, int S>
+__device__ __forceinline__ void flush_lin(const float* sm, float* g, int row_len, int lane) {
+  constexpr int DT = 32 / NC, DC = 32 % NC;
+  int t = lane / NC, c = lane - t * NC;
+  const float* sp = sm + t * S + c;
+  float* gp = g + (int64_t)t * row_len + c;
+  const int g_step = DT * row_len + DC, g_wrap = row_len - NC;
+#pragma unroll 9
+  for (int k = 0; k < NC; ++k) {  // 32 NC elements / 32 lanes
+    *gp = *sp;
+    c += DC; sp += DT * S + DC; gp += g_step;
+    if (c >= NC) { c -= NC; sp += S - NC; gp += g_wrap; }
   }
 }
 
@@ -131,6 +141,7 @@ __global__ void __launch_bounds__(kFkWarps * 32, 16) fk_kernel(const __grid_cons
   const int per_warp = 2 * 32 * kInRow + 32 * kStageRow + P.n_slots * 12 * 32;
   float* sm_in0 = smem + warp * per_warp;  // two input buffers (full tiles prefetch the next chunk)
   float* sm_out = sm_in0 + 2 * 32 * kInRow;
+  float* sm_pos = sm_out, *sm_rot = sm_pos + 32 * kPosRow, *sm_quat = sm_rot + 32 * kRotRow;
   float* sm_slot = sm_out + 32 * kStageRow;
   const int64_t p0 = ((int64_t)blockIdx.x * kFkWarps + warp) * tile;  // tile = poses per warp (32, or fewer for small batches)
   if (p0 >= n) return;
@@ -158,57 +169,77 @@ __global__ void __launch_bounds__(kFkWarps * 32, 16) fk_kernel(const __grid_cons
     }
     __syncwarp();
     if (live) {
-      for (int jj = 0; jj < nj; ++jj) {
-        const int i = j0 + jj;
-        const float* a = sm_in + lane * kInRow + 3 * jj;
-        const M3 Mj = aa_to_mat(a[0], a[1], a[2]);
-        if (P.parent[i] < 0) {
-          Rc = Mj;
-          const float* tr = trans + (p0 + lane) * 3;
-          pc[0] = tr[0]; pc[1] = tr[1]; pc[2] = tr[2];
-        } else {
-          M3 Rp = Rc;
-          float pp[3] = {pc[0], pc[1], pc[2]};
-          const int ls = P.load_slot[i];
-          if (ls >= 0) {
-            const float* s = sm_slot + ls * 12 * 32 + lane;
+      // Three unrolled passes per chunk so that the work that does not depend on the parent (axis-angle -> matrix,
+      // local_rot x joint matrix, matrix -> quaternion: three quarters of the arithmetic) is independent
+      // straight-line code the scheduler can interleave; only `parent x local` walks the chain.
+      M3 LM[kChunk], Rw[kChunk];
 #pragma unroll
-            for (int c = 0; c < 9; ++c) Rp.m[c] = s[c * 32];
-#pragma unroll
-            for (int c = 0; c < 3; ++c) pp[c] = s[(9 + c) * 32];
-          }
+      for (int jj = 0; jj < kChunk; ++jj) {
+        if (jj < nj) {
+          const int i = j0 + jj;
+          const float* a = sm_in + lane * kInRow + 3 * jj;
+          const M3 Mj = aa_to_mat(a[0], a[1], a[2]);
           M3 L;
 #pragma unroll
           for (int c = 0; c < 9; ++c) L.m[c] = P.lrot[i * 9 + c];
-          const float ox = P.off[i * 3], oy = P.off[i * 3 + 1], oz = P.off[i * 3 + 2];
-#pragma unroll
-          for (int c = 0; c < 3; ++c) pc[c] = ((Rp.m[c * 3] * ox + Rp.m[c * 3 + 1] * oy) + Rp.m[c * 3 + 2] * oz) + pp[c];
-          Rc = matmul3(Rp, matmul3(L, Mj));
+          LM[jj] = P.parent[i] < 0 ? Mj : matmul3(L, Mj);
         }
-        const int ss = P.save_slot[i];
-        if (ss >= 0) {
-          float* s = sm_slot + ss * 12 * 32 + lane;
+      }
 #pragma unroll
-          for (int c = 0; c < 9; ++c) s[c * 32] = Rc.m[c];
+      for (int jj = 0; jj < kChunk; ++jj) {
+        if (jj < nj) {
+          const int i = j0 + jj;
+          if (P.parent[i] < 0) {
+            Rc = LM[jj];
+            const float* tr = trans + (p0 + lane) * 3;
+            pc[0] = tr[0]; pc[1] = tr[1]; pc[2] = tr[2];
+          } else {
+            M3 Rp = Rc;
+            float pp[3] = {pc[0], pc[1], pc[2]};
+            const int ls = P.load_slot[i];
+            if (ls >= 0) {
+              const float* s = sm_slot + ls * 12 * 32 + lane;
 #pragma unroll
-          for (int c = 0; c < 3; ++c) s[(9 + c) * 32] = pc[c];
+              for (int c = 0; c < 9; ++c) Rp.m[c] = s[c * 32];
+#pragma unroll
+              for (int c = 0; c < 3; ++c) pp[c] = s[(9 + c) * 32];
+            }
+            const float ox = P.off[i * 3], oy = P.off[i * 3 + 1], oz = P.off[i * 3 + 2];
+#pragma unroll
+            for (int c = 0; c < 3; ++c) pc[c] = __fmaf_rn(Rp.m[c * 3 + 2], oz, __fmaf_rn(Rp.m[c * 3 + 1], oy, Rp.m[c * 3] * ox)) + pp[c];
+            Rc = matmul3(Rp, LM[jj]);
+          }
+          const int ss = P.save_slot[i];
+          if (ss >= 0) {
+            float* s = sm_slot + ss * 12 * 32 + lane;
+#pragma unroll
+            for (int c = 0; c < 9; ++c) s[c * 32] = Rc.m[c];
+#pragma unroll
+            for (int c = 0; c < 3; ++c) s[(9 + c) * 32] = pc[c];
+          }
+          float* op = sm_pos + lane * kPosRow + jj * 3;
+          op[0] = pc[0]; op[1] = pc[1]; op[2] = pc[2];
+          float* orot = sm_rot + lane * kRotRow + jj * 9;
+#pragma unroll
+          for (int c = 0; c < 9; ++c) orot[c] = Rc.m[c];
+          Rw[jj] = Rc;
         }
-        float* o = sm_out + lane * kStageRow + jj * 16;
-        o[0] = pc[0]; o[1] = pc[1]; o[2] = pc[2];
+      }
+      if (quat) {
 #pragma unroll
-        for (int c = 0; c < 9; ++c) o[3 + c] = Rc.m[c];
-        if (quat) mat_to_quat_xyzw(Rc, o + 12);
+        for (int jj = 0; jj < kChunk; ++jj)
+          if (jj < nj) mat_to_quat_xyzw(Rw[jj], sm_quat + lane * kQuatRow + jj * 4);
       }
     }
     __syncwarp();
     if (full) {
-      flush_full<3>(sm_out, 0, pos + p0 * (3 * J), 3 * J, 3 * j0, lane);
-      if (rotmat) flush_full<9>(sm_out, 3, rotmat + p0 * (9 * J), 9 * J, 9 * j0, lane);
-      if (quat) flush_full<4>(sm_out, 12, quat + p0 * (4 * J), 4 * J, 4 * j0, lane);
+      flush_lin<3 * kChunk, kPosRow>(sm_pos, pos + p0 * (3 * J) + 3 * j0, 3 * J, lane);
+      if (rotmat) flush_lin<9 * kChunk, kRotRow>(sm_rot, rotmat + p0 * (9 * J) + 9 * j0, 9 * J, lane);
+      if (quat) flush_lin<4 * kChunk, kQuatRow>(sm_quat, quat + p0 * (4 * J) + 4 * j0, 4 * J, lane);
     } else {
-      flush_rows<3>(sm_out, kStageRow, 0, 16, pos + p0 * (3 * J), 3 * J, 3 * j0, nj, npose, lane);
-      if (rotmat) flush_rows<9>(sm_out, kStageRow, 3, 16, rotmat + p0 * (9 * J), 9 * J, 9 * j0, nj, npose, lane);
-      if (quat) flush_rows<4>(sm_out, kStageRow, 12, 16, quat + p0 * (4 * J), 4 * J, 4 * j0, nj, npose, lane);
+      flush_rows<3>(sm_pos, kPosRow, 0, 3, pos + p0 * (3 * J), 3 * J, 3 * j0, nj, npose, lane);
+      if (rotmat) flush_rows<9>(sm_rot, kRotRow, 0, 9, rotmat + p0 * (9 * J), 9 * J, 9 * j0, nj, npose, lane);
+      if (quat) flush_rows<4>(sm_quat, kQuatRow, 0, 4, quat + p0 * (4 * J), 4 * J, 4 * j0, nj, npose, lane);
     }
   }
 }
