@@ -131,6 +131,31 @@ int pbhc_gather_keys(const PbhcGatherKey* keys, int32_t n_keys, const int64_t* i
 int pbhc_timeout_bootstrap(float* rewards, const float* values, const uint8_t* time_outs,
                            int64_t n_envs, int32_t R, float gamma, void* stream);
 
+/* ---- trajectory evaluation (humanoidverse/measure_traj.py), SURVEY.md 8f N4.
+ * blend_motion (measure_traj.py:67-133): one key of a loaded motion, src [num_frames, row_floats],
+ * resampled at times[n_out] (fp32) -> out [n_out, row_floats]: frame pair and blend of
+ * _calc_frame_blend (:68-84, motion length = num_frames / fps), then `b*x1 + (1-b)*x0`, or slerp
+ * over consecutive xyzw quaternions when quats != 0 (:121). */
+int pbhc_blend_frames(const float* src, int64_t num_frames, int32_t row_floats, int32_t quats,
+                      const float* times, int64_t n_out, float fps, float* out, void* stream);
+
+/* eval_accuracy (measure_traj.py:146-225) + eval_smoothness (:227-290) in one pass: pol/ref
+ * global_translation [T,J,3], dof_pos [T,D], optional contact_mask [T,C] (both or neither);
+ * delta = fps, or 1 for delta_per_frame.  out[PBHC_TRAJ_METRICS] doubles on the device, indexed by
+ * PBHC_TM_*; a mean over no terms is NaN like torch.  workspace: >= 592 * PBHC_TRAJ_METRICS doubles. */
+#define PBHC_TRAJ_METRICS 22
+enum {
+  PBHC_TM_GMPBPE = 0, PBHC_TM_MPBPE, PBHC_TM_MPJPE, PBHC_TM_MPJVE, PBHC_TM_MPJAE, PBHC_TM_PBVE, PBHC_TM_PBAE,
+  PBHC_TM_ROOT_ACC, PBHC_TM_ROOT_VEL, PBHC_TM_CONTACT,
+  PBHC_TM_L2_VEL, PBHC_TM_L2_ACC, PBHC_TM_L2_JERK, PBHC_TM_L2_DOF_VEL, PBHC_TM_L2_DOF_ACC, PBHC_TM_L2_DOF_JERK,
+  PBHC_TM_L2_REF_VEL, PBHC_TM_L2_REF_ACC, PBHC_TM_L2_REF_JERK, PBHC_TM_L2_REF_DOF_VEL, PBHC_TM_L2_REF_DOF_ACC,
+  PBHC_TM_L2_REF_DOF_JERK
+};
+int pbhc_traj_metrics(const float* pol_pos, const float* ref_pos, const float* pol_dof, const float* ref_dof,
+                      const float* pol_contact, const float* ref_contact, int64_t T, int32_t J, int32_t D,
+                      int32_t C, float delta, double* workspace, int64_t workspace_doubles, double* out,
+                      void* stream);
+
 /* ---- load-time clip preparation: FK output -> packed table records.
  * Replaces Humanoid_Batch._compute_velocity / _compute_angular_velocity / dof_pos / dof_vels
  * (torch_humanoid_batch.py:216-224, 272-290; numpy.gradient + scipy gaussian_filter1d sigma=2,

@@ -38,6 +38,12 @@ class GatherKey(C.Structure):
 
 
 MAX_GATHER_KEYS = 24
+# PBHC_TM_* order of pbhc_traj_metrics: eval_accuracy keys (measure_traj.py:207-221) then eval_smoothness keys (:277-290)
+TRAJ_ACCURACY = ["E_gmpbpe", "E_mpbpe", "E_mpjpe", "E_mpjve", "E_mpjae", "E_pbve", "E_pbae", "E_root_acc", "E_root_vel", "E_contact_acc"]
+TRAJ_SMOOTHNESS = ["L2_vel", "L2_acc", "L2_jerk", "L2_dof_vel", "L2_dof_acc", "L2_dof_jerk", "L2_ref_vel", "L2_ref_acc", "L2_ref_jerk",
+                   "L2_ref_dof_vel", "L2_ref_dof_acc", "L2_ref_dof_jerk"]
+TRAJ_METRICS = len(TRAJ_ACCURACY) + len(TRAJ_SMOOTHNESS)
+TRAJ_WORKSPACE = 592 * TRAJ_METRICS
 
 
 class Tree(C.Structure):
@@ -48,7 +54,7 @@ class Tree(C.Structure):
 _lib = None
 
 EXPORTS = ["pbhc_abi_version", "pbhc_struct_size", "pbhc_last_error", "pbhc_lookup", "pbhc_fk", "pbhc_gae", "pbhc_adv_normalize", "pbhc_clip_prepare",
-           "pbhc_track_max_blocks", "pbhc_track_step", "pbhc_track_finalize", "pbhc_gather_rows", "pbhc_gather_keys", "pbhc_timeout_bootstrap"]
+           "pbhc_track_max_blocks", "pbhc_track_step", "pbhc_track_finalize", "pbhc_gather_rows", "pbhc_gather_keys", "pbhc_timeout_bootstrap", "pbhc_blend_frames", "pbhc_traj_metrics"]
 
 
 def lib():
@@ -75,6 +81,11 @@ def lib():
     L.pbhc_gather_rows.argtypes = [C.c_void_p, C.c_int64, C.c_int64, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]
     L.pbhc_gather_keys.restype = C.c_int
     L.pbhc_gather_keys.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p]
+    L.pbhc_blend_frames.restype = C.c_int
+    L.pbhc_blend_frames.argtypes = [C.c_void_p, C.c_int64, C.c_int32, C.c_int32, C.c_void_p, C.c_int64, C.c_float, C.c_void_p, C.c_void_p]
+    L.pbhc_traj_metrics.restype = C.c_int
+    L.pbhc_traj_metrics.argtypes = [C.c_void_p] * 6 + [C.c_int64, C.c_int32, C.c_int32, C.c_int32, C.c_float, C.c_void_p, C.c_int64,
+                                                        C.c_void_p, C.c_void_p]
     L.pbhc_timeout_bootstrap.restype = C.c_int
     L.pbhc_timeout_bootstrap.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_float, C.c_void_p]
     L.pbhc_clip_prepare.restype = C.c_int
