@@ -23,7 +23,7 @@ extern "C" {
 
 int pbhc_abi_version(void);
 /* sizeof of an ABI struct, for bindings to verify their mirror: 0 PbhcTableDesc, 1 PbhcLookupOut, 2 PbhcTree,
- * 3 PbhcTrackCfg, 4 PbhcTrackIO, 5 PbhcHistDst, 6 PbhcCurriculum, 7 PbhcGatherKey; -1 for an unknown id */
+ * 3 PbhcTrackCfg, 4 PbhcTrackIO, 5 PbhcHistDst, 6 PbhcCurriculum, 7 PbhcGatherKey, 8 PbhcActuationCfg; -1 for an unknown id */
 int64_t pbhc_struct_size(int32_t which);
 const char* pbhc_last_error(void);
 
@@ -365,6 +365,45 @@ int pbhc_track_step(const PbhcTrackCfg* cfg, const PbhcTableDesc* tab, const Pbh
 /* advances `scalars` from `acc` (adaptive sigma, average episode length, curricula, log values);
  * call after pbhc_track_step (and after all-reducing acc when envs are sharded over ranks) */
 int pbhc_track_finalize(const PbhcTrackCfg* cfg, const double* acc, double* scalars, void* stream);
+
+/* ---- actuation half of the env step: LeggedRobotBase._pre_physics_step
+ * (envs/legged_base_task/legged_robot_base.py:268-286) and _compute_torques (:795-838). */
+typedef struct PbhcActuationCfg {
+  int32_t D;                 /* dofs */
+  int32_t Q;                 /* action-queue depth = ctrl_delay_step_range[1] + 1; 0 = randomize_ctrl_delay off */
+  float action_clip;         /* robot.control.action_clip_value */
+  int32_t control_type;      /* 0 "P", 1 "V", 2 "T" */
+  int32_t per_dof_action_scale;
+  float action_scale;        /* scalar robot.control.action_scale, or */
+  float action_scales[PBHC_MAX_DOF];
+  float p_gains[PBHC_MAX_DOF];
+  float d_gains[PBHC_MAX_DOF];
+  float torque_limits[PBHC_MAX_DOF];
+  int32_t rfi;               /* domain_rand.randomize_torque_rfi */
+  float rfi_lim;
+  int32_t rao;               /* domain_rand.use_rao */
+  int32_t clip_torques;
+  float sim_dt;              /* control type "V" */
+  uint64_t seed;             /* in-kernel Philox for the RFI draw when rfi_uniform is NULL */
+} PbhcActuationCfg;
+
+/* actions = clip(actions_in, +-action_clip); *clip_count += #(|actions| == action_clip) (zero it first;
+ * action_clip_frac = count / (N*D)); with Q > 0 the queue [N,Q,D] is shifted by one, actions enter
+ * at slot 0 and actions_after_delay[e] = queue[e, action_delay_idx[e]]; with Q == 0 it is actions. */
+int pbhc_pre_physics(const PbhcActuationCfg* cfg, const float* actions_in, float* actions,
+                     float* action_queue, const int64_t* action_delay_idx, float* actions_after_delay,
+                     uint64_t* clip_count, int64_t n_envs, void* stream);
+
+/* torques [N,D] from actions_after_delay and the Isaac Gym dof_state [N*D,2] = (pos, vel).
+ * default_dof_pos rows have default_dof_stride floats (0 = one shared row).  rfi_uniform [N,D]:
+ * the U[0,1) draws of torch.rand_like for this call (tests), NULL = Philox keyed by
+ * (seed, env, call_index, dof). */
+int pbhc_compute_torques(const PbhcActuationCfg* cfg, const float* actions_after_delay,
+                         const float* dof_state, const float* default_dof_pos,
+                         int32_t default_dof_stride, const float* last_dof_vel, const float* kp_scale,
+                         const float* kd_scale, const float* rfi_lim_scale, const float* rao_scale,
+                         const float* rfi_uniform, uint32_t call_index, float* torques,
+                         int64_t n_envs, void* stream);
 
 #ifdef __cplusplus
 }

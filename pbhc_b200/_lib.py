@@ -54,7 +54,7 @@ class Tree(C.Structure):
 _lib = None
 
 EXPORTS = ["pbhc_abi_version", "pbhc_struct_size", "pbhc_last_error", "pbhc_lookup", "pbhc_fk", "pbhc_gae", "pbhc_adv_normalize", "pbhc_clip_prepare",
-           "pbhc_track_max_blocks", "pbhc_track_step", "pbhc_track_finalize", "pbhc_gather_rows", "pbhc_gather_keys", "pbhc_timeout_bootstrap", "pbhc_blend_frames", "pbhc_traj_metrics"]
+           "pbhc_track_max_blocks", "pbhc_track_step", "pbhc_track_finalize", "pbhc_gather_rows", "pbhc_gather_keys", "pbhc_timeout_bootstrap", "pbhc_blend_frames", "pbhc_traj_metrics", "pbhc_pre_physics", "pbhc_compute_torques"]
 
 
 def lib():
@@ -86,6 +86,10 @@ def lib():
     L.pbhc_traj_metrics.restype = C.c_int
     L.pbhc_traj_metrics.argtypes = [C.c_void_p] * 6 + [C.c_int64, C.c_int32, C.c_int32, C.c_int32, C.c_float, C.c_void_p, C.c_int64,
                                                         C.c_void_p, C.c_void_p]
+    L.pbhc_pre_physics.restype = C.c_int
+    L.pbhc_pre_physics.argtypes = [C.c_void_p] * 7 + [C.c_int64, C.c_void_p]
+    L.pbhc_compute_torques.restype = C.c_int
+    L.pbhc_compute_torques.argtypes = [C.c_void_p] * 4 + [C.c_int32] + [C.c_void_p] * 6 + [C.c_uint32, C.c_void_p, C.c_int64, C.c_void_p]
     L.pbhc_timeout_bootstrap.restype = C.c_int
     L.pbhc_timeout_bootstrap.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_float, C.c_void_p]
     L.pbhc_clip_prepare.restype = C.c_int
@@ -97,7 +101,7 @@ def lib():
         raise PbhcError("ABI version mismatch")
     L.pbhc_struct_size.restype = C.c_int64
     L.pbhc_struct_size.argtypes = [C.c_int32]
-    for i, t in enumerate((TableDesc, LookupOut, Tree, TrackCfg, TrackIO, HistDst, Curriculum, GatherKey)):
+    for i, t in enumerate((TableDesc, LookupOut, Tree, TrackCfg, TrackIO, HistDst, Curriculum, GatherKey, ActuationCfg)):
         if L.pbhc_struct_size(i) != C.sizeof(t):
             raise PbhcError(f"ABI struct {t.__name__}: library {L.pbhc_struct_size(i)} B, binding {C.sizeof(t)} B")
     _lib = L
@@ -193,6 +197,14 @@ TRACK_IO_FIELDS = [
     "base_mass_scale",
     "episode_length_buf", "env_f32", "last_actions", "last_dof_pos", "last_dof_vel", "kp_scale", "kd_scale",
     "rfi_lim_scale", "rao_scale", "action_delay_idx", "hist", "episode_sums", "scalars"]
+
+
+class ActuationCfg(C.Structure):
+    _fields_ = [("D", C.c_int32), ("Q", C.c_int32), ("action_clip", C.c_float), ("control_type", C.c_int32),
+                ("per_dof_action_scale", C.c_int32), ("action_scale", C.c_float), ("action_scales", C.c_float * MAX_DOF),
+                ("p_gains", C.c_float * MAX_DOF), ("d_gains", C.c_float * MAX_DOF), ("torque_limits", C.c_float * MAX_DOF),
+                ("rfi", C.c_int32), ("rfi_lim", C.c_float), ("rao", C.c_int32), ("clip_torques", C.c_int32), ("sim_dt", C.c_float),
+                ("seed", C.c_uint64)]
 
 
 class TrackIO(C.Structure):

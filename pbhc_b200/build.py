@@ -14,7 +14,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libpbhc_b200.so")
-SOURCES = ["abi.cu", "lookup.cu", "fk.cu", "gae.cu", "track.cu", "motion_prep.cu", "rollout.cu", "traj.cu"]
+SOURCES = ["abi.cu", "lookup.cu", "fk.cu", "gae.cu", "track.cu", "motion_prep.cu", "rollout.cu", "traj.cu", "actuate.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-fmad=false",
               "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr"]
 

@@ -36,6 +36,7 @@ extern "C" int64_t pbhc_struct_size(int32_t which) {
     case 5: return sizeof(PbhcHistDst);
     case 6: return sizeof(PbhcCurriculum);
     case 7: return sizeof(PbhcGatherKey);
+    case 8: return sizeof(PbhcActuationCfg);
     default: return -1;
   }
 }

@@ -25,6 +25,19 @@ __device__ __forceinline__ float norm3(float x, float y, float z) {
 __device__ __forceinline__ float norm4(float x, float y, float z, float w) { return sqrtf(((x * x + y * y) + z * z) + w * w); }
 __device__ __forceinline__ float norm2(float x, float y) { return sqrtf(__fmaf_rn(y, y, x * x)); }
 
+// Philox4x32-10, counter-based RNG of the device-side domain randomisation / noise (keyed by seed; counter = ids + stream)
+__device__ __forceinline__ uint4 philox4x32_10(uint4 ctr, uint2 key) {
+#pragma unroll
+  for (int r = 0; r < 10; ++r) {
+    const uint32_t hi0 = __umulhi(0xD2511F53u, ctr.x), lo0 = 0xD2511F53u * ctr.x;
+    const uint32_t hi1 = __umulhi(0xCD9E8D57u, ctr.z), lo1 = 0xCD9E8D57u * ctr.z;
+    ctr = make_uint4(hi1 ^ ctr.y ^ key.x, lo1, hi0 ^ ctr.w ^ key.y, lo0);
+    key.x += 0x9E3779B9u; key.y += 0xBB67AE85u;
+  }
+  return ctr;
+}
+__device__ __forceinline__ float u01(uint32_t x) { return (float)(x & 0xFFFFFFu) * (1.0f / 16777216.0f); }  // [0, 1), 24 bits
+
 // slerp, isaac_utils/rotations.py:210-232 (not renormalised)
 __device__ __forceinline__ Q4 slerp(Q4 a, Q4 b, float t) {
   float c = ((a.x * b.x + a.y * b.y) + a.z * b.z) + a.w * b.w;

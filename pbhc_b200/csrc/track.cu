@@ -138,18 +138,8 @@ __device__ __forceinline__ float warp_sum16(float (&v)[16], int lane) {
   return v[0] + __shfl_xor_sync(0xffffffffu, v[0], 1);
 }
 
-// Philox4x32-10 (counter-based; one call per (env, step, stream))
-__device__ __noinline__ uint4 philox(uint4 ctr, uint2 key) {  // cold (resets, observation noise): kept out of line so the hot loop stays small
-#pragma unroll
-  for (int r = 0; r < 10; ++r) {
-    const uint32_t hi0 = __umulhi(0xD2511F53u, ctr.x), lo0 = 0xD2511F53u * ctr.x;
-    const uint32_t hi1 = __umulhi(0xCD9E8D57u, ctr.z), lo1 = 0xCD9E8D57u * ctr.z;
-    ctr = make_uint4(hi1 ^ ctr.y ^ key.x, lo1, hi0 ^ ctr.w ^ key.y, lo0);
-    key.x += 0x9E3779B9u; key.y += 0xBB67AE85u;
-  }
-  return ctr;
-}
-__device__ __forceinline__ float u01(uint32_t x) { return (float)(x & 0xFFFFFFu) * (1.0f / 16777216.0f); }
+// Philox4x32-10 (common.cuh), one call per (env, step, stream)
+__device__ __noinline__ uint4 philox(uint4 ctr, uint2 key) { return philox4x32_10(ctr, key); }  // cold (resets, observation noise): out of line so the hot loop stays small
 struct Rng {
   uint2 key; uint32_t env_lo, env_hi, step;
   __device__ __forceinline__ uint4 draw(uint32_t stream) const { return philox(make_uint4(env_lo, env_hi, step, stream), key); }

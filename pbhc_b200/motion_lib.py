@@ -181,6 +181,27 @@ class MotionLibRobot:
                                     self._clip_length.data_ptr(), self._clip_dt.data_ptr(), total, len(nf), J, Jb, D, Cm, stride)
         self._dims = (J, Jb, D, Cm)
 
+    def motion_data(self, motion=0):
+        """The per-motion dict the reference's load_motions returns (Humanoid_Batch.fk_batch(return_full=True) keys,
+        torch_humanoid_batch.py:189-229), as views of the packed table rows of loaded motion `motion`: what
+        measure_traj.get_motionlib_data hands to blend_motion / eval_accuracy (`load_motions(...)[0]` there).
+        Rotations are xyzw quaternions; the 3x3 `*_rotation_mat*` keys are not materialised."""
+        J, Jb, D, Cm = self._dims
+        clip = int(self._clip_of_motion[motion])
+        lo, T = int(self._clip_frame_start[clip]), int(self._clip_num_frames[clip])
+        rec = self._records[lo:lo + T]
+        rot, pos = rec[:, :4 * J].reshape(T, J, 4), rec[:, 4 * J:7 * J].reshape(T, J, 3)
+        vel, ang = rec[:, 7 * J:10 * J].reshape(T, J, 3), rec[:, 10 * J:13 * J].reshape(T, J, 3)
+        out = {"global_translation_extend": pos, "global_rotation_extend": rot, "global_velocity_extend": vel,
+               "global_angular_velocity_extend": ang, "global_translation": pos[:, :Jb], "global_rotation": rot[:, :Jb],
+               "global_velocity": vel[:, :Jb], "global_angular_velocity": ang[:, :Jb],
+               "global_root_velocity": vel[:, 0], "global_root_angular_velocity": ang[:, 0],
+               "dof_pos": rec[:, 13 * J:13 * J + D], "dof_vels": rec[:, 13 * J + D:13 * J + 2 * D],
+               "fps": int(self._clip_fps[clip])}
+        if Cm:
+            out["contact_mask"] = rec[:, 13 * J + 2 * D:13 * J + 2 * D + Cm]
+        return out
+
     # ---- small accessors (motion_lib_base.py:474-501) ------------------------------------------
     def num_motions(self):
         return self._num_motions

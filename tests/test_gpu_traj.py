@@ -108,3 +108,31 @@ def test_multistep_reference_window_matches_per_step_lookups(tmp_path):
         assert torch.equal(got[k], v), k
     fp, fv = MT.future_ref_obs(got)
     assert fp.shape == (B, steps * 23) and torch.equal(fv, want["dof_vel"].reshape(B, -1))
+
+
+def test_motion_data_feeds_the_metrics_end_to_end(tmp_path):
+    """measure_traj.load_traj_data flow on device: loaded reference motion -> motion_data -> blend at 50-fps policy times ->
+    metrics against a perturbed copy; checked against the oracle run on the same table rows"""
+    from oracle import pbhc_oracle_traj as OT
+    from pbhc_b200 import measure_traj as MT
+    from pbhc_b200.motion_lib import MotionLibRobot
+    ml = MotionLibRobot(product_cfg("23", str(tmp_path), ["Horse-stance_pose"]), 1, DEV)
+    ml.load_motions(random_sample=False)
+    pre = ml.motion_data(0)
+    T = pre["dof_pos"].shape[0]
+    assert pre["global_translation"].shape == (T, 24, 3) and pre["global_translation_extend"].shape == (T, 27, 3)
+    assert pre["dof_pos"].shape == (T, 23) and pre["fps"] == 30
+    times = torch.arange(int(T / 30 * 50) - 2, device=DEV, dtype=torch.float32) / 50
+    ref = MT.blend_motion(pre, times)
+    gen = torch.Generator().manual_seed(0)
+    pol = {k: v + 0.01 * torch.randn(v.shape, generator=gen).to(DEV) for k, v in ref.items() if k in ("global_translation", "dof_pos")}
+    traj = {"pol": pol, "ref": ref, "appendix": {"fps": 50}}
+    cpu = lambda d: {k: (v.cpu() if torch.is_tensor(v) else v) for k, v in d.items()}
+    pre_c = {k: (v.cpu().contiguous() if torch.is_tensor(v) else v) for k, v in pre.items()}
+    ref_c = OT.blend_motion(pre_c, times.cpu())
+    for k in ("global_translation", "dof_pos", "global_velocity_extend"):
+        assert np.array_equal(ref[k].cpu().numpy(), ref_c[k].numpy()), k
+    traj_c = {"pol": cpu(pol), "ref": ref_c, "appendix": {"fps": 50}}
+    for k, v in {**OT.eval_accuracy(traj_c), **OT.eval_smoothness(traj_c)}.items():
+        got = {**MT.eval_accuracy(traj), **MT.eval_smoothness(traj)}[k]
+        assert_close(got.cpu(), v, what=k)
