@@ -6,7 +6,7 @@
 namespace pbhc {
 
 constexpr int kGaeThreads = 256;
-constexpr int kTB = 4;  // time steps whose loads are issued together
+constexpr int kTB = 8;  // time steps whose loads are issued together (and whose head sums share one barrier pair)
 
 __device__ __forceinline__ double block_sum(double v, double* sm) {
   for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
@@ -25,11 +25,12 @@ __global__ void __launch_bounds__(kGaeThreads) gae_kernel(
     const float* __restrict__ rewards, const float* __restrict__ values, const uint8_t* __restrict__ dones,
     const float* __restrict__ last_values, int T, int64_t N, int R, int E, float gamma, float lam,
     float* __restrict__ returns, float* __restrict__ adv_raw, double* __restrict__ stats3) {
-  __shared__ float sm_adv[kGaeThreads];
+  __shared__ float sm_adv[kTB][kGaeThreads];
   __shared__ double sm_red[8];
   const int local = threadIdx.x;
   const int e = local / R, r = local - e * R;
-  const int64_t n = (int64_t)blockIdx.x * E + e;
+  const int64_t n0 = (int64_t)blockIdx.x * E;
+  const int64_t n = n0 + e;
   const bool active = (e < E) && (n < N);
   const int64_t NR = N * R;
   const int64_t col = active ? n * R + r : 0;
@@ -65,22 +66,27 @@ __global__ void __launch_bounds__(kGaeThreads) gae_kernel(
       if (R == 1) {
         if (active) { adv_raw[t * N + n] = a; s1 += (double)a; s2 += (double)a * (double)a; }
       } else {
-        __syncthreads();
-        sm_adv[local] = a;
-        __syncthreads();
-        if (local < E && (int64_t)blockIdx.x * E + local < N) {
-          float s = 0.0f;
-          for (int i = 0; i < R; ++i) s += sm_adv[local * R + i];
-          adv_raw[t * N + (int64_t)blockIdx.x * E + local] = s;
-          s1 += (double)s; s2 += (double)s * (double)s;
+        sm_adv[k][local] = a;
+      }
+    }
+    if (R > 1) {
+      // sum over the reward heads (mh_ppo.py:391): thread (step k, env ee) adds the R values of its env in head order
+      __syncthreads();
+      for (int idx = local; idx < kTB * E; idx += kGaeThreads) {
+        const int k = idx / E, ee = idx - k * E, t = t1 - 1 - k;
+        if (t >= 0 && n0 + ee < N) {
+          float sum = 0.0f;
+          for (int i = 0; i < R; ++i) sum += sm_adv[k][ee * R + i];
+          adv_raw[t * N + n0 + ee] = sum;
+          s1 += (double)sum; s2 += (double)sum * (double)sum;
         }
       }
+      __syncthreads();
     }
   }
   s1 = block_sum(s1, sm_red);
   s2 = block_sum(s2, sm_red);
   if (threadIdx.x == 0) {
-    const int64_t n0 = (int64_t)blockIdx.x * E;
     const int64_t cnt = (N - n0 < E ? N - n0 : E) * (int64_t)T;
     atomicAdd(stats3 + 0, (double)cnt);
     atomicAdd(stats3 + 1, s1);
