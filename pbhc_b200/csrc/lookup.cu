@@ -1,16 +1,30 @@
-// lookup.cu - K1: motion-state lookup.  One warp per query: frame index + blend (bit-exact
-// restatement of _calc_frame_blend), then the two adjacent packed records are streamed with
-// float4 loads (quaternions -> slerp) and coalesced scalar loads (everything else -> lerp) and
-// scattered into the reference's output dict layout.
+// lookup.cu - K1: motion-state lookup.  One warp per query, eight consecutive queries per block: frame index +
+// blend (bit-exact restatement of _calc_frame_blend), then the two adjacent packed records are streamed with
+// float4 loads (quaternions -> slerp) and coalesced scalar loads (everything else -> lerp).  The results are NOT
+// scattered from registers: each warp assembles its query's rows in shared memory in the reference's output
+// layout, one staging region per output tensor holding the block's eight rows back to back - which is exactly
+// the tensor's global layout for those eight queries - and each region then leaves with ONE TMA bulk store
+// (cp.async.bulk shared -> global; 8 rows are always a multiple of 32 bytes), issued by one thread per tensor.
+// No 324-byte rows written in 4-byte pieces, no 64-bit index arithmetic per element.  Ragged last blocks and
+// tensors whose base is not 16-byte aligned are flushed by a plain cooperative copy.
 // Reference: utils/motion_lib/motion_lib_base.py:123-259, 503-513; isaac_utils/rotations.py:210-232.
 #include "common.cuh"
 #include "table.cuh"
 
 namespace pbhc {
 
+constexpr int kQ = 8;  // queries (= warps) per block
+// staging regions, in PbhcLookupOut's field order (the struct is 20 pointers)
+enum LookupArr { A_ROOT_POS, A_ROOT_ROT, A_DOF_POS, A_ROOT_VEL, A_ROOT_ANG, A_DOF_VEL, A_AA, A_BODIES, A_RG_POS, A_RB_ROT,
+                 A_BODY_VEL, A_BODY_ANG, A_RG_POS_T, A_RG_ROT_T, A_BODY_VEL_T, A_BODY_ANG_T, A_CONTACT, A_F0, A_F1, A_BLEND, kArr };
+static_assert(sizeof(PbhcLookupOut) == kArr * sizeof(void*), "PbhcLookupOut is not 20 pointers");
+
 struct LookupParams {
   PbhcTableDesc tab;
-  PbhcLookupOut out;
+  void* dst[kArr];     // output tensors (NULL: not requested)
+  int row[kArr];       // row length in 32-bit words (the int64 frame indices: 2)
+  int off[kArr];       // word offset of the tensor's staging region (kQ rows)
+  uint32_t bulk_mask;  // tensors whose base pointer is 16-byte aligned
   const int32_t* clip_of_motion;
   const int64_t* motion_ids;
   const float* motion_times;
@@ -18,67 +32,99 @@ struct LookupParams {
   int64_t n;
 };
 
-__device__ __forceinline__ void emit3(float* ext, float* base, float* root, int64_t q, int J, int Jb, int idx, float v) {
-  if (ext) ext[q * (3 * J) + idx] = v;
-  if (base && idx < 3 * Jb) base[q * (3 * Jb) + idx] = v;
-  if (root && idx < 3) root[q * 3 + idx] = v;
-}
-
-constexpr int kWarps = 8;
-
-__global__ void __launch_bounds__(kWarps * 32) lookup_kernel(const LookupParams p) {
-  const int lane = threadIdx.x & 31;
-  const int64_t q = (int64_t)blockIdx.x * kWarps + (threadIdx.x >> 5);
-  if (q >= p.n) return;
+__global__ void __launch_bounds__(kQ * 32) lookup_kernel(const __grid_constant__ LookupParams p) {
+  extern __shared__ __align__(16) float sm[];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const int64_t q0 = (int64_t)blockIdx.x * kQ, q = q0 + w;
+  const int nq = (int)min((int64_t)kQ, p.n - q0);
   const PbhcTableDesc& tab = p.tab;
-  const PbhcLookupOut& o = p.out;
   const int J = tab.num_joints, Jb = tab.num_bodies, D = tab.num_dof, C = tab.contact_size;
+  auto S = [&](int a) { return sm + p.off[a] + w * p.row[a]; };  // this warp's row of tensor a
 
-  const int clip = resolve_clip(tab, p.clip_of_motion, p.motion_ids[q]);
-  const FrameBlend fb = frame_blend(tab, clip, p.motion_times[q]);
-  const float b = fb.blend, omb = 1.0f - b;
-  const float* r0 = tab.records + fb.f0 * tab.rec_stride;
-  const float* r1 = tab.records + fb.f1 * tab.rec_stride;
-  if (lane == 0) {
-    if (o.f0l) o.f0l[q] = fb.f0;
-    if (o.f1l) o.f1l[q] = fb.f1;
-    if (o.blend) o.blend[q] = b;
-  }
-  float off[3] = {0.f, 0.f, 0.f};
-  if (p.offset) { off[0] = p.offset[q * 3]; off[1] = p.offset[q * 3 + 1]; off[2] = p.offset[q * 3 + 2]; }
+  if (q < p.n) {
+    const int clip = resolve_clip(tab, p.clip_of_motion, p.motion_ids[q]);
+    const FrameBlend fb = frame_blend(tab, clip, p.motion_times[q]);
+    const float b = fb.blend, omb = 1.0f - b;
+    const float* r0 = tab.records + fb.f0 * tab.rec_stride;
+    const float* r1 = tab.records + fb.f1 * tab.rec_stride;
+    if (lane == 0) {
+      *reinterpret_cast<long long*>(S(A_F0)) = fb.f0;
+      *reinterpret_cast<long long*>(S(A_F1)) = fb.f1;
+      *S(A_BLEND) = b;
+    }
+    float ox = 0.f, oy = 0.f, oz = 0.f;
+    if (p.offset) { ox = p.offset[q * 3]; oy = p.offset[q * 3 + 1]; oz = p.offset[q * 3 + 2]; }
 
-  // rotations: one quaternion per lane
-  for (int j = lane; j < J; j += 32) {
-    float4 a = __ldg(reinterpret_cast<const float4*>(r0) + j);
-    float4 c = __ldg(reinterpret_cast<const float4*>(r1) + j);
-    Q4 s = slerp({a.x, a.y, a.z, a.w}, {c.x, c.y, c.z, c.w}, b);
-    float4 v = make_float4(s.x, s.y, s.z, s.w);
-    if (o.rg_rot_t) reinterpret_cast<float4*>(o.rg_rot_t)[q * J + j] = v;
-    if (o.rb_rot && j < Jb) reinterpret_cast<float4*>(o.rb_rot)[q * Jb + j] = v;
-    if (o.root_rot && j == 0) reinterpret_cast<float4*>(o.root_rot)[q] = v;
-  }
-  // everything else: lerp, element e of the record
-  const int e_pos = 4 * J, e_vel = 7 * J, e_ang = 10 * J, e_dp = 13 * J, e_dv = e_dp + D, e_c = e_dv + D, e_end = e_c + C;
-#pragma unroll 4
-  for (int e = e_pos + lane; e < e_end; e += 32) {
-    float v = omb * __ldg(r0 + e) + b * __ldg(r1 + e);
-    if (e < e_vel) {
-      int idx = e - e_pos;
-      emit3(o.rg_pos_t, o.rg_pos, o.root_pos, q, J, Jb, idx, v + off[idx % 3]);
-    } else if (e < e_ang) {
-      emit3(o.body_vel_t, o.body_vel, o.root_vel, q, J, Jb, e - e_vel, v);
-    } else if (e < e_dp) {
-      emit3(o.body_ang_vel_t, o.body_ang_vel, o.root_ang_vel, q, J, Jb, e - e_ang, v);
-    } else if (e < e_dv) {
-      if (o.dof_pos) o.dof_pos[q * D + (e - e_dp)] = v;
-    } else if (e < e_c) {
-      if (o.dof_vel) o.dof_vel[q * D + (e - e_dv)] = v;
-    } else {
-      if (o.contact_mask) o.contact_mask[q * C + (e - e_c)] = v;
+    // rotations: one quaternion per lane
+    {
+      float4* ext = reinterpret_cast<float4*>(S(A_RG_ROT_T));
+      float4* base = reinterpret_cast<float4*>(S(A_RB_ROT));
+      for (int j = lane; j < J; j += 32) {
+        const float4 a = __ldg(reinterpret_cast<const float4*>(r0) + j);
+        const float4 c = __ldg(reinterpret_cast<const float4*>(r1) + j);
+        const Q4 s = slerp({a.x, a.y, a.z, a.w}, {c.x, c.y, c.z, c.w}, b);
+        const float4 v = make_float4(s.x, s.y, s.z, s.w);
+        ext[j] = v;
+        if (j < Jb) base[j] = v;
+        if (j == 0) *reinterpret_cast<float4*>(S(A_ROOT_ROT)) = v;
+      }
+    }
+    // body vectors: lerp of record elements [e0, e0 + 3 J) -> extended, base-body and root rows
+    auto vec3 = [&](int e0, int a_ext, int a_base, int a_root, bool add_off) {
+      float* ext = S(a_ext);
+      float* base = S(a_base);
+      float* root = S(a_root);
+      for (int i = lane; i < 3 * J; i += 32) {
+        float v = omb * __ldg(r0 + e0 + i) + b * __ldg(r1 + e0 + i);
+        if (add_off) { const int k = i % 3; v = v + (k == 0 ? ox : k == 1 ? oy : oz); }
+        ext[i] = v;
+        if (i < 3 * Jb) base[i] = v;
+        if (i < 3) root[i] = v;
+      }
+    };
+    vec3(4 * J, A_RG_POS_T, A_RG_POS, A_ROOT_POS, true);
+    vec3(7 * J, A_BODY_VEL_T, A_BODY_VEL, A_ROOT_VEL, false);
+    vec3(10 * J, A_BODY_ANG_T, A_BODY_ANG, A_ROOT_ANG, false);
+    // dof_pos | dof_vel | contact are adjacent in the record
+    {
+      const int e0 = 13 * J;
+      float* dp = S(A_DOF_POS);
+      float* dv = S(A_DOF_VEL);
+      float* cm = S(A_CONTACT);
+      for (int i = lane; i < 2 * D + C; i += 32) {
+        const float v = omb * __ldg(r0 + e0 + i) + b * __ldg(r1 + e0 + i);
+        if (i < D) dp[i] = v;
+        else if (i < 2 * D) dv[i - D] = v;
+        else cm[i - 2 * D] = v;
+      }
+    }
+    {
+      float* aa = S(A_AA);
+      for (int i = lane; i < 3 * Jb; i += 32) aa[i] = 0.0f;
+      if (lane < 17) S(A_BODIES)[lane] = 0.0f;
     }
   }
-  if (o.motion_aa) for (int i = lane; i < 3 * Jb; i += 32) o.motion_aa[q * (3 * Jb) + i] = 0.0f;
-  if (o.motion_bodies && lane < 17) o.motion_bodies[q * 17 + lane] = 0.0f;
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy writes -> visible to the bulk stores
+  __syncthreads();
+  // flush: thread a owns tensor a
+  const int a = threadIdx.x;
+  if (a < kArr && p.dst[a] != nullptr && nq == kQ && ((p.bulk_mask >> a) & 1u)) {
+    const uint32_t bytes = (uint32_t)(kQ * p.row[a]) * 4u;
+    char* g = reinterpret_cast<char*>(p.dst[a]) + q0 * (int64_t)p.row[a] * 4;
+    const uint32_t s = (uint32_t)__cvta_generic_to_shared(sm + p.off[a]);
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(g), "r"(s), "r"(bytes) : "memory");
+    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+  }
+  // ragged last block / unaligned tensors: cooperative word copy (block-uniform conditions)
+  if (nq < kQ || p.bulk_mask != (1u << kArr) - 1u) {
+    for (int t = 0; t < kArr; ++t) {
+      if (p.dst[t] == nullptr || (nq == kQ && ((p.bulk_mask >> t) & 1u))) continue;
+      const uint32_t* s = reinterpret_cast<const uint32_t*>(sm + p.off[t]);
+      uint32_t* g = reinterpret_cast<uint32_t*>(p.dst[t]) + q0 * (int64_t)p.row[t];
+      for (int i = threadIdx.x; i < nq * p.row[t]; i += kQ * 32) g[i] = s[i];
+    }
+  }
+  if (a < kArr) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");  // the staging rows must outlive the copies
 }
 
 }  // namespace pbhc
@@ -97,9 +143,28 @@ extern "C" int pbhc_lookup(const PbhcTableDesc* tab, const int32_t* clip_of_moti
   const uintptr_t al = (uintptr_t)tab->records | (uintptr_t)out->rg_rot_t | (uintptr_t)out->rb_rot | (uintptr_t)out->root_rot;
   if (al & 15) { set_error("pbhc_lookup: records / quaternion outputs must be 16-byte aligned"); return PBHC_E_ALIGN; }
   if (n == 0) return PBHC_OK;
-  LookupParams p{*tab, *out, clip_of_motion, motion_ids, motion_times, offset, n};
-  const int64_t blocks = (n + kWarps - 1) / kWarps;
+  LookupParams p;
+  p.tab = *tab; p.clip_of_motion = clip_of_motion; p.motion_ids = motion_ids; p.motion_times = motion_times; p.offset = offset; p.n = n;
+  const int J = tab->num_joints, Jb = tab->num_bodies, D = tab->num_dof, C = tab->contact_size;
+  const int rows[kArr] = {3, 4, D, 3, 3, D, 3 * Jb, 17, 3 * Jb, 4 * Jb, 3 * Jb, 3 * Jb, 3 * J, 4 * J, 3 * J, 3 * J, C, 2, 2, 1};
+  void* const* dst = reinterpret_cast<void* const*>(out);
+  int words = 0;
+  p.bulk_mask = 0;
+  for (int a = 0; a < kArr; ++a) {
+    p.dst[a] = rows[a] > 0 ? dst[a] : nullptr;
+    p.row[a] = rows[a];
+    p.off[a] = words;                         // kQ rows = a multiple of 8 words: every region stays 32-byte aligned
+    words += kQ * rows[a];
+    if (p.dst[a] == nullptr || ((uintptr_t)p.dst[a] & 15) == 0) p.bulk_mask |= 1u << a;
+  }
+  const size_t shmem = (size_t)words * 4;
+  static thread_local size_t configured = 48 * 1024;
+  if (shmem > configured) {
+    if (cudaFuncSetAttribute(lookup_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shmem) != cudaSuccess) return check_launch("pbhc_lookup(attr)");
+    configured = shmem;
+  }
+  const int64_t blocks = (n + kQ - 1) / kQ;
   if (blocks > 0x7fffffffLL) { set_error("pbhc_lookup: too many queries"); return PBHC_E_RANGE; }
-  lookup_kernel<<<(unsigned)blocks, kWarps * 32, 0, (cudaStream_t)stream>>>(p);
+  lookup_kernel<<<(unsigned)blocks, kQ * 32, shmem, (cudaStream_t)stream>>>(p);
   return check_launch("pbhc_lookup");
 }

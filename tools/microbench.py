@@ -28,6 +28,21 @@ def timeit(fn, iters, warmup=3):
     return ts[len(ts) // 2]
 
 
+def timeit_graph(fn, iters, warmup=3):
+    """the same call captured once in a CUDA graph and replayed: device time without the host-side call overhead"""
+    st = torch.cuda.Stream()
+    st.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(st):
+        for _ in range(warmup):
+            fn()
+    torch.cuda.current_stream().wait_stream(st)
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        keep = fn()  # noqa: F841  (outputs stay alive in the graph's pool)
+    return timeit(g.replay, iters, warmup)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--envs", type=int, default=65536)
@@ -56,6 +71,9 @@ def main():
         outf = 3 + 4 + D + 3 + 3 + D + 3 * Jb + 17 + 13 * Jb + 13 * J + Cm
         byt = 24 + 2 * rec * 4 + outf * 4
         print(json.dumps(dict(kernel=f"lookup_{tag}", n=n, ms=ms, bytes_per_unit=byt, gbs=byt * n / ms / 1e6,
+                              frac=byt * n / ms / 1e6 / peak)))
+        ms = timeit_graph(lambda: ml.get_motion_state(ids, t, off), a.iters)
+        print(json.dumps(dict(kernel=f"lookup_{tag}_graph_replay", n=n, ms=ms, bytes_per_unit=byt, gbs=byt * n / ms / 1e6,
                               frac=byt * n / ms / 1e6 / peak)))
         pose = torch.randn(n, J, 3, device=dev) * 0.5
         trans = torch.randn(n, 3, device=dev)
