@@ -82,7 +82,10 @@ def main():
         byt = J * 12 + 12 + J * (12 + 16 + 36)
         print(json.dumps(dict(kernel=f"fk_{tag}", n=n, ms=ms, bytes_per_unit=byt, gbs=byt * n / ms / 1e6,
                               frac=byt * n / ms / 1e6 / peak)))
-    for R, N in ((1, n * 4), (21, n)):
+        ms = timeit_graph(lambda: hb.fk(pose, trans), a.iters)
+        print(json.dumps(dict(kernel=f"fk_{tag}_graph_replay", n=n, ms=ms, bytes_per_unit=byt, gbs=byt * n / ms / 1e6,
+                              frac=byt * n / ms / 1e6 / peak)))
+    for R, N in ((1, n * 2), (1, n * 4), (1, n * 16), (21, n)):
         T = 24
         v, r = torch.randn(T, N, R, device=dev), torch.randn(T, N, R, device=dev)
         d = torch.rand(T, N, 1, device=dev) < 0.02
@@ -91,6 +94,10 @@ def main():
         byt = T * R * 12 + T + R * 4 + T * 4 + T * 8
         print(json.dumps(dict(kernel=f"gae_R{R}", n=N, ms=ms, bytes_per_unit=byt, gbs=byt * N / ms / 1e6,
                               frac=byt * N / ms / 1e6 / peak)))
+        ms = timeit_graph(lambda: compute_returns(v, r, d, lv, 0.99, 0.95), a.iters)
+        print(json.dumps(dict(kernel=f"gae_R{R}_graph_replay", n=N, ms=ms, bytes_per_unit=byt, gbs=byt * N / ms / 1e6,
+                              frac=byt * N / ms / 1e6 / peak)))
+        del v, r, d, lv
     # RolloutStorage shuffle-gather: the keys PPO._setup_storage registers (ppo.py:124-135) at config A's
     # widths, T = 24 steps; bytes = every stored row read once + written once + the int64 permutation.  The eager-torch
     # line is the reference expression (one index_select + contiguous per key) on the same buffers.
