@@ -151,6 +151,39 @@ def test_lookup_multiclip_large_vs_oracle(tmp_path):
     assert e["rg_pos_t"].shape == (0, 27, 3)
 
 
+@pytest.mark.parametrize("n", [1, 5, 8, 43])
+def test_lookup_flush_paths_agree(n, tmp_path):
+    """K1 flushes full 8-query blocks with bulk stores and everything else (ragged last block, output tensors whose base
+    is not 16-byte aligned, tensors that were not requested) with a plain copy: every path must write the same bits,
+    and nothing outside the requested rows."""
+    import ctypes as C
+    from pbhc_b200 import _lib
+    ml = _lib_with("23", ["Horse-stance_pose", "Side_kick"], tmp_path, 4)
+    J, Jb, D, Cm = ml._dims
+    gen = torch.Generator().manual_seed(n)
+    ids = torch.randint(0, 4, (n,), generator=gen).to(DEV)
+    t = (torch.rand(n, generator=gen) * 3.0).to(DEV)
+    off = torch.randn(n, 3, generator=gen).to(DEV)
+    ref = ml.get_motion_state(ids, t, off, with_indices=True)
+    rows = {"root_pos": 3, "dof_pos": D, "root_vel": 3, "dof_vel": D, "rg_pos": 3 * Jb, "body_vel": 3 * Jb, "rg_pos_t": 3 * J,
+            "body_ang_vel_t": 3 * J, "contact_mask": Cm, "blend": 1}
+    # every tensor sits one float past a 16-byte boundary inside a NaN-filled slab with guard rows on both sides
+    slabs = {k: torch.full((4 + (n + 2) * w,), float("nan"), device=DEV) for k, w in rows.items()}
+    out = _lib.LookupOut()
+    for k in _lib.LOOKUP_FIELDS:
+        setattr(out, k, None)
+    for k, w in rows.items():
+        setattr(out, k, slabs[k].data_ptr() + 4 * (1 + w))
+    _lib.check(_lib.lib().pbhc_lookup(C.byref(ml._desc), ml._clip_of_motion.data_ptr(), ids.data_ptr(), t.data_ptr(),
+                                      off.data_ptr(), n, C.byref(out), _lib.stream_ptr(torch.device(DEV))))
+    torch.cuda.synchronize()
+    for k, w in rows.items():
+        got = slabs[k][1 + w:1 + w + n * w]
+        want = ref["_blend" if k == "blend" else k].reshape(-1)
+        assert torch.equal(got, want), k
+        assert torch.isnan(slabs[k][:1 + w]).all() and torch.isnan(slabs[k][1 + w + n * w:]).all(), k + " guard rows"
+
+
 @pytest.mark.parametrize("tag,vec", [("ppo", False), ("mhppo", True)])
 def test_gae_matches_reference_golden(tag, vec):
     from pbhc_b200.gae import compute_returns
