@@ -32,15 +32,24 @@ struct LookupParams {
   int64_t n;
 };
 
-__global__ void __launch_bounds__(kQ * 32) lookup_kernel(const __grid_constant__ LookupParams p) {
+#ifndef K1_MINB
+#define K1_MINB 6  // 40 registers: six blocks (48 warps) per SM hide the ids -> clip -> frame -> record load chain (64 registers / 4 blocks: 0.094 ms, 40 / 6: 0.082 ms)
+#endif
+__global__ void __launch_bounds__(kQ * 32, K1_MINB) lookup_kernel(const __grid_constant__ LookupParams p) {
   extern __shared__ __align__(16) float sm[];
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   const int64_t q0 = (int64_t)blockIdx.x * kQ, q = q0 + w;
   const int nq = (int)min((int64_t)kQ, p.n - q0);
   const PbhcTableDesc& tab = p.tab;
   const int J = tab.num_joints, Jb = tab.num_bodies, D = tab.num_dof, C = tab.contact_size;
-  auto S = [&](int a) { return sm + p.off[a] + w * p.row[a]; };  // this warp's row of tensor a
+  auto O = [&](int a) { return p.off[a] + w * p.row[a]; };  // word offset of this warp's row of tensor a
 
+  // the all-zero tensors (motion_aa, motion_bodies): the block clears both staging regions with 128-bit stores
+  {
+    float4* z = reinterpret_cast<float4*>(sm + p.off[A_AA]);  // A_AA and A_BODIES are adjacent regions, kQ rows each (multiples of 32 B)
+    const int nz = (kQ * (p.row[A_AA] + p.row[A_BODIES])) >> 2;
+    for (int i = threadIdx.x; i < nz; i += kQ * 32) z[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+  }
   if (q < p.n) {
     const int clip = resolve_clip(tab, p.clip_of_motion, p.motion_ids[q]);
     const FrameBlend fb = frame_blend(tab, clip, p.motion_times[q]);
@@ -48,17 +57,24 @@ __global__ void __launch_bounds__(kQ * 32) lookup_kernel(const __grid_constant__
     const float* r0 = tab.records + fb.f0 * tab.rec_stride;
     const float* r1 = tab.records + fb.f1 * tab.rec_stride;
     if (lane == 0) {
-      *reinterpret_cast<long long*>(S(A_F0)) = fb.f0;
-      *reinterpret_cast<long long*>(S(A_F1)) = fb.f1;
-      *S(A_BLEND) = b;
+      *reinterpret_cast<long long*>(sm + O(A_F0)) = fb.f0;
+      *reinterpret_cast<long long*>(sm + O(A_F1)) = fb.f1;
+      sm[O(A_BLEND)] = b;
     }
-    float ox = 0.f, oy = 0.f, oz = 0.f;
-    if (p.offset) { ox = p.offset[q * 3]; oy = p.offset[q * 3 + 1]; oz = p.offset[q * 3 + 2]; }
+    // offset component of element i = lane + 32 k of a [J,3] row: (lane + 2 k) % 3 - three values that rotate with k
+    float oa = 0.f, ob = 0.f, oc = 0.f;
+    if (p.offset) {
+      const float ox = p.offset[q * 3], oy = p.offset[q * 3 + 1], oz = p.offset[q * 3 + 2];
+      const int m = lane % 3;
+      oa = m == 0 ? ox : m == 1 ? oy : oz;  // k = 0: component m
+      ob = m == 0 ? oz : m == 1 ? ox : oy;  // k = 1: component (m + 2) % 3
+      oc = m == 0 ? oy : m == 1 ? oz : ox;  // k = 2: component (m + 1) % 3
+    }
 
     // rotations: one quaternion per lane
     {
-      float4* ext = reinterpret_cast<float4*>(S(A_RG_ROT_T));
-      float4* base = reinterpret_cast<float4*>(S(A_RB_ROT));
+      float4* ext = reinterpret_cast<float4*>(sm + O(A_RG_ROT_T));
+      float4* base = reinterpret_cast<float4*>(sm + O(A_RB_ROT));
       for (int j = lane; j < J; j += 32) {
         const float4 a = __ldg(reinterpret_cast<const float4*>(r0) + j);
         const float4 c = __ldg(reinterpret_cast<const float4*>(r1) + j);
@@ -66,42 +82,40 @@ __global__ void __launch_bounds__(kQ * 32) lookup_kernel(const __grid_constant__
         const float4 v = make_float4(s.x, s.y, s.z, s.w);
         ext[j] = v;
         if (j < Jb) base[j] = v;
-        if (j == 0) *reinterpret_cast<float4*>(S(A_ROOT_ROT)) = v;
+        if (j == 0) *reinterpret_cast<float4*>(sm + O(A_ROOT_ROT)) = v;
       }
     }
-    // body vectors: lerp of record elements [e0, e0 + 3 J) -> extended, base-body and root rows
-    auto vec3 = [&](int e0, int a_ext, int a_base, int a_root, bool add_off) {
-      float* ext = S(a_ext);
-      float* base = S(a_base);
-      float* root = S(a_root);
-      for (int i = lane; i < 3 * J; i += 32) {
-        float v = omb * __ldg(r0 + e0 + i) + b * __ldg(r1 + e0 + i);
-        if (add_off) { const int k = i % 3; v = v + (k == 0 ? ox : k == 1 ? oy : oz); }
-        ext[i] = v;
-        if (i < 3 * Jb) base[i] = v;
-        if (i < 3) root[i] = v;
+    // positions / velocities / angular velocities: element i of the three [J,3] record segments per pass - six loads in
+    // flight, one set of predicates for the extended, base-body and root rows.  (Requesting every record element up
+    // front - 30 loads in flight per lane, 64-80 registers - was measured SLOWER, 0.088 vs 0.082 ms: resident warps
+    // matter more than per-warp memory parallelism here.)
+    {
+      const int J3 = 3 * J, Jb3 = 3 * Jb;
+      const float* a0 = r0 + 4 * J + lane;
+      const float* a1 = r1 + 4 * J + lane;
+      float* e_pos = sm + O(A_RG_POS_T) + lane; float* e_vel = sm + O(A_BODY_VEL_T) + lane; float* e_ang = sm + O(A_BODY_ANG_T) + lane;
+      float* b_pos = sm + O(A_RG_POS) + lane;   float* b_vel = sm + O(A_BODY_VEL) + lane;   float* b_ang = sm + O(A_BODY_ANG) + lane;
+      for (int i = lane, k = 0; i < J3; i += 32, k += 32) {
+        const float p0 = __ldg(a0 + k), p1 = __ldg(a1 + k);
+        const float v0 = __ldg(a0 + J3 + k), v1 = __ldg(a1 + J3 + k);
+        const float w0 = __ldg(a0 + 2 * J3 + k), w1 = __ldg(a1 + 2 * J3 + k);
+        const float vp = (omb * p0 + b * p1) + oa;
+        const float vv = omb * v0 + b * v1;
+        const float vw = omb * w0 + b * w1;
+        const float t = oa; oa = ob; ob = oc; oc = t;
+        e_pos[k] = vp; e_vel[k] = vv; e_ang[k] = vw;
+        if (i < Jb3) { b_pos[k] = vp; b_vel[k] = vv; b_ang[k] = vw; }
+        if (i < 3) { sm[O(A_ROOT_POS) + i] = vp; sm[O(A_ROOT_VEL) + i] = vv; sm[O(A_ROOT_ANG) + i] = vw; }
       }
-    };
-    vec3(4 * J, A_RG_POS_T, A_RG_POS, A_ROOT_POS, true);
-    vec3(7 * J, A_BODY_VEL_T, A_BODY_VEL, A_ROOT_VEL, false);
-    vec3(10 * J, A_BODY_ANG_T, A_BODY_ANG, A_ROOT_ANG, false);
+    }
     // dof_pos | dof_vel | contact are adjacent in the record
     {
       const int e0 = 13 * J;
-      float* dp = S(A_DOF_POS);
-      float* dv = S(A_DOF_VEL);
-      float* cm = S(A_CONTACT);
+      const int o_dp = O(A_DOF_POS), o_dv = O(A_DOF_VEL) - D, o_cm = O(A_CONTACT) - 2 * D;
       for (int i = lane; i < 2 * D + C; i += 32) {
         const float v = omb * __ldg(r0 + e0 + i) + b * __ldg(r1 + e0 + i);
-        if (i < D) dp[i] = v;
-        else if (i < 2 * D) dv[i - D] = v;
-        else cm[i - 2 * D] = v;
+        sm[(i < D ? o_dp : i < 2 * D ? o_dv : o_cm) + i] = v;
       }
-    }
-    {
-      float* aa = S(A_AA);
-      for (int i = lane; i < 3 * Jb; i += 32) aa[i] = 0.0f;
-      if (lane < 17) S(A_BODIES)[lane] = 0.0f;
     }
   }
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy writes -> visible to the bulk stores
@@ -124,7 +138,7 @@ __global__ void __launch_bounds__(kQ * 32) lookup_kernel(const __grid_constant__
       for (int i = threadIdx.x; i < nq * p.row[t]; i += kQ * 32) g[i] = s[i];
     }
   }
-  if (a < kArr) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");  // the staging rows must outlive the copies
+  if (a < kArr) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");  // the staging rows must outlive the copies' reads
 }
 
 }  // namespace pbhc
