@@ -68,6 +68,7 @@ class Workload:
         self.env_origins, self.motion_ids = h["env_origins"].to(dev), h["motion_ids"].to(dev)
         self.pose_aa, self.trans = h["pose_aa"].to(dev), h["trans"].to(dev)
         self.load_env_state(h)
+        self._fk_stream = None  # side stream of step(): K2 overlaps the all-reduce + finalize tail
         self.ts.bind(self.sim, self.actions, self.torques, self.env_origins, self.motion_ids)
 
     # ---- seeded synthetic inputs (CPU tensors: the CPU oracle consumes the very same bits) -------------------
@@ -122,11 +123,29 @@ class Workload:
         return self.fk_out
 
     def step(self, with_fk=True):
-        """one tracked env step: [K2 FK] + fused lookup/diff/termination/reward/reset/obs/history kernel + finalize."""
-        if with_fk:
+        """one tracked env step: [K2 FK] + fused lookup/diff/termination/reward/reset/obs/history kernel + finalize.
+        K2 does not depend on the fused kernel's results, so it runs on a side stream forked AFTER the fused kernel and
+        its block reduction (the persistent kernel keeps every SM to itself) and joined at the end of the step: the
+        serial tail of the step - the 64-double all-reduce across ranks and the one-warp finalize kernel - hides behind
+        K2 instead of adding to it.  Captured in a CUDA graph this is a fork / join of two branches."""
+        if not with_fk:
+            self.ts.launch()
+            self.ts.finalize()
+            return self.ts.obs_buf_dict, self.ts.rew_buf, self.ts.reset_buf
+        if self._fk_stream is None:
+            self._fk_stream = torch.cuda.Stream(self.device)
+        cur = torch.cuda.current_stream(self.device)
+        import os
+        if os.environ.get("PBHC_FK_FORK") == "before":
+            self._fk_stream.wait_stream(cur)
+            self.ts.launch()
+        else:
+            self.ts.launch()
+            self._fk_stream.wait_stream(cur)
+        with torch.cuda.stream(self._fk_stream):
             self.fk()
-        self.ts.launch()
         self.ts.finalize()
+        cur.wait_stream(self._fk_stream)
         return self.ts.obs_buf_dict, self.ts.rew_buf, self.ts.reset_buf
 
     LAUNCHES_PER_STEP = {"fk": 1, "track": 2, "finalize": 1}
