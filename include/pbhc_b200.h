@@ -360,6 +360,9 @@ typedef struct {
 
 /* number of rows `partials` must have */
 int pbhc_track_max_blocks(void);
+/* what the last pbhc_track_step of this process launched (host-side bookkeeping for benchmarks, not thread-safe):
+ * out4 = {kernel: 0 warp-per-env / 1 tile, blocks, dynamic shared memory bytes, resident blocks per SM} */
+int pbhc_track_launch_info(int32_t* out4);
 /* main kernel + deterministic reduction of the per-block partial sums into io->acc */
 int pbhc_track_step(const PbhcTrackCfg* cfg, const PbhcTableDesc* tab, const PbhcTrackIO* io, int64_t n_envs, void* stream);
 /* advances `scalars` from `acc` (adaptive sigma, average episode length, curricula, log values);

@@ -54,7 +54,7 @@ class Tree(C.Structure):
 _lib = None
 
 EXPORTS = ["pbhc_abi_version", "pbhc_struct_size", "pbhc_last_error", "pbhc_lookup", "pbhc_fk", "pbhc_gae", "pbhc_adv_normalize", "pbhc_clip_prepare",
-           "pbhc_track_max_blocks", "pbhc_track_step", "pbhc_track_finalize", "pbhc_gather_rows", "pbhc_gather_keys", "pbhc_timeout_bootstrap", "pbhc_blend_frames", "pbhc_traj_metrics", "pbhc_pre_physics", "pbhc_compute_torques"]
+           "pbhc_track_max_blocks", "pbhc_track_launch_info", "pbhc_track_step", "pbhc_track_finalize", "pbhc_gather_rows", "pbhc_gather_keys", "pbhc_timeout_bootstrap", "pbhc_blend_frames", "pbhc_traj_metrics", "pbhc_pre_physics", "pbhc_compute_torques"]
 
 
 def lib():

@@ -14,8 +14,9 @@
 // Arithmetic is the reference's unfused fp32 op sequence (-fmad=false): see DESIGN.md "arithmetic parity".
 // Reference: legged_robot_base.py:297-338, 346-380, 408-489, 715-793, 944-1087; motion_tracking.py:330-358,
 // 548-747, 1030-1328; helpers.py:128-152; history_handler.py:33-48 (paths under humanoidverse/envs|utils).
-#include "common.cuh"
-#include "table.cuh"
+
+#include <cstdlib>
+#include "track_common.cuh"
 
 namespace pbhc {
 
@@ -27,64 +28,7 @@ namespace pbhc {
 #endif
 constexpr int kTW = F_TW;
 constexpr int kTrackMaxBlocks = 148 * 8;
-constexpr int kPre = 24;                    // per-env values of the pre phase
 constexpr int kChunk = 16;                  // envs per pre phase (lanes used by it)
-constexpr int kRv = 72;                     // per-env scalar table (see enum Rv)
-constexpr int kFut = 12;                    // per-future-step values staged by the general_tracking future pass
-constexpr int kMaxHistDstPerKey = 4;
-
-enum ObsSrc { S_BASE_LIN_VEL, S_BASE_ANG_VEL, S_PROJ_GRAV, S_DOF_POS, S_DOF_VEL, S_ACTIONS, S_PHASE, S_DIF_LOCAL,
-              S_LOCAL_REF, S_DR_COM, S_DR_MASS, S_DR_KP, S_DR_KD, S_DR_FRICTION, S_DR_DELAY, S_LOCAL_REF_VEL,
-              S_GLOBAL_REF_VEL, S_DIF_JOINT, S_DIF_JOINT_VEL, S_BASE_POS_Z,
-              // LeggedRobotGeneralTracking
-              S_ROLL_PITCH, S_LKEY_POS, S_LKEY_ROT, S_ANCHOR_POS, S_ANCHOR_ROT, S_NEXT_STEP, S_CONTACT_MASK, S_ROOT_HEIGHT,
-              S_DR_BASE_MASS, S_FUT_HEIGHT, S_FUT_RP, S_FUT_LIN, S_FUT_YAW, S_FUT_DOF, S_FUT_KEY };
-static_assert(S_FUT_KEY + 1 == PBHC_NUM_OBS_SRC, "ObsSrc and PBHC_NUM_OBS_SRC disagree");
-enum RewardId { R_CONTACT_MASK, R_MAX_JOINT_POS, R_BODY_POS_EXT, R_VR3, R_FEET_POS, R_BODY_ROT, R_BODY_ANG_VEL,
-                R_BODY_VEL, R_JOINT_POS, R_JOINT_VEL, R_TORQUES, R_ACTION_RATE, R_FEET_AIR_TIME, R_FEET_FORCES,
-                R_STUMBLE, R_SLIPPAGE, R_LIM_DOF_POS, R_LIM_DOF_VEL, R_LIM_TORQUE, R_COLLISION, R_DOF_VEL, R_DOF_ACC,
-                R_FOOT_SLIP, R_ALIVE, R_ORIENTATION, R_CONTACT_MASK_V2,
-                R_ROOT_VEL, R_ANCHOR_POS, R_ANCHOR_ROT, R_LKEY_POS, R_LKEY_ROT, R_KEY_VEL, R_KEY_ANG };
-enum SigmaId { G_MAX_JOINT, G_UPPER, G_LOWER, G_VR3, G_FEET, G_ROT, G_VEL, G_ANG_VEL, G_JOINT_POS, G_JOINT_VEL,
-               G_ROOT_VEL, G_ANCHOR_POS, G_ANCHOR_ROT, G_LKEY_POS, G_LKEY_ROT, G_KEY_VEL, G_KEY_ANG };
-static_assert(G_KEY_ANG + 1 == PBHC_NUM_SIGMA, "SigmaId and PBHC_NUM_SIGMA disagree");
-// per-env scalar table `rv`: slots 0..39 are laid out like `acc` (PBHC_A_*), the rest are raw reward values
-enum Rv { V_SIGMA_ERR = 0, V_UP_N = 17, V_LO_N, V_VR_N, V_JOINT_N, V_T_GRAV, V_T_FAR, V_T_OUT, V_T_END, V_RESET, V_RESET_EPLEN,
-          V_ETR, V_ETR_SQ, V_ONE, V_KEY_N = 32, V_LUP_N, V_LLO_N, V_LVR_N, V_LKEY_N, V_T_REFZ, V_T_ORI, V_T_BODYZ,
-          V_CONTACT = 40, V_CONTACT_V2, V_TQ2, V_DACT2, V_DV2, V_ACC2, V_ORIENT, V_ALIVE, V_AIR, V_FORCE,
-          V_STUMBLE, V_SLIP, V_FSLIP, V_LIM_POS, V_LIM_VEL, V_LIM_TQ, V_COLLIDE, V_ENVF = 60 /* 8 floats */, V_EP = 68 /* int64 */ };
-static_assert(V_UP_N == PBHC_A_UPPER_NORM && V_ONE == PBHC_A_NUM_ENVS && V_KEY_N == PBHC_A_KEY_NORM && V_T_BODYZ == PBHC_A_TERM_BODY_Z &&
-              V_RESET_EPLEN == PBHC_A_RESET_EPLEN && V_ETR_SQ == PBHC_A_ETR_SQ, "rv and acc layouts disagree");
-constexpr int kAccLo = PBHC_A_NUM_ENVS + 1;  // slots [0, kAccLo) are accumulated by lane = slot; general_tracking adds [32, 40)
-enum RewardKind { K_RAW, K_EXP, K_EXP2 };
-// pre-phase values (per env)
-enum Pre { P_F0, P_F1, P_BLEND, P_PHASE, P_HZ, P_HW, P_RPX, P_RPY, P_RPZ, P_BLV, P_BAV = P_BLV + 3, P_PG = P_BAV + 3,
-           P_CLIP = P_PG + 3, P_GRAVN, P_ORIENT, P_ROLL, P_PITCH };
-static_assert(P_PITCH + 1 <= kPre, "pre table too small");
-// general_tracking: per-future-step values (lane s = step s) staged in the idle simulator-state buffer
-enum Fut { F_F0, F_F1, F_BLEND, F_APX, F_APY, F_APZ, F_AQX, F_AQY, F_AQZ, F_AQW };
-static_assert(F_AQW + 1 <= kFut, "future table too small");
-
-__host__ __device__ inline int src_dim(int k, int D, int J, int L, int K = 0, int F = 0) {
-  switch (k) {
-    case S_ROLL_PITCH: case S_CONTACT_MASK: return 2;
-    case S_LKEY_POS: return 3 * K;
-    case S_LKEY_ROT: return 6 * K;
-    case S_ANCHOR_ROT: return 6;
-    case S_NEXT_STEP: return 7 + D + 3 * K;
-    case S_ROOT_HEIGHT: case S_DR_BASE_MASS: return 1;
-    case S_FUT_HEIGHT: case S_FUT_YAW: return F;
-    case S_FUT_RP: return 2 * F;
-    case S_FUT_LIN: return 3 * F;
-    case S_FUT_DOF: return F * D;
-    case S_FUT_KEY: return F * 3 * K;
-    case S_DOF_POS: case S_DOF_VEL: case S_ACTIONS: case S_DR_KP: case S_DR_KD: case S_DIF_JOINT: case S_DIF_JOINT_VEL: return D;
-    case S_DIF_LOCAL: case S_LOCAL_REF: case S_LOCAL_REF_VEL: case S_GLOBAL_REF_VEL: return 3 * J;
-    case S_DR_MASS: return L;
-    case S_PHASE: case S_DR_FRICTION: case S_DR_DELAY: case S_BASE_POS_Z: return 1;
-    default: return 3;
-  }
-}
 
 struct TrackParams {
   PbhcTrackCfg c;
@@ -108,69 +52,6 @@ struct TrackParams {
   int hist_any_mul;                      // some history destination has mul != 1
   int n_hdst_max;                        // max destinations of one history element
 };
-
-__device__ __forceinline__ float warp_sum(float v) {
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-  return v;
-}
-__device__ __forceinline__ float warp_max(float v) {
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
-  return v;
-}
-
-// Sums 16 per-lane values across the warp with 16 shuffles.  Round r keeps, in each lane, the half of the values
-// selected by one lane bit and adds the partner's copy of them; after the xor-16/8/4/2 rounds every lane holds one
-// value index ((lane >> 1) & 15), the xor-1 round completes it.  For each value the additions are the same pairs in
-// the same order as the plain xor butterfly (16, 8, 4, 2, 1), so the results are bit-identical to warp_sum().
-__device__ __forceinline__ float warp_sum16(float (&v)[16], int lane) {
-#pragma unroll
-  for (int half = 8, bit = 16; half >= 1; half >>= 1, bit >>= 1) {
-    const bool upper = (lane & bit) != 0;
-#pragma unroll
-    for (int i = 0; i < half; ++i) {
-      const float send = upper ? v[i] : v[i + half];
-      const float keep = upper ? v[i + half] : v[i];
-      v[i] = keep + __shfl_xor_sync(0xffffffffu, send, bit);
-    }
-  }
-  return v[0] + __shfl_xor_sync(0xffffffffu, v[0], 1);
-}
-
-// Philox4x32-10 (common.cuh), one call per (env, step, stream)
-__device__ __noinline__ uint4 philox(uint4 ctr, uint2 key) { return philox4x32_10(ctr, key); }  // cold (resets, observation noise): out of line so the hot loop stays small
-struct Rng {
-  uint2 key; uint32_t env_lo, env_hi, step;
-  __device__ __forceinline__ uint4 draw(uint32_t stream) const { return philox(make_uint4(env_lo, env_hi, step, stream), key); }
-  __device__ __forceinline__ float uniform(uint32_t stream) const { return u01(draw(stream).x); }
-  __device__ __noinline__ float normal(uint32_t stream) const {
-    const uint4 r = draw(stream);
-    const float u1 = fmaxf(u01(r.x), 1.0f / 16777216.0f), u2 = u01(r.y);
-    return sqrtf(-2.0f * logf(u1)) * cosf(6.283185307179586f * u2);
-  }
-};
-
-// calc_heading_quat_inv (rotations.py:256-268, 296-306) = quat_from_angle_axis(-heading, z) (rotations.py:138-146)
-__device__ __forceinline__ Q4 heading_quat_inv(Q4 q) {
-  const V3 d = quat_rotate(q, {1.0f, 0.0f, 0.0f});
-  const float heading = atan2f(d.y, d.x);
-  const float theta = (-heading) / 2.0f;
-  // normalize(axis) with axis = (0,0,1): x / norm.clamp(1e-9) = (0,0,1); xyz = axis * sin(theta); w = cos(theta)
-  const float sz = 1.0f * sinf(theta), w = cosf(theta);
-  const float n = fmaxf(norm4(0.0f * sinf(theta), 0.0f * sinf(theta), sz, w), 1e-9f);
-  return {0.0f / n, 0.0f / n, sz / n, w / n};
-}
-
-// my_quat_rotate(q, v) for q = (0, 0, z, w) - the heading quaternion.  Same expression tree as quat_rotate_impl with
-// the terms that multiply q.x = q.y = 0 dropped: they are exact zeros, so only the sign of a zero result can differ.
-__device__ __forceinline__ V3 quat_rotate_z(float qz, float qw, V3 v) {
-  const float s = 2.0f * (qw * qw) - 1.0f;
-  const V3 a = {v.x * s, v.y * s, v.z * s};
-  const V3 b = {(0.0f - qz * v.y) * qw * 2.0f, (qz * v.x) * qw * 2.0f, 0.0f};
-  const float d = qz * v.z;
-  return {a.x + b.x, a.y + b.y, a.z + qz * d * 2.0f};
-}
 
 // block-level tables (built once per block from the launch parameters)
 struct BlockTables {
@@ -1350,10 +1231,18 @@ __global__ void track_finalize_kernel(const __grid_constant__ PbhcTrackCfg c, co
 
 
 static int g_track_blocks_per_sm = 0;
+int track_tile_launch(const PbhcTrackCfg& c, const PbhcTableDesc& tab, const PbhcTrackIO& io, int64_t n, cudaStream_t stream, int* blocks_out);  // track_tile.cu
 
 }  // namespace pbhc
 
 extern "C" int pbhc_track_max_blocks(void) { return pbhc::kTrackMaxBlocks; }
+
+namespace pbhc { int g_track_info[4] = {0, 0, 0, 0}; }  // kernel (0 warp-per-env, 1 tile), blocks, dynamic shared memory, resident blocks / SM
+extern "C" int pbhc_track_launch_info(int32_t* out4) {
+  if (!out4) return PBHC_E_BADARG;
+  for (int i = 0; i < 4; ++i) out4[i] = pbhc::g_track_info[i];
+  return PBHC_OK;
+}
 
 extern "C" int pbhc_track_step(const PbhcTrackCfg* cfg, const PbhcTableDesc* tab, const PbhcTrackIO* io, int64_t n, void* stream) {
   using namespace pbhc;
@@ -1372,6 +1261,7 @@ extern "C" int pbhc_track_step(const PbhcTrackCfg* cfg, const PbhcTableDesc* tab
                         io->action_delay_idx, io->episode_sums, io->scalars, io->rew_buf, io->reset_buf, io->time_out_buf,
                         io->last_episode_sums, io->partials, io->acc};
   for (const void* p : need) if (!p) { set_error("pbhc_track_step: a required PbhcTrackIO pointer is NULL"); return PBHC_E_BADARG; }
+  if (c.L < 0 || c.L > 48) { set_error("pbhc_track_step: L outside [0, 48]"); return PBHC_E_RANGE; }
   if ((c.L > 0 && !io->link_mass_scale) || (c.hist_row > 0 && !io->hist)) { set_error("pbhc_track_step: NULL link_mass_scale / hist"); return PBHC_E_BADARG; }
   for (int g = 0; g < c.n_groups; ++g) if (!io->obs[g] || c.group_dim[g] <= 0) { set_error("pbhc_track_step: NULL / empty obs group %d", g); return PBHC_E_BADARG; }
   if (((uintptr_t)tab->records & 15) || ((uintptr_t)io->dof_state & 7) || ((uintptr_t)io->env_f32 & 15) ||
@@ -1437,8 +1327,30 @@ extern "C" int pbhc_track_step(const PbhcTrackCfg* cfg, const PbhcTableDesc* tab
   }
   for (int k = 0; k < c.n_hist_keys; ++k) if (c.hist_len[k] <= 0 || c.hist_dim[k] != src_dim(c.hist_src[k], c.D, c.J, c.L, c.n_key, c.n_future)) { set_error("pbhc_track_step: bad history key %d", k); return PBHC_E_BADARG; }
   if (n == 0) return PBHC_OK;
+  // LeggedRobotMotionTracking runs on the tile kernel (csrc/track_tile.cu); the warp-per-env kernel below serves
+  // LeggedRobotGeneralTracking and the configs the tile kernel does not take (a body- or joint-difference source kept in
+  // the history; PBHC_TRACK_KERNEL=warp forces it for A/B measurements)
+  if (!c.general) {
+    static const bool force_warp = [] { const char* e = getenv("PBHC_TRACK_KERNEL"); return e && e[0] == 'w'; }();
+    bool tile_ok = !force_warp && c.n_feet >= 1;
+    for (int k = 0; k < c.n_hist_keys; ++k) {
+      const int s = c.hist_src[k];
+      if (s == S_DIF_LOCAL || s == S_LOCAL_REF || s == S_LOCAL_REF_VEL || s == S_GLOBAL_REF_VEL || s == S_DIF_JOINT || s == S_DIF_JOINT_VEL) tile_ok = false;
+    }
+    if (tile_ok) {
+      int blocks = 0;
+      const int rc = track_tile_launch(c, *tab, *io, n, (cudaStream_t)stream, &blocks);
+      if (rc != PBHC_OK) return rc;
+      track_reduce_kernel<<<1, kReduceGroups * PBHC_ACC, 0, (cudaStream_t)stream>>>(io->partials, blocks, io->acc);
+      return check_launch("pbhc_track_step");
+    }
+  }
   P.dump = P.rows_len;                                   // scratch for absent destinations: one source wide
-  const int dump_len = up4h(3 * c.J + 4);
+  // (widest source: 3*J body features, 6*n_key key-body rotations, 7+D+3K next-step block, L link masses, 64 history lanes)
+  int widest = 3 * c.J + 4;
+  for (int k = 0; k < PBHC_NUM_OBS_SRC; ++k) { const int w = src_dim(k, c.D, c.J, c.L, c.n_key, 0); if (w > widest) widest = w; }
+  if (widest < 64) widest = 64;
+  const int dump_len = up4h(widest);
   // per-warp layout: the fixed-size tables first, so that the kernel reaches rv / pre / the staging buffer with
   // compile-time offsets from one base register
   P.sm_rv = 0;
@@ -1488,6 +1400,7 @@ extern "C" int pbhc_track_step(const PbhcTrackCfg* cfg, const PbhcTableDesc* tab
   int64_t blocks = (n + kTW - 1) / kTW;
   const int64_t cap = 148LL * g_track_blocks_per_sm;
   if (blocks > cap) blocks = cap;
+  g_track_info[0] = 0; g_track_info[1] = (int)blocks; g_track_info[2] = (int)shmem; g_track_info[3] = g_track_blocks_per_sm;
   kern<<<(unsigned)blocks, kTW * 32, shmem, (cudaStream_t)stream>>>(P);
   track_reduce_kernel<<<1, kReduceGroups * PBHC_ACC, 0, (cudaStream_t)stream>>>(io->partials, (int)blocks, io->acc);
   return check_launch("pbhc_track_step");
