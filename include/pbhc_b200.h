@@ -9,7 +9,9 @@
  */
 #ifndef PBHC_B200_H
 #define PBHC_B200_H
+#ifndef __CUDACC_RTC__ /* NVRTC compiles the kernels without host headers; the fixed-width types are typedef'd by the includer */
 #include <stdint.h>
+#endif
 #ifdef __cplusplus
 extern "C" {
 #endif
@@ -361,8 +363,13 @@ typedef struct {
 /* number of rows `partials` must have */
 int pbhc_track_max_blocks(void);
 /* what the last pbhc_track_step of this process launched (host-side bookkeeping for benchmarks, not thread-safe):
- * out4 = {kernel: 0 warp-per-env / 1 tile, blocks, dynamic shared memory bytes, resident blocks per SM} */
+ * out4 = {kernel: 0 warp-per-env / 1 tile (generic) / 2 tile (specialised for the config), blocks, dynamic shared memory bytes, resident blocks per SM} */
 int pbhc_track_launch_info(int32_t* out4);
+/* Optional warm-up: compiles the kernel specialised for this env config into the on-disk cache (NVRTC, no GPU and no
+ * device memory needed: of `tab` only the dimensions and of `io` only default_dof_stride and the NULL-ness of the
+ * optional outputs are read).  pbhc_track_step does the same lazily on its first launch of a config and falls back to
+ * the generic kernel when NVRTC is unavailable; < 0 here just means "no specialised kernel". */
+int pbhc_track_specialize(const PbhcTrackCfg* cfg, const PbhcTableDesc* tab, const PbhcTrackIO* io);
 /* main kernel + deterministic reduction of the per-block partial sums into io->acc */
 int pbhc_track_step(const PbhcTrackCfg* cfg, const PbhcTableDesc* tab, const PbhcTrackIO* io, int64_t n_envs, void* stream);
 /* advances `scalars` from `acc` (adaptive sigma, average episode length, curricula, log values);

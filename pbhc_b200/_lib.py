@@ -54,7 +54,7 @@ class Tree(C.Structure):
 _lib = None
 
 EXPORTS = ["pbhc_abi_version", "pbhc_struct_size", "pbhc_last_error", "pbhc_lookup", "pbhc_fk", "pbhc_gae", "pbhc_adv_normalize", "pbhc_clip_prepare",
-           "pbhc_track_max_blocks", "pbhc_track_launch_info", "pbhc_track_step", "pbhc_track_finalize", "pbhc_gather_rows", "pbhc_gather_keys", "pbhc_timeout_bootstrap", "pbhc_blend_frames", "pbhc_traj_metrics", "pbhc_pre_physics", "pbhc_compute_torques"]
+           "pbhc_track_max_blocks", "pbhc_track_launch_info", "pbhc_track_specialize", "pbhc_track_step", "pbhc_track_finalize", "pbhc_gather_rows", "pbhc_gather_keys", "pbhc_timeout_bootstrap", "pbhc_blend_frames", "pbhc_traj_metrics", "pbhc_pre_physics", "pbhc_compute_torques"]
 
 
 def lib():
@@ -222,3 +222,7 @@ def bind_track(L):
     L.pbhc_track_step.argtypes = [C.POINTER(TrackCfg), C.POINTER(TableDesc), C.POINTER(TrackIO), C.c_int64, C.c_void_p]
     L.pbhc_track_finalize.restype = C.c_int
     L.pbhc_track_finalize.argtypes = [C.POINTER(TrackCfg), C.c_void_p, C.c_void_p, C.c_void_p]
+    L.pbhc_track_specialize.restype = C.c_int
+    L.pbhc_track_specialize.argtypes = [C.POINTER(TrackCfg), C.POINTER(TableDesc), C.POINTER(TrackIO)]
+    L.pbhc_track_launch_info.restype = C.c_int
+    L.pbhc_track_launch_info.argtypes = [C.POINTER(C.c_int32 * 4)]

@@ -2,14 +2,21 @@
 // roundings exactly like the reference's unfused torch ops; explicit __fmaf_rn marks the places
 // where ATen itself fuses (vector norm).
 #pragma once
+#ifdef __CUDACC_RTC__  // NVRTC (csrc/jit.cu): no host headers
+typedef signed char int8_t; typedef unsigned char uint8_t; typedef int int32_t; typedef unsigned int uint32_t;
+typedef long long int64_t; typedef unsigned long long uint64_t; typedef unsigned long long uintptr_t;
+#else
 #include <cuda_runtime.h>
 #include <stdint.h>
+#endif
 #include "../../include/pbhc_b200.h"
 
 namespace pbhc {
 
+#ifndef __CUDACC_RTC__
 void set_error(const char* fmt, ...);
 int check_launch(const char* what);
+#endif
 
 struct Q4 { float x, y, z, w; };  // xyzw
 struct V3 { float x, y, z; };

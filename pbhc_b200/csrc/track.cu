@@ -1232,6 +1232,7 @@ __global__ void track_finalize_kernel(const __grid_constant__ PbhcTrackCfg c, co
 
 static int g_track_blocks_per_sm = 0;
 int track_tile_launch(const PbhcTrackCfg& c, const PbhcTableDesc& tab, const PbhcTrackIO& io, int64_t n, cudaStream_t stream, int* blocks_out);  // track_tile.cu
+int track_tile_prepare(const PbhcTrackCfg& c, const PbhcTableDesc& tab, const PbhcTrackIO& io);
 
 }  // namespace pbhc
 
@@ -1242,6 +1243,12 @@ extern "C" int pbhc_track_launch_info(int32_t* out4) {
   if (!out4) return PBHC_E_BADARG;
   for (int i = 0; i < 4; ++i) out4[i] = pbhc::g_track_info[i];
   return PBHC_OK;
+}
+
+extern "C" int pbhc_track_specialize(const PbhcTrackCfg* cfg, const PbhcTableDesc* tab, const PbhcTrackIO* io) {
+  if (!cfg || !tab || !io) { pbhc::set_error("pbhc_track_specialize: null argument"); return PBHC_E_BADARG; }
+  if (cfg->general) return PBHC_OK;  // (LeggedRobotGeneralTracking runs on the generic warp-per-env kernel)
+  return pbhc::track_tile_prepare(*cfg, *tab, *io);
 }
 
 extern "C" int pbhc_track_step(const PbhcTrackCfg* cfg, const PbhcTableDesc* tab, const PbhcTrackIO* io, int64_t n, void* stream) {

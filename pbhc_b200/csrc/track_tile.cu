@@ -1,62 +1,94 @@
 // track_tile.cu - K3 for LeggedRobotMotionTracking (config A/B): the fused env step as a TILE kernel.
 //
-// A block owns a tile of kTE = 8 consecutive envs per iteration of a grid-stride loop.  Every per-env array of the step
-// ([N, row] tensors) is one contiguous slab for such a tile, so the whole input of a tile (rigid-body state, contact
-// forces, dof state, actions, gains, history ring, episode sums, per-env scalars: ~3.9 KB / env) arrives in shared
-// memory by ~20 TMA bulk copies (cp.async.bulk + mbarrier, issued by the lanes of one warp from a descriptor table) and
-// the whole output (observation rows assembled in their final layout, rewards, episode sums, state: ~4.6 KB / env)
-// leaves by ~10 bulk stores; the next tile's loads are issued as soon as the inputs are dead, before the stores.
-// No lane spends an instruction on moving simulator state or observation rows.
+// A block owns a tile of kTE = 8 consecutive envs per iteration of a grid-stride loop, one warp per env.  Every per-env
+// array of the step ([N, row] tensors) is one contiguous slab for such a tile, so the whole input of a tile (rigid-body
+// state, contact forces, dof state, actions, gains, history ring, episode sums, per-env scalars: ~3.9 KB / env) arrives
+// in shared memory by ~20 TMA bulk copies (cp.async.bulk + mbarrier, issued by the lanes of one warp from a descriptor
+// table) and the whole output (observation rows assembled in their final layout, rewards, episode sums, state:
+// ~4.6 KB / env) leaves by ~10 bulk stores; the next tile's loads are issued as soon as the inputs are dead, before the
+// stores.  No lane spends an instruction on moving simulator state or observation rows.
 //
-// Work is mapped as FLAT ITEMS over the tile so that all 32 lanes of a warp are busy: (env, body), (env, dof),
-// (env, reward), (env, feature) ...; per-env reductions go through small per-item tables in shared memory that one
-// thread per (env, sum) adds up in index order (deterministic, no shuffles, no atomics on floats).  Block-wide phases:
-//   1 pre (frame pair / blend, root-frame velocities, gravity, heading) + history ring -> observation rows
-//   2 dofs, extended bodies, feet                    3 bodies (+ dof sums)
-//   4 body sums, per-env scalars / termination, scalar features      5 rewards + episode sums
-//   6 per-env state, resets (warp per env, rare)      7 bulk stores, next tile's loads, cross-env sums (fp64)
+// Between the two block barriers of a tile (inputs arrived / outputs complete) the warps are independent: warp e runs
+// env e start to finish - history ring -> rows, dofs (lane = dof), bodies (lane = body), feet, termination, rewards
+// (lane = term), scalar features, state / reset - with per-env reductions through a small scratch row in shared memory
+// (three lanes per sum, no 16-value shuffle butterflies).  The work that is scalar per env (frame pair / blend,
+// root-frame velocities, projected gravity, heading quaternion) is split into pieces, piece w computed by warp w for
+// all 8 envs of the NEXT tile (lane = env) from double-buffered copies of the small per-env inputs, so it is amortised
+// over lanes and off the critical path.
 //
 // Arithmetic: this file is compiled with FMA contraction allowed.  The chains that feed bit-exact results - frame
-// indices / blend, motion_end, the gravity and motion_far comparisons - are written with __fmul_rn / __fadd_rn
-// (exact.cuh-style helpers below) and reproduce the reference's unfused fp32 sequence; everything else is checked
-// against the reference within 1e-5 rel / 1e-6 abs.  See DESIGN.md "arithmetic parity".
+// indices / blend, motion_end, the gravity and motion_far comparisons, the slerp branch decisions, simulator state
+// written at resets - use __fmul_rn / __fadd_rn and reproduce the reference's unfused fp32 sequence; everything else is
+// checked against the reference within 1e-5 rel / 1e-6 abs.  See DESIGN.md "arithmetic parity".
 // Reference: legged_robot_base.py:297-338, 346-380, 408-489, 715-793, 944-1087; motion_tracking.py:330-358,
 // 548-747, 1030-1328; helpers.py:128-152; history_handler.py:33-48 (paths under humanoidverse/envs|utils).
+#ifndef __CUDACC_RTC__
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <unordered_map>
+#endif
 #include "track_common.cuh"
 
 namespace pbhc {
 
 constexpr int kTE = 8;             // envs per tile = warps per block
 constexpr int kNT = kTE * 32;
-constexpr int kMaxIn = 24, kMaxOut = 16;
-constexpr int kBodyRaw = 5;        // per-(env, body) values the body sums are made of
-constexpr int kDofRaw = 9;         // per-(env, dof) values the dof sums are made of
-constexpr int kRvT = 80;           // per-env scalar table: [0, 57) = enum Rv, then the per-foot values
+constexpr int kMaxIn = 20, kMaxSmall = 4, kMaxOut = 16;
+constexpr int kBodyRaw = 5;        // per-body values the body sums are made of
+constexpr int kDofRaw = 9;         // per-dof values the dof sums are made of
+constexpr int kRvT = 60;           // per-env scalar table: [0, 57) = enum Rv
 constexpr int kSrcT = S_BASE_POS_Z + 1;  // observation sources of LeggedRobotMotionTracking
-enum RvTile { V_FOOT = 57 /* 2 x 8 */, V_AIR0 = 73, V_AIR1, V_CONT0, V_CONT1 };
-enum FootVal { FV_AIR, FV_FORCE, FV_SLIP, FV_FSLIP, FV_CM, FV_STUMBLE, FV_AIRF, FV_CONTACT };
 enum BodyRaw { BR_MPOS, BR_NRM, BR_ROT, BR_VEL, BR_ANG };
 enum DofRaw { DR_DJA, DR_DJV2, DR_TQ2, DR_DACT2, DR_DV2, DR_ACC2, DR_LPOS, DR_LVEL, DR_LTQ };
 constexpr int kBodySums = 10;
+constexpr int kPieces = 5;         // pieces of the per-env scalar pre-computation
 
-struct TileDesc { const char* g; int row_bytes, g_stride, soff, pad; };  // one per-env array: global rows -> slab at byte offset soff
+struct TileDesc { const char* g; int row_bytes, g_stride, soff, soff2; };  // one per-env array: global rows -> slab at byte offset soff (soff2: second buffer)
+
+// Launch constants of the hot loop.  The generic (ahead-of-time) kernel reads them from the launch parameters; the
+// specialised kernel (jit.cu: the same source compiled by NVRTC for one env config) sees them as compile-time constants
+// from a generated header, so shapes, shared-memory offsets and config flags fold into immediates and dead branches.
+#define PBHC_HOTK_INT(X) \
+  X(J) X(Jb) X(D) X(L) X(H) X(n_ext) X(n_feet) X(n_groups) X(R) X(n_sums) X(n_hd) X(hist_any_mul) X(has_air_time) X(n_feat) \
+  X(contact_size) X(rec_stride) X(use_vec_reward) X(only_positive) X(has_termination) X(cur_torque_enable) X(term_gravity) \
+  X(term_motion_far) X(term_motion_end) X(dif_joint_used) X(ref_vel_used) X(ref_pos_out) X(ref_rot_out) X(default_dof_stride) \
+  X(e_pos) X(e_vel) X(e_ang) X(e_dp) X(e_dv) X(e_c) \
+  X(o_bar) X(o_tab) X(o_hmap) X(o_hmul) X(o_rv) X(o_pre) X(o_rows) X(o_scr) X(scr_pitch) \
+  X(i_body) X(i_cf) X(i_hist) X(i_dof) X(i_act) X(i_tq) X(i_lact) X(i_ldv) X(i_kp) X(i_kd) X(i_es) X(i_org) X(i_com) X(i_fric) \
+  X(i_delay) X(i_mass) X(i_root0) X(i_root1) X(i_ep0) X(i_ep1) X(i_envf0) X(i_envf1) X(i_mid0) X(i_mid1) \
+  X(q_rew) X(q_es) X(q_envf) X(q_ep) X(q_reset) X(q_lact) X(q_ldpos) X(q_ldvel) \
+  X(row_base0) X(row_base1) X(row_base2) X(row_base3) X(gdim0) X(gdim1) X(gdim2) X(gdim3) X(ghist0) X(ghist1) X(ghist2) X(ghist3)
+#define PBHC_HOTK_FLT(X) X(dt) X(clip_obs) X(term_gravity_thr) X(w_lower) X(w_upper) X(termination_scale) X(desired_feet_air_time) X(max_contact_force)
+#define PBHC_HOTK_I64(X) X(max_episode_length) X(penalised_mask)
+struct HotK {
+#define X(n) int n;
+  PBHC_HOTK_INT(X)
+#undef X
+#define X(n) float n;
+  PBHC_HOTK_FLT(X)
+#undef X
+#define X(n) long long n;
+  PBHC_HOTK_I64(X)
+#undef X
+};
 
 struct TileParams {
   PbhcTrackCfg c;
   PbhcTableDesc tab;
   PbhcTrackIO io;
-  int n, n_tiles, n_in, n_out, bulk_ok, in_bytes;
-  TileDesc in[kMaxIn], out[kMaxOut];
-  int o_bar, o_flags, o_tab, o_hmap, o_hmul, o_rv, o_pre, o_rows;   // byte offsets of the fixed regions
-  int i_body, i_cf, i_hist, i_dof, i_act, i_tq, i_lact, i_ldv, i_kp, i_kd, i_es, i_envf, i_root, i_org, i_ep, i_mid, i_com,
-      i_fric, i_delay, i_mass;                                       // input slabs
-  int q_rew, q_es, q_envf, q_ep, q_reset, q_lact, q_ldpos, q_ldvel;  // output slabs (the obs groups are at o_rows + 4 * row_base[g])
-  int o_dpart, o_ext, o_bpart, o_rw;                                 // scratch: aliases of dead input slabs
-  int row_base[PBHC_MAX_OBS_GROUPS];                                 // float offset of group g's slab inside the rows region
+  HotK k;
+  int n, n_tiles, n_in, n_small, n_out, bulk_ok, in_bytes, small_bytes;
+  TileDesc in[kMaxIn], small[kMaxSmall], out[kMaxOut];
   int hist_base[PBHC_MAX_HIST_KEYS];
-  int e_pos, e_vel, e_ang, e_dp, e_dv, e_c;
-  int has_air_time, hist_any_mul, n_hd, inv_j, inv_d, inv_r, inv_f, n_cols, n_feat;
 };
+
+#ifdef PBHC_SPEC
+#include "track_spec.h"   // namespace spec { constexpr ... } generated for one env config (jit.cu)
+#define KC(n) (spec::n)
+#else
+#define KC(n) (P.k.n)
+#endif
 
 // ---- exact (unfused) arithmetic for the bit-exact chains --------------------------------------------------------------
 __device__ __forceinline__ float xm(float a, float b) { return __fmul_rn(a, b); }
@@ -92,7 +124,6 @@ __device__ __forceinline__ float div3(float x) {
   const float q = x * 0.333333343f;
   return __fmaf_rn(__fmaf_rn(-3.0f, q, x), 0.333333343f, q);
 }
-
 // slerp (isaac_utils/rotations.py:210-232): the dot product and sin_half_theta decide the branches, so they keep the
 // reference's unfused operation order; the interpolation itself may contract
 __device__ __forceinline__ Q4 slerp_t(Q4 a, Q4 b, float t) {
@@ -110,68 +141,79 @@ __device__ __forceinline__ Q4 slerp_t(Q4 a, Q4 b, float t) {
 }
 
 // ---- block tables ---------------------------------------------------------------------------------------------------
-struct SrcDst { int n; int base[PBHC_MAX_OBS_GROUPS]; int stride[PBHC_MAX_OBS_GROUPS]; int grp[PBHC_MAX_OBS_GROUPS]; int push; };
+// where one observation source goes: up to four obs groups {slab offset, env stride} and its history push slot
+struct alignas(16) SrcDst { int base0, stride0, base1, stride1, base2, stride2, base3, stride3; int n, push, grp, pad; };
 struct TileTables {
   float sigma[PBHC_NUM_SIGMA];
   float far_thr;
   uint32_t push_count;
+  uint32_t noise_mask;
   float lim_lo[PBHC_MAX_DOF], lim_hi[PBHC_MAX_DOF], lim_vel[PBHC_MAX_DOF], lim_tq[PBHC_MAX_DOF];
   float r_scale[PBHC_MAX_REWARDS], r_pen[PBHC_MAX_REWARDS], r_sigma[PBHC_MAX_REWARDS];
-  int r_kind[PBHC_MAX_REWARDS], r_arg[PBHC_MAX_REWARDS];
+  signed char r_kind[PBHC_MAX_REWARDS], r_arg[PBHC_MAX_REWARDS];
   uint64_t bs_mask[kBodySums];
-  int bs_raw[kBodySums], bs_slot[kBodySums];
+  signed char bs_raw[kBodySums + 2], bs_slot[kBodySums + 2];
   float bs_div[kBodySums];
   SrcDst sd[kSrcT];
   float obs_scale[kSrcT], obs_noise[kSrcT];
-  uint32_t noise_mask;
-  int gdim[PBHC_MAX_OBS_GROUPS];
-  int feat_src[64], feat_el[64];   // scalar feature i of an env: source and element
+  unsigned char feat_src[64], feat_el[64];   // scalar feature i of an env: source and element
 };
 
 struct NoiseKeyT { uint64_t seed; int64_t env; uint32_t step; };
-struct Rows { float* rows; float* ghist; };   // observation slabs (shared) and the env's global history row
+struct Rows { float* rows; float* ghist; int e; };   // observation slabs (shared), the env's global history row, tile-local env
 
 __device__ __forceinline__ float clampf(float v, float c) { return fminf(fmaxf(v, -c), c); }
 
 // (value + U(-1,1) * noise) * scale with an independent draw per destination (helpers.py:128-152)
-__device__ __noinline__ void emit_noisy_t(const TileTables& T, const Rows& R, int k, int e, int el, float raw, float clip, const NoiseKeyT& nk) {
+__device__ __noinline__ void emit_noisy_t(const TileTables& T, const Rows& R, int k, int el, float raw, float clip, const NoiseKeyT& nk) {
   const Rng rng = {make_uint2((uint32_t)nk.seed, (uint32_t)(nk.seed >> 32)), (uint32_t)nk.env, (uint32_t)((uint64_t)nk.env >> 32), nk.step};
   const uint32_t st = 4096u + ((uint32_t)k * 256u + (uint32_t)el) * 2u;
   const uint4 a = rng.draw(st);
   const uint32_t b = rng.draw(st + 1u).x;
   const float ns = T.obs_noise[k], sc = T.obs_scale[k];
   const SrcDst& d = T.sd[k];
+  const int base[4] = {d.base0, d.base1, d.base2, d.base3}, stride[4] = {d.stride0, d.stride1, d.stride2, d.stride3};
   for (int i = 0; i < d.n; ++i) {
-    const int g = d.grp[i];
+    const int g = (d.grp >> (8 * i)) & 0xff;
     const uint32_t bits = g == 0 ? a.x : g == 1 ? a.y : g == 2 ? a.z : a.w;
-    R.rows[d.base[i] + e * d.stride[i] + el] = clampf((raw + (u01(bits) * 2.0f - 1.0f) * ns) * sc, clip);
+    R.rows[base[i] + R.e * stride[i] + el] = clampf((raw + (u01(bits) * 2.0f - 1.0f) * ns) * sc, clip);
   }
   if (d.push >= 0) R.ghist[d.push + el] = (raw + (u01(b) * 2.0f - 1.0f) * ns) * sc;
 }
-// one element of observation source k of env e (tile-local) to every row that shows it (clipped) and to the history ring
+// one element of observation source k to every row that shows it (clipped) and to the history ring (unclipped)
 template <bool kNoise>
-__device__ __forceinline__ void emit1(const TileTables& T, const Rows& R, int k, int e, int el, float raw, float clip, const NoiseKeyT& nk) {
-  if (kNoise && ((T.noise_mask >> k) & 1u)) { emit_noisy_t(T, R, k, e, el, raw, clip, nk); return; }
+__device__ __forceinline__ void emit1(const TileTables& T, const Rows& R, int k, int el, float raw, float clip, const NoiseKeyT& nk) {
+  if (kNoise && ((T.noise_mask >> k) & 1u)) { emit_noisy_t(T, R, k, el, raw, clip, nk); return; }
   const SrcDst& d = T.sd[k];
+  const int4 a = *reinterpret_cast<const int4*>(&d.base0);
+  const int2 np = *reinterpret_cast<const int2*>(&d.n);
   const float sv = raw * T.obs_scale[k], cv = clampf(sv, clip);
-  for (int i = 0; i < d.n; ++i) R.rows[d.base[i] + e * d.stride[i] + el] = cv;
-  if (d.push >= 0) R.ghist[d.push + el] = sv;
+  float* r = R.rows + el;
+  if (np.x > 0) r[a.x + R.e * a.y] = cv;
+  if (np.x > 1) r[a.z + R.e * a.w] = cv;
+  if (np.x > 2) { r[d.base2 + R.e * d.stride2] = cv; if (np.x > 3) r[d.base3 + R.e * d.stride3] = cv; }
+  if (np.y >= 0) R.ghist[np.y + el] = sv;
 }
 template <bool kNoise>
-__device__ __forceinline__ void emit3(const TileTables& T, const Rows& R, int k, int e, int el, float x, float y, float z, float clip, const NoiseKeyT& nk) {
+__device__ __forceinline__ void emit3(const TileTables& T, const Rows& R, int k, int el, float x, float y, float z, float clip, const NoiseKeyT& nk) {
   if (kNoise && ((T.noise_mask >> k) & 1u)) {
-    emit_noisy_t(T, R, k, e, el, x, clip, nk); emit_noisy_t(T, R, k, e, el + 1, y, clip, nk); emit_noisy_t(T, R, k, e, el + 2, z, clip, nk);
+    emit_noisy_t(T, R, k, el, x, clip, nk); emit_noisy_t(T, R, k, el + 1, y, clip, nk); emit_noisy_t(T, R, k, el + 2, z, clip, nk);
     return;
   }
   const SrcDst& d = T.sd[k];
+  const int4 a = *reinterpret_cast<const int4*>(&d.base0);
+  const int2 np = *reinterpret_cast<const int2*>(&d.n);
   const float sc = T.obs_scale[k];
   const float sx = x * sc, sy = y * sc, sz = z * sc;
   const float cx = clampf(sx, clip), cy = clampf(sy, clip), cz = clampf(sz, clip);
-  for (int i = 0; i < d.n; ++i) {
-    float* r = R.rows + d.base[i] + e * d.stride[i] + el;
-    r[0] = cx; r[1] = cy; r[2] = cz;
+  float* r = R.rows + el;
+  if (np.x > 0) { float* o = r + a.x + R.e * a.y; o[0] = cx; o[1] = cy; o[2] = cz; }
+  if (np.x > 1) { float* o = r + a.z + R.e * a.w; o[0] = cx; o[1] = cy; o[2] = cz; }
+  if (np.x > 2) {
+    { float* o = r + d.base2 + R.e * d.stride2; o[0] = cx; o[1] = cy; o[2] = cz; }
+    if (np.x > 3) { float* o = r + d.base3 + R.e * d.stride3; o[0] = cx; o[1] = cy; o[2] = cz; }
   }
-  if (d.push >= 0) { float* h = R.ghist + d.push + el; h[0] = sx; h[1] = sy; h[2] = sz; }
+  if (np.y >= 0) { float* h = R.ghist + np.y + el; h[0] = sx; h[1] = sy; h[2] = sz; }
 }
 
 // ---- TMA / mbarrier ---------------------------------------------------------------------------------------------------
@@ -196,6 +238,8 @@ __device__ __forceinline__ void fence_async() { asm volatile("fence.proxy.async.
 __device__ void build_tile_tables(const TileParams& P, TileTables& T, int* hmap, float* hmul, const double* scal_g, double* scal) {
   const PbhcTrackCfg& c = P.c;
   const int tid = threadIdx.x, nt = blockDim.x;
+  auto row_base = [&](int g) { return g == 0 ? KC(row_base0) : g == 1 ? KC(row_base1) : g == 2 ? KC(row_base2) : KC(row_base3); };
+  auto ghist = [&](int g) { return g == 0 ? KC(ghist0) : g == 1 ? KC(ghist1) : g == 2 ? KC(ghist2) : KC(ghist3); };
   for (int i = tid; i < PBHC_SCALARS; i += nt) scal[i] = scal_g[i];
   __syncthreads();
   const uint64_t push_count = (uint64_t)scal[PBHC_S_PUSH_COUNT];
@@ -248,7 +292,7 @@ __device__ void build_tile_tables(const TileParams& P, TileTables& T, int* hmap,
       }
       if (kind != K_RAW) sig = (float)scal[PBHC_S_SIGMA + arg];
     }
-    T.r_kind[tid] = kind; T.r_arg[tid] = arg; T.r_sigma[tid] = sig;
+    T.r_kind[tid] = (signed char)kind; T.r_arg[tid] = (signed char)arg; T.r_sigma[tid] = sig;
     T.r_scale[tid] = tid < c.n_rewards ? c.reward_scale[tid] : 0.0f;
     T.r_pen[tid] = (tid < c.n_rewards && c.reward_is_penalty[tid]) ? (float)scal[PBHC_S_PENALTY] : 1.0f;
   }
@@ -269,14 +313,16 @@ __device__ void build_tile_tables(const TileParams& P, TileTables& T, int* hmap,
       case 8: m = c.lower_mask; raw = BR_NRM; slot = V_LO_N; break;
       default: m = c.vr3_mask; raw = BR_NRM; slot = V_VR_N; break;
     }
-    T.bs_mask[tid] = m & all; T.bs_raw[tid] = raw; T.bs_slot[tid] = slot; T.bs_div[tid] = div;
+    T.bs_mask[tid] = m & all; T.bs_raw[tid] = (signed char)raw; T.bs_slot[tid] = (signed char)slot; T.bs_div[tid] = div;
   }
   if (tid < kSrcT) {
+    int base[4] = {0, 0, 0, 0}, stride[4] = {0, 0, 0, 0};
     SrcDst d;
-    d.n = 0; d.push = -1;
-    for (int g = 0; g < PBHC_MAX_OBS_GROUPS; ++g) { d.base[g] = 0; d.stride[g] = 0; d.grp[g] = 0; }
+    d.n = 0; d.push = -1; d.grp = 0; d.pad = 0;
     for (int g = 0; g < c.n_groups; ++g)
-      if (c.src_dst[tid][g] >= 0) { d.base[d.n] = P.row_base[g] + c.src_dst[tid][g]; d.stride[d.n] = c.group_dim[g]; d.grp[d.n] = g; ++d.n; }
+      if (c.src_dst[tid][g] >= 0) { base[d.n] = row_base(g) + c.src_dst[tid][g]; stride[d.n] = c.group_dim[g]; d.grp |= g << (8 * d.n); ++d.n; }
+    d.base0 = base[0]; d.stride0 = stride[0]; d.base1 = base[1]; d.stride1 = stride[1];
+    d.base2 = base[2]; d.stride2 = stride[2]; d.base3 = base[3]; d.stride3 = stride[3];
     for (int h = 0; h < c.n_hist_keys; ++h)
       if (c.hist_src[h] == tid) {  // ring push: one slot per key (HistoryHandler.add, history_handler.py:40-44)
         const int len = c.hist_len[h];
@@ -290,22 +336,21 @@ __device__ void build_tile_tables(const TileParams& P, TileTables& T, int* hmap,
     uint32_t m = 0;
     for (int k = 0; k < kSrcT; ++k) if (c.obs_noise[k] != 0.0f) m |= 1u << k;
     T.noise_mask = m;
-    for (int g = 0; g < PBHC_MAX_OBS_GROUPS; ++g) T.gdim[g] = g < c.n_groups ? c.group_dim[g] : 0;
     // scalar features of an env (legged_robot_base.py:1114-1215, motion_tracking.py:944-1015)
     int n = 0;
-    for (int i = 0; i < 3; ++i) { T.feat_src[n] = S_BASE_LIN_VEL; T.feat_el[n++] = i; }
-    for (int i = 0; i < 3; ++i) { T.feat_src[n] = S_BASE_ANG_VEL; T.feat_el[n++] = i; }
-    for (int i = 0; i < 3; ++i) { T.feat_src[n] = S_PROJ_GRAV; T.feat_el[n++] = i; }
-    for (int i = 0; i < 3; ++i) { T.feat_src[n] = S_DR_COM; T.feat_el[n++] = i; }
+    for (int i = 0; i < 3; ++i) { T.feat_src[n] = S_BASE_LIN_VEL; T.feat_el[n++] = (unsigned char)i; }
+    for (int i = 0; i < 3; ++i) { T.feat_src[n] = S_BASE_ANG_VEL; T.feat_el[n++] = (unsigned char)i; }
+    for (int i = 0; i < 3; ++i) { T.feat_src[n] = S_PROJ_GRAV; T.feat_el[n++] = (unsigned char)i; }
+    for (int i = 0; i < 3; ++i) { T.feat_src[n] = S_DR_COM; T.feat_el[n++] = (unsigned char)i; }
     T.feat_src[n] = S_PHASE; T.feat_el[n++] = 0;
     T.feat_src[n] = S_DR_FRICTION; T.feat_el[n++] = 0;
     T.feat_src[n] = S_DR_DELAY; T.feat_el[n++] = 0;
     T.feat_src[n] = S_BASE_POS_Z; T.feat_el[n++] = 0;
-    for (int i = 0; i < c.L && n < 64; ++i) { T.feat_src[n] = S_DR_MASS; T.feat_el[n++] = i; }
+    for (int i = 0; i < c.L && n < 64; ++i) { T.feat_src[n] = S_DR_MASS; T.feat_el[n++] = (unsigned char)i; }
   }
   // history ring: physical slot of logical slot s of key k is (head_k + s) % len_k, head_k = -push_count mod len_k
-  // (HistoryHandler keeps newest-first order, history_handler.py:40-48).  hmap[d][i] = destination of physical element
-  // i of the ring in the d-th observation segment that shows it: row offset | group << 24, -1 = none.
+  // (HistoryHandler keeps newest-first order, history_handler.py:40-48).  One plane per obs group that shows history:
+  // hmap[plane][i] = float offset (inside the rows region, env 0) where physical ring element i goes in that group, -1 = none.
   for (int i = tid; i < c.hist_row; i += nt) {
     int k = 0;
     while (k + 1 < c.n_hist_keys && i >= P.hist_base[k + 1]) ++k;
@@ -313,447 +358,462 @@ __device__ void build_tile_tables(const TileParams& P, TileTables& T, int* hmap,
     const int r = i - P.hist_base[k], ps = r / dim, cc = r - ps * dim;
     const int head = (int)((len - (push_count % len)) % len);
     const int s = (ps - head + len) % len;  // logical slot
-    int nd = 0;
-    for (int e = 0; e < c.n_hist_dst && nd < P.n_hd; ++e) {
-      const PbhcHistDst& h = c.hist_dst[e];
-      if (h.key != k) continue;
-      hmap[nd * c.hist_row + i] = s < h.len ? ((P.row_base[h.group] + h.offset + s * dim + cc) | (h.group << 24)) : -1;
-      if (P.hist_any_mul) hmul[nd * c.hist_row + i] = h.mul;
-      ++nd;
+    int plane = 0;
+    for (int g = 0; g < c.n_groups; ++g) {
+      if (!ghist(g)) continue;
+      int m = -1; float mul = 1.0f;
+      for (int e = 0; e < c.n_hist_dst; ++e) {
+        const PbhcHistDst& h = c.hist_dst[e];
+        if (h.key == k && h.group == g && s < h.len) { m = row_base(g) + h.offset + s * dim + cc; mul = h.mul; }
+      }
+      hmap[plane * c.hist_row + i] = m;
+      if (KC(hist_any_mul)) hmul[plane * c.hist_row + i] = mul;
+      ++plane;
     }
-    for (; nd < P.n_hd; ++nd) { hmap[nd * c.hist_row + i] = -1; if (P.hist_any_mul) hmul[nd * c.hist_row + i] = 1.0f; }
   }
   __syncthreads();
 }
 
 template <bool kNoise>
-__global__ void __launch_bounds__(kNT, 3) track_tile_kernel(const __grid_constant__ TileParams P) {
+__device__ __forceinline__ void track_tile_body(const TileParams& P) {
   extern __shared__ __align__(128) unsigned char smem[];
   const PbhcTrackCfg& c = P.c;
   const PbhcTrackIO& io = P.io;
   const PbhcTableDesc& tab = P.tab;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  TileTables& T = *reinterpret_cast<TileTables*>(smem + P.o_tab);
-  int* hmap = reinterpret_cast<int*>(smem + P.o_hmap);
-  float* hmul = reinterpret_cast<float*>(smem + P.o_hmul);
-  int* s_far = reinterpret_cast<int*>(smem + P.o_flags);          // [kTE]
-  int* s_collide = s_far + kTE;                                   // [kTE]
-  int* s_state = s_collide + kTE;                                 // [kTE] bit 0 reset, bit 1 time_out
-  float* rv = reinterpret_cast<float*>(smem + P.o_rv);            // [kTE][kRvT]
-  float* pre = reinterpret_cast<float*>(smem + P.o_pre);          // [kTE][kPre]
-  float* rows = reinterpret_cast<float*>(smem + P.o_rows);
-  const float* s_body = reinterpret_cast<const float*>(smem + P.i_body);
-  const float* s_cf = reinterpret_cast<const float*>(smem + P.i_cf);
-  const float* s_hist = reinterpret_cast<const float*>(smem + P.i_hist);
-  const float2* s_dof = reinterpret_cast<const float2*>(smem + P.i_dof);
-  const float* s_act = reinterpret_cast<const float*>(smem + P.i_act);
-  const float* s_tq = reinterpret_cast<const float*>(smem + P.i_tq);
-  const float* s_lact = reinterpret_cast<const float*>(smem + P.i_lact);
-  const float* s_ldv = reinterpret_cast<const float*>(smem + P.i_ldv);
-  const float* s_kp = reinterpret_cast<const float*>(smem + P.i_kp);
-  const float* s_kd = reinterpret_cast<const float*>(smem + P.i_kd);
-  const float* s_es = reinterpret_cast<const float*>(smem + P.i_es);
-  const float* s_envf = reinterpret_cast<const float*>(smem + P.i_envf);
-  const float* s_root = reinterpret_cast<const float*>(smem + P.i_root);
-  const float* s_org = reinterpret_cast<const float*>(smem + P.i_org);
-  const long long* s_ep = reinterpret_cast<const long long*>(smem + P.i_ep);
-  const long long* s_mid = reinterpret_cast<const long long*>(smem + P.i_mid);
-  const float* s_com = reinterpret_cast<const float*>(smem + P.i_com);
-  const float* s_fric = reinterpret_cast<const float*>(smem + P.i_fric);
-  const long long* s_delay = reinterpret_cast<const long long*>(smem + P.i_delay);
-  const float* s_mass = reinterpret_cast<const float*>(smem + P.i_mass);
-  float* q_rew = reinterpret_cast<float*>(smem + P.q_rew);
-  float* q_es = reinterpret_cast<float*>(smem + P.q_es);
-  float* q_envf = reinterpret_cast<float*>(smem + P.q_envf);
-  long long* q_ep = reinterpret_cast<long long*>(smem + P.q_ep);
-  long long* q_reset = reinterpret_cast<long long*>(smem + P.q_reset);
-  float* q_lact = reinterpret_cast<float*>(smem + P.q_lact);
-  float* q_ldpos = reinterpret_cast<float*>(smem + P.q_ldpos);
-  float* q_ldvel = reinterpret_cast<float*>(smem + P.q_ldvel);
-  float* dpart = reinterpret_cast<float*>(smem + P.o_dpart);     // [kTE][kDofRaw][D]   (in the dead history slab)
-  float* s_ext = reinterpret_cast<float*>(smem + P.o_ext);       // [kTE][n_ext][13]    (in the dead history slab)
-  float* bpart = reinterpret_cast<float*>(smem + P.o_bpart);     // [kTE][kBodyRaw][J]  (in the dead dof-input slabs)
-  float* s_rw = reinterpret_cast<float*>(smem + P.o_rw);         // [kTE][32] raw reward terms (scalar reward mode)
+  TileTables& T = *reinterpret_cast<TileTables*>(smem + KC(o_tab));
+  int* hmap = reinterpret_cast<int*>(smem + KC(o_hmap));
+  float* hmul = reinterpret_cast<float*>(smem + KC(o_hmul));
+  float* rv = reinterpret_cast<float*>(smem + KC(o_rv));            // [kTE][kRvT]
+  float* rows = reinterpret_cast<float*>(smem + KC(o_rows));
   const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(smem);
-  const uint32_t bar = sbase + P.o_bar;
+  const uint32_t bar = sbase + KC(o_bar);
 
   if (tid == 0) { mbar_init(bar, 1); asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); fence_async(); }
   for (int i = tid; i < kTE * kRvT; i += kNT) rv[i] = 0.0f;  // slots nobody writes are accumulated too
-  build_tile_tables(P, T, hmap, hmul, io.scalars, reinterpret_cast<double*>(smem + P.o_rows));  // (the rows region is idle: scratch for the scalars)
+  build_tile_tables(P, T, hmap, hmul, io.scalars, reinterpret_cast<double*>(smem + KC(o_rows)));  // (the rows region is idle: scratch for the scalars)
 
-  const int J = c.J, Jb = c.Jb, D = c.D, n_ext = c.n_ext, H = c.hist_row, n_envs = P.n;
-  const int R = c.n_rewards;
-  const float clipv = c.clip_obs, dt = c.dt;
-  const int e_pos = P.e_pos, e_vel = P.e_vel, e_ang = P.e_ang, e_dp = P.e_dp, e_dv = P.e_dv, e_c = P.e_c;
+  const int J = KC(J), Jb = KC(Jb), D = KC(D), H = KC(H), n_envs = P.n;
+  const int R = KC(R);
+  const float clipv = KC(clip_obs), dt = KC(dt);
+  const int e_pos = KC(e_pos), e_vel = KC(e_vel), e_ang = KC(e_ang), e_dp = KC(e_dp), e_dv = KC(e_dv), e_c = KC(e_c);
   const float far_thr = T.far_thr;
   const uint32_t push_count = T.push_count;
-  double acc_reg = 0.0;  // slot = tid (< kAccLo)
+  double acc_reg = 0.0;  // slot = lane (< kAccLo), this warp's envs
 
-  auto issue_loads = [&](int tile0) {  // warp 0: one descriptor per lane
-    if (lane == 0) mbar_expect_tx(bar, P.in_bytes);
+  const int n_tiles = P.n_tiles, stride = (int)gridDim.x;
+  auto is_bulk = [&](int t) { return P.bulk_ok && t < n_tiles && (t + 1) * kTE <= n_envs; };
+  // warp 0: requests the big slabs of tile `tb` and the small (double-buffered) slabs of tile `ts` into buffer `buf`
+  auto issue_loads = [&](int tb, bool big, int ts, bool small, int buf) {
+    if (lane == 0) mbar_expect_tx(bar, (big ? P.in_bytes : 0) + (small ? P.small_bytes : 0));
     __syncwarp();
-    for (int i = lane; i < P.n_in; i += 32) {
-      const TileDesc d = P.in[i];
-      if (d.g_stride == d.row_bytes) bulk_load(sbase + d.soff, d.g + (int64_t)tile0 * d.row_bytes, kTE * d.row_bytes, bar);
-      else for (int e = 0; e < kTE; ++e) bulk_load(sbase + d.soff + e * d.row_bytes, d.g + (int64_t)(tile0 + e) * d.g_stride, d.row_bytes, bar);
+    if (big)
+      for (int i = lane; i < P.n_in; i += 32) {
+        const TileDesc d = P.in[i];
+        const int64_t t0 = (int64_t)tb * kTE;
+        if (d.g_stride == d.row_bytes) bulk_load(sbase + d.soff, d.g + t0 * d.row_bytes, kTE * d.row_bytes, bar);
+        else for (int e = 0; e < kTE; ++e) bulk_load(sbase + d.soff + e * d.row_bytes, d.g + (t0 + e) * d.g_stride, d.row_bytes, bar);
+      }
+    if (small && lane < P.n_small) {
+      const TileDesc d = P.small[lane];
+      bulk_load(sbase + (buf ? d.soff2 : d.soff), d.g + (int64_t)ts * kTE * d.row_bytes, kTE * d.row_bytes, bar);
+    }
+  };
+  // the per-env scalar work of a tile, piece = warp, lane = env (legged_robot_base.py:346-353, motion_tracking.py:548-558, 678-739)
+  auto pre_pieces = [&](int buf, int cnt) {
+    if (warp >= kPieces || lane >= cnt) return;
+    const int e = lane;
+    float* pe = reinterpret_cast<float*>(smem + KC(o_pre)) + (buf * kTE + e) * kPre;
+    const float* root = reinterpret_cast<const float*>(smem + (buf ? KC(i_root1) : KC(i_root0))) + e * 13;
+    const Q4 rq = {root[3], root[4], root[5], root[6]};
+    if (warp == 0) {
+      const int64_t ep = reinterpret_cast<const long long*>(smem + (buf ? KC(i_ep1) : KC(i_ep0)))[e] + 1;  // legged_robot_base.py:299
+      const float start = reinterpret_cast<const float*>(smem + (buf ? KC(i_envf1) : KC(i_envf0)))[e * PBHC_ENVF_STRIDE];
+      const int clip = resolve_clip(tab, io.clip_of_motion, reinterpret_cast<const long long*>(smem + (buf ? KC(i_mid1) : KC(i_mid0)))[e]);
+      const float t = xa(xm((float)(ep + 1), dt), start);  // kick_motion_res, motion_tracking.py:554
+      const FrameBlend fb = frame_blend_x(tab, clip, t);
+      pe[P_F0] = __int_as_float((int)fb.f0); pe[P_F1] = __int_as_float((int)fb.f1); pe[P_BLEND] = fb.blend;
+      pe[P_PHASE] = __fdiv_rn(t, tab.clip_length[clip]);  // motion_tracking.py:738-739
+      pe[P_CLIP] = __int_as_float(clip);
+    } else if (warp == 1) {
+      const V3 blv = quat_rotate_inverse(rq, {root[7], root[8], root[9]});
+      pe[P_BLV] = blv.x; pe[P_BLV + 1] = blv.y; pe[P_BLV + 2] = blv.z;
+      pe[P_RPX] = root[0]; pe[P_RPY] = root[1]; pe[P_RPZ] = root[2];
+    } else if (warp == 2) {
+      const V3 bav = quat_rotate_inverse(rq, {root[10], root[11], root[12]});
+      pe[P_BAV] = bav.x; pe[P_BAV + 1] = bav.y; pe[P_BAV + 2] = bav.z;
+    } else if (warp == 3) {
+      const V3 pg = quat_rotate_x(rq, {0.0f, 0.0f, -1.0f}, true);
+      pe[P_PG] = pg.x; pe[P_PG + 1] = pg.y; pe[P_PG + 2] = pg.z;
+      pe[P_GRAVN] = norm2(pg.x, pg.y);
+      pe[P_ORIENT] = pg.x * pg.x + pg.y * pg.y;
+    } else {
+      const Q4 hinv = heading_quat_inv(rq);
+      pe[P_HZ] = hinv.z; pe[P_HW] = hinv.w;
     }
   };
 
-  const int n_tiles = P.n_tiles;
-  int tile = blockIdx.x;
-  bool loaded = false;
+  int tile = blockIdx.x, it = 0;
   uint32_t phase = 0;
-  if (P.bulk_ok && tile < n_tiles && (tile + 1) * kTE <= n_envs) { if (warp == 0) issue_loads(tile * kTE); loaded = true; }
+  bool have_small_next = false, pre_ready = false;
+  if (is_bulk(tile)) {  // prologue: this block's first tile (big + small) and the small inputs of its second tile
+    have_small_next = is_bulk(tile + stride);
+    if (warp == 0) {
+      if (lane == 0) mbar_expect_tx(bar, P.in_bytes + P.small_bytes * (have_small_next ? 2 : 1));
+      __syncwarp();
+      for (int i = lane; i < P.n_in; i += 32) {
+        const TileDesc d = P.in[i];
+        const int64_t t0 = (int64_t)tile * kTE;
+        if (d.g_stride == d.row_bytes) bulk_load(sbase + d.soff, d.g + t0 * d.row_bytes, kTE * d.row_bytes, bar);
+        else for (int e = 0; e < kTE; ++e) bulk_load(sbase + d.soff + e * d.row_bytes, d.g + (t0 + e) * d.g_stride, d.row_bytes, bar);
+      }
+      if (lane < P.n_small) {
+        const TileDesc d = P.small[lane];
+        bulk_load(sbase + d.soff, d.g + (int64_t)tile * kTE * d.row_bytes, kTE * d.row_bytes, bar);
+        if (have_small_next) bulk_load(sbase + d.soff2, d.g + (int64_t)(tile + stride) * kTE * d.row_bytes, kTE * d.row_bytes, bar);
+      }
+    }
+  }
 
-  for (; tile < n_tiles; tile += gridDim.x) {
+  for (; tile < n_tiles; tile += stride, ++it) {
     const int tile0 = tile * kTE;
     const int cnt = min(kTE, n_envs - tile0);
+    const int sb = it & 1;
+    const bool bulk = is_bulk(tile);
     if (warp == 0) bulk_wait_read();  // the previous tile's bulk stores have left the output slabs
-    if (loaded) { mbar_wait_t(bar, phase); phase ^= 1u; }
+    if (bulk) { if (tid == 0) mbar_wait_t(bar, phase); phase ^= 1u; }
     else {  // ragged last tile / unaligned tensors: cooperative word copies
-      for (int i = 0; i < P.n_in; ++i) {
-        const TileDesc d = P.in[i];
+      for (int i = 0; i < P.n_in + P.n_small; ++i) {
+        const TileDesc d = i < P.n_in ? P.in[i] : P.small[i - P.n_in];
         const int rw = d.row_bytes >> 2;
-        uint32_t* dst = reinterpret_cast<uint32_t*>(smem + d.soff);
+        uint32_t* dst = reinterpret_cast<uint32_t*>(smem + ((i >= P.n_in && sb) ? d.soff2 : d.soff));
         for (int w = tid; w < cnt * rw; w += kNT) {
           const int e = w / rw, x = w - e * rw;
           dst[w] = reinterpret_cast<const uint32_t*>(d.g + (int64_t)(tile0 + e) * d.g_stride)[x];
         }
       }
     }
-    if (tid < kTE) { s_far[tid] = 0; s_collide[tid] = 0; }
     __syncthreads();
+    if (!pre_ready) { pre_pieces(sb, cnt); __syncthreads(); }
+    if (have_small_next) pre_pieces(sb ^ 1, kTE);  // the next tile's scalars, consumed after the end-of-tile barrier
 
-    // ---- 1. pre (legged_robot_base.py:346-353, motion_tracking.py:548-558, 678-739) + history ring -> rows ------------------
-    if (warp < 3 && lane < cnt) {
-      const int e = lane;
-      float* pe = pre + e * kPre;
-      const float* root = s_root + e * 13;
-      const Q4 rq = {root[3], root[4], root[5], root[6]};
-      if (warp == 0) {
-        const int64_t ep = s_ep[e] + 1;  // legged_robot_base.py:299
-        const float start = s_envf[e * PBHC_ENVF_STRIDE];
-        const int clip = resolve_clip(tab, io.clip_of_motion, s_mid[e]);
-        const float t = xa(xm((float)(ep + 1), dt), start);  // kick_motion_res, motion_tracking.py:554
-        const FrameBlend fb = frame_blend_x(tab, clip, t);
-        pe[P_F0] = __int_as_float((int)fb.f0); pe[P_F1] = __int_as_float((int)fb.f1); pe[P_BLEND] = fb.blend;
-        pe[P_PHASE] = __fdiv_rn(t, tab.clip_length[clip]);  // motion_tracking.py:738-739
-        pe[P_CLIP] = __int_as_float(clip);
-      } else if (warp == 1) {
-        const V3 blv = quat_rotate_inverse(rq, {root[7], root[8], root[9]});
-        const V3 bav = quat_rotate_inverse(rq, {root[10], root[11], root[12]});
-        pe[P_BLV] = blv.x; pe[P_BLV + 1] = blv.y; pe[P_BLV + 2] = blv.z;
-        pe[P_BAV] = bav.x; pe[P_BAV + 1] = bav.y; pe[P_BAV + 2] = bav.z;
-        pe[P_RPX] = root[0]; pe[P_RPY] = root[1]; pe[P_RPZ] = root[2];
-      } else {
-        const V3 pg = quat_rotate_x(rq, {0.0f, 0.0f, -1.0f}, true);
-        const Q4 hinv = heading_quat_inv(rq);
-        pe[P_PG] = pg.x; pe[P_PG + 1] = pg.y; pe[P_PG + 2] = pg.z;
-        pe[P_GRAVN] = norm2(pg.x, pg.y);
-        pe[P_ORIENT] = pg.x * pg.x + pg.y * pg.y;
-        pe[P_HZ] = hinv.z; pe[P_HW] = hinv.w;
-      }
-    }
-    // HistoryHandler.query (history_handler.py:46-48): every physical ring element to its places in the rows
-    for (int i = tid; i < H; i += kNT) {
-      for (int d = 0; d < P.n_hd; ++d) {
-        const int m = hmap[d * H + i];
-        if (m < 0) continue;
-        const float mul = P.hist_any_mul ? hmul[d * H + i] : 1.0f;
-        float* dst = rows + (m & 0xffffff);
-        const int es = T.gdim[m >> 24];
-        for (int e = 0; e < cnt; ++e) dst[e * es] = clampf(s_hist[e * H + i] * mul, clipv);
-      }
-    }
-    __syncthreads();
-
-    // ---- 2. dofs (item = env x dof), extended bodies, feet ----------------------------------------------------------------------
-    for (int it = tid; it < cnt * D; it += kNT) {
-      const int e = (it * P.inv_d) >> 16, d = it - e * D;
-      const int64_t n = tile0 + e;
-      const float* pe = pre + e * kPre;
-      const float b = pe[P_BLEND], omb = 1.0f - b;
-      const float* r0 = tab.records + (int64_t)__float_as_int(pe[P_F0]) * tab.rec_stride;
-      const float* r1 = tab.records + (int64_t)__float_as_int(pe[P_F1]) * tab.rec_stride;
-      const float2 ds = s_dof[it];
-      const float dpos = ds.x, dvel = ds.y;
-      const float act = s_act[it], tq = s_tq[it], lact = s_lact[it], ldv = s_ldv[it];
-      const float ddef = io.default_dof_pos[n * io.default_dof_stride + d];
-      const float dja = (omb * __ldg(r0 + e_dp + d) + b * __ldg(r1 + e_dp + d)) - dpos;   // motion_tracking.py:661-665
-      const float djv = (omb * __ldg(r0 + e_dv + d) + b * __ldg(r1 + e_dv + d)) - dvel;
-      const float dact = lact - act, dacc = (ldv - dvel) / dt;
-      const float lim_t = T.lim_tq[d];
-      float* dp_ = dpart + e * (kDofRaw * D) + d;
-      dp_[DR_DJA * D] = dja; dp_[DR_DJV2 * D] = djv * djv; dp_[DR_TQ2 * D] = tq * tq; dp_[DR_DACT2 * D] = dact * dact;
-      dp_[DR_DV2 * D] = dvel * dvel; dp_[DR_ACC2 * D] = dacc * dacc;
-      dp_[DR_LPOS * D] = -fminf(dpos - T.lim_lo[d], 0.0f) + fmaxf(dpos - T.lim_hi[d], 0.0f);  // legged_robot_base.py:974-1002
-      dp_[DR_LVEL * D] = fminf(fmaxf(fabsf(dvel) - T.lim_vel[d], 0.0f), 1.0f);
-      dp_[DR_LTQ * D] = c.cur_torque.enable ? fminf(fmaxf(fabsf(tq) - lim_t, 0.0f), 1.0f) : fmaxf(fabsf(tq) - lim_t, 0.0f);
-      const Rows Rw = {rows, io.hist + n * H};
-      const NoiseKeyT nk = {c.seed, n + io.env_offset, push_count};
-      emit1<kNoise>(T, Rw, S_DOF_POS, e, d, dpos - ddef, clipv, nk);
-      emit1<kNoise>(T, Rw, S_DOF_VEL, e, d, dvel, clipv, nk);
-      emit1<kNoise>(T, Rw, S_ACTIONS, e, d, act, clipv, nk);
-      emit1<kNoise>(T, Rw, S_DR_KP, e, d, s_kp[it], clipv, nk);
-      emit1<kNoise>(T, Rw, S_DR_KD, e, d, s_kd[it], clipv, nk);
-      if (c.src_used_mask & ((1ull << S_DIF_JOINT) | (1ull << S_DIF_JOINT_VEL))) {
-        emit1<kNoise>(T, Rw, S_DIF_JOINT, e, d, dja, clipv, nk);
-        emit1<kNoise>(T, Rw, S_DIF_JOINT_VEL, e, d, djv, clipv, nk);
-      }
-      q_lact[it] = act; q_ldpos[it] = dpos; q_ldvel[it] = dvel;  // _post_compute_observations_callback, legged_robot_base.py:398-405
-    }
-    if (warp == kTE - 2) {  // extended bodies (motion_tracking.py:619-643): position chain unfused (it feeds the motion_far comparison)
-      for (int it = lane; it < cnt * n_ext; it += 32) {
-        const int e = it / n_ext, x = it - e * n_ext;
-        const float* bs = s_body + (e * Jb + c.ext_parent[x]) * 13;
-        const Q4 qp = {bs[3], bs[4], bs[5], bs[6]};
-        const V3 off = {c.ext_pos[x][0], c.ext_pos[x][1], c.ext_pos[x][2]};
-        const Q4 qe = {c.ext_rot_xyzw[x][0], c.ext_rot_xyzw[x][1], c.ext_rot_xyzw[x][2], c.ext_rot_xyzw[x][3]};
-        const V3 r = quat_rotate_x(qe, quat_rotate_x(qp, off, false), false);
-        const Q4 q = quat_mul(qp, qe);
-        float* o = s_ext + it * 13;
-        o[0] = xa(r.x, bs[0]); o[1] = xa(r.y, bs[1]); o[2] = xa(r.z, bs[2]);
-        o[3] = q.x; o[4] = q.y; o[5] = q.z; o[6] = q.w;
-        const V3 w = {bs[10], bs[11], bs[12]};
-        o[7] = bs[7] + (w.y * off.z - w.z * off.y); o[8] = bs[8] + (w.z * off.x - w.x * off.z); o[9] = bs[9] + (w.x * off.y - w.y * off.x);
-        o[10] = w.x; o[11] = w.y; o[12] = w.z;
-      }
-    }
-    if (warp == kTE - 1) {  // feet: contacts, feet_air_time, contact-force / slip terms (item = env x foot)
-      for (int it = lane; it < cnt * c.n_feet; it += 32) {
-        const int e = it / c.n_feet, f = it - e * c.n_feet;
-        const int fb = c.feet_ids[f];
-        const float* pe = pre + e * kPre;
-        const float b = pe[P_BLEND], omb = 1.0f - b;
-        const float* fc = s_cf + (e * Jb + fb) * 3;
-        const float* bs = s_body + (e * Jb + fb) * 13;
-        const float* ef = s_envf + e * PBHC_ENVF_STRIDE;
-        const float last_c = ef[4 + f];
-        float air_f = ef[2 + f];
-        const float fn = norm3(fc[0], fc[1], fc[2]);
-        const float contact_f = fn > 1.0f ? 1.0f : 0.0f;                       // legged_robot_base.py:352-353
-        const float filt = (contact_f != 0.0f || last_c != 0.0f) ? 1.0f : 0.0f;
-        float x_cm = 0.0f, x_air = 0.0f;
-        if (tab.contact_size) {
-          const float* r0 = tab.records + (int64_t)__float_as_int(pe[P_F0]) * tab.rec_stride;
-          const float* r1 = tab.records + (int64_t)__float_as_int(pe[P_F1]) * tab.rec_stride;
-          x_cm = fabsf(filt - (omb * __ldg(r0 + e_c + f) + b * __ldg(r1 + e_c + f)));
-        }
-        const bool fz = fc[2] > 1.0f || last_c != 0.0f;                         // motion_tracking.py:1307-1319
-        if (P.has_air_time) {
-          const float first = (air_f > 0.0f && fz) ? 1.0f : 0.0f;
-          air_f = xa(air_f, dt);
-          x_air = (air_f - c.desired_feet_air_time) * first;
-          air_f *= fz ? 0.0f : 1.0f;
-        }
-        float* o = rv + e * kRvT + V_FOOT + f * 8;
-        o[FV_AIR] = x_air;
-        o[FV_FORCE] = fmaxf(fn - c.max_contact_force, 0.0f);                     // :1321-1323
-        o[FV_STUMBLE] = norm2(fc[0], fc[1]) > 5.0f * fabsf(fc[2]) ? 1.0f : 0.0f;  // :1325-1328
-        o[FV_SLIP] = norm3(bs[7], bs[8], bs[9]) * contact_f;                     // legged_robot_base.py:1004-1010
-        o[FV_FSLIP] = contact_f * norm2(bs[7], bs[8]);                           // :1012-1017
-        o[FV_CM] = x_cm; o[FV_AIRF] = air_f; o[FV_CONTACT] = contact_f;
-      }
-    }
-    __syncthreads();
-
-    // ---- 3. bodies (item = env x body): reference pose (lerp / slerp of the frame pair), differences, heading-frame features --
-    if (warp == kTE - 1) {  // dof sums (item = env x value), added in dof order
-      for (int it = lane; it < cnt * kDofRaw; it += 32) {
-        const int e = it / kDofRaw, k = it - e * kDofRaw;
-        const float* src = dpart + (e * kDofRaw + k) * D;
-        float* r = rv + e * kRvT;
-        if (k == DR_DJA) {
-          float s = 0.0f, mx = 0.0f;
-          for (int d = 0; d < D; ++d) { const float v = src[d]; s += v * v; mx = fmaxf(mx, fabsf(v)); }
-          r[V_SIGMA_ERR + G_JOINT_POS] = s / (float)D; r[V_JOINT_N] = sqrtf(s); r[V_SIGMA_ERR + G_MAX_JOINT] = mx;
-        } else {
-          float s = 0.0f;
-          for (int d = 0; d < D; ++d) s += src[d];
-          if (k == DR_DJV2) r[V_SIGMA_ERR + G_JOINT_VEL] = s / (float)D;
-          else r[k == DR_TQ2 ? V_TQ2 : k == DR_DACT2 ? V_DACT2 : k == DR_DV2 ? V_DV2 : k == DR_ACC2 ? V_ACC2 : k == DR_LPOS ? V_LIM_POS : k == DR_LVEL ? V_LIM_VEL : V_LIM_TQ] = s;
-        }
-      }
-    }
-    for (int it = tid; it < cnt * J; it += kNT) {
-      const int e = (it * P.inv_j) >> 16, j = it - e * J;
-      const int64_t n = tile0 + e;
-      const float* pe = pre + e * kPre;
-      const float b = pe[P_BLEND], omb = 1.0f - b;
-      const float* r0 = tab.records + (int64_t)__float_as_int(pe[P_F0]) * tab.rec_stride;
-      const float* r1 = tab.records + (int64_t)__float_as_int(pe[P_F1]) * tab.rec_stride;
-      const float* bs = j < Jb ? s_body + (e * Jb + j) * 13 : s_ext + (e * n_ext + (j - Jb)) * 13;
-      const float4 qa = __ldg(reinterpret_cast<const float4*>(r0) + j);
-      const float4 qb = __ldg(reinterpret_cast<const float4*>(r1) + j);
-      float rpz[3], rvv[3], rw[3];
-#pragma unroll
-      for (int k = 0; k < 3; ++k) {
-        rpz[k] = xa(xa(xm(omb, __ldg(r0 + e_pos + 3 * j + k)), xm(b, __ldg(r1 + e_pos + 3 * j + k))), s_org[e * 3 + k]);
-        rvv[k] = omb * __ldg(r0 + e_vel + 3 * j + k) + b * __ldg(r1 + e_vel + 3 * j + k);
-        rw[k] = omb * __ldg(r0 + e_ang + 3 * j + k) + b * __ldg(r1 + e_ang + 3 * j + k);
-      }
-      const Q4 rr = slerp_t({qa.x, qa.y, qa.z, qa.w}, {qb.x, qb.y, qb.z, qb.w}, b);
-      if (io.ref_body_pos_extend) {
-        float* o = io.ref_body_pos_extend + n * (3 * J) + 3 * j;
-        o[0] = rpz[0]; o[1] = rpz[1]; o[2] = rpz[2];
-      }
-      if (io.ref_body_rot_extend) reinterpret_cast<float4*>(io.ref_body_rot_extend)[n * J + j] = make_float4(rr.x, rr.y, rr.z, rr.w);
-      const V3 dp = {xs(rpz[0], bs[0]), xs(rpz[1], bs[1]), xs(rpz[2], bs[2])};
-      const float dq0 = rr.x - bs[3], dq1 = rr.y - bs[4], dq2 = rr.z - bs[5], dq3 = rr.w - bs[6];
-      const V3 dv = {rvv[0] - bs[7], rvv[1] - bs[8], rvv[2] - bs[9]};
-      const V3 dw = {rw[0] - bs[10], rw[1] - bs[11], rw[2] - bs[12]};
-      const float nrm = norm3(dp.x, dp.y, dp.z);
-      float* bp = bpart + e * (kBodyRaw * J) + j;
-      bp[BR_MPOS * J] = div3((dp.x * dp.x + dp.y * dp.y) + dp.z * dp.z);
-      bp[BR_NRM * J] = nrm;
-      bp[BR_ROT * J] = (((dq0 * dq0 + dq1 * dq1) + dq2 * dq2) + dq3 * dq3) * 0.25f;
-      bp[BR_VEL * J] = div3((dv.x * dv.x + dv.y * dv.y) + dv.z * dv.z);
-      bp[BR_ANG * J] = div3((dw.x * dw.x + dw.y * dw.y) + dw.z * dw.z);
-      if (nrm > far_thr) s_far[e] = 1;
-      if (j < Jb && ((c.penalised_mask >> j) & 1ull)) {
-        const float* fc = s_cf + (e * Jb + j) * 3;
-        if (norm3(fc[0], fc[1], fc[2]) > 0.1f) atomicAdd(&s_collide[e], 1);
-      }
-      const Rows Rw = {rows, io.hist + n * H};
-      const NoiseKeyT nk = {c.seed, n + io.env_offset, push_count};
-      const float hz = pe[P_HZ], hw = pe[P_HW];
-      {
-        const V3 dl = quat_rotate_z(hz, hw, dp);  // motion_tracking.py:694-697
-        emit3<kNoise>(T, Rw, S_DIF_LOCAL, e, 3 * j, dl.x, dl.y, dl.z, clipv, nk);
-        const V3 lr = quat_rotate_z(hz, hw, {rpz[0] - pe[P_RPX], rpz[1] - pe[P_RPY], rpz[2] - pe[P_RPZ]});  // :705-707
-        emit3<kNoise>(T, Rw, S_LOCAL_REF, e, 3 * j, lr.x, lr.y, lr.z, clipv, nk);
-      }
-      if (c.src_used_mask & ((1ull << S_LOCAL_REF_VEL) | (1ull << S_GLOBAL_REF_VEL))) {
-        const V3 lv = quat_rotate_z(hz, hw, {rvv[0], rvv[1], rvv[2]});
-        emit3<kNoise>(T, Rw, S_LOCAL_REF_VEL, e, 3 * j, lv.x, lv.y, lv.z, clipv, nk);
-        emit3<kNoise>(T, Rw, S_GLOBAL_REF_VEL, e, 3 * j, rvv[0], rvv[1], rvv[2], clipv, nk);
-      }
-    }
-    __syncthreads();
-
-    // ---- 4. body sums (item = env x sum, bodies added in index order), per-env scalars + termination, scalar features ------------
-    for (int it = tid; it < cnt * kBodySums; it += kNT) {
-      const int e = it / kBodySums, k = it - e * kBodySums;
-      const float* src = bpart + (e * kBodyRaw + T.bs_raw[k]) * J;
-      uint64_t m = T.bs_mask[k];
-      float s = 0.0f;
-      while (m) { const int j = __ffsll((long long)m) - 1; m &= m - 1; s += src[j]; }
-      rv[e * kRvT + T.bs_slot[k]] = s / T.bs_div[k];
-    }
-    if (warp == kTE - 1 && lane < cnt) {  // legged_robot_base.py:408-489, motion_tracking.py:330-358
-      const int e = lane;
-      float* r = rv + e * kRvT;
-      const float* pe = pre + e * kPre;
-      const float* f0 = r + V_FOOT;
-      const float* f1 = r + V_FOOT + 8;
-      const bool two = c.n_feet > 1;
-      const int64_t ep = s_ep[e] + 1;
-      const float start = s_envf[e * PBHC_ENVF_STRIDE], mlen = s_envf[e * PBHC_ENVF_STRIDE + 1];
-      const bool t_grav = c.term_gravity && pe[P_GRAVN] > c.term_gravity_thr;
-      const bool t_far = c.term_motion_far && s_far[e] != 0;
-      const bool t_out = ep > c.max_episode_length;
-      const bool t_end = c.term_motion_end && (xa(xm((float)ep, dt), start) > mlen);
-      const bool time_out = t_out || t_end;
-      const bool reset = t_grav || t_far || time_out;
-      const float x_cm = f0[FV_CM] + (two ? f1[FV_CM] : 0.0f);
-      r[V_T_GRAV] = t_grav; r[V_T_FAR] = t_far; r[V_T_OUT] = time_out; r[V_T_END] = t_end;
-      r[V_RESET] = reset; r[V_ONE] = 1.0f; r[V_ALIVE] = 1.0f;
-      r[V_CONTACT] = 1.0f - x_cm / (float)c.n_feet; r[V_CONTACT_V2] = 0.5f - x_cm / (float)c.n_feet;
-      r[V_ORIENT] = pe[P_ORIENT];
-      r[V_AIR] = f0[FV_AIR] + (two ? f1[FV_AIR] : 0.0f); r[V_FORCE] = f0[FV_FORCE] + (two ? f1[FV_FORCE] : 0.0f);
-      r[V_STUMBLE] = (f0[FV_STUMBLE] != 0.0f || (two && f1[FV_STUMBLE] != 0.0f)) ? 1.0f : 0.0f;
-      r[V_SLIP] = f0[FV_SLIP] + (two ? f1[FV_SLIP] : 0.0f); r[V_FSLIP] = f0[FV_FSLIP] + (two ? f1[FV_FSLIP] : 0.0f);
-      r[V_COLLIDE] = (float)s_collide[e];
-      r[V_AIR0] = f0[FV_AIRF]; r[V_AIR1] = two ? f1[FV_AIRF] : 0.0f; r[V_CONT0] = f0[FV_CONTACT]; r[V_CONT1] = two ? f1[FV_CONTACT] : 0.0f;
-      s_state[e] = (reset ? 1 : 0) | (time_out ? 2 : 0);
-    }
-    for (int it = tid; it < cnt * P.n_feat; it += kNT) {  // scalar features (the reset branch re-emits them for its env)
-      const int e = (it * P.inv_f) >> 16, i = it - e * P.n_feat;
-      const int64_t n = tile0 + e;
-      const float* pe = pre + e * kPre;
-      const int k = T.feat_src[i], el = T.feat_el[i];
-      float val;
-      if (i < 9) val = pe[P_BLV + i];
-      else if (k == S_DR_COM) val = s_com[e * 3 + el];
-      else if (k == S_PHASE) val = pe[P_PHASE];        // stale for envs that reset, like the reference
-      else if (k == S_DR_FRICTION) val = s_fric[e];
-      else if (k == S_DR_DELAY) val = (float)s_delay[e];
-      else if (k == S_BASE_POS_Z) val = pe[P_RPZ];
-      else val = s_mass[e * c.L + el];
-      const Rows Rw = {rows, io.hist + n * H};
-      const NoiseKeyT nk = {c.seed, n + io.env_offset, push_count};
-      emit1<kNoise>(T, Rw, k, e, el, val, clipv, nk);
-    }
-    __syncthreads();
-
-    // ---- 5. rewards (item = env x term; legged_robot_base.py:715-761) + episode sums ----------------------------------------------
-    for (int it = tid; it < cnt * P.n_cols; it += kNT) {
-      const int e = (it * P.inv_r) >> 16, r = it - e * P.n_cols;
-      const int64_t n = tile0 + e;
-      const float* rve = rv + e * kRvT;
-      const int st = s_state[e];
-      const bool reset = st & 1, time_out = st & 2;
-      float rew = 0.0f;
-      if (r < R) {
-        const int kind = T.r_kind[r];
-        float v = rve[T.r_arg[r]];
-        if (kind != K_RAW) {
-          v = expf(-v / T.r_sigma[r]);
-          if (kind == K_EXP2)  // teleop_body_position_extend, motion_tracking.py:1177-1199
-            v = v * c.w_lower + expf(-rve[V_SIGMA_ERR + G_UPPER] / T.sigma[G_UPPER]) * c.w_upper;
-        }
-        rew = v * T.r_scale[r] * T.r_pen[r];
-      }
-      const float term_rew = c.has_termination ? ((reset && !time_out) ? 1.0f : 0.0f) * c.termination_scale : 0.0f;
-      if (c.use_vec_reward) {
-        float v = rew;
-        if (c.only_positive_rewards) v = fmaxf(v, 0.0f);
-        if (r == R - 1) v += term_rew;  // the reference's stale loop index, legged_robot_base.py:744
-        if (r < R) q_rew[e * (R + 1) + r] = v;
-        if (r == R) q_rew[e * (R + 1) + R] = 0.0f;
-      } else if (r < R) s_rw[e * 32 + r] = rew;
-      if (r < c.n_episode_sums) {
-        float ev = s_es[e * c.n_episode_sums + r] + (r < R ? rew : term_rew);
-        if (reset) { io.last_episode_sums[n * c.n_episode_sums + r] = ev; ev = 0.0f; }  // extras["episode"], legged_robot_base.py:509-513
-        q_es[e * c.n_episode_sums + r] = ev;
-      }
-    }
-    __syncthreads();
-
-    // ---- 6. per-env state; reset (warp = env; legged_robot_base.py:491-516, 647-686, 587-635; motion_tracking.py:274-296, 369-384, 445-543)
+    // ================================ warp = env =====================================================================
     if (warp < cnt) {
       const int e = warp;
       const int64_t n = tile0 + e;
+      const float* pe = reinterpret_cast<const float*>(smem + KC(o_pre)) + (sb * kTE + e) * kPre;
+      const float* s_envf = reinterpret_cast<const float*>(smem + (sb ? KC(i_envf1) : KC(i_envf0))) + e * PBHC_ENVF_STRIDE;
+      const int64_t ep_in = reinterpret_cast<const long long*>(smem + (sb ? KC(i_ep1) : KC(i_ep0)))[e];
+      const float* s_body = reinterpret_cast<const float*>(smem + KC(i_body)) + e * (Jb * 13);
+      const float* s_cf = reinterpret_cast<const float*>(smem + KC(i_cf)) + e * (Jb * 3);
+      const float* s_org = reinterpret_cast<const float*>(smem + KC(i_org)) + e * 3;
+      float* scr = reinterpret_cast<float*>(smem + KC(o_scr) + e * KC(scr_pitch));
       float* rve = rv + e * kRvT;
-      const float* pe = pre + e * kPre;
-      const int st = s_state[e];
-      const bool reset = st & 1, time_out = st & 2;
-      const int64_t last_ep = s_ep[e] + 1;
-      int64_t ep = last_ep;
-      float start = s_envf[e * PBHC_ENVF_STRIDE], mlen = s_envf[e * PBHC_ENVF_STRIDE + 1], etr = s_envf[e * PBHC_ENVF_STRIDE + 6];
-      float air0 = rve[V_AIR0], air1 = rve[V_AIR1], contact0 = rve[V_CONT0], contact1 = rve[V_CONT1];
-      if (!c.use_vec_reward && lane == 0) {
-        float tot = 0.0f;
-        for (int r = 0; r < R; ++r) tot += s_rw[e * 32 + r];
-        if (c.only_positive_rewards) tot = fmaxf(tot, 0.0f);
-        const float term_rew = c.has_termination ? ((reset && !time_out) ? 1.0f : 0.0f) * c.termination_scale : 0.0f;
-        q_rew[e] = tot + term_rew;
+      const Rows Rw = {rows, io.hist + n * H, e};
+      const NoiseKeyT nk = {c.seed, n + io.env_offset, push_count};
+      const float b = pe[P_BLEND], omb = 1.0f - b;
+      const float* r0 = tab.records + (int64_t)__float_as_int(pe[P_F0]) * KC(rec_stride);
+      const float* r1 = tab.records + (int64_t)__float_as_int(pe[P_F1]) * KC(rec_stride);
+
+      // ---- a. history ring -> its places in the rows (HistoryHandler.query, history_handler.py:46-48) ------------------------
+      {
+        const float* sh = reinterpret_cast<const float*>(smem + KC(i_hist)) + e * H;
+        if ((H & 3) == 0 && !KC(hist_any_mul)) {  // four ring elements per lane and pass
+          auto plane4 = [&](int has, int plane, int gd, int i, const float4& v) {
+            if (!has) return;
+            const int4 m = reinterpret_cast<const int4*>(hmap)[plane * (H >> 2) + i];
+            float* r = rows + e * gd;
+            if (m.x >= 0) r[m.x] = v.x;
+            if (m.y >= 0) r[m.y] = v.y;
+            if (m.z >= 0) r[m.z] = v.z;
+            if (m.w >= 0) r[m.w] = v.w;
+          };
+          for (int i = lane; i < (H >> 2); i += 32) {
+            float4 v = reinterpret_cast<const float4*>(sh)[i];
+            v.x = clampf(v.x, clipv); v.y = clampf(v.y, clipv); v.z = clampf(v.z, clipv); v.w = clampf(v.w, clipv);
+            plane4(KC(ghist0), 0, KC(gdim0), i, v);
+            plane4(KC(ghist1), KC(ghist0), KC(gdim1), i, v);
+            plane4(KC(ghist2), KC(ghist0) + KC(ghist1), KC(gdim2), i, v);
+            plane4(KC(ghist3), KC(ghist0) + KC(ghist1) + KC(ghist2), KC(gdim3), i, v);
+          }
+        } else {
+          auto plane1 = [&](int has, int plane, int gd, int i, float v) {
+            if (!has) return;
+            const int m = hmap[plane * H + i];
+            if (m >= 0) rows[m + e * gd] = clampf(KC(hist_any_mul) ? v * hmul[plane * H + i] : v, clipv);
+          };
+          for (int i = lane; i < H; i += 32) {
+            const float v = sh[i];
+            plane1(KC(ghist0), 0, KC(gdim0), i, v);
+            plane1(KC(ghist1), KC(ghist0), KC(gdim1), i, v);
+            plane1(KC(ghist2), KC(ghist0) + KC(ghist1), KC(gdim2), i, v);
+            plane1(KC(ghist3), KC(ghist0) + KC(ghist1) + KC(ghist2), KC(gdim3), i, v);
+          }
+        }
       }
+      __syncwarp();  // (the scratch row may alias this env's history row)
+
+      // ---- b. dofs (lane = dof) -------------------------------------------------------------------------------------------
+      if (lane < D) {
+        const int d = lane, x = e * D + d;
+        const float2 ds = reinterpret_cast<const float2*>(smem + KC(i_dof))[x];
+        const float dpos = ds.x, dvel = ds.y;
+        const float act = reinterpret_cast<const float*>(smem + KC(i_act))[x], tq = reinterpret_cast<const float*>(smem + KC(i_tq))[x];
+        const float lact = reinterpret_cast<const float*>(smem + KC(i_lact))[x], ldv = reinterpret_cast<const float*>(smem + KC(i_ldv))[x];
+        const float ddef = io.default_dof_pos[n * KC(default_dof_stride) + d];
+        const float dja = (omb * __ldg(r0 + e_dp + d) + b * __ldg(r1 + e_dp + d)) - dpos;   // motion_tracking.py:661-665
+        const float djv = (omb * __ldg(r0 + e_dv + d) + b * __ldg(r1 + e_dv + d)) - dvel;
+        const float dact = lact - act, dacc = (ldv - dvel) / dt;
+        const float lim_t = T.lim_tq[d];
+        float* dp_ = scr + d;
+        dp_[DR_DJA * D] = dja; dp_[DR_DJV2 * D] = djv * djv; dp_[DR_TQ2 * D] = tq * tq; dp_[DR_DACT2 * D] = dact * dact;
+        dp_[DR_DV2 * D] = dvel * dvel; dp_[DR_ACC2 * D] = dacc * dacc;
+        dp_[DR_LPOS * D] = -fminf(dpos - T.lim_lo[d], 0.0f) + fmaxf(dpos - T.lim_hi[d], 0.0f);  // legged_robot_base.py:974-1002
+        dp_[DR_LVEL * D] = fminf(fmaxf(fabsf(dvel) - T.lim_vel[d], 0.0f), 1.0f);
+        dp_[DR_LTQ * D] = KC(cur_torque_enable) ? fminf(fmaxf(fabsf(tq) - lim_t, 0.0f), 1.0f) : fmaxf(fabsf(tq) - lim_t, 0.0f);
+        emit1<kNoise>(T, Rw, S_DOF_POS, d, dpos - ddef, clipv, nk);
+        emit1<kNoise>(T, Rw, S_DOF_VEL, d, dvel, clipv, nk);
+        emit1<kNoise>(T, Rw, S_ACTIONS, d, act, clipv, nk);
+        emit1<kNoise>(T, Rw, S_DR_KP, d, reinterpret_cast<const float*>(smem + KC(i_kp))[x], clipv, nk);
+        emit1<kNoise>(T, Rw, S_DR_KD, d, reinterpret_cast<const float*>(smem + KC(i_kd))[x], clipv, nk);
+        if (KC(dif_joint_used)) {
+          emit1<kNoise>(T, Rw, S_DIF_JOINT, d, dja, clipv, nk);
+          emit1<kNoise>(T, Rw, S_DIF_JOINT_VEL, d, djv, clipv, nk);
+        }
+        // _post_compute_observations_callback, legged_robot_base.py:398-405
+        reinterpret_cast<float*>(smem + KC(q_lact))[x] = act; reinterpret_cast<float*>(smem + KC(q_ldpos))[x] = dpos; reinterpret_cast<float*>(smem + KC(q_ldvel))[x] = dvel;
+      }
+      __syncwarp();
+      {  // dof sums: three lanes per value (dofs part, part + 3, ...), combined in lane order - a fixed summation order
+        const int k = lane / 3, part = lane - 3 * k;
+        float v = 0.0f;
+        if (k < kDofRaw) {
+          const float* src = scr + k * D;
+          if (k == DR_DJA) for (int d = part; d < D; d += 3) v += src[d] * src[d];
+          else for (int d = part; d < D; d += 3) v += src[d];
+        } else if (k == kDofRaw) {
+          for (int d = part; d < D; d += 3) v = fmaxf(v, fabsf(scr[DR_DJA * D + d]));
+        }
+        const float v1 = __shfl_down_sync(0xffffffffu, v, 1), v2 = __shfl_down_sync(0xffffffffu, v, 2);
+        const float tot = k == kDofRaw ? fmaxf(fmaxf(v, v1), v2) : (v + v1) + v2;
+        if (part == 0 && k <= kDofRaw) {
+          if (k == DR_DJA) { rve[V_SIGMA_ERR + G_JOINT_POS] = tot / (float)D; rve[V_JOINT_N] = sqrtf(tot); }
+          else if (k == DR_DJV2) rve[V_SIGMA_ERR + G_JOINT_VEL] = tot / (float)D;
+          else if (k == kDofRaw) rve[V_SIGMA_ERR + G_MAX_JOINT] = tot;
+          else rve[k == DR_TQ2 ? V_TQ2 : k == DR_DACT2 ? V_DACT2 : k == DR_DV2 ? V_DV2 : k == DR_ACC2 ? V_ACC2 : k == DR_LPOS ? V_LIM_POS : k == DR_LVEL ? V_LIM_VEL : V_LIM_TQ] = tot;
+        }
+      }
+      __syncwarp();
+
+      // ---- c. bodies (lane = body): reference pose (lerp / slerp of the frame pair), extended bodies, differences, heading-frame features
+      int far = 0, n_collide = 0;
+      const float hz = pe[P_HZ], hw = pe[P_HW];
+      for (int j0 = 0; j0 < J; j0 += 32) {
+        const int j = j0 + lane;
+        bool collide = false;
+        if (j < J) {
+          V3 p, v, w; Q4 q;
+          if (j < Jb) {
+            const float* bs = s_body + j * 13;
+            p = {bs[0], bs[1], bs[2]}; q = {bs[3], bs[4], bs[5], bs[6]}; v = {bs[7], bs[8], bs[9]}; w = {bs[10], bs[11], bs[12]};
+          } else {  // motion_tracking.py:619-643; the position chain is unfused (it feeds the motion_far comparison)
+            const int x = j - Jb;
+            const float* bs = s_body + c.ext_parent[x] * 13;
+            const Q4 qp = {bs[3], bs[4], bs[5], bs[6]};
+            const V3 off = {c.ext_pos[x][0], c.ext_pos[x][1], c.ext_pos[x][2]};
+            const Q4 qe = {c.ext_rot_xyzw[x][0], c.ext_rot_xyzw[x][1], c.ext_rot_xyzw[x][2], c.ext_rot_xyzw[x][3]};
+            const V3 r = quat_rotate_x(qe, quat_rotate_x(qp, off, false), false);
+            p = {xa(r.x, bs[0]), xa(r.y, bs[1]), xa(r.z, bs[2])};
+            q = quat_mul(qp, qe);
+            w = {bs[10], bs[11], bs[12]};
+            v = {bs[7] + (w.y * off.z - w.z * off.y), bs[8] + (w.z * off.x - w.x * off.z), bs[9] + (w.x * off.y - w.y * off.x)};
+          }
+          const float4 qa = __ldg(reinterpret_cast<const float4*>(r0) + j);
+          const float4 qb = __ldg(reinterpret_cast<const float4*>(r1) + j);
+          float rpz[3], rvv[3], rw[3];
+#pragma unroll
+          for (int k = 0; k < 3; ++k) {
+            rpz[k] = xa(xa(xm(omb, __ldg(r0 + e_pos + 3 * j + k)), xm(b, __ldg(r1 + e_pos + 3 * j + k))), s_org[k]);
+            rvv[k] = omb * __ldg(r0 + e_vel + 3 * j + k) + b * __ldg(r1 + e_vel + 3 * j + k);
+            rw[k] = omb * __ldg(r0 + e_ang + 3 * j + k) + b * __ldg(r1 + e_ang + 3 * j + k);
+          }
+          const Q4 rr = slerp_t({qa.x, qa.y, qa.z, qa.w}, {qb.x, qb.y, qb.z, qb.w}, b);
+          if (KC(ref_pos_out)) {
+            float* o = io.ref_body_pos_extend + n * (3 * J) + 3 * j;
+            o[0] = rpz[0]; o[1] = rpz[1]; o[2] = rpz[2];
+          }
+          if (KC(ref_rot_out)) reinterpret_cast<float4*>(io.ref_body_rot_extend)[n * J + j] = make_float4(rr.x, rr.y, rr.z, rr.w);
+          const V3 dp = {xs(rpz[0], p.x), xs(rpz[1], p.y), xs(rpz[2], p.z)};
+          const float dq0 = rr.x - q.x, dq1 = rr.y - q.y, dq2 = rr.z - q.z, dq3 = rr.w - q.w;
+          const V3 dv = {rvv[0] - v.x, rvv[1] - v.y, rvv[2] - v.z};
+          const V3 dw = {rw[0] - w.x, rw[1] - w.y, rw[2] - w.z};
+          const float nrm = norm3(dp.x, dp.y, dp.z);
+          float* bp = scr + j;
+          bp[BR_MPOS * J] = div3((dp.x * dp.x + dp.y * dp.y) + dp.z * dp.z);
+          bp[BR_NRM * J] = nrm;
+          bp[BR_ROT * J] = (((dq0 * dq0 + dq1 * dq1) + dq2 * dq2) + dq3 * dq3) * 0.25f;
+          bp[BR_VEL * J] = div3((dv.x * dv.x + dv.y * dv.y) + dv.z * dv.z);
+          bp[BR_ANG * J] = div3((dw.x * dw.x + dw.y * dw.y) + dw.z * dw.z);
+          if (nrm > far_thr) far = 1;
+          if (j < Jb && (((unsigned long long)KC(penalised_mask) >> j) & 1ull)) {
+            const float* fc = s_cf + 3 * j;
+            collide = norm3(fc[0], fc[1], fc[2]) > 0.1f;
+          }
+          {
+            const V3 dl = quat_rotate_z(hz, hw, dp);  // motion_tracking.py:694-697
+            emit3<kNoise>(T, Rw, S_DIF_LOCAL, 3 * j, dl.x, dl.y, dl.z, clipv, nk);
+            const V3 lr = quat_rotate_z(hz, hw, {rpz[0] - pe[P_RPX], rpz[1] - pe[P_RPY], rpz[2] - pe[P_RPZ]});  // :705-707
+            emit3<kNoise>(T, Rw, S_LOCAL_REF, 3 * j, lr.x, lr.y, lr.z, clipv, nk);
+          }
+          if (KC(ref_vel_used)) {
+            const V3 lv = quat_rotate_z(hz, hw, {rvv[0], rvv[1], rvv[2]});
+            emit3<kNoise>(T, Rw, S_LOCAL_REF_VEL, 3 * j, lv.x, lv.y, lv.z, clipv, nk);
+            emit3<kNoise>(T, Rw, S_GLOBAL_REF_VEL, 3 * j, rvv[0], rvv[1], rvv[2], clipv, nk);
+          }
+        }
+        n_collide += __popc(__ballot_sync(0xffffffffu, collide));
+      }
+      const bool any_far = __any_sync(0xffffffffu, far);
+      __syncwarp();
+      {  // body sums: three lanes per sum (bodies part, part + 3, ...), combined in lane order
+        const int k = lane / 3, part = lane - 3 * k;
+        float v = 0.0f;
+        if (k < kBodySums) {
+          const float* src = scr + T.bs_raw[k] * J;
+          const uint64_t m = T.bs_mask[k] >> part;
+          const uint32_t mlo = (uint32_t)m, mhi = (uint32_t)(m >> 32);
+          for (int j = part, s = 0; j < J; j += 3, s += 3) {
+            const uint32_t bit = s < 32 ? (mlo >> s) : (mhi >> (s - 32));
+            if (bit & 1u) v += src[j];
+          }
+        }
+        const float v1 = __shfl_down_sync(0xffffffffu, v, 1), v2 = __shfl_down_sync(0xffffffffu, v, 2);
+        if (part == 0 && k < kBodySums) rve[T.bs_slot[k]] = ((v + v1) + v2) / T.bs_div[k];
+      }
+
+      // ---- d. feet (lane = foot): contacts, feet_air_time, contact-force / slip terms ---------------------------------------------
+      float x_air = 0.f, x_force = 0.f, x_slip = 0.f, x_fslip = 0.f, x_cm = 0.f, contact_f = 0.f, air_f = 0.f;
+      bool x_stumble = false;
+      if (lane < KC(n_feet)) {
+        const int fb = c.feet_ids[lane];
+        const float* fc = s_cf + 3 * fb;
+        const float* bs = s_body + 13 * fb;
+        const float last_c = s_envf[4 + lane];
+        air_f = s_envf[2 + lane];
+        const float fn = norm3(fc[0], fc[1], fc[2]);
+        contact_f = fn > 1.0f ? 1.0f : 0.0f;                                   // legged_robot_base.py:352-353
+        const float filt = (contact_f != 0.0f || last_c != 0.0f) ? 1.0f : 0.0f;
+        if (KC(contact_size)) x_cm = fabsf(filt - (omb * __ldg(r0 + e_c + lane) + b * __ldg(r1 + e_c + lane)));
+        const bool fz = fc[2] > 1.0f || last_c != 0.0f;                        // feet_air_time, motion_tracking.py:1307-1319
+        if (KC(has_air_time)) {
+          const float first = (air_f > 0.0f && fz) ? 1.0f : 0.0f;
+          air_f = xa(air_f, dt);
+          x_air = (air_f - KC(desired_feet_air_time)) * first;
+          air_f *= fz ? 0.0f : 1.0f;
+        }
+        x_force = fmaxf(fn - KC(max_contact_force), 0.0f);                        // :1321-1323
+        x_stumble = norm2(fc[0], fc[1]) > 5.0f * fabsf(fc[2]);                  // :1325-1328
+        x_slip = norm3(bs[7], bs[8], bs[9]) * contact_f;                        // legged_robot_base.py:1004-1010
+        x_fslip = contact_f * norm2(bs[7], bs[8]);                              // :1012-1017
+      }
+      x_air += __shfl_xor_sync(0xffffffffu, x_air, 1); x_force += __shfl_xor_sync(0xffffffffu, x_force, 1);
+      x_slip += __shfl_xor_sync(0xffffffffu, x_slip, 1); x_fslip += __shfl_xor_sync(0xffffffffu, x_fslip, 1);
+      x_cm += __shfl_xor_sync(0xffffffffu, x_cm, 1);
+      const bool stumble = __any_sync(0xffffffffu, x_stumble);
+      float air1 = __shfl_sync(0xffffffffu, air_f, 1), contact1 = __shfl_sync(0xffffffffu, contact_f, 1);  // lane 0 packs the state
+
+      // ---- e. termination (legged_robot_base.py:408-489, motion_tracking.py:330-358) -------------------------------------------
+      const int64_t last_ep = ep_in + 1;
+      int64_t ep = last_ep;
+      float start = s_envf[0], mlen = s_envf[1], etr = s_envf[6];
+      const bool t_grav = KC(term_gravity) && pe[P_GRAVN] > KC(term_gravity_thr);
+      const bool t_far = KC(term_motion_far) && any_far;
+      const bool t_out = ep > KC(max_episode_length);
+      const bool t_end = KC(term_motion_end) && (xa(xm((float)ep, dt), start) > mlen);
+      const bool time_out = t_out || t_end;
+      const bool reset = t_grav || t_far || time_out;
+      if (lane == 0) {
+        rve[V_T_GRAV] = t_grav; rve[V_T_FAR] = t_far; rve[V_T_OUT] = time_out; rve[V_T_END] = t_end;
+        rve[V_RESET] = reset; rve[V_ONE] = 1.0f; rve[V_ALIVE] = 1.0f;
+        rve[V_CONTACT] = 1.0f - x_cm / (float)KC(n_feet); rve[V_CONTACT_V2] = 0.5f - x_cm / (float)KC(n_feet);
+        rve[V_ORIENT] = pe[P_ORIENT];
+        rve[V_AIR] = x_air; rve[V_FORCE] = x_force; rve[V_STUMBLE] = stumble ? 1.0f : 0.0f; rve[V_SLIP] = x_slip; rve[V_FSLIP] = x_fslip;
+        rve[V_COLLIDE] = (float)n_collide;
+      }
+      __syncwarp();
+
+      // ---- f. rewards (lane = term; legged_robot_base.py:715-761) + episode sums ---------------------------------------------------
+      {
+        float rew = 0.0f;
+        if (lane < R) {
+          const int kind = T.r_kind[lane];
+          float v = rve[T.r_arg[lane]];
+          if (kind != K_RAW) {
+            v = expf(-v / T.r_sigma[lane]);
+            if (kind == K_EXP2)  // teleop_body_position_extend, motion_tracking.py:1177-1199
+              v = v * KC(w_lower) + expf(-rve[V_SIGMA_ERR + G_UPPER] / T.sigma[G_UPPER]) * KC(w_upper);
+          }
+          rew = v * T.r_scale[lane] * T.r_pen[lane];
+        }
+        const float term_rew = KC(has_termination) ? ((reset && !time_out) ? 1.0f : 0.0f) * KC(termination_scale) : 0.0f;
+        float* q_rew = reinterpret_cast<float*>(smem + KC(q_rew));
+        if (KC(use_vec_reward)) {
+          float v = rew;
+          if (KC(only_positive)) v = fmaxf(v, 0.0f);
+          if (lane == R - 1) v += term_rew;  // the reference's stale loop index, legged_robot_base.py:744
+          if (lane < R) q_rew[e * (R + 1) + lane] = v;
+          if (lane == R) q_rew[e * (R + 1) + R] = 0.0f;
+        } else {  // rew_buf += rew term by term (legged_robot_base.py:733): a sequential fp32 sum in term order
+          float tot = 0.0f;
+          for (int r = 0; r < R; ++r) tot += __shfl_sync(0xffffffffu, rew, r);
+          if (KC(only_positive)) tot = fmaxf(tot, 0.0f);
+          if (lane == 0) q_rew[e] = tot + term_rew;
+        }
+        if (lane < KC(n_sums)) {
+          float ev = reinterpret_cast<const float*>(smem + KC(i_es))[e * KC(n_sums) + lane] + (lane < R ? rew : term_rew);
+          if (reset) { io.last_episode_sums[n * KC(n_sums) + lane] = ev; ev = 0.0f; }  // extras["episode"], legged_robot_base.py:509-513
+          reinterpret_cast<float*>(smem + KC(q_es))[e * KC(n_sums) + lane] = ev;
+        }
+      }
+
+      // ---- g. scalar features into the rows (legged_robot_base.py:1114-1215; motion_tracking.py:944-1015) -------------------------
+      int64_t delay = reinterpret_cast<const long long*>(smem + KC(i_delay))[e];
+      auto emit_scalar_features = [&](int64_t delay_) {
+        for (int i = lane; i < KC(n_feat); i += 32) {
+          const int k = T.feat_src[i], el = T.feat_el[i];
+          float val;
+          if (i < 9) val = pe[P_BLV + i];
+          else if (k == S_DR_COM) val = reinterpret_cast<const float*>(smem + KC(i_com))[e * 3 + el];
+          else if (k == S_PHASE) val = pe[P_PHASE];        // stale for envs that reset, like the reference
+          else if (k == S_DR_FRICTION) val = reinterpret_cast<const float*>(smem + KC(i_fric))[e];
+          else if (k == S_DR_DELAY) val = (float)delay_;
+          else if (k == S_BASE_POS_Z) val = pe[P_RPZ];
+          else val = reinterpret_cast<const float*>(smem + KC(i_mass))[e * KC(L) + el];
+          emit1<kNoise>(T, Rw, k, el, val, clipv, nk);
+        }
+      };
+      if (!reset) emit_scalar_features(delay);
+
+      // ---- h. reset (legged_robot_base.py:491-516, 647-686, 587-635; motion_tracking.py:274-296, 369-384, 445-543) ---------------
+      float air0 = air_f, contact0 = contact_f;  // meaningful in lane 0
       if (reset) {
         const int clip = __float_as_int(pe[P_CLIP]);
         const bool ld = lane < D;
-        const Rows Rw = {rows, io.hist + n * H};
-        const NoiseKeyT nk = {c.seed, n + io.env_offset, push_count};
         const Rng rng = {make_uint2((uint32_t)c.seed, (uint32_t)(c.seed >> 32)), (uint32_t)(n + io.env_offset), (uint32_t)((uint64_t)(n + io.env_offset) >> 32), push_count};
         if (ld) io.actions[n * D + lane] = 0.0f;
         air0 = 0.0f; air1 = 0.0f; contact0 = 0.0f; contact1 = 0.0f;
         // HistoryHandler.reset: zero the ring and what the observation rows already took from it
         for (int i = lane; i < H; i += 32) {
           io.hist[n * H + i] = 0.0f;
-          for (int d = 0; d < P.n_hd; ++d) {
-            const int m = hmap[d * H + i];
-            if (m >= 0) rows[(m & 0xffffff) + e * T.gdim[m >> 24]] = 0.0f;
-          }
+          auto zero1 = [&](int has, int plane, int gd) {
+            if (!has) return;
+            const int m = hmap[plane * H + i];
+            if (m >= 0) rows[m + e * gd] = 0.0f;
+          };
+          zero1(KC(ghist0), 0, KC(gdim0));
+          zero1(KC(ghist1), KC(ghist0), KC(gdim1));
+          zero1(KC(ghist2), KC(ghist0) + KC(ghist1), KC(gdim2));
+          zero1(KC(ghist3), KC(ghist0) + KC(ghist1) + KC(ghist2), KC(gdim3));
         }
         __syncwarp();
         ep = 0;
@@ -770,19 +830,18 @@ __global__ void __launch_bounds__(kNT, 3) track_tile_kernel(const __grid_constan
           if (c.use_rao)
             io.rao_scale[n * D + lane] = io.inject_rao ? io.inject_rao[n * D + lane] : xa(xm(xs(c.rao_lim, -c.rao_lim), rng.uniform(112 + lane)), -c.rao_lim);
         }
-        int64_t delay = s_delay[e];
         if (c.randomize_ctrl_delay) {
           delay = io.inject_delay ? io.inject_delay[n] : c.delay_lo + (int64_t)(rng.draw(1).x % (uint32_t)(c.delay_hi - c.delay_lo + 1));
           if (lane == 0) io.action_delay_idx[n] = delay;
         }
-        etr = __fdiv_rn(xa(xm((float)last_ep, dt), start), mlen);              // motion_tracking.py:281-282
+        etr = __fdiv_rn(xa(xm((float)last_ep, dt), start), mlen);           // motion_tracking.py:281-282
         mlen = tab.clip_length[clip];                                       // _resample_motion_times
         start = io.inject_start_times ? io.inject_start_times[n] : xm(rng.uniform(0), mlen);
         // _reset_dofs / _reset_root_states from the motion state at the new time (unfused: these are simulator state)
         const FrameBlend f2 = frame_blend_x(tab, clip, xa(xm((float)(ep + 1), dt), start));
         const float b2 = f2.blend, omb2 = 1.0f - b2;
-        const float* q0 = tab.records + f2.f0 * tab.rec_stride;
-        const float* q1 = tab.records + f2.f1 * tab.rec_stride;
+        const float* q0 = tab.records + f2.f0 * KC(rec_stride);
+        const float* q1 = tab.records + f2.f1 * KC(rec_stride);
         if (ld) {
           dpos2 = xa(xm(omb2, q0[e_dp + lane]), xm(b2, q1[e_dp + lane]));
           dvel2 = xa(xm(omb2, q0[e_dv + lane]), xm(b2, q1[e_dv + lane]));
@@ -808,53 +867,49 @@ __global__ void __launch_bounds__(kNT, 3) track_tile_kernel(const __grid_constan
           } else {
             const int el = lane < 3 ? e_pos + lane : (lane < 10 ? e_vel + (lane - 7) : e_ang + (lane - 10));
             v = xa(xm(omb2, q0[el]), xm(b2, q1[el]));
-            if (lane < 3) v = xa(v, s_org[e * 3 + lane]);
+            if (lane < 3) v = xa(v, s_org[lane]);
             const float ns = lane < 3 ? c.reset_noise[2] : (lane < 10 ? c.reset_noise[4] : c.reset_noise[5]);
             if (ns != 0.0f) v = xa(v, xm(rng.normal(8 + lane), ns));
           }
           io.root_state[n * 13 + lane] = v;
         }
-        // the observations of an env that reset: dof-wise features from the new state, scalar features again (their push
-        // slots were just zeroed; ref_motion_phase & co. stay stale like the reference's)
+        // the observations of an env that reset: dof-wise features from the new state; the scalar features go in (again)
+        // after the ring was zeroed (ref_motion_phase & co. stay stale like the reference's)
         if (ld) {
-          const float ddef = io.default_dof_pos[n * io.default_dof_stride + lane];
-          emit1<kNoise>(T, Rw, S_DOF_POS, e, lane, dpos2 - ddef, clipv, nk);
-          emit1<kNoise>(T, Rw, S_DOF_VEL, e, lane, dvel2, clipv, nk);
-          emit1<kNoise>(T, Rw, S_ACTIONS, e, lane, 0.0f, clipv, nk);
-          emit1<kNoise>(T, Rw, S_DR_KP, e, lane, kp2, clipv, nk);
-          emit1<kNoise>(T, Rw, S_DR_KD, e, lane, kd2, clipv, nk);
-          q_lact[e * D + lane] = 0.0f; q_ldpos[e * D + lane] = dpos2; q_ldvel[e * D + lane] = dvel2;
+          const float ddef = io.default_dof_pos[n * KC(default_dof_stride) + lane];
+          emit1<kNoise>(T, Rw, S_DOF_POS, lane, dpos2 - ddef, clipv, nk);
+          emit1<kNoise>(T, Rw, S_DOF_VEL, lane, dvel2, clipv, nk);
+          emit1<kNoise>(T, Rw, S_ACTIONS, lane, 0.0f, clipv, nk);
+          emit1<kNoise>(T, Rw, S_DR_KP, lane, kp2, clipv, nk);
+          emit1<kNoise>(T, Rw, S_DR_KD, lane, kd2, clipv, nk);
+          const int x = e * D + lane;
+          reinterpret_cast<float*>(smem + KC(q_lact))[x] = 0.0f; reinterpret_cast<float*>(smem + KC(q_ldpos))[x] = dpos2; reinterpret_cast<float*>(smem + KC(q_ldvel))[x] = dvel2;
         }
-        for (int i = lane; i < P.n_feat; i += 32) {
-          const int k = T.feat_src[i], el = T.feat_el[i];
-          float val;
-          if (i < 9) val = pe[P_BLV + i];
-          else if (k == S_DR_COM) val = s_com[e * 3 + el];
-          else if (k == S_PHASE) val = pe[P_PHASE];
-          else if (k == S_DR_FRICTION) val = s_fric[e];
-          else if (k == S_DR_DELAY) val = (float)delay;
-          else if (k == S_BASE_POS_Z) val = pe[P_RPZ];
-          else val = s_mass[e * c.L + el];
-          emit1<kNoise>(T, Rw, k, e, el, val, clipv, nk);
-        }
+        emit_scalar_features(delay);
       }
+
+      // ---- i. state write-back, cross-env sums ----------------------------------------------------------------------------------------
       if (lane == 0) {
-        float4* of = reinterpret_cast<float4*>(q_envf + e * PBHC_ENVF_STRIDE);
-        of[0] = make_float4(start, mlen, air0, c.n_feet > 1 ? air1 : 0.0f);
-        of[1] = make_float4(contact0, c.n_feet > 1 ? contact1 : 0.0f, etr, s_envf[e * PBHC_ENVF_STRIDE + 7]);
-        q_ep[e] = ep;
-        q_reset[e] = reset ? 1 : 0;
+        float4* of = reinterpret_cast<float4*>(smem + KC(q_envf)) + e * 2;
+        of[0] = make_float4(start, mlen, air0, KC(n_feet) > 1 ? air1 : 0.0f);
+        of[1] = make_float4(contact0, KC(n_feet) > 1 ? contact1 : 0.0f, etr, s_envf[7]);
+        reinterpret_cast<long long*>(smem + KC(q_ep))[e] = ep;
+        reinterpret_cast<long long*>(smem + KC(q_reset))[e] = reset ? 1 : 0;
         io.time_out_buf[n] = time_out ? 1 : 0;
-        rve[V_ETR] = etr;
-        rve[V_RESET_EPLEN] = reset ? (float)last_ep : 0.0f;
+      }
+      if (lane < kAccLo) {  // per-lane fp64 accumulation of the cross-env sums (slot = lane, layout PBHC_A_*)
+        double a = (double)rve[lane];
+        if (lane == V_RESET_EPLEN) a = reset ? (double)last_ep : 0.0;
+        if (lane == V_ETR) a = (double)etr;
+        if (lane == V_ETR_SQ) a = (double)etr * (double)etr;
+        acc_reg += a;
       }
     }
     fence_async();
     __syncthreads();
 
-    // ---- 7. outputs leave, the next tile's inputs are requested, cross-env sums -----------------------------------------------------
-    const bool bulk_now = P.bulk_ok && cnt == kTE;
-    if (bulk_now) {
+    // ---- outputs leave, the next tile's inputs are requested -----------------------------------------------------------------------------
+    if (bulk) {
       if (warp == 0) {
         for (int i = lane; i < P.n_out; i += 32) {
           const TileDesc d = P.out[i];
@@ -871,144 +926,230 @@ __global__ void __launch_bounds__(kNT, 3) track_tile_kernel(const __grid_constan
         for (int w = tid; w < nw; w += kNT) dst[w] = src[w];
       }
     }
-    const int next = tile + (int)gridDim.x;
-    loaded = false;
-    if (P.bulk_ok && next < n_tiles && (next + 1) * kTE <= n_envs) { if (warp == 0) issue_loads(next * kTE); loaded = true; }
-    if (tid < kAccLo) {  // per-thread fp64 accumulation of the cross-env sums (slot = tid, layout PBHC_A_*), envs in index order
-      for (int e = 0; e < cnt; ++e) {
-        double a = (double)rv[e * kRvT + tid];
-        if (tid == V_ETR_SQ) { const double x = (double)rv[e * kRvT + V_ETR]; a = x * x; }
-        acc_reg += a;
-      }
-    }
+    pre_ready = have_small_next;  // (the next tile's scalars were computed above)
+    const bool big = is_bulk(tile + stride), small = is_bulk(tile + 2 * stride);
+    if (big && warp == 0) issue_loads(tile + stride, true, tile + 2 * stride, small, sb);
+    have_small_next = small;
   }
   if (warp == 0) bulk_wait_read();
-  if (tid < PBHC_ACC) io.partials[(int64_t)blockIdx.x * PBHC_ACC + tid] = tid < kAccLo ? acc_reg : 0.0;
+  // block partials: 64 threads add the warps' sums up in warp order
+  __syncthreads();
+  double* wacc = reinterpret_cast<double*>(smem + KC(o_rows));
+  if (lane < PBHC_ACC / 2) { wacc[warp * 32 + lane] = lane < kAccLo ? acc_reg : 0.0; }
+  __syncthreads();
+  if (tid < PBHC_ACC) {
+    double v = 0.0;
+    if (tid < 32) for (int w = 0; w < kTE; ++w) v += wacc[w * 32 + tid];
+    io.partials[(int64_t)blockIdx.x * PBHC_ACC + tid] = v;
+  }
 }
 
-extern int g_track_info[4];
+#ifdef __CUDACC_RTC__
+}  // namespace pbhc
+// the specialised kernel: this file compiled by NVRTC with -DPBHC_SPEC and the generated "track_spec.h" (jit.cu)
+extern "C" __global__ void __launch_bounds__(pbhc::kNT, 3) pbhc_track_tile_spec(const __grid_constant__ pbhc::TileParams P) {
+  pbhc::track_tile_body<PBHC_NOISE != 0>(P);
+}
+#else
 
-// host side: slab layout + descriptor tables + launch (called by pbhc_track_step for general == 0)
-int track_tile_launch(const PbhcTrackCfg& c, const PbhcTableDesc& tab, const PbhcTrackIO& io, int64_t n, cudaStream_t stream, int* blocks_out) {
-  static thread_local TileParams P;
+template <bool kNoise>
+__global__ void __launch_bounds__(kNT, 3) track_tile_kernel(const __grid_constant__ TileParams P) { track_tile_body<kNoise>(P); }
+
+extern int g_track_info[4];
+int jit_get(const char* what, const std::string& spec_header, bool noise, const void** kernel);   // jit.cu: 0 = *kernel is the cudaKernel_t of the specialised kernel
+
+std::string tile_spec_header(const HotK& k) {
+  char buf[128];
+  std::string h = "// generated by pbhc_b200 (track_tile.cu tile_spec_header): launch constants of one env config\nnamespace spec {\n";
+#define X(n) snprintf(buf, sizeof(buf), "constexpr int %s = %d;\n", #n, k.n); h += buf;
+  PBHC_HOTK_INT(X)
+#undef X
+#define X(n) snprintf(buf, sizeof(buf), "constexpr float %s = %af;\n", #n, (double)k.n); h += buf;
+  PBHC_HOTK_FLT(X)
+#undef X
+#define X(n) snprintf(buf, sizeof(buf), "constexpr long long %s = (long long)0x%llxULL;\n", #n, (unsigned long long)k.n); h += buf;
+  PBHC_HOTK_I64(X)
+#undef X
+  h += "}  // namespace spec\n";
+  return h;
+}
+
+// the kernel specialised for these constants (kernel == nullptr: compile into the on-disk cache only)
+static int jit_track_tile(const HotK& k, bool noise, const void** kernel) {
+  static thread_local HotK last_k;
+  static thread_local bool last_noise = false, have = false;
+  static thread_local const void* last_fn = nullptr;
+  static thread_local int last_rc = 0;
+  if (kernel && have && last_noise == noise && !memcmp(&last_k, &k, sizeof(k))) { *kernel = last_fn; return last_rc; }
+  const void* fn = nullptr;
+  const int rc = jit_get("track_tile", tile_spec_header(k), noise, kernel ? &fn : nullptr);
+  if (kernel) { last_k = k; last_noise = noise; have = true; last_fn = fn; last_rc = rc; *kernel = fn; }
+  return rc;
+}
+
+// shared-memory layout + hot constants + descriptor tables of one launch; returns the dynamic shared memory size (< 0: error)
+static int tile_plan(const PbhcTrackCfg& c, const PbhcTableDesc& tab, const PbhcTrackIO& io, int64_t n, TileParams& P) {
   P.c = c; P.tab = tab; P.io = io;
   if (n > 0x7fffffffLL / 64) { set_error("pbhc_track_step: too many envs for one launch"); return PBHC_E_RANGE; }
   P.n = (int)n; P.n_tiles = (int)((n + kTE - 1) / kTE);
+  HotK& k = P.k;
+  memset(&k, 0, sizeof(k));
   const int D = c.D, J = c.J, Jb = c.Jb, H = c.hist_row, L = c.L;
   if (c.n_feet > 2) { set_error("pbhc_track_step: at most two feet"); return PBHC_E_RANGE; }
-  P.has_air_time = 0;
-  for (int r = 0; r < c.n_rewards; ++r) if (c.reward_id[r] == R_FEET_AIR_TIME) P.has_air_time = 1;
+  if (c.n_rewards > 30) { set_error("pbhc_track_step: more than 30 reward terms"); return PBHC_E_RANGE; }
+  if (L > 48) { set_error("pbhc_track_step: more than 48 randomised link masses"); return PBHC_E_RANGE; }
+  k.J = J; k.Jb = Jb; k.D = D; k.L = L; k.H = H; k.n_ext = c.n_ext; k.n_feet = c.n_feet; k.n_groups = c.n_groups; k.R = c.n_rewards;
+  k.n_sums = c.n_episode_sums; k.n_feat = 16 + L; k.contact_size = tab.contact_size; k.rec_stride = tab.rec_stride;
+  k.use_vec_reward = c.use_vec_reward; k.only_positive = c.only_positive_rewards; k.has_termination = c.has_termination;
+  k.cur_torque_enable = c.cur_torque.enable; k.term_gravity = c.term_gravity; k.term_motion_far = c.term_motion_far; k.term_motion_end = c.term_motion_end;
+  k.dif_joint_used = (c.src_used_mask & ((1ull << S_DIF_JOINT) | (1ull << S_DIF_JOINT_VEL))) ? 1 : 0;
+  k.ref_vel_used = (c.src_used_mask & ((1ull << S_LOCAL_REF_VEL) | (1ull << S_GLOBAL_REF_VEL))) ? 1 : 0;
+  k.ref_pos_out = io.ref_body_pos_extend ? 1 : 0; k.ref_rot_out = io.ref_body_rot_extend ? 1 : 0;
+  k.default_dof_stride = (int)io.default_dof_stride;
+  k.dt = c.dt; k.clip_obs = c.clip_obs; k.term_gravity_thr = c.term_gravity_thr; k.w_lower = c.w_lower; k.w_upper = c.w_upper;
+  k.termination_scale = c.termination_scale; k.desired_feet_air_time = c.desired_feet_air_time; k.max_contact_force = c.max_contact_force;
+  k.max_episode_length = c.max_episode_length; k.penalised_mask = (long long)c.penalised_mask;
+  for (int r = 0; r < c.n_rewards; ++r) if (c.reward_id[r] == R_FEET_AIR_TIME) k.has_air_time = 1;
   int hrow = 0;
-  for (int k = 0; k < PBHC_MAX_HIST_KEYS; ++k) { P.hist_base[k] = hrow; if (k < c.n_hist_keys) hrow += c.hist_len[k] * c.hist_dim[k]; }
-  int per_key[PBHC_MAX_HIST_KEYS] = {0};
-  P.hist_any_mul = 0; P.n_hd = 0;
+  for (int i = 0; i < PBHC_MAX_HIST_KEYS; ++i) { P.hist_base[i] = hrow; if (i < c.n_hist_keys) hrow += c.hist_len[i] * c.hist_dim[i]; }
+  int ghist[PBHC_MAX_OBS_GROUPS] = {0, 0, 0, 0};
   for (int e = 0; e < c.n_hist_dst; ++e) {
     const PbhcHistDst& h = c.hist_dst[e];
-    if (++per_key[h.key] > P.n_hd) P.n_hd = per_key[h.key];
-    if (h.mul != 1.0f) P.hist_any_mul = 1;
+    ghist[h.group] = 1;
+    if (h.mul != 1.0f) k.hist_any_mul = 1;
   }
-  P.e_pos = 4 * J; P.e_vel = 7 * J; P.e_ang = 10 * J; P.e_dp = 13 * J; P.e_dv = P.e_dp + D; P.e_c = P.e_dv + D;
-  auto inv16 = [](int d) { return d > 0 ? (65536 + d - 1) / d : 0; };
-  P.n_cols = c.use_vec_reward ? (c.n_rewards + 1 > c.n_episode_sums ? c.n_rewards + 1 : c.n_episode_sums) : (c.n_rewards > c.n_episode_sums ? c.n_rewards : c.n_episode_sums);
-  if (P.n_cols < 1) P.n_cols = 1;
-  P.n_feat = 16 + (L < 48 ? L : 48);
-  if (L > 48) { set_error("pbhc_track_step: more than 48 randomised link masses"); return PBHC_E_RANGE; }
-  P.inv_j = inv16(J); P.inv_d = inv16(D); P.inv_r = inv16(P.n_cols); P.inv_f = inv16(P.n_feat);
+  k.ghist0 = ghist[0]; k.ghist1 = ghist[1]; k.ghist2 = ghist[2]; k.ghist3 = ghist[3];
+  k.n_hd = ghist[0] + ghist[1] + ghist[2] + ghist[3];
+  k.e_pos = 4 * J; k.e_vel = 7 * J; k.e_ang = 10 * J; k.e_dp = 13 * J; k.e_dv = k.e_dp + D; k.e_c = k.e_dv + D;
   // ---- shared-memory layout ----
   int off = 0;
   auto take = [&](int bytes) { const int o = off; off += (bytes + 15) & ~15; return o; };
-  P.o_bar = take(16);
-  P.o_flags = take(3 * kTE * 4);
-  P.o_tab = take((int)sizeof(TileTables));
-  P.o_hmap = take(4 * (P.n_hd > 0 ? P.n_hd : 1) * (H > 0 ? H : 1));
-  P.o_hmul = P.hist_any_mul ? take(4 * P.n_hd * H) : P.o_hmap;
-  P.o_rv = take(4 * kTE * kRvT);
-  P.o_pre = take(4 * kTE * kPre);
-  P.o_rw = take(c.use_vec_reward ? 16 : 4 * kTE * 32);
-  P.n_in = 0; P.n_out = 0; P.in_bytes = 0;
+  k.o_bar = take(16);
+  k.o_tab = take((int)sizeof(TileTables));
+  k.o_hmap = take(4 * (k.n_hd > 0 ? k.n_hd : 1) * (H > 0 ? H : 1));
+  k.o_hmul = k.hist_any_mul ? take(4 * k.n_hd * H) : k.o_hmap;
+  k.o_rv = take(4 * kTE * kRvT);
+  k.o_pre = take(4 * 2 * kTE * kPre);
+  P.n_in = 0; P.n_small = 0; P.n_out = 0; P.in_bytes = 0; P.small_bytes = 0;
   bool ok = true;
-  auto slab_in = [&](const void* g, int row_bytes, int64_t g_stride, int min_bytes = 0) {
-    int bytes = kTE * row_bytes;
-    const int o = take(bytes > min_bytes ? bytes : min_bytes);
-    TileDesc d = {reinterpret_cast<const char*>(g), row_bytes, (int)g_stride, o, 0};
+  auto slab_in = [&](const void* g, int row_bytes, int64_t g_stride) {
+    const int bytes = kTE * row_bytes;
+    const int o = take(bytes);
+    TileDesc d = {reinterpret_cast<const char*>(g), row_bytes, (int)g_stride, o, o};
     P.in[P.n_in++] = d;
     P.in_bytes += bytes;
     const bool contig = g_stride == row_bytes;
     if (((uintptr_t)g & 15) || (!contig && ((row_bytes & 15) || (g_stride & 15)))) ok = false;
     return o;
   };
+  auto slab_small = [&](const void* g, int row_bytes, int* o0, int* o1) {
+    const int bytes = kTE * row_bytes;
+    *o0 = take(bytes); *o1 = take(bytes);
+    TileDesc d = {reinterpret_cast<const char*>(g), row_bytes, row_bytes, *o0, *o1};
+    P.small[P.n_small++] = d;
+    P.small_bytes += bytes;
+    if ((uintptr_t)g & 15) ok = false;
+  };
   auto slab_out = [&](void* g, int row_bytes) {
     const int o = take(kTE * row_bytes);
-    TileDesc d = {reinterpret_cast<const char*>(g), row_bytes, row_bytes, o, 0};
+    TileDesc d = {reinterpret_cast<const char*>(g), row_bytes, row_bytes, o, o};
     P.out[P.n_out++] = d;
     if ((uintptr_t)g & 15) ok = false;
     return o;
   };
-  P.i_body = slab_in(io.body_state, Jb * 13 * 4, io.body_env_stride * 4);
-  P.i_cf = slab_in(io.contact_forces, Jb * 12, Jb * 12);
-  // the history slab doubles as scratch once it is scattered: dof partials + extended-body states
-  const int scratch1 = 4 * kTE * (kDofRaw * D + c.n_ext * 13);
-  if (H > 0) P.i_hist = slab_in(io.hist, H * 4, H * 4, scratch1);
-  else P.i_hist = take(scratch1);
-  P.o_dpart = P.i_hist; P.o_ext = P.i_hist + 4 * kTE * kDofRaw * D;
-  const int dof_in0 = off;
-  P.i_dof = slab_in(io.dof_state, D * 8, D * 8);
-  P.i_act = slab_in(io.actions, D * 4, D * 4);
-  P.i_tq = slab_in(io.torques, D * 4, D * 4);
-  P.i_lact = slab_in(io.last_actions, D * 4, D * 4);
-  P.i_ldv = slab_in(io.last_dof_vel, D * 4, D * 4);
-  P.i_kp = slab_in(io.kp_scale, D * 4, D * 4);
-  P.i_kd = slab_in(io.kd_scale, D * 4, D * 4);
-  const int scratch2 = 4 * kTE * kBodyRaw * J;   // body partials live in the dead dof-input slabs
-  if (off - dof_in0 < scratch2) take(scratch2 - (off - dof_in0));
-  P.o_bpart = dof_in0;
-  P.i_es = slab_in(io.episode_sums, c.n_episode_sums * 4, c.n_episode_sums * 4);
-  P.i_envf = slab_in(io.env_f32, PBHC_ENVF_STRIDE * 4, PBHC_ENVF_STRIDE * 4);
-  P.i_root = slab_in(io.root_state, 52, 52);
-  P.i_org = slab_in(io.env_origins, 12, 12);
-  P.i_ep = slab_in(io.episode_length_buf, 8, 8);
-  P.i_mid = slab_in(io.motion_ids, 8, 8);
-  P.i_com = slab_in(io.base_com_bias, 12, 12);
-  P.i_fric = slab_in(io.friction, 4, 4);
-  P.i_delay = slab_in(io.action_delay_idx, 8, 8);
-  P.i_mass = L > 0 ? slab_in(io.link_mass_scale, L * 4, L * 4) : P.i_fric;
-  P.o_rows = off;
+  k.i_body = slab_in(io.body_state, Jb * 13 * 4, io.body_env_stride * 4);
+  k.i_cf = slab_in(io.contact_forces, Jb * 12, Jb * 12);
+  // per-env scratch row (dof partials, then body partials): the env's history row once it is scattered, if that is large enough
+  const int scr_floats = kDofRaw * D > kBodyRaw * J ? kDofRaw * D : kBodyRaw * J;
+  if (H > 0) k.i_hist = slab_in(io.hist, H * 4, H * 4);
+  else k.i_hist = off;
+  if (H >= scr_floats) { k.o_scr = k.i_hist; k.scr_pitch = H * 4; }
+  else { k.scr_pitch = ((scr_floats * 4) + 15) & ~15; k.o_scr = take(kTE * k.scr_pitch); }
+  k.i_dof = slab_in(io.dof_state, D * 8, D * 8);
+  k.i_act = slab_in(io.actions, D * 4, D * 4);
+  k.i_tq = slab_in(io.torques, D * 4, D * 4);
+  k.i_lact = slab_in(io.last_actions, D * 4, D * 4);
+  k.i_ldv = slab_in(io.last_dof_vel, D * 4, D * 4);
+  k.i_kp = slab_in(io.kp_scale, D * 4, D * 4);
+  k.i_kd = slab_in(io.kd_scale, D * 4, D * 4);
+  k.i_es = slab_in(io.episode_sums, c.n_episode_sums * 4, c.n_episode_sums * 4);
+  k.i_org = slab_in(io.env_origins, 12, 12);
+  k.i_com = slab_in(io.base_com_bias, 12, 12);
+  k.i_fric = slab_in(io.friction, 4, 4);
+  k.i_delay = slab_in(io.action_delay_idx, 8, 8);
+  k.i_mass = L > 0 ? slab_in(io.link_mass_scale, L * 4, L * 4) : k.i_fric;
+  slab_small(io.root_state, 52, &k.i_root0, &k.i_root1);
+  slab_small(io.episode_length_buf, 8, &k.i_ep0, &k.i_ep1);
+  slab_small(io.env_f32, PBHC_ENVF_STRIDE * 4, &k.i_envf0, &k.i_envf1);
+  slab_small(io.motion_ids, 8, &k.i_mid0, &k.i_mid1);
+  k.o_rows = off;
+  int row_base[PBHC_MAX_OBS_GROUPS], gdim[PBHC_MAX_OBS_GROUPS];
   for (int g = 0; g < PBHC_MAX_OBS_GROUPS; ++g) {
-    P.row_base[g] = (off - P.o_rows) >> 2;
+    row_base[g] = (off - k.o_rows) >> 2;
+    gdim[g] = g < c.n_groups ? c.group_dim[g] : 0;
     if (g < c.n_groups) slab_out(io.obs[g], c.group_dim[g] * 4);
   }
-  P.q_rew = slab_out(io.rew_buf, c.use_vec_reward ? (c.n_rewards + 1) * 4 : 4);
-  P.q_es = slab_out(io.episode_sums, c.n_episode_sums * 4);
-  P.q_envf = slab_out(io.env_f32, PBHC_ENVF_STRIDE * 4);
-  P.q_ep = slab_out(io.episode_length_buf, 8);
-  P.q_reset = slab_out(io.reset_buf, 8);
-  P.q_lact = slab_out(io.last_actions, D * 4);
-  P.q_ldpos = slab_out(io.last_dof_pos, D * 4);
-  P.q_ldvel = slab_out(io.last_dof_vel, D * 4);
+  k.row_base0 = row_base[0]; k.row_base1 = row_base[1]; k.row_base2 = row_base[2]; k.row_base3 = row_base[3];
+  k.gdim0 = gdim[0]; k.gdim1 = gdim[1]; k.gdim2 = gdim[2]; k.gdim3 = gdim[3];
+  if (off - k.o_rows < 8 * 32 * kTE) take(8 * 32 * kTE - (off - k.o_rows));  // (the rows region also parks the scalars / the warps' sums)
+  k.q_rew = slab_out(io.rew_buf, c.use_vec_reward ? (c.n_rewards + 1) * 4 : 4);
+  k.q_es = slab_out(io.episode_sums, c.n_episode_sums * 4);
+  k.q_envf = slab_out(io.env_f32, PBHC_ENVF_STRIDE * 4);
+  k.q_ep = slab_out(io.episode_length_buf, 8);
+  k.q_reset = slab_out(io.reset_buf, 8);
+  k.q_lact = slab_out(io.last_actions, D * 4);
+  k.q_ldpos = slab_out(io.last_dof_pos, D * 4);
+  k.q_ldvel = slab_out(io.last_dof_vel, D * 4);
   P.bulk_ok = ok ? 1 : 0;
-  const size_t shmem = (size_t)off;
-  if (shmem > 220 * 1024) { set_error("pbhc_track_step: shared memory %zu B too large", shmem); return PBHC_E_RANGE; }
+  if (off > 220 * 1024) { set_error("pbhc_track_step: shared memory %d B too large", off); return PBHC_E_RANGE; }
+  return off;
+}
+
+struct KernelState { size_t configured = 0; int per_sm = 0; };
+
+// host side: plan + kernel choice + launch (called by pbhc_track_step for general == 0).  The kernel specialised for this env
+// config is used when it can be had (compiled by NVRTC once per config and cached on disk, PBHC_JIT=0 turns it off);
+// otherwise the generic kernel built with the library runs the same source with the constants read from the parameters.
+int track_tile_launch(const PbhcTrackCfg& c, const PbhcTableDesc& tab, const PbhcTrackIO& io, int64_t n, cudaStream_t stream, int* blocks_out) {
+  static thread_local TileParams P;
+  const int shmem = tile_plan(c, tab, io, n, P);
+  if (shmem < 0) return shmem;
   bool noise = false;
-  for (int k = 0; k < kSrcT; ++k) noise |= c.obs_noise[k] != 0.0f;
-  auto kern = noise ? track_tile_kernel<true> : track_tile_kernel<false>;
-  static thread_local size_t configured[2] = {0, 0};
-  static thread_local int per_sm_of[2] = {0, 0};
-  const int variant = noise ? 1 : 0;
-  if (shmem > configured[variant] || per_sm_of[variant] == 0) {
-    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shmem) != cudaSuccess) return check_launch("pbhc_track_step(attr)");
+  for (int s = 0; s < kSrcT; ++s) noise |= c.obs_noise[s] != 0.0f;
+  const void* kern = noise ? (const void*)track_tile_kernel<true> : (const void*)track_tile_kernel<false>;
+  static thread_local KernelState generic[2];
+  static thread_local std::unordered_map<const void*, KernelState> jitted;
+  KernelState* st = &generic[noise ? 1 : 0];
+  int which = 1;
+  const void* jk = nullptr;
+  if (jit_track_tile(P.k, noise, &jk) == 0 && jk) { kern = jk; st = &jitted[jk]; which = 2; }
+  if ((size_t)shmem > st->configured || st->per_sm == 0) {
+    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, shmem) != cudaSuccess) return check_launch("pbhc_track_step(attr)");
     (void)cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
-    configured[variant] = shmem;
+    st->configured = (size_t)shmem;
     int per_sm = 0;
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kNT, shmem);
-    per_sm_of[variant] = per_sm < 1 ? 1 : (per_sm > 8 ? 8 : per_sm);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kNT, (size_t)shmem);
+    st->per_sm = per_sm < 1 ? 1 : (per_sm > 8 ? 8 : per_sm);
   }
   int blocks = P.n_tiles;
-  const int cap = 148 * per_sm_of[variant];
+  const int cap = 148 * st->per_sm;
   if (blocks > cap) blocks = cap;
-  g_track_info[0] = 1; g_track_info[1] = blocks; g_track_info[2] = (int)shmem; g_track_info[3] = per_sm_of[variant];
-  kern<<<(unsigned)blocks, kNT, shmem, stream>>>(P);
+  g_track_info[0] = which; g_track_info[1] = blocks; g_track_info[2] = shmem; g_track_info[3] = st->per_sm;
+  void* args[] = {(void*)&P};
+  if (cudaLaunchKernel(kern, dim3((unsigned)blocks), dim3(kNT), args, (size_t)shmem, stream) != cudaSuccess) return check_launch("pbhc_track_step(tile)");
   *blocks_out = blocks;
   return PBHC_OK;
 }
 
+// the specialised kernel of a config without a launch (build-time warm-up of the on-disk cache; needs no GPU)
+int track_tile_prepare(const PbhcTrackCfg& c, const PbhcTableDesc& tab, const PbhcTrackIO& io) {
+  static thread_local TileParams P;
+  const int shmem = tile_plan(c, tab, io, 8, P);
+  if (shmem < 0) return shmem;
+  bool noise = false;
+  for (int s = 0; s < kSrcT; ++s) noise |= c.obs_noise[s] != 0.0f;
+  return jit_track_tile(P.k, noise, nullptr) == 0 ? PBHC_OK : PBHC_E_CUDA;
+}
+
 }  // namespace pbhc
+#endif  // __CUDACC_RTC__

@@ -242,6 +242,29 @@ class TrackingStep:
                 c.future_steps[i] = v
         self._cfg = c
 
+    @classmethod
+    def specialize(cls, spec, dims, rec_stride, seed=0):
+        """Compiles the kernel specialised for `spec` into the on-disk cache (pbhc_track_specialize) without a GPU:
+        dims = (J, Jb, D, contact_size) of the motion library.  Returns True when the specialised kernel is cached."""
+        self = object.__new__(cls)
+        self.spec, self.device = spec, None
+        self.n_sums = len(spec.reward_names) + (1 if spec.termination_scale is not None else 0)
+        self.hist_row = sum(spec.hist_len[k] * spec.hist_dim[k] for k in spec.hist_keys)
+        self._build_cfg(seed)
+        J, Jb, D, Cm = dims
+        desc = _lib.TableDesc(None, None, None, None, None, 0, 1, J, Jb, D, Cm, rec_stride)
+        io = _lib.TrackIO()
+        io.default_dof_stride = spec.D
+        io.ref_body_pos_extend, io.ref_body_rot_extend = 16, 16  # (only their NULL-ness is read)
+        return _lib.lib().pbhc_track_specialize(C.byref(self._cfg), C.byref(desc), C.byref(io)) == 0
+
+    def launch_info(self):
+        """what the last pbhc_track_step launched: dict(kernel, blocks, smem_bytes, blocks_per_sm)."""
+        out = (C.c_int32 * 4)()
+        self._L.pbhc_track_launch_info(C.byref(out))
+        return dict(kernel={0: "warp-per-env", 1: "tile (generic)", 2: "tile (specialised for the config)"}.get(out[0], "?"),
+                    blocks=out[1], smem_bytes=out[2], blocks_per_sm=out[3])
+
     # ---- one env step -----------------------------------------------------------------------------------
     def bind(self, sim, actions, torques, env_origins, motion_ids, inject=None):
         """Records the device pointers of this step's borrowed tensors in the PbhcTrackIO block (no launch).
