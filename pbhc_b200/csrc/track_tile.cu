@@ -35,12 +35,11 @@ namespace pbhc {
 constexpr int kTE = 8;             // envs per tile = warps per block
 constexpr int kNT = kTE * 32;
 constexpr int kMaxIn = 20, kMaxSmall = 4, kMaxOut = 16;
-constexpr int kBodyRaw = 5;        // per-body values the body sums are made of
+constexpr int kBodyRaw = 10;       // per-body values of the body sums (already masked by the body's set memberships)
 constexpr int kDofRaw = 9;         // per-dof values the dof sums are made of
 constexpr int kRvT = 60;           // per-env scalar table: [0, 57) = enum Rv
 constexpr int kSrcT = S_BASE_POS_Z + 1;  // observation sources of LeggedRobotMotionTracking
-enum BodyRaw { BR_MPOS, BR_NRM, BR_ROT, BR_VEL, BR_ANG };
-enum DofRaw { DR_DJA, DR_DJV2, DR_TQ2, DR_DACT2, DR_DV2, DR_ACC2, DR_LPOS, DR_LVEL, DR_LTQ };
+enum DofRaw { DR_DJA2, DR_DJV2, DR_TQ2, DR_DACT2, DR_DV2, DR_ACC2, DR_LPOS, DR_LVEL, DR_LTQ };
 constexpr int kBodySums = 10;
 constexpr int kPieces = 5;         // pieces of the per-env scalar pre-computation
 
@@ -52,7 +51,7 @@ struct TileDesc { const char* g; int row_bytes, g_stride, soff, soff2; };  // on
 #define PBHC_HOTK_INT(X) \
   X(J) X(Jb) X(D) X(L) X(H) X(n_ext) X(n_feet) X(n_groups) X(R) X(n_sums) X(n_hd) X(hist_any_mul) X(has_air_time) X(n_feat) \
   X(contact_size) X(rec_stride) X(use_vec_reward) X(only_positive) X(has_termination) X(cur_torque_enable) X(term_gravity) \
-  X(term_motion_far) X(term_motion_end) X(dif_joint_used) X(ref_vel_used) X(ref_pos_out) X(ref_rot_out) X(default_dof_stride) \
+  X(term_motion_far) X(term_motion_end) X(dif_joint_used) X(ref_vel_used) X(ext_identity) X(ref_pos_out) X(ref_rot_out) X(default_dof_stride) \
   X(e_pos) X(e_vel) X(e_ang) X(e_dp) X(e_dv) X(e_c) \
   X(o_bar) X(o_tab) X(o_hmap) X(o_hmul) X(o_rv) X(o_pre) X(o_rows) X(o_scr) X(scr_pitch) \
   X(i_body) X(i_cf) X(i_hist) X(i_dof) X(i_act) X(i_tq) X(i_lact) X(i_ldv) X(i_kp) X(i_kd) X(i_es) X(i_org) X(i_com) X(i_fric) \
@@ -73,11 +72,16 @@ struct HotK {
 #undef X
 };
 
+// where each observation source goes - part of the specialised kernel's constants too (the emits of a known source fold
+// into stores at immediate offsets); the generic kernel reads the same from a shared-memory table
+struct SpecExtra { int n[20], base[20][4], stride[20][4], pushed[20], noisy[20]; float scale[20]; };
+
 struct TileParams {
   PbhcTrackCfg c;
   PbhcTableDesc tab;
   PbhcTrackIO io;
   HotK k;
+  SpecExtra x;
   int n, n_tiles, n_in, n_small, n_out, bulk_ok, in_bytes, small_bytes;
   TileDesc in[kMaxIn], small[kMaxSmall], out[kMaxOut];
   int hist_base[PBHC_MAX_HIST_KEYS];
@@ -151,8 +155,8 @@ struct TileTables {
   float lim_lo[PBHC_MAX_DOF], lim_hi[PBHC_MAX_DOF], lim_vel[PBHC_MAX_DOF], lim_tq[PBHC_MAX_DOF];
   float r_scale[PBHC_MAX_REWARDS], r_pen[PBHC_MAX_REWARDS], r_sigma[PBHC_MAX_REWARDS];
   signed char r_kind[PBHC_MAX_REWARDS], r_arg[PBHC_MAX_REWARDS];
-  uint64_t bs_mask[kBodySums];
-  signed char bs_raw[kBodySums + 2], bs_slot[kBodySums + 2];
+  signed char bs_slot[kBodySums + 2];
+  unsigned char member[64];
   float bs_div[kBodySums];
   SrcDst sd[kSrcT];
   float obs_scale[kSrcT], obs_noise[kSrcT];
@@ -214,6 +218,41 @@ __device__ __forceinline__ void emit3(const TileTables& T, const Rows& R, int k,
     if (np.x > 3) { float* o = r + d.base3 + R.e * d.stride3; o[0] = cx; o[1] = cy; o[2] = cz; }
   }
   if (np.y >= 0) { float* h = R.ghist + np.y + el; h[0] = sx; h[1] = sy; h[2] = sz; }
+}
+
+// the same for a source known at compile time: in the specialised kernel the destinations are immediates
+template <bool kNoise, int K>
+__device__ __forceinline__ void emit1k(const TileTables& T, const Rows& R, int el, float raw, float clip, const NoiseKeyT& nk) {
+#ifdef PBHC_SPEC
+  if (kNoise && spec::sd_noisy[K]) { emit_noisy_t(T, R, K, el, raw, clip, nk); return; }
+  const float sv = spec::sd_scale[K] == 1.0f ? raw : raw * spec::sd_scale[K], cv = clampf(sv, clip);
+  float* r = R.rows + el;
+  if (spec::sd_n[K] > 0) r[spec::sd_base[K][0] + R.e * spec::sd_stride[K][0]] = cv;
+  if (spec::sd_n[K] > 1) r[spec::sd_base[K][1] + R.e * spec::sd_stride[K][1]] = cv;
+  if (spec::sd_n[K] > 2) r[spec::sd_base[K][2] + R.e * spec::sd_stride[K][2]] = cv;
+  if (spec::sd_n[K] > 3) r[spec::sd_base[K][3] + R.e * spec::sd_stride[K][3]] = cv;
+  if (spec::sd_pushed[K]) R.ghist[T.sd[K].push + el] = sv;
+#else
+  emit1<kNoise>(T, R, K, el, raw, clip, nk);
+#endif
+}
+template <bool kNoise, int K>
+__device__ __forceinline__ void emit3k(const TileTables& T, const Rows& R, int el, float x, float y, float z, float clip, const NoiseKeyT& nk) {
+#ifdef PBHC_SPEC
+  if (kNoise && spec::sd_noisy[K]) { emit3<kNoise>(T, R, K, el, x, y, z, clip, nk); return; }
+  if (spec::sd_n[K] == 0 && !spec::sd_pushed[K]) return;
+  const float sc = spec::sd_scale[K];
+  const float sx = x * sc, sy = y * sc, sz = z * sc;
+  const float cx = clampf(sx, clip), cy = clampf(sy, clip), cz = clampf(sz, clip);
+  float* r = R.rows + el;
+  if (spec::sd_n[K] > 0) { float* o = r + spec::sd_base[K][0] + R.e * spec::sd_stride[K][0]; o[0] = cx; o[1] = cy; o[2] = cz; }
+  if (spec::sd_n[K] > 1) { float* o = r + spec::sd_base[K][1] + R.e * spec::sd_stride[K][1]; o[0] = cx; o[1] = cy; o[2] = cz; }
+  if (spec::sd_n[K] > 2) { float* o = r + spec::sd_base[K][2] + R.e * spec::sd_stride[K][2]; o[0] = cx; o[1] = cy; o[2] = cz; }
+  if (spec::sd_n[K] > 3) { float* o = r + spec::sd_base[K][3] + R.e * spec::sd_stride[K][3]; o[0] = cx; o[1] = cy; o[2] = cz; }
+  if (spec::sd_pushed[K]) { float* h = R.ghist + T.sd[K].push + el; h[0] = sx; h[1] = sy; h[2] = sz; }
+#else
+  emit3<kNoise>(T, R, K, el, x, y, z, clip, nk);
+#endif
 }
 
 // ---- TMA / mbarrier ---------------------------------------------------------------------------------------------------
@@ -296,24 +335,29 @@ __device__ void build_tile_tables(const TileParams& P, TileTables& T, int* hmap,
     T.r_scale[tid] = tid < c.n_rewards ? c.reward_scale[tid] : 0.0f;
     T.r_pen[tid] = (tid < c.n_rewards && c.reward_is_penalty[tid]) ? (float)scal[PBHC_S_PENALTY] : 1.0f;
   }
-  if (tid < kBodySums) {
-    uint64_t feet_mask = 0;
-    for (int f = 0; f < c.n_feet; ++f) feet_mask |= 1ull << c.feet_ids[f];
-    const uint64_t all = c.J >= 64 ? ~0ull : ((1ull << c.J) - 1ull);
-    uint64_t m = all; int raw = BR_MPOS, slot = 0; float div = 1.0f;
+  if (tid < kBodySums) {  // body sum k: divisor and rv slot (motion_tracking.py:646-676, 397-418)
+    int slot = 0; float div = 1.0f;
     switch (tid) {
-      case 0: m = c.upper_mask; raw = BR_MPOS; div = (float)c.n_upper; slot = V_SIGMA_ERR + G_UPPER; break;
-      case 1: m = c.lower_mask; raw = BR_MPOS; div = (float)c.n_lower; slot = V_SIGMA_ERR + G_LOWER; break;
-      case 2: m = c.vr3_mask; raw = BR_MPOS; div = (float)c.n_vr3; slot = V_SIGMA_ERR + G_VR3; break;
-      case 3: m = feet_mask; raw = BR_MPOS; div = (float)c.n_feet; slot = V_SIGMA_ERR + G_FEET; break;
-      case 4: raw = BR_ROT; div = (float)c.J; slot = V_SIGMA_ERR + G_ROT; break;
-      case 5: raw = BR_VEL; div = (float)c.J; slot = V_SIGMA_ERR + G_VEL; break;
-      case 6: raw = BR_ANG; div = (float)c.J; slot = V_SIGMA_ERR + G_ANG_VEL; break;
-      case 7: m = c.upper_mask; raw = BR_NRM; slot = V_UP_N; break;
-      case 8: m = c.lower_mask; raw = BR_NRM; slot = V_LO_N; break;
-      default: m = c.vr3_mask; raw = BR_NRM; slot = V_VR_N; break;
+      case 0: div = (float)c.n_upper; slot = V_SIGMA_ERR + G_UPPER; break;
+      case 1: div = (float)c.n_lower; slot = V_SIGMA_ERR + G_LOWER; break;
+      case 2: div = (float)c.n_vr3; slot = V_SIGMA_ERR + G_VR3; break;
+      case 3: div = (float)c.n_feet; slot = V_SIGMA_ERR + G_FEET; break;
+      case 4: div = (float)c.J; slot = V_SIGMA_ERR + G_ROT; break;
+      case 5: div = (float)c.J; slot = V_SIGMA_ERR + G_VEL; break;
+      case 6: div = (float)c.J; slot = V_SIGMA_ERR + G_ANG_VEL; break;
+      case 7: slot = V_UP_N; break;
+      case 8: slot = V_LO_N; break;
+      default: slot = V_VR_N; break;
     }
-    T.bs_mask[tid] = m & all; T.bs_raw[tid] = (signed char)raw; T.bs_slot[tid] = (signed char)slot; T.bs_div[tid] = div;
+    T.bs_slot[tid] = (signed char)slot; T.bs_div[tid] = div;
+  }
+  if (tid < 64) {  // set memberships of body tid: bit 0 upper, 1 lower, 2 vr3, 3 feet
+    int mb = 0;
+    if ((c.upper_mask >> tid) & 1ull) mb |= 1;
+    if ((c.lower_mask >> tid) & 1ull) mb |= 2;
+    if ((c.vr3_mask >> tid) & 1ull) mb |= 4;
+    for (int f = 0; f < c.n_feet; ++f) if (c.feet_ids[f] == tid) mb |= 8;
+    T.member[tid] = (unsigned char)mb;
   }
   if (tid < kSrcT) {
     int base[4] = {0, 0, 0, 0}, stride[4] = {0, 0, 0, 0};
@@ -402,7 +446,8 @@ __device__ __forceinline__ void track_tile_body(const TileParams& P) {
   double acc_reg = 0.0;  // slot = lane (< kAccLo), this warp's envs
 
   const int n_tiles = P.n_tiles, stride = (int)gridDim.x;
-  auto is_bulk = [&](int t) { return P.bulk_ok && t < n_tiles && (t + 1) * kTE <= n_envs; };
+  const int n_full = P.bulk_ok ? n_envs / kTE : 0;  // tiles that move by TMA
+  auto is_bulk = [&](int t) { return t < n_full; };
   // warp 0: requests the big slabs of tile `tb` and the small (double-buffered) slabs of tile `ts` into buffer `buf`
   auto issue_loads = [&](int tb, bool big, int ts, bool small, int buf) {
     if (lane == 0) mbar_expect_tx(bar, (big ? P.in_bytes : 0) + (small ? P.small_bytes : 0));
@@ -458,7 +503,7 @@ __device__ __forceinline__ void track_tile_body(const TileParams& P) {
   bool have_small_next = false, pre_ready = false;
   if (is_bulk(tile)) {  // prologue: this block's first tile (big + small) and the small inputs of its second tile
     have_small_next = is_bulk(tile + stride);
-    if (warp == 0) {
+    if (warp == kTE - 1) {
       if (lane == 0) mbar_expect_tx(bar, P.in_bytes + P.small_bytes * (have_small_next ? 2 : 1));
       __syncwarp();
       for (int i = lane; i < P.n_in; i += 32) {
@@ -480,8 +525,8 @@ __device__ __forceinline__ void track_tile_body(const TileParams& P) {
     const int cnt = min(kTE, n_envs - tile0);
     const int sb = it & 1;
     const bool bulk = is_bulk(tile);
-    if (warp == 0) bulk_wait_read();  // the previous tile's bulk stores have left the output slabs
-    if (bulk) { if (tid == 0) mbar_wait_t(bar, phase); phase ^= 1u; }
+    if (warp == kTE - 1) bulk_wait_read();  // the previous tile's bulk stores have left the output slabs
+    if (bulk) { if (tid == kNT - 32) mbar_wait_t(bar, phase); phase ^= 1u; }
     else {  // ragged last tile / unaligned tensors: cooperative word copies
       for (int i = 0; i < P.n_in + P.n_small; ++i) {
         const TileDesc d = i < P.n_in ? P.in[i] : P.small[i - P.n_in];
@@ -554,6 +599,7 @@ __device__ __forceinline__ void track_tile_body(const TileParams& P) {
       __syncwarp();  // (the scratch row may alias this env's history row)
 
       // ---- b. dofs (lane = dof) -------------------------------------------------------------------------------------------
+      float adja = 0.0f;  // |dif_joint_angles| of this lane's dof
       if (lane < D) {
         const int d = lane, x = e * D + d;
         const float2 ds = reinterpret_cast<const float2*>(smem + KC(i_dof))[x];
@@ -562,26 +608,31 @@ __device__ __forceinline__ void track_tile_body(const TileParams& P) {
         const float lact = reinterpret_cast<const float*>(smem + KC(i_lact))[x], ldv = reinterpret_cast<const float*>(smem + KC(i_ldv))[x];
         const float ddef = io.default_dof_pos[n * KC(default_dof_stride) + d];
         const float dja = (omb * __ldg(r0 + e_dp + d) + b * __ldg(r1 + e_dp + d)) - dpos;   // motion_tracking.py:661-665
+        adja = fabsf(dja);
         const float djv = (omb * __ldg(r0 + e_dv + d) + b * __ldg(r1 + e_dv + d)) - dvel;
         const float dact = lact - act, dacc = (ldv - dvel) / dt;
         const float lim_t = T.lim_tq[d];
         float* dp_ = scr + d;
-        dp_[DR_DJA * D] = dja; dp_[DR_DJV2 * D] = djv * djv; dp_[DR_TQ2 * D] = tq * tq; dp_[DR_DACT2 * D] = dact * dact;
+        dp_[DR_DJA2 * D] = dja * dja; dp_[DR_DJV2 * D] = djv * djv; dp_[DR_TQ2 * D] = tq * tq; dp_[DR_DACT2 * D] = dact * dact;
         dp_[DR_DV2 * D] = dvel * dvel; dp_[DR_ACC2 * D] = dacc * dacc;
         dp_[DR_LPOS * D] = -fminf(dpos - T.lim_lo[d], 0.0f) + fmaxf(dpos - T.lim_hi[d], 0.0f);  // legged_robot_base.py:974-1002
         dp_[DR_LVEL * D] = fminf(fmaxf(fabsf(dvel) - T.lim_vel[d], 0.0f), 1.0f);
         dp_[DR_LTQ * D] = KC(cur_torque_enable) ? fminf(fmaxf(fabsf(tq) - lim_t, 0.0f), 1.0f) : fmaxf(fabsf(tq) - lim_t, 0.0f);
-        emit1<kNoise>(T, Rw, S_DOF_POS, d, dpos - ddef, clipv, nk);
-        emit1<kNoise>(T, Rw, S_DOF_VEL, d, dvel, clipv, nk);
-        emit1<kNoise>(T, Rw, S_ACTIONS, d, act, clipv, nk);
-        emit1<kNoise>(T, Rw, S_DR_KP, d, reinterpret_cast<const float*>(smem + KC(i_kp))[x], clipv, nk);
-        emit1<kNoise>(T, Rw, S_DR_KD, d, reinterpret_cast<const float*>(smem + KC(i_kd))[x], clipv, nk);
+        emit1k<kNoise, S_DOF_POS>(T, Rw, d, dpos - ddef, clipv, nk);
+        emit1k<kNoise, S_DOF_VEL>(T, Rw, d, dvel, clipv, nk);
+        emit1k<kNoise, S_ACTIONS>(T, Rw, d, act, clipv, nk);
+        emit1k<kNoise, S_DR_KP>(T, Rw, d, reinterpret_cast<const float*>(smem + KC(i_kp))[x], clipv, nk);
+        emit1k<kNoise, S_DR_KD>(T, Rw, d, reinterpret_cast<const float*>(smem + KC(i_kd))[x], clipv, nk);
         if (KC(dif_joint_used)) {
-          emit1<kNoise>(T, Rw, S_DIF_JOINT, d, dja, clipv, nk);
-          emit1<kNoise>(T, Rw, S_DIF_JOINT_VEL, d, djv, clipv, nk);
+          emit1k<kNoise, S_DIF_JOINT>(T, Rw, d, dja, clipv, nk);
+          emit1k<kNoise, S_DIF_JOINT_VEL>(T, Rw, d, djv, clipv, nk);
         }
         // _post_compute_observations_callback, legged_robot_base.py:398-405
         reinterpret_cast<float*>(smem + KC(q_lact))[x] = act; reinterpret_cast<float*>(smem + KC(q_ldpos))[x] = dpos; reinterpret_cast<float*>(smem + KC(q_ldvel))[x] = dvel;
+      }
+      {
+        const float mx = warp_max(adja);
+        if (lane == 0) rve[V_SIGMA_ERR + G_MAX_JOINT] = mx;
       }
       __syncwarp();
       {  // dof sums: three lanes per value (dofs part, part + 3, ...), combined in lane order - a fixed summation order
@@ -589,18 +640,18 @@ __device__ __forceinline__ void track_tile_body(const TileParams& P) {
         float v = 0.0f;
         if (k < kDofRaw) {
           const float* src = scr + k * D;
-          if (k == DR_DJA) for (int d = part; d < D; d += 3) v += src[d] * src[d];
-          else for (int d = part; d < D; d += 3) v += src[d];
-        } else if (k == kDofRaw) {
-          for (int d = part; d < D; d += 3) v = fmaxf(v, fabsf(scr[DR_DJA * D + d]));
+          for (int d = part; d < D; d += 3) v += src[d];
         }
         const float v1 = __shfl_down_sync(0xffffffffu, v, 1), v2 = __shfl_down_sync(0xffffffffu, v, 2);
-        const float tot = k == kDofRaw ? fmaxf(fmaxf(v, v1), v2) : (v + v1) + v2;
-        if (part == 0 && k <= kDofRaw) {
-          if (k == DR_DJA) { rve[V_SIGMA_ERR + G_JOINT_POS] = tot / (float)D; rve[V_JOINT_N] = sqrtf(tot); }
-          else if (k == DR_DJV2) rve[V_SIGMA_ERR + G_JOINT_VEL] = tot / (float)D;
-          else if (k == kDofRaw) rve[V_SIGMA_ERR + G_MAX_JOINT] = tot;
-          else rve[k == DR_TQ2 ? V_TQ2 : k == DR_DACT2 ? V_DACT2 : k == DR_DV2 ? V_DV2 : k == DR_ACC2 ? V_ACC2 : k == DR_LPOS ? V_LIM_POS : k == DR_LVEL ? V_LIM_VEL : V_LIM_TQ] = tot;
+        const float tot = (v + v1) + v2;
+        if (part == 0 && k < kDofRaw) {
+          // slots of DR_DJA2 .. DR_LTQ, one byte each
+          const unsigned long long slots = (unsigned long long)(V_SIGMA_ERR + G_JOINT_POS) | ((unsigned long long)(V_SIGMA_ERR + G_JOINT_VEL) << 8) |
+              ((unsigned long long)V_TQ2 << 16) | ((unsigned long long)V_DACT2 << 24) | ((unsigned long long)V_DV2 << 32) | ((unsigned long long)V_ACC2 << 40) |
+              ((unsigned long long)V_LIM_POS << 48) | ((unsigned long long)V_LIM_VEL << 56);
+          const int slot = k == DR_LTQ ? (int)V_LIM_TQ : (int)((slots >> (8 * k)) & 0xffull);
+          rve[slot] = k <= DR_DJV2 ? tot / (float)D : tot;
+          if (k == DR_DJA2) rve[V_JOINT_N] = sqrtf(tot);
         }
       }
       __syncwarp();
@@ -622,9 +673,10 @@ __device__ __forceinline__ void track_tile_body(const TileParams& P) {
             const Q4 qp = {bs[3], bs[4], bs[5], bs[6]};
             const V3 off = {c.ext_pos[x][0], c.ext_pos[x][1], c.ext_pos[x][2]};
             const Q4 qe = {c.ext_rot_xyzw[x][0], c.ext_rot_xyzw[x][1], c.ext_rot_xyzw[x][2], c.ext_rot_xyzw[x][3]};
-            const V3 r = quat_rotate_x(qe, quat_rotate_x(qp, off, false), false);
+            V3 r = quat_rotate_x(qp, off, false);
+            if (!KC(ext_identity)) r = quat_rotate_x(qe, r, false);  // (an identity rotation returns its argument bit for bit)
             p = {xa(r.x, bs[0]), xa(r.y, bs[1]), xa(r.z, bs[2])};
-            q = quat_mul(qp, qe);
+            q = KC(ext_identity) ? qp : quat_mul(qp, qe);           // (quat_mul by the identity: equal within 1 ulp, feeds tolerance-checked values only)
             w = {bs[10], bs[11], bs[12]};
             v = {bs[7] + (w.y * off.z - w.z * off.y), bs[8] + (w.z * off.x - w.x * off.z), bs[9] + (w.x * off.y - w.y * off.x)};
           }
@@ -648,12 +700,16 @@ __device__ __forceinline__ void track_tile_body(const TileParams& P) {
           const V3 dv = {rvv[0] - v.x, rvv[1] - v.y, rvv[2] - v.z};
           const V3 dw = {rw[0] - w.x, rw[1] - w.y, rw[2] - w.z};
           const float nrm = norm3(dp.x, dp.y, dp.z);
-          float* bp = scr + j;
-          bp[BR_MPOS * J] = div3((dp.x * dp.x + dp.y * dp.y) + dp.z * dp.z);
-          bp[BR_NRM * J] = nrm;
-          bp[BR_ROT * J] = (((dq0 * dq0 + dq1 * dq1) + dq2 * dq2) + dq3 * dq3) * 0.25f;
-          bp[BR_VEL * J] = div3((dv.x * dv.x + dv.y * dv.y) + dv.z * dv.z);
-          bp[BR_ANG * J] = div3((dw.x * dw.x + dw.y * dw.y) + dw.z * dw.z);
+          {
+            const float m_pos = div3((dp.x * dp.x + dp.y * dp.y) + dp.z * dp.z);
+            const int mb = T.member[j];
+            float* bp = scr + j;
+            bp[0 * J] = (mb & 1) ? m_pos : 0.0f; bp[1 * J] = (mb & 2) ? m_pos : 0.0f; bp[2 * J] = (mb & 4) ? m_pos : 0.0f; bp[3 * J] = (mb & 8) ? m_pos : 0.0f;
+            bp[4 * J] = (((dq0 * dq0 + dq1 * dq1) + dq2 * dq2) + dq3 * dq3) * 0.25f;
+            bp[5 * J] = div3((dv.x * dv.x + dv.y * dv.y) + dv.z * dv.z);
+            bp[6 * J] = div3((dw.x * dw.x + dw.y * dw.y) + dw.z * dw.z);
+            bp[7 * J] = (mb & 1) ? nrm : 0.0f; bp[8 * J] = (mb & 2) ? nrm : 0.0f; bp[9 * J] = (mb & 4) ? nrm : 0.0f;
+          }
           if (nrm > far_thr) far = 1;
           if (j < Jb && (((unsigned long long)KC(penalised_mask) >> j) & 1ull)) {
             const float* fc = s_cf + 3 * j;
@@ -661,14 +717,14 @@ __device__ __forceinline__ void track_tile_body(const TileParams& P) {
           }
           {
             const V3 dl = quat_rotate_z(hz, hw, dp);  // motion_tracking.py:694-697
-            emit3<kNoise>(T, Rw, S_DIF_LOCAL, 3 * j, dl.x, dl.y, dl.z, clipv, nk);
+            emit3k<kNoise, S_DIF_LOCAL>(T, Rw, 3 * j, dl.x, dl.y, dl.z, clipv, nk);
             const V3 lr = quat_rotate_z(hz, hw, {rpz[0] - pe[P_RPX], rpz[1] - pe[P_RPY], rpz[2] - pe[P_RPZ]});  // :705-707
-            emit3<kNoise>(T, Rw, S_LOCAL_REF, 3 * j, lr.x, lr.y, lr.z, clipv, nk);
+            emit3k<kNoise, S_LOCAL_REF>(T, Rw, 3 * j, lr.x, lr.y, lr.z, clipv, nk);
           }
           if (KC(ref_vel_used)) {
             const V3 lv = quat_rotate_z(hz, hw, {rvv[0], rvv[1], rvv[2]});
-            emit3<kNoise>(T, Rw, S_LOCAL_REF_VEL, 3 * j, lv.x, lv.y, lv.z, clipv, nk);
-            emit3<kNoise>(T, Rw, S_GLOBAL_REF_VEL, 3 * j, rvv[0], rvv[1], rvv[2], clipv, nk);
+            emit3k<kNoise, S_LOCAL_REF_VEL>(T, Rw, 3 * j, lv.x, lv.y, lv.z, clipv, nk);
+            emit3k<kNoise, S_GLOBAL_REF_VEL>(T, Rw, 3 * j, rvv[0], rvv[1], rvv[2], clipv, nk);
           }
         }
         n_collide += __popc(__ballot_sync(0xffffffffu, collide));
@@ -679,13 +735,8 @@ __device__ __forceinline__ void track_tile_body(const TileParams& P) {
         const int k = lane / 3, part = lane - 3 * k;
         float v = 0.0f;
         if (k < kBodySums) {
-          const float* src = scr + T.bs_raw[k] * J;
-          const uint64_t m = T.bs_mask[k] >> part;
-          const uint32_t mlo = (uint32_t)m, mhi = (uint32_t)(m >> 32);
-          for (int j = part, s = 0; j < J; j += 3, s += 3) {
-            const uint32_t bit = s < 32 ? (mlo >> s) : (mhi >> (s - 32));
-            if (bit & 1u) v += src[j];
-          }
+          const float* src = scr + k * J;
+          for (int j = part; j < J; j += 3) v += src[j];
         }
         const float v1 = __shfl_down_sync(0xffffffffu, v, 1), v2 = __shfl_down_sync(0xffffffffu, v, 2);
         if (part == 0 && k < kBodySums) rve[T.bs_slot[k]] = ((v + v1) + v2) / T.bs_div[k];
@@ -817,71 +868,95 @@ __device__ __forceinline__ void track_tile_body(const TileParams& P) {
         }
         __syncwarp();
         ep = 0;
+        // Random draws (when the caller does not inject the reference's): Philox4x32-10 keyed by (seed, global env id, step);
+        // every call yields four words, so one call serves the four DR scales of a dof, one a Box-Muller pair, one the
+        // env-level scalars - a reset costs six calls per lane instead of sixteen (the other lanes of the tile wait for it).
+        auto gauss2 = [](uint32_t a, uint32_t b_, float& n0, float& n1) {
+          const float r = sqrtf(-2.0f * __logf(fmaxf(u01(a), 1.0f / 16777216.0f)));
+          float sn, cs;
+          __sincosf(6.283185307179586f * u01(b_), &sn, &cs);
+          n0 = r * cs; n1 = r * sn;
+        };
+        const uint4 r_env = rng.draw(0);   // x: start time, y: control delay, z: root-rotation angle
         float kp2 = 1.f, kd2 = 1.f, dpos2 = 0.f, dvel2 = 0.f;
         if (ld) {  // _episodic_domain_randomization
+          const uint4 r_dr = rng.draw(16 + lane);
           kp2 = io.kp_scale[n * D + lane]; kd2 = io.kd_scale[n * D + lane];
           if (c.randomize_pd_gain) {
-            kp2 = io.inject_kp ? io.inject_kp[n * D + lane] : xa(xm(xs(c.kp_hi, c.kp_lo), rng.uniform(16 + lane)), c.kp_lo);
-            kd2 = io.inject_kd ? io.inject_kd[n * D + lane] : xa(xm(xs(c.kd_hi, c.kd_lo), rng.uniform(48 + lane)), c.kd_lo);
+            kp2 = io.inject_kp ? io.inject_kp[n * D + lane] : xa(xm(xs(c.kp_hi, c.kp_lo), u01(r_dr.x)), c.kp_lo);
+            kd2 = io.inject_kd ? io.inject_kd[n * D + lane] : xa(xm(xs(c.kd_hi, c.kd_lo), u01(r_dr.y)), c.kd_lo);
             io.kp_scale[n * D + lane] = kp2; io.kd_scale[n * D + lane] = kd2;
           }
           if (c.randomize_rfi_lim)
-            io.rfi_lim_scale[n * D + lane] = io.inject_rfi ? io.inject_rfi[n * D + lane] : xa(xm(xs(c.rfi_hi, c.rfi_lo), rng.uniform(80 + lane)), c.rfi_lo);
+            io.rfi_lim_scale[n * D + lane] = io.inject_rfi ? io.inject_rfi[n * D + lane] : xa(xm(xs(c.rfi_hi, c.rfi_lo), u01(r_dr.z)), c.rfi_lo);
           if (c.use_rao)
-            io.rao_scale[n * D + lane] = io.inject_rao ? io.inject_rao[n * D + lane] : xa(xm(xs(c.rao_lim, -c.rao_lim), rng.uniform(112 + lane)), -c.rao_lim);
+            io.rao_scale[n * D + lane] = io.inject_rao ? io.inject_rao[n * D + lane] : xa(xm(xs(c.rao_lim, -c.rao_lim), u01(r_dr.w)), -c.rao_lim);
         }
         if (c.randomize_ctrl_delay) {
-          delay = io.inject_delay ? io.inject_delay[n] : c.delay_lo + (int64_t)(rng.draw(1).x % (uint32_t)(c.delay_hi - c.delay_lo + 1));
+          delay = io.inject_delay ? io.inject_delay[n] : c.delay_lo + (int64_t)(r_env.y % (uint32_t)(c.delay_hi - c.delay_lo + 1));
           if (lane == 0) io.action_delay_idx[n] = delay;
         }
         etr = __fdiv_rn(xa(xm((float)last_ep, dt), start), mlen);           // motion_tracking.py:281-282
         mlen = tab.clip_length[clip];                                       // _resample_motion_times
-        start = io.inject_start_times ? io.inject_start_times[n] : xm(rng.uniform(0), mlen);
+        start = io.inject_start_times ? io.inject_start_times[n] : xm(u01(r_env.x), mlen);
         // _reset_dofs / _reset_root_states from the motion state at the new time (unfused: these are simulator state)
         const FrameBlend f2 = frame_blend_x(tab, clip, xa(xm((float)(ep + 1), dt), start));
         const float b2 = f2.blend, omb2 = 1.0f - b2;
         const float* q0 = tab.records + f2.f0 * KC(rec_stride);
         const float* q1 = tab.records + f2.f1 * KC(rec_stride);
+        const bool any_noise = c.reset_noise[0] != 0.0f || c.reset_noise[1] != 0.0f || c.reset_noise[2] != 0.0f || c.reset_noise[3] != 0.0f ||
+                               c.reset_noise[4] != 0.0f || c.reset_noise[5] != 0.0f;
+        float g0 = 0.0f, g1 = 0.0f, g2 = 0.0f;   // this lane's standard normals: dof position, dof velocity, root-state component
+        Q4 nq = {0.0f, 0.0f, 0.0f, 1.0f};  // small_random_quaternions(n, max_angle): the same value in every lane
+        if (any_noise) {
+          const uint4 r_n = rng.draw(144 + lane);
+          gauss2(r_n.x, r_n.y, g0, g1);
+          { float unused; gauss2(r_n.z, r_n.w, g2, unused); }
+          if (c.reset_noise[3] != 0.0f) {
+            const uint4 r_q = rng.draw(2);
+            V3 ax; float unused;
+            gauss2(r_q.x, r_q.y, ax.x, ax.y);
+            gauss2(r_q.z, r_q.w, ax.z, unused);
+            const float an = norm3(ax.x, ax.y, ax.z);
+            const float ang = c.reset_noise[3] * u01(r_env.z);
+            float sh, ch;
+            __sincosf(ang * 0.5f, &sh, &ch);
+            nq = {sh * (ax.x / an), sh * (ax.y / an), sh * (ax.z / an), ch};
+          }
+        }
         if (ld) {
           dpos2 = xa(xm(omb2, q0[e_dp + lane]), xm(b2, q1[e_dp + lane]));
           dvel2 = xa(xm(omb2, q0[e_dv + lane]), xm(b2, q1[e_dv + lane]));
-          if (c.reset_noise[0] != 0.0f) dpos2 = xa(dpos2, xm(rng.normal(144 + lane), c.reset_noise[0]));
-          if (c.reset_noise[1] != 0.0f) dvel2 = xa(dvel2, xm(rng.normal(176 + lane), c.reset_noise[1]));
+          if (c.reset_noise[0] != 0.0f) dpos2 = xa(dpos2, xm(g0, c.reset_noise[0]));
+          if (c.reset_noise[1] != 0.0f) dvel2 = xa(dvel2, xm(g1, c.reset_noise[1]));
           reinterpret_cast<float2*>(io.dof_state)[n * D + lane] = make_float2(dpos2, dvel2);
         }
-        if (lane < 13) {
-          float v;
-          if (lane >= 3 && lane < 7) {
-            const float4 a = reinterpret_cast<const float4*>(q0)[0], d4 = reinterpret_cast<const float4*>(q1)[0];
-            const Q4 rr = slerp_t({a.x, a.y, a.z, a.w}, {d4.x, d4.y, d4.z, d4.w}, b2);
-            Q4 nq = {0.0f, 0.0f, 0.0f, 1.0f};  // small_random_quaternions(n, 0)
-            if (c.reset_noise[3] != 0.0f) {
-              V3 ax = {rng.normal(2), rng.normal(3), rng.normal(4)};
-              const float an = norm3(ax.x, ax.y, ax.z);
-              const float ang = c.reset_noise[3] * rng.uniform(5);
-              const float sh = sinf(ang / 2.0f);
-              nq = {sh * (ax.x / an), sh * (ax.y / an), sh * (ax.z / an), cosf(ang / 2.0f)};
+        {
+          const float4 a = reinterpret_cast<const float4*>(q0)[0], d4 = reinterpret_cast<const float4*>(q1)[0];
+          const Q4 rr = slerp_t({a.x, a.y, a.z, a.w}, {d4.x, d4.y, d4.z, d4.w}, b2);
+          const Q4 o = quat_mul(nq, rr);
+          if (lane < 13) {
+            float v;
+            if (lane >= 3 && lane < 7) v = lane == 3 ? o.x : (lane == 4 ? o.y : (lane == 5 ? o.z : o.w));
+            else {
+              const int el = lane < 3 ? e_pos + lane : (lane < 10 ? e_vel + (lane - 7) : e_ang + (lane - 10));
+              v = xa(xm(omb2, q0[el]), xm(b2, q1[el]));
+              if (lane < 3) v = xa(v, s_org[lane]);
+              const float ns = lane < 3 ? c.reset_noise[2] : (lane < 10 ? c.reset_noise[4] : c.reset_noise[5]);
+              if (ns != 0.0f) v = xa(v, xm(g2, ns));
             }
-            const Q4 o = quat_mul(nq, rr);
-            v = lane == 3 ? o.x : (lane == 4 ? o.y : (lane == 5 ? o.z : o.w));
-          } else {
-            const int el = lane < 3 ? e_pos + lane : (lane < 10 ? e_vel + (lane - 7) : e_ang + (lane - 10));
-            v = xa(xm(omb2, q0[el]), xm(b2, q1[el]));
-            if (lane < 3) v = xa(v, s_org[lane]);
-            const float ns = lane < 3 ? c.reset_noise[2] : (lane < 10 ? c.reset_noise[4] : c.reset_noise[5]);
-            if (ns != 0.0f) v = xa(v, xm(rng.normal(8 + lane), ns));
+            io.root_state[n * 13 + lane] = v;
           }
-          io.root_state[n * 13 + lane] = v;
         }
         // the observations of an env that reset: dof-wise features from the new state; the scalar features go in (again)
         // after the ring was zeroed (ref_motion_phase & co. stay stale like the reference's)
         if (ld) {
           const float ddef = io.default_dof_pos[n * KC(default_dof_stride) + lane];
-          emit1<kNoise>(T, Rw, S_DOF_POS, lane, dpos2 - ddef, clipv, nk);
-          emit1<kNoise>(T, Rw, S_DOF_VEL, lane, dvel2, clipv, nk);
-          emit1<kNoise>(T, Rw, S_ACTIONS, lane, 0.0f, clipv, nk);
-          emit1<kNoise>(T, Rw, S_DR_KP, lane, kp2, clipv, nk);
-          emit1<kNoise>(T, Rw, S_DR_KD, lane, kd2, clipv, nk);
+          emit1k<kNoise, S_DOF_POS>(T, Rw, lane, dpos2 - ddef, clipv, nk);
+          emit1k<kNoise, S_DOF_VEL>(T, Rw, lane, dvel2, clipv, nk);
+          emit1k<kNoise, S_ACTIONS>(T, Rw, lane, 0.0f, clipv, nk);
+          emit1k<kNoise, S_DR_KP>(T, Rw, lane, kp2, clipv, nk);
+          emit1k<kNoise, S_DR_KD>(T, Rw, lane, kd2, clipv, nk);
           const int x = e * D + lane;
           reinterpret_cast<float*>(smem + KC(q_lact))[x] = 0.0f; reinterpret_cast<float*>(smem + KC(q_ldpos))[x] = dpos2; reinterpret_cast<float*>(smem + KC(q_ldvel))[x] = dvel2;
         }
@@ -910,7 +985,7 @@ __device__ __forceinline__ void track_tile_body(const TileParams& P) {
 
     // ---- outputs leave, the next tile's inputs are requested -----------------------------------------------------------------------------
     if (bulk) {
-      if (warp == 0) {
+      if (warp == kTE - 1) {
         for (int i = lane; i < P.n_out; i += 32) {
           const TileDesc d = P.out[i];
           bulk_store(const_cast<char*>(d.g) + (int64_t)tile0 * d.row_bytes, sbase + d.soff, kTE * d.row_bytes);
@@ -928,10 +1003,10 @@ __device__ __forceinline__ void track_tile_body(const TileParams& P) {
     }
     pre_ready = have_small_next;  // (the next tile's scalars were computed above)
     const bool big = is_bulk(tile + stride), small = is_bulk(tile + 2 * stride);
-    if (big && warp == 0) issue_loads(tile + stride, true, tile + 2 * stride, small, sb);
+    if (big && warp == kTE - 1) issue_loads(tile + stride, true, tile + 2 * stride, small, sb);
     have_small_next = small;
   }
-  if (warp == 0) bulk_wait_read();
+  if (warp == kTE - 1) bulk_wait_read();
   // block partials: 64 threads add the warps' sums up in warp order
   __syncthreads();
   double* wacc = reinterpret_cast<double*>(smem + KC(o_rows));
@@ -958,7 +1033,7 @@ __global__ void __launch_bounds__(kNT, 3) track_tile_kernel(const __grid_constan
 extern int g_track_info[4];
 int jit_get(const char* what, const std::string& spec_header, bool noise, const void** kernel);   // jit.cu: 0 = *kernel is the cudaKernel_t of the specialised kernel
 
-std::string tile_spec_header(const HotK& k) {
+std::string tile_spec_header(const HotK& k, const SpecExtra& x) {
   char buf[128];
   std::string h = "// generated by pbhc_b200 (track_tile.cu tile_spec_header): launch constants of one env config\nnamespace spec {\n";
 #define X(n) snprintf(buf, sizeof(buf), "constexpr int %s = %d;\n", #n, k.n); h += buf;
@@ -970,20 +1045,35 @@ std::string tile_spec_header(const HotK& k) {
 #define X(n) snprintf(buf, sizeof(buf), "constexpr long long %s = (long long)0x%llxULL;\n", #n, (unsigned long long)k.n); h += buf;
   PBHC_HOTK_I64(X)
 #undef X
+  auto arr_i = [&](const char* name, const int* v, int n0, int n1) {
+    h += std::string("constexpr int ") + name + "[" + std::to_string(n0) + "]" + (n1 ? "[" + std::to_string(n1) + "]" : std::string()) + " = {";
+    for (int i = 0; i < n0; ++i) {
+      if (n1) { h += "{"; for (int j = 0; j < n1; ++j) { h += std::to_string(v[i * n1 + j]); h += j + 1 < n1 ? "," : ""; } h += "}"; }
+      else h += std::to_string(v[i]);
+      h += i + 1 < n0 ? "," : "";
+    }
+    h += "};\n";
+  };
+  arr_i("sd_n", x.n, 20, 0); arr_i("sd_base", &x.base[0][0], 20, 4); arr_i("sd_stride", &x.stride[0][0], 20, 4);
+  arr_i("sd_pushed", x.pushed, 20, 0); arr_i("sd_noisy", x.noisy, 20, 0);
+  h += "constexpr float sd_scale[20] = {";
+  for (int i = 0; i < 20; ++i) { snprintf(buf, sizeof(buf), "%af%s", (double)x.scale[i], i < 19 ? "," : ""); h += buf; }
+  h += "};\n";
   h += "}  // namespace spec\n";
   return h;
 }
 
 // the kernel specialised for these constants (kernel == nullptr: compile into the on-disk cache only)
-static int jit_track_tile(const HotK& k, bool noise, const void** kernel) {
+static int jit_track_tile(const HotK& k, const SpecExtra& x, bool noise, const void** kernel) {
   static thread_local HotK last_k;
+  static thread_local SpecExtra last_x;
   static thread_local bool last_noise = false, have = false;
   static thread_local const void* last_fn = nullptr;
   static thread_local int last_rc = 0;
-  if (kernel && have && last_noise == noise && !memcmp(&last_k, &k, sizeof(k))) { *kernel = last_fn; return last_rc; }
+  if (kernel && have && last_noise == noise && !memcmp(&last_k, &k, sizeof(k)) && !memcmp(&last_x, &x, sizeof(x))) { *kernel = last_fn; return last_rc; }
   const void* fn = nullptr;
-  const int rc = jit_get("track_tile", tile_spec_header(k), noise, kernel ? &fn : nullptr);
-  if (kernel) { last_k = k; last_noise = noise; have = true; last_fn = fn; last_rc = rc; *kernel = fn; }
+  const int rc = jit_get("track_tile", tile_spec_header(k, x), noise, kernel ? &fn : nullptr);
+  if (kernel) { last_k = k; last_x = x; last_noise = noise; have = true; last_fn = fn; last_rc = rc; *kernel = fn; }
   return rc;
 }
 
@@ -1004,6 +1094,8 @@ static int tile_plan(const PbhcTrackCfg& c, const PbhcTableDesc& tab, const Pbhc
   k.cur_torque_enable = c.cur_torque.enable; k.term_gravity = c.term_gravity; k.term_motion_far = c.term_motion_far; k.term_motion_end = c.term_motion_end;
   k.dif_joint_used = (c.src_used_mask & ((1ull << S_DIF_JOINT) | (1ull << S_DIF_JOINT_VEL))) ? 1 : 0;
   k.ref_vel_used = (c.src_used_mask & ((1ull << S_LOCAL_REF_VEL) | (1ull << S_GLOBAL_REF_VEL))) ? 1 : 0;
+  k.ext_identity = 1;
+  for (int x = 0; x < c.n_ext; ++x) if (c.ext_rot_xyzw[x][0] != 0.0f || c.ext_rot_xyzw[x][1] != 0.0f || c.ext_rot_xyzw[x][2] != 0.0f || c.ext_rot_xyzw[x][3] != 1.0f) k.ext_identity = 0;
   k.ref_pos_out = io.ref_body_pos_extend ? 1 : 0; k.ref_rot_out = io.ref_body_rot_extend ? 1 : 0;
   k.default_dof_stride = (int)io.default_dof_stride;
   k.dt = c.dt; k.clip_obs = c.clip_obs; k.term_gravity_thr = c.term_gravity_thr; k.w_lower = c.w_lower; k.w_upper = c.w_upper;
@@ -1060,7 +1152,7 @@ static int tile_plan(const PbhcTrackCfg& c, const PbhcTableDesc& tab, const Pbhc
   k.i_body = slab_in(io.body_state, Jb * 13 * 4, io.body_env_stride * 4);
   k.i_cf = slab_in(io.contact_forces, Jb * 12, Jb * 12);
   // per-env scratch row (dof partials, then body partials): the env's history row once it is scattered, if that is large enough
-  const int scr_floats = kDofRaw * D > kBodyRaw * J ? kDofRaw * D : kBodyRaw * J;
+  const int scr_floats = kDofRaw * D > kBodyRaw * J ? kDofRaw * D : kBodyRaw * J;  // (10 x 27 = 270 <= 316 for G1 23-DoF obs=main)
   if (H > 0) k.i_hist = slab_in(io.hist, H * 4, H * 4);
   else k.i_hist = off;
   if (H >= scr_floats) { k.o_scr = k.i_hist; k.scr_pitch = H * 4; }
@@ -1091,6 +1183,15 @@ static int tile_plan(const PbhcTrackCfg& c, const PbhcTableDesc& tab, const Pbhc
   }
   k.row_base0 = row_base[0]; k.row_base1 = row_base[1]; k.row_base2 = row_base[2]; k.row_base3 = row_base[3];
   k.gdim0 = gdim[0]; k.gdim1 = gdim[1]; k.gdim2 = gdim[2]; k.gdim3 = gdim[3];
+  memset(&P.x, 0, sizeof(P.x));
+  static_assert(kSrcT <= 20, "SpecExtra is sized for 20 sources");
+  for (int s = 0; s < kSrcT; ++s) {
+    for (int g = 0; g < c.n_groups; ++g)
+      if (c.src_dst[s][g] >= 0) { P.x.base[s][P.x.n[s]] = row_base[g] + c.src_dst[s][g]; P.x.stride[s][P.x.n[s]] = c.group_dim[g]; ++P.x.n[s]; }
+    for (int h = 0; h < c.n_hist_keys; ++h) if (c.hist_src[h] == s) P.x.pushed[s] = 1;
+    P.x.noisy[s] = c.obs_noise[s] != 0.0f ? 1 : 0;
+    P.x.scale[s] = c.obs_scale[s];
+  }
   if (off - k.o_rows < 8 * 32 * kTE) take(8 * 32 * kTE - (off - k.o_rows));  // (the rows region also parks the scalars / the warps' sums)
   k.q_rew = slab_out(io.rew_buf, c.use_vec_reward ? (c.n_rewards + 1) * 4 : 4);
   k.q_es = slab_out(io.episode_sums, c.n_episode_sums * 4);
@@ -1122,7 +1223,7 @@ int track_tile_launch(const PbhcTrackCfg& c, const PbhcTableDesc& tab, const Pbh
   KernelState* st = &generic[noise ? 1 : 0];
   int which = 1;
   const void* jk = nullptr;
-  if (jit_track_tile(P.k, noise, &jk) == 0 && jk) { kern = jk; st = &jitted[jk]; which = 2; }
+  if (jit_track_tile(P.k, P.x, noise, &jk) == 0 && jk) { kern = jk; st = &jitted[jk]; which = 2; }
   if ((size_t)shmem > st->configured || st->per_sm == 0) {
     if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, shmem) != cudaSuccess) return check_launch("pbhc_track_step(attr)");
     (void)cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
@@ -1148,7 +1249,7 @@ int track_tile_prepare(const PbhcTrackCfg& c, const PbhcTableDesc& tab, const Pb
   if (shmem < 0) return shmem;
   bool noise = false;
   for (int s = 0; s < kSrcT; ++s) noise |= c.obs_noise[s] != 0.0f;
-  return jit_track_tile(P.k, noise, nullptr) == 0 ? PBHC_OK : PBHC_E_CUDA;
+  return jit_track_tile(P.k, P.x, noise, nullptr) == 0 ? PBHC_OK : PBHC_E_CUDA;
 }
 
 }  // namespace pbhc
