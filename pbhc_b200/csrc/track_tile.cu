@@ -418,6 +418,15 @@ __device__ void build_tile_tables(const TileParams& P, TileTables& T, int* hmap,
   __syncthreads();
 }
 
+// development aid (PBHC_TILE_PROF=1 at JIT time): lane 0 of every warp of blocks 0..7 stamps clock64() at six points of its
+// first 16 tiles into the unused tail of io.partials (rows 600 + 16 * block), read back by tools/tile_prof.py.  (BAR.SYNC does
+// not block at issue but at the next shared-memory access: the stamp reads shared memory first.)
+#ifdef PBHC_TILE_PROF
+#define TPROF(slot) do { unsigned tp_; asm volatile("ld.volatile.shared.u32 %0, [%1];" : "=r"(tp_) : "r"(bar) : "memory"); if (lane == 0 && blockIdx.x < 8 && it < 16) reinterpret_cast<long long*>(P.io.partials)[(long long)(600 + blockIdx.x * 16) * 64 + ((it * 8 + warp) * 6 + (slot))] = clock64() + (tp_ & 0u); } while (0)
+#else
+#define TPROF(slot) do { } while (0)
+#endif
+
 template <bool kNoise>
 __device__ __forceinline__ void track_tile_body(const TileParams& P) {
   extern __shared__ __align__(128) unsigned char smem[];
@@ -525,6 +534,7 @@ __device__ __forceinline__ void track_tile_body(const TileParams& P) {
     const int cnt = min(kTE, n_envs - tile0);
     const int sb = it & 1;
     const bool bulk = is_bulk(tile);
+    TPROF(0);
     if (warp == kTE - 1) bulk_wait_read();  // the previous tile's bulk stores have left the output slabs
     if (bulk) { if (tid == kNT - 32) mbar_wait_t(bar, phase); phase ^= 1u; }
     else {  // ragged last tile / unaligned tensors: cooperative word copies
@@ -539,9 +549,10 @@ __device__ __forceinline__ void track_tile_body(const TileParams& P) {
       }
     }
     __syncthreads();
+    TPROF(1);
     if (!pre_ready) { pre_pieces(sb, cnt); __syncthreads(); }
-    if (have_small_next) pre_pieces(sb ^ 1, kTE);  // the next tile's scalars, consumed after the end-of-tile barrier
 
+    TPROF(2);
     // ================================ warp = env =====================================================================
     if (warp < cnt) {
       const int e = warp;
@@ -980,10 +991,15 @@ __device__ __forceinline__ void track_tile_body(const TileParams& P) {
         acc_reg += a;
       }
     }
+    TPROF(3);
     fence_async();
     __syncthreads();
+    TPROF(4);
 
-    // ---- outputs leave, the next tile's inputs are requested -----------------------------------------------------------------------------
+    // ---- the next tile's inputs are requested (first: they are on the critical path), outputs leave; meanwhile the warps
+    // that carry a piece of the next tile's per-env scalars compute it (its small inputs arrived a tile ago) ----------------------
+    const bool big = is_bulk(tile + stride), small = is_bulk(tile + 2 * stride);
+    if (big && warp == kTE - 1) issue_loads(tile + stride, true, tile + 2 * stride, small, sb);
     if (bulk) {
       if (warp == kTE - 1) {
         for (int i = lane; i < P.n_out; i += 32) {
@@ -1001,10 +1017,10 @@ __device__ __forceinline__ void track_tile_body(const TileParams& P) {
         for (int w = tid; w < nw; w += kNT) dst[w] = src[w];
       }
     }
-    pre_ready = have_small_next;  // (the next tile's scalars were computed above)
-    const bool big = is_bulk(tile + stride), small = is_bulk(tile + 2 * stride);
-    if (big && warp == kTE - 1) issue_loads(tile + stride, true, tile + 2 * stride, small, sb);
+    if (have_small_next) pre_pieces(sb ^ 1, kTE);
+    pre_ready = have_small_next;
     have_small_next = small;
+    TPROF(5);
   }
   if (warp == kTE - 1) bulk_wait_read();
   // block partials: 64 threads add the warps' sums up in warp order

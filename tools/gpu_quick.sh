@@ -6,6 +6,6 @@ for j in 1 0; do
   PBHC_JIT=$j timeout 300 python bench.py --steps 50 --warmup 5 --no-e2e --no-cpu-baseline "$@" 2>gpurun_out/quick.err | python -c "
 import sys, json
 d = json.loads(sys.stdin.read())
-print('JIT=$j step_ms %.4f track_ms %.4f frac %.3f' % (d['ms_per_step'], d['roofline']['kernel_ms'], d['roofline']['frac']), d['stages_ms'])"
+print('JIT=$j', d['config'].get('track_launch'), 'step_ms %.4f track_ms %.4f frac %.3f' % (d['ms_per_step'], d['roofline']['kernel_ms'], d['roofline']['frac']), d['stages_ms'])"
 done
 tail -2 gpurun_out/quick.err
