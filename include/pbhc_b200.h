@@ -95,6 +95,12 @@ typedef struct {
  * (may be NULL). */
 int pbhc_fk(const PbhcTree* tree, const float* pose_aa, const float* trans, int64_t n_poses,
             float* pos, float* rotmat, float* quat_xyzw, void* stream);
+/* The same with the reference's operation sequence kept step for step (IEEE sqrt / division, separate sin and cos, all
+ * four matrix_to_quaternion candidates): what load_motions uses, because the angular velocities of the motion table
+ * amplify last-ulp differences of the frame quaternions.  pbhc_fk is within the same tolerance of the
+ * reference (1e-5 rel / 1e-6 abs) with fewer instructions. */
+int pbhc_fk_exact(const PbhcTree* tree, const float* pose_aa, const float* trans, int64_t n_poses,
+                  float* pos, float* rotmat, float* quat_xyzw, void* stream);
 
 /* ---- GAE: PPO._compute_returns (agents/ppo/ppo.py:338-355), MHPPO._compute_returns
  * (agents/mh_ppo/mh_ppo.py:376-395).  rewards/values/returns [T,N,R], dones [T,N] (bool bytes),

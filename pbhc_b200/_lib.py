@@ -53,7 +53,7 @@ class Tree(C.Structure):
 
 _lib = None
 
-EXPORTS = ["pbhc_abi_version", "pbhc_struct_size", "pbhc_last_error", "pbhc_lookup", "pbhc_fk", "pbhc_gae", "pbhc_adv_normalize", "pbhc_clip_prepare",
+EXPORTS = ["pbhc_abi_version", "pbhc_struct_size", "pbhc_last_error", "pbhc_lookup", "pbhc_fk", "pbhc_fk_exact", "pbhc_gae", "pbhc_adv_normalize", "pbhc_clip_prepare",
            "pbhc_track_max_blocks", "pbhc_track_launch_info", "pbhc_track_specialize", "pbhc_track_step", "pbhc_track_finalize", "pbhc_gather_rows", "pbhc_gather_keys", "pbhc_timeout_bootstrap", "pbhc_blend_frames", "pbhc_traj_metrics", "pbhc_pre_physics", "pbhc_compute_torques"]
 
 
@@ -70,6 +70,8 @@ def lib():
     L.pbhc_lookup.argtypes = [C.POINTER(TableDesc), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64,
                               C.POINTER(LookupOut), C.c_void_p]
     L.pbhc_fk.restype = C.c_int
+    L.pbhc_fk_exact.restype = C.c_int
+    L.pbhc_fk_exact.argtypes = [C.POINTER(Tree), C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
     L.pbhc_fk.argtypes = [C.POINTER(Tree), C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p,
                           C.c_void_p]
     L.pbhc_gae.restype = C.c_int

@@ -24,6 +24,11 @@ struct FkParams {
   int8_t load_slot[PBHC_MAX_JOINTS];  // slot holding the parent's transform, or -1 (= previous joint)
   float off[PBHC_MAX_JOINTS * 3];
   float lrot[PBHC_MAX_JOINTS * 9];
+  // the tree is cut into n_parts joint ranges [part_begin, part_end) walked by different warps of the same 32 poses (a thread
+  // per pose leaves a B200 with 14 warps per SM at 65536 poses: latency-bound); a part first recomputes, without output,
+  // the ancestors of its range that lie outside it (`silent`, root first)
+  int n_parts, part_begin[2], part_end[2], n_silent[2];
+  int8_t silent[2][8];
 };
 
 struct M3 { float m[9]; };
@@ -49,6 +54,45 @@ __device__ __forceinline__ M3 aa_to_mat(float ax, float ay, float az) {
   o.m[3] = two_s * (i * j + kk * r); o.m[4] = 1.0f - two_s * (i * i + kk * kk); o.m[5] = two_s * (j * kk - i * r);
   o.m[6] = two_s * (i * kk - j * r); o.m[7] = two_s * (j * kk + i * r); o.m[8] = 1.0f - two_s * (i * i + j * j);
   return o;
+}
+
+// The same two conversions for the per-step fk_batch (kFast): within the 1e-5 rel / 1e-6 abs bar of the reference but not
+// operation-for-operation - one sincosf, reciprocal square root / approximate division (2 ulp) instead of IEEE sqrt and
+// division, FMA everywhere; matrix_to_quaternion takes ONE square root (the candidate with the largest 1 +- m00 +- m11 +- m22
+// is the one with the largest sqrt).  Load-time FK (load_motions -> the motion table, whose angular velocities amplify
+// last-ulp differences) keeps the exact sequence below.
+__device__ __forceinline__ M3 aa_to_mat_fast(float ax, float ay, float az) {
+  const float s2 = __fmaf_rn(az, az, __fmaf_rn(ay, ay, ax * ax));
+  const float rinv = rsqrtf(fmaxf(s2, 1e-30f)), ang = s2 * rinv;
+  const float half = ang * 0.5f;
+  float sh, r;
+  sincosf(half, &sh, &r);
+  const float k = (ang < 1e-6f) ? __fmaf_rn(s2, -1.0f / 48.0f, 0.5f) : sh * rinv;
+  const float i = ax * k, j = ay * k, kk = az * k;
+  const float two_s = __fdividef(2.0f, __fmaf_rn(kk, kk, __fmaf_rn(j, j, __fmaf_rn(i, i, r * r))));
+  const float ii = two_s * i, jj = two_s * j, k2 = two_s * kk;
+  M3 o;
+  o.m[0] = __fmaf_rn(-jj, j, __fmaf_rn(-k2, kk, 1.0f)); o.m[1] = __fmaf_rn(ii, j, -k2 * r); o.m[2] = __fmaf_rn(ii, kk, jj * r);
+  o.m[3] = __fmaf_rn(ii, j, k2 * r); o.m[4] = __fmaf_rn(-ii, i, __fmaf_rn(-k2, kk, 1.0f)); o.m[5] = __fmaf_rn(jj, kk, -ii * r);
+  o.m[6] = __fmaf_rn(ii, kk, -jj * r); o.m[7] = __fmaf_rn(jj, kk, ii * r); o.m[8] = __fmaf_rn(-ii, i, __fmaf_rn(-jj, j, 1.0f));
+  return o;
+}
+__device__ __forceinline__ void mat_to_quat_xyzw_fast(const M3& R, float* q) {
+  const float m00 = R.m[0], m01 = R.m[1], m02 = R.m[2], m10 = R.m[3], m11 = R.m[4], m12 = R.m[5], m20 = R.m[6], m21 = R.m[7], m22 = R.m[8];
+  const float p0 = 1.0f + m00 + m11 + m22, p1 = 1.0f + m00 - m11 - m22, p2 = 1.0f - m00 + m11 - m22, p3 = 1.0f - m00 - m11 + m22;
+  int best = 0;
+  float pb = fmaxf(p0, 0.0f);
+  if (p1 > pb) { best = 1; pb = p1; }
+  if (p2 > pb) { best = 2; pb = p2; }
+  if (p3 > pb) { best = 3; pb = p3; }
+  float c0, c1, c2, c3;  // wxyz candidate of `best`
+  if (best == 0) { c0 = pb; c1 = m21 - m12; c2 = m02 - m20; c3 = m10 - m01; }
+  else if (best == 1) { c0 = m21 - m12; c1 = pb; c2 = m10 + m01; c3 = m02 + m20; }
+  else if (best == 2) { c0 = m02 - m20; c1 = m10 + m01; c2 = pb; c3 = m12 + m21; }
+  else { c0 = m10 - m01; c1 = m20 + m02; c2 = m21 + m12; c3 = pb; }
+  const float qa = pb * rsqrtf(fmaxf(pb, 1e-30f));
+  const float inv = __fdividef(0.5f, fmaxf(qa, 0.1f));
+  q[0] = c1 * inv; q[1] = c2 * inv; q[2] = c3 * inv; q[3] = c0 * inv;
 }
 
 // matrix_to_quaternion (rotations.py:589-647) then wxyz_to_xyzw (torch_humanoid_batch.py:188)
@@ -132,6 +176,7 @@ __device__ __forceinline__ void flush_lin(const float* sm, float* g, int row_len
   }
 }
 
+template <bool kFast>
 __global__ void __launch_bounds__(kFkWarps * 32, 16) fk_kernel(const __grid_constant__ FkParams P, const float* __restrict__ pose_aa,
                                                             const float* __restrict__ trans, int64_t n, float* __restrict__ pos,
                                                             float* __restrict__ rotmat, float* __restrict__ quat, int tile) {
@@ -143,7 +188,9 @@ __global__ void __launch_bounds__(kFkWarps * 32, 16) fk_kernel(const __grid_cons
   float* sm_out = sm_in0 + 2 * 32 * kInRow;
   float* sm_pos = sm_out, *sm_rot = sm_pos + 32 * kPosRow, *sm_quat = sm_rot + 32 * kRotRow;
   float* sm_slot = sm_out + 32 * kStageRow;
-  const int64_t p0 = ((int64_t)blockIdx.x * kFkWarps + warp) * tile;  // tile = poses per warp (32, or fewer for small batches)
+  const int part = (int)(blockIdx.x % (unsigned)P.n_parts);
+  const int64_t p0 = ((int64_t)(blockIdx.x / (unsigned)P.n_parts) * kFkWarps + warp) * tile;  // tile = poses per warp (32, or fewer for small batches)
+  const int jb = P.part_begin[part], je = P.part_end[part];
   if (p0 >= n) return;
   const int npose = (int)min((int64_t)tile, n - p0);
   const bool live = lane < npose;
@@ -154,16 +201,47 @@ __global__ void __launch_bounds__(kFkWarps * 32, 16) fk_kernel(const __grid_cons
   for (int i = 0; i < 9; ++i) Rc.m[i] = 0.f;
 
   const bool tile32 = npose == 32;
-  if (tile32 && J >= kChunk) fill_full_async<3 * kChunk>(sm_in0, g_in, 3 * J, 0, lane);
+  if (tile32 && je - jb >= kChunk) fill_full_async<3 * kChunk>(sm_in0, g_in, 3 * J, 3 * jb, lane);
+  if (live) {  // ancestors of this part's range outside it: world transform only (their outputs belong to another part)
+    for (int s = 0; s < P.n_silent[part]; ++s) {
+      const int i = P.silent[part][s];
+      const float* a = g_in + (int64_t)lane * (3 * J) + 3 * i;
+      const M3 Mj = kFast ? aa_to_mat_fast(__ldg(a), __ldg(a + 1), __ldg(a + 2)) : aa_to_mat(__ldg(a), __ldg(a + 1), __ldg(a + 2));
+      if (P.parent[i] < 0) {
+        Rc = Mj;
+        const float* tr = trans + (p0 + lane) * 3;
+        pc[0] = tr[0]; pc[1] = tr[1]; pc[2] = tr[2];
+      } else {  // (the silent chain is root first: the previous one is the parent)
+        M3 L;
+#pragma unroll
+        for (int c = 0; c < 9; ++c) L.m[c] = P.lrot[i * 9 + c];
+        const M3 LMj = matmul3(L, Mj);
+        const float ox = P.off[i * 3], oy = P.off[i * 3 + 1], oz = P.off[i * 3 + 2];
+        float np_[3];
+#pragma unroll
+        for (int c = 0; c < 3; ++c) np_[c] = __fmaf_rn(Rc.m[c * 3 + 2], oz, __fmaf_rn(Rc.m[c * 3 + 1], oy, Rc.m[c * 3] * ox)) + pc[c];
+        pc[0] = np_[0]; pc[1] = np_[1]; pc[2] = np_[2];
+        Rc = matmul3(Rc, LMj);
+      }
+      const int ss = P.save_slot[i];
+      if (ss >= 0) {
+        float* sl = sm_slot + ss * 12 * 32 + lane;
+#pragma unroll
+        for (int c = 0; c < 9; ++c) sl[c * 32] = Rc.m[c];
+#pragma unroll
+        for (int c = 0; c < 3; ++c) sl[(9 + c) * 32] = pc[c];
+      }
+    }
+  }
   int buf = 0;
-  for (int j0 = 0; j0 < J; j0 += kChunk, buf ^= 1) {
-    const int nj = min(kChunk, J - j0);
+  for (int j0 = jb; j0 < je; j0 += kChunk, buf ^= 1) {
+    const int nj = min(kChunk, je - j0);
     float* sm_in = sm_in0 + buf * 32 * kInRow;
     __syncwarp();
     const bool full = tile32 && nj == kChunk;
     if (full) {
       asm volatile("cp.async.wait_all;" ::: "memory");
-      if (j0 + 2 * kChunk <= J) fill_full_async<3 * kChunk>(sm_in0 + (buf ^ 1) * 32 * kInRow, g_in, 3 * J, 3 * (j0 + kChunk), lane);
+      if (j0 + 2 * kChunk <= je) fill_full_async<3 * kChunk>(sm_in0 + (buf ^ 1) * 32 * kInRow, g_in, 3 * J, 3 * (j0 + kChunk), lane);
     } else {
       fill_rows(sm_in, kInRow, g_in, 3 * J, 3 * j0, 3 * nj, npose, lane);
     }
@@ -178,7 +256,7 @@ __global__ void __launch_bounds__(kFkWarps * 32, 16) fk_kernel(const __grid_cons
         if (jj < nj) {
           const int i = j0 + jj;
           const float* a = sm_in + lane * kInRow + 3 * jj;
-          const M3 Mj = aa_to_mat(a[0], a[1], a[2]);
+          const M3 Mj = kFast ? aa_to_mat_fast(a[0], a[1], a[2]) : aa_to_mat(a[0], a[1], a[2]);
           M3 L;
 #pragma unroll
           for (int c = 0; c < 9; ++c) L.m[c] = P.lrot[i * 9 + c];
@@ -228,7 +306,7 @@ __global__ void __launch_bounds__(kFkWarps * 32, 16) fk_kernel(const __grid_cons
       if (quat) {
 #pragma unroll
         for (int jj = 0; jj < kChunk; ++jj)
-          if (jj < nj) mat_to_quat_xyzw(Rw[jj], sm_quat + lane * kQuatRow + jj * 4);
+          if (jj < nj) { if (kFast) mat_to_quat_xyzw_fast(Rw[jj], sm_quat + lane * kQuatRow + jj * 4); else mat_to_quat_xyzw(Rw[jj], sm_quat + lane * kQuatRow + jj * 4); }
       }
     }
     __syncwarp();
@@ -246,8 +324,8 @@ __global__ void __launch_bounds__(kFkWarps * 32, 16) fk_kernel(const __grid_cons
 
 }  // namespace pbhc
 
-extern "C" int pbhc_fk(const PbhcTree* tree, const float* pose_aa, const float* trans, int64_t n, float* pos,
-                       float* rotmat, float* quat_xyzw, void* stream) {
+static int fk_launch(const PbhcTree* tree, const float* pose_aa, const float* trans, int64_t n, float* pos,
+                     float* rotmat, float* quat_xyzw, bool fast, void* stream) {
   using namespace pbhc;
   if (!tree || !tree->parents || !tree->offsets || !tree->local_rot_mat || !pose_aa || !trans || !pos || n < 0) {
     set_error("pbhc_fk: null argument"); return PBHC_E_BADARG;
@@ -274,24 +352,55 @@ extern "C" int pbhc_fk(const PbhcTree* tree, const float* pose_aa, const float* 
     P.load_slot[i] = P.save_slot[p];
   }
   if (n == 0) return PBHC_OK;
-  const size_t shmem = (size_t)kFkWarps * (2 * 32 * kInRow + 32 * kStageRow + P.n_slots * 12 * 32) * sizeof(float);
-  static thread_local size_t configured = 0;
-  static thread_local bool carved = false;
-  if (!carved) {  // shared memory bounds the resident warps: ask for the largest carve-out
-    (void)cudaFuncSetAttribute(fk_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
-    carved = true;
+  // two parts when the batch alone cannot fill the machine (<= 64 warps per SM) and the tree splits: the cut s is the joint
+  // nearest J/2 such that every joint >= s has its parent either >= s or among the ancestors of s (a chain of at most 8)
+  P.n_parts = 1; P.part_begin[0] = 0; P.part_end[0] = J; P.n_silent[0] = 0; P.n_silent[1] = 0;
+  if (J >= 8 && n <= 148LL * 32 * 32) {
+    int best = -1;
+    for (int s = 2; s < J - 1; ++s) {
+      bool anc[PBHC_MAX_JOINTS] = {false};
+      int depth = 0;
+      for (int a = P.parent[s]; a >= 0; a = P.parent[a]) { anc[a] = true; ++depth; }
+      bool ok = depth <= 8;
+      for (int i = s; i < J && ok; ++i) ok = P.parent[i] >= s || (P.parent[i] >= 0 && anc[P.parent[i]]);
+      if (ok && (best < 0 || abs(2 * s - J) < abs(2 * best - J))) best = s;
+    }
+    if (best > 0) {
+      P.n_parts = 2; P.part_end[0] = best; P.part_begin[1] = best; P.part_end[1] = J;
+      int chain[8], d = 0;
+      for (int a = P.parent[best]; a >= 0; a = P.parent[a]) chain[d++] = a;
+      P.n_silent[1] = d;
+      for (int i = 0; i < d; ++i) P.silent[1][i] = (int8_t)chain[d - 1 - i];  // root first
+    }
   }
-  if (shmem > 48 * 1024 && shmem > configured) {
-    if (cudaFuncSetAttribute(fk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shmem) != cudaSuccess) return check_launch("pbhc_fk(attr)");
-    configured = shmem;
+  const size_t shmem = (size_t)kFkWarps * (2 * 32 * kInRow + 32 * kStageRow + P.n_slots * 12 * 32) * sizeof(float);
+  auto kern = fast ? fk_kernel<true> : fk_kernel<false>;
+  static thread_local size_t configured[2] = {0, 0};
+  static thread_local bool carved[2] = {false, false};
+  if (!carved[fast]) {  // shared memory bounds the resident warps: ask for the largest carve-out
+    (void)cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    carved[fast] = true;
+  }
+  if (shmem > 48 * 1024 && shmem > configured[fast]) {
+    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shmem) != cudaSuccess) return check_launch("pbhc_fk(attr)");
+    configured[fast] = shmem;
   }
   // small batches: with 32 poses per warp fewer warps than SMs would exist and the kernel is pure latency; narrower
   // tiles (idle lanes) keep every SM busy and shorten the per-pose staging loops
   int tile = 32;
   while (tile > 8 && (n + tile - 1) / tile < 2 * 148) tile >>= 1;
   const int64_t per_block = (int64_t)kFkWarps * tile;
-  const int64_t blocks = (n + per_block - 1) / per_block;
+  const int64_t blocks = (n + per_block - 1) / per_block * P.n_parts;
   if (blocks > 0x7fffffffLL) { set_error("pbhc_fk: too many poses"); return PBHC_E_RANGE; }
-  fk_kernel<<<(unsigned)blocks, kFkWarps * 32, shmem, (cudaStream_t)stream>>>(P, pose_aa, trans, n, pos, rotmat, quat_xyzw, tile);
+  kern<<<(unsigned)blocks, kFkWarps * 32, shmem, (cudaStream_t)stream>>>(P, pose_aa, trans, n, pos, rotmat, quat_xyzw, tile);
   return check_launch("pbhc_fk");
+}
+
+extern "C" int pbhc_fk(const PbhcTree* tree, const float* pose_aa, const float* trans, int64_t n, float* pos,
+                       float* rotmat, float* quat_xyzw, void* stream) {
+  return fk_launch(tree, pose_aa, trans, n, pos, rotmat, quat_xyzw, true, stream);
+}
+extern "C" int pbhc_fk_exact(const PbhcTree* tree, const float* pose_aa, const float* trans, int64_t n, float* pos,
+                             float* rotmat, float* quat_xyzw, void* stream) {
+  return fk_launch(tree, pose_aa, trans, n, pos, rotmat, quat_xyzw, false, stream);
 }

@@ -1224,7 +1224,7 @@ __global__ void track_finalize_kernel(const __grid_constant__ PbhcTrackCfg c, co
     const double mean = acc[PBHC_A_ETR_SUM] / n;
     L[PBHC_L_ETR_MEAN] = mean;
     const double var = n > 1.0 ? (acc[PBHC_A_ETR_SQ] - acc[PBHC_A_ETR_SUM] * mean) / (n - 1.0) : 0.0;
-    L[PBHC_L_ETR_STD] = sqrt(fmax(var, 0.0));
+    L[PBHC_L_ETR_STD] = n > 1.0 ? sqrt(fmax(var, 0.0)) : nan("");  // torch.std() of one element is NaN (motion_tracking.py:414)
   }
   S[PBHC_S_PUSH_COUNT] += 1.0;
 }

@@ -124,9 +124,11 @@ class Humanoid_Batch:
         self._c_tree = _lib.Tree(len(parents), self._c_parents, self._c_offsets, self._c_lrot)
 
     # ------------------------------------------------------------------------------------------
-    def fk(self, pose_aa, trans, want_mat=True, want_quat=True, out=None):
+    def fk(self, pose_aa, trans, want_mat=True, want_quat=True, out=None, exact=False):
         """pose_aa [n,J,3], trans [n,3] CUDA fp32 -> (pos [n,J,3], rotmat [n,J,3,3] | None, quat_xyzw [n,J,4] | None).
-        `out` = a previous result tuple to overwrite instead of allocating."""
+        `out` = a previous result tuple to overwrite instead of allocating.  exact: the reference's operation sequence step
+        for step (pbhc_fk_exact) - what the motion table is built with; the default is the faster kernel within the same
+        1e-5 rel / 1e-6 abs tolerance."""
         J = self.num_bodies_augment
         n = pose_aa.shape[0]
         pose_aa = pose_aa.contiguous()
@@ -138,16 +140,16 @@ class Humanoid_Batch:
             pos = torch.empty(n, J, 3, device=dev, dtype=torch.float32)
             mat = torch.empty(n, J, 3, 3, device=dev, dtype=torch.float32) if want_mat else None
             quat = torch.empty(n, J, 4, device=dev, dtype=torch.float32) if want_quat else None
-        _lib.check(_lib.lib().pbhc_fk(C.byref(self._c_tree), _lib.ptr(pose_aa, torch.float32),
-                                      _lib.ptr(trans, torch.float32), n, _lib.ptr(pos), _lib.ptr(mat), _lib.ptr(quat),
-                                      _lib.stream_ptr(dev)))
+        fn = _lib.lib().pbhc_fk_exact if exact else _lib.lib().pbhc_fk
+        _lib.check(fn(C.byref(self._c_tree), _lib.ptr(pose_aa, torch.float32),
+                      _lib.ptr(trans, torch.float32), n, _lib.ptr(pos), _lib.ptr(mat), _lib.ptr(quat), _lib.stream_ptr(dev)))
         return pos, mat, quat
 
     def clip_kinematics(self, pose_aa, trans, dt, contact=None):
         """FK + filtered velocities + dof_pos/dof_vel of one clip, packed as table records
         [T, rec_stride] (layout: include/pbhc_b200.h).  pose_aa [T,J,3], trans [T,3] CUDA fp32."""
         pose_aa = pose_aa.contiguous()
-        pos, _, quat = self.fk(pose_aa, trans, want_mat=False, want_quat=True)
+        pos, _, quat = self.fk(pose_aa, trans, want_mat=False, want_quat=True, exact=True)
         return self.pack_clip(pos, quat, pose_aa, dt, contact)
 
     def pack_clip(self, pos, quat, pose_aa, dt, contact=None):
@@ -170,8 +172,8 @@ class Humanoid_Batch:
                                                 _lib.stream_ptr(dev)))
         return records
 
-    def fk_batch(self, pose, trans, convert_to_mat=True, return_full=False, dt=1 / 30):
-        """torch_humanoid_batch.py:168-226: same keys.  pose [B,T,J,3] axis-angle, trans [B,T,3] (CUDA)."""
+    def fk_batch(self, pose, trans, convert_to_mat=True, return_full=False, dt=1 / 30, exact=False):
+        """torch_humanoid_batch.py:168-226: same keys.  pose [B,T,J,3] axis-angle, trans [B,T,3] (CUDA).  exact: see fk()."""
         if not convert_to_mat:
             raise NotImplementedError("fk_batch(convert_to_mat=False) is not part of the B200 path")
         if not pose.is_cuda:
@@ -180,7 +182,7 @@ class Humanoid_Batch:
         B, T = pose.shape[:2]
         p = pose[..., :J, :].to(torch.float32).reshape(B * T, J, 3)
         t = trans.to(torch.float32).reshape(B * T, 3)
-        pos, mat, quat = self.fk(p, t)
+        pos, mat, quat = self.fk(p, t, exact=exact or return_full)
         pos, mat, quat = pos.view(B, T, J, 3), mat.view(B, T, J, 3, 3), quat.view(B, T, J, 4)
         r = AttrDict()
         ext = len(self.extend_config) > 0

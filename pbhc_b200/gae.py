@@ -30,9 +30,8 @@ def compute_returns(values, rewards, dones, last_values, gamma, lam, group=None,
                           _lib.ptr(adv), _lib.ptr(stats), st))
     if not normalize:
         return returns, adv
-    if group is not None or (torch.distributed.is_available() and torch.distributed.is_initialized()
-                             and torch.distributed.get_world_size() > 1):
-        torch.distributed.all_reduce(stats, group=group)
+    from .dist import all_reduce_sum_
+    all_reduce_sum_(stats, group)
     _lib.check(L.pbhc_adv_normalize(_lib.ptr(adv), T * N, _lib.ptr(stats), st))
     return returns, adv
 

@@ -157,7 +157,7 @@ class MotionLibRobot:
             dt = 1 / c["fps"]
             pose = torch.as_tensor(np.ascontiguousarray(c["pose_aa"][:, :J]), dtype=torch.float32).to(dev)
             trans = torch.as_tensor(np.ascontiguousarray(c["trans"]), dtype=torch.float32).to(dev)
-            pos, _, quat = hb.fk(pose, trans, want_mat=False, want_quat=True)
+            pos, _, quat = hb.fk(pose, trans, want_mat=False, want_quat=True, exact=True)
             contact = None
             if Cm:
                 contact = torch.as_tensor(np.ascontiguousarray(c["contact"]), dtype=torch.float32).to(dev)

@@ -328,9 +328,8 @@ class TrackingStep:
     def finalize(self, group=None):
         """all-reduce of `acc` when envs are sharded over ranks (the only cross-rank exchange of the step),
         then pbhc_track_finalize advances the device scalars (adaptive sigma, curricula, log values)."""
-        dist = torch.distributed
-        if group is not None or (dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1):
-            dist.all_reduce(self.acc, group=group)
+        from .dist import all_reduce_sum_
+        all_reduce_sum_(self.acc, group)  # (the world-size-2 gloo test drives this very call, tests/test_dist_cpu.py)
         _lib.check(self._L.pbhc_track_finalize(C.byref(self._cfg), _lib.ptr(self.acc), _lib.ptr(self.scalars),
                                                _lib.stream_ptr(self.device)))
 

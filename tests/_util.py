@@ -28,9 +28,15 @@ def assert_close(a, b, rtol=RTOL, atol=ATOL, what=""):
     a = torch.as_tensor(np.asarray(a)).double()
     b = torch.as_tensor(np.asarray(b)).double()
     assert a.shape == b.shape, f"{what}: shape {tuple(a.shape)} vs {tuple(b.shape)}"
+    # NaN / Inf must sit in the same places with the same sign: `err > tol` is False for NaN, so compare the masks first
+    na, nb = ~torch.isfinite(a), ~torch.isfinite(b)
+    if na.any() or nb.any():
+        same = torch.equal(a.isnan(), b.isnan()) and torch.equal(torch.where(a.isinf(), a, torch.zeros_like(a)), torch.where(b.isinf(), b, torch.zeros_like(b)))
+        assert same, f"{what}: non-finite values differ (got {int(na.sum())} non-finite, want {int(nb.sum())})"
+        a, b = torch.where(na, torch.zeros_like(a), a), torch.where(nb, torch.zeros_like(b), b)
     err = (a - b).abs()
     tol = atol + rtol * b.abs()
-    bad = err > tol
+    bad = ~(err <= tol)
     if bad.any():
         i = torch.argmax(err - tol)
         raise AssertionError(f"{what}: {int(bad.sum())}/{bad.numel()} outside tol; worst |d|={err.flatten()[i]:.3e} "

@@ -28,13 +28,16 @@ def _lib_with(tag, names, tmp_path, n):
 from tests._util import install_exact_table as _install_exact_table  # noqa: E402
 
 
+@pytest.mark.parametrize("exact", [False, True])
 @pytest.mark.parametrize("tag,name", [("23", "Horse-stance_pose"), ("29", "g1_29dof_clip")])
-def test_fk_matches_oracle_and_reference_golden(tag, name, tmp_path):
+def test_fk_matches_oracle_and_reference_golden(tag, name, exact, tmp_path):
+    """both kernels - pbhc_fk (per-step fk_batch: fewer instructions) and pbhc_fk_exact (the reference's operation
+    sequence; builds the motion table) - against the reference golden and the oracle, same tolerance"""
     from pbhc_b200.fk import Humanoid_Batch
     hb = Humanoid_Batch(product_cfg(tag, str(tmp_path), [name]))
     g = gold(f"ref_fk_{tag}.npz")
     pose, trans = torch.from_numpy(g["pose"]), torch.from_numpy(g["trans"])
-    r = hb.fk_batch(pose.to(DEV), trans.to(DEV))
+    r = hb.fk_batch(pose.to(DEV), trans.to(DEV), exact=exact)
     assert_close(r.global_translation_extend.cpu(), g["pos"], what="pos")
     assert_close(r.global_rotation_mat_extend.cpu(), g["rotmat"], what="rotmat")
     assert_close(r.global_rotation_extend.cpu(), g["quat"], what="quat")
@@ -45,7 +48,7 @@ def test_fk_matches_oracle_and_reference_golden(tag, name, tmp_path):
     pose = torch.randn(1, 1000 + 7, J, 3, generator=gen) * 0.7
     trans = torch.randn(1, 1007, 3, generator=gen)
     pos, rot, quat, _ = O.fk(oracle_tree(tag), pose, trans)
-    r = hb.fk_batch(pose.to(DEV), trans.to(DEV))
+    r = hb.fk_batch(pose.to(DEV), trans.to(DEV), exact=exact)
     assert_close(r.global_translation_extend.cpu(), pos, what="pos")
     assert_close(r.global_rotation_mat_extend.cpu(), rot, what="rotmat")
     q = r.global_rotation_extend.cpu()
