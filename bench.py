@@ -50,6 +50,8 @@ def parse_args():
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="CPU baseline time budget")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-config-c", action="store_true", help="skip the config C object (general_tracking on the 1024-clip library) of the default line")
+    ap.add_argument("--library-clips", type=int, default=1024, help="clips of the config C motion library (SURVEY 8d: 1024)")
     ap.add_argument("--e2e-chunks", type=int, default=4, help="env chunks of the host-buffer pipeline (HostStep)")
     ap.add_argument("--workload", default="A", choices=["A", "C"],
                     help="A: BASELINE configs[0..1] (23-DoF motion_tracking, the headline); C: configs[2] (29-DoF general_tracking)")
@@ -304,6 +306,9 @@ def run_b200_arm(a):
     e2e = None
     if not a.no_e2e:
         e2e = e2e_pass(torch, dist, wl, min(K, 20), with_fk, world, dev, chunks=a.e2e_chunks)
+    cfg_c = None
+    if a.workload == "A" and world == 1 and not a.no_config_c:
+        cfg_c = config_c_pass(torch, a, dev, peaks()[0])
     sampler.mark("load_end")
     sampler.stop()
     if rank != 0:
@@ -333,6 +338,8 @@ def run_b200_arm(a):
     }
     if e2e is not None:
         line["e2e"] = e2e
+    if cfg_c is not None:
+        line["config_C"] = cfg_c
     if not a.no_cpu_baseline:
         r = cpu_reference(a.cpu_envs, 10 ** 9, 2, seconds=a.cpu_seconds, with_fk=with_fk, workload=a.workload)
         line["cpu_baseline"] = {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "port",
@@ -341,6 +348,60 @@ def run_b200_arm(a):
                                 "ms_per_step": r["ms_per_step"]}
     print(json.dumps(line), flush=True)
     return _finish(torch, dist, world, graph)
+
+
+def config_c_pass(torch, a, dev, peak):
+    """BASELINE configs[2]: the G1 29-DoF general_tracking step (teacher obs, general_main rewards, 20-step future window)
+    at 65 536 envs on the SURVEY 8d library - `--library-clips` 29-DoF clips of 150-600 frames with per-env motion ids, so
+    that the motion table (~0.75 GB at 1024 clips) is served from HBM.  Same timing rules as the headline: CUDA-graph
+    replay of the whole step, CUDA events, K steps after warm-up; roofline against SURVEY 8d's 36 165 B / env-step."""
+    import time as _t
+    from pbhc_b200.workload import Workload, CASE_C, fk_bytes
+    t0 = _t.perf_counter()
+    wl = Workload(a.envs, dev, tempfile.mkdtemp(prefix="pbhc_bench_C_"), seed=2000, case=CASE_C, library_clips=a.library_clips)
+    load_s = _t.perf_counter() - t0
+    for _ in range(3):
+        wl.step(True)
+    torch.cuda.synchronize()
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        wl.step(True)
+    torch.cuda.current_stream().wait_stream(side)
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        wl.step(True)
+    for _ in range(3):
+        g.replay()
+    K = min(a.steps, 50)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    e0.record()
+    for _ in range(K):
+        g.replay()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / K
+    ev = [[torch.cuda.Event(enable_timing=True) for _ in range(2)] for _ in range(10)]
+    for p in ev:
+        p[0].record()
+        wl.ts.launch()
+        p[1].record()
+    torch.cuda.synchronize()
+    kms = sum(p[0].elapsed_time(p[1]) for p in ev) / len(ev)
+    bytes_c = 36165  # SURVEY.md 8d "Fused tracked env-step C" (table rows from HBM)
+    rec = wl.lib._records
+    out = {"workload": WORKLOADS["C"].replace("3-clip library", f"{wl.lib._desc.num_clips}-clip library"), "envs_per_gpu": a.envs, "steps": K,
+           "value": a.envs / (ms * 1e-3), "unit": UNIT, "ms_per_step": ms, "kernel_ms": kms,
+           "roofline": {"bound": "hbm", "algorithmic_bytes_per_env_step": bytes_c, "achieved": bytes_c * a.envs / (kms * 1e-3) / 1e9,
+                        "peak": peak, "unit": "GB/s", "frac": bytes_c * a.envs / (kms * 1e-3) / 1e9 / peak},
+           "motion_table": {"clips": int(wl.lib._desc.num_clips), "frames": int(rec.shape[0]), "mbytes": rec.numel() * 4 / 1e6,
+                            "load_motions_s": load_s, "note": "built on the device: one FK launch + one pbhc_clips_prepare over all frames"},
+           "track_launch": wl.ts.launch_info()}
+    del g, wl
+    torch.cuda.empty_cache()
+    return out
 
 
 def _finish(torch, dist, world, graph):

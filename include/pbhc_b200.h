@@ -176,6 +176,14 @@ int pbhc_clip_prepare(const float* pos, const float* quat, const float* pose_aa,
                       const double* gauss_weights_host, int32_t radius, float* scratch,
                       float* records, int32_t rec_stride, void* stream);
 
+/* The same for the frames of MANY clips back to back (one launch pair for a whole library instead of one per clip):
+ * pos / quat / pose_aa / contact / scratch / records hold total_frames frames; clip_of_frame [total_frames] int32 and the
+ * per-clip first frame / frame count / dt are DEVICE arrays.  Identical results to per-clip pbhc_clip_prepare calls. */
+int pbhc_clips_prepare(const float* pos, const float* quat, const float* pose_aa, const float* contact, int64_t total_frames,
+                       const int32_t* clip_of_frame, const int64_t* clip_start, const int32_t* clip_frames, const float* clip_dt,
+                       int32_t J, int32_t Jb, int32_t D, int32_t C, const double* gauss_weights_host, int32_t radius,
+                       float* scratch, float* records, int32_t rec_stride, void* stream);
+
 /* ---- K3: fused motion-tracking env step (lookup + diffs + termination + rewards + reset + observations +
  * history), i.e. everything LeggedRobotBase._post_physics_step does between refresh_sim_tensors and
  * extras["to_log"] for LeggedRobotMotionTracking or LeggedRobotGeneralTracking (envs/legged_base_task/legged_robot_base.py:297-338,

@@ -325,6 +325,7 @@ class MotionTable:
         motion; with this indirection the oracle stores each unique clip once - same values, same indices
         relative to the clip start."""
         self.num_bodies = num_bodies
+        self.clips = list(clips)
         cat = lambda k: torch.cat([getattr(c, k) for c in clips], dim=0).float()
         self.pos, self.rot, self.vel, self.ang_vel = cat("pos"), cat("rot"), cat("vel"), cat("ang_vel")
         self.dof_pos, self.dof_vel = cat("dof_pos"), cat("dof_vel")

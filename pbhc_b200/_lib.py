@@ -53,7 +53,7 @@ class Tree(C.Structure):
 
 _lib = None
 
-EXPORTS = ["pbhc_abi_version", "pbhc_struct_size", "pbhc_last_error", "pbhc_lookup", "pbhc_fk", "pbhc_fk_exact", "pbhc_gae", "pbhc_adv_normalize", "pbhc_clip_prepare",
+EXPORTS = ["pbhc_abi_version", "pbhc_struct_size", "pbhc_last_error", "pbhc_lookup", "pbhc_fk", "pbhc_fk_exact", "pbhc_gae", "pbhc_adv_normalize", "pbhc_clip_prepare", "pbhc_clips_prepare",
            "pbhc_track_max_blocks", "pbhc_track_launch_info", "pbhc_track_specialize", "pbhc_track_step", "pbhc_track_finalize", "pbhc_gather_rows", "pbhc_gather_keys", "pbhc_timeout_bootstrap", "pbhc_blend_frames", "pbhc_traj_metrics", "pbhc_pre_physics", "pbhc_compute_torques"]
 
 
@@ -98,6 +98,10 @@ def lib():
     L.pbhc_clip_prepare.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32,
                                     C.c_int32, C.c_int32, C.c_float, C.POINTER(C.c_double), C.c_int32, C.c_void_p,
                                     C.c_void_p, C.c_int32, C.c_void_p]
+    L.pbhc_clips_prepare.restype = C.c_int
+    L.pbhc_clips_prepare.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                     C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.POINTER(C.c_double), C.c_int32, C.c_void_p,
+                                     C.c_void_p, C.c_int32, C.c_void_p]
     bind_track(L)
     if L.pbhc_abi_version() != ABI_VERSION:
         raise PbhcError("ABI version mismatch")

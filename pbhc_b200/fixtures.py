@@ -30,6 +30,41 @@ def motion_npz(name):
     return gold(f"motion_{name}.npz")
 
 
+CLIPS23 = ["Horse-stance_pose", "Bruce_Lee_pose", "Charleston_dance", "Hooks_punch", "Horse-stance_punch", "Roundhouse_kick", "Side_kick"]
+
+
+def library29(n_clips=1024, seed=0, min_frames=150, max_frames=600):
+    """The multi-clip 29-DoF motion library of SURVEY.md 8d (config C): the shipped 29-DoF clip plus the seven 23-DoF example
+    clips with zero wrist joints inserted (inverse of convert_29dof_to_23dof.py:39-46: dofs 19:22 and 26:29, i.e. pose_aa
+    joints 20..22 and 27..29), each time-warped (linear resampling of pose_aa / root translation) to min_frames..max_frames
+    frames.  1024 clips are ~0.38 M frames = ~0.75 GB of packed records: the table streams from HBM, not from L2.
+    Returns {name: entry} in the joblib layout MotionLibRobot loads (deterministic in seed)."""
+    rng = np.random.RandomState(seed)
+    base = []
+    m = gold("motion_g1_29dof_clip.npz")
+    base.append((np.asarray(m["pose_aa"], np.float32), np.asarray(m["root_trans_offset"], np.float32), int(m["fps"])))
+    for nm in CLIPS23:
+        m = gold(f"motion_{nm}.npz")
+        p23 = np.asarray(m["pose_aa"], np.float32)
+        p29 = np.zeros((p23.shape[0], 33, 3), np.float32)
+        p29[:, 0:20] = p23[:, 0:20]
+        p29[:, 23:27] = p23[:, 20:24]
+        base.append((p29, np.asarray(m["root_trans_offset"], np.float32), int(m["fps"])))
+    out = {}
+    for i in range(n_clips):
+        pose, trans, fps = base[i % len(base)]
+        T0 = pose.shape[0]
+        T = int(rng.randint(min_frames, max_frames + 1))
+        x = np.linspace(0.0, T0 - 1.0, T, dtype=np.float64)
+        i0 = np.floor(x).astype(np.int64)
+        i1 = np.minimum(i0 + 1, T0 - 1)
+        w = (x - i0).astype(np.float32)
+        p = pose[i0] * (1.0 - w)[:, None, None] + pose[i1] * w[:, None, None]
+        t = trans[i0] * (1.0 - w)[:, None] + trans[i1] * w[:, None]
+        out[f"clip{i:04d}"] = dict(root_trans_offset=t.astype(np.float32), pose_aa=p.astype(np.float32), dof=None, root_rot=None, fps=fps)
+    return out
+
+
 MAIN_NOISE = dict(base_ang_vel=0.3, projected_gravity=0.2, dof_pos=0.01, dof_vel=1.0)  # config/obs/motion_tracking/main.yaml:81-99
 
 
@@ -74,12 +109,16 @@ def write_mjcf(tag, path):
     return path
 
 
-def product_cfg(tag, tmpdir, motion_names):
-    """motion_lib_cfg for pbhc_b200.MotionLibRobot built only from committed fixtures."""
+def product_cfg(tag, tmpdir, motion_names, motion_data=None):
+    """motion_lib_cfg for pbhc_b200.MotionLibRobot built only from committed fixtures.  motion_data: an in-memory
+    {name: entry} library (library29) instead of the named fixture clips."""
     import joblib
     from pbhc_b200.fk import AttrDict
     os.makedirs(tmpdir, exist_ok=True)
     write_mjcf(tag, os.path.join(tmpdir, f"g1_{tag}.xml"))
+    if motion_data is not None:
+        return AttrDict(asset=AttrDict(assetRoot=str(tmpdir), assetFileName=f"g1_{tag}.xml"), motion_file=motion_data,
+                        extend_config=[AttrDict(e) for e in EXTEND], step_dt=0.02)
     data = {}
     for nm in motion_names:
         m = motion_npz(nm)

@@ -151,24 +151,28 @@ class MotionLibRobot:
         radius, w = gaussian_weights()
         w_c = (C.c_double * len(w))(*w.tolist())
         L, st = _lib.lib(), _lib.stream_ptr(dev)
-        fps_l, dt_l, len_l = [], [], []
-        row = 0
-        for c, T in zip(clips, nf):
-            dt = 1 / c["fps"]
-            pose = torch.as_tensor(np.ascontiguousarray(c["pose_aa"][:, :J]), dtype=torch.float32).to(dev)
-            trans = torch.as_tensor(np.ascontiguousarray(c["trans"]), dtype=torch.float32).to(dev)
-            pos, _, quat = hb.fk(pose, trans, want_mat=False, want_quat=True, exact=True)
-            contact = None
-            if Cm:
-                contact = torch.as_tensor(np.ascontiguousarray(c["contact"]), dtype=torch.float32).to(dev)
-            scratch = torch.empty(T, J, 6, device=dev, dtype=torch.float32)
-            _lib.check(L.pbhc_clip_prepare(_lib.ptr(pos), _lib.ptr(quat), _lib.ptr(pose), _lib.ptr(contact), T, J, Jb, D,
-                                           Cm, dt, w_c, radius, _lib.ptr(scratch), records[row:row + T].data_ptr(), stride, st))
-            fps = int(1 / dt)  # torch_humanoid_batch.py:225
-            fps_l.append(fps)
-            dt_l.append(1.0 / fps)
-            len_l.append(1.0 / fps * (T - 1))
-            row += T
+        # every frame of every clip in ONE host->device copy, ONE FK launch and ONE velocity / pack launch pair
+        # (pbhc_clips_prepare); a 1024-clip library used to cost ~5000 tiny launches and copies
+        pose_h = np.concatenate([np.asarray(c["pose_aa"][:, :J], dtype=np.float32) for c in clips], axis=0)
+        trans_h = np.concatenate([np.asarray(c["trans"], dtype=np.float32) for c in clips], axis=0)
+        pose = torch.from_numpy(np.ascontiguousarray(pose_h)).to(dev)
+        trans = torch.from_numpy(np.ascontiguousarray(trans_h)).to(dev)
+        contact = None
+        if Cm:
+            contact = torch.from_numpy(np.ascontiguousarray(np.concatenate([np.asarray(c["contact"], dtype=np.float32) for c in clips], axis=0))).to(dev)
+        fps_l = [int(1 / (1 / c["fps"])) for c in clips]  # torch_humanoid_batch.py:225
+        dt_l = [1.0 / f for f in fps_l]
+        len_l = [1.0 / f * (T - 1) for f, T in zip(fps_l, nf)]
+        starts_h = np.concatenate([[0], np.cumsum(nf)[:-1]]).astype(np.int64)
+        clip_of_frame = torch.from_numpy(np.repeat(np.arange(len(nf), dtype=np.int32), nf)).to(dev)
+        clip_start = torch.from_numpy(starts_h).to(dev)
+        clip_frames = torch.tensor(nf, dtype=torch.int32, device=dev)
+        clip_dt_prep = torch.tensor([1 / c["fps"] for c in clips], dtype=torch.float32, device=dev)  # the dt fk_batch is called with
+        pos, _, quat = hb.fk(pose, trans, want_mat=False, want_quat=True, exact=True)
+        scratch = torch.empty(total, J, 6, device=dev, dtype=torch.float32)
+        _lib.check(L.pbhc_clips_prepare(_lib.ptr(pos), _lib.ptr(quat), _lib.ptr(pose), _lib.ptr(contact), total, clip_of_frame.data_ptr(),
+                                        clip_start.data_ptr(), clip_frames.data_ptr(), clip_dt_prep.data_ptr(), J, Jb, D, Cm, w_c, radius,
+                                        _lib.ptr(scratch), records.data_ptr(), stride, st))
         self._records = records
         self._rec_stride = stride
         self._clip_num_frames = torch.tensor(nf, dtype=torch.int32, device=dev)

@@ -45,15 +45,22 @@ def fk_bytes(J):
 class Workload:
     """Everything one rank needs to run env steps on `device` for `n_envs` environments."""
 
-    def __init__(self, n_envs, device, tmpdir, seed=0, case=CASE, clip=CLIP, noise=None):
-        from .fixtures import CLIPS29
+    def __init__(self, n_envs, device, tmpdir, seed=0, case=CASE, clip=CLIP, noise=None, library_clips=0):
+        """library_clips > 0 (config C only): the SURVEY 8d motion library of that many 29-DoF clips (fixtures.library29)
+        instead of the 3-clip one, so that the table is served from HBM."""
+        from .fixtures import CLIPS29, library29
         from .motion_lib import MotionLibRobot
         from .tracking_step import TrackingStep
         self.N, self.device = int(n_envs), torch.device(device)
         self.spec = spec = TrackSpec.from_config(env_config(case, noise))
         self.tag = "29" if spec.general else "23"
         self.clips = list(CLIPS29) if spec.general else [clip]
-        self.lib = MotionLibRobot(product_cfg(self.tag, tmpdir, self.clips), self.N, self.device)
+        self.library_clips = int(library_clips) if spec.general else 0
+        data = library29(self.library_clips, seed=0) if self.library_clips else None
+        self.library = data
+        if data is not None:
+            self.clips = list(data)
+        self.lib = MotionLibRobot(product_cfg(self.tag, tmpdir, self.clips, motion_data=data), self.N, self.device)
         self.lib.load_motions(random_sample=False)
         self.ts = TrackingStep(spec, self.lib, self.N, self.device, seed=seed)
         self.host = self.make_inputs(seed)

@@ -24,6 +24,14 @@ def oracle_clip(tag, name):
                        m.get("contact_mask"))
 
 
+def oracle_clips_of(wl):
+    """the oracle's clips of a Workload's motion library (fixture clips by name, or the in-memory library29 entries)"""
+    if getattr(wl, "library", None):
+        tree = oracle_tree(wl.tag)
+        return [O.load_clip(tree, e["pose_aa"], e["root_trans_offset"], int(e["fps"]), e.get("contact_mask")) for e in wl.library.values()]
+    return [oracle_clip(wl.tag, c) for c in wl.clips]
+
+
 def assert_close(a, b, rtol=RTOL, atol=ATOL, what=""):
     a = torch.as_tensor(np.asarray(a)).double()
     b = torch.as_tensor(np.asarray(b)).double()
@@ -65,7 +73,7 @@ def oracle_env_from_workload(wl):
     from oracle import pbhc_oracle_env as OE
     spec, h, N = wl.spec, wl.host, wl.N
     nc = len(wl.clips)
-    tab = O.MotionTable([oracle_clip(wl.tag, c) for c in wl.clips], spec.Jb, motion_to_clip=[i % nc for i in range(N)])
+    tab = O.MotionTable(oracle_clips_of(wl), spec.Jb, motion_to_clip=[i % nc for i in range(N)])
     S = OE.new_state(spec, N, env_origins=h["env_origins"].clone())
     S["motion_ids"] = h["motion_ids"].clone()
     for k in ("motion_len", "motion_start_times", "episode_length_buf", "kp_scale", "kd_scale", "last_actions", "last_dof_vel",
@@ -80,8 +88,8 @@ def check_workload_step_against_oracle(wl, n_steps=2, seed=5):
     injected into both) and compares observations, rewards, masks and per-env state."""
     from oracle import pbhc_oracle_env as OE
     spec, ts, N = wl.spec, wl.ts, wl.N
-    install_exact_table(wl.lib, [oracle_clip(wl.tag, c) for c in wl.clips])
     tab, S, inp = oracle_env_from_workload(wl)
+    install_exact_table(wl.lib, tab.clips)
     gen = torch.Generator().manual_seed(seed)
     dev = wl.device
     for step in range(n_steps):

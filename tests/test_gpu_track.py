@@ -157,6 +157,18 @@ def test_workload_step_vs_oracle_general_tracking(n_envs, tmp_path):
         assert n_reset > 0
 
 
+def test_workload_step_vs_oracle_general_tracking_large_library(tmp_path):
+    """config C on the SURVEY 8d style library (fixtures.library29: the 29-DoF clip + the zero-padded, time-warped 23-DoF
+    clips; 96 clips here so that the CPU oracle builds it in seconds - bench.py runs 1024): per-env motion ids over all
+    clips, the table built by ONE batched FK + pbhc_clips_prepare launch"""
+    from pbhc_b200.workload import Workload, CASE_C
+    from tests._util import check_workload_step_against_oracle
+    wl = Workload(4096, DEV, str(tmp_path), seed=6, case=CASE_C, library_clips=96)
+    assert wl.lib._desc.num_clips == 96
+    n_reset = check_workload_step_against_oracle(wl, n_steps=2)
+    assert n_reset > 0
+
+
 def test_host_step_chunked_pipeline_equals_single_launch(tmp_path):
     """HostStep (host buffers, 5 ragged env chunks on 3 streams) gives bit-identical per-env results to one launch;
     in-kernel reset draws are keyed by the global env id, so they do not depend on the chunking either."""
