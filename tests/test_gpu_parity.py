@@ -25,7 +25,7 @@ def _lib_with(tag, names, tmp_path, n):
     return ml
 
 
-from tests._util import install_exact_table as _install_exact_table  # noqa: E402
+from tests._util import install_exact_table as _install_exact_table, SLERP_FLIP  # noqa: E402
 
 
 @pytest.mark.parametrize("exact", [False, True])
@@ -91,14 +91,20 @@ def test_clip_prepare_matches_reference_on_identical_fk(tag, name, tmp_path):
 
 @pytest.mark.parametrize("tag,name", [("23", "Horse-stance_pose"), ("29", "g1_29dof_clip")])
 def test_table_built_on_gpu_matches_reference(tag, name, tmp_path):
-    """End to end (GPU FK -> velocities -> table).  Positions/rotations/dofs: strict.  The reference derives
-    velocities from differences of fp32 FK outputs times fps, and angular velocity from acos(2w^2-1) of a
-    near-identity quaternion - both amplify the last-ulp FK differences, so these two compare at the
-    conditioning of the reference's own algorithm (documented in DESIGN.md)."""
+    """End to end (GPU FK -> velocities -> table), the table the PRODUCT builds.  Positions / rotations / dofs / dof
+    velocities: the north_star bar.  Body velocities are differences of fp32 FK positions times fps, angular velocities are
+    acos(2 w^2 - 1) of a near-identity quaternion times fps: both amplify the last-ulp differences between CUDA's and the
+    reference's sin / cos (FK cannot be bit-identical), so they are held to what tools/table_error.py measures
+    (profiles/r02_table_error.json: vel max 3.8e-6 abs; ang vel max 3.9e-3 / p99 8.5e-4 abs on the near-static horse
+    stance, where 1 ulp of w moves the angle by ~10 %, max 4.8e-4 on the 29-DoF clip) with a 2x margin - see DESIGN.md."""
     ml = _lib_with(tag, [name], tmp_path, 2)
     g = gold(f"ref_table_{name}.npz")
     assert ml._clip_num_frames.tolist() == [int(g["num_frames"][0])]
-    _check_records(ml._records.cpu(), g, ml._dims, dict(atol=1e-4, rtol=1e-4), dict(atol=2e-2, rtol=5e-2))
+    rec = ml._records.cpu()
+    _check_records(rec, g, ml._dims, dict(atol=8e-6, rtol=1e-5), dict(atol=8e-3, rtol=0.0))
+    J, T = ml._dims[0], rec.shape[0]
+    ang_err = (rec[:, 10 * J:13 * J].reshape(T, J, 3) - torch.from_numpy(g["gavs_t"])).abs().flatten()
+    assert torch.quantile(ang_err, 0.99) < 2e-3 and torch.quantile(ang_err, 0.5) < 5e-5
     assert np.array_equal(ml._motion_lengths.cpu().numpy()[:1], g["lengths"][:1])
     assert np.array_equal(ml._motion_dt.cpu().numpy()[:1], g["dt"][:1])
 
@@ -125,6 +131,27 @@ def test_lookup_matches_reference_golden(case, tag, name, tmp_path):
     assert torch.equal(out["_f0l"].cpu(), o["_f0l"] - starts + ref_f0)
     assert torch.equal(out["_f1l"].cpu(), o["_f1l"] - starts)
     assert torch.equal(out["_blend"].cpu(), o["_blend"])
+
+
+# what the outputs of K1 / K3 inherit from the product-built table (measured, see test_table_built_on_gpu_matches_reference)
+PRODUCT_TABLE_TOL = dict(vel=dict(atol=8e-6, rtol=1e-5), ang=dict(atol=8e-3, rtol=0.0))
+
+
+@pytest.mark.parametrize("case,tag,name", [("23_1d", "23", "Horse-stance_pose"), ("23_2d", "23", "Horse-stance_pose"),
+                                           ("29_1d", "29", "g1_29dof_clip")])
+def test_lookup_on_product_built_table_matches_reference_golden(case, tag, name, tmp_path):
+    """K1 on the table load_motions builds on the device (no oracle table installed) against the reference's
+    get_motion_state outputs: frame indices / blend bit-exact, positions / rotations / dofs at the north_star bar,
+    velocities at the measured conditioning of the reference's own table construction.  A slerp that takes a different
+    branch than the reference's (|sin| < 1e-3, |cos| >= 1: a last-ulp table difference can flip it) is only accepted
+    because both branches agree within the bar for such frame pairs - asserted by the rotation comparison itself."""
+    g = gold(f"ref_lookup_{case}.npz")
+    ml = _lib_with(tag, [name], tmp_path, 3)
+    ids, t, off = (torch.from_numpy(g[k]).to(DEV) for k in ("motion_ids", "motion_times", "offset"))
+    out = ml.get_motion_state(ids, t, off, with_indices=True)
+    for k in KEYS + (["contact_mask"] if "out_contact_mask" in g else []):
+        tol = PRODUCT_TABLE_TOL["ang"] if "ang_vel" in k else PRODUCT_TABLE_TOL["vel"] if ("vel" in k and k != "dof_vel") else {}
+        assert_close(out[k].cpu(), g["out_" + k], what=k, allow=SLERP_FLIP if "rot" in k else None, **tol)
 
 
 def test_lookup_multiclip_large_vs_oracle(tmp_path):

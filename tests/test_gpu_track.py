@@ -12,12 +12,15 @@ from oracle import pbhc_oracle as O, pbhc_oracle_env as OE
 from pbhc_b200 import synth
 from pbhc_b200 import _lib
 from pbhc_b200.spec import TrackSpec, SIGMA_IDS
-from tests._util import gold, oracle_clip, product_cfg, assert_close
+from tests._util import gold, oracle_clip, product_cfg, assert_close, SLERP_FLIP
 
 pytestmark = pytest.mark.gpu
 DEV = "cuda:0"
 INJECT = ("motion_start_times", "kp_scale", "kd_scale", "rfi_lim_scale", "rao_scale", "action_delay_idx")
 NAMES = ["Horse-stance_pose"]
+# observation keys that contain reference (table) velocities
+VEL_OBS = {"next_step_ref_motion", "future_motion_base_lin_vel", "future_motion_base_yaw_vel", "local_ref_rigid_body_vel",
+           "global_ref_rigid_body_vel", "dif_joint_velocities"}
 
 
 def make_step(spec, N, tmp_path, clip_names=None, exact=True):
@@ -59,14 +62,16 @@ def load_state(ts, S, spec):
         ts._episode_sums[:, i] = t("epsum_" + name)
 
 
-def compare_state(ts, G, spec, tag):
-    """G: dict of expected (reference / oracle) post-step buffers."""
+def compare_state(ts, G, spec, tag, loose=None):
+    """G: dict of expected (reference / oracle) post-step buffers.  loose: see _run_golden_case."""
+    rew_tol = (loose or {}).get("rew", {})
+    sig_tol = (loose or {}).get("sigma", 1e-6)
     e = lambda k: np.asarray(G[k])
     assert np.array_equal(ts.episode_length_buf.cpu().numpy(), e("episode_length_buf")), tag
     assert np.array_equal(ts.reset_buf.cpu().numpy(), e("reset_buf")), tag
     assert np.array_equal(ts.time_out_buf.cpu().numpy(), e("time_out_buf")), tag
     assert np.array_equal(ts.action_delay_idx.cpu().numpy(), e("action_delay_idx")), tag
-    assert_close(ts.rew_buf.cpu(), e("rew_buf"), what=f"{tag} rew_buf")
+    assert_close(ts.rew_buf.cpu(), e("rew_buf"), what=f"{tag} rew_buf", **rew_tol)
     for name, mine in (("motion_start_times", ts.motion_start_times), ("motion_len", ts.motion_len),
                        ("feet_air_time", ts.feet_air_time), ("end_time_ratio_buf", ts.end_time_ratio_buf),
                        ("last_actions", ts.last_actions), ("last_dof_pos", ts.last_dof_pos), ("last_dof_vel", ts.last_dof_vel),
@@ -77,26 +82,27 @@ def compare_state(ts, G, spec, tag):
     for k in spec.hist_keys:
         assert_close(ts.history_handler.query(k).cpu(), e("hist_" + k), what=f"{tag} hist_{k}")
     for name, v in ts.episode_sums.items():
-        assert_close(v.cpu(), e("epsum_" + name), what=f"{tag} epsum_{name}")
+        assert_close(v.cpu(), e("epsum_" + name), what=f"{tag} epsum_{name}", **rew_tol)
     sc = ts.scalars.cpu().numpy()
     for name, i in SIGMA_IDS.items():
         if "sigma_" + name not in G:
             continue
-        assert abs(sc[_lib.S_SIGMA + i] - float(G["sigma_" + name])) <= 1e-6 * abs(float(G["sigma_" + name])), (tag, name)
+        assert abs(sc[_lib.S_SIGMA + i] - float(G["sigma_" + name])) <= sig_tol * abs(float(G["sigma_" + name])), (tag, name)
         if "ema_" + name in G:
-            assert abs(sc[_lib.S_EMA + i] - float(G["ema_" + name])) <= 1e-6 * abs(float(G["ema_" + name])), (tag, name)
+            assert abs(sc[_lib.S_EMA + i] - float(G["ema_" + name])) <= sig_tol * abs(float(G["ema_" + name])), (tag, name)
     for name, i in (("average_episode_length", _lib.S_AVG_EPL), ("reward_penalty_scale", _lib.S_PENALTY),
                     ("motion_far_threshold", _lib.S_FAR_THR), ("soft_dof_pos", _lib.S_SOFT_DOF_POS),
                     ("soft_dof_vel", _lib.S_SOFT_DOF_VEL), ("soft_torque", _lib.S_SOFT_TORQUE)):
         assert abs(sc[i] - float(G[name])) <= 1e-6 * abs(float(G[name])) + 1e-12, (tag, name, sc[i], float(G[name]))
 
 
-@pytest.mark.parametrize("case", ["mt23_main", "mt23_bench", "gt29_teacher", "gt29_student"])
-def test_track_step_matches_reference_golden(case, tmp_path):
+def _run_golden_case(case, tmp_path, exact, loose=None):
+    """loose: dict of looser assert_close tolerances for the quantities that inherit the velocity error of a
+    product-built table (None: the north_star bar everywhere)."""
     g = gold(f"ref_env_{case}.npz")
     spec = TrackSpec.from_config(json.loads(str(g["meta_config_json"])))
     N = int(g["meta_n_envs"])
-    ts, ml = make_step(spec, N, tmp_path)
+    ts, ml = make_step(spec, N, tmp_path, exact=exact)
     sim = make_sim(N, spec.Jb, spec.D, spec.L)
     init = {k[5:]: g[k] for k in g if k.startswith("init_")}
     load_state(ts, init, spec)
@@ -120,18 +126,42 @@ def test_track_step_matches_reference_golden(case, tmp_path):
         torch.cuda.synchronize()
         tag = f"{case} step {step}"
         for name, v in obs.items():
-            assert_close(v.cpu(), g[p + "obs_" + name], what=f"{tag} obs {name}")
+            otol = {}
+            if loose:  # columns that show reference velocities inherit the table's velocity error, the rest its position error
+                at = torch.full((v.shape[1],), loose["obs"]["atol"], dtype=torch.float64)
+                for seg in spec.obs_groups[name]["segs"]:
+                    if seg["key"] in VEL_OBS:
+                        at[seg["off"]:seg["off"] + seg["dim"] * (seg.get("len") or 1)] = loose["state"]["atol"]
+                otol = dict(atol=at, rtol=loose["obs"]["rtol"])
+            assert_close(v.cpu(), g[p + "obs_" + name], what=f"{tag} obs {name}", **otol)
         G = {k[len(p) + 4:]: g[k] for k in g if k.startswith(p + "out_")}
-        compare_state(ts, G, spec, tag)
+        compare_state(ts, G, spec, tag, loose)
         assert_close(actions.cpu(), g[p + "out_actions"], what=f"{tag} actions")
         assert_close(sim.dof_state.cpu(), g[p + "out_dof_state"], what=f"{tag} dof_state")
-        assert_close(sim.all_root_states.cpu(), g[p + "out_root_state"], what=f"{tag} root_state")
+        assert_close(sim.all_root_states.cpu(), g[p + "out_root_state"], what=f"{tag} root_state", **(loose or {}).get("state", {}))
         assert_close(extras["ref_body_pos_extend"].cpu(), g[p + "extras_ref_body_pos_extend"], what=f"{tag} ref pos")
-        assert_close(extras["ref_body_rot_extend"].cpu(), g[p + "extras_ref_body_rot_extend"], what=f"{tag} ref rot")
+        assert_close(extras["ref_body_rot_extend"].cpu(), g[p + "extras_ref_body_rot_extend"], what=f"{tag} ref rot", allow=SLERP_FLIP if loose else None)
         log = ts.log_dict
         for k in g:
             if k.startswith(p + "log_") and k[len(p) + 4:] in log:
-                assert_close(log[k[len(p) + 4:]].cpu(), np.float32(g[k]), rtol=1e-5, atol=1e-6, what=f"{tag} log {k}")
+                assert_close(log[k[len(p) + 4:]].cpu(), np.float32(g[k]), what=f"{tag} log {k}", **(loose or {}).get("log", dict(rtol=1e-5, atol=1e-6)))
+
+
+@pytest.mark.parametrize("case", ["mt23_main", "mt23_bench", "gt29_teacher", "gt29_student"])
+def test_track_step_matches_reference_golden(case, tmp_path):
+    _run_golden_case(case, tmp_path, exact=True)
+
+
+@pytest.mark.parametrize("case", ["mt23_main", "gt29_teacher"])
+def test_track_step_on_product_built_table_matches_reference_golden(case, tmp_path):
+    """the fused step on the motion table load_motions builds on the device (no oracle table installed) against the
+    goldens of the unmodified reference env: masks, episode lengths and frame-dependent integers bit-exact; observations
+    at the north_star bar (none of these configs observes reference velocities); the quantities that contain the table's
+    body / angular velocities - the velocity rewards and their episode sums, adaptive sigma, root / dof state written at
+    resets - at the error measured for the table (tools/table_error.py, profiles/r02_table_error.json)."""
+    loose = dict(rew=dict(atol=5e-5, rtol=1e-4), state=dict(atol=8e-3, rtol=0.0), sigma=2e-3, log=dict(rtol=1e-4, atol=1e-5),
+                 obs=dict(atol=5e-6, rtol=1e-5))
+    _run_golden_case(case, tmp_path, exact=False, loose=loose)
 
 
 @pytest.mark.parametrize("n_envs", [1, 37, 4096])
