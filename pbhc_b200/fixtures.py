@@ -65,6 +65,17 @@ def library29(n_clips=1024, seed=0, min_frames=150, max_frames=600):
     return out
 
 
+def clips_of_case(cfg):
+    """(robot tag, fixture clip names) of a golden env fixture, from the motion file name recorded in its config:
+    "Horse-stance_pose", "clips29" (the 3-clip library CLIPS29), or a single named fixture clip ("edge23", "edge29")."""
+    general = cfg.get("env_class") == "general_tracking"
+    name = cfg["robot"]["motion"]["motion_file"]
+    tag = "29" if general else "23"
+    if name == "clips29":
+        return tag, list(CLIPS29)
+    return tag, [name]
+
+
 MAIN_NOISE = dict(base_ang_vel=0.3, projected_gravity=0.2, dof_pos=0.01, dof_vel=1.0)  # config/obs/motion_tracking/main.yaml:81-99
 
 

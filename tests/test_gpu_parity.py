@@ -110,7 +110,10 @@ def test_table_built_on_gpu_matches_reference(tag, name, tmp_path):
 
 
 @pytest.mark.parametrize("case,tag,name", [("23_1d", "23", "Horse-stance_pose"), ("23_2d", "23", "Horse-stance_pose"),
-                                           ("29_1d", "29", "g1_29dof_clip")])
+                                           ("29_1d", "29", "g1_29dof_clip"),
+                                           # slerp edge cases (tools/make_golden_edge.py): identical frames, sign-flipped frame
+                                           # quaternions, sin(half angle) straddling 1e-3 - every frame pair x 5 blends
+                                           ("edge23", "23", "edge23"), ("edge29", "29", "edge29")])
 def test_lookup_matches_reference_golden(case, tag, name, tmp_path):
     g = gold(f"ref_lookup_{case}.npz")
     ml = _lib_with(tag, [name], tmp_path, 3)
@@ -124,7 +127,7 @@ def test_lookup_matches_reference_golden(case, tag, name, tmp_path):
     T = int(ml._clip_num_frames[0])
     ref_f0 = torch.from_numpy(gold(f"ref_lookup_{case}.npz")["motion_ids"]) * 0  # shape helper
     c = oracle_clip(tag, name)
-    tab = O.MotionTable([c] * 3, oracle_tree(tag).num_bodies)
+    tab = O.MotionTable([c] * 3, oracle_tree(tag).num_bodies)  # (motion ids of the goldens are < 3)
     o = O.get_motion_state(tab, torch.from_numpy(g["motion_ids"]), torch.from_numpy(g["motion_times"]),
                            torch.from_numpy(g["offset"]))
     starts = tab.starts[torch.from_numpy(g["motion_ids"])]

@@ -102,7 +102,8 @@ def _run_golden_case(case, tmp_path, exact, loose=None):
     g = gold(f"ref_env_{case}.npz")
     spec = TrackSpec.from_config(json.loads(str(g["meta_config_json"])))
     N = int(g["meta_n_envs"])
-    ts, ml = make_step(spec, N, tmp_path, exact=exact)
+    from pbhc_b200.fixtures import clips_of_case
+    ts, ml = make_step(spec, N, tmp_path, clip_names=clips_of_case(json.loads(str(g["meta_config_json"])))[1], exact=exact)
     sim = make_sim(N, spec.Jb, spec.D, spec.L)
     init = {k[5:]: g[k] for k in g if k.startswith("init_")}
     load_state(ts, init, spec)
@@ -147,8 +148,11 @@ def _run_golden_case(case, tmp_path, exact, loose=None):
                 assert_close(log[k[len(p) + 4:]].cpu(), np.float32(g[k]), what=f"{tag} log {k}", **(loose or {}).get("log", dict(rtol=1e-5, atol=1e-6)))
 
 
-@pytest.mark.parametrize("case", ["mt23_main", "mt23_bench", "gt29_teacher", "gt29_student"])
+@pytest.mark.parametrize("case", ["mt23_main", "mt23_bench", "gt29_teacher", "gt29_student", "mt23_edge", "gt29_edge"])
 def test_track_step_matches_reference_golden(case, tmp_path):
+    """*_edge: the synthetic clips of tools/make_golden_edge.py - envs sitting on identical frames, sign-flipped frame
+    quaternions and sin(half angle) on both sides of slerp's 1e-3; in gt29_edge also body rotations within 0 .. 40 urad of
+    the reference's, i.e. quat_to_angle_axis on both sides of its 1e-5 threshold (rotations.py:185-232)"""
     _run_golden_case(case, tmp_path, exact=True)
 
 

@@ -18,12 +18,10 @@ def load_case(name):
     g = gold(f"ref_env_{name}.npz")
     spec = TrackSpec.from_config(json.loads(str(g["meta_config_json"])))
     N = int(g["meta_n_envs"])
-    if spec.general:
-        from pbhc_b200.fixtures import CLIPS29
-        clips = [oracle_clip("29", nm) for nm in CLIPS29]
-        tab = O.MotionTable(clips, spec.Jb, motion_to_clip=[i % len(clips) for i in range(N)])  # load_motions(random_sample=False)
-    else:
-        tab = O.MotionTable([oracle_clip("23", "Horse-stance_pose")], spec.Jb, motion_to_clip=[0] * N)
+    from pbhc_b200.fixtures import clips_of_case
+    tag, names = clips_of_case(json.loads(str(g["meta_config_json"])))
+    clips = [oracle_clip(tag, nm) for nm in names]
+    tab = O.MotionTable(clips, spec.Jb, motion_to_clip=[i % len(clips) for i in range(N)])  # load_motions(random_sample=False)
     return g, spec, N, tab
 
 
@@ -38,7 +36,7 @@ def state_from(g, prefix, spec):
     return S
 
 
-@pytest.mark.parametrize("case", ["mt23_main", "mt23_bench", "gt29_teacher", "gt29_student"])
+@pytest.mark.parametrize("case", ["mt23_main", "mt23_bench", "gt29_teacher", "gt29_student", "mt23_edge", "gt29_edge"])
 def test_env_step_oracle_matches_reference(case):
     g, spec, N, tab = load_case(case)
     S = state_from(g, "init_", spec)

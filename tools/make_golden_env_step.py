@@ -63,17 +63,20 @@ def _library29(tmp="/tmp/pbhc_golden"):
     return path
 
 
-def run_case(name, n_envs, n_steps, obs, seed, overrides=None, general=False):
+def run_case(name, n_envs, n_steps, obs, seed, overrides=None, general=False, motion_file=None, motion_name=None, start_times=None, tweak=None):
+    """motion_file / motion_name: a joblib motion file instead of the default clip(s) and the fixture name recorded for it;
+    start_times(env) -> tensor: motion start times instead of the seeded spread; tweak(step, body, root, dof, cf, ref): edits
+    the synthetic simulator state in place (edge-case fixtures, tools/make_golden_edge.py)."""
     ov = {"domain_rand.push_robots": False}
     ov.update(overrides or {})
     if general:
-        cfg = E.build_config(n_envs, _library29(), robot="g1/g1_29dof_general", rewards="motion_tracking/general_main", obs=obs,
+        cfg = E.build_config(n_envs, motion_file or _library29(), robot="g1/g1_29dof_general", rewards="motion_tracking/general_main", obs=obs,
                              env="general_tracking", overrides=ov)
     else:
-        cfg = E.build_config(n_envs, R.example_motion("Horse-stance_pose"), obs=obs, overrides=ov)
+        cfg = E.build_config(n_envs, motion_file or R.example_motion("Horse-stance_pose"), obs=obs, overrides=ov)
     import copy, json
     cj = copy.deepcopy(cfg)  # before the env mutates it (reward_scales *= dt, adaptive sigmas)
-    cj["robot"]["motion"]["motion_file"] = "clips29" if general else "Horse-stance_pose"
+    cj["robot"]["motion"]["motion_file"] = motion_name or ("clips29" if general else "Horse-stance_pose")
     cj["robot"]["motion"]["asset"]["assetRoot"] = "description/robots/g1/"
     cj["env_class"] = "general_tracking" if general else "motion_tracking"
     cfg_json = json.dumps(cj)
@@ -86,6 +89,9 @@ def run_case(name, n_envs, n_steps, obs, seed, overrides=None, general=False):
     env.motion_start_times[:3] = env.motion_len[:3] - torch.tensor([0.01, 0.03, 0.05])
     env.episode_length_buf[:] = torch.randint(0, 50, (N,), generator=gen)
     env.episode_length_buf[:3] = 0
+    if start_times is not None:
+        env.motion_start_times[:] = start_times(env)
+        env.episode_length_buf[:] = 0
     # privileged DR tensors that the critic observes
     sim._base_com_bias[:] = (torch.rand(N, 3, generator=gen) - 0.5) * 0.1
     sim._link_mass_scale[:] = 0.9 + 0.2 * torch.rand(N, sim._link_mass_scale.shape[1], generator=gen)
@@ -107,6 +113,8 @@ def run_case(name, n_envs, n_steps, obs, seed, overrides=None, general=False):
         t = (env.episode_length_buf + 2) * env.dt + env.motion_start_times
         ref = env._motion_lib.get_motion_state(env.motion_ids, t, offset=env.env_origins)
         body, root, dof, cf = synth.synth_sim_state(ref, Jb, gen, feet=tuple(int(i) for i in env.feet_indices))
+        if tweak is not None:
+            tweak(step, body, root, dof, cf, ref)
         sim.set_state(body, root, dof, cf)
         p = f"s{step}_"
         out.update({p + "in_body_state": _np(body), p + "in_root_state": _np(root), p + "in_dof_state": _np(dof),
