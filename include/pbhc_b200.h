@@ -16,7 +16,7 @@
 extern "C" {
 #endif
 
-#define PBHC_ABI_VERSION 4
+#define PBHC_ABI_VERSION 5
 #define PBHC_OK 0
 #define PBHC_E_BADARG (-1)
 #define PBHC_E_ALIGN (-2)
@@ -372,6 +372,13 @@ typedef struct {
   const float* inject_start_times; const float* inject_kp; const float* inject_kd; const float* inject_rfi;
   const float* inject_rao; const int64_t* inject_delay;
   int64_t env_offset;           /* global id of env 0 of this call (keys the in-kernel RNG when a step is launched in chunks) */
+  /* ABI 5 */
+  int64_t* last_episode_length_buf; /* [N] nullable: episode length (after this step's increment) of envs reset this step, i.e.
+                                     * last_episode_length_buf[env_ids] of extras["episode"]["end_epis_length"] (legged_robot_base.py:302,515);
+                                     * rows of envs that did not reset are untouched */
+  const uint8_t* force_reset;   /* [N] nullable: nonzero = reset this env now whatever its termination says - what
+                                 * resample_motion's reset_envs_idx(arange(num_envs)) does (motion_tracking.py:385-389).  A forced reset
+                                 * is not a time-out and earns no termination reward; reset_buf reports it. */
 } PbhcTrackIO;
 
 /* number of rows `partials` must have */
@@ -389,6 +396,13 @@ int pbhc_track_step(const PbhcTrackCfg* cfg, const PbhcTableDesc* tab, const Pbh
 /* advances `scalars` from `acc` (adaptive sigma, average episode length, curricula, log values);
  * call after pbhc_track_step (and after all-reducing acc when envs are sharded over ranks) */
 int pbhc_track_finalize(const PbhcTrackCfg* cfg, const double* acc, double* scalars, void* stream);
+
+/* ---- env ids of a reset mask: `env_ids = self.reset_buf.nonzero(as_tuple=False).flatten()` and the need_to_refresh_envs
+ * twin (legged_robot_base.py:311,315) without a host round trip per mask: ids [n] int32 receives the indices of the nonzero
+ * flags in ascending order, *count (device int32) their number; entries of ids past *count are untouched.
+ * scratch: device int32[pbhc_compact_scratch_ints(n)].  Two launches, no atomics: the order is deterministic. */
+int64_t pbhc_compact_scratch_ints(int64_t n);
+int pbhc_compact_ids(const int64_t* flags, int64_t n, int32_t* ids, int32_t* count, int32_t* scratch, void* stream);
 
 /* ---- actuation half of the env step: LeggedRobotBase._pre_physics_step
  * (envs/legged_base_task/legged_robot_base.py:268-286) and _compute_torques (:795-838). */

@@ -915,7 +915,8 @@ __global__ void __launch_bounds__(kTW * 32, kGeneral ? 2 : F_BPS) track_kernel(c
       const bool time_out = t_out || t_end;
       bool t_bodyz = false;
       if constexpr (kGeneral) t_bodyz = c.term_body_z && __any_sync(0xffffffffu, bodyz);
-      const bool reset = t_grav || t_far || time_out || t_refz || t_ori || t_bodyz;
+      const bool terminated = t_grav || t_far || time_out || t_refz || t_ori || t_bodyz;
+      const bool reset = terminated || (io.force_reset != nullptr && io.force_reset[n] != 0);  // forced: resample_motion (motion_tracking.py:385-389)
       if (lane == 0) {
         rv[V_SIGMA_ERR + G_MAX_JOINT] = max_dja;
         rv[V_T_GRAV] = t_grav; rv[V_T_FAR] = t_far; rv[V_T_OUT] = time_out; rv[V_T_END] = t_end;
@@ -939,7 +940,7 @@ __global__ void __launch_bounds__(kTW * 32, kGeneral ? 2 : F_BPS) track_kernel(c
         }
         rew = r * T.r_scale[lane] * T.r_pen[lane];
       }
-      const float term_rew = c.has_termination ? ((reset && !time_out) ? 1.0f : 0.0f) * c.termination_scale : 0.0f;
+      const float term_rew = c.has_termination ? ((terminated && !time_out) ? 1.0f : 0.0f) * c.termination_scale : 0.0f;
       {
         const int R = c.n_rewards;
         float* es = io.episode_sums + n * c.n_episode_sums;
@@ -969,6 +970,7 @@ __global__ void __launch_bounds__(kTW * 32, kGeneral ? 2 : F_BPS) track_kernel(c
       if (reset) {
         const Rng rng = {make_uint2((uint32_t)c.seed, (uint32_t)(c.seed >> 32)), (uint32_t)(n + io.env_offset), (uint32_t)((uint64_t)(n + io.env_offset) >> 32), push_count};
         if (ld) io.actions[n * D + lane] = 0.0f;
+        if (lane == 0 && io.last_episode_length_buf) io.last_episode_length_buf[n] = last_ep;  // extras["episode"]["end_epis_length"], legged_robot_base.py:515
         air0 = 0.0f; air1 = 0.0f; contact0 = 0.0f; contact1 = 0.0f;
         if (c.hist_row > 0) {  // HistoryHandler.reset: zero the ring (and what the observation rows already took from it)
           for (int i = lane; i < c.hist_row; i += 32) io.hist[n * c.hist_row + i] = 0.0f;

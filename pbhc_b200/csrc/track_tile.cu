@@ -793,7 +793,8 @@ __device__ __forceinline__ void track_tile_body(const TileParams& P) {
       const bool t_out = ep > KC(max_episode_length);
       const bool t_end = KC(term_motion_end) && (xa(xm((float)ep, dt), start) > mlen);
       const bool time_out = t_out || t_end;
-      const bool reset = t_grav || t_far || time_out;
+      const bool terminated = t_grav || t_far || time_out;
+      const bool reset = terminated || (io.force_reset != nullptr && io.force_reset[n] != 0);  // forced: resample_motion (motion_tracking.py:385-389)
       if (lane == 0) {
         rve[V_T_GRAV] = t_grav; rve[V_T_FAR] = t_far; rve[V_T_OUT] = time_out; rve[V_T_END] = t_end;
         rve[V_RESET] = reset; rve[V_ONE] = 1.0f; rve[V_ALIVE] = 1.0f;
@@ -817,7 +818,7 @@ __device__ __forceinline__ void track_tile_body(const TileParams& P) {
           }
           rew = v * T.r_scale[lane] * T.r_pen[lane];
         }
-        const float term_rew = KC(has_termination) ? ((reset && !time_out) ? 1.0f : 0.0f) * KC(termination_scale) : 0.0f;
+        const float term_rew = KC(has_termination) ? ((terminated && !time_out) ? 1.0f : 0.0f) * KC(termination_scale) : 0.0f;
         float* q_rew = reinterpret_cast<float*>(smem + KC(q_rew));
         if (KC(use_vec_reward)) {
           float v = rew;
@@ -863,6 +864,7 @@ __device__ __forceinline__ void track_tile_body(const TileParams& P) {
         const bool ld = lane < D;
         const Rng rng = {make_uint2((uint32_t)c.seed, (uint32_t)(c.seed >> 32)), (uint32_t)(n + io.env_offset), (uint32_t)((uint64_t)(n + io.env_offset) >> 32), push_count};
         if (ld) io.actions[n * D + lane] = 0.0f;
+        if (lane == 0 && io.last_episode_length_buf) io.last_episode_length_buf[n] = last_ep;  // extras["episode"]["end_epis_length"], legged_robot_base.py:515
         air0 = 0.0f; air1 = 0.0f; contact0 = 0.0f; contact1 = 0.0f;
         // HistoryHandler.reset: zero the ring and what the observation rows already took from it
         for (int i = lane; i < H; i += 32) {

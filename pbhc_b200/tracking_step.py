@@ -97,6 +97,14 @@ class TrackingStep:
         self.acc = torch.zeros(_lib.ACC, device=dev, dtype=torch.float64)
         self.history_handler = _History(self)
         self.extras = {}
+        # boundary state of _post_physics_step (legged_robot_base.py:302, 311-319, 509-515)
+        self.last_episode_length_buf = torch.zeros(N, device=dev, dtype=torch.int64)
+        self._force_reset = torch.zeros(N, device=dev, dtype=torch.uint8)
+        self._force_pending = False
+        self.inject_next = None  # values for the reset draws of the next step() only (tests: the reference's own draws)
+        self._reset_ids = torch.zeros(N, device=dev, dtype=torch.int32)
+        self._reset_count = torch.zeros(1, device=dev, dtype=torch.int32)
+        self._compact_scratch = torch.zeros(max(int(self._L.pbhc_compact_scratch_ints(N)), 1), device=dev, dtype=torch.int32)
         self._build_cfg(seed)
         self._io = _lib.TrackIO()
         self._keep = None
@@ -299,6 +307,8 @@ class TrackingStep:
         io.time_out_buf = self.time_out_buf.data_ptr()
         io.ref_body_pos_extend, io.ref_body_rot_extend = p(self.ref_body_pos_extend), p(self.ref_body_rot_extend)
         io.last_episode_sums, io.partials, io.acc = p(self.last_episode_sums), p(self.partials), p(self.acc)
+        io.last_episode_length_buf = p(self.last_episode_length_buf)
+        io.force_reset = p(self._force_reset) if self._force_pending else None
         inj = inject or {}
         io.inject_start_times = p(inj.get("motion_start_times"))
         io.inject_kp, io.inject_kd = p(inj.get("kp_scale")), p(inj.get("kd_scale"))
@@ -335,12 +345,54 @@ class TrackingStep:
 
     def step(self, sim, actions, torques, env_origins, motion_ids, inject=None, group=None):
         """Returns (obs_buf_dict, rew_buf, reset_buf, extras) like LeggedRobotBase.step (see bind() for the inputs)."""
+        if inject is None and self.inject_next is not None:
+            inject, self.inject_next = self.inject_next, None
         self.bind(sim, actions, torques, env_origins, motion_ids, inject)
         self.launch()
+        if self._force_pending:  # the forced resets (resample_motion) are consumed by this launch
+            self._force_reset.zero_()
+            self._force_pending = False
         self.finalize(group)
         self.extras = {"time_outs": self.time_out_buf, "ref_body_pos_extend": self.ref_body_pos_extend,
                        "ref_body_rot_extend": self.ref_body_rot_extend, "to_log": None}
         return self.obs_buf_dict, self.rew_buf, self.reset_buf, self.extras
+
+    # ---- the rest of _post_physics_step's contract: env ids of the resets, extras["episode"], resample_motion -----------
+    @property
+    def need_to_refresh_envs(self):
+        """legged_robot_base.py:315: after step() exactly the envs of reset_buf wait for the simulator setters."""
+        return self.reset_buf != 0
+
+    def reset_env_ids(self):
+        """`self.reset_buf.nonzero(as_tuple=False).flatten()` (legged_robot_base.py:311) without leaving the device:
+        (ids int32 [N], count int32 [1]) - ids[:count] are the envs reset by the last step, ascending (pbhc_compact_ids)."""
+        _lib.check(self._L.pbhc_compact_ids(_lib.ptr(self.reset_buf), self.N, _lib.ptr(self._reset_ids), _lib.ptr(self._reset_count),
+                                            _lib.ptr(self._compact_scratch), _lib.stream_ptr(self.device)))
+        return self._reset_ids, self._reset_count
+
+    def reset_env_ids_host(self):
+        """The same as an int32 device tensor of exactly `count` ids, for setters that need len(env_ids) on the host
+        (simulator/isaacgym/isaacgym.py:642-660).  One 4-byte read-back - the only synchronisation of the step."""
+        ids, count = self.reset_env_ids()
+        return ids[:int(count.item())]
+
+    def episode_extras(self, env_ids):
+        """extras["episode"] of reset_envs_idx (legged_robot_base.py:508-515) for the envs reset by the last step:
+        rew_<name> = episode sums / max_episode_length_s, end_epis_length = last_episode_length_buf[env_ids]."""
+        idx = env_ids.long()
+        sums = self.last_episode_sums[idx] / self.spec.max_episode_length_s
+        ep = {"rew_" + n: sums[:, i] for i, n in enumerate(self._sum_names)}
+        ep["end_epis_length"] = self.last_episode_length_buf[idx]
+        return ep
+
+    def resample_motion(self, **load_kwargs):
+        """LeggedRobotMotionTracking.resample_motion (motion_tracking.py:385-389): a new draw of clips for the envs, then
+        every env is reset.  The reference resets inside _update_tasks_callback of the running step; here the reset of all
+        envs is part of the next step() (PbhcTrackIO.force_reset), which samples start times from the new clips."""
+        load_kwargs.setdefault("random_sample", True)
+        self.lib.load_motions(**load_kwargs)
+        self._force_reset.fill_(1)
+        self._force_pending = True
 
     # ---- chunked launches and the host-buffer pipeline --------------------------------------------------------
     def _row_bytes(self):
@@ -354,6 +406,7 @@ class TrackingStep:
                   last_dof_vel=D * 4, kp_scale=D * 4, kd_scale=D * 4, rfi_lim_scale=D * 4, rao_scale=D * 4, action_delay_idx=8,
                   hist=self.hist_row * 4, episode_sums=self.n_sums * 4, rew_buf=rew, reset_buf=8, time_out_buf=1,
                   ref_body_pos_extend=J * 12, ref_body_rot_extend=J * 16, last_episode_sums=self.n_sums * 4,
+                  last_episode_length_buf=8, force_reset=1,
                   inject_start_times=4, inject_kp=D * 4, inject_kd=D * 4, inject_rfi=D * 4, inject_rao=D * 4, inject_delay=8)
         return rb
 
