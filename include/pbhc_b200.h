@@ -404,6 +404,18 @@ int pbhc_track_finalize(const PbhcTrackCfg* cfg, const double* acc, double* scal
 int64_t pbhc_compact_scratch_ints(int64_t n);
 int pbhc_compact_ids(const int64_t* flags, int64_t n, int32_t* ids, int32_t* count, int32_t* scratch, void* stream);
 
+/* pbhc_compact_ids for callers that cannot allocate (CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc).  NO COUNTERPART IN THE REFERENCE.  Same inputs, outputs and
+ * results as pbhc_compact_ids, but the per-block counts live in a file-scope `static __device__` array of the library
+ * (16 KB, held by every GPU that loads the library until exit) instead of caller scratch; the call allocates nothing
+ * (no cudaMalloc / cudaFree / allocating library routine).  Limits: n <= PBHC_COMPACT_STATIC_MAX_N, else PBHC_E_RANGE.
+ * Every call on a device shares the one array (it keeps the last call's contents; nothing in it has to start at zero
+ * because the first pass overwrites every count the second reads): calls that overlap on the GPU - different streams
+ * without an ordering between them - race; serialise them or use pbhc_compact_ids.  The first call on a device looks up
+ * the array's address (cudaGetSymbolAddress) - make that call outside a stream capture. */
+#define PBHC_COMPACT_STATIC_MAX_N 16777216
+int pbhc_compact_ids_static(const int64_t* flags, int64_t n, int32_t* ids, int32_t* count, void* stream);
+
 /* ---- actuation half of the env step: LeggedRobotBase._pre_physics_step
  * (envs/legged_base_task/legged_robot_base.py:268-286) and _compute_torques (:795-838). */
 typedef struct PbhcActuationCfg {

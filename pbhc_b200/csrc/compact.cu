@@ -5,6 +5,8 @@
 //   pass 2: a block sums scratch[0 .. block) (its first output slot), ranks its own nonzero flags with warp ballots
 //           and writes the ids in ascending order; the last block writes the total.
 // No atomics, so the output order does not depend on scheduling.
+#include <mutex>
+
 #include "common.cuh"
 
 namespace pbhc {
@@ -106,8 +108,57 @@ int compact_check(const int64_t* flags, int64_t n, const int32_t* ids, const int
   return PBHC_OK;
 }
 
+// ---- the variant that allocates nothing: the per-block counts live in a file-scope device array --------------------------------
+// 4096 block counts = 16 KB that every GPU that loads the library holds until exit; enough for kStaticMaxN flags.
+constexpr int kStaticBlocks = 4096;
+constexpr int64_t kStaticMaxN = (int64_t)kStaticBlocks * kSpan;  // 16 777 216 = PBHC_COMPACT_STATIC_MAX_N
+static_assert(kStaticMaxN == PBHC_COMPACT_STATIC_MAX_N, "header and kernel disagree on the static scratch size");
+static __device__ __align__(256) int32_t g_static_block_count[kStaticBlocks];
+
+// In host code `g_static_block_count` is only a stand-in for the symbol, not a device address: the address is asked for
+// once per device, with that device current, and cached.
+constexpr int kMaxDevices = 64;
+std::mutex g_static_mu;
+int32_t* g_static_ptr[kMaxDevices] = {};
+
+int static_scratch(int32_t** out) {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess || dev < 0 || dev >= kMaxDevices) {
+    set_error("pbhc_compact_ids_static: cudaGetDevice: %s (device %d)", cudaGetErrorString(e), dev);
+    return PBHC_E_CUDA;
+  }
+  std::lock_guard<std::mutex> lock(g_static_mu);
+  if (!g_static_ptr[dev]) {
+    int32_t* p = nullptr;
+    e = cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_static_block_count);
+    if (e != cudaSuccess || !p) {
+      set_error("pbhc_compact_ids_static: cudaGetSymbolAddress on device %d: %s", dev, cudaGetErrorString(e));
+      (void)cudaGetLastError();
+      return PBHC_E_CUDA;
+    }
+    g_static_ptr[dev] = p;
+  }
+  *out = g_static_ptr[dev];
+  return PBHC_OK;
+}
+
 }  // namespace
 }  // namespace pbhc
+
+extern "C" int pbhc_compact_ids_static(const int64_t* flags, int64_t n, int32_t* ids, int32_t* count, void* stream) {
+  using namespace pbhc;
+  if (const int rc = compact_check(flags, n, ids, count)) return rc;
+  if (n > kStaticMaxN) {
+    set_error("pbhc_compact_ids_static: n = %lld exceeds PBHC_COMPACT_STATIC_MAX_N = %lld (use pbhc_compact_ids with caller scratch)",
+              (long long)n, (long long)kStaticMaxN);
+    return PBHC_E_RANGE;
+  }
+  int32_t* scratch = nullptr;
+  if (const int rc = static_scratch(&scratch)) return rc;
+  // nothing in the array has to start at zero: pass 1 overwrites the counts of every block pass 2 reads
+  return compact_launch(flags, n, ids, count, scratch, static_cast<cudaStream_t>(stream));
+}
 
 extern "C" int64_t pbhc_compact_scratch_ints(int64_t n) { return n <= 0 ? 0 : (n + pbhc::kSpan - 1) / pbhc::kSpan; }
 
