@@ -1349,9 +1349,11 @@ extern "C" int pbhc_track_step(const PbhcTrackCfg* cfg, const PbhcTableDesc* tab
     if (tile_ok) {
       int blocks = 0;
       const int rc = track_tile_launch(c, *tab, *io, n, (cudaStream_t)stream, &blocks);
-      if (rc != PBHC_OK) return rc;
-      track_reduce_kernel<<<1, kReduceGroups * PBHC_ACC, 0, (cudaStream_t)stream>>>(io->partials, blocks, io->acc);
-      return check_launch("pbhc_track_step");
+      if (rc < 0) return rc;
+      if (rc == PBHC_OK) {
+        track_reduce_kernel<<<1, kReduceGroups * PBHC_ACC, 0, (cudaStream_t)stream>>>(io->partials, blocks, io->acc);
+        return check_launch("pbhc_track_step");
+      }  // (rc > 0: tensors the tile kernel does not take, e.g. not 16-byte aligned - the kernel below runs)
     }
   }
   P.dump = P.rows_len;                                   // scratch for absent destinations: one source wide

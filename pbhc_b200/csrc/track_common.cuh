@@ -117,6 +117,20 @@ __device__ __forceinline__ Q4 heading_quat_inv(Q4 q) {
   return {0.0f / n, 0.0f / n, sz / n, w / n};
 }
 
+// The same value without atan2f / sinf / cosf: with (c, s) = (cos, sin) of the heading, cos(h / 2) = sqrt((1 + c) / 2) >= 0 and
+// sin(h / 2) = s / (2 cos(h / 2)) (or the mirrored pair where c < 0, which keeps the subtraction well conditioned).  Within
+// 1.2e-7 of the exact value over all headings, like the sequence above (its normalisation divides by 1 +- 1 ulp).
+__device__ __forceinline__ Q4 heading_quat_inv_fast(Q4 q) {
+  const V3 d = quat_rotate(q, {1.0f, 0.0f, 0.0f});
+  const float r = sqrtf(d.x * d.x + d.y * d.y);
+  if (!(r > 1e-30f)) return {0.0f, 0.0f, 0.0f, 1.0f};  // atan2f(0, 0) = 0
+  const float c = d.x / r, s = d.y / r;
+  float sh, ch;
+  if (c >= 0.0f) { ch = sqrtf((1.0f + c) * 0.5f); sh = s / (2.0f * ch); }
+  else { const float a = sqrtf((1.0f - c) * 0.5f); sh = copysignf(a, s); ch = fabsf(s) / (2.0f * a); }
+  return {0.0f, 0.0f, -sh, ch};
+}
+
 // my_quat_rotate(q, v) for q = (0, 0, z, w) - the heading quaternion.  Same expression tree as quat_rotate_impl with
 // the terms that multiply q.x = q.y = 0 dropped: they are exact zeros, so only the sign of a zero result can differ.
 __device__ __forceinline__ V3 quat_rotate_z(float qz, float qw, V3 v) {

@@ -34,7 +34,6 @@ namespace pbhc {
 
 constexpr int kTE = 8;             // envs per tile = warps per block
 constexpr int kNT = kTE * 32;
-constexpr int kMaxIn = 20, kMaxSmall = 4, kMaxOut = 16;
 constexpr int kBodyRaw = 10;       // per-body values of the body sums (already masked by the body's set memberships)
 constexpr int kDofRaw = 9;         // per-dof values the dof sums are made of
 constexpr int kRvT = 60;           // per-env scalar table: [0, 57) = enum Rv
@@ -43,7 +42,6 @@ enum DofRaw { DR_DJA2, DR_DJV2, DR_TQ2, DR_DACT2, DR_DV2, DR_ACC2, DR_LPOS, DR_L
 constexpr int kBodySums = 10;
 constexpr int kPieces = 5;         // pieces of the per-env scalar pre-computation
 
-struct TileDesc { const char* g; int row_bytes, g_stride, soff, soff2; };  // one per-env array: global rows -> slab at byte offset soff (soff2: second buffer)
 
 // Launch constants of the hot loop.  The generic (ahead-of-time) kernel reads them from the launch parameters; the
 // specialised kernel (jit.cu: the same source compiled by NVRTC for one env config) sees them as compile-time constants
@@ -53,11 +51,10 @@ struct TileDesc { const char* g; int row_bytes, g_stride, soff, soff2; };  // on
   X(contact_size) X(rec_stride) X(use_vec_reward) X(only_positive) X(has_termination) X(cur_torque_enable) X(term_gravity) \
   X(term_motion_far) X(term_motion_end) X(dif_joint_used) X(ref_vel_used) X(ext_identity) X(ref_pos_out) X(ref_rot_out) X(default_dof_stride) \
   X(e_pos) X(e_vel) X(e_ang) X(e_dp) X(e_dv) X(e_c) \
-  X(o_bar) X(o_tab) X(o_hmap) X(o_hmul) X(o_rv) X(o_pre) X(o_rows) X(o_scr) X(scr_pitch) \
-  X(i_body) X(i_cf) X(i_hist) X(i_dof) X(i_act) X(i_tq) X(i_lact) X(i_ldv) X(i_kp) X(i_kd) X(i_es) X(i_org) X(i_com) X(i_fric) \
-  X(i_delay) X(i_mass) X(i_root0) X(i_root1) X(i_ep0) X(i_ep1) X(i_envf0) X(i_envf1) X(i_mid0) X(i_mid1) \
-  X(q_rew) X(q_es) X(q_envf) X(q_ep) X(q_reset) X(q_lact) X(q_ldpos) X(q_ldvel) \
-  X(row_base0) X(row_base1) X(row_base2) X(row_base3) X(gdim0) X(gdim1) X(gdim2) X(gdim3) X(ghist0) X(ghist1) X(ghist2) X(ghist3)
+  X(o_tab) X(o_stab) X(n_slots) X(o_hmap) X(o_hmul) X(o_rv) X(o_pre) X(o_rows) X(o_scr) X(scr_pitch) \
+  X(i_body) X(i_cf) X(i_hist) X(i_dof) X(i_act) X(i_tq) X(i_lact) X(i_ldv) X(i_kp) X(i_kd) X(i_es0) X(i_es1) X(i_org0) X(i_org1) X(i_com0) X(i_com1) X(i_fric0) X(i_fric1) \
+  X(i_delay0) X(i_delay1) X(i_mass0) X(i_mass1) X(i_root0) X(i_root1) X(i_ep0) X(i_ep1) X(i_envf0) X(i_envf1) X(i_mid0) X(i_mid1) \
+    X(row_base0) X(row_base1) X(row_base2) X(row_base3) X(gdim0) X(gdim1) X(gdim2) X(gdim3) X(ghist0) X(ghist1) X(ghist2) X(ghist3)
 #define PBHC_HOTK_FLT(X) X(dt) X(clip_obs) X(term_gravity_thr) X(w_lower) X(w_upper) X(termination_scale) X(desired_feet_air_time) X(max_contact_force)
 #define PBHC_HOTK_I64(X) X(max_episode_length) X(penalised_mask)
 struct HotK {
@@ -82,8 +79,7 @@ struct TileParams {
   PbhcTrackIO io;
   HotK k;
   SpecExtra x;
-  int n, n_tiles, n_in, n_small, n_out, bulk_ok, in_bytes, small_bytes;
-  TileDesc in[kMaxIn], small[kMaxSmall], out[kMaxOut];
+  int n, n_tiles;
   int hist_base[PBHC_MAX_HIST_KEYS];
 };
 
@@ -164,6 +160,7 @@ struct TileTables {
 };
 
 struct NoiseKeyT { uint64_t seed; int64_t env; uint32_t step; };
+struct SmallSlot { const char* src; int row_bytes; int dst; };  // one 4-byte word of a late-read per-env array: global word of env 0, row size, shared-memory byte offset (row 0)
 struct Rows { float* rows; float* ghist; int e; };   // observation slabs (shared), the env's global history row, tile-local env
 
 __device__ __forceinline__ float clampf(float v, float c) { return fminf(fmaxf(v, -c), c); }
@@ -255,9 +252,17 @@ __device__ __forceinline__ void emit3k(const TileTables& T, const Rows& R, int e
 #endif
 }
 
+// ---- cp.async (LDGSTS) ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src) { asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory"); }
+__device__ __forceinline__ void cp_async8(uint32_t dst, const void* src) { asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(dst), "l"(src) : "memory"); }
+__device__ __forceinline__ void cp_async4(uint32_t dst, const void* src) { asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(src) : "memory"); }
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+
 // ---- TMA / mbarrier ---------------------------------------------------------------------------------------------------
 __device__ __forceinline__ void mbar_init(uint32_t bar, int count) { asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory"); }
 __device__ __forceinline__ void mbar_expect_tx(uint32_t bar, int bytes) { asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory"); }
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) { asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory"); }
 __device__ __forceinline__ void mbar_wait_t(uint32_t bar, uint32_t parity) {
   asm volatile(
       "{\n.reg .pred p;\nTWAIT_LOOP:\nmbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n@p bra TWAIT_DONE;\nbra TWAIT_LOOP;\nTWAIT_DONE:\n}\n" ::"r"(bar),
@@ -274,7 +279,7 @@ __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.comm
 __device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
 __device__ __forceinline__ void fence_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
-__device__ void build_tile_tables(const TileParams& P, TileTables& T, int* hmap, float* hmul, const double* scal_g, double* scal) {
+__device__ void build_tile_tables(const TileParams& P, TileTables& T, short* hmap, float* hmul, const double* scal_g, double* scal) {
   const PbhcTrackCfg& c = P.c;
   const int tid = threadIdx.x, nt = blockDim.x;
   auto row_base = [&](int g) { return g == 0 ? KC(row_base0) : g == 1 ? KC(row_base1) : g == 2 ? KC(row_base2) : KC(row_base3); };
@@ -394,7 +399,8 @@ __device__ void build_tile_tables(const TileParams& P, TileTables& T, int* hmap,
   }
   // history ring: physical slot of logical slot s of key k is (head_k + s) % len_k, head_k = -push_count mod len_k
   // (HistoryHandler keeps newest-first order, history_handler.py:40-48).  One plane per obs group that shows history:
-  // hmap[plane][i] = float offset (inside the rows region, env 0) where physical ring element i goes in that group, -1 = none.
+  // hmap[plane][i] = float offset (inside the rows region, env 0) where physical ring element i goes in that group, -1 = none
+  // (16-bit: the rows region of a tile is far below 32768 floats - checked by tile_plan).
   for (int i = tid; i < c.hist_row; i += nt) {
     int k = 0;
     while (k + 1 < c.n_hist_keys && i >= P.hist_base[k + 1]) ++k;
@@ -410,22 +416,13 @@ __device__ void build_tile_tables(const TileParams& P, TileTables& T, int* hmap,
         const PbhcHistDst& h = c.hist_dst[e];
         if (h.key == k && h.group == g && s < h.len) { m = row_base(g) + h.offset + s * dim + cc; mul = h.mul; }
       }
-      hmap[plane * c.hist_row + i] = m;
+      hmap[plane * c.hist_row + i] = (short)m;
       if (KC(hist_any_mul)) hmul[plane * c.hist_row + i] = mul;
       ++plane;
     }
   }
   __syncthreads();
 }
-
-// development aid (PBHC_TILE_PROF=1 at JIT time): lane 0 of every warp of blocks 0..7 stamps clock64() at six points of its
-// first 16 tiles into the unused tail of io.partials (rows 600 + 16 * block), read back by tools/tile_prof.py.  (BAR.SYNC does
-// not block at issue but at the next shared-memory access: the stamp reads shared memory first.)
-#ifdef PBHC_TILE_PROF
-#define TPROF(slot) do { unsigned tp_; asm volatile("ld.volatile.shared.u32 %0, [%1];" : "=r"(tp_) : "r"(bar) : "memory"); if (lane == 0 && blockIdx.x < 8 && it < 16) reinterpret_cast<long long*>(P.io.partials)[(long long)(600 + blockIdx.x * 16) * 64 + ((it * 8 + warp) * 6 + (slot))] = clock64() + (tp_ & 0u); } while (0)
-#else
-#define TPROF(slot) do { } while (0)
-#endif
 
 template <bool kNoise>
 __device__ __forceinline__ void track_tile_body(const TileParams& P) {
@@ -435,18 +432,31 @@ __device__ __forceinline__ void track_tile_body(const TileParams& P) {
   const PbhcTableDesc& tab = P.tab;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   TileTables& T = *reinterpret_cast<TileTables*>(smem + KC(o_tab));
-  int* hmap = reinterpret_cast<int*>(smem + KC(o_hmap));
+  short* hmap = reinterpret_cast<short*>(smem + KC(o_hmap));
   float* hmul = reinterpret_cast<float*>(smem + KC(o_hmul));
   float* rv = reinterpret_cast<float*>(smem + KC(o_rv));            // [kTE][kRvT]
   float* rows = reinterpret_cast<float*>(smem + KC(o_rows));
   const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(smem);
-  const uint32_t bar = sbase + KC(o_bar);
 
-  if (tid == 0) { mbar_init(bar, 1); asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); fence_async(); }
   for (int i = tid; i < kTE * kRvT; i += kNT) rv[i] = 0.0f;  // slots nobody writes are accumulated too
+  {  // slot table of the late-read arrays (both buffers)
+    constexpr int kArr = 10;
+    const void* const ag[kArr] = {io.episode_sums, io.env_origins, io.base_com_bias, io.friction, io.action_delay_idx, io.link_mass_scale,
+                                  io.root_state, io.episode_length_buf, io.env_f32, io.motion_ids};
+    const int ab[kArr] = {KC(n_sums) * 4, 12, 12, 4, 8, KC(L) * 4, 52, 8, PBHC_ENVF_STRIDE * 4, 8};
+    const int a0[kArr] = {KC(i_es0), KC(i_org0), KC(i_com0), KC(i_fric0), KC(i_delay0), KC(i_mass0), KC(i_root0), KC(i_ep0), KC(i_envf0), KC(i_mid0)};
+    const int a1[kArr] = {KC(i_es1), KC(i_org1), KC(i_com1), KC(i_fric1), KC(i_delay1), KC(i_mass1), KC(i_root1), KC(i_ep1), KC(i_envf1), KC(i_mid1)};
+    SmallSlot* st = reinterpret_cast<SmallSlot*>(smem + KC(o_stab));
+    for (int i = tid; i < 2 * KC(n_slots); i += kNT) {
+      const int buf = i >= KC(n_slots) ? 1 : 0;
+      int w = i - buf * KC(n_slots), a = 0;
+      while (a < kArr - 1 && w >= (ab[a] >> 2)) { w -= ab[a] >> 2; ++a; }
+      st[i] = {reinterpret_cast<const char*>(ag[a]) + 4 * w, ab[a], (buf ? a1[a] : a0[a]) + 4 * w};
+    }
+  }
   build_tile_tables(P, T, hmap, hmul, io.scalars, reinterpret_cast<double*>(smem + KC(o_rows)));  // (the rows region is idle: scratch for the scalars)
 
-  const int J = KC(J), Jb = KC(Jb), D = KC(D), H = KC(H), n_envs = P.n;
+  const int J = KC(J), Jb = KC(Jb), D = KC(D), H = KC(H);
   const int R = KC(R);
   const float clipv = KC(clip_obs), dt = KC(dt);
   const int e_pos = KC(e_pos), e_vel = KC(e_vel), e_ang = KC(e_ang), e_dp = KC(e_dp), e_dv = KC(e_dv), e_c = KC(e_c);
@@ -454,33 +464,70 @@ __device__ __forceinline__ void track_tile_body(const TileParams& P) {
   const uint32_t push_count = T.push_count;
   double acc_reg = 0.0;  // slot = lane (< kAccLo), this warp's envs
 
-  const int n_tiles = P.n_tiles, stride = (int)gridDim.x;
-  const int n_full = P.bulk_ok ? n_envs / kTE : 0;  // tiles that move by TMA
-  auto is_bulk = [&](int t) { return t < n_full; };
-  // warp 0: requests the big slabs of tile `tb` and the small (double-buffered) slabs of tile `ts` into buffer `buf`
-  auto issue_loads = [&](int tb, bool big, int ts, bool small, int buf) {
-    if (lane == 0) mbar_expect_tx(bar, (big ? P.in_bytes : 0) + (small ? P.small_bytes : 0));
-    __syncwarp();
-    if (big)
-      for (int i = lane; i < P.n_in; i += 32) {
-        const TileDesc d = P.in[i];
-        const int64_t t0 = (int64_t)tb * kTE;
-        if (d.g_stride == d.row_bytes) bulk_load(sbase + d.soff, d.g + t0 * d.row_bytes, kTE * d.row_bytes, bar);
-        else for (int e = 0; e < kTE; ++e) bulk_load(sbase + d.soff + e * d.row_bytes, d.g + (t0 + e) * d.g_stride, d.row_bytes, bar);
-      }
-    if (small && lane < P.n_small) {
-      const TileDesc d = P.small[lane];
-      bulk_load(sbase + (buf ? d.soff2 : d.soff), d.g + (int64_t)ts * kTE * d.row_bytes, kTE * d.row_bytes, bar);
+  // Every warp runs its own pipeline over its own envs (row `e` = warp of every slab): no block barrier inside the loop.
+  // Inputs arrive by cp.async (LDGSTS: 16 / 8 / 4 bytes per lane, whatever the row size allows - rows of 23 floats are
+  // not 16-byte multiples): the rows read only by sections a-d (simulator state, history ring, dof-wise arrays) are
+  // single-buffered and re-requested for the warp's next env as soon as section d is done, the ones read until the
+  // end of an env are double-buffered; both arrive while sections e-i and the row write-out of the current env run.
+  const int e = warp;
+  const int64_t n_envs = P.n, step = (int64_t)gridDim.x * kTE;
+  const SmallSlot* stab = reinterpret_cast<const SmallSlot*>(smem + KC(o_stab));
+  auto row_load = [&](int soff, int bytes, const void* g, int64_t m, int64_t g_row_bytes) {
+    const uint32_t dst = sbase + soff + e * bytes;
+    const char* src = reinterpret_cast<const char*>(g) + m * g_row_bytes;
+    if (((bytes | (int)g_row_bytes) & 15) == 0) {
+      const uint32_t d = dst + lane * 16; const char* p = src + lane * 16;
+      for (int o = 0; o < bytes; o += 512) if (o + lane * 16 < bytes) cp_async16(d + o, p + o);
+    } else if (((bytes | (int)g_row_bytes) & 7) == 0) {
+      const uint32_t d = dst + lane * 8; const char* p = src + lane * 8;
+      for (int o = 0; o < bytes; o += 256) if (o + lane * 8 < bytes) cp_async8(d + o, p + o);
+    } else {
+      const uint32_t d = dst + lane * 4; const char* p = src + lane * 4;
+      for (int o = 0; o < bytes; o += 128) if (o + lane * 4 < bytes) cp_async4(d + o, p + o);
     }
   };
-  // the per-env scalar work of a tile, piece = warp, lane = env (legged_robot_base.py:346-353, motion_tracking.py:548-558, 678-739)
-  auto pre_pieces = [&](int buf, int cnt) {
-    if (warp >= kPieces || lane >= cnt) return;
-    const int e = lane;
-    float* pe = reinterpret_cast<float*>(smem + KC(o_pre)) + (buf * kTE + e) * kPre;
+  auto request = [&](int64_t m, int buf) {  // env m's inputs -> this warp's rows (late-read ones into buffer `buf`)
+    row_load(KC(i_body), Jb * 52, io.body_state, m, io.body_env_stride * 4);
+    row_load(KC(i_cf), Jb * 12, io.contact_forces, m, Jb * 12);
+    if (H > 0) row_load(KC(i_hist), H * 4, io.hist, m, H * 4);
+    row_load(KC(i_dof), D * 8, io.dof_state, m, D * 8);
+    {  // the six dof-wise arrays: equal rows, equally sized consecutive slabs (tile_plan) - one offset serves all of them
+      const int64_t o = m * (D * 4) + lane * 4;
+      const uint32_t d = sbase + KC(i_act) + e * (D * 4) + lane * 4;
+      constexpr int kDofWise = 6;
+      const float* const g[kDofWise] = {io.actions, io.torques, io.last_actions, io.last_dof_vel, io.kp_scale, io.kd_scale};
+      if (lane < D) {
+#pragma unroll
+        for (int a = 0; a < kDofWise; ++a) cp_async4(d + a * (kTE * D * 4), reinterpret_cast<const char*>(g[a]) + o);
+      }
+    }
+    // the late-read arrays, a 4-byte word per lane and round through the slot table (rewards' episode sums, origins, domain-
+    // randomisation scalars, root state, episode length, env scalars, motion id)
+    for (int sl = lane; sl < KC(n_slots); sl += 32) {
+      const SmallSlot t = stab[buf * KC(n_slots) + sl];
+      cp_async4(sbase + t.dst + e * t.row_bytes, t.src + m * t.row_bytes);
+    }
+    cp_async_commit();
+  };
+  // the per-env scalars of the env in buffer `buf`, lane = piece (legged_robot_base.py:346-353, motion_tracking.py:548-558, 678-739)
+  auto pre_pieces = [&](int buf) {
+    if (lane >= kPieces) return;
+    float* pe = reinterpret_cast<float*>(smem + KC(o_pre)) + e * kPre;
     const float* root = reinterpret_cast<const float*>(smem + (buf ? KC(i_root1) : KC(i_root0))) + e * 13;
     const Q4 rq = {root[3], root[4], root[5], root[6]};
-    if (warp == 0) {
+    if (lane < 3) {  // base linear velocity, base angular velocity, projected gravity: one code, three vectors (the
+      // reference's own operation sequence - the gravity feeds the termination check)
+      const bool gv = lane == 2;
+      const V3 v = {gv ? 0.0f : root[7 + 3 * lane], gv ? 0.0f : root[8 + 3 * lane], gv ? -1.0f : root[9 + 3 * lane]};
+      const V3 o = quat_rotate_x(rq, v, true);
+      float* d = pe + P_BLV + 3 * lane;
+      d[0] = o.x; d[1] = o.y; d[2] = o.z;
+      if (gv) { pe[P_GRAVN] = norm2(o.x, o.y); pe[P_ORIENT] = o.x * o.x + o.y * o.y; }
+      if (lane == 0) { pe[P_RPX] = root[0]; pe[P_RPY] = root[1]; pe[P_RPZ] = root[2]; }
+    } else if (lane == 3) {
+      const Q4 hinv = heading_quat_inv_fast(rq);
+      pe[P_HZ] = hinv.z; pe[P_HW] = hinv.w;
+    } else {
       const int64_t ep = reinterpret_cast<const long long*>(smem + (buf ? KC(i_ep1) : KC(i_ep0)))[e] + 1;  // legged_robot_base.py:299
       const float start = reinterpret_cast<const float*>(smem + (buf ? KC(i_envf1) : KC(i_envf0)))[e * PBHC_ENVF_STRIDE];
       const int clip = resolve_clip(tab, io.clip_of_motion, reinterpret_cast<const long long*>(smem + (buf ? KC(i_mid1) : KC(i_mid0)))[e]);
@@ -489,80 +536,24 @@ __device__ __forceinline__ void track_tile_body(const TileParams& P) {
       pe[P_F0] = __int_as_float((int)fb.f0); pe[P_F1] = __int_as_float((int)fb.f1); pe[P_BLEND] = fb.blend;
       pe[P_PHASE] = __fdiv_rn(t, tab.clip_length[clip]);  // motion_tracking.py:738-739
       pe[P_CLIP] = __int_as_float(clip);
-    } else if (warp == 1) {
-      const V3 blv = quat_rotate_inverse(rq, {root[7], root[8], root[9]});
-      pe[P_BLV] = blv.x; pe[P_BLV + 1] = blv.y; pe[P_BLV + 2] = blv.z;
-      pe[P_RPX] = root[0]; pe[P_RPY] = root[1]; pe[P_RPZ] = root[2];
-    } else if (warp == 2) {
-      const V3 bav = quat_rotate_inverse(rq, {root[10], root[11], root[12]});
-      pe[P_BAV] = bav.x; pe[P_BAV + 1] = bav.y; pe[P_BAV + 2] = bav.z;
-    } else if (warp == 3) {
-      const V3 pg = quat_rotate_x(rq, {0.0f, 0.0f, -1.0f}, true);
-      pe[P_PG] = pg.x; pe[P_PG + 1] = pg.y; pe[P_PG + 2] = pg.z;
-      pe[P_GRAVN] = norm2(pg.x, pg.y);
-      pe[P_ORIENT] = pg.x * pg.x + pg.y * pg.y;
-    } else {
-      const Q4 hinv = heading_quat_inv(rq);
-      pe[P_HZ] = hinv.z; pe[P_HW] = hinv.w;
     }
   };
 
-  int tile = blockIdx.x, it = 0;
-  uint32_t phase = 0;
-  bool have_small_next = false, pre_ready = false;
-  if (is_bulk(tile)) {  // prologue: this block's first tile (big + small) and the small inputs of its second tile
-    have_small_next = is_bulk(tile + stride);
-    if (warp == kTE - 1) {
-      if (lane == 0) mbar_expect_tx(bar, P.in_bytes + P.small_bytes * (have_small_next ? 2 : 1));
-      __syncwarp();
-      for (int i = lane; i < P.n_in; i += 32) {
-        const TileDesc d = P.in[i];
-        const int64_t t0 = (int64_t)tile * kTE;
-        if (d.g_stride == d.row_bytes) bulk_load(sbase + d.soff, d.g + t0 * d.row_bytes, kTE * d.row_bytes, bar);
-        else for (int e = 0; e < kTE; ++e) bulk_load(sbase + d.soff + e * d.row_bytes, d.g + (t0 + e) * d.g_stride, d.row_bytes, bar);
-      }
-      if (lane < P.n_small) {
-        const TileDesc d = P.small[lane];
-        bulk_load(sbase + d.soff, d.g + (int64_t)tile * kTE * d.row_bytes, kTE * d.row_bytes, bar);
-        if (have_small_next) bulk_load(sbase + d.soff2, d.g + (int64_t)(tile + stride) * kTE * d.row_bytes, kTE * d.row_bytes, bar);
-      }
-    }
-  }
-
-  for (; tile < n_tiles; tile += stride, ++it) {
-    const int tile0 = tile * kTE;
-    const int cnt = min(kTE, n_envs - tile0);
-    const int sb = it & 1;
-    const bool bulk = is_bulk(tile);
-    TPROF(0);
-    if (warp == kTE - 1) bulk_wait_read();  // the previous tile's bulk stores have left the output slabs
-    if (bulk) { if (tid == kNT - 32) mbar_wait_t(bar, phase); phase ^= 1u; }
-    else {  // ragged last tile / unaligned tensors: cooperative word copies
-      for (int i = 0; i < P.n_in + P.n_small; ++i) {
-        const TileDesc d = i < P.n_in ? P.in[i] : P.small[i - P.n_in];
-        const int rw = d.row_bytes >> 2;
-        uint32_t* dst = reinterpret_cast<uint32_t*>(smem + ((i >= P.n_in && sb) ? d.soff2 : d.soff));
-        for (int w = tid; w < cnt * rw; w += kNT) {
-          const int e = w / rw, x = w - e * rw;
-          dst[w] = reinterpret_cast<const uint32_t*>(d.g + (int64_t)(tile0 + e) * d.g_stride)[x];
-        }
-      }
-    }
-    __syncthreads();
-    TPROF(1);
-    if (!pre_ready) { pre_pieces(sb, cnt); __syncthreads(); }
-
-    TPROF(2);
+  int64_t n = (int64_t)blockIdx.x * kTE + warp;
+  if (n < n_envs) request(n, 0);
+  for (int sb = 0; n < n_envs; n += step, sb ^= 1) {
+    cp_async_wait_all();
+    __syncwarp();
+    pre_pieces(sb);
+    __syncwarp();
     // ================================ warp = env =====================================================================
-    if (warp < cnt) {
-      const int e = warp;
-      const int64_t n = tile0 + e;
-      const float* pe = reinterpret_cast<const float*>(smem + KC(o_pre)) + (sb * kTE + e) * kPre;
+    {
+      const float* pe = reinterpret_cast<const float*>(smem + KC(o_pre)) + e * kPre;
       const float* s_envf = reinterpret_cast<const float*>(smem + (sb ? KC(i_envf1) : KC(i_envf0))) + e * PBHC_ENVF_STRIDE;
       const int64_t ep_in = reinterpret_cast<const long long*>(smem + (sb ? KC(i_ep1) : KC(i_ep0)))[e];
       const float* s_body = reinterpret_cast<const float*>(smem + KC(i_body)) + e * (Jb * 13);
       const float* s_cf = reinterpret_cast<const float*>(smem + KC(i_cf)) + e * (Jb * 3);
-      const float* s_org = reinterpret_cast<const float*>(smem + KC(i_org)) + e * 3;
+      const float* s_org = reinterpret_cast<const float*>(smem + (sb ? KC(i_org1) : KC(i_org0))) + e * 3;
       float* scr = reinterpret_cast<float*>(smem + KC(o_scr) + e * KC(scr_pitch));
       float* rve = rv + e * kRvT;
       const Rows Rw = {rows, io.hist + n * H, e};
@@ -577,7 +568,7 @@ __device__ __forceinline__ void track_tile_body(const TileParams& P) {
         if ((H & 3) == 0 && !KC(hist_any_mul)) {  // four ring elements per lane and pass
           auto plane4 = [&](int has, int plane, int gd, int i, const float4& v) {
             if (!has) return;
-            const int4 m = reinterpret_cast<const int4*>(hmap)[plane * (H >> 2) + i];
+            const short4 m = reinterpret_cast<const short4*>(hmap)[plane * (H >> 2) + i];
             float* r = rows + e * gd;
             if (m.x >= 0) r[m.x] = v.x;
             if (m.y >= 0) r[m.y] = v.y;
@@ -639,7 +630,7 @@ __device__ __forceinline__ void track_tile_body(const TileParams& P) {
           emit1k<kNoise, S_DIF_JOINT_VEL>(T, Rw, d, djv, clipv, nk);
         }
         // _post_compute_observations_callback, legged_robot_base.py:398-405
-        reinterpret_cast<float*>(smem + KC(q_lact))[x] = act; reinterpret_cast<float*>(smem + KC(q_ldpos))[x] = dpos; reinterpret_cast<float*>(smem + KC(q_ldvel))[x] = dvel;
+        io.last_actions[n * D + d] = act; io.last_dof_pos[n * D + d] = dpos; io.last_dof_vel[n * D + d] = dvel;  // (small per-env results go straight to global: a bulk copy per array costs its issuer more than these stores)
       }
       {
         const float mx = warp_max(adja);
@@ -784,6 +775,11 @@ __device__ __forceinline__ void track_tile_body(const TileParams& P) {
       const bool stumble = __any_sync(0xffffffffu, x_stumble);
       float air1 = __shfl_sync(0xffffffffu, air_f, 1), contact1 = __shfl_sync(0xffffffffu, contact_f, 1);  // lane 0 packs the state
 
+      // ---- the single-buffered input rows (simulator state, history ring / scratch, dof-wise arrays) are not read past this point:
+      // the warp's next env is requested, so that its inputs arrive while sections e-i and the row write-out run --------------------
+      __syncwarp();
+      if (n + step < n_envs) request(n + step, sb ^ 1);
+
       // ---- e. termination (legged_robot_base.py:408-489, motion_tracking.py:330-358) -------------------------------------------
       const int64_t last_ep = ep_in + 1;
       int64_t ep = last_ep;
@@ -819,39 +815,38 @@ __device__ __forceinline__ void track_tile_body(const TileParams& P) {
           rew = v * T.r_scale[lane] * T.r_pen[lane];
         }
         const float term_rew = KC(has_termination) ? ((terminated && !time_out) ? 1.0f : 0.0f) * KC(termination_scale) : 0.0f;
-        float* q_rew = reinterpret_cast<float*>(smem + KC(q_rew));
         if (KC(use_vec_reward)) {
           float v = rew;
           if (KC(only_positive)) v = fmaxf(v, 0.0f);
           if (lane == R - 1) v += term_rew;  // the reference's stale loop index, legged_robot_base.py:744
-          if (lane < R) q_rew[e * (R + 1) + lane] = v;
-          if (lane == R) q_rew[e * (R + 1) + R] = 0.0f;
+          if (lane < R) io.rew_buf[n * (R + 1) + lane] = v;
+          if (lane == R) io.rew_buf[n * (R + 1) + R] = 0.0f;
         } else {  // rew_buf += rew term by term (legged_robot_base.py:733): a sequential fp32 sum in term order
           float tot = 0.0f;
           for (int r = 0; r < R; ++r) tot += __shfl_sync(0xffffffffu, rew, r);
           if (KC(only_positive)) tot = fmaxf(tot, 0.0f);
-          if (lane == 0) q_rew[e] = tot + term_rew;
+          if (lane == 0) io.rew_buf[n] = tot + term_rew;
         }
         if (lane < KC(n_sums)) {
-          float ev = reinterpret_cast<const float*>(smem + KC(i_es))[e * KC(n_sums) + lane] + (lane < R ? rew : term_rew);
+          float ev = reinterpret_cast<const float*>(smem + (sb ? KC(i_es1) : KC(i_es0)))[e * KC(n_sums) + lane] + (lane < R ? rew : term_rew);
           if (reset) { io.last_episode_sums[n * KC(n_sums) + lane] = ev; ev = 0.0f; }  // extras["episode"], legged_robot_base.py:509-513
-          reinterpret_cast<float*>(smem + KC(q_es))[e * KC(n_sums) + lane] = ev;
+          io.episode_sums[n * KC(n_sums) + lane] = ev;
         }
       }
 
       // ---- g. scalar features into the rows (legged_robot_base.py:1114-1215; motion_tracking.py:944-1015) -------------------------
-      int64_t delay = reinterpret_cast<const long long*>(smem + KC(i_delay))[e];
+      int64_t delay = reinterpret_cast<const long long*>(smem + (sb ? KC(i_delay1) : KC(i_delay0)))[e];
       auto emit_scalar_features = [&](int64_t delay_) {
         for (int i = lane; i < KC(n_feat); i += 32) {
           const int k = T.feat_src[i], el = T.feat_el[i];
           float val;
           if (i < 9) val = pe[P_BLV + i];
-          else if (k == S_DR_COM) val = reinterpret_cast<const float*>(smem + KC(i_com))[e * 3 + el];
+          else if (k == S_DR_COM) val = reinterpret_cast<const float*>(smem + (sb ? KC(i_com1) : KC(i_com0)))[e * 3 + el];
           else if (k == S_PHASE) val = pe[P_PHASE];        // stale for envs that reset, like the reference
-          else if (k == S_DR_FRICTION) val = reinterpret_cast<const float*>(smem + KC(i_fric))[e];
+          else if (k == S_DR_FRICTION) val = reinterpret_cast<const float*>(smem + (sb ? KC(i_fric1) : KC(i_fric0)))[e];
           else if (k == S_DR_DELAY) val = (float)delay_;
           else if (k == S_BASE_POS_Z) val = pe[P_RPZ];
-          else val = reinterpret_cast<const float*>(smem + KC(i_mass))[e * KC(L) + el];
+          else val = reinterpret_cast<const float*>(smem + (sb ? KC(i_mass1) : KC(i_mass0)))[e * KC(L) + el];
           emit1<kNoise>(T, Rw, k, el, val, clipv, nk);
         }
       };
@@ -971,18 +966,18 @@ __device__ __forceinline__ void track_tile_body(const TileParams& P) {
           emit1k<kNoise, S_DR_KP>(T, Rw, lane, kp2, clipv, nk);
           emit1k<kNoise, S_DR_KD>(T, Rw, lane, kd2, clipv, nk);
           const int x = e * D + lane;
-          reinterpret_cast<float*>(smem + KC(q_lact))[x] = 0.0f; reinterpret_cast<float*>(smem + KC(q_ldpos))[x] = dpos2; reinterpret_cast<float*>(smem + KC(q_ldvel))[x] = dvel2;
+          io.last_actions[n * D + lane] = 0.0f; io.last_dof_pos[n * D + lane] = dpos2; io.last_dof_vel[n * D + lane] = dvel2;
         }
         emit_scalar_features(delay);
       }
 
       // ---- i. state write-back, cross-env sums ----------------------------------------------------------------------------------------
       if (lane == 0) {
-        float4* of = reinterpret_cast<float4*>(smem + KC(q_envf)) + e * 2;
+        float4* of = reinterpret_cast<float4*>(io.env_f32) + n * 2;
         of[0] = make_float4(start, mlen, air0, KC(n_feet) > 1 ? air1 : 0.0f);
         of[1] = make_float4(contact0, KC(n_feet) > 1 ? contact1 : 0.0f, etr, s_envf[7]);
-        reinterpret_cast<long long*>(smem + KC(q_ep))[e] = ep;
-        reinterpret_cast<long long*>(smem + KC(q_reset))[e] = reset ? 1 : 0;
+        io.episode_length_buf[n] = ep;
+        io.reset_buf[n] = reset ? 1 : 0;
         io.time_out_buf[n] = time_out ? 1 : 0;
       }
       if (lane < kAccLo) {  // per-lane fp64 accumulation of the cross-env sums (slot = lane, layout PBHC_A_*)
@@ -992,39 +987,24 @@ __device__ __forceinline__ void track_tile_body(const TileParams& P) {
         if (lane == V_ETR_SQ) a = (double)etr * (double)etr;
         acc_reg += a;
       }
+      // ---- j. the env's observation rows leave (16 bytes per lane where the row size allows) -----------------------------------
+      __syncwarp();
+      auto row_out = [&](int has, int row_base, int gd, float* g) {
+        if (!has) return;
+        const float* src = rows + row_base + e * gd;
+        float* dst = g + n * gd;
+        if ((gd & 3) == 0) { for (int i = lane; i < (gd >> 2); i += 32) reinterpret_cast<float4*>(dst)[i] = reinterpret_cast<const float4*>(src)[i]; }
+        else if ((gd & 1) == 0) { for (int i = lane; i < (gd >> 1); i += 32) reinterpret_cast<float2*>(dst)[i] = reinterpret_cast<const float2*>(src)[i]; }
+        else { for (int i = lane; i < gd; i += 32) dst[i] = src[i]; }
+      };
+      row_out(KC(n_groups) > 0, KC(row_base0), KC(gdim0), io.obs[0]);
+      row_out(KC(n_groups) > 1, KC(row_base1), KC(gdim1), io.obs[1]);
+      row_out(KC(n_groups) > 2, KC(row_base2), KC(gdim2), io.obs[2]);
+      row_out(KC(n_groups) > 3, KC(row_base3), KC(gdim3), io.obs[3]);
+      __syncwarp();  // (the rows are written again by the next env)
     }
-    TPROF(3);
-    fence_async();
-    __syncthreads();
-    TPROF(4);
-
-    // ---- the next tile's inputs are requested (first: they are on the critical path), outputs leave; meanwhile the warps
-    // that carry a piece of the next tile's per-env scalars compute it (its small inputs arrived a tile ago) ----------------------
-    const bool big = is_bulk(tile + stride), small = is_bulk(tile + 2 * stride);
-    if (big && warp == kTE - 1) issue_loads(tile + stride, true, tile + 2 * stride, small, sb);
-    if (bulk) {
-      if (warp == kTE - 1) {
-        for (int i = lane; i < P.n_out; i += 32) {
-          const TileDesc d = P.out[i];
-          bulk_store(const_cast<char*>(d.g) + (int64_t)tile0 * d.row_bytes, sbase + d.soff, kTE * d.row_bytes);
-        }
-        bulk_commit();
-      }
-    } else {
-      for (int i = 0; i < P.n_out; ++i) {
-        const TileDesc d = P.out[i];
-        const int nw = (cnt * d.row_bytes) >> 2;
-        const uint32_t* src = reinterpret_cast<const uint32_t*>(smem + d.soff);
-        uint32_t* dst = reinterpret_cast<uint32_t*>(const_cast<char*>(d.g) + (int64_t)tile0 * d.row_bytes);
-        for (int w = tid; w < nw; w += kNT) dst[w] = src[w];
-      }
-    }
-    if (have_small_next) pre_pieces(sb ^ 1, kTE);
-    pre_ready = have_small_next;
-    have_small_next = small;
-    TPROF(5);
   }
-  if (warp == kTE - 1) bulk_wait_read();
+  cp_async_wait_all();
   // block partials: 64 threads add the warps' sums up in warp order
   __syncthreads();
   double* wacc = reinterpret_cast<double*>(smem + KC(o_rows));
@@ -1134,38 +1114,25 @@ static int tile_plan(const PbhcTrackCfg& c, const PbhcTableDesc& tab, const Pbhc
   // ---- shared-memory layout ----
   int off = 0;
   auto take = [&](int bytes) { const int o = off; off += (bytes + 15) & ~15; return o; };
-  k.o_bar = take(16);
   k.o_tab = take((int)sizeof(TileTables));
-  k.o_hmap = take(4 * (k.n_hd > 0 ? k.n_hd : 1) * (H > 0 ? H : 1));
+  k.n_slots = c.n_episode_sums + 3 + 3 + 1 + 2 + L + 13 + 2 + PBHC_ENVF_STRIDE + 2;  // 4-byte words of the late-read arrays
+  k.o_stab = take(2 * k.n_slots * (int)sizeof(SmallSlot));
+  k.o_hmap = take(2 * (k.n_hd > 0 ? k.n_hd : 1) * (H > 0 ? H : 1));
   k.o_hmul = k.hist_any_mul ? take(4 * k.n_hd * H) : k.o_hmap;
   k.o_rv = take(4 * kTE * kRvT);
-  k.o_pre = take(4 * 2 * kTE * kPre);
-  P.n_in = 0; P.n_small = 0; P.n_out = 0; P.in_bytes = 0; P.small_bytes = 0;
-  bool ok = true;
+  k.o_pre = take(4 * kTE * kPre);
+  bool ok = true;  // every per-env array starts on a 16-byte boundary (what the vector widths of the loads / stores assume)
   auto slab_in = [&](const void* g, int row_bytes, int64_t g_stride) {
-    const int bytes = kTE * row_bytes;
-    const int o = take(bytes);
-    TileDesc d = {reinterpret_cast<const char*>(g), row_bytes, (int)g_stride, o, o};
-    P.in[P.n_in++] = d;
-    P.in_bytes += bytes;
-    const bool contig = g_stride == row_bytes;
-    if (((uintptr_t)g & 15) || (!contig && ((row_bytes & 15) || (g_stride & 15)))) ok = false;
-    return o;
+    if (((uintptr_t)g & 15) || (g_stride & 3)) ok = false;
+    return take(kTE * row_bytes);
   };
   auto slab_small = [&](const void* g, int row_bytes, int* o0, int* o1) {
-    const int bytes = kTE * row_bytes;
-    *o0 = take(bytes); *o1 = take(bytes);
-    TileDesc d = {reinterpret_cast<const char*>(g), row_bytes, row_bytes, *o0, *o1};
-    P.small[P.n_small++] = d;
-    P.small_bytes += bytes;
+    *o0 = take(kTE * row_bytes); *o1 = take(kTE * row_bytes);
     if ((uintptr_t)g & 15) ok = false;
   };
   auto slab_out = [&](void* g, int row_bytes) {
-    const int o = take(kTE * row_bytes);
-    TileDesc d = {reinterpret_cast<const char*>(g), row_bytes, row_bytes, o, o};
-    P.out[P.n_out++] = d;
     if ((uintptr_t)g & 15) ok = false;
-    return o;
+    return take(kTE * row_bytes);
   };
   k.i_body = slab_in(io.body_state, Jb * 13 * 4, io.body_env_stride * 4);
   k.i_cf = slab_in(io.contact_forces, Jb * 12, Jb * 12);
@@ -1182,12 +1149,16 @@ static int tile_plan(const PbhcTrackCfg& c, const PbhcTableDesc& tab, const Pbhc
   k.i_ldv = slab_in(io.last_dof_vel, D * 4, D * 4);
   k.i_kp = slab_in(io.kp_scale, D * 4, D * 4);
   k.i_kd = slab_in(io.kd_scale, D * 4, D * 4);
-  k.i_es = slab_in(io.episode_sums, c.n_episode_sums * 4, c.n_episode_sums * 4);
-  k.i_org = slab_in(io.env_origins, 12, 12);
-  k.i_com = slab_in(io.base_com_bias, 12, 12);
-  k.i_fric = slab_in(io.friction, 4, 4);
-  k.i_delay = slab_in(io.action_delay_idx, 8, 8);
-  k.i_mass = L > 0 ? slab_in(io.link_mass_scale, L * 4, L * 4) : k.i_fric;
+  if (k.i_kd != k.i_act + 5 * kTE * D * 4) { set_error("pbhc_track_step: internal layout error (dof-wise slabs)"); return PBHC_E_BADARG; }
+  // read late in a tile (rewards, scalar features, reset): double-buffered like the per-env scalars, so that the big slabs above
+  // can be re-filled for the next tile while this one still runs
+  slab_small(io.episode_sums, c.n_episode_sums * 4, &k.i_es0, &k.i_es1);
+  slab_small(io.env_origins, 12, &k.i_org0, &k.i_org1);
+  slab_small(io.base_com_bias, 12, &k.i_com0, &k.i_com1);
+  slab_small(io.friction, 4, &k.i_fric0, &k.i_fric1);
+  slab_small(io.action_delay_idx, 8, &k.i_delay0, &k.i_delay1);
+  if (L > 0) slab_small(io.link_mass_scale, L * 4, &k.i_mass0, &k.i_mass1);
+  else { k.i_mass0 = k.i_fric0; k.i_mass1 = k.i_fric1; }
   slab_small(io.root_state, 52, &k.i_root0, &k.i_root1);
   slab_small(io.episode_length_buf, 8, &k.i_ep0, &k.i_ep1);
   slab_small(io.env_f32, PBHC_ENVF_STRIDE * 4, &k.i_envf0, &k.i_envf1);
@@ -1211,16 +1182,11 @@ static int tile_plan(const PbhcTrackCfg& c, const PbhcTableDesc& tab, const Pbhc
     P.x.scale[s] = c.obs_scale[s];
   }
   if (off - k.o_rows < 8 * 32 * kTE) take(8 * 32 * kTE - (off - k.o_rows));  // (the rows region also parks the scalars / the warps' sums)
-  k.q_rew = slab_out(io.rew_buf, c.use_vec_reward ? (c.n_rewards + 1) * 4 : 4);
-  k.q_es = slab_out(io.episode_sums, c.n_episode_sums * 4);
-  k.q_envf = slab_out(io.env_f32, PBHC_ENVF_STRIDE * 4);
-  k.q_ep = slab_out(io.episode_length_buf, 8);
-  k.q_reset = slab_out(io.reset_buf, 8);
-  k.q_lact = slab_out(io.last_actions, D * 4);
-  k.q_ldpos = slab_out(io.last_dof_pos, D * 4);
-  k.q_ldvel = slab_out(io.last_dof_vel, D * 4);
-  P.bulk_ok = ok ? 1 : 0;
+  const int rows_end = off;
+  for (const void* g : {(const void*)io.rew_buf, (const void*)io.env_f32, (const void*)io.last_dof_pos}) if ((uintptr_t)g & 15) ok = false;
+  if (!ok) return 0;  // (0: not for this kernel - the caller falls back to the warp-per-env kernel)
   if (off > 220 * 1024) { set_error("pbhc_track_step: shared memory %d B too large", off); return PBHC_E_RANGE; }
+  if (((rows_end - k.o_rows) >> 2) > 32767) { set_error("pbhc_track_step: observation rows too wide for the 16-bit history map"); return PBHC_E_RANGE; }
   return off;
 }
 
@@ -1233,6 +1199,7 @@ int track_tile_launch(const PbhcTrackCfg& c, const PbhcTableDesc& tab, const Pbh
   static thread_local TileParams P;
   const int shmem = tile_plan(c, tab, io, n, P);
   if (shmem < 0) return shmem;
+  if (shmem == 0) return 1;  // unaligned tensors: not an error, the warp-per-env kernel takes the step
   bool noise = false;
   for (int s = 0; s < kSrcT; ++s) noise |= c.obs_noise[s] != 0.0f;
   const void* kern = noise ? (const void*)track_tile_kernel<true> : (const void*)track_tile_kernel<false>;
@@ -1264,7 +1231,8 @@ int track_tile_launch(const PbhcTrackCfg& c, const PbhcTableDesc& tab, const Pbh
 int track_tile_prepare(const PbhcTrackCfg& c, const PbhcTableDesc& tab, const PbhcTrackIO& io) {
   static thread_local TileParams P;
   const int shmem = tile_plan(c, tab, io, 8, P);
-  if (shmem < 0) return shmem;
+  if (shmem <= 0) return shmem < 0 ? shmem : PBHC_E_ALIGN;
+  g_track_info[0] = 2; g_track_info[1] = 0; g_track_info[2] = shmem; g_track_info[3] = 0;  // (pbhc_track_launch_info after a warm-up: the planned shared memory)
   bool noise = false;
   for (int s = 0; s < kSrcT; ++s) noise |= c.obs_noise[s] != 0.0f;
   return jit_track_tile(P.k, P.x, noise, nullptr) == 0 ? PBHC_OK : PBHC_E_CUDA;
