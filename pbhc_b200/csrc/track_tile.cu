@@ -164,6 +164,12 @@ struct SmallSlot { const char* src; int row_bytes; int dst; };  // one 4-byte wo
 struct Rows { float* rows; float* ghist; int e; };   // observation slabs (shared), the env's global history row, tile-local env
 
 __device__ __forceinline__ float clampf(float v, float c) { return fminf(fmaxf(v, -c), c); }
+// sqrtf / norms whose argument is very often an exact zero (contact forces of bodies in the air, velocities of standing feet):
+// sqrtf takes an out-of-line slow path for zero and denormal arguments, and one such lane sends the whole warp through it.
+// The zero lanes compute sqrtf(1) instead and the result is put back: identical values, no slow path.
+__device__ __forceinline__ float sqrt_z(float x) { const bool z = x == 0.0f; const float r = sqrtf(z ? 1.0f : x); return z ? 0.0f : r; }
+__device__ __forceinline__ float norm3_z(float x, float y, float z) { return sqrt_z(__fmaf_rn(z, z, __fmaf_rn(y, y, x * x))); }
+__device__ __forceinline__ float norm2_z(float x, float y) { return sqrt_z(__fmaf_rn(y, y, x * x)); }
 
 // (value + U(-1,1) * noise) * scale with an independent draw per destination (helpers.py:128-152)
 __device__ __noinline__ void emit_noisy_t(const TileTables& T, const Rows& R, int k, int el, float raw, float clip, const NoiseKeyT& nk) {
@@ -612,7 +618,7 @@ __device__ __forceinline__ void track_tile_body(const TileParams& P) {
         const float dja = (omb * __ldg(r0 + e_dp + d) + b * __ldg(r1 + e_dp + d)) - dpos;   // motion_tracking.py:661-665
         adja = fabsf(dja);
         const float djv = (omb * __ldg(r0 + e_dv + d) + b * __ldg(r1 + e_dv + d)) - dvel;
-        const float dact = lact - act, dacc = (ldv - dvel) / dt;
+        const float dact = lact - act, dacc = (ldv - dvel) * (1.0f / dt);  // (tolerance-checked penalty term; the division's slow path is taken for a zero difference)
         const float lim_t = T.lim_tq[d];
         float* dp_ = scr + d;
         dp_[DR_DJA2 * D] = dja * dja; dp_[DR_DJV2 * D] = djv * djv; dp_[DR_TQ2 * D] = tq * tq; dp_[DR_DACT2 * D] = dact * dact;
@@ -652,7 +658,7 @@ __device__ __forceinline__ void track_tile_body(const TileParams& P) {
               ((unsigned long long)V_TQ2 << 16) | ((unsigned long long)V_DACT2 << 24) | ((unsigned long long)V_DV2 << 32) | ((unsigned long long)V_ACC2 << 40) |
               ((unsigned long long)V_LIM_POS << 48) | ((unsigned long long)V_LIM_VEL << 56);
           const int slot = k == DR_LTQ ? (int)V_LIM_TQ : (int)((slots >> (8 * k)) & 0xffull);
-          rve[slot] = k <= DR_DJV2 ? tot / (float)D : tot;
+          rve[slot] = k <= DR_DJV2 ? tot * (1.0f / (float)D) : tot;  // (a mean: within 1 ulp of the division, whose slow path a zero sum would take)
           if (k == DR_DJA2) rve[V_JOINT_N] = sqrtf(tot);
         }
       }
@@ -715,7 +721,8 @@ __device__ __forceinline__ void track_tile_body(const TileParams& P) {
           if (nrm > far_thr) far = 1;
           if (j < Jb && (((unsigned long long)KC(penalised_mask) >> j) & 1ull)) {
             const float* fc = s_cf + 3 * j;
-            collide = norm3(fc[0], fc[1], fc[2]) > 0.1f;
+            // |f| > 0.1 without the square root: sqrtf is monotonic and correctly rounded, 0x1.47ae16p-7 is the largest fp32 whose root is <= 0.1f
+            collide = __fmaf_rn(fc[2], fc[2], __fmaf_rn(fc[1], fc[1], fc[0] * fc[0])) > 0x1.47ae16p-7f;
           }
           {
             const V3 dl = quat_rotate_z(hz, hw, dp);  // motion_tracking.py:694-697
@@ -753,7 +760,7 @@ __device__ __forceinline__ void track_tile_body(const TileParams& P) {
         const float* bs = s_body + 13 * fb;
         const float last_c = s_envf[4 + lane];
         air_f = s_envf[2 + lane];
-        const float fn = norm3(fc[0], fc[1], fc[2]);
+        const float fn = norm3_z(fc[0], fc[1], fc[2]);
         contact_f = fn > 1.0f ? 1.0f : 0.0f;                                   // legged_robot_base.py:352-353
         const float filt = (contact_f != 0.0f || last_c != 0.0f) ? 1.0f : 0.0f;
         if (KC(contact_size)) x_cm = fabsf(filt - (omb * __ldg(r0 + e_c + lane) + b * __ldg(r1 + e_c + lane)));
@@ -765,9 +772,9 @@ __device__ __forceinline__ void track_tile_body(const TileParams& P) {
           air_f *= fz ? 0.0f : 1.0f;
         }
         x_force = fmaxf(fn - KC(max_contact_force), 0.0f);                        // :1321-1323
-        x_stumble = norm2(fc[0], fc[1]) > 5.0f * fabsf(fc[2]);                  // :1325-1328
-        x_slip = norm3(bs[7], bs[8], bs[9]) * contact_f;                        // legged_robot_base.py:1004-1010
-        x_fslip = contact_f * norm2(bs[7], bs[8]);                              // :1012-1017
+        x_stumble = norm2_z(fc[0], fc[1]) > 5.0f * fabsf(fc[2]);                  // :1325-1328
+        x_slip = norm3_z(bs[7], bs[8], bs[9]) * contact_f;                        // legged_robot_base.py:1004-1010
+        x_fslip = contact_f * norm2_z(bs[7], bs[8]);                              // :1012-1017
       }
       x_air += __shfl_xor_sync(0xffffffffu, x_air, 1); x_force += __shfl_xor_sync(0xffffffffu, x_force, 1);
       x_slip += __shfl_xor_sync(0xffffffffu, x_slip, 1); x_fslip += __shfl_xor_sync(0xffffffffu, x_fslip, 1);
