@@ -3,6 +3,9 @@
 // are parked in per-warp shared memory).  Global I/O is staged through shared memory in chunks of
 // kChunk joints so every global access is a run of contiguous floats per pose.
 // Reference: utils/motion_lib/torch_humanoid_batch.py:168-269; isaac_utils/rotations.py:519-647.
+#include <cstdio>
+#include <cstdlib>
+
 #include "common.cuh"
 
 namespace pbhc {
@@ -322,6 +325,141 @@ __global__ void __launch_bounds__(kFkWarps * 32, 16) fk_kernel(const __grid_cons
   }
 }
 
+
+// ---- the limb kernel: lane = (pose, limb) ------------------------------------------------------------------------------------------
+// A warp owns 8 consecutive poses; the tree is cut into up to 4 joint ranges ("limbs") and the 4 lanes of a pose walk one
+// each - first, without quaternion output, the ancestors of its range that lie outside it, then the range.  Every world
+// transform a lane computes goes to the warp's staging area, which has the layout of the global outputs of the 8 poses
+// ([pose][joint][..], contiguous and 16-byte aligned in global memory), so a parent that is not the previous step is read back from
+// there (the same lane wrote it), ancestors computed by several limbs are written with identical values, and the tile
+// leaves as three contiguous copies of 16 bytes per lane.  Per pose ~2.3x fewer warp-instructions than a thread per pose
+// (whose 27-joint chain is serial and whose staged chunks leave float by float), and a batch of 4096 poses still fills the GPU.
+constexpr int kLimbs = 4, kLimbPoses = 8, kLimbWarps = 2;
+struct FkLimbParams {
+  int J, n_limbs, max_steps;
+  int8_t parent[PBHC_MAX_JOINTS];
+  int8_t step_joint[kLimbs][PBHC_MAX_JOINTS];  // joint of step s of limb k (its outside ancestors root first, then its range), -1 = no step
+  int8_t n_silent[kLimbs];
+  float off[PBHC_MAX_JOINTS * 3];
+  float lrot[PBHC_MAX_JOINTS * 9];
+};
+
+template <bool kFast>
+__global__ void __launch_bounds__(kLimbWarps * 32) fk_limb_kernel(const __grid_constant__ FkLimbParams P, const float* __restrict__ pose_aa,
+                                                                 const float* __restrict__ trans, int64_t n, float* __restrict__ pos,
+                                                                 float* __restrict__ rotmat, float* __restrict__ quat, int aligned) {
+  extern __shared__ __align__(16) float smem[];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int J = P.J;
+  // block constants: [J][12] = local rotation (9) + offset (3), then parent / step tables as ints
+  float* s_tree = smem;
+  int* s_parent = reinterpret_cast<int*>(smem + 12 * J);
+  int* s_step = s_parent + J;                       // [kLimbs][max_steps]
+  const int const_floats = (12 * J + J + kLimbs * P.max_steps + 3) & ~3;
+  for (int i = threadIdx.x; i < J; i += blockDim.x) {
+    for (int c = 0; c < 9; ++c) s_tree[i * 12 + c] = P.lrot[i * 9 + c];
+    for (int c = 0; c < 3; ++c) s_tree[i * 12 + 9 + c] = P.off[i * 3 + c];
+    s_parent[i] = P.parent[i];
+  }
+  for (int i = threadIdx.x; i < kLimbs * P.max_steps; i += blockDim.x) s_step[i] = P.step_joint[i / P.max_steps][i % P.max_steps];
+  __syncthreads();
+  // per warp: two input buffers [8][3J] + [8][3], staging pos [8][3J] | rot [8][9J] | quat [8][4J]
+  const int in_floats = (kLimbPoses * 3 * J + kLimbPoses * 3 + 3) & ~3;
+  const int out_floats = kLimbPoses * 16 * J;
+  float* w_base = smem + const_floats + warp * (2 * in_floats + out_floats);
+  float* st_pos = w_base + 2 * in_floats, *st_rot = st_pos + kLimbPoses * 3 * J, *st_quat = st_rot + kLimbPoses * 9 * J;
+  const int p = lane >> 2, k = lane & 3;
+  const int n_silent = P.n_silent[k];
+  const int64_t n_tiles = (n + kLimbPoses - 1) / kLimbPoses, tstep = (int64_t)gridDim.x * kLimbWarps;
+
+  auto request = [&](int64_t t, int buf) {  // the tile's axis-angles and root translations -> input buffer `buf`
+    float* dst = w_base + buf * in_floats;
+    const int64_t p0 = t * kLimbPoses;
+    const int np = (int)min((int64_t)kLimbPoses, n - p0);
+    const float* g = pose_aa + p0 * (3 * J);
+    const float* gt = trans + p0 * 3;
+    if (aligned && np == kLimbPoses) {
+      const uint32_t d = (uint32_t)__cvta_generic_to_shared(dst);
+      for (int i = lane; i < (kLimbPoses * 3 * J) / 4; i += 32) asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d + 16 * i), "l"(g + 4 * i) : "memory");
+      if (lane < kLimbPoses * 3 / 4) asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d + 4 * (kLimbPoses * 3 * J) + 16 * lane), "l"(gt + 4 * lane) : "memory");
+    } else {
+      const uint32_t d = (uint32_t)__cvta_generic_to_shared(dst);
+      for (int i = lane; i < np * 3 * J; i += 32) asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d + 4 * i), "l"(g + i) : "memory");
+      if (lane < np * 3) asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d + 4 * (kLimbPoses * 3 * J + lane)), "l"(gt + lane) : "memory");
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+
+  int64_t t = (int64_t)blockIdx.x * kLimbWarps + warp;
+  if (t < n_tiles) request(t, 0);
+  for (int buf = 0; t < n_tiles; t += tstep, buf ^= 1) {
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    __syncwarp();
+    if (t + tstep < n_tiles) request(t + tstep, buf ^ 1);
+    const int64_t p0 = t * kLimbPoses;
+    const int np = (int)min((int64_t)kLimbPoses, n - p0);
+    const float* in = w_base + buf * in_floats;
+    if (p < np && k < P.n_limbs) {
+      const float* a_row = in + p * (3 * J);
+      M3 Rc;
+      float pc[3] = {0.f, 0.f, 0.f};
+#pragma unroll
+      for (int c = 0; c < 9; ++c) Rc.m[c] = 0.f;
+      int prev = -2;
+      for (int s = 0; s < P.max_steps; ++s) {
+        const int i = s_step[k * P.max_steps + s];
+        if (i < 0) break;
+        const float* a = a_row + 3 * i;
+        const M3 Mj = kFast ? aa_to_mat_fast(a[0], a[1], a[2]) : aa_to_mat(a[0], a[1], a[2]);
+        const int par = s_parent[i];
+        if (par < 0) {
+          Rc = Mj;
+          const float* tr = in + kLimbPoses * 3 * J + p * 3;
+          pc[0] = tr[0]; pc[1] = tr[1]; pc[2] = tr[2];
+        } else {
+          const float* tc = s_tree + i * 12;
+          M3 L;
+#pragma unroll
+          for (int c = 0; c < 9; ++c) L.m[c] = tc[c];
+          const M3 LMj = matmul3(L, Mj);
+          if (par != prev) {  // a branch point further up: this lane staged its transform earlier
+            const float* sr = st_rot + (p * J + par) * 9;
+            const float* sp = st_pos + (p * J + par) * 3;
+#pragma unroll
+            for (int c = 0; c < 9; ++c) Rc.m[c] = sr[c];
+            pc[0] = sp[0]; pc[1] = sp[1]; pc[2] = sp[2];
+          }
+          const float ox = tc[9], oy = tc[10], oz = tc[11];
+          float np_[3];
+#pragma unroll
+          for (int c = 0; c < 3; ++c) np_[c] = __fmaf_rn(Rc.m[c * 3 + 2], oz, __fmaf_rn(Rc.m[c * 3 + 1], oy, Rc.m[c * 3] * ox)) + pc[c];
+          pc[0] = np_[0]; pc[1] = np_[1]; pc[2] = np_[2];
+          Rc = matmul3(Rc, LMj);
+        }
+        prev = i;
+        float* op = st_pos + (p * J + i) * 3;
+        op[0] = pc[0]; op[1] = pc[1]; op[2] = pc[2];
+        float* orot = st_rot + (p * J + i) * 9;
+#pragma unroll
+        for (int c = 0; c < 9; ++c) orot[c] = Rc.m[c];
+        if (quat && s >= n_silent) { if (kFast) mat_to_quat_xyzw_fast(Rc, st_quat + (p * J + i) * 4); else mat_to_quat_xyzw(Rc, st_quat + (p * J + i) * 4); }
+      }
+    }
+    __syncwarp();
+    // the tile leaves: three contiguous runs of np poses
+    auto flush = [&](const float* st, float* g, int row) {
+      float* dst = g + p0 * row;
+      const int nf = np * row;
+      if (aligned && np == kLimbPoses) { for (int i = lane; i < nf / 4; i += 32) reinterpret_cast<float4*>(dst)[i] = reinterpret_cast<const float4*>(st)[i]; }
+      else { for (int i = lane; i < nf; i += 32) dst[i] = st[i]; }
+    };
+    flush(st_pos, pos, 3 * J);
+    if (rotmat) flush(st_rot, rotmat, 9 * J);
+    if (quat) flush(st_quat, quat, 4 * J);
+    __syncwarp();
+  }
+}
+
 }  // namespace pbhc
 
 static int fk_launch(const PbhcTree* tree, const float* pose_aa, const float* trans, int64_t n, float* pos,
@@ -352,6 +490,109 @@ static int fk_launch(const PbhcTree* tree, const float* pose_aa, const float* tr
     P.load_slot[i] = P.save_slot[p];
   }
   if (n == 0) return PBHC_OK;
+  {  // the limb kernel when the tree cuts into 2..4 ranges (any pre-order numbered tree with a few branches does)
+    static thread_local FkLimbParams LP;
+    static thread_local int lp_valid = 0;           // 0: not built, 1: usable, -1: this tree does not split
+    static thread_local int8_t lp_parents[PBHC_MAX_JOINTS];
+    static thread_local int lp_J = 0;
+    bool same = lp_valid != 0 && lp_J == J;
+    for (int i = 0; same && i < J; ++i) same = lp_parents[i] == P.parent[i];
+    if (!same) {
+      lp_J = J;
+      for (int i = 0; i < J; ++i) lp_parents[i] = P.parent[i];
+      int depth[PBHC_MAX_JOINTS];
+      for (int i = 0; i < J; ++i) depth[i] = P.parent[i] < 0 ? 0 : depth[P.parent[i]] + 1;
+      // pre-order walk (children in index order): in this order every parent of a contiguous range that lies outside the
+      // range is an ancestor of the range's first joint.  (The joint numbering itself need not be pre-order: the extended
+      // bodies of torch_humanoid_batch.py:80-102 are appended at the end, whatever their parent.)
+      int ord[PBHC_MAX_JOINTS], n_ord = 0;
+      {
+        int stack[PBHC_MAX_JOINTS], sp = 0;
+        stack[sp++] = 0;
+        while (sp > 0) {
+          const int v = stack[--sp];
+          ord[n_ord++] = v;
+          for (int c2 = J - 1; c2 > v; --c2) if (P.parent[c2] == v) stack[sp++] = c2;  // (pushed in reverse: popped in index order)
+        }
+      }
+      auto walkable = [&](int b, int e) {  // positions [b, e) of ord
+        bool anc[PBHC_MAX_JOINTS] = {false}, in[PBHC_MAX_JOINTS] = {false};
+        for (int a = P.parent[ord[b]]; a >= 0; a = P.parent[a]) anc[a] = true;
+        for (int i = b; i < e; ++i) {
+          const int q = P.parent[ord[i]];
+          if (!((q >= 0 && (in[q] || anc[q])) || (q < 0 && i == 0))) return false;
+          in[ord[i]] = true;
+        }
+        return true;
+      };
+      int best_cost = 1 << 30, best_cut[kLimbs + 1] = {0, J, J, J, J}, best_n = 1;
+      // cuts 0 = c0 < c1 <= c2 <= c3 <= c4 = J (equal cuts = fewer limbs); cost = the longest walk (ancestors + range)
+      for (int c1 = 1; c1 <= J && n_ord == J; ++c1)
+        for (int c2 = c1; c2 <= J; ++c2)
+          for (int c3 = c2; c3 <= J; ++c3) {
+            const int cut[kLimbs + 1] = {0, c1, c2, c3, J};
+            int cost = 0, nl = 0;
+            bool ok = true;
+            for (int k = 0; k < kLimbs && ok; ++k) {
+              const int bb = cut[k], ee = cut[k + 1];
+              if (ee == bb) continue;
+              if (nl != k) { ok = false; break; }  // empty limbs only at the end
+              ++nl;
+              const int w = depth[ord[bb]] + (ee - bb);
+              if (w > cost) cost = w;
+              if (w >= best_cost || !walkable(bb, ee)) ok = false;
+            }
+            if (ok && cost < best_cost) { best_cost = cost; best_n = nl; for (int k = 0; k <= kLimbs; ++k) best_cut[k] = cut[k]; }
+          }
+      if (best_n < 2) lp_valid = -1;
+      else {
+        LP.J = J; LP.n_limbs = best_n; LP.max_steps = best_cost;
+        for (int i = 0; i < J; ++i) LP.parent[i] = P.parent[i];
+        for (int i = 0; i < 3 * J; ++i) LP.off[i] = 0.f;
+        for (int k = 0; k < kLimbs; ++k) {
+          for (int q = 0; q < PBHC_MAX_JOINTS; ++q) LP.step_joint[k][q] = -1;
+          LP.n_silent[k] = 0;
+          if (k >= best_n) continue;
+          const int bb = best_cut[k], ee = best_cut[k + 1];
+          int chain[PBHC_MAX_JOINTS], d = 0;
+          for (int a = P.parent[ord[bb]]; a >= 0; a = P.parent[a]) chain[d++] = a;
+          LP.n_silent[k] = (int8_t)d;
+          int q = 0;
+          for (int i = d - 1; i >= 0; --i) LP.step_joint[k][q++] = (int8_t)chain[i];
+          for (int i = bb; i < ee; ++i) LP.step_joint[k][q++] = (int8_t)ord[i];
+        }
+        lp_valid = 1;
+        if (const char* v = getenv("PBHC_FK_VERBOSE")) if (v[0] == '1')
+          fprintf(stderr, "[pbhc fk] %d joints -> %d limbs, cuts %d %d %d, longest walk %d steps\n", J, best_n, best_cut[1], best_cut[2], best_cut[3], best_cost);
+      }
+    }
+    if (lp_valid == 1) {
+      for (int i = 0; i < 3 * J; ++i) LP.off[i] = P.off[i];     // (the constants may change between calls with the same topology)
+      for (int i = 0; i < 9 * J; ++i) LP.lrot[i] = P.lrot[i];
+      const int const_floats = (12 * J + J + kLimbs * LP.max_steps + 3) & ~3;
+      const int in_floats = (kLimbPoses * 3 * J + kLimbPoses * 3 + 3) & ~3;
+      const size_t shmem = (size_t)(const_floats + kLimbWarps * (2 * in_floats + kLimbPoses * 16 * J)) * sizeof(float);
+      auto kern = fast ? fk_limb_kernel<true> : fk_limb_kernel<false>;
+      static thread_local size_t configured[2] = {0, 0};
+      static thread_local int per_sm[2] = {0, 0};
+      if (shmem > configured[fast]) {
+        if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shmem) != cudaSuccess) return check_launch("pbhc_fk(attr)");
+        (void)cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+        configured[fast] = shmem;
+        int m = 0;
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&m, kern, kLimbWarps * 32, shmem);
+        per_sm[fast] = m < 1 ? 1 : m;
+      }
+      const int64_t n_tiles = (n + kLimbPoses - 1) / kLimbPoses;
+      int64_t blocks = (n_tiles + kLimbWarps - 1) / kLimbWarps;
+      const int64_t cap = 148LL * per_sm[fast];
+      if (blocks > cap) blocks = cap;
+      const int aligned = !(((uintptr_t)pose_aa | (uintptr_t)trans | (uintptr_t)pos | (uintptr_t)rotmat | (uintptr_t)quat_xyzw) & 15);
+      kern<<<(unsigned)blocks, kLimbWarps * 32, shmem, (cudaStream_t)stream>>>(LP, pose_aa, trans, n, pos, rotmat, quat_xyzw, aligned);
+      return check_launch("pbhc_fk");
+    }
+  }
+  // (trees that do not split - a single chain - take the thread-per-pose kernel below)
   // two parts when the batch alone cannot fill the machine (<= 64 warps per SM) and the tree splits: the cut s is the joint
   // nearest J/2 such that every joint >= s has its parent either >= s or among the ancestors of s (a chain of at most 8)
   P.n_parts = 1; P.part_begin[0] = 0; P.part_end[0] = J; P.n_silent[0] = 0; P.n_silent[1] = 0;

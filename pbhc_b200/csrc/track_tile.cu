@@ -1000,8 +1000,9 @@ __device__ __forceinline__ void track_tile_body(const TileParams& P) {
         if (!has) return;
         const float* src = rows + row_base + e * gd;
         float* dst = g + n * gd;
-        if ((gd & 3) == 0) { for (int i = lane; i < (gd >> 2); i += 32) reinterpret_cast<float4*>(dst)[i] = reinterpret_cast<const float4*>(src)[i]; }
-        else if ((gd & 1) == 0) { for (int i = lane; i < (gd >> 1); i += 32) reinterpret_cast<float2*>(dst)[i] = reinterpret_cast<const float2*>(src)[i]; }
+        const uintptr_t al = reinterpret_cast<uintptr_t>(g);  // (a storage slot the caller redirected the group to may start anywhere)
+        if ((gd & 3) == 0 && (al & 15) == 0) { for (int i = lane; i < (gd >> 2); i += 32) reinterpret_cast<float4*>(dst)[i] = reinterpret_cast<const float4*>(src)[i]; }
+        else if ((gd & 1) == 0 && (al & 7) == 0) { for (int i = lane; i < (gd >> 1); i += 32) reinterpret_cast<float2*>(dst)[i] = reinterpret_cast<const float2*>(src)[i]; }
         else { for (int i = lane; i < gd; i += 32) dst[i] = src[i]; }
       };
       row_out(KC(n_groups) > 0, KC(row_base0), KC(gdim0), io.obs[0]);
@@ -1138,7 +1139,7 @@ static int tile_plan(const PbhcTrackCfg& c, const PbhcTableDesc& tab, const Pbhc
     if ((uintptr_t)g & 15) ok = false;
   };
   auto slab_out = [&](void* g, int row_bytes) {
-    if ((uintptr_t)g & 15) ok = false;
+    if ((uintptr_t)g & 3) ok = false;
     return take(kTE * row_bytes);
   };
   k.i_body = slab_in(io.body_state, Jb * 13 * 4, io.body_env_stride * 4);
