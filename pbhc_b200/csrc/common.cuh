@@ -21,6 +21,7 @@ int check_launch(const char* what);
 struct Q4 { float x, y, z, w; };  // xyzw
 struct V3 { float x, y, z; };
 
+__device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 __device__ __forceinline__ float clip01(float v) { return fminf(fmaxf(v, 0.0f), 1.0f); }
 
 // torch.linalg.vector_norm over 3 contiguous floats on CPU = sqrt(fma(z,z,fma(y,y,x*x)))

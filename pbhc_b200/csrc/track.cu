@@ -844,6 +844,11 @@ __global__ void __launch_bounds__(kTW * 32, kGeneral ? 2 : F_BPS) track_kernel(c
             const float* q0 = tab.records + fb.f0 * tab.rec_stride;
             const float* q1 = tab.records + fb.f1 * tab.rec_stride;
             const float bb = fb.blend, ob = 1.0f - bb;
+            // the passes below read this step's dof positions and key-body positions: on a library larger than L2 every one of
+            // those reads would be a dependent HBM access - ask for the lines now (positions: J x 12 B, dofs: D x 4 B per frame)
+            for (int o = 0; o < 3 * J; o += 32) { prefetch_l2(q0 + e_pos + o); prefetch_l2(q1 + e_pos + o); }
+            for (int o = 0; o < D; o += 32) { prefetch_l2(q0 + e_dp + o); prefetch_l2(q1 + e_dp + o); }
+            prefetch_l2(q0 + e_dp + D - 1); prefetch_l2(q1 + e_dp + D - 1);
             const float4 a0 = __ldg(reinterpret_cast<const float4*>(q0)), a1 = __ldg(reinterpret_cast<const float4*>(q1));
             const Q4 rq = slerp({a0.x, a0.y, a0.z, a0.w}, {a1.x, a1.y, a1.z, a1.w}, bb);
             const V3 rvl = quat_rotate_inverse(rq, {ob * __ldg(q0 + e_vel) + bb * __ldg(q1 + e_vel), ob * __ldg(q0 + e_vel + 1) + bb * __ldg(q1 + e_vel + 1),
