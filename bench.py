@@ -143,9 +143,16 @@ def cpu_reference(n_envs, steps, warmup, seconds=None, with_fk=True, seed=0, wor
     """Times `steps` env steps (or as many as fit in `seconds`, at least 3) of the CPU oracle on n_envs envs."""
     import torch
     from oracle import pbhc_oracle as O, pbhc_oracle_env as OE
-    from tests._util import oracle_clip, oracle_tree
     from pbhc_b200 import synth
-    from pbhc_b200.fixtures import env_config
+    from pbhc_b200.fixtures import env_config, tree_json, motion_npz
+
+    def oracle_tree(tag):
+        t = tree_json(tag)
+        return O.make_tree(t["names"], t["parents"], t["offsets"], t["local_rot_wxyz"], t["num_bodies"], t["dof_axis"])
+
+    def oracle_clip(tag, name):
+        m = motion_npz(name)
+        return O.load_clip(oracle_tree(tag), m["pose_aa"], m["root_trans_offset"], int(m["fps"]), m.get("contact_mask"))
     from pbhc_b200.spec import TrackSpec
     from pbhc_b200.fixtures import CLIPS29
     from pbhc_b200.workload import CASE, CASE_C, CLIP
@@ -191,19 +198,31 @@ def cpu_reference(n_envs, steps, warmup, seconds=None, with_fk=True, seed=0, wor
                 torch=torch.__version__)
 
 
+def port_calibration():
+    """the port against the unmodified reference env, timed in the build container (tools/calibrate_cpu_port.py)"""
+    p = os.path.join(ROOT, "profiles", "r02_cpu_port_calibration.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            return json.load(f)
+    return None
+
+
 def run_reference_arm(a):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
-    r = cpu_reference(a.cpu_envs, a.steps, a.warmup, seconds=150.0, with_fk=not a.no_fk, workload=a.workload)
-    sample = (f"{r['n_envs']} envs per step (a slice of the {a.envs}-env workload), {r['steps']} timed steps after {a.warmup} warm-up; "
+    # the arm runs the GPU arm's config: all a.envs envs per step (the oracle port steps 65536 envs in about a second on the
+    # host cores); the time budget only guards against a very slow host
+    r = cpu_reference(a.envs, a.steps, a.warmup, seconds=240.0, with_fk=not a.no_fk, workload=a.workload)
+    sample = (f"{r['n_envs']} envs per step (the whole {a.envs}-env workload), {r['steps']} timed steps after {a.warmup} warm-up; "
               "CPU oracle port of the reference torch path (oracle/pbhc_oracle_env.py, pinned bit-exact to the reference env), "
               f"torch {r['torch']} with {r['cores']} threads")
     line = {"impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": a.gpus, "steps": r["steps"],
             "warmup": a.warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
             "config": {"workload": WORKLOAD, "envs_per_gpu": a.envs, "fk_in_step": not a.no_fk, "sample_envs": r["n_envs"]},
-            "cpu_baseline": {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "port", "sample": sample},
+            "cpu_baseline": {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "port", "sample": sample,
+                             "calibration": port_calibration()},
             "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line), flush=True)

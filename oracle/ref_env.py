@@ -1,8 +1,9 @@
 """TEST INFRASTRUCTURE ONLY - runs the UNMODIFIED reference env classes (LeggedRobotMotionTracking /
 LeggedRobotGeneralTracking) headless on a fake simulator made of synthetic tensors with Isaac Gym's
 layouts (simulator/isaacgym/isaacgym.py:596-618).  Used by tools/make_golden_env_step.py to dump golden
-fixtures that pin oracle/pbhc_oracle_env.py, and by bench.py --impl reference when the reference tree
-is present.  Needs /root/reference: never imported on the GPU box by tests, smoke() or the product.
+fixtures that pin oracle/pbhc_oracle_env.py, and by tools/calibrate_cpu_port.py to time the reference's own
+step beside the port that bench.py times (bench.py itself never imports this module: /root/reference does not
+exist on the GPU box).  Needs /root/reference: never imported on the GPU box by tests, smoke() or the product.
 """
 import os
 import re
