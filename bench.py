@@ -346,7 +346,7 @@ def run_b200_arm(a):
                    "l2": f"inputs larger than L2 ({bytes_step * N / 1e6:.0f} MB touched per step per GPU vs 126 MB L2)",
                    "parallelism": f"envs sharded over {world} GPU(s); one all-reduce of 64 doubles per step" if world > 1 else "single GPU",
                    "reset_fraction_last_step": resets, "track_launch": ts.launch_info()},
-        "roofline": {"bound": "hbm", "kernel": "track_kernel (pbhc_track_step: fused K1+K3 + block-partials reduction)",
+        "roofline": {"bound": "hbm", "kernel": "pbhc_track_step: fused K1+K3 kernel (%s) + block-partials reduction" % ts.launch_info()["kernel"],
                      "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": ncu_traffic() if a.workload == "A" else None,
                      "peak_source": peak_src, "algorithmic_bytes_per_env_step": bytes_step, "kernel_ms": track_ms,
                      "envs_per_launch": N},
@@ -364,7 +364,7 @@ def run_b200_arm(a):
         line["cpu_baseline"] = {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "port",
                                 "sample": f"{r['n_envs']} envs per step, {r['steps']} steps in ~{a.cpu_seconds:.0f} s, CPU oracle port of the "
                                           f"reference torch path (torch {r['torch']}, {r['cores']} threads), FK {'in' if with_fk else 'not in'} step",
-                                "ms_per_step": r["ms_per_step"]}
+                                "ms_per_step": r["ms_per_step"], "calibration": port_calibration()}
     print(json.dumps(line), flush=True)
     return _finish(torch, dist, world, graph)
 
