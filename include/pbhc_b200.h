@@ -416,6 +416,20 @@ int pbhc_compact_ids(const int64_t* flags, int64_t n, int32_t* ids, int32_t* cou
 #define PBHC_COMPACT_STATIC_MAX_N 16777216
 int pbhc_compact_ids_static(const int64_t* flags, int64_t n, int32_t* ids, int32_t* count, void* stream);
 
+/* ---- the cross-rank exchange of the path.  The reference is single-process (no torch.distributed anywhere); when
+ * the envs are sharded over the GPUs of a box the path needs exactly two tiny SUM all-reduces: the PBHC_ACC statistics of a
+ * step (between pbhc_track_step and pbhc_track_finalize) and (n, sum, sum of squares) of the advantages (between pbhc_gae
+ * and pbhc_adv_normalize).  This entry point does them over NVLink peer memory in ONE single-block kernel per rank -
+ * peer stores, release/acquire flags, a rank-ordered (deterministic, rank-identical) sum - instead of a library
+ * collective whose cost at this size is all latency.  data [n] doubles, summed in place.  peer_buffers / peer_signal_pads:
+ * DEVICE arrays [world] of device pointers to every rank's buffer (>= 2 * world * PBHC_PEER_MAX_DOUBLES doubles, zero at
+ * first use) and signal pad (uint32 entries; entries signal_base .. signal_base + world are used), all mapped in this
+ * process (torch symmetric memory: pbhc_b200/dist.py).  counter: this rank's device uint32, zero at first use, advanced
+ * by the kernel - the call can be captured in a CUDA graph.  Every rank of the group must make the same sequence of calls. */
+#define PBHC_PEER_MAX_DOUBLES 256
+int pbhc_peer_allreduce_sum(double* data, int32_t n, const uint64_t* peer_buffers, const uint64_t* peer_signal_pads,
+                            uint32_t* counter, int32_t rank, int32_t world, int32_t signal_base, void* stream);
+
 /* ---- actuation half of the env step: LeggedRobotBase._pre_physics_step
  * (envs/legged_base_task/legged_robot_base.py:268-286) and _compute_torques (:795-838). */
 typedef struct PbhcActuationCfg {

@@ -55,7 +55,7 @@ _lib = None
 
 EXPORTS = ["pbhc_abi_version", "pbhc_struct_size", "pbhc_last_error", "pbhc_lookup", "pbhc_fk", "pbhc_fk_exact", "pbhc_gae", "pbhc_adv_normalize", "pbhc_clip_prepare", "pbhc_clips_prepare",
            "pbhc_track_max_blocks", "pbhc_track_launch_info", "pbhc_track_specialize", "pbhc_track_step", "pbhc_track_finalize", "pbhc_gather_rows", "pbhc_gather_keys", "pbhc_timeout_bootstrap", "pbhc_blend_frames", "pbhc_traj_metrics", "pbhc_pre_physics", "pbhc_compute_torques",
-           "pbhc_compact_scratch_ints", "pbhc_compact_ids", "pbhc_compact_ids_static"]
+           "pbhc_compact_scratch_ints", "pbhc_compact_ids", "pbhc_compact_ids_static", "pbhc_peer_allreduce_sum"]
 
 
 def lib():
@@ -140,6 +140,7 @@ def stream_ptr(device=None):
 # ---- K3 structs (mirror include/pbhc_b200.h exactly) ------------------------------------------------
 MAX_DOF, MAX_REWARDS, MAX_EXT, MAX_FEET, MAX_OBS_GROUPS, MAX_HIST_KEYS, MAX_HIST_DST = 32, 32, 4, 4, 4, 8, 16
 NUM_OBS_SRC, NUM_SIGMA, ENVF_STRIDE, SCALARS, ACC, MAX_KEY, MAX_FUTURE = 35, 17, 8, 112, 64, 16, 32
+PEER_MAX_DOUBLES = 256
 COMPACT_STATIC_MAX_N = 1 << 24  # PBHC_COMPACT_STATIC_MAX_N: flags per call of pbhc_compact_ids_static (its scratch is a 16 KB device array of the library)
 L_ADP_SIGMA, L_ERROR_EMA = 16, 33
 S_SIGMA, S_EMA, S_AVG_EPL, S_PENALTY, S_FAR_THR, S_SOFT_DOF_POS, S_SOFT_DOF_VEL, S_SOFT_TORQUE, S_PUSH_COUNT, S_LOG = 0, 17, 34, 35, 36, 37, 38, 39, 40, 48
@@ -238,5 +239,7 @@ def bind_track(L):
     L.pbhc_compact_scratch_ints.argtypes = [C.c_int64]
     L.pbhc_compact_ids.restype = C.c_int
     L.pbhc_compact_ids.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    L.pbhc_peer_allreduce_sum.restype = C.c_int
+    L.pbhc_peer_allreduce_sum.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_void_p]
     L.pbhc_compact_ids_static.restype = C.c_int
     L.pbhc_compact_ids_static.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]
