@@ -16,7 +16,7 @@
 extern "C" {
 #endif
 
-#define PBHC_ABI_VERSION 5
+#define PBHC_ABI_VERSION 6
 #define PBHC_OK 0
 #define PBHC_E_BADARG (-1)
 #define PBHC_E_ALIGN (-2)
@@ -241,6 +241,12 @@ int pbhc_clips_prepare(const float* pos, const float* quat, const float* pose_aa
 #define PBHC_A_TERM_REF_POS_Z 37
 #define PBHC_A_TERM_REF_ORI 38
 #define PBHC_A_TERM_BODY_Z 39
+/* base-class terminations (legged_robot_base.py:433-476), ABI 6 */
+#define PBHC_A_TERM_CONTACT 40
+#define PBHC_A_TERM_LOW_HEIGHT 41
+#define PBHC_A_TERM_DOF_POS 42
+#define PBHC_A_TERM_DOF_VEL 43
+#define PBHC_A_TERM_TORQUE 44
 #define PBHC_ACC 64
 #define PBHC_L_UPPER 0
 #define PBHC_L_LOWER 1
@@ -268,6 +274,11 @@ int pbhc_clips_prepare(const float* pos, const float* quat, const float* pose_aa
 #define PBHC_L_TERM_REF_POS_Z 55
 #define PBHC_L_TERM_REF_ORI 56
 #define PBHC_L_TERM_BODY_Z 57
+#define PBHC_L_TERM_CONTACT 58
+#define PBHC_L_TERM_LOW_HEIGHT 59
+#define PBHC_L_TERM_DOF_POS 60
+#define PBHC_L_TERM_DOF_VEL 61
+#define PBHC_L_TERM_TORQUE 62
 
 typedef struct { int32_t enable; double lo, hi, degree, down, up; } PbhcCurriculum;
 /* history key `key` (index into hist_src) appears in obs group `group` at `offset`, newest `len` slots, scaled by mul */
@@ -331,6 +342,17 @@ typedef struct {
   float term_ref_pos_z_thr, term_ref_ori_thr, term_body_z_thr;
   int32_t n_future;                  /* obs.future_num_steps; future_steps = linspace(1, future_max_steps, n).long() (:501-507) */
   int32_t future_steps[PBHC_MAX_FUTURE];
+  /* ABI 6: the base-class terminations (legged_robot_base.py:433-476; LeggedRobotMotionTracking only for now) */
+  int32_t term_contact;              /* terminate_by_contact: any |contact_forces[b]| > 1 over the bodies of the mask */
+  uint64_t term_contact_mask;        /* bit b = simulator body b is in termination_contact_indices (base_task.py:179-197) */
+  int32_t term_low_height;           /* terminate_by_low_height: root z < term_min_height */
+  float term_min_height;
+  int32_t term_dof_pos, term_dof_vel, term_torque;  /* terminate_when_close_to_{dof_pos,dof_vel,torque}_limit */
+  float term_dof_pos_prob, term_dof_vel_prob, term_torque_prob;  /* termination_probality.*: the check applies in a step when U[0,1) < p
+                                      * (ONE draw per step for all envs, `torch.rand(1)` in the reference; here Philox keyed by
+                                      * (seed, step) unless PbhcTrackIO.inject_term_gates says otherwise) */
+  float term_dof_vel_scale, term_torque_scale;       /* termination_scales.termination_close_to_{dof_vel,torque}_limit */
+  float term_pos_lo[PBHC_MAX_DOF], term_pos_hi[PBHC_MAX_DOF];  /* simulator.dof_pos_limits_termination (isaacgym.py:387-388) */
 } PbhcTrackCfg;
 
 typedef struct {
@@ -379,6 +401,9 @@ typedef struct {
   const uint8_t* force_reset;   /* [N] nullable: nonzero = reset this env now whatever its termination says - what
                                  * resample_motion's reset_envs_idx(arange(num_envs)) does (motion_tracking.py:385-389).  A forced reset
                                  * is not a time-out and earns no termination reward; reset_buf reports it. */
+  /* ABI 6 */
+  int32_t inject_term_gates;    /* < 0: the per-step gates of the dof_pos / dof_vel / torque terminations are drawn in the kernel;
+                                 * >= 0: bit 0 / 1 / 2 = that check applies in this step (tests: the reference's own torch.rand(1) draws) */
 } PbhcTrackIO;
 
 /* number of rows `partials` must have */

@@ -188,15 +188,44 @@ def _pre_compute_general(spec, tab, S, inp, W):
                            - O.quat_rotate_inverse(rot_ext[:, a, :], grav)[:, 2])
 
 
-def _termination(spec, S, W, log):
+def _termination(spec, S, W, log, inp=None, inject=None):
     """_check_termination (legged_robot_base.py:408-431) with the motion_tracking overrides (:330-358)."""
     N = S["reset_buf"].shape[0]
     S["reset_buf"][:] = 0
     S["time_out_buf"][:] = 0
     by = {}
+    # base class (legged_robot_base.py:433-476); the three `torch.rand(1) < p` gates come in as inject["term_gates"] (bits 0..2)
+    gates = int((inject or {}).get("term_gates", 7))
+    if getattr(spec, "term_contact", False):
+        by["contact"] = torch.any(torch.norm(inp["contact_forces"][:, spec.term_contact_ids, :], dim=-1) > 1.0, dim=1)
+        S["reset_buf"] |= by["contact"]
     if spec.term_gravity:
         by["gravity"] = torch.norm(W["projected_gravity"][:, 0:2], dim=-1) > spec.term_gravity_thr
         S["reset_buf"] |= by["gravity"]
+    if getattr(spec, "term_low_height", False):
+        by["low_height"] = torch.any(inp["root_state"][:, 2:3] < spec.term_min_height, dim=1)
+        S["reset_buf"] |= by["low_height"]
+    if getattr(spec, "term_dof_pos", False):
+        lo_h, hi_h = torch.tensor(spec.hard_dof_lo), torch.tensor(spec.hard_dof_hi)
+        m, r = (lo_h + hi_h) / 2, hi_h - lo_h
+        lo, hi = m - 0.5 * r * spec.term_dof_pos_scale, m + 0.5 * r * spec.term_dof_pos_scale  # isaacgym.py:387-388
+        dof_pos = inp["dof_state"][..., 0]
+        out = -(dof_pos - lo).clip(max=0.0)
+        out += (dof_pos - hi).clip(min=0.0)
+        out = torch.sum(out, dim=1)
+        by["dof_pos_limit"] = (out > 0.0) if gates & 1 else torch.zeros_like(out)
+        if gates & 1:
+            S["reset_buf"] |= by["dof_pos_limit"]
+    if getattr(spec, "term_dof_vel", False):
+        out = torch.sum((torch.abs(inp["dof_state"][..., 1]) - torch.tensor(spec.dof_vel_limit) * spec.term_dof_vel_scale).clip(min=0.0, max=1.0), dim=1)
+        by["dof_vel_limit"] = (out > 0.0) if gates & 2 else torch.zeros_like(out)
+        if gates & 2:
+            S["reset_buf"] |= by["dof_vel_limit"]
+    if getattr(spec, "term_torque", False):
+        out = torch.sum((torch.abs(inp["torques"]) - torch.tensor(spec.torque_limit) * spec.term_torque_scale).clip(min=0.0, max=1.0), dim=1)
+        by["torque_limit"] = (out > 0.0) if gates & 4 else torch.zeros_like(out)
+        if gates & 4:
+            S["reset_buf"] |= by["torque_limit"]
     if spec.term_motion_far:
         by["motion_far"] = torch.any(torch.norm(W["dif_pos"], dim=-1) > S["motion_far_threshold"], dim=-1)
         S["reset_buf"] |= by["motion_far"]
@@ -496,7 +525,7 @@ def step(spec, tab, S, inp, inject=None):
         log["local_lower_body_diff_norm"] = dl[:, spec.lower_ids, :].norm(dim=-1).mean()
         log["local_vr_3point_diff_norm"] = dl[:, spec.vr3_ids, :].norm(dim=-1).mean()
         log["local_key_body_diff_norm"] = dl[:, spec.key_ids, :].norm(dim=-1).mean()
-    _termination(spec, S, W, log)
+    _termination(spec, S, W, log, inp, inject)
     _rewards(spec, S, W, inp, log)
     extras = {"ref_body_pos_extend": W["ref"]["rg_pos_t"].clone(), "ref_body_rot_extend": W["ref"]["rg_rot_t"].clone()}
     ep = _reset(spec, tab, S, W, inp, inject, log, last_ep_len)

@@ -9,7 +9,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("PBHC_B200_LIB") or os.path.join(_HERE, "libpbhc_b200.so")  # override: development A/B builds
 
 c_f32p = C.c_void_p
-ABI_VERSION = 5
+ABI_VERSION = 6
 MAX_JOINTS = 40
 
 
@@ -150,6 +150,9 @@ LOG_NAMES = ["upper_body_diff_norm", "lower_body_diff_norm", "vr_3point_diff_nor
              "average_episode_length", "soft_dof_pos_curriculum_value", "soft_dof_vel_curriculum_value",
              "soft_torque_curriculum_value"]
 # general_tracking logs: name -> PBHC_L_* index
+# base-class terminations (legged_robot_base.py:433-476): name -> PBHC_L_* index, logged when enabled
+LOG_NAMES_TERM = {"terminate_by_contact": 58, "terminate_by_low_height": 59, "terminate_by_dof_pos_limit": 60,
+                  "terminate_by_dof_vel_limit": 61, "terminate_by_torque_limit": 62}
 LOG_NAMES_GENERAL = {"key_body_diff_norm": 50, "local_upper_body_diff_norm": 51, "local_lower_body_diff_norm": 52,
                      "local_vr_3point_diff_norm": 53, "local_key_body_diff_norm": 54, "terminate_by_ref_pos_z": 55,
                      "terminate_by_ref_ori": 56, "terminate_by_body_z": 57}
@@ -197,7 +200,12 @@ class TrackCfg(C.Structure):
         ("key_mask", C.c_uint64), ("body_z_mask", C.c_uint64),
         ("term_ref_pos_z", C.c_int32), ("term_ref_ori", C.c_int32), ("term_body_z", C.c_int32),
         ("term_ref_pos_z_thr", C.c_float), ("term_ref_ori_thr", C.c_float), ("term_body_z_thr", C.c_float),
-        ("n_future", C.c_int32), ("future_steps", C.c_int32 * MAX_FUTURE)]
+        ("n_future", C.c_int32), ("future_steps", C.c_int32 * MAX_FUTURE),
+        ("term_contact", C.c_int32), ("term_contact_mask", C.c_uint64), ("term_low_height", C.c_int32), ("term_min_height", C.c_float),
+        ("term_dof_pos", C.c_int32), ("term_dof_vel", C.c_int32), ("term_torque", C.c_int32),
+        ("term_dof_pos_prob", C.c_float), ("term_dof_vel_prob", C.c_float), ("term_torque_prob", C.c_float),
+        ("term_dof_vel_scale", C.c_float), ("term_torque_scale", C.c_float),
+        ("term_pos_lo", C.c_float * MAX_DOF), ("term_pos_hi", C.c_float * MAX_DOF)]
 
 
 TRACK_IO_FIELDS = [
@@ -222,7 +230,7 @@ class TrackIO(C.Structure):
                 + [(k, C.c_void_p) for k in ("rew_buf", "reset_buf", "time_out_buf", "ref_body_pos_extend", "ref_body_rot_extend",
                                              "last_episode_sums", "partials", "acc", "inject_start_times", "inject_kp",
                                              "inject_kd", "inject_rfi", "inject_rao", "inject_delay")]
-                + [("env_offset", C.c_int64), ("last_episode_length_buf", C.c_void_p), ("force_reset", C.c_void_p)])
+                + [("env_offset", C.c_int64), ("last_episode_length_buf", C.c_void_p), ("force_reset", C.c_void_p), ("inject_term_gates", C.c_int32)])
 
 
 def bind_track(L):

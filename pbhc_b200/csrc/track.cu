@@ -1215,6 +1215,11 @@ __global__ void track_finalize_kernel(const __grid_constant__ PbhcTrackCfg c, co
     L[PBHC_L_TERM_REF_ORI] = (double)((float)(acc[PBHC_A_TERM_REF_ORI] / n) / reset_mean);
     L[PBHC_L_TERM_BODY_Z] = (double)((float)(acc[PBHC_A_TERM_BODY_Z] / n) / reset_mean);
   }
+  if (c.term_contact) L[PBHC_L_TERM_CONTACT] = (double)((float)(acc[PBHC_A_TERM_CONTACT] / n) / reset_mean);        // legged_robot_base.py:425-429
+  if (c.term_low_height) L[PBHC_L_TERM_LOW_HEIGHT] = (double)((float)(acc[PBHC_A_TERM_LOW_HEIGHT] / n) / reset_mean);
+  if (c.term_dof_pos) L[PBHC_L_TERM_DOF_POS] = (double)((float)(acc[PBHC_A_TERM_DOF_POS] / n) / reset_mean);
+  if (c.term_dof_vel) L[PBHC_L_TERM_DOF_VEL] = (double)((float)(acc[PBHC_A_TERM_DOF_VEL] / n) / reset_mean);
+  if (c.term_torque) L[PBHC_L_TERM_TORQUE] = (double)((float)(acc[PBHC_A_TERM_TORQUE] / n) / reset_mean);
   L[PBHC_L_TERM_GRAVITY] = (double)((float)(acc[PBHC_A_TERM_GRAVITY] / n) / reset_mean);
   L[PBHC_L_TERM_FAR] = (double)((float)(acc[PBHC_A_TERM_FAR] / n) / reset_mean);
   L[PBHC_L_TERM_TIMEOUT] = (double)((float)(acc[PBHC_A_TERM_TIMEOUT] / n) / reset_mean);
@@ -1360,6 +1365,10 @@ extern "C" int pbhc_track_step(const PbhcTrackCfg* cfg, const PbhcTableDesc* tab
         return check_launch("pbhc_track_step");
       }  // (rc > 0: tensors the tile kernel does not take, e.g. not 16-byte aligned - the kernel below runs)
     }
+  }
+  if (c.term_contact || c.term_low_height || c.term_dof_pos || c.term_dof_vel || c.term_torque) {
+    set_error("pbhc_track_step: the contact / low-height / dof-limit terminations are built into the tile kernel only (LeggedRobotMotionTracking, 16-byte aligned tensors)");
+    return PBHC_E_RANGE;
   }
   P.dump = P.rows_len;                                   // scratch for absent destinations: one source wide
   // (widest source: 3*J body features, 6*n_key key-body rotations, 7+D+3K next-step block, L link masses, 64 history lanes)

@@ -49,14 +49,14 @@ constexpr int kPieces = 5;         // pieces of the per-env scalar pre-computati
 #define PBHC_HOTK_INT(X) \
   X(J) X(Jb) X(D) X(L) X(H) X(n_ext) X(n_feet) X(n_groups) X(R) X(n_sums) X(n_hd) X(hist_any_mul) X(has_air_time) X(n_feat) \
   X(contact_size) X(rec_stride) X(use_vec_reward) X(only_positive) X(has_termination) X(cur_torque_enable) X(term_gravity) \
-  X(term_motion_far) X(term_motion_end) X(dif_joint_used) X(ref_vel_used) X(ext_identity) X(ref_pos_out) X(ref_rot_out) X(default_dof_stride) \
+  X(term_motion_far) X(term_motion_end) X(term_contact) X(term_low_height) X(term_dof_pos) X(term_dof_vel) X(term_torque) X(term_base) X(dif_joint_used) X(ref_vel_used) X(ext_identity) X(ref_pos_out) X(ref_rot_out) X(default_dof_stride) \
   X(e_pos) X(e_vel) X(e_ang) X(e_dp) X(e_dv) X(e_c) \
   X(o_tab) X(o_stab) X(n_slots) X(o_hmap) X(o_hmul) X(o_rv) X(o_pre) X(o_rows) X(o_scr) X(scr_pitch) \
   X(i_body) X(i_cf) X(i_hist) X(i_dof) X(i_act) X(i_tq) X(i_lact) X(i_ldv) X(i_kp) X(i_kd) X(i_es0) X(i_es1) X(i_org0) X(i_org1) X(i_com0) X(i_com1) X(i_fric0) X(i_fric1) \
   X(i_delay0) X(i_delay1) X(i_mass0) X(i_mass1) X(i_root0) X(i_root1) X(i_ep0) X(i_ep1) X(i_envf0) X(i_envf1) X(i_mid0) X(i_mid1) \
     X(row_base0) X(row_base1) X(row_base2) X(row_base3) X(gdim0) X(gdim1) X(gdim2) X(gdim3) X(ghist0) X(ghist1) X(ghist2) X(ghist3)
-#define PBHC_HOTK_FLT(X) X(dt) X(clip_obs) X(term_gravity_thr) X(w_lower) X(w_upper) X(termination_scale) X(desired_feet_air_time) X(max_contact_force)
-#define PBHC_HOTK_I64(X) X(max_episode_length) X(penalised_mask)
+#define PBHC_HOTK_FLT(X) X(dt) X(clip_obs) X(term_gravity_thr) X(term_min_height) X(term_dof_vel_scale) X(term_torque_scale) X(w_lower) X(w_upper) X(termination_scale) X(desired_feet_air_time) X(max_contact_force)
+#define PBHC_HOTK_I64(X) X(max_episode_length) X(penalised_mask) X(term_contact_mask)
 struct HotK {
 #define X(n) int n;
   PBHC_HOTK_INT(X)
@@ -149,6 +149,8 @@ struct TileTables {
   uint32_t push_count;
   uint32_t noise_mask;
   float lim_lo[PBHC_MAX_DOF], lim_hi[PBHC_MAX_DOF], lim_vel[PBHC_MAX_DOF], lim_tq[PBHC_MAX_DOF];
+  float t_vel[PBHC_MAX_DOF], t_tq[PBHC_MAX_DOF];  // termination limits: dof_vel_limits / torque_limits x termination scale (legged_robot_base.py:459, 470)
+  int term_gates;                                 // bit 0 / 1 / 2: the dof_pos / dof_vel / torque termination applies in this step
   float r_scale[PBHC_MAX_REWARDS], r_pen[PBHC_MAX_REWARDS], r_sigma[PBHC_MAX_REWARDS];
   signed char r_kind[PBHC_MAX_REWARDS], r_arg[PBHC_MAX_REWARDS];
   signed char bs_slot[kBodySums + 2];
@@ -306,6 +308,17 @@ __device__ void build_tile_tables(const TileParams& P, TileTables& T, short* hma
     const float vs = c.cur_dof_vel.enable ? (float)scal[PBHC_S_SOFT_DOF_VEL] : c.soft_dof_vel_limit;
     T.lim_vel[tid] = xm(c.vel_limit[tid], vs);
     T.lim_tq[tid] = xm(c.torque_limit[tid], c.cur_torque.enable ? (float)scal[PBHC_S_SOFT_TORQUE] : c.soft_torque_limit);
+    T.t_vel[tid] = xm(c.vel_limit[tid], c.term_dof_vel_scale);
+    T.t_tq[tid] = xm(c.torque_limit[tid], c.term_torque_scale);
+  }
+  if (tid == 0) {  // `if torch.rand(1) < p` (legged_robot_base.py:455, 464, 473): one draw per step and check, the same for every env
+    int gates = P.io.inject_term_gates;
+    if (gates < 0) {
+      const Rng rng = {make_uint2((uint32_t)c.seed, (uint32_t)(c.seed >> 32)), 0xffffffffu, 0xffffffffu, (uint32_t)push_count};
+      const uint4 r = rng.draw(3);
+      gates = (u01(r.x) < c.term_dof_pos_prob ? 1 : 0) | (u01(r.y) < c.term_dof_vel_prob ? 2 : 0) | (u01(r.z) < c.term_torque_prob ? 4 : 0);
+    }
+    T.term_gates = gates;
   }
   if (tid < PBHC_MAX_REWARDS) {
     int kind = K_RAW, arg = V_ONE;
@@ -469,6 +482,7 @@ __device__ __forceinline__ void track_tile_body(const TileParams& P) {
   const float far_thr = T.far_thr;
   const uint32_t push_count = T.push_count;
   double acc_reg = 0.0;  // slot = lane (< kAccLo), this warp's envs
+  double acc_hi = 0.0;   // slot = 32 + lane: the base-class termination counts (PBHC_A_TERM_CONTACT ..)
 
   // Every warp runs its own pipeline over its own envs (row `e` = warp of every slab): no block barrier inside the loop.
   // Inputs arrive by cp.async (LDGSTS: 16 / 8 / 4 bytes per lane, whatever the row size allows - rows of 23 floats are
@@ -608,6 +622,7 @@ __device__ __forceinline__ void track_tile_body(const TileParams& P) {
 
       // ---- b. dofs (lane = dof) -------------------------------------------------------------------------------------------
       float adja = 0.0f;  // |dif_joint_angles| of this lane's dof
+      int dof_viol = 0;   // bit 0 / 1 / 2: this dof is beyond its position / velocity / torque termination limit
       if (lane < D) {
         const int d = lane, x = e * D + d;
         const float2 ds = reinterpret_cast<const float2*>(smem + KC(i_dof))[x];
@@ -620,6 +635,11 @@ __device__ __forceinline__ void track_tile_body(const TileParams& P) {
         const float djv = (omb * __ldg(r0 + e_dv + d) + b * __ldg(r1 + e_dv + d)) - dvel;
         const float dact = lact - act, dacc = (ldv - dvel) * (1.0f / dt);  // (tolerance-checked penalty term; the division's slow path is taken for a zero difference)
         const float lim_t = T.lim_tq[d];
+        if (KC(term_base)) {  // legged_robot_base.py:449-476: sum over dofs of the clipped excess > 0  <=>  some dof exceeds
+          if (KC(term_dof_pos) && (dpos < c.term_pos_lo[d] || dpos > c.term_pos_hi[d])) dof_viol |= 1;
+          if (KC(term_dof_vel) && fabsf(dvel) > T.t_vel[d]) dof_viol |= 2;
+          if (KC(term_torque) && fabsf(tq) > T.t_tq[d]) dof_viol |= 4;
+        }
         float* dp_ = scr + d;
         dp_[DR_DJA2 * D] = dja * dja; dp_[DR_DJV2 * D] = djv * djv; dp_[DR_TQ2 * D] = tq * tq; dp_[DR_DACT2 * D] = dact * dact;
         dp_[DR_DV2 * D] = dvel * dvel; dp_[DR_ACC2 * D] = dacc * dacc;
@@ -665,7 +685,7 @@ __device__ __forceinline__ void track_tile_body(const TileParams& P) {
       __syncwarp();
 
       // ---- c. bodies (lane = body): reference pose (lerp / slerp of the frame pair), extended bodies, differences, heading-frame features
-      int far = 0, n_collide = 0;
+      int far = 0, n_collide = 0, hit = 0;
       const float hz = pe[P_HZ], hw = pe[P_HW];
       for (int j0 = 0; j0 < J; j0 += 32) {
         const int j = j0 + lane;
@@ -719,6 +739,10 @@ __device__ __forceinline__ void track_tile_body(const TileParams& P) {
             bp[7 * J] = (mb & 1) ? nrm : 0.0f; bp[8 * J] = (mb & 2) ? nrm : 0.0f; bp[9 * J] = (mb & 4) ? nrm : 0.0f;
           }
           if (nrm > far_thr) far = 1;
+          if (KC(term_contact) && j < Jb && (((unsigned long long)KC(term_contact_mask) >> j) & 1ull)) {  // |f| > 1 (legged_robot_base.py:435); 0x1.000002p0 is the largest fp32 whose root is <= 1
+            const float* fc = s_cf + 3 * j;
+            if (__fmaf_rn(fc[2], fc[2], __fmaf_rn(fc[1], fc[1], fc[0] * fc[0])) > 0x1.000002p0f) hit = 1;
+          }
           if (j < Jb && (((unsigned long long)KC(penalised_mask) >> j) & 1ull)) {
             const float* fc = s_cf + 3 * j;
             // |f| > 0.1 without the square root: sqrtf is monotonic and correctly rounded, 0x1.47ae16p-7 is the largest fp32 whose root is <= 0.1f
@@ -796,7 +820,16 @@ __device__ __forceinline__ void track_tile_body(const TileParams& P) {
       const bool t_out = ep > KC(max_episode_length);
       const bool t_end = KC(term_motion_end) && (xa(xm((float)ep, dt), start) > mlen);
       const bool time_out = t_out || t_end;
-      const bool terminated = t_grav || t_far || time_out;
+      bool t_contact = false, t_low = false, t_dpos = false, t_dvel = false, t_tq = false;
+      if (KC(term_base)) {
+        const int gates = T.term_gates;
+        t_contact = KC(term_contact) && __any_sync(0xffffffffu, hit);
+        t_low = KC(term_low_height) && pe[P_RPZ] < KC(term_min_height);                  // root z (legged_robot_base.py:445)
+        t_dpos = KC(term_dof_pos) && (gates & 1) && __any_sync(0xffffffffu, dof_viol & 1);
+        t_dvel = KC(term_dof_vel) && (gates & 2) && __any_sync(0xffffffffu, dof_viol & 2);
+        t_tq = KC(term_torque) && (gates & 4) && __any_sync(0xffffffffu, dof_viol & 4);
+      }
+      const bool terminated = t_grav || t_far || time_out || t_contact || t_low || t_dpos || t_dvel || t_tq;
       const bool reset = terminated || (io.force_reset != nullptr && io.force_reset[n] != 0);  // forced: resample_motion (motion_tracking.py:385-389)
       if (lane == 0) {
         rve[V_T_GRAV] = t_grav; rve[V_T_FAR] = t_far; rve[V_T_OUT] = time_out; rve[V_T_END] = t_end;
@@ -857,11 +890,11 @@ __device__ __forceinline__ void track_tile_body(const TileParams& P) {
           emit1<kNoise>(T, Rw, k, el, val, clipv, nk);
         }
       };
-      if (!reset) emit_scalar_features(delay);
+      if (__builtin_expect(!reset, 1)) emit_scalar_features(delay);
 
       // ---- h. reset (legged_robot_base.py:491-516, 647-686, 587-635; motion_tracking.py:274-296, 369-384, 445-543) ---------------
       float air0 = air_f, contact0 = contact_f;  // meaningful in lane 0
-      if (reset) {
+      if (__builtin_expect(reset, 0)) {  // (rare: keep the block out of the hot instruction stream)
         const int clip = __float_as_int(pe[P_CLIP]);
         const bool ld = lane < D;
         const Rng rng = {make_uint2((uint32_t)c.seed, (uint32_t)(c.seed >> 32)), (uint32_t)(n + io.env_offset), (uint32_t)((uint64_t)(n + io.env_offset) >> 32), push_count};
@@ -994,6 +1027,11 @@ __device__ __forceinline__ void track_tile_body(const TileParams& P) {
         if (lane == V_ETR_SQ) a = (double)etr * (double)etr;
         acc_reg += a;
       }
+      if (KC(term_base)) {
+        const int slot = 32 + lane;
+        acc_hi += slot == PBHC_A_TERM_CONTACT ? (double)t_contact : slot == PBHC_A_TERM_LOW_HEIGHT ? (double)t_low : slot == PBHC_A_TERM_DOF_POS ? (double)t_dpos :
+                  slot == PBHC_A_TERM_DOF_VEL ? (double)t_dvel : slot == PBHC_A_TERM_TORQUE ? (double)t_tq : 0.0;
+      }
       // ---- j. the env's observation rows leave (16 bytes per lane where the row size allows) -----------------------------------
       __syncwarp();
       auto row_out = [&](int has, int row_base, int gd, float* g) {
@@ -1016,11 +1054,11 @@ __device__ __forceinline__ void track_tile_body(const TileParams& P) {
   // block partials: 64 threads add the warps' sums up in warp order
   __syncthreads();
   double* wacc = reinterpret_cast<double*>(smem + KC(o_rows));
-  if (lane < PBHC_ACC / 2) { wacc[warp * 32 + lane] = lane < kAccLo ? acc_reg : 0.0; }
+  if (lane < PBHC_ACC / 2) { wacc[warp * 32 + lane] = lane < kAccLo ? acc_reg : 0.0; wacc[(kTE + warp) * 32 + lane] = acc_hi; }
   __syncthreads();
   if (tid < PBHC_ACC) {
     double v = 0.0;
-    if (tid < 32) for (int w = 0; w < kTE; ++w) v += wacc[w * 32 + tid];
+    for (int w = 0; w < kTE; ++w) v += wacc[((tid >> 5) * kTE + w) * 32 + (tid & 31)];
     io.partials[(int64_t)blockIdx.x * PBHC_ACC + tid] = v;
   }
 }
@@ -1097,6 +1135,10 @@ static int tile_plan(const PbhcTrackCfg& c, const PbhcTableDesc& tab, const Pbhc
   k.J = J; k.Jb = Jb; k.D = D; k.L = L; k.H = H; k.n_ext = c.n_ext; k.n_feet = c.n_feet; k.n_groups = c.n_groups; k.R = c.n_rewards;
   k.n_sums = c.n_episode_sums; k.n_feat = 16 + L; k.contact_size = tab.contact_size; k.rec_stride = tab.rec_stride;
   k.use_vec_reward = c.use_vec_reward; k.only_positive = c.only_positive_rewards; k.has_termination = c.has_termination;
+  k.term_contact = c.term_contact; k.term_low_height = c.term_low_height; k.term_dof_pos = c.term_dof_pos; k.term_dof_vel = c.term_dof_vel;
+  k.term_torque = c.term_torque; k.term_base = (c.term_contact || c.term_low_height || c.term_dof_pos || c.term_dof_vel || c.term_torque) ? 1 : 0;
+  k.term_min_height = c.term_min_height; k.term_dof_vel_scale = c.term_dof_vel_scale; k.term_torque_scale = c.term_torque_scale;
+  k.term_contact_mask = (long long)c.term_contact_mask;
   k.cur_torque_enable = c.cur_torque.enable; k.term_gravity = c.term_gravity; k.term_motion_far = c.term_motion_far; k.term_motion_end = c.term_motion_end;
   k.dif_joint_used = (c.src_used_mask & ((1ull << S_DIF_JOINT) | (1ull << S_DIF_JOINT_VEL))) ? 1 : 0;
   k.ref_vel_used = (c.src_used_mask & ((1ull << S_LOCAL_REF_VEL) | (1ull << S_GLOBAL_REF_VEL))) ? 1 : 0;
@@ -1189,7 +1231,7 @@ static int tile_plan(const PbhcTrackCfg& c, const PbhcTableDesc& tab, const Pbhc
     P.x.noisy[s] = c.obs_noise[s] != 0.0f ? 1 : 0;
     P.x.scale[s] = c.obs_scale[s];
   }
-  if (off - k.o_rows < 8 * 32 * kTE) take(8 * 32 * kTE - (off - k.o_rows));  // (the rows region also parks the scalars / the warps' sums)
+  if (off - k.o_rows < 16 * 32 * kTE) take(16 * 32 * kTE - (off - k.o_rows));  // (the rows region also parks the scalars / the warps' sums)
   const int rows_end = off;
   for (const void* g : {(const void*)io.rew_buf, (const void*)io.env_f32, (const void*)io.last_dof_pos}) if ((uintptr_t)g & 15) ok = false;
   if (!ok) return 0;  // (0: not for this kernel - the caller falls back to the warp-per-env kernel)

@@ -177,12 +177,29 @@ class TrackSpec:
     # ---- termination (legged_robot_base.py:408-489, motion_tracking.py:330-358) -------------------------
     def _from_termination(self, cfg):
         t = _get(cfg, "termination")
-        unsupported = ["terminate_by_contact", "terminate_by_low_height", "terminate_when_dof_far",
-                       "terminate_when_close_to_dof_pos_limit", "terminate_when_close_to_dof_vel_limit",
-                       "terminate_when_close_to_torque_limit"]
-        for k in unsupported:
-            if _get(t, k, False):
-                raise NotImplementedError(f"termination '{k}' is not implemented by the B200 tracking step")
+        if _get(t, "terminate_when_dof_far", False):
+            raise NotImplementedError("termination 'terminate_when_dof_far' is not implemented by the B200 tracking step")
+        # base-class terminations (legged_robot_base.py:433-476)
+        ts_, tp = _get(cfg, "termination_scales"), _get(cfg, "termination_probality")
+        self.term_contact = bool(_get(t, "terminate_by_contact", False))
+        self.term_low_height = bool(_get(t, "terminate_by_low_height", False))
+        self.term_dof_pos = bool(_get(t, "terminate_when_close_to_dof_pos_limit", False))
+        self.term_dof_vel = bool(_get(t, "terminate_when_close_to_dof_vel_limit", False))
+        self.term_torque = bool(_get(t, "terminate_when_close_to_torque_limit", False))
+        if self.general and (self.term_contact or self.term_low_height or self.term_dof_pos or self.term_dof_vel or self.term_torque):
+            raise NotImplementedError("contact / low-height / dof-limit terminations are built for LeggedRobotMotionTracking only")
+        self.term_min_height = float(_get(ts_, "termination_min_base_height", 0.0))
+        self.term_dof_pos_scale = float(_get(ts_, "termination_close_to_dof_pos_limit", 1.0))
+        self.term_dof_vel_scale = float(_get(ts_, "termination_close_to_dof_vel_limit", 1.0))
+        self.term_torque_scale = float(_get(ts_, "termination_close_to_torque_limit", 1.0))
+        self.term_dof_pos_prob = float(_get(tp, "terminate_when_close_to_dof_pos_limit", 1.0))
+        self.term_dof_vel_prob = float(_get(tp, "terminate_when_close_to_dof_vel_limit", 1.0))
+        self.term_torque_prob = float(_get(tp, "terminate_when_close_to_torque_limit", 1.0))
+        robot = _get(cfg, "robot")
+        ids = []
+        for name in _get(robot, "terminate_after_contacts_on", []) or []:  # base_task.py:179-197: every body whose name contains it
+            ids.extend(i for i, n in enumerate(self.body_names) if name in n)
+        self.term_contact_ids = ids
         self.term_gravity = bool(_get(t, "terminate_by_gravity", False))
         self.term_motion_far = bool(_get(t, "terminate_when_motion_far", False))
         self.term_motion_end = bool(_get(t, "terminate_when_motion_end", False))

@@ -132,6 +132,12 @@ class TrackingStep:
         if self.spec.general:  # general_tracking.py:303-335, 241-255
             for name, i in _lib.LOG_NAMES_GENERAL.items():
                 d[name] = self.scalars[b + i].float()
+        sp = self.spec
+        for on, name in ((sp.term_contact, "terminate_by_contact"), (sp.term_low_height, "terminate_by_low_height"),
+                         (sp.term_dof_pos, "terminate_by_dof_pos_limit"), (sp.term_dof_vel, "terminate_by_dof_vel_limit"),
+                         (sp.term_torque, "terminate_by_torque_limit")):
+            if on:  # legged_robot_base.py:425-429
+                d[name] = self.scalars[b + _lib.LOG_NAMES_TERM[name]].float()
         return d
 
     def reward_tracking_sigma(self):
@@ -248,6 +254,16 @@ class TrackingStep:
             c.n_future = s.future_num_steps
             for i, v in enumerate(s.future_steps):
                 c.future_steps[i] = v
+        # base-class terminations (legged_robot_base.py:433-476)
+        c.term_contact, c.term_contact_mask = int(s.term_contact), _mask(s.term_contact_ids)
+        c.term_low_height, c.term_min_height = int(s.term_low_height), s.term_min_height
+        c.term_dof_pos, c.term_dof_vel, c.term_torque = int(s.term_dof_pos), int(s.term_dof_vel), int(s.term_torque)
+        c.term_dof_pos_prob, c.term_dof_vel_prob, c.term_torque_prob = s.term_dof_pos_prob, s.term_dof_vel_prob, s.term_torque_prob
+        c.term_dof_vel_scale, c.term_torque_scale = s.term_dof_vel_scale, s.term_torque_scale
+        # simulator.dof_pos_limits_termination exactly as isaacgym.py:383-388 derives it in fp32
+        tlo, thi = m - 0.5 * r * s.term_dof_pos_scale, m + 0.5 * r * s.term_dof_pos_scale
+        for d in range(s.D):
+            c.term_pos_lo[d], c.term_pos_hi[d] = float(tlo[d]), float(thi[d])
         self._cfg = c
 
     @classmethod
@@ -314,6 +330,7 @@ class TrackingStep:
         io.inject_kp, io.inject_kd = p(inj.get("kp_scale")), p(inj.get("kd_scale"))
         io.inject_rfi, io.inject_rao = p(inj.get("rfi_lim_scale")), p(inj.get("rao_scale"))
         io.inject_delay = p(inj.get("action_delay_idx"))
+        io.inject_term_gates = int(inj.get("term_gates", -1))
         self._keep = (sim, actions, torques, env_origins, motion_ids, inj)
 
     def write_obs_into(self, buffers):
@@ -437,9 +454,8 @@ class HostStep:
         """host_in: dict name -> pinned CPU tensor for body_state / root_state / dof_state / contact_forces / actions /
         torques, shaped like the device tensors; extra: optional (fn(lo, hi), [(host, device), ...]) run per chunk before
         the tracking kernel (the benchmark uses it for K2 on the same envs); graph: after one eager step the whole
-        three-stream pipeline (copies, kernels, finalize) is captured into a CUDA graph and replayed - the ~15 x chunks
-        host-side launches per step otherwise sit on the critical path of a PCIe-bound step (single-process only: the
-        all-reduce of a sharded step is issued by finalize() outside a graph)."""
+        three-stream pipeline (copies, kernels, exchange, finalize) is captured into a CUDA graph and replayed - the
+        ~15 x chunks host-side launches per step otherwise sit on the critical path of a PCIe-bound step."""
         ts = self.ts = tracking_step
         self._graph, self._want_graph, self._steps = None, bool(graph), 0
         self.N, self.dev = ts.N, ts.device
@@ -476,14 +492,16 @@ class HostStep:
             self._graph.replay()
             torch.cuda.current_stream(self.dev).synchronize()
             return self.host_out
-        import torch.distributed as dist
-        sharded = dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1
-        if self._want_graph and not sharded and self._steps >= 1:  # the first step ran eagerly (lazy one-time setup done)
-            g = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(g):
-                self._enqueue()
-            self._graph = g
-            return self.step()
+        if self._want_graph and self._steps >= 2:  # the first steps ran eagerly (lazy one-time set-up done, incl. the peer-memory exchange)
+            try:  # sharded steps too: the exchange of finalize() is a capturable kernel (csrc/peer.cu) or a capturable NCCL call
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g):
+                    self._enqueue()
+                self._graph = g
+                return self.step()
+            except Exception:  # noqa: BLE001 - a collective that cannot be captured here: stay eager
+                self._want_graph = False
+                torch.cuda.synchronize(self.dev)
         self._steps += 1
         self._enqueue()
         torch.cuda.current_stream(self.dev).synchronize()  # the caller owns the results on the host when step() returns

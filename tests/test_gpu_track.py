@@ -123,6 +123,8 @@ def _run_golden_case(case, tmp_path, exact, loose=None):
         actions = torch.from_numpy(g[p + "in_actions"]).to(DEV).contiguous()
         torques = torch.from_numpy(g[p + "in_torques"]).to(DEV).contiguous()
         inject = {k: torch.from_numpy(g[p + "out_" + k]).to(DEV).contiguous() for k in INJECT}
+        if p + "in_term_gates" in g:
+            inject["term_gates"] = int(g[p + "in_term_gates"])
         obs, rew, reset, extras = ts.step(sim, actions, torques, origins, mids, inject=inject)
         torch.cuda.synchronize()
         tag = f"{case} step {step}"
@@ -148,9 +150,10 @@ def _run_golden_case(case, tmp_path, exact, loose=None):
                 assert_close(log[k[len(p) + 4:]].cpu(), np.float32(g[k]), what=f"{tag} log {k}", **(loose or {}).get("log", dict(rtol=1e-5, atol=1e-6)))
 
 
-@pytest.mark.parametrize("case", ["mt23_main", "mt23_bench", "gt29_teacher", "gt29_student", "mt23_edge", "gt29_edge"])
+@pytest.mark.parametrize("case", ["mt23_main", "mt23_bench", "gt29_teacher", "gt29_student", "mt23_edge", "gt29_edge", "mt23_term"])
 def test_track_step_matches_reference_golden(case, tmp_path):
-    """*_edge: the synthetic clips of tools/make_golden_edge.py - envs sitting on identical frames, sign-flipped frame
+    """mt23_term: the base-class terminations on (contact with |f| just above / below 1, low base, dof position / velocity /
+    torque limits behind the reference's own per-step gates; legged_robot_base.py:433-476).  *_edge: the synthetic clips of tools/make_golden_edge.py - envs sitting on identical frames, sign-flipped frame
     quaternions and sin(half angle) on both sides of slerp's 1e-3; in gt29_edge also body rotations within 0 .. 40 urad of
     the reference's, i.e. quat_to_angle_axis on both sides of its 1e-5 threshold (rotations.py:185-232)"""
     _run_golden_case(case, tmp_path, exact=True)

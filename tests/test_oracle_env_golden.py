@@ -36,7 +36,7 @@ def state_from(g, prefix, spec):
     return S
 
 
-@pytest.mark.parametrize("case", ["mt23_main", "mt23_bench", "gt29_teacher", "gt29_student", "mt23_edge", "gt29_edge"])
+@pytest.mark.parametrize("case", ["mt23_main", "mt23_bench", "gt29_teacher", "gt29_student", "mt23_edge", "gt29_edge", "mt23_term"])
 def test_env_step_oracle_matches_reference(case):
     g, spec, N, tab = load_case(case)
     S = state_from(g, "init_", spec)
@@ -45,6 +45,8 @@ def test_env_step_oracle_matches_reference(case):
         inp = {k: torch.from_numpy(g[p + "in_" + k].copy()) for k in
                ("body_state", "root_state", "dof_state", "contact_forces", "actions", "torques")}
         inject = {k: torch.from_numpy(g[p + "out_" + k]) for k in INJECT}
+        if p + "in_term_gates" in g:  # the reference's `torch.rand(1) < p` draws of this step (legged_robot_base.py:455-473)
+            inject["term_gates"] = int(g[p + "in_term_gates"])
         obs, log, extras = OE.step(spec, tab, S, inp, inject)
         for gname, v in obs.items():
             assert np.array_equal(v.numpy(), g[p + "obs_" + gname]), (step, gname)

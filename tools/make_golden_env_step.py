@@ -63,10 +63,13 @@ def _library29(tmp="/tmp/pbhc_golden"):
     return path
 
 
-def run_case(name, n_envs, n_steps, obs, seed, overrides=None, general=False, motion_file=None, motion_name=None, start_times=None, tweak=None):
+def run_case(name, n_envs, n_steps, obs, seed, overrides=None, general=False, motion_file=None, motion_name=None, start_times=None, tweak=None,
+             tweak_env=None):
     """motion_file / motion_name: a joblib motion file instead of the default clip(s) and the fixture name recorded for it;
     start_times(env) -> tensor: motion start times instead of the seeded spread; tweak(step, body, root, dof, cf, ref): edits
-    the synthetic simulator state in place (edge-case fixtures, tools/make_golden_edge.py)."""
+    the synthetic simulator state in place (edge-case fixtures, tools/make_golden_edge.py); tweak_env(step, env): edits env
+    tensors (torques) before the step.  The `torch.rand(1)` draws of the step (the gates of the dof-limit terminations,
+    legged_robot_base.py:455-473) are recorded as s<k>_in_term_gates (bit i = i-th enabled check applies)."""
     ov = {"domain_rand.push_robots": False}
     ov.update(overrides or {})
     if general:
@@ -116,10 +119,30 @@ def run_case(name, n_envs, n_steps, obs, seed, overrides=None, general=False, mo
         if tweak is not None:
             tweak(step, body, root, dof, cf, ref)
         sim.set_state(body, root, dof, cf)
+        if tweak_env is not None:
+            tweak_env(step, env)
         p = f"s{step}_"
         out.update({p + "in_body_state": _np(body), p + "in_root_state": _np(root), p + "in_dof_state": _np(dof),
                     p + "in_contact_forces": _np(cf), p + "in_actions": _np(env.actions), p + "in_torques": _np(env.torques)})
-        env._post_physics_step()
+        draws, orig_rand = [], torch.rand
+
+        def rec_rand(*a_, **k_):
+            r_ = orig_rand(*a_, **k_)
+            if a_ == (1,) and not k_:
+                draws.append(float(r_))
+            return r_
+        torch.rand = rec_rand
+        try:
+            env._post_physics_step()
+        finally:
+            torch.rand = orig_rand
+        tcfg, tprob = cfg["termination"], cfg.get("termination_probality", {})
+        bits, di = 0, 0
+        for bit, key in enumerate(("terminate_when_close_to_dof_pos_limit", "terminate_when_close_to_dof_vel_limit", "terminate_when_close_to_torque_limit")):
+            if tcfg.get(key, False):
+                bits |= (1 << bit) if draws[di] < tprob[key] else 0
+                di += 1
+        out[p + "in_term_gates"] = np.int64(bits)
         for k, v in env.obs_buf_dict.items():
             out[p + "obs_" + k] = _np(v)
         for k, v in env_state(env).items():
@@ -144,6 +167,39 @@ def run_case(name, n_envs, n_steps, obs, seed, overrides=None, general=False, mo
 ZERO_NOISE = {f"obs.noise_scales.{k}": 0.0 for k in ("base_ang_vel", "projected_gravity", "dof_pos", "dof_vel")}
 
 
+def run_term():
+    """mt23_term: the base-class terminations switched on (contact, low height, close-to-dof-pos / dof-vel / torque limit with
+    their per-step `torch.rand(1) < p` gates, legged_robot_base.py:433-476), a few envs driven into each of them"""
+    ov = dict(ZERO_NOISE)
+    ov.update({"termination.terminate_by_contact": True, "termination.terminate_by_low_height": True,
+               "termination.terminate_when_close_to_dof_pos_limit": True, "termination.terminate_when_close_to_dof_vel_limit": True,
+               "termination.terminate_when_close_to_torque_limit": True,
+               "termination_probality.terminate_when_close_to_dof_pos_limit": 0.5, "termination_probality.terminate_when_close_to_dof_vel_limit": 0.5,
+               "termination_probality.terminate_when_close_to_torque_limit": 0.5})
+    state = {}
+
+    def tweak(step, body, root, dof, cf, ref):
+        cf[5, 0, 2] = 50.0                      # pelvis contact
+        cf[6, 0, :] = torch.tensor([0.6, 0.6, 0.53])   # |f| just above 1 (0.36 + 0.36 + 0.2809 = 1.0009)
+        cf[11, 0, :] = torch.tensor([0.6, 0.6, 0.52])  # |f| just below 1 (0.9904)
+        root[7, 2] = 0.1; body[7, 0, 2] = 0.1   # low base
+        lim = state["lim"]
+        dof[8, 3, 0] = lim[3, 1] + 0.05         # beyond the upper termination limit
+        dof[12, 4, 0] = lim[4, 0] - 0.05        # beyond the lower one
+        dof[9, 2, 1] = 100.0                    # far beyond the velocity limit
+
+    def tweak_env(step, env):
+        state["lim"] = env.simulator.dof_pos_limits_termination.clone()
+        env.torques[10, 1] = env.torque_limits[1]   # at the limit: above 0.98 x limit
+
+    def tweak_first(step, body, root, dof, cf, ref):
+        if "lim" in state:
+            tweak(step, body, root, dof, cf, ref)
+
+    # the limits are only known once the env exists: tweak_env runs before the step's state is recorded, so read them there first
+    run_case("mt23_term", 32, 6, "motion_tracking/main", 13, ov, tweak=tweak_first, tweak_env=tweak_env)
+
+
 def run(ns=None):
     # obs=main ships uniform observation noise (helpers.py:152, torch.rand_like): parity runs set the four
     # non-zero noise scales to 0 exactly like the reference's own obs/motion_tracking/benchmark.yaml does.
@@ -164,4 +220,4 @@ def run_general():
 
 if __name__ == "__main__":
     import sys
-    run_general() if "general" in sys.argv else run()
+    run_general() if "general" in sys.argv else (run_term() if "term" in sys.argv else run())
