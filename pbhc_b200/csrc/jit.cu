@@ -115,7 +115,10 @@ int jit_get(const char* what, const std::string& spec_header, bool noise, const 
   static const bool verbose = [] { const char* e = getenv("PBHC_JIT_VERBOSE"); return e && e[0] != '0'; }();
   if (off) return PBHC_E_CUDA;
   static const bool prof = [] { const char* e = getenv("PBHC_TILE_PROF"); return e && e[0] == '1'; }();  // development: clock stamps in the tile kernel
-  const std::string opts_tag = std::string("sm_100a;c++17;lineinfo;default-device;noise=") + (noise ? "1" : "0") + ";" + what + (prof ? ";prof" : "");
+  // csrc/track.cu is the reference's unfused fp32 operation sequence (built with -fmad=false by build.py): the same here;
+  // csrc/track_tile.cu spells its bit-exact chains with __fmul_rn & co. and lets the rest contract
+  const bool nofma = strcmp(what, "track") == 0;
+  const std::string opts_tag = std::string("sm_100a;c++17;lineinfo;default-device;noise=") + (noise ? "1" : "0") + ";" + what + (prof ? ";prof" : "") + (nofma ? ";fmad=false" : "");
   uint64_t key = 0xcbf29ce484222325ULL;
   key = fnv(key, opts_tag.data(), opts_tag.size());
   key = fnv(key, spec_header.data(), spec_header.size());
@@ -147,8 +150,10 @@ int jit_get(const char* what, const std::string& spec_header, bool noise, const 
         e.loaded = true; set_error("jit: nvrtcCreateProgram failed"); return e.rc = PBHC_E_CUDA;
       }
       const std::string dnoise = std::string("-DPBHC_NOISE=") + (noise ? "1" : "0");
-      const char* opts[] = {"--gpu-architecture=sm_100a", "-std=c++17", "-lineinfo", "-default-device", "-DPBHC_SPEC=1", dnoise.c_str(), "-DPBHC_TILE_PROF=1"};  // (-default-device: the C ABI declarations of the header are host functions)
-      const nvrtcResult r = n.compile(prog, prof ? 7 : 6, opts);
+      std::vector<const char*> opts = {"--gpu-architecture=sm_100a", "-std=c++17", "-lineinfo", "-default-device", "-DPBHC_SPEC=1", dnoise.c_str()};  // (-default-device: the C ABI declarations of the header are host functions)
+      if (prof) opts.push_back("-DPBHC_TILE_PROF=1");
+      if (nofma) opts.push_back("--fmad=false");
+      const nvrtcResult r = n.compile(prog, (int)opts.size(), opts.data());
       size_t ls = 0;
       n.log_size(prog, &ls);
       std::string log(ls, '\0');

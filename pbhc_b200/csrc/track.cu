@@ -15,8 +15,14 @@
 // Reference: legged_robot_base.py:297-338, 346-380, 408-489, 715-793, 944-1087; motion_tracking.py:330-358,
 // 548-747, 1030-1328; helpers.py:128-152; history_handler.py:33-48 (paths under humanoidverse/envs|utils).
 
+#ifndef __CUDACC_RTC__
 #include <cstdlib>
+#include <string>
+#endif
 #include "track_common.cuh"
+#ifdef PBHC_SPEC
+#include "track_spec.h"  // spec::cfg_bytes: the PbhcTrackCfg of one env config as a constant (csrc/jit.cu compiles this file once per config)
+#endif
 
 namespace pbhc {
 
@@ -473,10 +479,15 @@ __host__ __device__ inline int vec_of(int64_t row_floats, const void* base) {
 __device__ __forceinline__ int up4(int v) { return (v + 3) & ~3; }
 
 template <bool kNoise, bool kGeneral>
-__global__ void __launch_bounds__(kTW * 32, kGeneral ? 2 : F_BPS) track_kernel(const __grid_constant__ TrackParams P) {
+__device__ __forceinline__ void track_body(const TrackParams& P) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   BlockTables& T = *reinterpret_cast<BlockTables*>(smem_raw);
+#ifdef PBHC_SPEC
+  // the config is a compile-time constant: flags fold, loops over J / D / future steps have known trip counts
+  const PbhcTrackCfg& c = *reinterpret_cast<const PbhcTrackCfg*>(spec::cfg_bytes);
+#else
   const PbhcTrackCfg& c = P.c;
+#endif
   const PbhcTrackIO& io = P.io;
   const PbhcTableDesc& tab = P.tab;
   int* hmap = reinterpret_cast<int*>(smem_raw + P.o_hmap);
@@ -551,7 +562,7 @@ __global__ void __launch_bounds__(kTW * 32, kGeneral ? 2 : F_BPS) track_kernel(c
       const int n32 = chunk + e * stride;
       if (n32 >= n_envs) break;
       const int64_t n = n32;  // sign-extended 32-bit: every n * row_size below is one IMAD.WIDE
-      const NoiseKey nk = {c.seed, n + io.env_offset, push_count, c.n_groups > 2};
+      const NoiseKey nk = {P.c.seed, n + io.env_offset, push_count, c.n_groups > 2};
       cp_async_wait();  // this env's simulator state, queued while the previous env was being written out
       __syncwarp();
       // ---- A. per-env scalars ------------------------------------------------------------------------------
@@ -973,7 +984,7 @@ __global__ void __launch_bounds__(kTW * 32, kGeneral ? 2 : F_BPS) track_kernel(c
       float air0 = air_f, contact0 = contact_f;  // meaningful in lane 0
       float root_z = rp.z;                       // simulator root height as the observations see it (live view: new value after a reset)
       if (reset) {
-        const Rng rng = {make_uint2((uint32_t)c.seed, (uint32_t)(c.seed >> 32)), (uint32_t)(n + io.env_offset), (uint32_t)((uint64_t)(n + io.env_offset) >> 32), push_count};
+        const Rng rng = {make_uint2((uint32_t)P.c.seed, (uint32_t)(P.c.seed >> 32)), (uint32_t)(n + io.env_offset), (uint32_t)((uint64_t)(n + io.env_offset) >> 32), push_count};
         if (ld) io.actions[n * D + lane] = 0.0f;
         if (lane == 0 && io.last_episode_length_buf) io.last_episode_length_buf[n] = last_ep;  // extras["episode"]["end_epis_length"], legged_robot_base.py:515
         air0 = 0.0f; air1 = 0.0f; contact0 = 0.0f; contact1 = 0.0f;
@@ -1125,6 +1136,15 @@ __global__ void __launch_bounds__(kTW * 32, kGeneral ? 2 : F_BPS) track_kernel(c
   }
 }
 
+#ifdef __CUDACC_RTC__
+}  // namespace pbhc
+extern "C" __global__ void __launch_bounds__(pbhc::kTW * 32, 2) pbhc_track_spec(const __grid_constant__ pbhc::TrackParams P) {
+  pbhc::track_body<PBHC_NOISE != 0, true>(P);
+}
+#else
+template <bool kNoise, bool kGeneral>
+__global__ void __launch_bounds__(kTW * 32, kGeneral ? 2 : F_BPS) track_kernel(const __grid_constant__ TrackParams P) { track_body<kNoise, kGeneral>(P); }
+
 // deterministic reduction of the per-block partials: 32 groups of threads take every 32nd block (independent loads in
 // flight instead of one serial chain), then a fixed-order sum over the groups
 constexpr int kReduceGroups = 1024 / PBHC_ACC;
@@ -1243,6 +1263,35 @@ __global__ void track_finalize_kernel(const __grid_constant__ PbhcTrackCfg c, co
 
 
 static int g_track_blocks_per_sm = 0;
+int jit_get(const char* what, const std::string& spec_header, bool noise, const void** kernel);   // jit.cu
+
+// "track_spec.h" of the warp-per-env kernel: the env config as a constant byte image (seed zeroed: it stays a launch parameter)
+static std::string track_spec_header(const PbhcTrackCfg& c) {
+  PbhcTrackCfg z = c;
+  z.seed = 0;
+  const unsigned char* b = reinterpret_cast<const unsigned char*>(&z);
+  std::string h = "// generated by pbhc_b200 (track.cu track_spec_header): the PbhcTrackCfg of one env config\nnamespace spec {\n"
+                  "__device__ const unsigned char __align__(16) cfg_bytes[" + std::to_string(sizeof(z)) + "] = {";
+  char buf[8];
+  for (size_t i = 0; i < sizeof(z); ++i) { snprintf(buf, sizeof(buf), "%u,", (unsigned)b[i]); h += buf; if ((i & 63) == 63) h += "\n"; }
+  h += "};\n}  // namespace spec\n";
+  return h;
+}
+
+// the kernel specialised for this config (kernel == nullptr: compile into the on-disk cache only); cached per thread
+static int jit_track(const PbhcTrackCfg& c, bool noise, const void** kernel) {
+  static thread_local PbhcTrackCfg last;
+  static thread_local bool last_noise = false, have = false;
+  static thread_local const void* last_fn = nullptr;
+  static thread_local int last_rc = 0;
+  PbhcTrackCfg z = c;
+  z.seed = 0;
+  if (kernel && have && last_noise == noise && !memcmp(&last, &z, sizeof(z))) { *kernel = last_fn; return last_rc; }
+  const void* fn = nullptr;
+  const int rc = jit_get("track", track_spec_header(c), noise, kernel ? &fn : nullptr);
+  if (kernel) { last = z; last_noise = noise; have = true; last_fn = fn; last_rc = rc; *kernel = fn; }
+  return rc;
+}
 int track_tile_launch(const PbhcTrackCfg& c, const PbhcTableDesc& tab, const PbhcTrackIO& io, int64_t n, cudaStream_t stream, int* blocks_out);  // track_tile.cu
 int track_tile_prepare(const PbhcTrackCfg& c, const PbhcTableDesc& tab, const PbhcTrackIO& io);
 
@@ -1259,7 +1308,11 @@ extern "C" int pbhc_track_launch_info(int32_t* out4) {
 
 extern "C" int pbhc_track_specialize(const PbhcTrackCfg* cfg, const PbhcTableDesc* tab, const PbhcTrackIO* io) {
   if (!cfg || !tab || !io) { pbhc::set_error("pbhc_track_specialize: null argument"); return PBHC_E_BADARG; }
-  if (cfg->general) return PBHC_OK;  // (LeggedRobotGeneralTracking runs on the generic warp-per-env kernel)
+  if (cfg->general) {  // LeggedRobotGeneralTracking: the warp-per-env kernel, specialised for the config
+    bool noise = false;
+    for (int k = 0; k < PBHC_NUM_OBS_SRC; ++k) noise |= cfg->obs_noise[k] != 0.0f;
+    return pbhc::jit_track(*cfg, noise, nullptr) == 0 ? PBHC_OK : PBHC_E_CUDA;
+  }
   return pbhc::track_tile_prepare(*cfg, *tab, *io);
 }
 
@@ -1410,9 +1463,35 @@ extern "C" int pbhc_track_step(const PbhcTrackCfg* cfg, const PbhcTableDesc* tab
   // two instantiations: the noise-free one (benchmark.yaml, evaluation) carries no Philox code in its observation stores
   if (c.general && c.n_future > 0 && kFut * 32 > P.sm_rows - P.sm_body) { set_error("pbhc_track_step: future table does not fit the staging buffer"); return PBHC_E_RANGE; }
   const int variant = (noise ? 1 : 0) + (c.general ? 2 : 0);
-  auto kern = variant == 0 ? track_kernel<false, false> : variant == 1 ? track_kernel<true, false> : variant == 2 ? track_kernel<false, true> : track_kernel<true, true>;
+  const void* kern = variant == 0 ? (const void*)track_kernel<false, false> : variant == 1 ? (const void*)track_kernel<true, false> :
+                     variant == 2 ? (const void*)track_kernel<false, true> : (const void*)track_kernel<true, true>;
   static thread_local size_t configured[4] = {0, 0, 0, 0};
   static thread_local int per_sm_of[4] = {0, 0, 0, 0};
+  int which = 0;
+  if (c.general) {  // the kernel specialised for this env config, when it can be had (NVRTC, cached on disk; PBHC_JIT=0 turns it off)
+    const void* jk = nullptr;
+    if (jit_track(c, noise, &jk) == 0 && jk) {
+      static thread_local const void* jk_configured = nullptr;
+      static thread_local size_t jk_shmem = 0;
+      static thread_local int jk_per_sm = 0;
+      if (jk != jk_configured || shmem > jk_shmem) {
+        if (cudaFuncSetAttribute(jk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shmem) != cudaSuccess) return check_launch("pbhc_track_step(attr)");
+        (void)cudaFuncSetAttribute(jk, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+        int per_sm = 0;
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, jk, kTW * 32, shmem);
+        jk_configured = jk; jk_shmem = shmem; jk_per_sm = per_sm < 1 ? 1 : (per_sm > 8 ? 8 : per_sm);
+      }
+      g_track_blocks_per_sm = jk_per_sm;
+      int64_t blocks = (n + kTW - 1) / kTW;
+      if (blocks > 148LL * jk_per_sm) blocks = 148LL * jk_per_sm;
+      g_track_info[0] = 3; g_track_info[1] = (int)blocks; g_track_info[2] = (int)shmem; g_track_info[3] = jk_per_sm;
+      void* args[] = {(void*)&P};
+      if (cudaLaunchKernel(jk, dim3((unsigned)blocks), dim3(kTW * 32), args, shmem, (cudaStream_t)stream) != cudaSuccess) return check_launch("pbhc_track_step(spec)");
+      track_reduce_kernel<<<1, kReduceGroups * PBHC_ACC, 0, (cudaStream_t)stream>>>(io->partials, (int)blocks, io->acc);
+      return check_launch("pbhc_track_step");
+    }
+  }
+  (void)which;
   if (shmem > configured[variant] || per_sm_of[variant] == 0) {
     if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shmem) != cudaSuccess) return check_launch("pbhc_track_step(attr)");
     (void)cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
@@ -1426,7 +1505,10 @@ extern "C" int pbhc_track_step(const PbhcTrackCfg* cfg, const PbhcTableDesc* tab
   const int64_t cap = 148LL * g_track_blocks_per_sm;
   if (blocks > cap) blocks = cap;
   g_track_info[0] = 0; g_track_info[1] = (int)blocks; g_track_info[2] = (int)shmem; g_track_info[3] = g_track_blocks_per_sm;
-  kern<<<(unsigned)blocks, kTW * 32, shmem, (cudaStream_t)stream>>>(P);
+  {
+    void* args[] = {(void*)&P};
+    if (cudaLaunchKernel(kern, dim3((unsigned)blocks), dim3(kTW * 32), args, shmem, (cudaStream_t)stream) != cudaSuccess) return check_launch("pbhc_track_step(launch)");
+  }
   track_reduce_kernel<<<1, kReduceGroups * PBHC_ACC, 0, (cudaStream_t)stream>>>(io->partials, (int)blocks, io->acc);
   return check_launch("pbhc_track_step");
 }
@@ -1437,3 +1519,4 @@ extern "C" int pbhc_track_finalize(const PbhcTrackCfg* cfg, const double* acc, d
   track_finalize_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(*cfg, acc, scalars);
   return check_launch("pbhc_track_finalize");
 }
+#endif  // __CUDACC_RTC__

@@ -286,7 +286,7 @@ class TrackingStep:
         """what the last pbhc_track_step launched: dict(kernel, blocks, smem_bytes, blocks_per_sm)."""
         out = (C.c_int32 * 4)()
         self._L.pbhc_track_launch_info(C.byref(out))
-        return dict(kernel={0: "warp-per-env", 1: "tile (generic)", 2: "tile (specialised for the config)"}.get(out[0], "?"),
+        return dict(kernel={0: "warp-per-env", 1: "tile (generic)", 2: "tile (specialised for the config)", 3: "warp-per-env (specialised for the config)"}.get(out[0], "?"),
                     blocks=out[1], smem_bytes=out[2], blocks_per_sm=out[3])
 
     # ---- one env step -----------------------------------------------------------------------------------
