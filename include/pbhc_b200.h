@@ -16,7 +16,7 @@
 extern "C" {
 #endif
 
-#define PBHC_ABI_VERSION 6
+#define PBHC_ABI_VERSION 7
 #define PBHC_OK 0
 #define PBHC_E_BADARG (-1)
 #define PBHC_E_ALIGN (-2)
@@ -404,7 +404,20 @@ typedef struct {
   /* ABI 6 */
   int32_t inject_term_gates;    /* < 0: the per-step gates of the dof_pos / dof_vel / torque terminations are drawn in the kernel;
                                  * >= 0: bit 0 / 1 / 2 = that check applies in this step (tests: the reference's own torch.rand(1) draws) */
+  /* ABI 7 */
+  const float* fut_table;       /* nullable: compact per-frame records for the future window of general_tracking (pbhc_future_table_build) */
+  int32_t fut_stride;           /* floats per compact record */
 } PbhcTrackIO;
+
+/* The future window of LeggedRobotGeneralTracking (_get_future_motion_targets, general_tracking.py:500-565) reads, for 20 future
+ * steps x 2 frames per env, a handful of values scattered over a 2-KB table record (root and anchor pose, root velocities,
+ * dof positions, key-body positions): on a motion library larger than L2 that is ~400 scattered 32-byte sectors per env.
+ * This builds the same values as ONE contiguous compact record per frame,
+ *   [ root quat 4 | anchor quat 4 | root vel 3 | root ang vel 3 | root pos 3 | anchor pos 3 | dof_pos D | key-body pos 3 x n_key | pad ]
+ * (pbhc_future_table_stride floats, a multiple of 4), copied bit for bit from the packed table; pass it as
+ * PbhcTrackIO.fut_table and the kernel reads ~3 lines per frame instead.  Rebuild after every load_motions. */
+int32_t pbhc_future_table_stride(const PbhcTrackCfg* cfg);
+int pbhc_future_table_build(const PbhcTrackCfg* cfg, const PbhcTableDesc* tab, float* out, int32_t stride, void* stream);
 
 /* number of rows `partials` must have */
 int pbhc_track_max_blocks(void);

@@ -9,7 +9,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("PBHC_B200_LIB") or os.path.join(_HERE, "libpbhc_b200.so")  # override: development A/B builds
 
 c_f32p = C.c_void_p
-ABI_VERSION = 6
+ABI_VERSION = 7
 MAX_JOINTS = 40
 
 
@@ -55,7 +55,8 @@ _lib = None
 
 EXPORTS = ["pbhc_abi_version", "pbhc_struct_size", "pbhc_last_error", "pbhc_lookup", "pbhc_fk", "pbhc_fk_exact", "pbhc_gae", "pbhc_adv_normalize", "pbhc_clip_prepare", "pbhc_clips_prepare",
            "pbhc_track_max_blocks", "pbhc_track_launch_info", "pbhc_track_specialize", "pbhc_track_step", "pbhc_track_finalize", "pbhc_gather_rows", "pbhc_gather_keys", "pbhc_timeout_bootstrap", "pbhc_blend_frames", "pbhc_traj_metrics", "pbhc_pre_physics", "pbhc_compute_torques",
-           "pbhc_compact_scratch_ints", "pbhc_compact_ids", "pbhc_compact_ids_static", "pbhc_peer_allreduce_sum"]
+           "pbhc_compact_scratch_ints", "pbhc_compact_ids", "pbhc_compact_ids_static", "pbhc_peer_allreduce_sum",
+           "pbhc_future_table_stride", "pbhc_future_table_build"]
 
 
 def lib():
@@ -230,7 +231,8 @@ class TrackIO(C.Structure):
                 + [(k, C.c_void_p) for k in ("rew_buf", "reset_buf", "time_out_buf", "ref_body_pos_extend", "ref_body_rot_extend",
                                              "last_episode_sums", "partials", "acc", "inject_start_times", "inject_kp",
                                              "inject_kd", "inject_rfi", "inject_rao", "inject_delay")]
-                + [("env_offset", C.c_int64), ("last_episode_length_buf", C.c_void_p), ("force_reset", C.c_void_p), ("inject_term_gates", C.c_int32)])
+                + [("env_offset", C.c_int64), ("last_episode_length_buf", C.c_void_p), ("force_reset", C.c_void_p), ("inject_term_gates", C.c_int32),
+                   ("fut_table", C.c_void_p), ("fut_stride", C.c_int32)])
 
 
 def bind_track(L):
@@ -249,5 +251,9 @@ def bind_track(L):
     L.pbhc_compact_ids.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
     L.pbhc_peer_allreduce_sum.restype = C.c_int
     L.pbhc_peer_allreduce_sum.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_void_p]
+    L.pbhc_future_table_stride.restype = C.c_int32
+    L.pbhc_future_table_stride.argtypes = [C.POINTER(TrackCfg)]
+    L.pbhc_future_table_build.restype = C.c_int
+    L.pbhc_future_table_build.argtypes = [C.POINTER(TrackCfg), C.POINTER(TableDesc), C.c_void_p, C.c_int32, C.c_void_p]
     L.pbhc_compact_ids_static.restype = C.c_int
     L.pbhc_compact_ids_static.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]

@@ -849,33 +849,43 @@ __device__ __forceinline__ void track_body(const TrackParams& P) {
           float* fut = sm_body;
           const int F = c.n_future, K = c.n_key, a = c.anchor_index;
           const float t0 = (float)ep * c.dt + start;                 // episode_length_buf * dt + start (:509), no +1
+          // where the window's values sit in a record: the packed table, or the compact per-frame records built from it
+          // (pbhc_future_table_build: the same bits, contiguous - ~3 lines per frame instead of ~10 scattered sectors)
+          const bool ft = io.fut_table != nullptr;
+          const float* f_rec = ft ? io.fut_table : tab.records;
+          const int64_t f_stride = ft ? io.fut_stride : tab.rec_stride;
+          const int o_aq = ft ? 4 : 4 * a, o_rv = ft ? 8 : e_vel, o_ra = ft ? 11 : e_ang, o_rp = ft ? 14 : e_pos, o_ap = ft ? 17 : e_pos + 3 * a;
+          const int o_dp = ft ? 20 : e_dp, o_key = ft ? 20 + D : e_pos, f_lines = ft ? io.fut_stride : 0;
           if (lane < F) {  // lane = future step: frame pair, root-frame quantities, anchor pose
             const float ts = (float)c.future_steps[lane] * c.dt + t0;
             const FrameBlend fb = frame_blend(tab, clip, ts);
-            const float* q0 = tab.records + fb.f0 * tab.rec_stride;
-            const float* q1 = tab.records + fb.f1 * tab.rec_stride;
+            const float* q0 = f_rec + fb.f0 * f_stride;
+            const float* q1 = f_rec + fb.f1 * f_stride;
             const float bb = fb.blend, ob = 1.0f - bb;
             // the passes below read this step's dof positions and key-body positions: on a library larger than L2 every one of
             // those reads would be a dependent HBM access - ask for the lines now (positions: J x 12 B, dofs: D x 4 B per frame)
-            for (int o = 0; o < 3 * J; o += 32) { prefetch_l2(q0 + e_pos + o); prefetch_l2(q1 + e_pos + o); }
-            for (int o = 0; o < D; o += 32) { prefetch_l2(q0 + e_dp + o); prefetch_l2(q1 + e_dp + o); }
-            prefetch_l2(q0 + e_dp + D - 1); prefetch_l2(q1 + e_dp + D - 1);
+            if (ft) { for (int o = 32; o < f_lines; o += 32) { prefetch_l2(q0 + o); prefetch_l2(q1 + o); } }
+            else {
+              for (int o = 0; o < 3 * J; o += 32) { prefetch_l2(q0 + e_pos + o); prefetch_l2(q1 + e_pos + o); }
+              for (int o = 0; o < D; o += 32) { prefetch_l2(q0 + e_dp + o); prefetch_l2(q1 + e_dp + o); }
+              prefetch_l2(q0 + e_dp + D - 1); prefetch_l2(q1 + e_dp + D - 1);
+            }
             const float4 a0 = __ldg(reinterpret_cast<const float4*>(q0)), a1 = __ldg(reinterpret_cast<const float4*>(q1));
             const Q4 rq = slerp({a0.x, a0.y, a0.z, a0.w}, {a1.x, a1.y, a1.z, a1.w}, bb);
-            const V3 rvl = quat_rotate_inverse(rq, {ob * __ldg(q0 + e_vel) + bb * __ldg(q1 + e_vel), ob * __ldg(q0 + e_vel + 1) + bb * __ldg(q1 + e_vel + 1),
-                                                    ob * __ldg(q0 + e_vel + 2) + bb * __ldg(q1 + e_vel + 2)});
-            const V3 ral = quat_rotate_inverse(rq, {ob * __ldg(q0 + e_ang) + bb * __ldg(q1 + e_ang), ob * __ldg(q0 + e_ang + 1) + bb * __ldg(q1 + e_ang + 1),
-                                                    ob * __ldg(q0 + e_ang + 2) + bb * __ldg(q1 + e_ang + 2)});
-            const float rz = (ob * __ldg(q0 + e_pos + 2) + bb * __ldg(q1 + e_pos + 2)) + org[2];
+            const V3 rvl = quat_rotate_inverse(rq, {ob * __ldg(q0 + o_rv) + bb * __ldg(q1 + o_rv), ob * __ldg(q0 + o_rv + 1) + bb * __ldg(q1 + o_rv + 1),
+                                                    ob * __ldg(q0 + o_rv + 2) + bb * __ldg(q1 + o_rv + 2)});
+            const V3 ral = quat_rotate_inverse(rq, {ob * __ldg(q0 + o_ra) + bb * __ldg(q1 + o_ra), ob * __ldg(q0 + o_ra + 1) + bb * __ldg(q1 + o_ra + 1),
+                                                    ob * __ldg(q0 + o_ra + 2) + bb * __ldg(q1 + o_ra + 2)});
+            const float rz = (ob * __ldg(q0 + o_rp + 2) + bb * __ldg(q1 + o_rp + 2)) + org[2];
             float roll, pitch;
             euler_roll_pitch(rq, roll, pitch);
-            const float4 b0 = __ldg(reinterpret_cast<const float4*>(q0) + a), b1 = __ldg(reinterpret_cast<const float4*>(q1) + a);
+            const float4 b0 = __ldg(reinterpret_cast<const float4*>(q0 + o_aq)), b1 = __ldg(reinterpret_cast<const float4*>(q1 + o_aq));
             const Q4 aq = slerp({b0.x, b0.y, b0.z, b0.w}, {b1.x, b1.y, b1.z, b1.w}, bb);
             fut[F_F0 * 32 + lane] = __int_as_float((int)fb.f0); fut[F_F1 * 32 + lane] = __int_as_float((int)fb.f1);
             fut[F_BLEND * 32 + lane] = bb;
-            fut[F_APX * 32 + lane] = (ob * __ldg(q0 + e_pos + 3 * a) + bb * __ldg(q1 + e_pos + 3 * a)) + org[0];
-            fut[F_APY * 32 + lane] = (ob * __ldg(q0 + e_pos + 3 * a + 1) + bb * __ldg(q1 + e_pos + 3 * a + 1)) + org[1];
-            fut[F_APZ * 32 + lane] = (ob * __ldg(q0 + e_pos + 3 * a + 2) + bb * __ldg(q1 + e_pos + 3 * a + 2)) + org[2];
+            fut[F_APX * 32 + lane] = (ob * __ldg(q0 + o_ap) + bb * __ldg(q1 + o_ap)) + org[0];
+            fut[F_APY * 32 + lane] = (ob * __ldg(q0 + o_ap + 1) + bb * __ldg(q1 + o_ap + 1)) + org[1];
+            fut[F_APZ * 32 + lane] = (ob * __ldg(q0 + o_ap + 2) + bb * __ldg(q1 + o_ap + 2)) + org[2];
             fut[F_AQX * 32 + lane] = aq.x; fut[F_AQY * 32 + lane] = aq.y; fut[F_AQZ * 32 + lane] = aq.z; fut[F_AQW * 32 + lane] = aq.w;
             fput(fdst(S_FUT_HEIGHT), lane, rz);
             { const FDst d = fdst(S_FUT_RP); fput(d, 2 * lane, roll); fput(d, 2 * lane + 1, pitch); }
@@ -890,11 +900,11 @@ __device__ __forceinline__ void track_body(const TrackParams& P) {
           __syncwarp();
           const FDst d_dof = fdst(S_FUT_DOF), d_key = fdst(S_FUT_KEY);
           for (int s = 0; s < F; ++s) {  // dof_pos of every future step: lane = dof
-            const float* q0 = tab.records + (int64_t)__float_as_int(fut[F_F0 * 32 + s]) * tab.rec_stride;
-            const float* q1 = tab.records + (int64_t)__float_as_int(fut[F_F1 * 32 + s]) * tab.rec_stride;
+            const float* q0 = f_rec + (int64_t)__float_as_int(fut[F_F0 * 32 + s]) * f_stride;
+            const float* q1 = f_rec + (int64_t)__float_as_int(fut[F_F1 * 32 + s]) * f_stride;
             const float bb = fut[F_BLEND * 32 + s], ob = 1.0f - bb;
             if (ld) {
-              const float v = ob * __ldg(q0 + e_dp + lane) + bb * __ldg(q1 + e_dp + lane);
+              const float v = ob * __ldg(q0 + o_dp + lane) + bb * __ldg(q1 + o_dp + lane);
               fput(d_dof, s * D + lane, v);
               if (s == 0) emit1<kNoise>(T, rows, S_NEXT_STEP, 7 + lane, v, nk);
             }
@@ -902,13 +912,13 @@ __device__ __forceinline__ void track_body(const TrackParams& P) {
           for (int s0 = 0; s0 < F; s0 += 2) {  // key bodies in the reference anchor frame: two steps per pass, lane = (step, key)
             const int s = s0 + (lane >> 4), k = lane & 15;
             if (s < F && k < K) {
-              const int j = c.key_ids[k];
-              const float* q0 = tab.records + (int64_t)__float_as_int(fut[F_F0 * 32 + s]) * tab.rec_stride;
-              const float* q1 = tab.records + (int64_t)__float_as_int(fut[F_F1 * 32 + s]) * tab.rec_stride;
+              const int jo = o_key + 3 * (ft ? k : c.key_ids[k]);
+              const float* q0 = f_rec + (int64_t)__float_as_int(fut[F_F0 * 32 + s]) * f_stride;
+              const float* q1 = f_rec + (int64_t)__float_as_int(fut[F_F1 * 32 + s]) * f_stride;
               const float bb = fut[F_BLEND * 32 + s], ob = 1.0f - bb;
-              const V3 d = {((ob * __ldg(q0 + e_pos + 3 * j) + bb * __ldg(q1 + e_pos + 3 * j)) + org[0]) - fut[F_APX * 32 + s],
-                            ((ob * __ldg(q0 + e_pos + 3 * j + 1) + bb * __ldg(q1 + e_pos + 3 * j + 1)) + org[1]) - fut[F_APY * 32 + s],
-                            ((ob * __ldg(q0 + e_pos + 3 * j + 2) + bb * __ldg(q1 + e_pos + 3 * j + 2)) + org[2]) - fut[F_APZ * 32 + s]};
+              const V3 d = {((ob * __ldg(q0 + jo) + bb * __ldg(q1 + jo)) + org[0]) - fut[F_APX * 32 + s],
+                            ((ob * __ldg(q0 + jo + 1) + bb * __ldg(q1 + jo + 1)) + org[1]) - fut[F_APY * 32 + s],
+                            ((ob * __ldg(q0 + jo + 2) + bb * __ldg(q1 + jo + 2)) + org[2]) - fut[F_APZ * 32 + s]};
               const Q4 aq = {fut[F_AQX * 32 + s], fut[F_AQY * 32 + s], fut[F_AQZ * 32 + s], fut[F_AQW * 32 + s]};
               const V3 lp = quat_apply(quat_conj(aq), d);
               const int el = s * 3 * K + 3 * k;
@@ -1296,6 +1306,52 @@ int track_tile_launch(const PbhcTrackCfg& c, const PbhcTableDesc& tab, const Pbh
 int track_tile_prepare(const PbhcTrackCfg& c, const PbhcTableDesc& tab, const PbhcTrackIO& io);
 
 }  // namespace pbhc
+
+namespace pbhc {
+// compact future-window records (include/pbhc_b200.h): one thread per (frame, float)
+struct FutKeys { int v[PBHC_MAX_KEY]; };
+__global__ void future_table_kernel(const float* __restrict__ rec, int64_t frames, int rec_stride, int J, int D, int a, int K, const __grid_constant__ FutKeys keys,
+                                    float* __restrict__ out, int stride) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= frames * stride) return;
+  const int64_t f = i / stride;
+  const int o = (int)(i - f * stride);
+  const float* r = rec + f * rec_stride;
+  const int e_pos = 4 * J, e_vel = 7 * J, e_ang = 10 * J, e_dp = 13 * J;
+  float v = 0.0f;
+  if (o < 4) v = r[o];
+  else if (o < 8) v = r[4 * a + (o - 4)];
+  else if (o < 11) v = r[e_vel + (o - 8)];
+  else if (o < 14) v = r[e_ang + (o - 11)];
+  else if (o < 17) v = r[e_pos + (o - 14)];
+  else if (o < 20) v = r[e_pos + 3 * a + (o - 17)];
+  else if (o < 20 + D) v = r[e_dp + (o - 20)];
+  else if (o < 20 + D + 3 * K) { const int q = o - 20 - D; v = r[e_pos + 3 * keys.v[q / 3] + q % 3]; }
+  out[i] = v;
+}
+}  // namespace pbhc
+
+extern "C" int32_t pbhc_future_table_stride(const PbhcTrackCfg* cfg) {
+  if (!cfg || !cfg->general || cfg->n_future <= 0) return 0;
+  return (20 + cfg->D + 3 * cfg->n_key + 3) & ~3;
+}
+
+extern "C" int pbhc_future_table_build(const PbhcTrackCfg* cfg, const PbhcTableDesc* tab, float* out, int32_t stride, void* stream) {
+  using namespace pbhc;
+  if (!cfg || !tab || !tab->records || !out) { set_error("pbhc_future_table_build: null argument"); return PBHC_E_BADARG; }
+  if (stride != pbhc_future_table_stride(cfg) || stride <= 0 || cfg->n_key > PBHC_MAX_KEY || cfg->J != tab->num_joints || cfg->D != tab->num_dof) {
+    set_error("pbhc_future_table_build: stride %d does not fit the config", stride); return PBHC_E_RANGE;
+  }
+  if (((uintptr_t)out & 15)) { set_error("pbhc_future_table_build: out must be 16-byte aligned"); return PBHC_E_ALIGN; }
+  if (tab->total_frames == 0) return PBHC_OK;
+  FutKeys keys;  // (the key ids travel in the kernel's argument block)
+  for (int k = 0; k < PBHC_MAX_KEY; ++k) keys.v[k] = k < cfg->n_key ? cfg->key_ids[k] : 0;
+  const int64_t total = tab->total_frames * stride;
+  const int64_t blocks = (total + 255) / 256;
+  future_table_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(tab->records, tab->total_frames, tab->rec_stride, cfg->J, cfg->D, cfg->anchor_index,
+                                                                         cfg->n_key, keys, out, stride);
+  return check_launch("pbhc_future_table_build");
+}
 
 extern "C" int pbhc_track_max_blocks(void) { return pbhc::kTrackMaxBlocks; }
 

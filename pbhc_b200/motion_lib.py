@@ -174,6 +174,7 @@ class MotionLibRobot:
                                         clip_start.data_ptr(), clip_frames.data_ptr(), clip_dt_prep.data_ptr(), J, Jb, D, Cm, w_c, radius,
                                         _lib.ptr(scratch), records.data_ptr(), stride, st))
         self._records = records
+        self._table_version = getattr(self, "_table_version", 0) + 1  # (derived tables - TrackingStep's compact future-window records - follow it)
         self._rec_stride = stride
         self._clip_num_frames = torch.tensor(nf, dtype=torch.int32, device=dev)
         starts = np.concatenate([[0], np.cumsum(nf)[:-1]]).astype(np.int64)

@@ -331,7 +331,24 @@ class TrackingStep:
         io.inject_rfi, io.inject_rao = p(inj.get("rfi_lim_scale")), p(inj.get("rao_scale"))
         io.inject_delay = p(inj.get("action_delay_idx"))
         io.inject_term_gates = int(inj.get("term_gates", -1))
+        ft = self._future_table()
+        io.fut_table, io.fut_stride = (p(ft), ft.shape[1]) if ft is not None else (None, 0)
         self._keep = (sim, actions, torques, env_origins, motion_ids, inj)
+
+    def _future_table(self):
+        """general_tracking: compact per-frame records for the 20-step future window (pbhc_future_table_build), rebuilt when
+        the motion library's table changes (load_motions / resample_motion); None when the config has no future window."""
+        if not (self.spec.general and self.spec.future_num_steps > 0):
+            return None
+        ver = (getattr(self.lib, "_table_version", 0), self.lib._records.data_ptr())
+        if getattr(self, "_fut_ver", None) != ver:
+            stride = int(self._L.pbhc_future_table_stride(C.byref(self._cfg)))
+            frames = int(self.lib._desc.total_frames)
+            self._fut = torch.empty(frames, stride, device=self.device, dtype=torch.float32)
+            _lib.check(self._L.pbhc_future_table_build(C.byref(self._cfg), C.byref(self.lib._desc), _lib.ptr(self._fut), stride,
+                                                       _lib.stream_ptr(self.device)))
+            self._fut_ver = ver
+        return self._fut
 
     def write_obs_into(self, buffers):
         """Redirects observation groups to caller-owned [N, dim] fp32 CUDA tensors from the next bind() on, e.g.

@@ -78,6 +78,7 @@ def install_exact_table(ml, clips):
     rec = torch.cat(rows).float()
     assert rec.shape == ml._records.shape
     ml._records.copy_(rec.to(ml._records.device))
+    ml._table_version = getattr(ml, "_table_version", 0) + 1  # derived tables (the step's compact future-window records) follow
 
 
 def oracle_env_from_workload(wl):
