@@ -8,6 +8,7 @@ motion_start_times, motion_len, feet_air_time, last_contacts, episode_sums[name]
 time_out_buf, obs_buf_dict, log_dict, history_handler.query(key), ...).  No CPU fallback.
 """
 import ctypes as C
+import os
 
 import torch
 
@@ -338,8 +339,8 @@ class TrackingStep:
     def _future_table(self):
         """general_tracking: compact per-frame records for the 20-step future window (pbhc_future_table_build), rebuilt when
         the motion library's table changes (load_motions / resample_motion); None when the config has no future window."""
-        if not (self.spec.general and self.spec.future_num_steps > 0):
-            return None
+        if not (self.spec.general and self.spec.future_num_steps > 0) or os.environ.get("PBHC_FUTURE_TABLE", "1") == "0":
+            return None  # (PBHC_FUTURE_TABLE=0: the window reads the packed table itself - same results, for A/B runs)
         ver = (getattr(self.lib, "_table_version", 0), self.lib._records.data_ptr())
         if getattr(self, "_fut_ver", None) != ver:
             stride = int(self._L.pbhc_future_table_stride(C.byref(self._cfg)))

@@ -159,6 +159,13 @@ def test_track_step_matches_reference_golden(case, tmp_path):
     _run_golden_case(case, tmp_path, exact=True)
 
 
+def test_general_tracking_without_the_compact_future_table(tmp_path, monkeypatch):
+    """the future window read from the packed motion table itself (PbhcTrackIO.fut_table = NULL) gives the same golden
+    results as through the compact per-frame records every other general_tracking test uses"""
+    monkeypatch.setenv("PBHC_FUTURE_TABLE", "0")
+    _run_golden_case("gt29_teacher", tmp_path, exact=True)
+
+
 @pytest.mark.parametrize("case", ["mt23_main", "gt29_teacher"])
 def test_track_step_on_product_built_table_matches_reference_golden(case, tmp_path):
     """the fused step on the motion table load_motions builds on the device (no oracle table installed) against the
