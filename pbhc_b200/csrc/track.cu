@@ -63,6 +63,7 @@ struct TrackParams {
 struct BlockTables {
   double scal[PBHC_SCALARS];
   float lim_lo[PBHC_MAX_DOF], lim_hi[PBHC_MAX_DOF], lim_vel[PBHC_MAX_DOF], lim_tq[PBHC_MAX_DOF];
+  int term_gates;  // bit 0 / 1 / 2: the dof_pos / dof_vel / torque termination applies in this step (legged_robot_base.py:455-473)
   float r_scale[PBHC_MAX_REWARDS], r_pen[PBHC_MAX_REWARDS], r_sigma[PBHC_MAX_REWARDS];
   int r_kind[PBHC_MAX_REWARDS], r_arg[PBHC_MAX_REWARDS];
   float sum_div[32];                 // divisor applied to the k-th value of the 16-way reduction ([16..31]: second reduction of general_tracking)
@@ -100,6 +101,15 @@ __device__ void build_tables(const TrackParams& P, BlockTables& T, int* hmap, in
     const float vs = c.cur_dof_vel.enable ? (float)T.scal[PBHC_S_SOFT_DOF_VEL] : c.soft_dof_vel_limit;
     T.lim_vel[tid] = c.vel_limit[tid] * vs;
     T.lim_tq[tid] = c.torque_limit[tid] * (c.cur_torque.enable ? (float)T.scal[PBHC_S_SOFT_TORQUE] : c.soft_torque_limit);
+  }
+  if (tid == 0) {  // `if torch.rand(1) < p` (legged_robot_base.py:455, 464, 473): one draw per step and check, the same for every env
+    int gates = P.io.inject_term_gates;
+    if (gates < 0) {
+      const Rng rng = {make_uint2((uint32_t)c.seed, (uint32_t)(c.seed >> 32)), 0xffffffffu, 0xffffffffu, (uint32_t)push_count};
+      const uint4 r = rng.draw(3);
+      gates = (u01(r.x) < c.term_dof_pos_prob ? 1 : 0) | (u01(r.y) < c.term_dof_vel_prob ? 2 : 0) | (u01(r.z) < c.term_torque_prob ? 4 : 0);
+    }
+    T.term_gates = gates;
   }
   if (tid < PBHC_MAX_REWARDS) {
     int kind = K_RAW, arg = V_ONE;
@@ -631,7 +641,7 @@ __device__ __forceinline__ void track_body(const TrackParams& P) {
       float sums[16];
 #pragma unroll
       for (int i = 0; i < 16; ++i) sums[i] = 0.0f;
-      int far = 0, n_collide = 0, bodyz = 0;
+      int far = 0, n_collide = 0, bodyz = 0, hit = 0;
       for (int j0 = 0; j0 < J; j0 += 32) {
         const int j = j0 + lane;
         bool collide = false;
@@ -713,6 +723,10 @@ __device__ __forceinline__ void track_body(const TrackParams& P) {
             const float* fc = sm_cf + 3 * j;
             collide = norm3(fc[0], fc[1], fc[2]) > 0.1f;
           }
+          if (c.term_contact && j < Jb && (c.term_contact_mask & bit)) {  // |f| > 1 (legged_robot_base.py:435)
+            const float* fc = sm_cf + 3 * j;
+            if (norm3(fc[0], fc[1], fc[2]) > 1.0f) hit = 1;
+          }
           if (!kGeneral || (c.src_used_mask & ((1ull << S_DIF_LOCAL) | (1ull << S_LOCAL_REF)))) {
             const V3 dl = quat_rotate_z(hz, hw, dp);  // motion_tracking.py:694-697
             emit3<kNoise>(T, rows, S_DIF_LOCAL, 3 * j, dl.x, dl.y, dl.z, nk);
@@ -754,6 +768,12 @@ __device__ __forceinline__ void track_body(const TrackParams& P) {
       sums[U_DACT2] = dact * dact; sums[U_DV2] = dvel * dvel;
       const float dacc = (ldv - dvel) / c.dt;
       sums[U_ACC2] = ld ? dacc * dacc : 0.f;
+      int dof_viol = 0;  // bit 0 / 1 / 2: this dof is beyond its position / velocity / torque termination limit (legged_robot_base.py:449-476)
+      if (ld) {
+        if (c.term_dof_pos && (dpos < c.term_pos_lo[lane] || dpos > c.term_pos_hi[lane])) dof_viol |= 1;
+        if (c.term_dof_vel && fabsf(dvel) > c.vel_limit[lane] * c.term_dof_vel_scale) dof_viol |= 2;
+        if (c.term_torque && fabsf(tq) > c.torque_limit[lane] * c.term_torque_scale) dof_viol |= 4;
+      }
       float l_pos = 0.f, l_vel = 0.f, l_tq = 0.f;
       if (ld) {  // legged_robot_base.py:974-1002
         l_pos = -fminf(dpos - lim_lo, 0.0f) + fmaxf(dpos - lim_hi, 0.0f);
@@ -941,7 +961,16 @@ __device__ __forceinline__ void track_body(const TrackParams& P) {
       const bool time_out = t_out || t_end;
       bool t_bodyz = false;
       if constexpr (kGeneral) t_bodyz = c.term_body_z && __any_sync(0xffffffffu, bodyz);
-      const bool terminated = t_grav || t_far || time_out || t_refz || t_ori || t_bodyz;
+      bool t_contact = false, t_low = false, t_dpos = false, t_dvel = false, t_tq = false;
+      if (c.term_contact || c.term_low_height || c.term_dof_pos || c.term_dof_vel || c.term_torque) {  // base class, legged_robot_base.py:433-476
+        const int gates = T.term_gates;
+        t_contact = c.term_contact && __any_sync(0xffffffffu, hit);
+        t_low = c.term_low_height && rp.z < c.term_min_height;
+        t_dpos = c.term_dof_pos && (gates & 1) && __any_sync(0xffffffffu, dof_viol & 1);
+        t_dvel = c.term_dof_vel && (gates & 2) && __any_sync(0xffffffffu, dof_viol & 2);
+        t_tq = c.term_torque && (gates & 4) && __any_sync(0xffffffffu, dof_viol & 4);
+      }
+      const bool terminated = t_grav || t_far || time_out || t_refz || t_ori || t_bodyz || t_contact || t_low || t_dpos || t_dvel || t_tq;
       const bool reset = terminated || (io.force_reset != nullptr && io.force_reset[n] != 0);  // forced: resample_motion (motion_tracking.py:385-389)
       if (lane == 0) {
         rv[V_SIGMA_ERR + G_MAX_JOINT] = max_dja;
@@ -1131,13 +1160,18 @@ __device__ __forceinline__ void track_body(const TrackParams& P) {
         acc_reg += a;
       }
       if constexpr (kGeneral) if (lane < 8) acc_reg2 += (double)rv[32 + lane];
+      if (lane >= 8 && lane < 13) {  // PBHC_A_TERM_CONTACT .. PBHC_A_TERM_TORQUE
+        const int slot = 32 + lane;
+        acc_reg2 += slot == PBHC_A_TERM_CONTACT ? (double)t_contact : slot == PBHC_A_TERM_LOW_HEIGHT ? (double)t_low : slot == PBHC_A_TERM_DOF_POS ? (double)t_dpos :
+                    slot == PBHC_A_TERM_DOF_VEL ? (double)t_dvel : (double)t_tq;
+      }
     }
   }
   // block partials: every warp parks its 64 sums in its (now idle) pre-phase buffer, 64 threads add them up in warp order
   __syncwarp();
   double* wacc = reinterpret_cast<double*>(pre);
   wacc[lane] = lane < kAccLo ? acc_reg : 0.0;
-  wacc[32 + lane] = (kGeneral && lane < 8) ? acc_reg2 : 0.0;
+  wacc[32 + lane] = ((kGeneral && lane < 8) || (lane >= 8 && lane < 13)) ? acc_reg2 : 0.0;
   __syncthreads();
   if (threadIdx.x < PBHC_ACC) {
     double v = 0.0;
@@ -1474,10 +1508,6 @@ extern "C" int pbhc_track_step(const PbhcTrackCfg* cfg, const PbhcTableDesc* tab
         return check_launch("pbhc_track_step");
       }  // (rc > 0: tensors the tile kernel does not take, e.g. not 16-byte aligned - the kernel below runs)
     }
-  }
-  if (c.term_contact || c.term_low_height || c.term_dof_pos || c.term_dof_vel || c.term_torque) {
-    set_error("pbhc_track_step: the contact / low-height / dof-limit terminations are built into the tile kernel only (LeggedRobotMotionTracking, 16-byte aligned tensors)");
-    return PBHC_E_RANGE;
   }
   P.dump = P.rows_len;                                   // scratch for absent destinations: one source wide
   // (widest source: 3*J body features, 6*n_key key-body rotations, 7+D+3K next-step block, L link masses, 64 history lanes)

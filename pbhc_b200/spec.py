@@ -186,8 +186,6 @@ class TrackSpec:
         self.term_dof_pos = bool(_get(t, "terminate_when_close_to_dof_pos_limit", False))
         self.term_dof_vel = bool(_get(t, "terminate_when_close_to_dof_vel_limit", False))
         self.term_torque = bool(_get(t, "terminate_when_close_to_torque_limit", False))
-        if self.general and (self.term_contact or self.term_low_height or self.term_dof_pos or self.term_dof_vel or self.term_torque):
-            raise NotImplementedError("contact / low-height / dof-limit terminations are built for LeggedRobotMotionTracking only")
         self.term_min_height = float(_get(ts_, "termination_min_base_height", 0.0))
         self.term_dof_pos_scale = float(_get(ts_, "termination_close_to_dof_pos_limit", 1.0))
         self.term_dof_vel_scale = float(_get(ts_, "termination_close_to_dof_vel_limit", 1.0))

@@ -150,7 +150,7 @@ def _run_golden_case(case, tmp_path, exact, loose=None):
                 assert_close(log[k[len(p) + 4:]].cpu(), np.float32(g[k]), what=f"{tag} log {k}", **(loose or {}).get("log", dict(rtol=1e-5, atol=1e-6)))
 
 
-@pytest.mark.parametrize("case", ["mt23_main", "mt23_bench", "gt29_teacher", "gt29_student", "mt23_edge", "gt29_edge", "mt23_term"])
+@pytest.mark.parametrize("case", ["mt23_main", "mt23_bench", "gt29_teacher", "gt29_student", "mt23_edge", "gt29_edge", "mt23_term", "gt29_term"])
 def test_track_step_matches_reference_golden(case, tmp_path):
     """mt23_term: the base-class terminations on (contact with |f| just above / below 1, low base, dof position / velocity /
     torque limits behind the reference's own per-step gates; legged_robot_base.py:433-476).  *_edge: the synthetic clips of tools/make_golden_edge.py - envs sitting on identical frames, sign-flipped frame

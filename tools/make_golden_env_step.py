@@ -198,6 +198,11 @@ def run_term():
 
     # the limits are only known once the env exists: tweak_env runs before the step's state is recorded, so read them there first
     run_case("mt23_term", 32, 6, "motion_tracking/main", 13, ov, tweak=tweak_first, tweak_env=tweak_env)
+    # the same five checks under LeggedRobotGeneralTracking (G1 29-DoF, teacher observations)
+    state.clear()
+    ovc = dict(ZERO_NOISE_C)
+    ovc.update({k: v for k, v in ov.items() if k.startswith("termination")})
+    run_case("gt29_term", 32, 4, "motion_tracking/obs_ppo_teacher", 23, ovc, general=True, tweak=tweak_first, tweak_env=tweak_env)
 
 
 def run(ns=None):
