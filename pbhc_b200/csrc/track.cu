@@ -551,7 +551,7 @@ __device__ __forceinline__ void track_body(const TrackParams& P) {
         const V3 blv = quat_rotate_inverse(rq, {root[7], root[8], root[9]});
         const V3 bav = quat_rotate_inverse(rq, {root[10], root[11], root[12]});
         const V3 pg = quat_rotate_inverse(rq, {0.0f, 0.0f, -1.0f});
-        const Q4 hinv = heading_quat_inv(rq);
+        const Q4 hinv = heading_quat_inv_fast(rq);  // (within 1.2e-7 of the exact value like the reference's atan2 / sin / cos sequence, a fraction of its code)
         pre[(P_F0) * kChunk + lane] = __int_as_float((int)fb.f0);
         pre[(P_F1) * kChunk + lane] = __int_as_float((int)fb.f1);
         pre[(P_BLEND) * kChunk + lane] = fb.blend;
@@ -613,7 +613,7 @@ __device__ __forceinline__ void track_body(const TrackParams& P) {
         // delta_pos_w aliases robot_anchor_pos_w_repeat in the reference (:752-753): the z overwrite is seen by
         // _obs_local_body_pos too, so g_dpos stands for both
         g_dpos = {rap.x, rap.y, g_ap.z};
-        g_dori = yaw_quat(quat_mul(g_raq, quat_conj(ar)));
+        g_dori = yaw_quat_fast(quat_mul(g_raq, quat_conj(ar)));
         float m6[6];
         mat_cols2(quat_mul(quat_conj(g_raq), ar), m6);                                     // _obs_anchor_ref_rot (:785-792)
         const V3 arp = quat_apply(quat_conj(g_raq), {g_ap.x - rap.x, g_ap.y - rap.y, g_ap.z - rap.z});  // _obs_anchor_ref_pos

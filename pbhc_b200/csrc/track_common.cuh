@@ -131,6 +131,18 @@ __device__ __forceinline__ Q4 heading_quat_inv_fast(Q4 q) {
   return {0.0f, 0.0f, -sh, ch};
 }
 
+// yaw_quat (common.cuh) the same way: (0, 0, sin(yaw / 2), cos(yaw / 2)) from (cos, sin) of the yaw, no atan2f / sinf / cosf
+__device__ __forceinline__ Q4 yaw_quat_fast(Q4 q) {
+  const float dy = 2.0f * (q.w * q.z + q.x * q.y), dx = 1.0f - 2.0f * (q.y * q.y + q.z * q.z);
+  const float r = sqrtf(dx * dx + dy * dy);
+  if (!(r > 1e-30f)) return {0.0f, 0.0f, 0.0f, 1.0f};
+  const float c = dx / r, s = dy / r;
+  float sh, ch;
+  if (c >= 0.0f) { ch = sqrtf((1.0f + c) * 0.5f); sh = s / (2.0f * ch); }
+  else { const float a = sqrtf((1.0f - c) * 0.5f); sh = copysignf(a, s); ch = fabsf(s) / (2.0f * a); }
+  return {0.0f, 0.0f, sh, ch};
+}
+
 // my_quat_rotate(q, v) for q = (0, 0, z, w) - the heading quaternion.  Same expression tree as quat_rotate_impl with
 // the terms that multiply q.x = q.y = 0 dropped: they are exact zeros, so only the sign of a zero result can differ.
 __device__ __forceinline__ V3 quat_rotate_z(float qz, float qw, V3 v) {
