@@ -105,6 +105,12 @@ __device__ __forceinline__ Q4 yaw_quat(Q4 q) {
   const float n = fmaxf(norm4(0.0f, 0.0f, s, c), 1e-9f);
   return {0.0f / n, 0.0f / n, s / n, c / n};
 }
+// sqrtf / norms whose argument is very often an exact zero (contact forces of bodies in the air, velocities of standing feet):
+// sqrtf takes an out-of-line slow path for zero and denormal arguments, and one such lane sends the whole warp through it.
+// The zero lanes compute sqrtf(1) instead and the result is put back: identical values, no slow path.
+__device__ __forceinline__ float sqrt_z(float x) { const bool z = x == 0.0f; const float r = sqrtf(z ? 1.0f : x); return z ? 0.0f : r; }
+__device__ __forceinline__ float norm3_z(float x, float y, float z) { return sqrt_z(__fmaf_rn(z, z, __fmaf_rn(y, y, x * x))); }
+__device__ __forceinline__ float norm2_z(float x, float y) { return sqrt_z(__fmaf_rn(y, y, x * x)); }
 // first two columns of matrix_from_quat (torch_utils.py:274-297, w_last), row-major: m00 m01 m10 m11 m20 m21
 __device__ __forceinline__ void mat_cols2(Q4 q, float (&o)[6]) {
   const float i = q.x, j = q.y, k = q.z, r = q.w;

@@ -646,7 +646,8 @@ __device__ __forceinline__ void track_body(const TrackParams& P) {
 #pragma unroll
       for (int i = 0; i < 16; ++i) sums[i] = 0.0f;
       int far = 0, n_collide = 0, bodyz = 0, hit = 0;
-      for (int j0 = 0; j0 < J; j0 += 32) {
+#pragma unroll 1
+      for (int j0 = 0; j0 < J; j0 += 32) {  // (one copy of the body section: the specialised kernel knows J and would duplicate it for a 33rd body)
         const int j = j0 + lane;
         bool collide = false;
         if (j < J) {
@@ -725,11 +726,11 @@ __device__ __forceinline__ void track_body(const TrackParams& P) {
           if (nrm > far_thr) far = 1;
           if (j < Jb && (c.penalised_mask & bit)) {
             const float* fc = sm_cf + 3 * j;
-            collide = norm3(fc[0], fc[1], fc[2]) > 0.1f;
+            collide = __fmaf_rn(fc[2], fc[2], __fmaf_rn(fc[1], fc[1], fc[0] * fc[0])) > 0x1.47ae16p-7f;  // |f| > 0.1 on the squared norm (0x1.47ae16p-7: the largest fp32 whose root is <= 0.1f): no square root of the exact zeros of bodies in the air
           }
           if (c.term_contact && j < Jb && (c.term_contact_mask & bit)) {  // |f| > 1 (legged_robot_base.py:435)
             const float* fc = sm_cf + 3 * j;
-            if (norm3(fc[0], fc[1], fc[2]) > 1.0f) hit = 1;
+            if (__fmaf_rn(fc[2], fc[2], __fmaf_rn(fc[1], fc[1], fc[0] * fc[0])) > 0x1.000002p0f) hit = 1;
           }
           if (!kGeneral || (c.src_used_mask & ((1ull << S_DIF_LOCAL) | (1ull << S_LOCAL_REF)))) {
             const V3 dl = quat_rotate_z(hz, hw, dp);  // motion_tracking.py:694-697
@@ -827,7 +828,7 @@ __device__ __forceinline__ void track_body(const TrackParams& P) {
         const float* bs = sm_body + 13 * my_foot;
         const float last_c = lane == 0 ? ef1.x : ef1.y;
         air_f = lane == 0 ? ef0.z : ef0.w;
-        const float fn = norm3(fc[0], fc[1], fc[2]);
+        const float fn = norm3_z(fc[0], fc[1], fc[2]);
         contact_f = fn > 1.0f ? 1.0f : 0.0f;                                   // legged_robot_base.py:352-353
         const float filt = (contact_f != 0.0f || last_c != 0.0f) ? 1.0f : 0.0f;
         cm_f = filt;
@@ -841,9 +842,9 @@ __device__ __forceinline__ void track_body(const TrackParams& P) {
           air_f *= fz ? 0.0f : 1.0f;
         }
         x_force = fmaxf(fn - c.max_contact_force, 0.0f);                        // :1321-1323
-        x_stumble = norm2(fc[0], fc[1]) > 5.0f * fabsf(fc[2]);                  // :1325-1328
-        x_slip = norm3(bs[7], bs[8], bs[9]) * (fn > 1.0f ? 1.0f : 0.0f);        // legged_robot_base.py:1004-1010
-        x_fslip = (fn > 1.0f ? 1.0f : 0.0f) * norm2(bs[7], bs[8]);              // :1012-1017
+        x_stumble = norm2_z(fc[0], fc[1]) > 5.0f * fabsf(fc[2]);                  // :1325-1328
+        x_slip = norm3_z(bs[7], bs[8], bs[9]) * (fn > 1.0f ? 1.0f : 0.0f);        // legged_robot_base.py:1004-1010
+        x_fslip = (fn > 1.0f ? 1.0f : 0.0f) * norm2_z(bs[7], bs[8]);              // :1012-1017
       }
       x_air += __shfl_xor_sync(0xffffffffu, x_air, 1); x_force += __shfl_xor_sync(0xffffffffu, x_force, 1);
       x_slip += __shfl_xor_sync(0xffffffffu, x_slip, 1); x_fslip += __shfl_xor_sync(0xffffffffu, x_fslip, 1);

@@ -166,12 +166,7 @@ struct SmallSlot { const char* src; int row_bytes; int dst; };  // one 4-byte wo
 struct Rows { float* rows; float* ghist; int e; };   // observation slabs (shared), the env's global history row, tile-local env
 
 __device__ __forceinline__ float clampf(float v, float c) { return fminf(fmaxf(v, -c), c); }
-// sqrtf / norms whose argument is very often an exact zero (contact forces of bodies in the air, velocities of standing feet):
-// sqrtf takes an out-of-line slow path for zero and denormal arguments, and one such lane sends the whole warp through it.
-// The zero lanes compute sqrtf(1) instead and the result is put back: identical values, no slow path.
-__device__ __forceinline__ float sqrt_z(float x) { const bool z = x == 0.0f; const float r = sqrtf(z ? 1.0f : x); return z ? 0.0f : r; }
-__device__ __forceinline__ float norm3_z(float x, float y, float z) { return sqrt_z(__fmaf_rn(z, z, __fmaf_rn(y, y, x * x))); }
-__device__ __forceinline__ float norm2_z(float x, float y) { return sqrt_z(__fmaf_rn(y, y, x * x)); }
+
 
 // (value + U(-1,1) * noise) * scale with an independent draw per destination (helpers.py:128-152)
 __device__ __noinline__ void emit_noisy_t(const TileTables& T, const Rows& R, int k, int el, float raw, float clip, const NoiseKeyT& nk) {
