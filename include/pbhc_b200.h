@@ -16,7 +16,7 @@
 extern "C" {
 #endif
 
-#define PBHC_ABI_VERSION 7
+#define PBHC_ABI_VERSION 8
 #define PBHC_OK 0
 #define PBHC_E_BADARG (-1)
 #define PBHC_E_ALIGN (-2)
@@ -487,6 +487,11 @@ typedef struct PbhcActuationCfg {
   int32_t clip_torques;
   float sim_dt;              /* control type "V" */
   uint64_t seed;             /* in-kernel Philox for the RFI draw when rfi_uniform is NULL */
+  /* ABI 8 */
+  int64_t env_offset;        /* global id of env 0 of this call (keys the RFI stream when envs are sharded over ranks) */
+  uint32_t* call_counter;    /* nullable DEVICE counter: when set, the RFI stream of a call is keyed by *call_counter + call_index and
+                              * pbhc_compute_torques advances the counter by one after the kernel - a replayed CUDA graph then draws
+                              * fresh noise on every replay (a call index passed by value is frozen at capture) */
 } PbhcActuationCfg;
 
 /* actions = clip(actions_in, +-action_clip); *clip_count += #(|actions| == action_clip) (zero it first;
@@ -499,7 +504,7 @@ int pbhc_pre_physics(const PbhcActuationCfg* cfg, const float* actions_in, float
 /* torques [N,D] from actions_after_delay and the Isaac Gym dof_state [N*D,2] = (pos, vel).
  * default_dof_pos rows have default_dof_stride floats (0 = one shared row).  rfi_uniform [N,D]:
  * the U[0,1) draws of torch.rand_like for this call (tests), NULL = Philox keyed by
- * (seed, env, call_index, dof). */
+ * (seed, env_offset + env, [*call_counter +] call_index, dof). */
 int pbhc_compute_torques(const PbhcActuationCfg* cfg, const float* actions_after_delay,
                          const float* dof_state, const float* default_dof_pos,
                          int32_t default_dof_stride, const float* last_dof_vel, const float* kp_scale,

@@ -9,7 +9,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("PBHC_B200_LIB") or os.path.join(_HERE, "libpbhc_b200.so")  # override: development A/B builds
 
 c_f32p = C.c_void_p
-ABI_VERSION = 7
+ABI_VERSION = 8
 MAX_JOINTS = 40
 
 
@@ -222,7 +222,7 @@ class ActuationCfg(C.Structure):
                 ("per_dof_action_scale", C.c_int32), ("action_scale", C.c_float), ("action_scales", C.c_float * MAX_DOF),
                 ("p_gains", C.c_float * MAX_DOF), ("d_gains", C.c_float * MAX_DOF), ("torque_limits", C.c_float * MAX_DOF),
                 ("rfi", C.c_int32), ("rfi_lim", C.c_float), ("rao", C.c_int32), ("clip_torques", C.c_int32), ("sim_dt", C.c_float),
-                ("seed", C.c_uint64)]
+                ("seed", C.c_uint64), ("env_offset", C.c_int64), ("call_counter", C.c_void_p)]
 
 
 class TrackIO(C.Structure):

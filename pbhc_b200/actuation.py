@@ -23,7 +23,7 @@ CONTROL_TYPES = {"P": 0, "V": 1, "T": 2}
 
 
 class Actuation:
-    def __init__(self, cfg, num_envs, device, tracking_step=None, seed=0):
+    def __init__(self, cfg, num_envs, device, tracking_step=None, seed=0, env_offset=0):
         dev = torch.device(device)
         if dev.type != "cuda":
             raise _lib.PbhcError("Actuation needs a CUDA device (there is no CPU fallback)")
@@ -84,7 +84,11 @@ class Actuation:
         self.action_queue = torch.zeros(N, Q, D, **f32) if Q else None
         self._clip_count = torch.zeros(1, device=dev, dtype=torch.int64)
         self._numel = torch.tensor(float(N * D), **f32)
-        self._call = 0
+        # the RFI noise stream is keyed by a DEVICE call counter (advanced by pbhc_compute_torques) and the global env id, so a
+        # replayed CUDA graph draws fresh noise and ranks that share a seed draw different streams
+        self._call_counter = torch.zeros(1, device=dev, dtype=torch.int32)
+        c.call_counter = self._call_counter.data_ptr()
+        c.env_offset = int(ts._io.env_offset) if ts is not None else int(env_offset)
         self.log_dict = {}
         self._L = _lib.lib()
 
@@ -118,8 +122,7 @@ class Actuation:
         stride = self.default_dof_pos.shape[1] if self.default_dof_pos.dim() == 2 and self.default_dof_pos.shape[0] > 1 else 0
         _lib.check(self._L.pbhc_compute_torques(C.byref(self._cfg), p(a), p(ds), p(self.default_dof_pos), stride, p(self.last_dof_vel),
                                                 p(self._kp_scale), p(self._kd_scale), p(self._rfi_lim_scale), p(self._rao_scale), p(u),
-                                                self._call & 0xFFFFFFFF, p(out), self.num_envs, _lib.stream_ptr(self.device)))
-        self._call += 1
+                                                0, p(out), self.num_envs, _lib.stream_ptr(self.device)))
         return out
 
     compute_torques = _compute_torques

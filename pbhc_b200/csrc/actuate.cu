@@ -63,13 +63,19 @@ __global__ void __launch_bounds__(256) torques_kernel(const PbhcActuationCfg C, 
   if (C.rfi) {  // :820  torques + (rand*2 - 1) * rfi_lim * _rfi_lim_scale * torque_limits
     float u;
     if (rfi_uniform) u = rfi_uniform[i];
-    else u = u01(philox4x32_10(make_uint4((uint32_t)e, (uint32_t)(e >> 32), call, (uint32_t)d), make_uint2((uint32_t)C.seed, (uint32_t)(C.seed >> 32))).x);
+    else {
+      const int64_t ge = e + C.env_offset;
+      const uint32_t step = call + (C.call_counter ? *C.call_counter : 0u);
+      u = u01(philox4x32_10(make_uint4((uint32_t)ge, (uint32_t)(ge >> 32), step, (uint32_t)d), make_uint2((uint32_t)C.seed, (uint32_t)(C.seed >> 32))).x);
+    }
     t = t + (((u * 2.0f - 1.0f) * C.rfi_lim) * rfi_lim_scale[i]) * lim;
   }
   if (C.rao) t = t + rao_scale[i] * lim;  // :832
   if (C.clip_torques) t = t != t ? t : fminf(fmaxf(t, -lim), lim);  // :835
   torques[i] = t;
 }
+
+__global__ void counter_bump_kernel(uint32_t* counter) { *counter += 1u; }  // (after the torque kernel, same stream: every block read the old value)
 
 static int check_cfg(const PbhcActuationCfg* c, const char* who) {
   if (!c) { set_error("%s: null cfg", who); return PBHC_E_BADARG; }
@@ -115,5 +121,6 @@ extern "C" int pbhc_compute_torques(const PbhcActuationCfg* cfg, const float* ac
   torques_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(*cfg, actions_after_delay, dof_state, default_dof_pos, default_dof_stride,
                                                                                   last_dof_vel, kp_scale, kd_scale, rfi_lim_scale, rao_scale, rfi_uniform,
                                                                                   call_index, torques, n_envs);
+  if (cfg->call_counter && cfg->rfi && !rfi_uniform) counter_bump_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(cfg->call_counter);
   return check_launch("pbhc_compute_torques");
 }

@@ -45,7 +45,7 @@ class _History:
 
 
 class TrackingStep:
-    def __init__(self, spec, motion_lib, num_envs, device, seed=0):
+    def __init__(self, spec, motion_lib, num_envs, device, seed=0, env_offset=0):
         self.spec, self.lib, self.N = spec, motion_lib, int(num_envs)
         self.device = dev = torch.device(device)
         if dev.type != "cuda":
@@ -108,6 +108,7 @@ class TrackingStep:
         self._compact_scratch = torch.zeros(max(int(self._L.pbhc_compact_scratch_ints(N)), 1), device=dev, dtype=torch.int32)
         self._build_cfg(seed)
         self._io = _lib.TrackIO()
+        self._io.env_offset = int(env_offset)  # global id of this rank's env 0 (pbhc_b200.dist.shard_range): keys the in-kernel random streams
         self._keep = None
 
     # ---- reference attribute names as views ------------------------------------------------------------

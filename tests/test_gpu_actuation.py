@@ -116,6 +116,40 @@ def test_in_kernel_rfi_statistics():
     assert torch.equal(runs[1][0], v1) and not torch.equal(runs[2][0], v1)    # seed-reproducible
 
 
+def test_rfi_stream_advances_under_graph_replay_and_follows_the_global_env_id():
+    """the call index of the RFI Philox stream lives in device memory and is advanced by the launch itself: a replayed CUDA
+    graph draws fresh noise every replay, identical to the same number of eager calls; a shard with env_offset = k draws
+    what envs k.. of the unsharded run draw"""
+    g = gold("ref_actuation.npz")
+    from pbhc_b200.actuation import Actuation
+    cfg = json.loads(str(g["meta_config_json"]))
+    N, D = 512, 23
+    dof = torch.zeros(N, D, 2, device=DEV)
+    acts = torch.zeros(N, D, device=DEV)
+    eager = Actuation(cfg, N, DEV, seed=9)
+    want = [eager._compute_torques(acts, dof).clone() for _ in range(4)]
+    rep = Actuation(cfg, N, DEV, seed=9)
+    out = torch.empty(N, D, device=DEV)
+    s = torch.cuda.Stream()
+    s.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(s):
+        rep._compute_torques(acts, dof, out=out)  # call 0, eager (warm-up on the capture stream)
+        first = out.clone()
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph, stream=s):
+            rep._compute_torques(acts, dof, out=out)
+        got = [first]
+        for _ in range(3):
+            graph.replay()
+            got.append(out.clone())
+    torch.cuda.synchronize()
+    for i in range(4):
+        assert torch.equal(got[i], want[i]), f"call {i}"
+    assert not torch.equal(got[1], got[2]) and not torch.equal(got[2], got[3])
+    half = Actuation(cfg, N // 2, DEV, seed=9, env_offset=N // 2)
+    assert torch.equal(half._compute_torques(acts[N // 2:], dof[N // 2:]), want[0][N // 2:])
+
+
 def test_shares_randomisation_tensors_with_tracking_step(tmp_path):
     from pbhc_b200.actuation import Actuation
     from pbhc_b200.fixtures import env_config
