@@ -16,7 +16,7 @@
 extern "C" {
 #endif
 
-#define PBHC_ABI_VERSION 8
+#define PBHC_ABI_VERSION 9
 #define PBHC_OK 0
 #define PBHC_E_BADARG (-1)
 #define PBHC_E_ALIGN (-2)
@@ -199,7 +199,8 @@ int pbhc_clips_prepare(const float* pos, const float* quat, const float* pose_aa
 #define PBHC_MAX_OBS_GROUPS 4
 #define PBHC_MAX_HIST_KEYS 8
 #define PBHC_MAX_HIST_DST 16
-#define PBHC_NUM_OBS_SRC 35  /* 20 shared + 15 of LeggedRobotGeneralTracking, enum order of pbhc_b200/spec.py OBS_SRC */
+#define PBHC_NUM_OBS_SRC 40  /* 20 shared + 15 of LeggedRobotGeneralTracking + 5 added with ABI 9 (relyaw, local_ref_rigid_body_pos_relyaw,
+                              * vr_3point_pos, future_ref_dof_pos / _vel), enum order of pbhc_b200/spec.py OBS_SRC */
 #define PBHC_NUM_SIGMA 17   /* 10 + 7 of general_tracking, enum order of SIGMA_IDS */
 #define PBHC_MAX_KEY 16     /* key bodies (general_tracking) */
 #define PBHC_MAX_FUTURE 32  /* future reference steps (general_tracking) */
@@ -353,6 +354,10 @@ typedef struct {
                                       * (seed, step) unless PbhcTrackIO.inject_term_gates says otherwise) */
   float term_dof_vel_scale, term_torque_scale;       /* termination_scales.termination_close_to_{dof_vel,torque}_limit */
   float term_pos_lo[PBHC_MAX_DOF], term_pos_hi[PBHC_MAX_DOF];  /* simulator.dof_pos_limits_termination (isaacgym.py:387-388) */
+  /* ABI 9: the remaining heading-frame observations (motion_tracking.py:686-731, 594-599) */
+  float ref_init_yaw;                /* ref_init_rpy[0, 2] (motion_tracking.py:186-187): yaw of env 0's reference root rotation at construction */
+  int32_t vr3_ids[4];                /* motion_tracking_id in config order (the layout of vr_3point_pos follows it); n_vr3 <= 3 entries used */
+  /* LeggedRobotMotionTracking with obs.future_ref_steps > 0: n_future holds that count (future_steps is unused there) */
 } PbhcTrackCfg;
 
 typedef struct {
@@ -407,6 +412,10 @@ typedef struct {
   /* ABI 7 */
   const float* fut_table;       /* nullable: compact per-frame records for the future window of general_tracking (pbhc_future_table_build) */
   int32_t fut_stride;           /* floats per compact record */
+  /* ABI 9 */
+  float* heading_scratch;       /* [N,2] scratch, required when the vr_3point_pos observation is used: the reference rotates env i's k-th
+                                 * point by the heading of env (3 i + k) mod N (`heading_inv_rot.repeat(3, 1)`, motion_tracking.py:730-731), so
+                                 * every env's pre-reset heading is written here by a small kernel ahead of the step kernel */
 } PbhcTrackIO;
 
 /* The future window of LeggedRobotGeneralTracking (_get_future_motion_targets, general_tracking.py:500-565) reads, for 20 future

@@ -132,6 +132,23 @@ def get_euler_xyz_in_tensor(q):
     return torch.stack((roll, pitch, yaw), dim=-1)
 
 
+def calc_yaw_heading_quat_inv(yaw):
+    """rotations.py:309-322: (0, 0, -sin(yaw / 2), cos(yaw / 2)) for yaw [B,1]."""
+    half = yaw[..., 0] * 0.5
+    s, c = torch.sin(half), torch.cos(half)
+    z = torch.zeros_like(s)
+    return torch.stack([z, z, -s, c], dim=-1)
+
+
+def wrap_to_pi(angles):
+    """rotations.py:49-53 (in place there; on a copy here).  The reference function is @torch.jit.script, and TorchScript
+    compiles `angles %= 2*np.pi` to aten::fmod_ (sign of the dividend), not to the remainder eager Python would take: a
+    negative angle stays negative, and values in (-2 pi, -pi) are NOT wrapped."""
+    angles = torch.fmod(angles, 2 * np.pi)
+    angles -= 2 * np.pi * (angles > np.pi)
+    return angles
+
+
 def quat_apply(a, b):
     """utils/torch_utils.py:51-58 (xyzw): b + w*t + xyz x t, t = 2 (xyz x b)."""
     shape = b.shape

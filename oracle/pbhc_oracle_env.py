@@ -115,6 +115,22 @@ def _pre_compute(spec, tab, S, inp):
     W["local_ref_rigid_body_pos"] = O.quat_rotate(h_exp, g_ref.reshape(-1, 3)).view(N, -1)
     W["local_ref_rigid_body_vel"] = O.quat_rotate(h_exp, ref["body_vel_t"].reshape(-1, 3)).view(N, -1)
     W["global_ref_rigid_body_vel"] = ref["body_vel_t"].reshape(N, -1)
+    # relyaw / vr 3-point observations, motion_tracking.py:686-687, 720-731 (general_tracking.py:682-725)
+    W["rpy"] = O.get_euler_xyz_in_tensor(q)                      # legged_robot_base.py:349
+    W["relyaw"] = W["rpy"][:, 2:3] - float(S.get("ref_init_yaw", 0.0))
+    ry_exp = O.calc_yaw_heading_quat_inv(W["relyaw"]).unsqueeze(1).expand(-1, J, -1).reshape(-1, 4)
+    W["local_ref_rigid_body_pos_relyaw"] = O.quat_rotate(ry_exp, ref["body_vel_t"].reshape(-1, 3)).view(N, -1)  # velocities (sic)
+    if len(spec.vr3_ids) == 3:
+        vr = ref["rg_pos_t"][:, spec.vr3_ids, :] - root[:, 0:3].view(N, 1, 3)
+        W["vr_3point_pos"] = O.quat_rotate(h_inv.repeat(3, 1).view(-1, 4), vr.reshape(-1, 3)).view(N, -1)  # `repeat`, not repeat_interleave (sic)
+    if not spec.general and spec.future_num_steps > 0:  # kick_motion_res_multiplestep, motion_tracking.py:562-579, 594-599
+        fp, fv = [], []
+        for i in range(spec.future_num_steps):
+            t_i = (S["episode_length_buf"] + 1 + i) * spec.dt + S["motion_start_times"]
+            m = O.get_motion_state(tab, S["motion_ids"], t_i, offset=S["env_origins"])
+            fp.append(m["dof_pos"].unsqueeze(1)); fv.append(m["dof_vel"].unsqueeze(1))
+        W["future_ref_dof_pos"] = torch.cat(fp, dim=1).view(N, -1)
+        W["future_ref_dof_vel"] = torch.cat(fv, dim=1).view(N, -1)
     # phase, motion_tracking.py:738-744
     W["ref_motion_phase"] = (times / tab.length[S["motion_ids"]]).unsqueeze(1)
     if spec.general:
@@ -158,7 +174,6 @@ def _pre_compute_general(spec, tab, S, inp, W):
     ref, root = W["ref"], inp["root_state"]
     if spec.future_num_steps > 0:
         _future_targets(spec, tab, S, W)
-    W["rpy"] = O.get_euler_xyz_in_tensor(root[:, 3:7])          # legged_robot_base.py:349
     W["roll_pitch"] = W["rpy"][:, :2]
     # differences (:638-666): quaternion product instead of the component-wise subtraction of motion_tracking
     W["dif_rot"] = O.quat_mul(ref["rg_rot_t"], O.quat_conjugate(W["rot_ext"]))
@@ -303,7 +318,39 @@ def _rewards(spec, S, W, inp, log):
         out += (dof_pos - hi).clip(min=0.0)
         return torch.sum(out, dim=1)
 
+    def radial_velocity_potential(cur_vel, ref_vel, sigma_theta=0.75, alpha_norm=0.4):  # motion_tracking.py:78-94
+        cosine_error = 1 - torch.nn.functional.cosine_similarity(cur_vel, ref_vel, dim=-1)
+        potential_cosine = torch.exp(-cosine_error / sigma_theta)
+        norm_ratio = cur_vel.norm(dim=-1) / ref_vel.norm(dim=-1)
+        return potential_cosine * (norm_ratio * torch.exp(alpha_norm * (1 - norm_ratio ** (1 / alpha_norm))))
+
+    def r_radial_body():  # :1238-1244
+        cur = W["vel_ext"].reshape(N_, -1)
+        return radial_velocity_potential(cur, W["dif_vel"].reshape(N_, -1) + cur)
+
+    def feet_heading_diffs():  # legged_robot_base.py:1031-1047
+        fwd = torch.tensor([1.0, 0.0, 0.0]).repeat(N_, 1)
+        out = []
+        hr = O.quat_apply(inp["root_state"][:, 3:7], fwd)
+        heading_root = torch.atan2(hr[:, 1], hr[:, 0])
+        for f in feet[:2]:
+            ff = O.quat_apply(inp["body_state"][:, f, 3:7], fwd)
+            out.append(torch.abs(O.wrap_to_pi(torch.atan2(ff[:, 1], ff[:, 0]) - heading_root)))
+        return out
+
+    def feet_gravity():  # :1049-1054
+        grav = torch.tensor([0.0, 0.0, -1.0]).repeat(N_, 1)
+        return [O.quat_rotate_inverse(inp["body_state"][:, f, 3:7], grav) for f in feet[:2]]
+
+    N_ = dof_pos.shape[0]
+    cfilt = W["contacts_filt"]
     fn = {
+        "teleop_radial_body_velocity_extend": r_radial_body,
+        "teleop_radial_joint_velocity": lambda: radial_velocity_potential(dof_vel, W["dif_joint_velocities"] + dof_vel),
+        "feet_heading_alignment": lambda: (lambda d: d[0] + d[1])(feet_heading_diffs()),
+        "feet_heading_alignment_contact": lambda: (lambda d: d[0] * cfilt[:, 0] + d[1] * cfilt[:, 1])(feet_heading_diffs()),
+        "penalty_feet_ori": lambda: (lambda g: torch.sum(torch.square(g[0][:, :2]), dim=1) ** 0.5 + torch.sum(torch.square(g[1][:, :2]), dim=1) ** 0.5)(feet_gravity()),
+        "penalty_feet_ori_contact": lambda: (lambda g: torch.norm(g[0][:, :2], dim=-1) * cfilt[:, 0] + torch.norm(g[1][:, :2], dim=-1) * cfilt[:, 1])(feet_gravity()),
         "teleop_contact_mask": lambda: 1 - (W["contacts_filt"] - W["ref"]["contact_mask"]).abs().mean(dim=-1),
         "teleop_contact_mask_v2": lambda: 0.5 - (W["contacts_filt"] - W["ref"]["contact_mask"]).abs().mean(dim=-1),
         "teleop_max_joint_position": lambda: track(W["dif_joint_angles"].abs().max(dim=-1)[0], "teleop_max_joint_pos"),
@@ -469,7 +516,11 @@ def _observations(spec, S, W, inp):
         "local_ref_rigid_body_vel": W["local_ref_rigid_body_vel"], "global_ref_rigid_body_vel": W["global_ref_rigid_body_vel"],
         "dif_joint_angles": W["dif_joint_angles"], "dif_joint_velocities": W["dif_joint_velocities"],
         "base_pos_z": inp["root_state"][:, 2:3],
+        "relyaw": W["relyaw"], "local_ref_rigid_body_pos_relyaw": W["local_ref_rigid_body_pos_relyaw"],
     }
+    for k in ("vr_3point_pos", "future_ref_dof_pos", "future_ref_dof_vel"):
+        if k in W:
+            src[k] = W[k]
     if spec.general:  # getters of general_tracking.py:879-927; root_height is a live view of the root state (:608)
         K = spec.key_ids
         src.update({

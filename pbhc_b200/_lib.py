@@ -9,7 +9,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("PBHC_B200_LIB") or os.path.join(_HERE, "libpbhc_b200.so")  # override: development A/B builds
 
 c_f32p = C.c_void_p
-ABI_VERSION = 8
+ABI_VERSION = 9
 MAX_JOINTS = 40
 
 
@@ -140,7 +140,7 @@ def stream_ptr(device=None):
 
 # ---- K3 structs (mirror include/pbhc_b200.h exactly) ------------------------------------------------
 MAX_DOF, MAX_REWARDS, MAX_EXT, MAX_FEET, MAX_OBS_GROUPS, MAX_HIST_KEYS, MAX_HIST_DST = 32, 32, 4, 4, 4, 8, 16
-NUM_OBS_SRC, NUM_SIGMA, ENVF_STRIDE, SCALARS, ACC, MAX_KEY, MAX_FUTURE = 35, 17, 8, 112, 64, 16, 32
+NUM_OBS_SRC, NUM_SIGMA, ENVF_STRIDE, SCALARS, ACC, MAX_KEY, MAX_FUTURE = 40, 17, 8, 112, 64, 16, 32
 PEER_MAX_DOUBLES = 256
 COMPACT_STATIC_MAX_N = 1 << 24  # PBHC_COMPACT_STATIC_MAX_N: flags per call of pbhc_compact_ids_static (its scratch is a 16 KB device array of the library)
 L_ADP_SIGMA, L_ERROR_EMA = 16, 33
@@ -206,7 +206,8 @@ class TrackCfg(C.Structure):
         ("term_dof_pos", C.c_int32), ("term_dof_vel", C.c_int32), ("term_torque", C.c_int32),
         ("term_dof_pos_prob", C.c_float), ("term_dof_vel_prob", C.c_float), ("term_torque_prob", C.c_float),
         ("term_dof_vel_scale", C.c_float), ("term_torque_scale", C.c_float),
-        ("term_pos_lo", C.c_float * MAX_DOF), ("term_pos_hi", C.c_float * MAX_DOF)]
+        ("term_pos_lo", C.c_float * MAX_DOF), ("term_pos_hi", C.c_float * MAX_DOF),
+        ("ref_init_yaw", C.c_float), ("vr3_ids", C.c_int32 * 4)]
 
 
 TRACK_IO_FIELDS = [
@@ -232,7 +233,7 @@ class TrackIO(C.Structure):
                                              "last_episode_sums", "partials", "acc", "inject_start_times", "inject_kp",
                                              "inject_kd", "inject_rfi", "inject_rao", "inject_delay")]
                 + [("env_offset", C.c_int64), ("last_episode_length_buf", C.c_void_p), ("force_reset", C.c_void_p), ("inject_term_gates", C.c_int32),
-                   ("fut_table", C.c_void_p), ("fut_stride", C.c_int32)])
+                   ("fut_table", C.c_void_p), ("fut_stride", C.c_int32), ("heading_scratch", C.c_void_p)])
 
 
 def bind_track(L):

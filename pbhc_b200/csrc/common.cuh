@@ -138,4 +138,19 @@ __device__ __forceinline__ void euler_roll_pitch(Q4 q, float& roll, float& pitch
   pitch = fabsf(sinp) >= 1.0f ? fabsf(1.5707963267948966f) * sgn : asinf(sinp);
 }
 
+// yaw of get_euler_xyz_in_tensor (rotations.py:381-385)
+__device__ __forceinline__ float euler_yaw(Q4 q) {
+  const float siny = 2.0f * (q.w * q.z + q.x * q.y);
+  const float cosy = ((q.w * q.w + q.x * q.x) - q.y * q.y) - q.z * q.z;
+  return atan2f(siny, cosy);
+}
+// wrap_to_pi (rotations.py:49-53) as the reference RUNS it: the function is @torch.jit.script and TorchScript compiles
+// `angles %= 2*np.pi` to aten::fmod_ (C fmod, sign of the dividend) - negative angles stay negative - then subtracts
+// fp32(2 pi) where the value exceeds fp32(pi)
+__device__ __forceinline__ float wrap_to_pi(float a) {
+  const float two_pi = 6.283185307179586f;
+  const float r = fmodf(a, two_pi);
+  return r - (r > 3.141592653589793f ? two_pi : 0.0f);
+}
+
 }  // namespace pbhc

@@ -57,6 +57,8 @@ struct TrackParams {
   int has_air_time;                      // the feet_air_time reward is active (only then the reference advances feet_air_time)
   int hist_any_mul;                      // some history destination has mul != 1
   int n_hdst_max;                        // max destinations of one history element
+  int rew_extra;                         // bit (id - R_RADIAL_BODY_VEL): that R15 reward term is active
+  int need_rootq;                        // relyaw sources or the feet-heading rewards are in use: the loop reads the root quaternion
 };
 
 // block-level tables (built once per block from the launch parameters)
@@ -149,6 +151,12 @@ __device__ void build_tables(const TrackParams& P, BlockTables& T, int* hmap, in
         case R_LKEY_ROT: kind = K_EXP; arg = G_LKEY_ROT; break;
         case R_KEY_VEL: kind = K_EXP; arg = G_KEY_VEL; break;
         case R_KEY_ANG: kind = K_EXP; arg = G_KEY_ANG; break;
+        case R_RADIAL_BODY_VEL: arg = V_RAD_BODY; break;
+        case R_RADIAL_JOINT_VEL: arg = V_RAD_JOINT; break;
+        case R_FEET_HEADING: arg = V_FEET_HEAD; break;
+        case R_FEET_ORI: arg = V_FEET_ORI; break;
+        case R_FEET_HEADING_CONTACT: arg = V_FEET_HEAD_C; break;
+        case R_FEET_ORI_CONTACT: arg = V_FEET_ORI_C; break;
         default: break;
       }
       if (kind != K_RAW) sig = (float)T.scal[PBHC_S_SIGMA + arg];
@@ -483,6 +491,18 @@ __device__ __forceinline__ void hist_scatter(const float* gh, float* rows, const
 // instruction fetch (instruction-cache hit rate 72 %, 2.2 stall cycles per instruction on `no_instruction`): one shared body
 static __device__ __noinline__ Q4 slerp_nl(Q4 a, Q4 b, float t) { return slerp(a, b, t); }
 
+// radial_velocity_potential (motion_tracking.py:78-94) from the three sums over the flattened vectors: dot = cur . ref,
+// cc = |cur|^2, rr = |ref|^2.  F.cosine_similarity divides each vector by max(norm, 1e-8) before the product; here the sum of
+// products is divided once (same value up to rounding).  sigma_theta = 0.75, alpha_norm = 0.4 (the function's defaults).
+static __device__ __noinline__ float radial_potential(float dot, float cc, float rr) {
+  const float nc = sqrtf(cc), nr = sqrtf(rr);
+  const float cs = dot / (fmaxf(nc, 1e-8f) * fmaxf(nr, 1e-8f));
+  const float pc = expf(-(1.0f - cs) / 0.75f);
+  const float ratio = nc / nr;
+  const float pn = ratio * expf(0.4f * (1.0f - powf(ratio, 2.5f)));
+  return pc * pn;
+}
+
 __host__ __device__ inline int vec_of(int64_t row_floats, const void* base) {
   const uintptr_t a = (uintptr_t)base;
   if ((row_floats & 3) == 0 && (a & 15) == 0) return 4;
@@ -596,6 +616,19 @@ __device__ __forceinline__ void track_body(const TrackParams& P) {
       // history ring -> its places in the observation rows (HistoryHandler.query, history_handler.py:46-48)
       if (c.hist_row > 0 && !hist_stage) hist_scatter(io.hist + n * c.hist_row, rows, hmap, c, P.n_hdst_max, P.hist_any_mul, hist_vec, lane, false);
       __syncwarp();
+      // relyaw = rpy[:, 2] - ref_init_rpy[0, 2] and its inverse heading quaternion (motion_tracking.py:686-687, rotations.py:309-322);
+      // the root quaternion itself for the feet-heading rewards.  Rare configs: every lane computes the same values
+      Q4 rootq = {0.f, 0.f, 0.f, 1.f};
+      float relyaw = 0.f, ry_z = 0.f, ry_w = 1.f;
+      if (P.need_rootq) {
+        const float* root = io.root_state + n * 13;
+        rootq = {root[3], root[4], root[5], root[6]};
+        if (c.src_used_mask & ((1ull << S_RELYAW) | (1ull << S_LOCAL_REF_RELYAW))) {
+          relyaw = euler_yaw(rootq) - c.ref_init_yaw;
+          const float half = relyaw * 0.5f;
+          ry_z = -sinf(half); ry_w = cosf(half);
+        }
+      }
       // ---- general_tracking: anchor quantities (general_tracking.py:738-803), the same values in every lane -----------
       Q4 g_raq = {0.f, 0.f, 0.f, 1.f}, g_dori = {0.f, 0.f, 0.f, 1.f};  // robot anchor rotation; delta_ori_w
       V3 g_ap = {0.f, 0.f, 0.f}, g_dpos = {0.f, 0.f, 0.f};              // reference anchor position; delta_pos_w
@@ -646,6 +679,7 @@ __device__ __forceinline__ void track_body(const TrackParams& P) {
 #pragma unroll
       for (int i = 0; i < 16; ++i) sums[i] = 0.0f;
       int far = 0, n_collide = 0, bodyz = 0, hit = 0;
+      float rb_dot = 0.f, rb_cc = 0.f, rb_rr = 0.f;  // teleop_radial_body_velocity_extend
 #pragma unroll 1
       for (int j0 = 0; j0 < J; j0 += 32) {  // (one copy of the body section: the specialised kernel knows J and would duplicate it for a 33rd body)
         const int j = j0 + lane;
@@ -743,10 +777,34 @@ __device__ __forceinline__ void track_body(const TrackParams& P) {
             emit3<kNoise>(T, rows, S_LOCAL_REF_VEL, 3 * j, lv.x, lv.y, lv.z, nk);
             emit3<kNoise>(T, rows, S_GLOBAL_REF_VEL, 3 * j, rvv[0], rvv[1], rvv[2], nk);
           }
+          if (c.src_used_mask & (1ull << S_LOCAL_REF_RELYAW)) {  // the reference VELOCITIES in the relyaw frame (motion_tracking.py:720-721)
+            const V3 ly = quat_rotate_z(ry_z, ry_w, {rvv[0], rvv[1], rvv[2]});
+            emit3<kNoise>(T, rows, S_LOCAL_REF_RELYAW, 3 * j, ly.x, ly.y, ly.z, nk);
+          }
+          if ((c.src_used_mask & (1ull << S_VR3PT)) && (c.vr3_mask & bit)) {
+            // _obs_vr_3point_pos (:724-731): `heading_inv_rot.repeat(3, 1)` pairs row 3 n + k with the heading of env (3 n + k) mod N
+            for (int k = 0; k < 3; ++k)
+              if (c.vr3_ids[k] == j) {
+                const int64_t src = (3 * n + k) % P.n;
+                const float2 h = reinterpret_cast<const float2*>(io.heading_scratch)[src];
+                const V3 o = quat_rotate_z(h.x, h.y, {rpz[0] - rp.x, rpz[1] - rp.y, rpz[2] - rp.z});
+                emit3<kNoise>(T, rows, S_VR3PT, 3 * k, o.x, o.y, o.z, nk);
+              }
+          }
+          if (!kGeneral && (P.rew_extra & 1)) {  // cur = body velocity, ref = dif + cur (motion_tracking.py:1238-1244)
+            const V3 rf = {dv.x + v.x, dv.y + v.y, dv.z + v.z};
+            rb_dot += (v.x * rf.x + v.y * rf.y) + v.z * rf.z;
+            rb_cc += (v.x * v.x + v.y * v.y) + v.z * v.z;
+            rb_rr += (rf.x * rf.x + rf.y * rf.y) + rf.z * rf.z;
+          }
         }
         n_collide += __popc(__ballot_sync(0xffffffffu, collide));
       }
       const bool any_far = __any_sync(0xffffffffu, far);
+      if (!kGeneral && (P.rew_extra & 1)) {
+        rb_dot = warp_sum(rb_dot); rb_cc = warp_sum(rb_cc); rb_rr = warp_sum(rb_rr);
+        if (lane == 0) rv[V_RAD_BODY] = radial_potential(rb_dot, rb_cc, rb_rr);
+      }
       // ---- C. dofs (lane = dof) ---------------------------------------------------------------------------
       float dpos = 0.f, dvel = 0.f, act = 0.f, tq = 0.f, lact = 0.f, ldv = 0.f, ddef = 0.f, kp = 1.f, kd = 1.f;
       float dja = 0.f, djv = 0.f;
@@ -761,6 +819,29 @@ __device__ __forceinline__ void track_body(const TrackParams& P) {
         djv = (omb * __ldg(r0 + e_dv + lane) + b * __ldg(r1 + e_dv + lane)) - dvel;
       }
       const float max_dja = warp_max(fabsf(dja));
+      if constexpr (!kGeneral) {
+        if (P.rew_extra & 2) {  // teleop_radial_joint_velocity (motion_tracking.py:1286-1293): cur = dof_vel, ref = dif + cur
+          const float rf = djv + dvel;
+          const float d0 = warp_sum(ld ? dvel * rf : 0.f), d1 = warp_sum(ld ? dvel * dvel : 0.f), d2 = warp_sum(ld ? rf * rf : 0.f);
+          if (lane == 0) rv[V_RAD_JOINT] = radial_potential(d0, d1, d2);
+        }
+        if (c.n_future > 0 && (c.src_used_mask & ((1ull << S_FUT_REF_DOF_POS) | (1ull << S_FUT_REF_DOF_VEL)))) {
+          // kick_motion_res_multiplestep (motion_tracking.py:562-579, 594-599): reference dofs at (episode_length + 1 + i) dt + start
+          const int64_t ep1 = *reinterpret_cast<const long long*>(rv + V_EP) + 1;
+          const float st = rv[V_ENVF];
+#pragma unroll 1
+          for (int s2 = 0; s2 < c.n_future; ++s2) {
+            const FrameBlend fb = frame_blend(tab, clip, (float)(ep1 + 1 + s2) * c.dt + st);
+            const float* q0 = tab.records + fb.f0 * tab.rec_stride;
+            const float* q1 = tab.records + fb.f1 * tab.rec_stride;
+            const float bb = fb.blend, ob = 1.0f - bb;
+            if (ld) {
+              emit1<kNoise>(T, rows, S_FUT_REF_DOF_POS, s2 * D + lane, ob * __ldg(q0 + e_dp + lane) + bb * __ldg(q1 + e_dp + lane), nk);
+              emit1<kNoise>(T, rows, S_FUT_REF_DOF_VEL, s2 * D + lane, ob * __ldg(q0 + e_dv + lane) + bb * __ldg(q1 + e_dv + lane), nk);
+            }
+          }
+        }
+      }
       if constexpr (kGeneral) {  // the body sums take the whole first reduction; the dof sums get their own
         const float tot = warp_sum16(sums, lane);
         const int idx = (lane >> 1) & 15;
@@ -845,6 +926,21 @@ __device__ __forceinline__ void track_body(const TrackParams& P) {
         x_stumble = norm2_z(fc[0], fc[1]) > 5.0f * fabsf(fc[2]);                  // :1325-1328
         x_slip = norm3_z(bs[7], bs[8], bs[9]) * (fn > 1.0f ? 1.0f : 0.0f);        // legged_robot_base.py:1004-1010
         x_fslip = (fn > 1.0f ? 1.0f : 0.0f) * norm2_z(bs[7], bs[8]);              // :1012-1017
+      }
+      if (P.rew_extra & 0x3c) {  // feet_heading_alignment(_contact), penalty_feet_ori(_contact): legged_robot_base.py:1031-1082
+        float hd = 0.f, ori = 0.f;
+        if (lane < c.n_feet) {
+          const float* bs = sm_body + 13 * my_foot;
+          const Q4 fq = {bs[3], bs[4], bs[5], bs[6]};
+          const V3 ff = quat_apply(fq, {1.0f, 0.0f, 0.0f}), rf = quat_apply(rootq, {1.0f, 0.0f, 0.0f});
+          hd = fabsf(wrap_to_pi(atan2f(ff.y, ff.x) - atan2f(rf.y, rf.x)));
+          const V3 g = quat_rotate_inverse(fq, {0.0f, 0.0f, -1.0f});
+          ori = sqrtf(g.x * g.x + g.y * g.y);
+        }
+        const float hc = hd * cm_f, oc = ori * cm_f;
+        const float s_hd = hd + __shfl_xor_sync(0xffffffffu, hd, 1), s_ori = ori + __shfl_xor_sync(0xffffffffu, ori, 1);
+        const float s_hc = hc + __shfl_xor_sync(0xffffffffu, hc, 1), s_oc = oc + __shfl_xor_sync(0xffffffffu, oc, 1);
+        if (lane == 0) { rv[V_FEET_HEAD] = s_hd; rv[V_FEET_ORI] = s_ori; rv[V_FEET_HEAD_C] = s_hc; rv[V_FEET_ORI_C] = s_oc; }
       }
       x_air += __shfl_xor_sync(0xffffffffu, x_air, 1); x_force += __shfl_xor_sync(0xffffffffu, x_force, 1);
       x_slip += __shfl_xor_sync(0xffffffffu, x_slip, 1); x_fslip += __shfl_xor_sync(0xffffffffu, x_fslip, 1);
@@ -1122,6 +1218,7 @@ __device__ __forceinline__ void track_body(const TrackParams& P) {
         emit1<kNoise>(T, rows, k, ce, val, nk);
       }
       for (int i = lane; i < L; i += 32) emit1<kNoise>(T, rows, S_DR_MASS, i, io.link_mass_scale[n * L + i], nk);
+      if ((c.src_used_mask & (1ull << S_RELYAW)) && lane == 0) emit1<kNoise>(T, rows, S_RELYAW, 0, relyaw, nk);  // stale for envs that reset, like the reference
       if constexpr (kGeneral) {  // getters of general_tracking.py:879-891, legged_robot_base.py:1193
         const float cmv = __shfl_sync(0xffffffffu, cm_f, (lane - 2) & 31);  // contacts_filt (zeroed by a reset, :664-666)
         if (lane < 6) {
@@ -1193,6 +1290,22 @@ extern "C" __global__ void __launch_bounds__(pbhc::kTW * 32, 2) pbhc_track_spec(
   pbhc::track_body<PBHC_NOISE != 0, true>(P);
 }
 #else
+// every env's inverse heading quaternion (z, w) BEFORE the step: what the vr_3point_pos observation of another env reads
+__global__ void heading_kernel(const float* __restrict__ root_state, int64_t n, float* __restrict__ out) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const float* r = root_state + i * 13;
+  const Q4 h = heading_quat_inv_fast({r[3], r[4], r[5], r[6]});
+  reinterpret_cast<float2*>(out)[i] = make_float2(h.z, h.w);
+}
+
+// configs only the warp-per-env kernel serves: the observation sources and reward terms added with ABI 9
+static bool needs_warp_kernel(const PbhcTrackCfg& c) {
+  if (c.src_used_mask >> S_RELYAW) return true;
+  for (int r = 0; r < c.n_rewards; ++r) if (c.reward_id[r] >= R_RADIAL_BODY_VEL) return true;
+  return false;
+}
+
 template <bool kNoise, bool kGeneral>
 __global__ void __launch_bounds__(kTW * 32, kGeneral ? 2 : F_BPS) track_kernel(const __grid_constant__ TrackParams P) { track_body<kNoise, kGeneral>(P); }
 
@@ -1410,6 +1523,7 @@ extern "C" int pbhc_track_specialize(const PbhcTrackCfg* cfg, const PbhcTableDes
     for (int k = 0; k < PBHC_NUM_OBS_SRC; ++k) noise |= cfg->obs_noise[k] != 0.0f;
     return pbhc::jit_track(*cfg, noise, nullptr) == 0 ? PBHC_OK : PBHC_E_CUDA;
   }
+  if (pbhc::needs_warp_kernel(*cfg)) return PBHC_OK;  // served by the generic warp-per-env kernel
   return pbhc::track_tile_prepare(*cfg, *tab, *io);
 }
 
@@ -1443,24 +1557,43 @@ extern "C" int pbhc_track_step(const PbhcTrackCfg* cfg, const PbhcTableDesc* tab
     }
     for (int i = 0; i < c.n_key; ++i) if (c.key_ids[i] < 0 || c.key_ids[i] >= c.J) { set_error("pbhc_track_step: key body %d out of range", i); return PBHC_E_RANGE; }
     for (int k = S_FUT_HEIGHT; k <= S_FUT_KEY; ++k) if (c.obs_noise[k] != 0.0f) { set_error("pbhc_track_step: noise on future-target observations is not implemented"); return PBHC_E_RANGE; }
+    if ((c.src_used_mask >> S_FUT_REF_DOF_POS) & 3ull) { set_error("pbhc_track_step: future_ref_dof_pos / _vel exist only in motion_tracking"); return PBHC_E_RANGE; }
+    for (int r = 0; r < c.n_rewards; ++r)
+      if (c.reward_id[r] == R_RADIAL_BODY_VEL || c.reward_id[r] == R_RADIAL_JOINT_VEL) { set_error("pbhc_track_step: the radial velocity rewards exist only in motion_tracking"); return PBHC_E_RANGE; }
     for (int r = 0; r < c.n_rewards; ++r)
       if (c.reward_id[r] == R_BODY_ROT || c.reward_id[r] == R_BODY_VEL || c.reward_id[r] == R_BODY_ANG_VEL) {
         set_error("pbhc_track_step: whole-body rotation / velocity rewards are not implemented for general_tracking"); return PBHC_E_RANGE;
       }
   } else {
-    for (int k = S_ROLL_PITCH; k < PBHC_NUM_OBS_SRC; ++k)
+    for (int k = S_ROLL_PITCH; k <= S_FUT_KEY; ++k)
       if ((c.src_used_mask >> k) & 1ull) { set_error("pbhc_track_step: observation source %d exists only in general_tracking", k); return PBHC_E_RANGE; }
-    for (int r = 0; r < c.n_rewards; ++r) if (c.reward_id[r] >= R_ROOT_VEL) { set_error("pbhc_track_step: reward %d exists only in general_tracking", c.reward_id[r]); return PBHC_E_RANGE; }
+    if (c.n_future < 0 || c.n_future > PBHC_MAX_FUTURE) { set_error("pbhc_track_step: future_ref_steps outside [0, %d]", PBHC_MAX_FUTURE); return PBHC_E_RANGE; }
+    for (int r = 0; r < c.n_rewards; ++r) if (c.reward_id[r] >= R_ROOT_VEL && c.reward_id[r] <= R_KEY_ANG) { set_error("pbhc_track_step: reward %d exists only in general_tracking", c.reward_id[r]); return PBHC_E_RANGE; }
   }
   TrackParams P;
   P.c = c; P.tab = *tab; P.io = *io; P.n = n;
+  P.rew_extra = 0;
+  for (int r = 0; r < c.n_rewards; ++r) {
+    if (c.reward_id[r] > R_FEET_ORI_CONTACT || c.reward_id[r] < 0) { set_error("pbhc_track_step: unknown reward id %d", c.reward_id[r]); return PBHC_E_RANGE; }
+    if (c.reward_id[r] >= R_RADIAL_BODY_VEL) P.rew_extra |= 1 << (c.reward_id[r] - R_RADIAL_BODY_VEL);
+  }
+  if ((P.rew_extra & 0x3c) && c.n_feet != 2) { set_error("pbhc_track_step: the feet heading / orientation rewards take exactly two feet"); return PBHC_E_RANGE; }
+  P.need_rootq = ((P.rew_extra & 0x3c) || (c.src_used_mask & ((1ull << S_RELYAW) | (1ull << S_LOCAL_REF_RELYAW)))) ? 1 : 0;
+  if (c.src_used_mask & (1ull << S_VR3PT)) {
+    if (c.n_vr3 != 3 || !io->heading_scratch || ((uintptr_t)io->heading_scratch & 7)) {
+      set_error("pbhc_track_step: vr_3point_pos needs three motion_tracking_link bodies and an 8-byte aligned heading_scratch [N,2]"); return PBHC_E_BADARG;
+    }
+    for (int k = 0; k < 3; ++k) if (c.vr3_ids[k] < 0 || c.vr3_ids[k] >= c.J) { set_error("pbhc_track_step: vr3_ids[%d] out of range", k); return PBHC_E_RANGE; }
+  }
+  for (int k = S_FUT_REF_DOF_POS; k <= S_FUT_REF_DOF_VEL; ++k)
+    if (((c.src_used_mask >> k) & 1ull) && c.obs_noise[k] != 0.0f && c.n_future * c.D > 256) { set_error("pbhc_track_step: noise on future_ref_dof_* needs future_ref_steps * D <= 256"); return PBHC_E_RANGE; }
   P.has_air_time = 0;
   for (int r = 0; r < c.n_rewards; ++r) if (c.reward_id[r] == R_FEET_AIR_TIME) P.has_air_time = 1;
   // a group made only of future-target sources never passes through shared memory
   for (int g = 0; g < PBHC_MAX_OBS_GROUPS; ++g) {
     bool fut = false, other = false;
     if (c.general && g < c.n_groups) {
-      for (int k = 0; k < PBHC_NUM_OBS_SRC; ++k) if (c.src_dst[k][g] >= 0) (k >= S_FUT_HEIGHT ? fut : other) = true;
+      for (int k = 0; k < PBHC_NUM_OBS_SRC; ++k) if (c.src_dst[k][g] >= 0) ((k >= S_FUT_HEIGHT && k <= S_FUT_KEY) ? fut : other) = true;
       for (int e = 0; e < c.n_hist_dst; ++e) if (c.hist_dst[e].group == g) other = true;
     }
     P.group_direct[g] = (fut && !other) ? 1 : 0;
@@ -1496,12 +1629,13 @@ extern "C" int pbhc_track_step(const PbhcTrackCfg* cfg, const PbhcTableDesc* tab
   }
   for (int k = 0; k < c.n_hist_keys; ++k) if (c.hist_len[k] <= 0 || c.hist_dim[k] != src_dim(c.hist_src[k], c.D, c.J, c.L, c.n_key, c.n_future)) { set_error("pbhc_track_step: bad history key %d", k); return PBHC_E_BADARG; }
   if (n == 0) return PBHC_OK;
+  if (c.src_used_mask & (1ull << S_VR3PT)) heading_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(io->root_state, n, io->heading_scratch);
   // LeggedRobotMotionTracking runs on the tile kernel (csrc/track_tile.cu); the warp-per-env kernel below serves
   // LeggedRobotGeneralTracking and the configs the tile kernel does not take (a body- or joint-difference source kept in
   // the history; PBHC_TRACK_KERNEL=warp forces it for A/B measurements)
   if (!c.general) {
     static const bool force_warp = [] { const char* e = getenv("PBHC_TRACK_KERNEL"); return e && e[0] == 'w'; }();
-    bool tile_ok = !force_warp && c.n_feet >= 1;
+    bool tile_ok = !force_warp && c.n_feet >= 1 && !needs_warp_kernel(c);
     for (int k = 0; k < c.n_hist_keys; ++k) {
       const int s = c.hist_src[k];
       if (s == S_DIF_LOCAL || s == S_LOCAL_REF || s == S_LOCAL_REF_VEL || s == S_GLOBAL_REF_VEL || s == S_DIF_JOINT || s == S_DIF_JOINT_VEL) tile_ok = false;
@@ -1519,7 +1653,7 @@ extern "C" int pbhc_track_step(const PbhcTrackCfg* cfg, const PbhcTableDesc* tab
   P.dump = P.rows_len;                                   // scratch for absent destinations: one source wide
   // (widest source: 3*J body features, 6*n_key key-body rotations, 7+D+3K next-step block, L link masses, 64 history lanes)
   int widest = 3 * c.J + 4;
-  for (int k = 0; k < PBHC_NUM_OBS_SRC; ++k) { const int w = src_dim(k, c.D, c.J, c.L, c.n_key, 0); if (w > widest) widest = w; }
+  for (int k = 0; k < PBHC_NUM_OBS_SRC; ++k) { const int w = src_dim(k, c.D, c.J, c.L, c.n_key, c.general ? 0 : c.n_future); if (w > widest) widest = w; }
   if (widest < 64) widest = 64;
   const int dump_len = up4h(widest);
   // per-warp layout: the fixed-size tables first, so that the kernel reaches rv / pre / the staging buffer with

@@ -16,13 +16,21 @@ enum ObsSrc { S_BASE_LIN_VEL, S_BASE_ANG_VEL, S_PROJ_GRAV, S_DOF_POS, S_DOF_VEL,
               S_GLOBAL_REF_VEL, S_DIF_JOINT, S_DIF_JOINT_VEL, S_BASE_POS_Z,
               // LeggedRobotGeneralTracking
               S_ROLL_PITCH, S_LKEY_POS, S_LKEY_ROT, S_ANCHOR_POS, S_ANCHOR_ROT, S_NEXT_STEP, S_CONTACT_MASK, S_ROOT_HEIGHT,
-              S_DR_BASE_MASS, S_FUT_HEIGHT, S_FUT_RP, S_FUT_LIN, S_FUT_YAW, S_FUT_DOF, S_FUT_KEY };
-static_assert(S_FUT_KEY + 1 == PBHC_NUM_OBS_SRC, "ObsSrc and PBHC_NUM_OBS_SRC disagree");
+              S_DR_BASE_MASS, S_FUT_HEIGHT, S_FUT_RP, S_FUT_LIN, S_FUT_YAW, S_FUT_DOF, S_FUT_KEY,
+              // both env classes (motion_tracking.py:686-731 / general_tracking.py:682-725): warp-per-env kernel only
+              S_RELYAW, S_LOCAL_REF_RELYAW, S_VR3PT,
+              // LeggedRobotMotionTracking with obs.future_ref_steps > 0 (motion_tracking.py:594-599)
+              S_FUT_REF_DOF_POS, S_FUT_REF_DOF_VEL };
+static_assert(S_FUT_REF_DOF_VEL + 1 == PBHC_NUM_OBS_SRC, "ObsSrc and PBHC_NUM_OBS_SRC disagree");
 enum RewardId { R_CONTACT_MASK, R_MAX_JOINT_POS, R_BODY_POS_EXT, R_VR3, R_FEET_POS, R_BODY_ROT, R_BODY_ANG_VEL,
                 R_BODY_VEL, R_JOINT_POS, R_JOINT_VEL, R_TORQUES, R_ACTION_RATE, R_FEET_AIR_TIME, R_FEET_FORCES,
                 R_STUMBLE, R_SLIPPAGE, R_LIM_DOF_POS, R_LIM_DOF_VEL, R_LIM_TORQUE, R_COLLISION, R_DOF_VEL, R_DOF_ACC,
                 R_FOOT_SLIP, R_ALIVE, R_ORIENTATION, R_CONTACT_MASK_V2,
-                R_ROOT_VEL, R_ANCHOR_POS, R_ANCHOR_ROT, R_LKEY_POS, R_LKEY_ROT, R_KEY_VEL, R_KEY_ANG };
+                R_ROOT_VEL, R_ANCHOR_POS, R_ANCHOR_ROT, R_LKEY_POS, R_LKEY_ROT, R_KEY_VEL, R_KEY_ANG,
+                // zero-scaled in the shipped configs: warp-per-env kernel only.  The two radial terms exist in
+                // LeggedRobotMotionTracking only (motion_tracking.py:1238-1244, 1286-1293), the feet terms in the base class
+                // (legged_robot_base.py:1031-1082)
+                R_RADIAL_BODY_VEL, R_RADIAL_JOINT_VEL, R_FEET_HEADING, R_FEET_ORI, R_FEET_HEADING_CONTACT, R_FEET_ORI_CONTACT };
 enum SigmaId { G_MAX_JOINT, G_UPPER, G_LOWER, G_VR3, G_FEET, G_ROT, G_VEL, G_ANG_VEL, G_JOINT_POS, G_JOINT_VEL,
                G_ROOT_VEL, G_ANCHOR_POS, G_ANCHOR_ROT, G_LKEY_POS, G_LKEY_ROT, G_KEY_VEL, G_KEY_ANG };
 static_assert(G_KEY_ANG + 1 == PBHC_NUM_SIGMA, "SigmaId and PBHC_NUM_SIGMA disagree");
@@ -30,7 +38,9 @@ static_assert(G_KEY_ANG + 1 == PBHC_NUM_SIGMA, "SigmaId and PBHC_NUM_SIGMA disag
 enum Rv { V_SIGMA_ERR = 0, V_UP_N = 17, V_LO_N, V_VR_N, V_JOINT_N, V_T_GRAV, V_T_FAR, V_T_OUT, V_T_END, V_RESET, V_RESET_EPLEN,
           V_ETR, V_ETR_SQ, V_ONE, V_KEY_N = 32, V_LUP_N, V_LLO_N, V_LVR_N, V_LKEY_N, V_T_REFZ, V_T_ORI, V_T_BODYZ,
           V_CONTACT = 40, V_CONTACT_V2, V_TQ2, V_DACT2, V_DV2, V_ACC2, V_ORIENT, V_ALIVE, V_AIR, V_FORCE,
-          V_STUMBLE, V_SLIP, V_FSLIP, V_LIM_POS, V_LIM_VEL, V_LIM_TQ, V_COLLIDE, V_ENVF = 60 /* 8 floats */, V_EP = 68 /* int64 */ };
+          V_STUMBLE, V_SLIP, V_FSLIP, V_LIM_POS, V_LIM_VEL, V_LIM_TQ, V_COLLIDE, V_RAD_BODY, V_RAD_JOINT, V_FEET_HEAD,
+          V_ENVF = 60 /* 8 floats */, V_EP = 68 /* int64 */, V_FEET_ORI = 70, V_FEET_HEAD_C, V_FEET_ORI_C = 31 };
+static_assert(V_FEET_HEAD == 59 && V_FEET_HEAD_C == 71, "rv layout");
 static_assert(V_UP_N == PBHC_A_UPPER_NORM && V_ONE == PBHC_A_NUM_ENVS && V_KEY_N == PBHC_A_KEY_NORM && V_T_BODYZ == PBHC_A_TERM_BODY_Z &&
               V_RESET_EPLEN == PBHC_A_RESET_EPLEN && V_ETR_SQ == PBHC_A_ETR_SQ, "rv and acc layouts disagree");
 constexpr int kAccLo = PBHC_A_NUM_ENVS + 1;  // slots [0, kAccLo) are accumulated by lane = slot; general_tracking adds [32, 40)
@@ -50,14 +60,16 @@ __host__ __device__ inline int src_dim(int k, int D, int J, int L, int K = 0, in
     case S_LKEY_ROT: return 6 * K;
     case S_ANCHOR_ROT: return 6;
     case S_NEXT_STEP: return 7 + D + 3 * K;
-    case S_ROOT_HEIGHT: case S_DR_BASE_MASS: return 1;
+    case S_ROOT_HEIGHT: case S_DR_BASE_MASS: case S_RELYAW: return 1;
+    case S_VR3PT: return 9;
+    case S_FUT_REF_DOF_POS: case S_FUT_REF_DOF_VEL: return F * D;
     case S_FUT_HEIGHT: case S_FUT_YAW: return F;
     case S_FUT_RP: return 2 * F;
     case S_FUT_LIN: return 3 * F;
     case S_FUT_DOF: return F * D;
     case S_FUT_KEY: return F * 3 * K;
     case S_DOF_POS: case S_DOF_VEL: case S_ACTIONS: case S_DR_KP: case S_DR_KD: case S_DIF_JOINT: case S_DIF_JOINT_VEL: return D;
-    case S_DIF_LOCAL: case S_LOCAL_REF: case S_LOCAL_REF_VEL: case S_GLOBAL_REF_VEL: return 3 * J;
+    case S_DIF_LOCAL: case S_LOCAL_REF: case S_LOCAL_REF_VEL: case S_GLOBAL_REF_VEL: case S_LOCAL_REF_RELYAW: return 3 * J;
     case S_DR_MASS: return L;
     case S_PHASE: case S_DR_FRICTION: case S_DR_DELAY: case S_BASE_POS_Z: return 1;
     default: return 3;

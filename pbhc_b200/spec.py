@@ -18,7 +18,17 @@ REWARD_IDS = {name: i for i, name in enumerate([
     "foot_slip_penalty", "alive", "penalty_orientation", "teleop_contact_mask_v2",
     # general_tracking (general_tracking.py:1116-1270)
     "teleop_root_vel", "teleop_anchor_body_position", "teleop_anchor_body_rotation", "local_key_body_position",
-    "local_key_body_rotation", "key_body_velocity", "key_body_ang_velocity"])}
+    "local_key_body_rotation", "key_body_velocity", "key_body_ang_velocity",
+    # zero-scaled in every shipped config; the radial terms are LeggedRobotMotionTracking's
+    # (motion_tracking.py:1238-1244, 1286-1293), the feet terms the base class's (legged_robot_base.py:1031-1082)
+    "teleop_radial_body_velocity_extend", "teleop_radial_joint_velocity", "feet_heading_alignment", "penalty_feet_ori",
+    "feet_heading_alignment_contact", "penalty_feet_ori_contact"])}
+MT_ONLY_REWARDS = {"teleop_radial_body_velocity_extend", "teleop_radial_joint_velocity"}
+# reward functions of the reference that cannot run there (so there is nothing to be equal to): what they trip over
+BROKEN_IN_REFERENCE = {
+    "feet_max_height_for_this_air": "`~self.last_contacts_filt` on a float tensor raises (legged_robot_base.py:68, 1022)",
+    "teleop_key_body_position": "no config defines reward_tracking_sigma.teleop_key_body_pos (general_tracking.py:1112)",
+    "teleop_root_pose": "no config defines reward_tracking_sigma.teleop_root_pose (general_tracking.py:1276)"}
 
 # adaptive-sigma slots (config.rewards.reward_tracking_sigma keys), in enum order
 SIGMA_IDS = {name: i for i, name in enumerate([
@@ -37,8 +47,13 @@ OBS_SRC = ["base_lin_vel", "base_ang_vel", "projected_gravity", "dof_pos", "dof_
            "roll_pitch", "local_key_body_pos", "local_key_body_rot", "anchor_ref_pos", "anchor_ref_rot", "next_step_ref_motion",
            "contact_mask", "root_height", "dr_base_mass", "future_motion_root_height", "future_motion_roll_pitch",
            "future_motion_base_lin_vel", "future_motion_base_yaw_vel", "future_motion_dof_pos",
-           "future_motion_local_ref_key_body_pos"]
-GENERAL_ONLY_SRC = set(OBS_SRC[OBS_SRC.index("roll_pitch"):])
+           "future_motion_local_ref_key_body_pos",
+           # both env classes (motion_tracking.py:950-961 / general_tracking.py:837-850); warp-per-env kernel
+           "relyaw", "local_ref_rigid_body_pos_relyaw", "vr_3point_pos",
+           # LeggedRobotMotionTracking with obs.future_ref_steps > 0 (motion_tracking.py:594-599, 986-990)
+           "future_ref_dof_pos", "future_ref_dof_vel"]
+GENERAL_ONLY_SRC = set(OBS_SRC[OBS_SRC.index("roll_pitch"):OBS_SRC.index("relyaw")])
+MT_ONLY_SRC = {"future_ref_dof_pos", "future_ref_dof_vel"}
 OBS_SRC_IDS = {k: i for i, k in enumerate(OBS_SRC)}
 
 
@@ -46,6 +61,7 @@ def obs_src_dim(key, D, J, L, K=0, F=0):
     """K = number of key bodies, F = future_num_steps (general_tracking only)."""
     return {"roll_pitch": 2, "local_key_body_pos": 3 * K, "local_key_body_rot": 6 * K, "anchor_ref_pos": 3, "anchor_ref_rot": 6,
             "next_step_ref_motion": 7 + D + 3 * K, "contact_mask": 2, "root_height": 1, "dr_base_mass": 1,
+            "relyaw": 1, "local_ref_rigid_body_pos_relyaw": 3 * J, "vr_3point_pos": 9, "future_ref_dof_pos": F * D, "future_ref_dof_vel": F * D,
             "future_motion_root_height": F, "future_motion_roll_pitch": 2 * F, "future_motion_base_lin_vel": 3 * F,
             "future_motion_base_yaw_vel": F, "future_motion_dof_pos": F * D, "future_motion_local_ref_key_body_pos": F * 3 * K,
             "base_lin_vel": 3, "base_ang_vel": 3, "projected_gravity": 3, "dof_pos": D, "dof_vel": D, "actions": D,
@@ -135,9 +151,13 @@ class TrackSpec:
             if name == "termination":
                 self.termination_scale = scale
                 continue
+            if name in BROKEN_IN_REFERENCE:
+                raise NotImplementedError(f"reward term '{name}' cannot run in the reference: {BROKEN_IN_REFERENCE[name]}")
             if name not in REWARD_IDS:
                 raise NotImplementedError(f"reward term '{name}' is not implemented by the B200 tracking step")
-            general_only = REWARD_IDS[name] >= REWARD_IDS["teleop_root_vel"]
+            if name in MT_ONLY_REWARDS and self.general:
+                raise NotImplementedError(f"reward term '{name}' exists only in motion_tracking")
+            general_only = REWARD_IDS["teleop_root_vel"] <= REWARD_IDS[name] <= REWARD_IDS["key_body_ang_velocity"]
             if general_only and not self.general:
                 raise NotImplementedError(f"reward term '{name}' exists only in general_tracking")
             if self.general and name in ("teleop_body_rotation_extend", "teleop_body_velocity_extend", "teleop_body_ang_velocity_extend"):
@@ -227,10 +247,11 @@ class TrackSpec:
         D, J = self.D, self.J
         self.L = len(_get(dr, "randomize_link_body_names", []) or [])
         K = len(self.key_ids)
-        self.future_num_steps = int(_get(obs, "future_num_steps", 0) or 0) if self.general else 0
+        # general_tracking: obs.future_num_steps targets; motion_tracking: obs.future_ref_steps reference dof frames (:594-599)
+        self.future_num_steps = int(_get(obs, "future_num_steps", 0) or 0) if self.general else int(_get(obs, "future_ref_steps", 0) or 0)
         self.future_max_steps = int(_get(obs, "future_max_steps", 0) or 0)
         F = self.future_num_steps
-        if F > 0:  # torch.linspace(1, max, F, dtype=long) (general_tracking.py:501-507), evaluated by torch itself
+        if F > 0 and self.general:  # torch.linspace(1, max, F, dtype=long) (general_tracking.py:501-507), evaluated by torch itself
             import torch
             self.future_steps = [int(v) for v in torch.linspace(start=1, end=self.future_max_steps, steps=F, dtype=torch.long)]
         else:
@@ -262,6 +283,10 @@ class TrackSpec:
                 else:
                     if key in GENERAL_ONLY_SRC and not self.general:
                         raise NotImplementedError(f"observation '{key}' exists only in general_tracking")
+                    if key in MT_ONLY_SRC and (self.general or F <= 0):
+                        raise NotImplementedError(f"observation '{key}' needs motion_tracking with obs.future_ref_steps > 0")
+                    if key == "vr_3point_pos" and len(self.vr3_ids) != 3:
+                        raise ValueError("vr_3point_pos: the reference pairs 3 points per env with `heading_inv_rot.repeat(3, 1)`")
                     n = obs_src_dim(key, D, J, self.L, K, F)
                     segs.append(dict(kind="src", key=key, dim=n, off=off, scale=self.obs_scales[key],
                                      noise=self.noise_scales[key]))

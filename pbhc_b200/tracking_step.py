@@ -107,9 +107,23 @@ class TrackingStep:
         self._reset_count = torch.zeros(1, device=dev, dtype=torch.int32)
         self._compact_scratch = torch.zeros(max(int(self._L.pbhc_compact_scratch_ints(N)), 1), device=dev, dtype=torch.int32)
         self._build_cfg(seed)
+        used = int(self._cfg.src_used_mask)
+        self._heading_scratch = torch.zeros(N, 2, **f32) if used >> OBS_SRC_IDS["vr_3point_pos"] & 1 else None
+        if used >> OBS_SRC_IDS["relyaw"] & 3:
+            # ref_init_rpy (motion_tracking.py:186-187): the env is built with episode_length_buf = 0 and motion_start_times = 0,
+            # so kick_motion_res() reads motion 0 at time 1 * dt; euler yaw of that root rotation (rotations.py:381-385)
+            q = motion_lib.get_motion_state(torch.zeros(1, device=dev, dtype=torch.int64), torch.full((1,), float(s.dt), **f32))["root_rot"][0].float()
+            siny = 2.0 * (q[3] * q[2] + q[0] * q[1])
+            cosy = q[3] * q[3] + q[0] * q[0] - q[1] * q[1] - q[2] * q[2]
+            self.set_ref_init_yaw(float(torch.atan2(siny, cosy)))
         self._io = _lib.TrackIO()
         self._io.env_offset = int(env_offset)  # global id of this rank's env 0 (pbhc_b200.dist.shard_range): keys the in-kernel random streams
         self._keep = None
+
+    def set_ref_init_yaw(self, yaw):
+        """ref_init_rpy[0, 2] of the reference env (`relyaw = rpy[:, 2:3] - ref_init_rpy[0, 2]`, motion_tracking.py:686)."""
+        self.ref_init_yaw = float(yaw)
+        self._cfg.ref_init_yaw = float(yaw)
 
     # ---- reference attribute names as views ------------------------------------------------------------
     motion_start_times = property(lambda self: self.env_f32[:, 0])
@@ -256,6 +270,13 @@ class TrackingStep:
             c.n_future = s.future_num_steps
             for i, v in enumerate(s.future_steps):
                 c.future_steps[i] = v
+        else:
+            if s.future_num_steps > _lib.MAX_FUTURE:
+                raise NotImplementedError("too many future_ref_steps for the B200 tracking step")
+            c.n_future = s.future_num_steps  # obs.future_ref_steps (motion_tracking.py:594-599)
+        for i, v in enumerate(s.vr3_ids[:4]):
+            c.vr3_ids[i] = v
+        c.ref_init_yaw = 0.0  # set_ref_init_yaw / __init__
         # base-class terminations (legged_robot_base.py:433-476)
         c.term_contact, c.term_contact_mask = int(s.term_contact), _mask(s.term_contact_ids)
         c.term_low_height, c.term_min_height = int(s.term_low_height), s.term_min_height
@@ -335,6 +356,7 @@ class TrackingStep:
         io.inject_term_gates = int(inj.get("term_gates", -1))
         ft = self._future_table()
         io.fut_table, io.fut_stride = (p(ft), ft.shape[1]) if ft is not None else (None, 0)
+        io.heading_scratch = p(self._heading_scratch)
         self._keep = (sim, actions, torques, env_origins, motion_ids, inj)
 
     def _future_table(self):

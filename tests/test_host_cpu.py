@@ -58,3 +58,30 @@ def test_motion_lib_refuses_cpu(tmp_path):
     cfg = product_cfg("23", str(tmp_path), ["Horse-stance_pose"])
     with pytest.raises(_lib.PbhcError):
         MotionLibRobot(cfg, 4, "cpu")
+
+
+def test_track_spec_parses_the_unused_sources_and_names_the_terms_the_reference_cannot_run():
+    """TrackSpec (host logic, no GPU): the P4 / R15 keys of the reference resolve to source / reward ids; reward functions
+    that raise inside the reference itself are refused with the reason (spec.BROKEN_IN_REFERENCE)."""
+    import copy
+    import json
+    from pbhc_b200.spec import TrackSpec, OBS_SRC_IDS, REWARD_IDS, BROKEN_IN_REFERENCE
+    from tests._util import gold
+    cfg = json.loads(str(gold("ref_env_mt23_p4.npz")["meta_config_json"]))
+    s = TrackSpec.from_config(cfg)
+    assert s.future_num_steps == 3 and not s.general
+    keys = {seg["key"]: seg["dim"] for seg in s.obs_groups["critic_obs"]["segs"] if seg["kind"] == "src"}
+    assert keys["relyaw"] == 1 and keys["vr_3point_pos"] == 9 and keys["local_ref_rigid_body_pos_relyaw"] == 3 * s.J
+    assert keys["future_ref_dof_pos"] == keys["future_ref_dof_vel"] == 3 * s.D
+    assert OBS_SRC_IDS["future_ref_dof_vel"] == _lib.NUM_OBS_SRC - 1
+    for name in ("teleop_radial_body_velocity_extend", "teleop_radial_joint_velocity", "feet_heading_alignment", "penalty_feet_ori_contact"):
+        assert name in s.reward_names and name in REWARD_IDS
+    for name in BROKEN_IN_REFERENCE:
+        bad = copy.deepcopy(cfg)
+        bad["rewards"]["reward_scales"][name] = 1.0
+        with pytest.raises(NotImplementedError, match="cannot run in the reference"):
+            TrackSpec.from_config(bad)
+    g = json.loads(str(gold("ref_env_gt29_p4.npz")["meta_config_json"]))
+    g["rewards"]["reward_scales"]["teleop_radial_joint_velocity"] = 1.0  # LeggedRobotMotionTracking only
+    with pytest.raises(NotImplementedError, match="only in motion_tracking"):
+        TrackSpec.from_config(g)

@@ -36,7 +36,7 @@ def state_from(g, prefix, spec):
     return S
 
 
-@pytest.mark.parametrize("case", ["mt23_main", "mt23_bench", "gt29_teacher", "gt29_student", "mt23_edge", "gt29_edge", "mt23_term", "gt29_term"])
+@pytest.mark.parametrize("case", ["mt23_main", "mt23_bench", "gt29_teacher", "gt29_student", "mt23_edge", "gt29_edge", "mt23_term", "gt29_term", "mt23_p4", "gt29_p4"])
 def test_env_step_oracle_matches_reference(case):
     g, spec, N, tab = load_case(case)
     S = state_from(g, "init_", spec)

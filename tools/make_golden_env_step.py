@@ -109,6 +109,7 @@ def run_case(name, n_envs, n_steps, obs, seed, overrides=None, general=False, mo
            "meta_history_keys": np.array(list(env.history_handler.history.keys()))}
     for k, v in env_state(env).items():
         out["init_" + k] = v
+    out["init_ref_init_yaw"] = np.float64(float(env.ref_init_rpy[0, 2]))  # motion_tracking.py:186-187
     for step in range(n_steps):
         actions = synth.synth_actions(N, D, gen)
         env._pre_physics_step(actions)
@@ -205,6 +206,44 @@ def run_term():
     run_case("gt29_term", 32, 4, "motion_tracking/obs_ppo_teacher", 23, ovc, general=True, tweak=tweak_first, tweak_env=tweak_env)
 
 
+def run_p4():
+    """mt23_p4 / gt29_p4: the observation sources and reward terms no shipped config uses: relyaw,
+    local_ref_rigid_body_pos_relyaw, vr_3point_pos, future_ref_dof_pos / _vel (obs.future_ref_steps = 3; motion_tracking only);
+    teleop_radial_body_velocity_extend / teleop_radial_joint_velocity (motion_tracking only), feet_heading_alignment(_contact),
+    penalty_feet_ori(_contact)"""
+    import yaml
+    def obs_lists(path):
+        with open(os.path.join(R.REF_ROOT, "humanoidverse/config/obs", path + ".yaml")) as f:
+            d = yaml.safe_load(f)["obs"]["obs_dict"]
+        second = "critic_obs" if "critic_obs" in d else "priv_obs"
+        return list(d["actor_obs"]), list(d[second]), second
+    extra = ["relyaw", "local_ref_rigid_body_pos_relyaw", "vr_3point_pos"]
+    fut = ["future_ref_dof_pos", "future_ref_dof_vel"]
+    feet = {"feet_heading_alignment": -0.3, "penalty_feet_ori": -0.4, "feet_heading_alignment_contact": -0.2, "penalty_feet_ori_contact": -0.6}
+
+    def overrides(base, path, J, D, keys, rewards):
+        a, c, second = obs_lists(path)
+        ov = dict(base)
+        ov["obs.obs_dict.actor_obs"] = a + ["relyaw", "vr_3point_pos"]
+        ov[f"obs.obs_dict.{second}"] = c + keys
+        dims = {"relyaw": 1, "local_ref_rigid_body_pos_relyaw": 3 * J, "vr_3point_pos": 9, "future_ref_dof_pos": 3 * D, "future_ref_dof_vel": 3 * D}
+        scales = {"relyaw": 0.5, "local_ref_rigid_body_pos_relyaw": 1.0, "vr_3point_pos": 2.0, "future_ref_dof_pos": 1.0, "future_ref_dof_vel": 0.05}
+        for k in keys:
+            ov[f"obs.obs_dims.{k}"] = dims[k]
+            ov[f"obs.obs_scales.{k}"] = scales[k]
+            ov[f"obs.noise_scales.{k}"] = 0.0
+        for k, v in rewards.items():
+            ov[f"rewards.reward_scales.{k}"] = v
+        return ov
+    ov = overrides(ZERO_NOISE, "motion_tracking/main", 27, 23, extra + fut,
+                   dict(feet, teleop_radial_body_velocity_extend=0.7, teleop_radial_joint_velocity=0.9))
+    ov["obs.future_ref_steps"] = 3
+    if "general" not in sys.argv:
+        run_case("mt23_p4", 40, 5, "motion_tracking/main", 31, ov)
+    ovc = overrides(ZERO_NOISE_C, "motion_tracking/obs_ppo_teacher", 32, 29, extra, feet)
+    run_case("gt29_p4", 24, 3, "motion_tracking/obs_ppo_teacher", 32, ovc, general=True)
+
+
 def run(ns=None):
     # obs=main ships uniform observation noise (helpers.py:152, torch.rand_like): parity runs set the four
     # non-zero noise scales to 0 exactly like the reference's own obs/motion_tracking/benchmark.yaml does.
@@ -225,4 +264,4 @@ def run_general():
 
 if __name__ == "__main__":
     import sys
-    run_general() if "general" in sys.argv else (run_term() if "term" in sys.argv else run())
+    run_p4() if "p4" in sys.argv else (run_general() if "general" in sys.argv else (run_term() if "term" in sys.argv else run()))
