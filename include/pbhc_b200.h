@@ -16,7 +16,7 @@
 extern "C" {
 #endif
 
-#define PBHC_ABI_VERSION 9
+#define PBHC_ABI_VERSION 10
 #define PBHC_OK 0
 #define PBHC_E_BADARG (-1)
 #define PBHC_E_ALIGN (-2)
@@ -204,7 +204,8 @@ int pbhc_clips_prepare(const float* pos, const float* quat, const float* pose_aa
 #define PBHC_NUM_SIGMA 17   /* 10 + 7 of general_tracking, enum order of SIGMA_IDS */
 #define PBHC_MAX_KEY 16     /* key bodies (general_tracking) */
 #define PBHC_MAX_FUTURE 32  /* future reference steps (general_tracking) */
-#define PBHC_ENVF_STRIDE 8   /* env_f32 row: start_time, motion_len, air_time[2], last_contact[2], end_time_ratio, pad */
+#define PBHC_ENVF_STRIDE 8   /* env_f32 row: start_time, motion_len, air_time[2], last_contact[2], end_time_ratio, push word */
+/* the push word (ABI 10) is an int32 stored in the float slot: push_robot_counter | push_interval_s << 16 (legged_robot_base.py:135-147) */
 
 /* layout of `scalars` (device double[PBHC_SCALARS]) */
 #define PBHC_S_SIGMA 0        /* [17] reward_tracking_sigma, enum order of pbhc_b200/spec.py SIGMA_IDS */
@@ -358,6 +359,10 @@ typedef struct {
   float ref_init_yaw;                /* ref_init_rpy[0, 2] (motion_tracking.py:186-187): yaw of env 0's reference root rotation at construction */
   int32_t vr3_ids[4];                /* motion_tracking_id in config order (the layout of vr_3point_pos follows it); n_vr3 <= 3 entries used */
   /* LeggedRobotMotionTracking with obs.future_ref_steps > 0: n_future holds that count (future_steps is unused there) */
+  /* ABI 10: domain_rand.push_robots (legged_robot_base.py:134-147, 382-388, 1090-1106; on in the shipped domain_rand/main.yaml) */
+  int32_t push_robots, push_fixed;   /* _push_fixed: the drawn velocity is added to the root velocity instead of replacing it */
+  int32_t push_lo, push_hi;          /* push_interval_s: the next interval is randint(lo, hi) seconds */
+  float max_push_vel;                /* max_push_vel_xy: the push is U(-max, max) on root lin vel x / y */
 } PbhcTrackCfg;
 
 typedef struct {
@@ -416,6 +421,12 @@ typedef struct {
   float* heading_scratch;       /* [N,2] scratch, required when the vr_3point_pos observation is used: the reference rotates env i's k-th
                                  * point by the heading of env (3 i + k) mod N (`heading_inv_rot.repeat(3, 1)`, motion_tracking.py:730-731), so
                                  * every env's pre-reset heading is written here by a small kernel ahead of the step kernel */
+  /* ABI 10 */
+  int64_t* refresh_buf;         /* [N] nullable: need_to_refresh_envs after this step = reset or pushed (legged_robot_base.py:314-319, 1095);
+                                 * int64 0 / 1 like reset_buf, so pbhc_compact_ids turns it into refresh_env_ids */
+  float* push_vel;              /* [N,2] nullable: push_robot_vel_buf / record_push_robot_vel_buf rows of envs pushed this step */
+  const int64_t* inject_push_interval; /* [N] nullable: the next push_interval_s of envs pushed this step (the reference's torch.randint draw) */
+  const float* inject_push_vel; /* [N,2] nullable: their push velocity (torch_rand_float) */
 } PbhcTrackIO;
 
 /* The future window of LeggedRobotGeneralTracking (_get_future_motion_targets, general_tracking.py:500-565) reads, for 20 future

@@ -41,6 +41,10 @@ def new_state(spec, N, env_origins=None):
         average_episode_length=0.0, reward_penalty_scale=spec.penalty["initial"], motion_far_threshold=spec.motion_far_threshold0,
         soft_dof_pos=spec.limit_cur["dof_pos"]["initial"], soft_dof_vel=spec.limit_cur["dof_vel"]["initial"],
         soft_torque=spec.limit_cur["torque"]["initial"])
+    if spec.dr.get("push_robots"):  # legged_robot_base.py:135, 139
+        S["push_robot_counter"] = torch.zeros(N, dtype=torch.int)
+        S["push_interval_s"] = torch.randint(int(spec.dr["push_interval_s"][0]), int(spec.dr["push_interval_s"][1]), (N,))
+        S["push_robot_vel_buf"] = torch.zeros(N, 2)
     for k in spec.hist_keys:
         S["hist_" + k] = torch.zeros(N, spec.hist_len[k], spec.hist_dim[k])
     for k in spec.episode_sum_names:
@@ -576,6 +580,21 @@ def step(spec, tab, S, inp, inject=None):
         log["local_lower_body_diff_norm"] = dl[:, spec.lower_ids, :].norm(dim=-1).mean()
         log["local_vr_3point_diff_norm"] = dl[:, spec.vr3_ids, :].norm(dim=-1).mean()
         log["local_key_body_diff_norm"] = dl[:, spec.key_ids, :].norm(dim=-1).mean()
+    pushed = torch.zeros(S["episode_length_buf"].shape[0], dtype=torch.bool)
+    if spec.dr.get("push_robots"):
+        # _update_counters_each_step (legged_robot_base.py:143-148), the push part of _update_tasks_callback (:382-388) and
+        # _push_robots (:1090-1106); the torch.randint / torch_rand_float draws come from `inject`
+        S["push_robot_counter"] += 1
+        ids = (S["push_robot_counter"] == (S["push_interval_s"] / spec.dt).int()).nonzero(as_tuple=False).flatten()
+        S["push_robot_counter"][ids] = 0
+        S["push_interval_s"][ids] = inject["push_interval_s"][ids]
+        vel = inject["push_vel"][ids]
+        S["push_robot_vel_buf"][ids] = vel
+        if spec.dr.get("push_fixed"):
+            inp["root_state"][ids, 7:9] += vel
+        else:
+            inp["root_state"][ids, 7:9] = vel
+        pushed[ids] = True
     _termination(spec, S, W, log, inp, inject)
     _rewards(spec, S, W, inp, log)
     extras = {"ref_body_pos_extend": W["ref"]["rg_pos_t"].clone(), "ref_body_rot_extend": W["ref"]["rg_rot_t"].clone()}
@@ -583,5 +602,6 @@ def step(spec, tab, S, inp, inject=None):
     if ep is not None:
         extras["episode"] = ep
     extras["time_outs"] = S["time_out_buf"]
+    extras["refresh_env_ids"] = torch.logical_or(S["reset_buf"] != 0, pushed).nonzero(as_tuple=False).flatten()  # need_to_refresh_envs, :314-315
     obs = _observations(spec, S, W, inp)
     return obs, log, extras

@@ -9,7 +9,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("PBHC_B200_LIB") or os.path.join(_HERE, "libpbhc_b200.so")  # override: development A/B builds
 
 c_f32p = C.c_void_p
-ABI_VERSION = 9
+ABI_VERSION = 10
 MAX_JOINTS = 40
 
 
@@ -207,7 +207,8 @@ class TrackCfg(C.Structure):
         ("term_dof_pos_prob", C.c_float), ("term_dof_vel_prob", C.c_float), ("term_torque_prob", C.c_float),
         ("term_dof_vel_scale", C.c_float), ("term_torque_scale", C.c_float),
         ("term_pos_lo", C.c_float * MAX_DOF), ("term_pos_hi", C.c_float * MAX_DOF),
-        ("ref_init_yaw", C.c_float), ("vr3_ids", C.c_int32 * 4)]
+        ("ref_init_yaw", C.c_float), ("vr3_ids", C.c_int32 * 4),
+        ("push_robots", C.c_int32), ("push_fixed", C.c_int32), ("push_lo", C.c_int32), ("push_hi", C.c_int32), ("max_push_vel", C.c_float)]
 
 
 TRACK_IO_FIELDS = [
@@ -233,7 +234,8 @@ class TrackIO(C.Structure):
                                              "last_episode_sums", "partials", "acc", "inject_start_times", "inject_kp",
                                              "inject_kd", "inject_rfi", "inject_rao", "inject_delay")]
                 + [("env_offset", C.c_int64), ("last_episode_length_buf", C.c_void_p), ("force_reset", C.c_void_p), ("inject_term_gates", C.c_int32),
-                   ("fut_table", C.c_void_p), ("fut_stride", C.c_int32), ("heading_scratch", C.c_void_p)])
+                   ("fut_table", C.c_void_p), ("fut_stride", C.c_int32), ("heading_scratch", C.c_void_p),
+                   ("refresh_buf", C.c_void_p), ("push_vel", C.c_void_p), ("inject_push_interval", C.c_void_p), ("inject_push_vel", C.c_void_p)])
 
 
 def bind_track(L):

@@ -1251,8 +1251,17 @@ __device__ __forceinline__ void track_body(const TrackParams& P) {
         for (int i = lane; i < P.push_len; i += 32) gh[pmap[i]] = ps[i];
       }
       if (lane == 0) {
+        const PushOut po = push_update(c, io, n, __float_as_int(ef1.w), P.c.seed, push_count);
+        if (po.pushed) {
+          if (!reset) {
+            float* rs = io.root_state + n * 13 + 7;
+            rs[0] = c.push_fixed ? rs[0] + po.vx : po.vx; rs[1] = c.push_fixed ? rs[1] + po.vy : po.vy;
+          }
+          if (io.push_vel) { io.push_vel[2 * n] = po.vx; io.push_vel[2 * n + 1] = po.vy; }
+        }
+        if (io.refresh_buf) io.refresh_buf[n] = (reset || po.pushed) ? 1 : 0;
         reinterpret_cast<float4*>(envf)[0] = make_float4(start, mlen, air0, c.n_feet > 1 ? air1 : 0.0f);
-        reinterpret_cast<float4*>(envf)[1] = make_float4(contact0, c.n_feet > 1 ? contact1 : 0.0f, etr, ef1.w);
+        reinterpret_cast<float4*>(envf)[1] = make_float4(contact0, c.n_feet > 1 ? contact1 : 0.0f, etr, __int_as_float(po.word));
         io.episode_length_buf[n] = ep;
         io.reset_buf[n] = reset ? 1 : 0;
         io.time_out_buf[n] = time_out ? 1 : 0;
@@ -1544,6 +1553,9 @@ extern "C" int pbhc_track_step(const PbhcTrackCfg* cfg, const PbhcTableDesc* tab
                         io->action_delay_idx, io->episode_sums, io->scalars, io->rew_buf, io->reset_buf, io->time_out_buf,
                         io->last_episode_sums, io->partials, io->acc};
   for (const void* p : need) if (!p) { set_error("pbhc_track_step: a required PbhcTrackIO pointer is NULL"); return PBHC_E_BADARG; }
+  if (c.push_robots && (c.push_hi <= c.push_lo || c.push_lo < 1 || c.push_hi > 32767 || (float)c.push_hi / c.dt > 65535.0f)) {
+    set_error("pbhc_track_step: push_interval_s [%d, %d) outside what the 16 + 16 bit push word holds", c.push_lo, c.push_hi); return PBHC_E_RANGE;
+  }
   if (c.L < 0 || c.L > 48) { set_error("pbhc_track_step: L outside [0, 48]"); return PBHC_E_RANGE; }
   if ((c.L > 0 && !io->link_mass_scale) || (c.hist_row > 0 && !io->hist)) { set_error("pbhc_track_step: NULL link_mass_scale / hist"); return PBHC_E_BADARG; }
   for (int g = 0; g < c.n_groups; ++g) if (!io->obs[g] || c.group_dim[g] <= 0) { set_error("pbhc_track_step: NULL / empty obs group %d", g); return PBHC_E_BADARG; }

@@ -118,6 +118,30 @@ struct Rng {
   }
 };
 
+// _update_counters_each_step + the push part of _update_tasks_callback + _push_robots (legged_robot_base.py:143-148, 382-388,
+// 1090-1106) for one env, run by one lane.  `word` = the env's push word (env_f32 slot 7): counter | interval_s << 16.  A pushed
+// env gets a new interval and a root lin-vel x / y of U(-max, max); the caller writes it unless the env also resets this
+// step (the reset comes later in the reference's step and overwrites the root state).
+struct PushOut { int word; bool pushed; float vx, vy; };
+__device__ __forceinline__ PushOut push_update(const PbhcTrackCfg& c, const PbhcTrackIO& io, int64_t n, int word, uint64_t seed, uint32_t step) {
+  PushOut o = {word, false, 0.0f, 0.0f};
+  if (!c.push_robots) return o;
+  int cnt = (word & 0xffff) + 1, iv = word >> 16;
+  if (cnt == (int)__fdiv_rn((float)iv, c.dt)) {  // (self.push_interval_s / self.dt).int()
+    const int64_t g = n + io.env_offset;
+    const Rng rng = {make_uint2((uint32_t)seed, (uint32_t)(seed >> 32)), (uint32_t)g, (uint32_t)((uint64_t)g >> 32), step};
+    cnt = 0;
+    iv = io.inject_push_interval ? (int)io.inject_push_interval[n] : c.push_lo + (int)(rng.draw(240).x % (uint32_t)(c.push_hi - c.push_lo));
+    const uint4 r = rng.draw(241);
+    const float lo = -c.max_push_vel, hi = c.max_push_vel;  // torch_rand_float: (upper - lower) * rand + lower
+    o.vx = io.inject_push_vel ? io.inject_push_vel[2 * n] : __fadd_rn(__fmul_rn(hi - lo, u01(r.x)), lo);
+    o.vy = io.inject_push_vel ? io.inject_push_vel[2 * n + 1] : __fadd_rn(__fmul_rn(hi - lo, u01(r.y)), lo);
+    o.pushed = true;
+  }
+  o.word = (cnt & 0xffff) | (iv << 16);
+  return o;
+}
+
 // calc_heading_quat_inv (rotations.py:256-268, 296-306) = quat_from_angle_axis(-heading, z) (rotations.py:138-146)
 __device__ __forceinline__ Q4 heading_quat_inv(Q4 q) {
   const V3 d = quat_rotate(q, {1.0f, 0.0f, 0.0f});

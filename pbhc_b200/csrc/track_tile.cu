@@ -1009,8 +1009,17 @@ __device__ __forceinline__ void track_tile_body(const TileParams& P) {
       // ---- i. state write-back, cross-env sums ----------------------------------------------------------------------------------------
       if (lane == 0) {
         float4* of = reinterpret_cast<float4*>(io.env_f32) + n * 2;
+        const PushOut po = push_update(c, io, n, __float_as_int(s_envf[7]), P.c.seed, push_count);
+        if (po.pushed) {
+          if (!reset) {
+            float* rs = io.root_state + n * 13 + 7;
+            rs[0] = c.push_fixed ? rs[0] + po.vx : po.vx; rs[1] = c.push_fixed ? rs[1] + po.vy : po.vy;
+          }
+          if (io.push_vel) { io.push_vel[2 * n] = po.vx; io.push_vel[2 * n + 1] = po.vy; }
+        }
+        if (io.refresh_buf) io.refresh_buf[n] = (reset || po.pushed) ? 1 : 0;
         of[0] = make_float4(start, mlen, air0, KC(n_feet) > 1 ? air1 : 0.0f);
-        of[1] = make_float4(contact0, KC(n_feet) > 1 ? contact1 : 0.0f, etr, s_envf[7]);
+        of[1] = make_float4(contact0, KC(n_feet) > 1 ? contact1 : 0.0f, etr, __int_as_float(po.word));
         io.episode_length_buf[n] = ep;
         io.reset_buf[n] = reset ? 1 : 0;
         io.time_out_buf[n] = time_out ? 1 : 0;

@@ -133,7 +133,10 @@ class TrackSpec:
                     kd_range=list(_get(dr, "kd_range", [1, 1])), randomize_rfi_lim=bool(_get(dr, "randomize_rfi_lim", False)),
                     rfi_lim_range=list(_get(dr, "rfi_lim_range", [1, 1])), use_rao=bool(_get(dr, "use_rao", False)),
                     rao_lim=float(_get(dr, "rao_lim", 0.0)), randomize_ctrl_delay=bool(_get(dr, "randomize_ctrl_delay", False)),
-                    ctrl_delay_step_range=list(_get(dr, "ctrl_delay_step_range", [0, 0])))
+                    ctrl_delay_step_range=list(_get(dr, "ctrl_delay_step_range", [0, 0])),
+                    # legged_robot_base.py:134-147, 382-388, 1090-1106 (on in the shipped domain_rand/main.yaml)
+                    push_robots=bool(_get(dr, "push_robots", False)), push_interval_s=list(_get(dr, "push_interval_s", [5, 10])),
+                    max_push_vel_xy=float(_get(dr, "max_push_vel_xy", 0.0)), push_fixed=bool(_get(dr, "_push_fixed", False)))
         s.noise_to_initial_level = float(_get(cfg, "noise_to_initial_level", 0))
         s.init_noise_scale = {k: float(v) for k, v in dict(_get(cfg, "init_noise_scale", {}) or {}).items()}
         s.use_vec_reward = bool(_get(cfg, "use_vec_reward", False))

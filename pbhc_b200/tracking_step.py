@@ -107,6 +107,15 @@ class TrackingStep:
         self._reset_count = torch.zeros(1, device=dev, dtype=torch.int32)
         self._compact_scratch = torch.zeros(max(int(self._L.pbhc_compact_scratch_ints(N)), 1), device=dev, dtype=torch.int32)
         self._build_cfg(seed)
+        # push_robots: per-env counter and interval live in the spare slot of the env_f32 row (counter | interval_s << 16 as int32 bits)
+        self._refresh_buf = self.push_robot_vel_buf = None
+        if s.dr["push_robots"]:
+            lo, hi = s.dr["push_interval_s"]
+            self.set_push_state(torch.zeros(N, device=dev, dtype=torch.int32), torch.randint(int(lo), int(hi), (N,), device=dev))  # legged_robot_base.py:135, 139
+            self._refresh_buf = torch.zeros(N, device=dev, dtype=torch.int64)
+            self.push_robot_vel_buf = torch.zeros(N, 2, **f32)
+            self._refresh_ids = torch.zeros(N, device=dev, dtype=torch.int32)
+            self._refresh_count = torch.zeros(1, device=dev, dtype=torch.int32)
         used = int(self._cfg.src_used_mask)
         self._heading_scratch = torch.zeros(N, 2, **f32) if used >> OBS_SRC_IDS["vr_3point_pos"] & 1 else None
         if used >> OBS_SRC_IDS["relyaw"] & 3:
@@ -119,6 +128,14 @@ class TrackingStep:
         self._io = _lib.TrackIO()
         self._io.env_offset = int(env_offset)  # global id of this rank's env 0 (pbhc_b200.dist.shard_range): keys the in-kernel random streams
         self._keep = None
+
+    def set_push_state(self, counter, interval_s):
+        """push_robot_counter [N] and push_interval_s [N] (legged_robot_base.py:135, 139) into the packed per-env state."""
+        word = (counter.to(self.device).to(torch.int32) & 0xffff) | (interval_s.to(self.device).to(torch.int32) << 16)
+        self.env_f32[:, 7] = word.view(torch.float32)
+
+    push_robot_counter = property(lambda self: self.env_f32[:, 7].contiguous().view(torch.int32) & 0xffff)
+    push_interval_s = property(lambda self: (self.env_f32[:, 7].contiguous().view(torch.int32) >> 16).long())
 
     def set_ref_init_yaw(self, yaw):
         """ref_init_rpy[0, 2] of the reference env (`relyaw = rpy[:, 2:3] - ref_init_rpy[0, 2]`, motion_tracking.py:686)."""
@@ -277,6 +294,9 @@ class TrackingStep:
         for i, v in enumerate(s.vr3_ids[:4]):
             c.vr3_ids[i] = v
         c.ref_init_yaw = 0.0  # set_ref_init_yaw / __init__
+        # domain_rand.push_robots (legged_robot_base.py:134-147, 382-388, 1090-1106)
+        c.push_robots, c.push_fixed = int(dr["push_robots"]), int(dr["push_fixed"])
+        c.push_lo, c.push_hi, c.max_push_vel = int(dr["push_interval_s"][0]), int(dr["push_interval_s"][1]), dr["max_push_vel_xy"]
         # base-class terminations (legged_robot_base.py:433-476)
         c.term_contact, c.term_contact_mask = int(s.term_contact), _mask(s.term_contact_ids)
         c.term_low_height, c.term_min_height = int(s.term_low_height), s.term_min_height
@@ -357,6 +377,8 @@ class TrackingStep:
         ft = self._future_table()
         io.fut_table, io.fut_stride = (p(ft), ft.shape[1]) if ft is not None else (None, 0)
         io.heading_scratch = p(self._heading_scratch)
+        io.refresh_buf, io.push_vel = p(self._refresh_buf), p(self.push_robot_vel_buf)
+        io.inject_push_interval, io.inject_push_vel = p(inj.get("push_interval_s"), torch.int64), p(inj.get("push_vel"), torch.float32)
         self._keep = (sim, actions, torques, env_origins, motion_ids, inj)
 
     def _future_table(self):
@@ -418,8 +440,22 @@ class TrackingStep:
     # ---- the rest of _post_physics_step's contract: env ids of the resets, extras["episode"], resample_motion -----------
     @property
     def need_to_refresh_envs(self):
-        """legged_robot_base.py:315: after step() exactly the envs of reset_buf wait for the simulator setters."""
-        return self.reset_buf != 0
+        """legged_robot_base.py:315: after step() the envs of reset_buf wait for the simulator setters - and, with
+        domain_rand.push_robots, the envs whose root velocity the step just pushed (:1095)."""
+        return (self.reset_buf if self._refresh_buf is None else self._refresh_buf) != 0
+
+    def refresh_env_ids(self):
+        """`self.need_to_refresh_envs.nonzero(as_tuple=False).flatten()` (legged_robot_base.py:315) on the device: (ids, count) like
+        reset_env_ids().  Without push_robots these ARE the reset ids."""
+        if self._refresh_buf is None:
+            return self.reset_env_ids()
+        _lib.check(self._L.pbhc_compact_ids(_lib.ptr(self._refresh_buf), self.N, _lib.ptr(self._refresh_ids), _lib.ptr(self._refresh_count),
+                                            _lib.ptr(self._compact_scratch), _lib.stream_ptr(self.device)))
+        return self._refresh_ids, self._refresh_count
+
+    def refresh_env_ids_host(self):
+        ids, count = self.refresh_env_ids()
+        return ids[:int(count.item())]
 
     def reset_env_ids(self):
         """`self.reset_buf.nonzero(as_tuple=False).flatten()` (legged_robot_base.py:311) without leaving the device:

@@ -87,8 +87,9 @@ def make_env(case, tmp_path, resample=False, interval=1 << 30):
     return env, g, spec, N
 
 
-def test_integration_snippet_runs_verbatim_against_reference_golden(tmp_path):
-    case = "mt23_main"
+@pytest.mark.parametrize("case", ["mt23_main", "mt23_push"])
+def test_integration_snippet_runs_verbatim_against_reference_golden(case, tmp_path):
+    """mt23_push: domain_rand.push_robots on - the setters receive need_to_refresh_envs = reset | pushed (legged_robot_base.py:314-319)"""
     env, g, spec, N = make_env(case, tmp_path)
     sim, ts = env.simulator, env._b200
     # the attributes the binding re-exports are the very buffers of the step, not copies
@@ -102,6 +103,12 @@ def test_integration_snippet_runs_verbatim_against_reference_golden(tmp_path):
         env.actions = torch.from_numpy(g[p + "in_actions"]).to(DEV).contiguous()
         env.torques = torch.from_numpy(g[p + "in_torques"]).to(DEV).contiguous()
         ts.inject_next = {k: torch.from_numpy(g[p + "out_" + k]).to(DEV).contiguous() for k in INJECT}  # the reference's own reset draws
+        oinj = {k: torch.from_numpy(g[p + "out_" + k]) for k in INJECT}
+        if p + "in_push_robot_counter" in g:
+            ts.set_push_state(torch.from_numpy(g[p + "in_push_robot_counter"]), ts.push_interval_s)
+            S["push_robot_counter"] = torch.from_numpy(g[p + "in_push_robot_counter"].copy())
+            oinj.update(push_interval_s=torch.from_numpy(g[p + "out_push_interval_s"]), push_vel=torch.from_numpy(g[p + "out_push_robot_vel_buf"]))
+            ts.inject_next.update({k: v.to(DEV).contiguous() for k, v in oinj.items() if k.startswith("push")})
         prev_ep = ts.episode_length_buf.cpu().numpy().copy()
         env._post_physics_step()
         torch.cuda.synchronize()
@@ -115,15 +122,21 @@ def test_integration_snippet_runs_verbatim_against_reference_golden(tmp_path):
         assert_close(sim.all_root_states.cpu(), g[p + "out_root_state"], what=f"{tag} root_state")
         # env_ids = reset_buf.nonzero().flatten() of the REFERENCE went to both setters, root first (legged_robot_base.py:316-319)
         want_ids = np.flatnonzero(g[p + "out_reset_buf"]).astype(np.int32)
+        refresh = g[p + "out_reset_buf"] != 0
+        if p + "out_push_robot_counter" in g:
+            refresh = refresh | (g[p + "out_push_robot_counter"] == 0)
+            assert refresh.sum() > len(want_ids)
+        want_refresh = np.flatnonzero(refresh).astype(np.int32)
         assert len(want_ids) > 0
         assert [c[0] for c in sim.calls[n_calls:]] == ["root", "dof"], tag
         for kind, ids, n in sim.calls[n_calls:]:
-            assert n == len(want_ids) and np.array_equal(ids, want_ids), (tag, kind)
+            assert n == len(want_refresh) and np.array_equal(ids, want_refresh), (tag, kind)
         n_calls = len(sim.calls)
-        assert torch.equal(ts.need_to_refresh_envs.cpu(), torch.from_numpy(g[p + "out_reset_buf"] != 0))
+        assert torch.equal(ts.need_to_refresh_envs.cpu(), torch.from_numpy(refresh))
         # extras: the oracle (bit-exact against this fixture, tests/test_oracle_env_golden.py) gives extras["episode"]
         inp = {k: torch.from_numpy(g[p + "in_" + k].copy()) for k in ("body_state", "root_state", "dof_state", "contact_forces", "actions", "torques")}
-        _, olog, oex = OE.step(ospec, otab, S, inp, {k: torch.from_numpy(g[p + "out_" + k]) for k in INJECT})
+        _, olog, oex = OE.step(ospec, otab, S, inp, oinj)
+        assert np.array_equal(oex["refresh_env_ids"].numpy(), want_refresh)
         ep = env.extras["episode"]
         assert sorted(ep) == sorted(oex["episode"])
         assert np.array_equal(ep["end_epis_length"].cpu().numpy(), prev_ep[want_ids] + 1)

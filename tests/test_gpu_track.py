@@ -60,6 +60,8 @@ def load_state(ts, S, spec):
         ts.hist[:, base:base + n] = t("hist_" + k).reshape(ts.N, -1)
     for i, name in enumerate(ts._sum_names):
         ts._episode_sums[:, i] = t("epsum_" + name)
+    if "push_interval_s" in S:
+        ts.set_push_state(t("push_robot_counter"), t("push_interval_s"))
 
 
 def compare_state(ts, G, spec, tag, loose=None):
@@ -127,6 +129,10 @@ def _run_golden_case(case, tmp_path, exact, loose=None):
         inject = {k: torch.from_numpy(g[p + "out_" + k]).to(DEV).contiguous() for k in INJECT}
         if p + "in_term_gates" in g:
             inject["term_gates"] = int(g[p + "in_term_gates"])
+        if p + "in_push_robot_counter" in g:  # domain_rand.push_robots: the fixture moves a few envs next to their push before every step
+            ts.set_push_state(torch.from_numpy(g[p + "in_push_robot_counter"]), ts.push_interval_s)
+            inject["push_interval_s"] = torch.from_numpy(g[p + "out_push_interval_s"]).to(DEV).contiguous()
+            inject["push_vel"] = torch.from_numpy(g[p + "out_push_robot_vel_buf"]).to(DEV).contiguous()
         obs, rew, reset, extras = ts.step(sim, actions, torques, origins, mids, inject=inject)
         torch.cuda.synchronize()
         tag = f"{case} step {step}"
@@ -150,6 +156,15 @@ def _run_golden_case(case, tmp_path, exact, loose=None):
             assert_close(v.cpu(), g[p + "obs_" + name], what=f"{tag} obs {name}", **otol)
         G = {k[len(p) + 4:]: g[k] for k in g if k.startswith(p + "out_")}
         compare_state(ts, G, spec, tag, loose)
+        if "push_interval_s" in G:  # counters, new intervals, velocities of the pushed envs, need_to_refresh_envs = reset | pushed
+            assert np.array_equal(ts.push_robot_counter.cpu().numpy(), G["push_robot_counter"]), tag
+            assert np.array_equal(ts.push_interval_s.cpu().numpy(), G["push_interval_s"]), tag
+            pushed = G["push_robot_counter"] == 0
+            assert pushed.sum() >= 3
+            assert np.array_equal(ts.push_robot_vel_buf.cpu().numpy()[pushed], G["push_robot_vel_buf"][pushed]), tag
+            want = np.flatnonzero(pushed | (G["reset_buf"] != 0))
+            assert np.array_equal(ts.refresh_env_ids_host().cpu().numpy(), want), tag
+            assert np.array_equal(np.flatnonzero(ts.need_to_refresh_envs.cpu().numpy()), want), tag
         assert_close(actions.cpu(), g[p + "out_actions"], what=f"{tag} actions")
         assert_close(sim.dof_state.cpu(), g[p + "out_dof_state"], what=f"{tag} dof_state")
         assert_close(sim.all_root_states.cpu(), g[p + "out_root_state"], what=f"{tag} root_state", **(loose or {}).get("state", {}))
@@ -161,9 +176,11 @@ def _run_golden_case(case, tmp_path, exact, loose=None):
                 assert_close(log[k[len(p) + 4:]].cpu(), np.float32(g[k]), what=f"{tag} log {k}", **(loose or {}).get("log", dict(rtol=1e-5, atol=1e-6)))
 
 
-@pytest.mark.parametrize("case", ["mt23_main", "mt23_bench", "gt29_teacher", "gt29_student", "mt23_edge", "gt29_edge", "mt23_term", "gt29_term", "mt23_p4", "gt29_p4"])
+@pytest.mark.parametrize("case", ["mt23_main", "mt23_bench", "gt29_teacher", "gt29_student", "mt23_edge", "gt29_edge", "mt23_term", "gt29_term", "mt23_p4", "gt29_p4", "mt23_push", "gt29_push"])
 def test_track_step_matches_reference_golden(case, tmp_path):
-    """*_p4: the observation sources and reward terms no shipped config uses (tools/make_golden_env_step.py run_p4): relyaw,
+    """*_push: domain_rand.push_robots as the shipped domain_rand/main.yaml has it (legged_robot_base.py:382-388, 1090-1106): pushes
+    added to / replacing the root velocity, an env that is pushed and reset in the same step, need_to_refresh_envs.
+    *_p4: the observation sources and reward terms no shipped config uses (tools/make_golden_env_step.py run_p4): relyaw,
     local_ref_rigid_body_pos_relyaw, vr_3point_pos (with the reference's cross-env heading pairing), future_ref_dof_pos / _vel,
     the radial velocity rewards, feet_heading_alignment(_contact), penalty_feet_ori(_contact).
     mt23_term: the base-class terminations on (contact with |f| just above / below 1, low base, dof position / velocity /
@@ -316,3 +333,52 @@ def test_observation_noise_statistics(tmp_path):
             for g in groups:
                 if (g, k) in units:
                     assert abs((u * units[(g, k)]).mean().item()) < 0.02
+
+
+@pytest.mark.parametrize("case", ["mt23_push", "gt29_push"])
+def test_push_robots_in_kernel_draws(case, tmp_path):
+    """without injected draws the pushes come from the kernel's Philox stream: every env one step short of its interval is
+    pushed, gets a new interval in [lo, hi) and a velocity in U(-max, max) that is added to (mt23: _push_fixed) or replaces
+    (gt29) the root lin vel x / y of envs that do not reset; envs not at their interval only count up"""
+    g = gold(f"ref_env_{case}.npz")
+    cfg = json.loads(str(g["meta_config_json"]))
+    spec = TrackSpec.from_config(cfg)
+    N = 2048
+    from pbhc_b200.fixtures import clips_of_case
+    ts, ml = make_step(spec, N, tmp_path, clip_names=clips_of_case(cfg)[1], exact=False)
+    sim = make_sim(N, spec.Jb, spec.D, spec.L)
+    mids = torch.zeros(N, device=DEV, dtype=torch.int64)
+    # the robot sits exactly on its reference (nothing terminates), except for the root velocity the pushes act on
+    ref = ml.get_motion_state(mids, torch.full((N,), 2 * spec.dt, device=DEV))
+    body = sim._rigid_body_state.view(N, -1, 13)
+    body[:, :, 0:3], body[:, :, 3:7] = ref["rg_pos_t"][:, :spec.Jb], ref["rg_rot_t"][:, :spec.Jb]
+    body[:, :, 7:10], body[:, :, 10:13] = ref["body_vel_t"][:, :spec.Jb], ref["body_ang_vel_t"][:, :spec.Jb]
+    sim.all_root_states[:, 0:3], sim.all_root_states[:, 3:7] = ref["root_pos"], ref["root_rot"]
+    sim.all_root_states[:, 10:13] = ref["root_ang_vel"]
+    sim.all_root_states[:, 7:9] = 0.25
+    sim.dof_state.view(N, -1, 2)[:, :, 0], sim.dof_state.view(N, -1, 2)[:, :, 1] = ref["dof_pos"], ref["dof_vel"]
+    lo, hi = spec.dr["push_interval_s"]
+    iv = ts.push_interval_s.clone()
+    assert int(iv.min()) >= lo and int(iv.max()) < hi and ts.push_robot_vel_buf.shape == (N, 2)
+    thr = (iv / spec.dt).int()
+    due = torch.arange(N, device=DEV) % 2 == 0
+    ts.set_push_state(torch.where(due, thr - 1, torch.full_like(thr, 7)), iv)
+    ts.env_f32[:, 1] = 1e6  # (no motion-end resets)
+    z = torch.zeros(N, spec.D, device=DEV)
+    ts.step(sim, z.clone(), z.clone(), torch.zeros(N, 3, device=DEV), mids)
+    torch.cuda.synchronize()
+    cnt, iv2, vel, reset = ts.push_robot_counter, ts.push_interval_s, ts.push_robot_vel_buf, ts.reset_buf != 0
+    assert torch.equal(cnt[due], torch.zeros_like(cnt[due])) and bool((cnt[~due] == 8).all())
+    assert torch.equal(iv2[~due], iv[~due]) and int(iv2[due].min()) >= lo and int(iv2[due].max()) < hi
+    assert len(torch.unique(iv2[due])) == hi - lo
+    m = spec.dr["max_push_vel_xy"]
+    v = vel[due]
+    assert float(v.abs().max()) <= m and abs(float(v.mean())) < 0.06 * m and abs(float(v.var()) - m * m / 3) < 0.1 * m * m
+    assert bool((vel[~due] == 0).all())
+    keep = due & ~reset
+    assert int(keep.sum()) > N // 4
+    got = sim.all_root_states[keep, 7:9]
+    want = vel[keep] + 0.25 if spec.dr["push_fixed"] else vel[keep]
+    assert torch.equal(got, want)
+    assert bool((sim.all_root_states[~due & ~reset, 7:9] == 0.25).all())
+    assert torch.equal(ts.need_to_refresh_envs, due | reset)

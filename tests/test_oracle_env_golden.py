@@ -36,7 +36,7 @@ def state_from(g, prefix, spec):
     return S
 
 
-@pytest.mark.parametrize("case", ["mt23_main", "mt23_bench", "gt29_teacher", "gt29_student", "mt23_edge", "gt29_edge", "mt23_term", "gt29_term", "mt23_p4", "gt29_p4"])
+@pytest.mark.parametrize("case", ["mt23_main", "mt23_bench", "gt29_teacher", "gt29_student", "mt23_edge", "gt29_edge", "mt23_term", "gt29_term", "mt23_p4", "gt29_p4", "mt23_push", "gt29_push"])
 def test_env_step_oracle_matches_reference(case):
     g, spec, N, tab = load_case(case)
     S = state_from(g, "init_", spec)
@@ -47,6 +47,11 @@ def test_env_step_oracle_matches_reference(case):
         inject = {k: torch.from_numpy(g[p + "out_" + k]) for k in INJECT}
         if p + "in_term_gates" in g:  # the reference's `torch.rand(1) < p` draws of this step (legged_robot_base.py:455-473)
             inject["term_gates"] = int(g[p + "in_term_gates"])
+        if p + "in_push_robot_counter" in g:  # the fixture moves a few envs next to their push before every step
+            S["push_robot_counter"] = torch.from_numpy(g[p + "in_push_robot_counter"].copy())
+        if p + "out_push_interval_s" in g:  # the reference's torch.randint / torch_rand_float draws of the envs it pushed (legged_robot_base.py:387, 1097)
+            inject["push_interval_s"] = torch.from_numpy(g[p + "out_push_interval_s"])
+            inject["push_vel"] = torch.from_numpy(g[p + "out_push_robot_vel_buf"])
         obs, log, extras = OE.step(spec, tab, S, inp, inject)
         for gname, v in obs.items():
             assert np.array_equal(v.numpy(), g[p + "obs_" + gname]), (step, gname)

@@ -38,6 +38,8 @@ def env_state(env):
         end_time_ratio_buf=env.end_time_ratio_buf)
     if hasattr(env.simulator, "_base_mass_scale"):
         s["base_mass_scale"] = env.simulator._base_mass_scale
+    if env.config.domain_rand.push_robots:  # legged_robot_base.py:135-147, 1090-1106
+        s.update(push_robot_counter=env.push_robot_counter, push_interval_s=env.push_interval_s, push_robot_vel_buf=env.push_robot_vel_buf)
     for k, v in env.history_handler.history.items():
         s["hist_" + k] = v
     for k, v in env.episode_sums.items():
@@ -123,6 +125,8 @@ def run_case(name, n_envs, n_steps, obs, seed, overrides=None, general=False, mo
         if tweak_env is not None:
             tweak_env(step, env)
         p = f"s{step}_"
+        if cfg["domain_rand"]["push_robots"]:  # (tweak_env may have moved envs next to their push)
+            out[p + "in_push_robot_counter"] = _np(env.push_robot_counter)
         out.update({p + "in_body_state": _np(body), p + "in_root_state": _np(root), p + "in_dof_state": _np(dof),
                     p + "in_contact_forces": _np(cf), p + "in_actions": _np(env.actions), p + "in_torques": _np(env.torques)})
         draws, orig_rand = [], torch.rand
@@ -206,6 +210,24 @@ def run_term():
     run_case("gt29_term", 32, 4, "motion_tracking/obs_ppo_teacher", 23, ovc, general=True, tweak=tweak_first, tweak_env=tweak_env)
 
 
+def run_push():
+    """mt23_push / gt29_push: domain_rand.push_robots as shipped in domain_rand/main.yaml (legged_robot_base.py:382-388, 1090-1106):
+    a few envs are put one step short of their push interval in every step - among them env 0, which also resets at the end of
+    its clip (the reset wins over the push) - so that pushes, new intervals and need_to_refresh_envs are exercised."""
+    def tweak_env(step, env):
+        thr = (env.push_interval_s / env.dt).int()
+        ids = torch.tensor([0, 3 + step, 9, 14 - step])
+        env.push_robot_counter[ids] = thr[ids] - 1
+    ov = dict(ZERO_NOISE)
+    ov["domain_rand.push_robots"] = True
+    if "general" not in sys.argv:
+        run_case("mt23_push", 16, 4, "motion_tracking/main", 41, ov, tweak_env=tweak_env)
+    ovc = dict(ZERO_NOISE_C)
+    ovc["domain_rand.push_robots"] = True
+    ovc["domain_rand._push_fixed"] = False  # (main.yaml ships True: the push is added; False: it replaces the root velocity)
+    run_case("gt29_push", 16, 3, "motion_tracking/obs_ppo_teacher", 42, ovc, general=True, tweak_env=tweak_env)
+
+
 def run_p4():
     """mt23_p4 / gt29_p4: the observation sources and reward terms no shipped config uses: relyaw,
     local_ref_rigid_body_pos_relyaw, vr_3point_pos, future_ref_dof_pos / _vel (obs.future_ref_steps = 3; motion_tracking only);
@@ -264,4 +286,4 @@ def run_general():
 
 if __name__ == "__main__":
     import sys
-    run_p4() if "p4" in sys.argv else (run_general() if "general" in sys.argv else (run_term() if "term" in sys.argv else run()))
+    run_push() if "push" in sys.argv else run_p4() if "p4" in sys.argv else (run_general() if "general" in sys.argv else (run_term() if "term" in sys.argv else run()))
