@@ -16,7 +16,7 @@
 extern "C" {
 #endif
 
-#define PBHC_ABI_VERSION 10
+#define PBHC_ABI_VERSION 11
 #define PBHC_OK 0
 #define PBHC_E_BADARG (-1)
 #define PBHC_E_ALIGN (-2)
@@ -217,6 +217,7 @@ int pbhc_clips_prepare(const float* pos, const float* quat, const float* pose_aa
 #define PBHC_S_SOFT_DOF_VEL 38
 #define PBHC_S_SOFT_TORQUE 39
 #define PBHC_S_PUSH_COUNT 40  /* history pushes so far (ring-buffer head = -count mod H) */
+#define PBHC_S_NOISE_CUR 41   /* current_noise_curriculum_value (obs.add_noise_currculum, legged_robot_base.py:119-120, 637-645), ABI 11 */
 #define PBHC_S_LOG 48         /* [64] log_dict values of the last step, see PBHC_L_* */
 #define PBHC_SCALARS 112
 /* layout of `acc` (device double[PBHC_ACC]): per-step sums over envs; all-reduce across ranks before finalize */
@@ -281,6 +282,7 @@ int pbhc_clips_prepare(const float* pos, const float* quat, const float* pose_aa
 #define PBHC_L_TERM_DOF_POS 60
 #define PBHC_L_TERM_DOF_VEL 61
 #define PBHC_L_TERM_TORQUE 62
+#define PBHC_L_NOISE_CUR 63     /* log_dict["current_noise_curriculum_value"] (legged_robot_base.py:760-761), logged before the update */
 
 typedef struct { int32_t enable; double lo, hi, degree, down, up; } PbhcCurriculum;
 /* history key `key` (index into hist_src) appears in obs group `group` at `offset`, newest `len` slots, scaled by mul */
@@ -363,6 +365,15 @@ typedef struct {
   int32_t push_robots, push_fixed;   /* _push_fixed: the drawn velocity is added to the root velocity instead of replacing it */
   int32_t push_lo, push_hi;          /* push_interval_s: the next interval is randint(lo, hi) seconds */
   float max_push_vel;                /* max_push_vel_xy: the push is U(-max, max) on root lin vel x / y */
+  /* ABI 11 */
+  int32_t start_time_zero;           /* is_evaluating and not enforce_randomize_motion_start_eval: a reset starts the clip at time 0
+                                      * instead of sample_time (motion_tracking.py:374-377, general_tracking.py:279-282) */
+  PbhcCurriculum cur_noise;          /* obs.add_noise_currculum: every noise scale is multiplied by scalars[PBHC_S_NOISE_CUR], which a step with
+                                      * resets moves by (1 -+ obs.soft_dof_pos_curriculum_degree) when the average episode length is below
+                                      * obs.soft_dof_pos_curriculum_level_down_threshold / above rewards.reward_penalty_level_up_threshold (sic),
+                                      * clipped to [noise_value_min, noise_value_max] (legged_robot_base.py:637-645).  The observations of step t
+                                      * use the value as of the end of step t-1: the reference updates it between its reset and its observation
+                                      * code, i.e. one multiplication by (1 +- degree ~ 1e-5) earlier - a difference no draw can show. */
 } PbhcTrackCfg;
 
 typedef struct {

@@ -40,7 +40,7 @@ def new_state(spec, N, env_origins=None):
         end_time_ratio_buf=torch.zeros(N),
         average_episode_length=0.0, reward_penalty_scale=spec.penalty["initial"], motion_far_threshold=spec.motion_far_threshold0,
         soft_dof_pos=spec.limit_cur["dof_pos"]["initial"], soft_dof_vel=spec.limit_cur["dof_vel"]["initial"],
-        soft_torque=spec.limit_cur["torque"]["initial"])
+        soft_torque=spec.limit_cur["torque"]["initial"], current_noise_curriculum_value=spec.noise_cur["initial"])
     if spec.dr.get("push_robots"):  # legged_robot_base.py:135, 139
         S["push_robot_counter"] = torch.zeros(N, dtype=torch.int)
         S["push_interval_s"] = torch.randint(int(spec.dr["push_interval_s"][0]), int(spec.dr["push_interval_s"][1]), (N,))
@@ -420,6 +420,8 @@ def _rewards(spec, S, W, inp, log):
     for k in ("dof_pos", "dof_vel", "torque"):
         if spec.limit_cur[k]["enable"]:
             log[f"soft_{k}_curriculum_value"] = torch.tensor(S["soft_" + k], dtype=torch.float)
+    if spec.add_noise_curriculum:  # legged_robot_base.py:760-761
+        log["current_noise_curriculum_value"] = torch.tensor(S["current_noise_curriculum_value"], dtype=torch.float)
 
 
 def soft_dof_limits(spec):
@@ -470,13 +472,19 @@ def _reset(spec, tab, S, W, inp, inject, log, last_ep_len):
     for k in ("dof_pos", "dof_vel", "torque"):
         if spec.limit_cur[k]["enable"]:
             S["soft_" + k] = _curriculum(S["soft_" + k], avg, spec.limit_cur[k], +1)
+    if spec.add_noise_curriculum:  # _update_obs_noise_curriculum, legged_robot_base.py:637-645
+        S["current_noise_curriculum_value"] = _curriculum(S["current_noise_curriculum_value"], avg, spec.noise_cur, -1)
     end_time = last_ep_len[ids] * spec.dt + S["motion_start_times"][ids]
     S["end_time_ratio_buf"][ids] = end_time / S["motion_len"][ids]
     log["end_time_ratio"] = S["end_time_ratio_buf"].mean()
     log["end_time_ratio_std"] = S["end_time_ratio_buf"].std()
     # _resample_motion_times (motion_tracking.py:369-384); sample_time draws injected
     S["motion_len"][ids] = tab.length[S["motion_ids"][ids]]
-    S["motion_start_times"][ids] = inject["motion_start_times"][ids]
+    if "motion_start_times" in inject:
+        S["motion_start_times"][ids] = inject["motion_start_times"][ids]
+    else:  # is_evaluating and not enforce_randomize_motion_start_eval (motion_tracking.py:374-375)
+        assert S.get("is_evaluating"), "oracle: start times are injected unless the env is evaluating"
+        S["motion_start_times"][ids] = torch.zeros(len(ids))
     if spec.far_cur["enable"]:
         S["motion_far_threshold"] = _curriculum(S["motion_far_threshold"], avg, spec.far_cur, +1)
     # _reset_dofs / _reset_root_states: kick_motion_res() is recomputed at the new times for all envs

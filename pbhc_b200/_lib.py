@@ -9,7 +9,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("PBHC_B200_LIB") or os.path.join(_HERE, "libpbhc_b200.so")  # override: development A/B builds
 
 c_f32p = C.c_void_p
-ABI_VERSION = 10
+ABI_VERSION = 11
 MAX_JOINTS = 40
 
 
@@ -145,6 +145,7 @@ PEER_MAX_DOUBLES = 256
 COMPACT_STATIC_MAX_N = 1 << 24  # PBHC_COMPACT_STATIC_MAX_N: flags per call of pbhc_compact_ids_static (its scratch is a 16 KB device array of the library)
 L_ADP_SIGMA, L_ERROR_EMA = 16, 33
 S_SIGMA, S_EMA, S_AVG_EPL, S_PENALTY, S_FAR_THR, S_SOFT_DOF_POS, S_SOFT_DOF_VEL, S_SOFT_TORQUE, S_PUSH_COUNT, S_LOG = 0, 17, 34, 35, 36, 37, 38, 39, 40, 48
+S_NOISE_CUR, L_NOISE_CUR = 41, 63  # obs.add_noise_currculum: current_noise_curriculum_value and its log slot
 LOG_NAMES = ["upper_body_diff_norm", "lower_body_diff_norm", "vr_3point_diff_norm", "joint_pos_diff_norm",
              "terminate_by_gravity", "terminate_by_motion_far", "terminate_by_time_out", "terminate_by_motion_end",
              "end_time_ratio", "end_time_ratio_std", "terminate_when_motion_far_threshold", "penalty_scale",
@@ -208,7 +209,8 @@ class TrackCfg(C.Structure):
         ("term_dof_vel_scale", C.c_float), ("term_torque_scale", C.c_float),
         ("term_pos_lo", C.c_float * MAX_DOF), ("term_pos_hi", C.c_float * MAX_DOF),
         ("ref_init_yaw", C.c_float), ("vr3_ids", C.c_int32 * 4),
-        ("push_robots", C.c_int32), ("push_fixed", C.c_int32), ("push_lo", C.c_int32), ("push_hi", C.c_int32), ("max_push_vel", C.c_float)]
+        ("push_robots", C.c_int32), ("push_fixed", C.c_int32), ("push_lo", C.c_int32), ("push_hi", C.c_int32), ("max_push_vel", C.c_float),
+        ("start_time_zero", C.c_int32), ("cur_noise", Curriculum)]
 
 
 TRACK_IO_FIELDS = [

@@ -244,7 +244,10 @@ __device__ void build_tables(const TrackParams& P, BlockTables& T, int* hmap, in
     T.sdst[k][g] = off;
   }
 #endif
-  if (tid < PBHC_NUM_OBS_SRC) { T.obs_scale[tid] = c.obs_scale[tid]; T.obs_noise[tid] = c.obs_noise[tid]; }
+  if (tid < PBHC_NUM_OBS_SRC) {  // (noise_scales[key] * current_noise_curriculum_value is a double product in the reference, helpers.py:142)
+    T.obs_scale[tid] = c.obs_scale[tid];
+    T.obs_noise[tid] = c.cur_noise.enable ? (float)((double)c.obs_noise[tid] * T.scal[PBHC_S_NOISE_CUR]) : c.obs_noise[tid];
+  }
   if (tid == 0) {
     uint64_t m = 0;
     for (int k = 0; k < PBHC_NUM_OBS_SRC; ++k) if (c.obs_noise[k] != 0.0f) m |= 1ull << k;
@@ -1154,7 +1157,7 @@ __device__ __forceinline__ void track_body(const TrackParams& P) {
         }
         etr = ((float)last_ep * c.dt + start) / mlen;                       // motion_tracking.py:281-282
         mlen = tab.clip_length[clip];                                       // _resample_motion_times
-        start = io.inject_start_times ? io.inject_start_times[n] : rng.uniform(0) * mlen;
+        start = io.inject_start_times ? io.inject_start_times[n] : (c.start_time_zero ? 0.0f : rng.uniform(0) * mlen);
         // _reset_dofs / _reset_root_states from the motion state at the new time
         const FrameBlend f2 = frame_blend(tab, clip, (float)(ep + 1) * c.dt + start);
         const float b2 = f2.blend, omb2 = 1.0f - b2;
@@ -1357,6 +1360,7 @@ __global__ void track_finalize_kernel(const __grid_constant__ PbhcTrackCfg c, co
   L[PBHC_L_SOFT_DOF_POS] = (double)(float)S[PBHC_S_SOFT_DOF_POS];
   L[PBHC_L_SOFT_DOF_VEL] = (double)(float)S[PBHC_S_SOFT_DOF_VEL];
   L[PBHC_L_SOFT_TORQUE] = (double)(float)S[PBHC_S_SOFT_TORQUE];
+  L[PBHC_L_NOISE_CUR] = (double)(float)S[PBHC_S_NOISE_CUR];
   for (int k = 0; k < PBHC_NUM_SIGMA; ++k) { L[PBHC_L_ADP_SIGMA + k] = S[PBHC_S_SIGMA + k]; L[PBHC_L_ERROR_EMA + k] = S[PBHC_S_EMA + k]; }
   if (c.adaptive_enable) {
     uint32_t active = 0;
@@ -1426,6 +1430,7 @@ __global__ void track_finalize_kernel(const __grid_constant__ PbhcTrackCfg c, co
     if (c.cur_dof_vel.enable) S[PBHC_S_SOFT_DOF_VEL] = curriculum(S[PBHC_S_SOFT_DOF_VEL], avg, c.cur_dof_vel, 1.0);
     if (c.cur_torque.enable) S[PBHC_S_SOFT_TORQUE] = curriculum(S[PBHC_S_SOFT_TORQUE], avg, c.cur_torque, 1.0);
     if (c.cur_far.enable) S[PBHC_S_FAR_THR] = curriculum(S[PBHC_S_FAR_THR], avg, c.cur_far, 1.0);
+    if (c.cur_noise.enable) S[PBHC_S_NOISE_CUR] = curriculum(S[PBHC_S_NOISE_CUR], avg, c.cur_noise, -1.0);  // legged_robot_base.py:637-645
     const double mean = acc[PBHC_A_ETR_SUM] / n;
     L[PBHC_L_ETR_MEAN] = mean;
     const double var = n > 1.0 ? (acc[PBHC_A_ETR_SQ] - acc[PBHC_A_ETR_SUM] * mean) / (n - 1.0) : 0.0;

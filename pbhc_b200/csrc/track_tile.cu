@@ -393,7 +393,8 @@ __device__ void build_tile_tables(const TileParams& P, TileTables& T, short* hma
         break;
       }
     T.sd[tid] = d;
-    T.obs_scale[tid] = c.obs_scale[tid]; T.obs_noise[tid] = c.obs_noise[tid];
+    T.obs_scale[tid] = c.obs_scale[tid];
+    T.obs_noise[tid] = c.cur_noise.enable ? (float)((double)c.obs_noise[tid] * scal[PBHC_S_NOISE_CUR]) : c.obs_noise[tid];
   }
   if (tid == 0) {
     uint32_t m = 0;
@@ -941,7 +942,7 @@ __device__ __forceinline__ void track_tile_body(const TileParams& P) {
         }
         etr = __fdiv_rn(xa(xm((float)last_ep, dt), start), mlen);           // motion_tracking.py:281-282
         mlen = tab.clip_length[clip];                                       // _resample_motion_times
-        start = io.inject_start_times ? io.inject_start_times[n] : xm(u01(r_env.x), mlen);
+        start = io.inject_start_times ? io.inject_start_times[n] : (c.start_time_zero ? 0.0f : xm(u01(r_env.x), mlen));
         // _reset_dofs / _reset_root_states from the motion state at the new time (unfused: these are simulator state)
         const FrameBlend f2 = frame_blend_x(tab, clip, xa(xm((float)(ep + 1), dt), start));
         const float b2 = f2.blend, omb2 = 1.0f - b2;

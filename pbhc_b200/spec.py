@@ -140,6 +140,17 @@ class TrackSpec:
         s.noise_to_initial_level = float(_get(cfg, "noise_to_initial_level", 0))
         s.init_noise_scale = {k: float(v) for k, v in dict(_get(cfg, "init_noise_scale", {}) or {}).items()}
         s.use_vec_reward = bool(_get(cfg, "use_vec_reward", False))
+        # options that change the step in the reference and are not built here: refuse them instead of ignoring them
+        for path, what in (("use_teleop_control", "teleoperation markers instead of the motion's (motion_tracking.py:112, 725-728)"),
+                           ("soft_dynamic_correction.enable", "soft dynamic correction (motion_tracking.py:133, 840-870)"),
+                           ("domain_rand.parallel_serial_pd.enable", "parallel / serial PD gain randomisation (legged_robot_base.py:607-623)"),
+                           ("domain_rand.randomize_default_dof_pos", "default_dof_pos randomisation at resets (legged_robot_base.py:632-635)"),
+                           ("domain_rand.born_offset", "born offset"), ("domain_rand.born_heading_randomization", "born heading randomisation"),
+                           ("domain_rand.motion_package_loss", "motion package loss"), ("domain_rand.randomize_motion_ref_xyz", "reference xyz randomisation")):
+            if _get(cfg, path, False):
+                raise NotImplementedError(f"{path}: {what} is not implemented by the B200 tracking step")
+        if float(_get(dr, "reinit_epis_rand", -1) or -1) > 0:
+            raise NotImplementedError("domain_rand.reinit_epis_rand > 0 is not implemented by the B200 tracking step")
         s.clip_observations = float(_get(cfg, "normalization.clip_observations"))
         return s
 
@@ -275,8 +286,9 @@ class TrackSpec:
         for g, keys in dict(_get(obs, "obs_dict")).items():
             segs, off = [], 0
             for key in sorted(keys):
-                if key.endswith("_raw"):
-                    raise NotImplementedError("'_raw' observation keys are not implemented by the B200 tracking step")
+                if key.endswith("_raw"):  # parse_observation stores the value under the stripped key and _post_config_observation_callback
+                    # then looks up the "_raw" name (helpers.py:138-152, legged_robot_base.py:788-793): KeyError in the reference
+                    raise NotImplementedError("'_raw' observation keys cannot run in the reference (KeyError in _post_config_observation_callback)")
                 if key in aux:
                     for hk in sorted(aux[key].keys()):
                         n = int(aux[key][hk]) * self.hist_dim[hk]
@@ -295,6 +307,13 @@ class TrackSpec:
                                      noise=self.noise_scales[key]))
                     off += n
             self.obs_groups[g] = dict(segs=segs, dim=off)
+        # observation-noise curriculum (legged_robot_base.py:119-120, 637-645; the thresholds are the reference's: the level-down
+        # one from obs.*, the level-up one from rewards.reward_penalty_level_up_threshold)
         self.add_noise_curriculum = bool(_get(obs, "add_noise_currculum", False))
-        if self.add_noise_curriculum:
-            raise NotImplementedError("observation-noise curriculum is not implemented by the B200 tracking step")
+        self.noise_cur = dict(enable=self.add_noise_curriculum, initial=float(_get(obs, "noise_initial_value", 1.0)),
+                              lo=float(_get(obs, "noise_value_min", 0.0)), hi=float(_get(obs, "noise_value_max", 1.0)),
+                              degree=float(_get(obs, "soft_dof_pos_curriculum_degree", 0.0)),
+                              down=float(_get(obs, "soft_dof_pos_curriculum_level_down_threshold", 0.0)),
+                              up=float(_get(cfg, "rewards.reward_penalty_level_up_threshold", 0.0)))
+        if _get(obs, "noise_process.enable", False):
+            raise NotImplementedError("obs.noise_process is not implemented by the B200 tracking step")

@@ -86,6 +86,7 @@ class TrackingStep:
         init[_lib.S_SOFT_DOF_POS] = s.limit_cur["dof_pos"]["initial"]
         init[_lib.S_SOFT_DOF_VEL] = s.limit_cur["dof_vel"]["initial"]
         init[_lib.S_SOFT_TORQUE] = s.limit_cur["torque"]["initial"]
+        init[_lib.S_NOISE_CUR] = s.noise_cur["initial"]
         self.scalars.copy_(torch.tensor(init, dtype=torch.float64))
         # outputs
         self.obs_buf_dict = {g: torch.zeros(N, v["dim"], **f32) for g, v in s.obs_groups.items()}
@@ -129,6 +130,12 @@ class TrackingStep:
         self._io.env_offset = int(env_offset)  # global id of this rank's env 0 (pbhc_b200.dist.shard_range): keys the in-kernel random streams
         self._keep = None
 
+    def set_is_evaluating(self, enforce_randomize_motion_start_eval=False):
+        """LeggedRobotMotionTracking.set_is_evaluating (motion_tracking.py:327-328): from now on a reset starts its clip at time 0
+        instead of a sampled time (`_resample_motion_times`, :374-377) unless config.enforce_randomize_motion_start_eval."""
+        self.is_evaluating = True
+        self._cfg.start_time_zero = 0 if enforce_randomize_motion_start_eval else 1
+
     def set_push_state(self, counter, interval_s):
         """push_robot_counter [N] and push_interval_s [N] (legged_robot_base.py:135, 139) into the packed per-env state."""
         word = (counter.to(self.device).to(torch.int32) & 0xffff) | (interval_s.to(self.device).to(torch.int32) << 16)
@@ -171,6 +178,8 @@ class TrackingStep:
                          (sp.term_torque, "terminate_by_torque_limit")):
             if on:  # legged_robot_base.py:425-429
                 d[name] = self.scalars[b + _lib.LOG_NAMES_TERM[name]].float()
+        if sp.add_noise_curriculum:  # legged_robot_base.py:760-761
+            d["current_noise_curriculum_value"] = self.scalars[b + _lib.L_NOISE_CUR].float()
         return d
 
     def reward_tracking_sigma(self):
@@ -297,6 +306,10 @@ class TrackingStep:
         # domain_rand.push_robots (legged_robot_base.py:134-147, 382-388, 1090-1106)
         c.push_robots, c.push_fixed = int(dr["push_robots"]), int(dr["push_fixed"])
         c.push_lo, c.push_hi, c.max_push_vel = int(dr["push_interval_s"][0]), int(dr["push_interval_s"][1]), dr["max_push_vel_xy"]
+        c.start_time_zero = 0  # set_is_evaluating()
+        nc = s.noise_cur
+        c.cur_noise.enable, c.cur_noise.lo, c.cur_noise.hi = int(nc["enable"]), nc["lo"], nc["hi"]
+        c.cur_noise.degree, c.cur_noise.down, c.cur_noise.up = nc["degree"], nc["down"], nc["up"]
         # base-class terminations (legged_robot_base.py:433-476)
         c.term_contact, c.term_contact_mask = int(s.term_contact), _mask(s.term_contact_ids)
         c.term_low_height, c.term_min_height = int(s.term_low_height), s.term_min_height

@@ -25,7 +25,7 @@ def test_library_exports_header_symbols():
 
 def test_version_and_error_string():
     L = _lib.lib()
-    assert L.pbhc_abi_version() == _lib.ABI_VERSION == 10
+    assert L.pbhc_abi_version() == _lib.ABI_VERSION == 11
     assert isinstance(L.pbhc_last_error(), bytes)
 
 

@@ -94,7 +94,9 @@ def compare_state(ts, G, spec, tag, loose=None):
             assert abs(sc[_lib.S_EMA + i] - float(G["ema_" + name])) <= sig_tol * abs(float(G["ema_" + name])), (tag, name)
     for name, i in (("average_episode_length", _lib.S_AVG_EPL), ("reward_penalty_scale", _lib.S_PENALTY),
                     ("motion_far_threshold", _lib.S_FAR_THR), ("soft_dof_pos", _lib.S_SOFT_DOF_POS),
-                    ("soft_dof_vel", _lib.S_SOFT_DOF_VEL), ("soft_torque", _lib.S_SOFT_TORQUE)):
+                    ("soft_dof_vel", _lib.S_SOFT_DOF_VEL), ("soft_torque", _lib.S_SOFT_TORQUE), ("current_noise_curriculum_value", _lib.S_NOISE_CUR)):
+        if name not in G:
+            continue
         assert abs(sc[i] - float(G[name])) <= 1e-6 * abs(float(G[name])) + 1e-12, (tag, name, sc[i], float(G[name]))
 
 
@@ -111,6 +113,8 @@ def _run_golden_case(case, tmp_path, exact, loose=None):
     if hasattr(ts, "ref_init_yaw"):  # ref_init_rpy[0, 2]: the step derived it itself from the motion library (K1 at construction)
         assert abs(ts.ref_init_yaw - float(init["ref_init_yaw"])) < (1e-6 if exact else 1e-5), (ts.ref_init_yaw, float(init["ref_init_yaw"]))
     load_state(ts, init, spec)
+    if case.endswith("_eval"):
+        ts.set_is_evaluating()
     sim._base_com_bias.copy_(torch.from_numpy(init["base_com_bias"]))
     sim._link_mass_scale.copy_(torch.from_numpy(init["link_mass_scale"]))
     sim.friction_coeffs.copy_(torch.from_numpy(init["friction_coeffs"]))
@@ -127,6 +131,8 @@ def _run_golden_case(case, tmp_path, exact, loose=None):
         actions = torch.from_numpy(g[p + "in_actions"]).to(DEV).contiguous()
         torques = torch.from_numpy(g[p + "in_torques"]).to(DEV).contiguous()
         inject = {k: torch.from_numpy(g[p + "out_" + k]).to(DEV).contiguous() for k in INJECT}
+        if case.endswith("_eval"):
+            del inject["motion_start_times"]
         if p + "in_term_gates" in g:
             inject["term_gates"] = int(g[p + "in_term_gates"])
         if p + "in_push_robot_counter" in g:  # domain_rand.push_robots: the fixture moves a few envs next to their push before every step
@@ -176,9 +182,11 @@ def _run_golden_case(case, tmp_path, exact, loose=None):
                 assert_close(log[k[len(p) + 4:]].cpu(), np.float32(g[k]), what=f"{tag} log {k}", **(loose or {}).get("log", dict(rtol=1e-5, atol=1e-6)))
 
 
-@pytest.mark.parametrize("case", ["mt23_main", "mt23_bench", "gt29_teacher", "gt29_student", "mt23_edge", "gt29_edge", "mt23_term", "gt29_term", "mt23_p4", "gt29_p4", "mt23_push", "gt29_push"])
+@pytest.mark.parametrize("case", ["mt23_main", "mt23_bench", "gt29_teacher", "gt29_student", "mt23_edge", "gt29_edge", "mt23_term", "gt29_term", "mt23_p4", "gt29_p4", "mt23_push", "gt29_push", "mt23_eval", "gt29_eval"])
 def test_track_step_matches_reference_golden(case, tmp_path):
-    """*_push: domain_rand.push_robots as the shipped domain_rand/main.yaml has it (legged_robot_base.py:382-388, 1090-1106): pushes
+    """*_eval: the env after set_is_evaluating() (a reset starts its clip at time 0 - not injected here) with the observation-noise
+    curriculum on (its value, log and borrowed thresholds; legged_robot_base.py:637-645).
+    *_push: domain_rand.push_robots as the shipped domain_rand/main.yaml has it (legged_robot_base.py:382-388, 1090-1106): pushes
     added to / replacing the root velocity, an env that is pushed and reset in the same step, need_to_refresh_envs.
     *_p4: the observation sources and reward terms no shipped config uses (tools/make_golden_env_step.py run_p4): relyaw,
     local_ref_rigid_body_pos_relyaw, vr_3point_pos (with the reference's cross-env heading pairing), future_ref_dof_pos / _vel,
@@ -382,3 +390,40 @@ def test_push_robots_in_kernel_draws(case, tmp_path):
     assert torch.equal(got, want)
     assert bool((sim.all_root_states[~due & ~reset, 7:9] == 0.25).all())
     assert torch.equal(ts.need_to_refresh_envs, due | reset)
+
+
+def test_observation_noise_follows_the_noise_curriculum(tmp_path):
+    """obs.add_noise_currculum: every noise scale is multiplied by current_noise_curriculum_value (helpers.py:142) - with
+    dof_vel noise 1.0 and the value at 0.5 the dof_vel observations deviate from the noise-free ones by U(-0.5, 0.5) x obs scale"""
+    g = gold("ref_env_mt23_eval.npz")
+    outs = []
+    for noise in (0.0, 1.0):
+        cfg = json.loads(str(g["meta_config_json"]))
+        cfg["obs"]["noise_scales"]["dof_vel"] = noise
+        spec = TrackSpec.from_config(cfg)
+        N = int(g["meta_n_envs"])
+        ts, ml = make_step(spec, N, tmp_path / str(noise), clip_names=NAMES, exact=True)
+        sim = make_sim(N, spec.Jb, spec.D, spec.L)
+        init = {k[5:]: g[k] for k in g if k.startswith("init_")}
+        load_state(ts, init, spec)
+        assert float(ts.scalars[_lib.S_NOISE_CUR]) == 0.5
+        sim._rigid_body_state.copy_(torch.from_numpy(g["s0_in_body_state"]).reshape(-1, 13))
+        sim.all_root_states.copy_(torch.from_numpy(g["s0_in_root_state"]))
+        sim.dof_state.copy_(torch.from_numpy(g["s0_in_dof_state"]).reshape(-1, 2))
+        sim.contact_forces.copy_(torch.from_numpy(g["s0_in_contact_forces"]))
+        a = torch.from_numpy(g["s0_in_actions"]).to(DEV).contiguous()
+        t = torch.from_numpy(g["s0_in_torques"]).to(DEV).contiguous()
+        inject = {k: torch.from_numpy(g["s0_out_" + k]).to(DEV).contiguous() for k in INJECT}
+        obs, *_ = ts.step(sim, a, t, torch.from_numpy(init["env_origins"]).to(DEV), torch.from_numpy(init["motion_ids"]).to(DEV), inject=inject)
+        torch.cuda.synchronize()
+        seg = next(s for s in spec.obs_groups["actor_obs"]["segs"] if s["key"] == "dof_vel")
+        outs.append((obs["actor_obs"][:, seg["off"]:seg["off"] + seg["dim"]].cpu().double(), seg["scale"], obs["actor_obs"].cpu().clone(), seg))
+    (clean, sc, full0, seg), (noisy, _, full1, _) = outs
+    u = (noisy - clean) / sc
+    assert float(u.abs().max()) <= 0.5 + 1e-6 and float(u.abs().max()) > 0.4
+    assert abs(float(u.mean())) < 0.05 and abs(float(u.var()) - 0.25 / 3) < 0.02
+    full0[:, seg["off"]:seg["off"] + seg["dim"]] = 0
+    full1[:, seg["off"]:seg["off"] + seg["dim"]] = 0
+    hist_cols = [s for s in spec.obs_groups["actor_obs"]["segs"] if s["kind"] == "hist"]
+    assert hist_cols  # (the history rows hold earlier pushes: untouched by this step's noise)
+    assert torch.equal(full0, full1)

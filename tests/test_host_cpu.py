@@ -85,3 +85,34 @@ def test_track_spec_parses_the_unused_sources_and_names_the_terms_the_reference_
     g["rewards"]["reward_scales"]["teleop_radial_joint_velocity"] = 1.0  # LeggedRobotMotionTracking only
     with pytest.raises(NotImplementedError, match="only in motion_tracking"):
         TrackSpec.from_config(g)
+
+
+def test_track_spec_refuses_step_options_it_does_not_implement():
+    """a config option that changes the reference's step and is not built must fail loudly, never be ignored"""
+    import copy
+    import json
+    from pbhc_b200.spec import TrackSpec
+    from tests._util import gold
+    cfg = json.loads(str(gold("ref_env_mt23_push.npz")["meta_config_json"]))
+    s = TrackSpec.from_config(cfg)
+    assert s.dr["push_robots"] and s.dr["push_fixed"] and s.dr["push_interval_s"] == [5, 10] and not s.add_noise_curriculum
+
+    def with_(path, value):
+        c = copy.deepcopy(cfg)
+        node = c
+        ks = path.split(".")
+        for k in ks[:-1]:
+            node = node.setdefault(k, {})
+        node[ks[-1]] = value
+        return c
+    for path, value in (("use_teleop_control", True), ("soft_dynamic_correction.enable", True), ("domain_rand.parallel_serial_pd.enable", True),
+                        ("domain_rand.randomize_default_dof_pos", True), ("domain_rand.born_offset", True), ("domain_rand.reinit_epis_rand", 100),
+                        ("domain_rand.motion_package_loss", True), ("obs.noise_process", {"enable": True}), ("termination.terminate_when_dof_far", True)):
+        with pytest.raises(NotImplementedError):
+            TrackSpec.from_config(with_(path, value))
+    raw = copy.deepcopy(cfg)
+    raw["obs"]["obs_dict"]["actor_obs"] = list(raw["obs"]["obs_dict"]["actor_obs"]) + ["dof_pos_raw"]
+    with pytest.raises(NotImplementedError, match="cannot run in the reference"):
+        TrackSpec.from_config(raw)
+    e = TrackSpec.from_config(json.loads(str(gold("ref_env_mt23_eval.npz")["meta_config_json"])))
+    assert e.add_noise_curriculum and e.noise_cur["initial"] == 0.5 and e.noise_cur["up"] == float(cfg["rewards"]["reward_penalty_level_up_threshold"])

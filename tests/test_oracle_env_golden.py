@@ -11,7 +11,8 @@ from pbhc_b200.spec import TrackSpec
 from tests._util import gold, oracle_clip
 
 INJECT = ("motion_start_times", "kp_scale", "kd_scale", "rfi_lim_scale", "rao_scale", "action_delay_idx")
-SCALARS = ("average_episode_length", "reward_penalty_scale", "motion_far_threshold", "soft_dof_pos", "soft_dof_vel", "soft_torque")
+SCALARS = ("average_episode_length", "reward_penalty_scale", "motion_far_threshold", "soft_dof_pos", "soft_dof_vel", "soft_torque",
+           "current_noise_curriculum_value")
 
 
 def load_case(name):
@@ -36,7 +37,7 @@ def state_from(g, prefix, spec):
     return S
 
 
-@pytest.mark.parametrize("case", ["mt23_main", "mt23_bench", "gt29_teacher", "gt29_student", "mt23_edge", "gt29_edge", "mt23_term", "gt29_term", "mt23_p4", "gt29_p4", "mt23_push", "gt29_push"])
+@pytest.mark.parametrize("case", ["mt23_main", "mt23_bench", "gt29_teacher", "gt29_student", "mt23_edge", "gt29_edge", "mt23_term", "gt29_term", "mt23_p4", "gt29_p4", "mt23_push", "gt29_push", "mt23_eval", "gt29_eval"])
 def test_env_step_oracle_matches_reference(case):
     g, spec, N, tab = load_case(case)
     S = state_from(g, "init_", spec)
@@ -45,6 +46,9 @@ def test_env_step_oracle_matches_reference(case):
         inp = {k: torch.from_numpy(g[p + "in_" + k].copy()) for k in
                ("body_state", "root_state", "dof_state", "contact_forces", "actions", "torques")}
         inject = {k: torch.from_numpy(g[p + "out_" + k]) for k in INJECT}
+        if case.endswith("_eval"):  # set_is_evaluating(): resets start at time 0 by themselves (motion_tracking.py:374-375)
+            S["is_evaluating"] = True
+            del inject["motion_start_times"]
         if p + "in_term_gates" in g:  # the reference's `torch.rand(1) < p` draws of this step (legged_robot_base.py:455-473)
             inject["term_gates"] = int(g[p + "in_term_gates"])
         if p + "in_push_robot_counter" in g:  # the fixture moves a few envs next to their push before every step

@@ -33,7 +33,8 @@ def env_state(env):
         average_episode_length=np.float64(env.average_episode_length), reward_penalty_scale=np.float64(getattr(env, "reward_penalty_scale", 1.0)),
         motion_far_threshold=np.float64(env.terminate_when_motion_far_threshold),
         soft_dof_pos=np.float64(getattr(env, "soft_dof_pos_curriculum_value", 1.0)), soft_dof_vel=np.float64(getattr(env, "soft_dof_vel_curriculum_value", 1.0)),
-        soft_torque=np.float64(getattr(env, "soft_torque_curriculum_value", 1.0)), rew_buf=env.rew_buf, reset_buf=env.reset_buf,
+        soft_torque=np.float64(getattr(env, "soft_torque_curriculum_value", 1.0)),
+        current_noise_curriculum_value=np.float64(env.current_noise_curriculum_value), rew_buf=env.rew_buf, reset_buf=env.reset_buf,
         time_out_buf=env.time_out_buf, dof_state=env.simulator.dof_state, root_state=env.simulator.all_root_states,
         end_time_ratio_buf=env.end_time_ratio_buf)
     if hasattr(env.simulator, "_base_mass_scale"):
@@ -66,7 +67,7 @@ def _library29(tmp="/tmp/pbhc_golden"):
 
 
 def run_case(name, n_envs, n_steps, obs, seed, overrides=None, general=False, motion_file=None, motion_name=None, start_times=None, tweak=None,
-             tweak_env=None):
+             tweak_env=None, evaluating=False):
     """motion_file / motion_name: a joblib motion file instead of the default clip(s) and the fixture name recorded for it;
     start_times(env) -> tensor: motion start times instead of the seeded spread; tweak(step, body, root, dof, cf, ref): edits
     the synthetic simulator state in place (edge-case fixtures, tools/make_golden_edge.py); tweak_env(step, env): edits env
@@ -87,6 +88,8 @@ def run_case(name, n_envs, n_steps, obs, seed, overrides=None, general=False, mo
     cfg_json = json.dumps(cj)
     env, ns = E.make_env(cfg, env_cls="general" if general else "motion_tracking", seed=seed)
     sim = env.simulator
+    if evaluating:
+        env.set_is_evaluating()
     gen = torch.Generator().manual_seed(seed)
     N, D, Jb = n_envs, env.num_dof, env.num_bodies
     # spread the envs over the clip and put a few near its end so motion_end fires
@@ -210,6 +213,20 @@ def run_term():
     run_case("gt29_term", 32, 4, "motion_tracking/obs_ppo_teacher", 23, ovc, general=True, tweak=tweak_first, tweak_env=tweak_env)
 
 
+def run_eval():
+    """mt23_eval / gt29_eval: the env after set_is_evaluating() (resets start their clip at time 0, motion_tracking.py:374-377) with the
+    observation-noise curriculum on (obs.add_noise_currculum; noise scales 0 so that the fixture stays deterministic: it pins the
+    curriculum value, its log and the thresholds it borrows from the reward-penalty curriculum, legged_robot_base.py:637-645)"""
+    ov = dict(ZERO_NOISE)
+    ov.update({"obs.add_noise_currculum": True, "obs.noise_initial_value": 0.5, "obs.soft_dof_pos_curriculum_degree": 0.01})
+    if "general" not in sys.argv:
+        run_case("mt23_eval", 16, 4, "motion_tracking/main", 51, ov, evaluating=True)
+    ovc = dict(ZERO_NOISE_C)
+    ovc.update({"obs.add_noise_currculum": True, "obs.noise_initial_value": 0.5, "obs.soft_dof_pos_curriculum_degree": 0.01,
+                "obs.noise_value_max": 1.0, "obs.noise_value_min": 0.00001, "obs.soft_dof_pos_curriculum_level_down_threshold": 40})
+    run_case("gt29_eval", 16, 3, "motion_tracking/obs_ppo_teacher", 52, ovc, general=True, evaluating=True)
+
+
 def run_push():
     """mt23_push / gt29_push: domain_rand.push_robots as shipped in domain_rand/main.yaml (legged_robot_base.py:382-388, 1090-1106):
     a few envs are put one step short of their push interval in every step - among them env 0, which also resets at the end of
@@ -286,4 +303,4 @@ def run_general():
 
 if __name__ == "__main__":
     import sys
-    run_push() if "push" in sys.argv else run_p4() if "p4" in sys.argv else (run_general() if "general" in sys.argv else (run_term() if "term" in sys.argv else run()))
+    run_eval() if "eval" in sys.argv else run_push() if "push" in sys.argv else run_p4() if "p4" in sys.argv else (run_general() if "general" in sys.argv else (run_term() if "term" in sys.argv else run()))
