@@ -1254,17 +1254,9 @@ __device__ __forceinline__ void track_body(const TrackParams& P) {
         for (int i = lane; i < P.push_len; i += 32) gh[pmap[i]] = ps[i];
       }
       if (lane == 0) {
-        const PushOut po = push_update(c, io, n, __float_as_int(ef1.w), P.c.seed, push_count);
-        if (po.pushed) {
-          if (!reset) {
-            float* rs = io.root_state + n * 13 + 7;
-            rs[0] = c.push_fixed ? rs[0] + po.vx : po.vx; rs[1] = c.push_fixed ? rs[1] + po.vy : po.vy;
-          }
-          if (io.push_vel) { io.push_vel[2 * n] = po.vx; io.push_vel[2 * n + 1] = po.vy; }
-        }
-        if (io.refresh_buf) io.refresh_buf[n] = (reset || po.pushed) ? 1 : 0;
+        const int pw = push_step(c, io, n, __float_as_int(ef1.w), reset, P.c.seed, push_count);
         reinterpret_cast<float4*>(envf)[0] = make_float4(start, mlen, air0, c.n_feet > 1 ? air1 : 0.0f);
-        reinterpret_cast<float4*>(envf)[1] = make_float4(contact0, c.n_feet > 1 ? contact1 : 0.0f, etr, __int_as_float(po.word));
+        reinterpret_cast<float4*>(envf)[1] = make_float4(contact0, c.n_feet > 1 ? contact1 : 0.0f, etr, __int_as_float(pw));
         io.episode_length_buf[n] = ep;
         io.reset_buf[n] = reset ? 1 : 0;
         io.time_out_buf[n] = time_out ? 1 : 0;

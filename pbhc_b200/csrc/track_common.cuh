@@ -119,27 +119,34 @@ struct Rng {
 };
 
 // _update_counters_each_step + the push part of _update_tasks_callback + _push_robots (legged_robot_base.py:143-148, 382-388,
-// 1090-1106) for one env, run by one lane.  `word` = the env's push word (env_f32 slot 7): counter | interval_s << 16.  A pushed
-// env gets a new interval and a root lin-vel x / y of U(-max, max); the caller writes it unless the env also resets this
-// step (the reset comes later in the reference's step and overwrites the root state).
-struct PushOut { int word; bool pushed; float vx, vy; };
-__device__ __forceinline__ PushOut push_update(const PbhcTrackCfg& c, const PbhcTrackIO& io, int64_t n, int word, uint64_t seed, uint32_t step) {
-  PushOut o = {word, false, 0.0f, 0.0f};
-  if (!c.push_robots) return o;
-  int cnt = (word & 0xffff) + 1, iv = word >> 16;
-  if (cnt == (int)__fdiv_rn((float)iv, c.dt)) {  // (self.push_interval_s / self.dt).int()
-    const int64_t g = n + io.env_offset;
-    const Rng rng = {make_uint2((uint32_t)seed, (uint32_t)(seed >> 32)), (uint32_t)g, (uint32_t)((uint64_t)g >> 32), step};
-    cnt = 0;
-    iv = io.inject_push_interval ? (int)io.inject_push_interval[n] : c.push_lo + (int)(rng.draw(240).x % (uint32_t)(c.push_hi - c.push_lo));
-    const uint4 r = rng.draw(241);
-    const float lo = -c.max_push_vel, hi = c.max_push_vel;  // torch_rand_float: (upper - lower) * rand + lower
-    o.vx = io.inject_push_vel ? io.inject_push_vel[2 * n] : __fadd_rn(__fmul_rn(hi - lo, u01(r.x)), lo);
-    o.vy = io.inject_push_vel ? io.inject_push_vel[2 * n + 1] : __fadd_rn(__fmul_rn(hi - lo, u01(r.y)), lo);
-    o.pushed = true;
+// 1090-1106) for one env, run by one lane.  `word` = the env's push word (env_f32 slot 7): counter | interval_s << 16.
+// push_step() is the per-step part (count up, compare with (push_interval_s / dt).int()); the push itself - rare - is out of line:
+// a pushed env draws its next interval and a root lin-vel x / y of U(-max, max), which is added to / stored in the root state
+// unless the env also resets this step (the reset comes later in the reference's step and overwrites the root state).
+static __device__ __noinline__ int push_cold(const PbhcTrackCfg& c, const PbhcTrackIO& io, int64_t n, bool reset, uint64_t seed, uint32_t step) {
+  const int64_t g = n + io.env_offset;
+  const Rng rng = {make_uint2((uint32_t)seed, (uint32_t)(seed >> 32)), (uint32_t)g, (uint32_t)((uint64_t)g >> 32), step};
+  const int iv = io.inject_push_interval ? (int)io.inject_push_interval[n] : c.push_lo + (int)(rng.draw(240).x % (uint32_t)(c.push_hi - c.push_lo));
+  const uint4 r = rng.draw(241);
+  const float lo = -c.max_push_vel, hi = c.max_push_vel;  // torch_rand_float: (upper - lower) * rand + lower
+  const float vx = io.inject_push_vel ? io.inject_push_vel[2 * n] : __fadd_rn(__fmul_rn(hi - lo, u01(r.x)), lo);
+  const float vy = io.inject_push_vel ? io.inject_push_vel[2 * n + 1] : __fadd_rn(__fmul_rn(hi - lo, u01(r.y)), lo);
+  if (!reset) {
+    float* rs = io.root_state + n * 13 + 7;
+    rs[0] = c.push_fixed ? rs[0] + vx : vx; rs[1] = c.push_fixed ? rs[1] + vy : vy;
   }
-  o.word = (cnt & 0xffff) | (iv << 16);
-  return o;
+  if (io.push_vel) { io.push_vel[2 * n] = vx; io.push_vel[2 * n + 1] = vy; }
+  return iv << 16;  // counter 0
+}
+// returns the env's new push word; sets refresh_buf[n] = reset | pushed
+__device__ __forceinline__ int push_step(const PbhcTrackCfg& c, const PbhcTrackIO& io, int64_t n, int word, bool reset, uint64_t seed, uint32_t step) {
+  if (!c.push_robots) return word;
+  const int cnt = (word & 0xffff) + 1, iv = word >> 16;
+  const bool pushed = cnt == (int)__fdiv_rn((float)iv, c.dt);  // (self.push_interval_s / self.dt).int()
+  if (pushed) word = push_cold(c, io, n, reset, seed, step);
+  else word = (cnt & 0xffff) | (iv << 16);
+  if (io.refresh_buf) io.refresh_buf[n] = (reset || pushed) ? 1 : 0;
+  return word;
 }
 
 // calc_heading_quat_inv (rotations.py:256-268, 296-306) = quat_from_angle_axis(-heading, z) (rotations.py:138-146)

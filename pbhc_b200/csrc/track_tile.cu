@@ -49,7 +49,7 @@ constexpr int kPieces = 5;         // pieces of the per-env scalar pre-computati
 #define PBHC_HOTK_INT(X) \
   X(J) X(Jb) X(D) X(L) X(H) X(n_ext) X(n_feet) X(n_groups) X(R) X(n_sums) X(n_hd) X(hist_any_mul) X(has_air_time) X(n_feat) \
   X(contact_size) X(rec_stride) X(use_vec_reward) X(only_positive) X(has_termination) X(cur_torque_enable) X(term_gravity) \
-  X(term_motion_far) X(term_motion_end) X(term_contact) X(term_low_height) X(term_dof_pos) X(term_dof_vel) X(term_torque) X(term_base) X(dif_joint_used) X(ref_vel_used) X(ext_identity) X(ref_pos_out) X(ref_rot_out) X(default_dof_stride) \
+  X(term_motion_far) X(term_motion_end) X(term_contact) X(term_low_height) X(term_dof_pos) X(term_dof_vel) X(term_torque) X(term_base) X(push_robots) X(dif_joint_used) X(ref_vel_used) X(ext_identity) X(ref_pos_out) X(ref_rot_out) X(default_dof_stride) \
   X(e_pos) X(e_vel) X(e_ang) X(e_dp) X(e_dv) X(e_c) \
   X(o_tab) X(o_stab) X(n_slots) X(o_hmap) X(o_hmul) X(o_rv) X(o_pre) X(o_rows) X(o_scr) X(scr_pitch) \
   X(i_body) X(i_cf) X(i_hist) X(i_dof) X(i_act) X(i_tq) X(i_lact) X(i_ldv) X(i_kp) X(i_kd) X(i_es0) X(i_es1) X(i_org0) X(i_org1) X(i_com0) X(i_com1) X(i_fric0) X(i_fric1) \
@@ -1010,17 +1010,9 @@ __device__ __forceinline__ void track_tile_body(const TileParams& P) {
       // ---- i. state write-back, cross-env sums ----------------------------------------------------------------------------------------
       if (lane == 0) {
         float4* of = reinterpret_cast<float4*>(io.env_f32) + n * 2;
-        const PushOut po = push_update(c, io, n, __float_as_int(s_envf[7]), P.c.seed, push_count);
-        if (po.pushed) {
-          if (!reset) {
-            float* rs = io.root_state + n * 13 + 7;
-            rs[0] = c.push_fixed ? rs[0] + po.vx : po.vx; rs[1] = c.push_fixed ? rs[1] + po.vy : po.vy;
-          }
-          if (io.push_vel) { io.push_vel[2 * n] = po.vx; io.push_vel[2 * n + 1] = po.vy; }
-        }
-        if (io.refresh_buf) io.refresh_buf[n] = (reset || po.pushed) ? 1 : 0;
+        const int pw = KC(push_robots) ? push_step(c, io, n, __float_as_int(s_envf[7]), reset, P.c.seed, push_count) : __float_as_int(s_envf[7]);
         of[0] = make_float4(start, mlen, air0, KC(n_feet) > 1 ? air1 : 0.0f);
-        of[1] = make_float4(contact0, KC(n_feet) > 1 ? contact1 : 0.0f, etr, __int_as_float(po.word));
+        of[1] = make_float4(contact0, KC(n_feet) > 1 ? contact1 : 0.0f, etr, __int_as_float(pw));
         io.episode_length_buf[n] = ep;
         io.reset_buf[n] = reset ? 1 : 0;
         io.time_out_buf[n] = time_out ? 1 : 0;
@@ -1141,7 +1133,7 @@ static int tile_plan(const PbhcTrackCfg& c, const PbhcTableDesc& tab, const Pbhc
   k.n_sums = c.n_episode_sums; k.n_feat = 16 + L; k.contact_size = tab.contact_size; k.rec_stride = tab.rec_stride;
   k.use_vec_reward = c.use_vec_reward; k.only_positive = c.only_positive_rewards; k.has_termination = c.has_termination;
   k.term_contact = c.term_contact; k.term_low_height = c.term_low_height; k.term_dof_pos = c.term_dof_pos; k.term_dof_vel = c.term_dof_vel;
-  k.term_torque = c.term_torque; k.term_base = (c.term_contact || c.term_low_height || c.term_dof_pos || c.term_dof_vel || c.term_torque) ? 1 : 0;
+  k.push_robots = c.push_robots; k.term_torque = c.term_torque; k.term_base = (c.term_contact || c.term_low_height || c.term_dof_pos || c.term_dof_vel || c.term_torque) ? 1 : 0;
   k.term_min_height = c.term_min_height; k.term_dof_vel_scale = c.term_dof_vel_scale; k.term_torque_scale = c.term_torque_scale;
   k.term_contact_mask = (long long)c.term_contact_mask;
   k.cur_torque_enable = c.cur_torque.enable; k.term_gravity = c.term_gravity; k.term_motion_far = c.term_motion_far; k.term_motion_end = c.term_motion_end;
