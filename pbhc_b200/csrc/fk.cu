@@ -334,7 +334,19 @@ __global__ void __launch_bounds__(kFkWarps * 32, 16) fk_kernel(const __grid_cons
 // there (the same lane wrote it), ancestors computed by several limbs are written with identical values, and the tile
 // leaves as three contiguous copies of 16 bytes per lane.  Per pose ~2.3x fewer warp-instructions than a thread per pose
 // (whose 27-joint chain is serial and whose staged chunks leave float by float), and a batch of 4096 poses still fills the GPU.
-constexpr int kLimbs = 4, kLimbPoses = 8, kLimbWarps = 2;
+#ifndef F_FK_WARPS
+#define F_FK_WARPS 2
+#endif
+#ifndef F_FK_INBUFS
+#define F_FK_INBUFS 1   // 1: one input buffer, refilled as soon as the tile's joints are computed (13 KB of staging per warp, 16 warps per SM);
+                        // 2: the next tile's axis-angles arrive while this one is computed (15.8 KB, 14 warps per SM).
+                        // B200, 65536 poses of the 23-DoF tree: 0.0489 ms vs 0.0522 ms (and 0.0567 ms with the quaternions staged too)
+#endif
+constexpr int kLimbs = 4, kLimbPoses = 8, kLimbWarps = F_FK_WARPS, kLimbInBufs = F_FK_INBUFS;
+// floats of a warp's staging: input buffer(s) + world positions and rotations of the 8 poses in the layout of the global outputs
+// (the quaternions leave straight from registers, 16 bytes per joint: nothing reads them back)
+__host__ __device__ inline int fk_limb_in_floats(int J) { return (kLimbPoses * 3 * J + kLimbPoses * 3 + 3) & ~3; }
+__host__ __device__ inline int fk_limb_warp_floats(int J) { return kLimbInBufs * fk_limb_in_floats(J) + kLimbPoses * 12 * J; }
 struct FkLimbParams {
   int J, n_limbs, max_steps;
   int8_t parent[PBHC_MAX_JOINTS];
@@ -363,11 +375,10 @@ __global__ void __launch_bounds__(kLimbWarps * 32) fk_limb_kernel(const __grid_c
   }
   for (int i = threadIdx.x; i < kLimbs * P.max_steps; i += blockDim.x) s_step[i] = P.step_joint[i / P.max_steps][i % P.max_steps];
   __syncthreads();
-  // per warp: two input buffers [8][3J] + [8][3], staging pos [8][3J] | rot [8][9J] | quat [8][4J]
-  const int in_floats = (kLimbPoses * 3 * J + kLimbPoses * 3 + 3) & ~3;
-  const int out_floats = kLimbPoses * 16 * J;
-  float* w_base = smem + const_floats + warp * (2 * in_floats + out_floats);
-  float* st_pos = w_base + 2 * in_floats, *st_rot = st_pos + kLimbPoses * 3 * J, *st_quat = st_rot + kLimbPoses * 9 * J;
+  // per warp: input buffer(s) [8][3J] + [8][3], staging pos [8][3J] | rot [8][9J]
+  const int in_floats = fk_limb_in_floats(J);
+  float* w_base = smem + const_floats + warp * fk_limb_warp_floats(J);
+  float* st_pos = w_base + kLimbInBufs * in_floats, *st_rot = st_pos + kLimbPoses * 3 * J;
   const int p = lane >> 2, k = lane & 3;
   const int n_silent = P.n_silent[k];
   const int64_t n_tiles = (n + kLimbPoses - 1) / kLimbPoses, tstep = (int64_t)gridDim.x * kLimbWarps;
@@ -392,10 +403,10 @@ __global__ void __launch_bounds__(kLimbWarps * 32) fk_limb_kernel(const __grid_c
 
   int64_t t = (int64_t)blockIdx.x * kLimbWarps + warp;
   if (t < n_tiles) request(t, 0);
-  for (int buf = 0; t < n_tiles; t += tstep, buf ^= 1) {
+  for (int buf = 0; t < n_tiles; t += tstep, buf ^= (kLimbInBufs - 1)) {
     asm volatile("cp.async.wait_group 0;" ::: "memory");
     __syncwarp();
-    if (t + tstep < n_tiles) request(t + tstep, buf ^ 1);
+    if (kLimbInBufs == 2 && t + tstep < n_tiles) request(t + tstep, buf ^ 1);
     const int64_t p0 = t * kLimbPoses;
     const int np = (int)min((int64_t)kLimbPoses, n - p0);
     const float* in = w_base + buf * in_floats;
@@ -442,10 +453,17 @@ __global__ void __launch_bounds__(kLimbWarps * 32) fk_limb_kernel(const __grid_c
         float* orot = st_rot + (p * J + i) * 9;
 #pragma unroll
         for (int c = 0; c < 9; ++c) orot[c] = Rc.m[c];
-        if (quat && s >= n_silent) { if (kFast) mat_to_quat_xyzw_fast(Rc, st_quat + (p * J + i) * 4); else mat_to_quat_xyzw(Rc, st_quat + (p * J + i) * 4); }
+        if (quat && s >= n_silent) {
+          float q4[4];
+          if (kFast) mat_to_quat_xyzw_fast(Rc, q4); else mat_to_quat_xyzw(Rc, q4);
+          float* gq = quat + ((p0 + p) * J + i) * 4;
+          if (aligned) *reinterpret_cast<float4*>(gq) = make_float4(q4[0], q4[1], q4[2], q4[3]);
+          else { gq[0] = q4[0]; gq[1] = q4[1]; gq[2] = q4[2]; gq[3] = q4[3]; }
+        }
       }
     }
     __syncwarp();
+    if (kLimbInBufs == 1 && t + tstep < n_tiles) request(t + tstep, 0);  // (the input buffer is free again)
     // the tile leaves: three contiguous runs of np poses
     auto flush = [&](const float* st, float* g, int row) {
       float* dst = g + p0 * row;
@@ -455,7 +473,6 @@ __global__ void __launch_bounds__(kLimbWarps * 32) fk_limb_kernel(const __grid_c
     };
     flush(st_pos, pos, 3 * J);
     if (rotmat) flush(st_rot, rotmat, 9 * J);
-    if (quat) flush(st_quat, quat, 4 * J);
     __syncwarp();
   }
 }
@@ -570,8 +587,7 @@ static int fk_launch(const PbhcTree* tree, const float* pose_aa, const float* tr
       for (int i = 0; i < 3 * J; ++i) LP.off[i] = P.off[i];     // (the constants may change between calls with the same topology)
       for (int i = 0; i < 9 * J; ++i) LP.lrot[i] = P.lrot[i];
       const int const_floats = (12 * J + J + kLimbs * LP.max_steps + 3) & ~3;
-      const int in_floats = (kLimbPoses * 3 * J + kLimbPoses * 3 + 3) & ~3;
-      const size_t shmem = (size_t)(const_floats + kLimbWarps * (2 * in_floats + kLimbPoses * 16 * J)) * sizeof(float);
+      const size_t shmem = (size_t)(const_floats + kLimbWarps * fk_limb_warp_floats(J)) * sizeof(float);
       auto kern = fast ? fk_limb_kernel<true> : fk_limb_kernel<false>;
       static thread_local size_t configured[2] = {0, 0};
       static thread_local int per_sm[2] = {0, 0};
