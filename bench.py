@@ -30,8 +30,8 @@ if ROOT not in sys.path:
 METRIC = "tracked env-steps/s (motion lookup+FK+reward+obs)"
 UNIT = "env-steps/s"
 WORKLOADS = {
-    "A": "G1 23-DoF motion_tracking step (obs=main, rewards=main, clip Horse-stance_pose), synthetic sim state",
-    "C": "G1 29-DoF general_tracking step (obs=obs_ppo_teacher, rewards=general_main, 3-clip library, per-env motion ids, "
+    "A": "G1 23-DoF motion_tracking step (obs=main, rewards=main, domain_rand=main incl. push_robots, clip Horse-stance_pose), synthetic sim state",
+    "C": "G1 29-DoF general_tracking step (obs=obs_ppo_teacher, rewards=general_main, domain_rand=main incl. push_robots, 3-clip library, per-env motion ids, "
          "20-step future window), synthetic sim state",
 }
 WORKLOAD = WORKLOADS["A"]
@@ -158,7 +158,7 @@ def cpu_reference(n_envs, steps, warmup, seconds=None, with_fk=True, seed=0, wor
     from pbhc_b200.workload import CASE, CASE_C, CLIP
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
-    spec = TrackSpec.from_config(env_config(CASE_C if workload == "C" else CASE))
+    spec = TrackSpec.from_config(env_config(CASE_C if workload == "C" else CASE, push_robots=True))
     tag, clips = ("29", list(CLIPS29)) if spec.general else ("23", [CLIP])
     tree = oracle_tree(tag)
     N, D, Jb, J = n_envs, spec.D, spec.Jb, spec.J
@@ -248,7 +248,7 @@ def run_b200_arm(a):
         dist.init_process_group("nccl", device_id=dev)
     N, K, W, with_fk = a.envs, a.steps, max(a.warmup, 3), not a.no_fk
     from pbhc_b200.workload import CASE, CASE_C
-    wl = Workload(N, dev, tempfile.mkdtemp(prefix=f"pbhc_bench_r{rank}_"), seed=1000 + rank, case=CASE_C if a.workload == "C" else CASE)
+    wl = Workload(N, dev, tempfile.mkdtemp(prefix=f"pbhc_bench_r{rank}_"), seed=1000 + rank, case=CASE_C if a.workload == "C" else CASE, push_robots=True)
     ts = wl.ts
     sampler = ClockSampler(torch.cuda.current_device() if os.environ.get("CUDA_VISIBLE_DEVICES") is None else local)
     sampler.start()
@@ -379,7 +379,7 @@ def config_c_pass(torch, a, dev, peak):
     import time as _t
     from pbhc_b200.workload import Workload, CASE_C, fk_bytes
     t0 = _t.perf_counter()
-    wl = Workload(a.envs, dev, tempfile.mkdtemp(prefix="pbhc_bench_C_"), seed=2000, case=CASE_C, library_clips=a.library_clips)
+    wl = Workload(a.envs, dev, tempfile.mkdtemp(prefix="pbhc_bench_C_"), seed=2000, case=CASE_C, library_clips=a.library_clips, push_robots=True)
     load_s = _t.perf_counter() - t0
     for _ in range(3):
         wl.step(True)

@@ -205,7 +205,8 @@ int pbhc_clips_prepare(const float* pos, const float* quat, const float* pose_aa
 #define PBHC_MAX_KEY 16     /* key bodies (general_tracking) */
 #define PBHC_MAX_FUTURE 32  /* future reference steps (general_tracking) */
 #define PBHC_ENVF_STRIDE 8   /* env_f32 row: start_time, motion_len, air_time[2], last_contact[2], end_time_ratio, push word */
-/* the push word (ABI 10) is an int32 stored in the float slot: push_robot_counter | push_interval_s << 16 (legged_robot_base.py:135-147) */
+/* the push word (ABI 10) is an int32 stored in the float slot: push_robot_counter | push_threshold << 16, push_threshold =
+ * (push_interval_s / dt).int() - the step count the reference compares the counter with (legged_robot_base.py:135-147, 384) */
 
 /* layout of `scalars` (device double[PBHC_SCALARS]) */
 #define PBHC_S_SIGMA 0        /* [17] reward_tracking_sigma, enum order of pbhc_b200/spec.py SIGMA_IDS */
@@ -433,8 +434,10 @@ typedef struct {
                                  * point by the heading of env (3 i + k) mod N (`heading_inv_rot.repeat(3, 1)`, motion_tracking.py:730-731), so
                                  * every env's pre-reset heading is written here by a small kernel ahead of the step kernel */
   /* ABI 10 */
-  int64_t* refresh_buf;         /* [N] nullable: need_to_refresh_envs after this step = reset or pushed (legged_robot_base.py:314-319, 1095);
-                                 * int64 0 / 1 like reset_buf, so pbhc_compact_ids turns it into refresh_env_ids */
+  int64_t* refresh_buf;         /* [N] nullable: need_to_refresh_envs (legged_robot_base.py:314-319, 1095) as a step stamp - an env that this
+                                 * step resets or pushes gets (pushes so far, scalars[PBHC_S_PUSH_COUNT]) + 1, the value the counter has after
+                                 * pbhc_track_finalize; other rows are untouched (no per-env store on the hot path), so
+                                 * need_to_refresh_envs = (refresh_buf == scalars[PBHC_S_PUSH_COUNT]) */
   float* push_vel;              /* [N,2] nullable: push_robot_vel_buf / record_push_robot_vel_buf rows of envs pushed this step */
   const int64_t* inject_push_interval; /* [N] nullable: the next push_interval_s of envs pushed this step (the reference's torch.randint draw) */
   const float* inject_push_vel; /* [N,2] nullable: their push velocity (torch_rand_float) */

@@ -595,8 +595,14 @@ def step(spec, tab, S, inp, inject=None):
         S["push_robot_counter"] += 1
         ids = (S["push_robot_counter"] == (S["push_interval_s"] / spec.dt).int()).nonzero(as_tuple=False).flatten()
         S["push_robot_counter"][ids] = 0
-        S["push_interval_s"][ids] = inject["push_interval_s"][ids]
-        vel = inject["push_vel"][ids]
+        if inject is not None and "push_interval_s" in inject:
+            S["push_interval_s"][ids] = inject["push_interval_s"][ids]
+            vel = inject["push_vel"][ids]
+        else:  # the reference's own draws (torch.randint, torch_rand_float)
+            lo_s, hi_s = spec.dr["push_interval_s"]
+            S["push_interval_s"][ids] = torch.randint(int(lo_s), int(hi_s), (len(ids),))
+            mv = spec.dr["max_push_vel_xy"]
+            vel = (mv - (-mv)) * torch.rand(len(ids), 2) + (-mv)
         S["push_robot_vel_buf"][ids] = vel
         if spec.dr.get("push_fixed"):
             inp["root_state"][ids, 7:9] += vel

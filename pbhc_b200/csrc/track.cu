@@ -1132,6 +1132,7 @@ __device__ __forceinline__ void track_body(const TrackParams& P) {
         const Rng rng = {make_uint2((uint32_t)P.c.seed, (uint32_t)(P.c.seed >> 32)), (uint32_t)(n + io.env_offset), (uint32_t)((uint64_t)(n + io.env_offset) >> 32), push_count};
         if (ld) io.actions[n * D + lane] = 0.0f;
         if (lane == 0 && io.last_episode_length_buf) io.last_episode_length_buf[n] = last_ep;  // extras["episode"]["end_epis_length"], legged_robot_base.py:515
+        if (lane == 0 && io.refresh_buf) io.refresh_buf[n] = (int64_t)push_count + 1;             // need_to_refresh_envs, :493
         air0 = 0.0f; air1 = 0.0f; contact0 = 0.0f; contact1 = 0.0f;
         if (c.hist_row > 0) {  // HistoryHandler.reset: zero the ring (and what the observation rows already took from it)
           for (int i = lane; i < c.hist_row; i += 32) io.hist[n * c.hist_row + i] = 0.0f;
@@ -1550,8 +1551,8 @@ extern "C" int pbhc_track_step(const PbhcTrackCfg* cfg, const PbhcTableDesc* tab
                         io->action_delay_idx, io->episode_sums, io->scalars, io->rew_buf, io->reset_buf, io->time_out_buf,
                         io->last_episode_sums, io->partials, io->acc};
   for (const void* p : need) if (!p) { set_error("pbhc_track_step: a required PbhcTrackIO pointer is NULL"); return PBHC_E_BADARG; }
-  if (c.push_robots && (c.push_hi <= c.push_lo || c.push_lo < 1 || c.push_hi > 32767 || (float)c.push_hi / c.dt > 65535.0f)) {
-    set_error("pbhc_track_step: push_interval_s [%d, %d) outside what the 16 + 16 bit push word holds", c.push_lo, c.push_hi); return PBHC_E_RANGE;
+  if (c.push_robots && (c.push_hi <= c.push_lo || c.push_lo < 1 || c.push_hi > 32767 || (float)c.push_hi / c.dt > 32767.0f)) {
+    set_error("pbhc_track_step: push_interval_s [%d, %d) outside what the 16 + 15 bit push word holds", c.push_lo, c.push_hi); return PBHC_E_RANGE;
   }
   if (c.L < 0 || c.L > 48) { set_error("pbhc_track_step: L outside [0, 48]"); return PBHC_E_RANGE; }
   if ((c.L > 0 && !io->link_mass_scale) || (c.hist_row > 0 && !io->hist)) { set_error("pbhc_track_step: NULL link_mass_scale / hist"); return PBHC_E_BADARG; }

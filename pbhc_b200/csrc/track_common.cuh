@@ -119,8 +119,8 @@ struct Rng {
 };
 
 // _update_counters_each_step + the push part of _update_tasks_callback + _push_robots (legged_robot_base.py:143-148, 382-388,
-// 1090-1106) for one env, run by one lane.  `word` = the env's push word (env_f32 slot 7): counter | interval_s << 16.
-// push_step() is the per-step part (count up, compare with (push_interval_s / dt).int()); the push itself - rare - is out of line:
+// 1090-1106) for one env, run by one lane.  `word` = the env's push word (env_f32 slot 7): counter | threshold << 16 with
+// threshold = (push_interval_s / dt).int(), so that the per-step part push_step() is an increment and a compare; the push itself - rare - is out of line:
 // a pushed env draws its next interval and a root lin-vel x / y of U(-max, max), which is added to / stored in the root state
 // unless the env also resets this step (the reset comes later in the reference's step and overwrites the root state).
 static __device__ __noinline__ int push_cold(const PbhcTrackCfg& c, const PbhcTrackIO& io, int64_t n, bool reset, uint64_t seed, uint32_t step) {
@@ -136,16 +136,16 @@ static __device__ __noinline__ int push_cold(const PbhcTrackCfg& c, const PbhcTr
     rs[0] = c.push_fixed ? rs[0] + vx : vx; rs[1] = c.push_fixed ? rs[1] + vy : vy;
   }
   if (io.push_vel) { io.push_vel[2 * n] = vx; io.push_vel[2 * n + 1] = vy; }
-  return iv << 16;  // counter 0
+  return (int)__fdiv_rn((float)iv, c.dt) << 16;  // counter 0 | (self.push_interval_s / self.dt).int()
 }
-// returns the env's new push word; sets refresh_buf[n] = reset | pushed
+// returns the env's new push word; stamps refresh_buf[n] when the env is pushed (the reset path stamps the envs it resets)
 __device__ __forceinline__ int push_step(const PbhcTrackCfg& c, const PbhcTrackIO& io, int64_t n, int word, bool reset, uint64_t seed, uint32_t step) {
   if (!c.push_robots) return word;
-  const int cnt = (word & 0xffff) + 1, iv = word >> 16;
-  const bool pushed = cnt == (int)__fdiv_rn((float)iv, c.dt);  // (self.push_interval_s / self.dt).int()
-  if (pushed) word = push_cold(c, io, n, reset, seed, step);
-  else word = (cnt & 0xffff) | (iv << 16);
-  if (io.refresh_buf) io.refresh_buf[n] = (reset || pushed) ? 1 : 0;
+  const bool pushed = ((word + 1) & 0xffff) == (word >> 16);
+  if (pushed) {
+    word = push_cold(c, io, n, reset, seed, step);
+    if (io.refresh_buf) io.refresh_buf[n] = (int64_t)step + 1;
+  } else word = (word & 0xffff0000) | ((word + 1) & 0xffff);
   return word;
 }
 

@@ -896,6 +896,7 @@ __device__ __forceinline__ void track_tile_body(const TileParams& P) {
         const Rng rng = {make_uint2((uint32_t)c.seed, (uint32_t)(c.seed >> 32)), (uint32_t)(n + io.env_offset), (uint32_t)((uint64_t)(n + io.env_offset) >> 32), push_count};
         if (ld) io.actions[n * D + lane] = 0.0f;
         if (lane == 0 && io.last_episode_length_buf) io.last_episode_length_buf[n] = last_ep;  // extras["episode"]["end_epis_length"], legged_robot_base.py:515
+        if (lane == 0 && io.refresh_buf) io.refresh_buf[n] = (int64_t)push_count + 1;             // need_to_refresh_envs, :493
         air0 = 0.0f; air1 = 0.0f; contact0 = 0.0f; contact1 = 0.0f;
         // HistoryHandler.reset: zero the ring and what the observation rows already took from it
         for (int i = lane; i < H; i += 32) {

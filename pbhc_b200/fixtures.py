@@ -79,13 +79,15 @@ def clips_of_case(cfg):
 MAIN_NOISE = dict(base_ang_vel=0.3, projected_gravity=0.2, dof_pos=0.01, dof_vel=1.0)  # config/obs/motion_tracking/main.yaml:81-99
 
 
-def env_config(case="mt23_main", noise=None):
+def env_config(case="mt23_main", noise=None, push_robots=None):
     """the composed reference env config (hydra `env.config`) saved with the golden env fixture.  The fixture was
     recorded with every observation-noise scale at 0 (torch.rand_like cannot be replayed); `noise` = dict of
     noise_scales to put back (MAIN_NOISE = the values obs/motion_tracking/main.yaml ships)."""
     cfg = json.loads(str(gold(f"ref_env_{case}.npz")["meta_config_json"]))
     if noise:
         cfg["obs"]["noise_scales"].update(noise)
+    if push_robots is not None:  # the fixtures were recorded with pushes off; domain_rand/main.yaml ships them on (_push_fixed, [5, 10) s, 0.1 m/s)
+        cfg["domain_rand"]["push_robots"] = bool(push_robots)
     return cfg
 
 

@@ -113,7 +113,8 @@ class TrackingStep:
         if s.dr["push_robots"]:
             lo, hi = s.dr["push_interval_s"]
             self.set_push_state(torch.zeros(N, device=dev, dtype=torch.int32), torch.randint(int(lo), int(hi), (N,), device=dev))  # legged_robot_base.py:135, 139
-            self._refresh_buf = torch.zeros(N, device=dev, dtype=torch.int64)
+            self._refresh_buf = torch.zeros(N, device=dev, dtype=torch.int64)    # step stamps (PbhcTrackIO.refresh_buf)
+            self._refresh_flags = torch.zeros(N, device=dev, dtype=torch.int64)  # the mask of the last step, for pbhc_compact_ids
             self.push_robot_vel_buf = torch.zeros(N, 2, **f32)
             self._refresh_ids = torch.zeros(N, device=dev, dtype=torch.int32)
             self._refresh_count = torch.zeros(1, device=dev, dtype=torch.int32)
@@ -138,11 +139,20 @@ class TrackingStep:
 
     def set_push_state(self, counter, interval_s):
         """push_robot_counter [N] and push_interval_s [N] (legged_robot_base.py:135, 139) into the packed per-env state."""
-        word = (counter.to(self.device).to(torch.int32) & 0xffff) | (interval_s.to(self.device).to(torch.int32) << 16)
+        thr = (interval_s.to(self.device).long() / self.spec.dt).int()  # (self.push_interval_s / self.dt).int(), legged_robot_base.py:384
+        word = (counter.to(self.device).to(torch.int32) & 0xffff) | (thr << 16)
         self.env_f32[:, 7] = word.view(torch.float32)
 
     push_robot_counter = property(lambda self: self.env_f32[:, 7].contiguous().view(torch.int32) & 0xffff)
-    push_interval_s = property(lambda self: (self.env_f32[:, 7].contiguous().view(torch.int32) >> 16).long())
+
+    @property
+    def push_interval_s(self):
+        """[N] int64: the interval whose step count (interval / dt).int() the env's push word holds"""
+        lo, hi = self.spec.dr["push_interval_s"]
+        cand = torch.arange(int(lo), int(hi), device=self.device)
+        thr_of = (cand / self.spec.dt).int()
+        thr = self.env_f32[:, 7].contiguous().view(torch.int32) >> 16
+        return cand[(thr[:, None] == thr_of[None, :]).int().argmax(dim=1)]
 
     def set_ref_init_yaw(self, yaw):
         """ref_init_rpy[0, 2] of the reference env (`relyaw = rpy[:, 2:3] - ref_init_rpy[0, 2]`, motion_tracking.py:686)."""
@@ -455,14 +465,18 @@ class TrackingStep:
     def need_to_refresh_envs(self):
         """legged_robot_base.py:315: after step() the envs of reset_buf wait for the simulator setters - and, with
         domain_rand.push_robots, the envs whose root velocity the step just pushed (:1095)."""
-        return (self.reset_buf if self._refresh_buf is None else self._refresh_buf) != 0
+        if self._refresh_buf is None:
+            return self.reset_buf != 0
+        # the kernel stamps the envs it resets or pushes with the step count finalize() then reaches (no per-env store otherwise)
+        return self._refresh_buf == self.scalars[_lib.S_PUSH_COUNT].long()
 
     def refresh_env_ids(self):
         """`self.need_to_refresh_envs.nonzero(as_tuple=False).flatten()` (legged_robot_base.py:315) on the device: (ids, count) like
         reset_env_ids().  Without push_robots these ARE the reset ids."""
         if self._refresh_buf is None:
             return self.reset_env_ids()
-        _lib.check(self._L.pbhc_compact_ids(_lib.ptr(self._refresh_buf), self.N, _lib.ptr(self._refresh_ids), _lib.ptr(self._refresh_count),
+        self._refresh_flags.copy_(self.need_to_refresh_envs)
+        _lib.check(self._L.pbhc_compact_ids(_lib.ptr(self._refresh_flags), self.N, _lib.ptr(self._refresh_ids), _lib.ptr(self._refresh_count),
                                             _lib.ptr(self._compact_scratch), _lib.stream_ptr(self.device)))
         return self._refresh_ids, self._refresh_count
 
@@ -514,12 +528,15 @@ class TrackingStep:
                   hist=self.hist_row * 4, episode_sums=self.n_sums * 4, rew_buf=rew, reset_buf=8, time_out_buf=1,
                   ref_body_pos_extend=J * 12, ref_body_rot_extend=J * 16, last_episode_sums=self.n_sums * 4,
                   last_episode_length_buf=8, force_reset=1,
-                  inject_start_times=4, inject_kp=D * 4, inject_kd=D * 4, inject_rfi=D * 4, inject_rao=D * 4, inject_delay=8)
+                  inject_start_times=4, inject_kp=D * 4, inject_kd=D * 4, inject_rfi=D * 4, inject_rao=D * 4, inject_delay=8,
+                  refresh_buf=8, push_vel=8, inject_push_interval=8, inject_push_vel=8)
         return rb
 
     def launch_range(self, lo, hi, acc):
         """pbhc_track_step on envs [lo, hi) of the last bind(), per-step sums into `acc` (a [PBHC_ACC] fp64 tensor).
         Used to pipeline a step in chunks; sum the chunk `acc`s into self.acc before finalize()."""
+        if self._heading_scratch is not None:
+            raise NotImplementedError("vr_3point_pos pairs env i with the heading of env (3 i + k) mod N (motion_tracking.py:730-731): not defined for a launch on a sub-range")
         io = _lib.TrackIO.from_buffer_copy(self._io)
         for name, nbytes in self._row_bytes().items():
             v = getattr(io, name)

@@ -45,14 +45,14 @@ def fk_bytes(J):
 class Workload:
     """Everything one rank needs to run env steps on `device` for `n_envs` environments."""
 
-    def __init__(self, n_envs, device, tmpdir, seed=0, case=CASE, clip=CLIP, noise=None, library_clips=0):
+    def __init__(self, n_envs, device, tmpdir, seed=0, case=CASE, clip=CLIP, noise=None, library_clips=0, push_robots=None):
         """library_clips > 0 (config C only): the SURVEY 8d motion library of that many 29-DoF clips (fixtures.library29)
         instead of the 3-clip one, so that the table is served from HBM."""
         from .fixtures import CLIPS29, library29
         from .motion_lib import MotionLibRobot
         from .tracking_step import TrackingStep
         self.N, self.device = int(n_envs), torch.device(device)
-        self.spec = spec = TrackSpec.from_config(env_config(case, noise))
+        self.spec = spec = TrackSpec.from_config(env_config(case, noise, push_robots))
         self.tag = "29" if spec.general else "23"
         self.clips = list(CLIPS29) if spec.general else [clip]
         self.library_clips = int(library_clips) if spec.general else 0
@@ -115,7 +115,9 @@ class Workload:
     def load_env_state(self, h):
         ts = self.ts
         ts.episode_length_buf.copy_(h["episode_length_buf"])
+        push_word = ts.env_f32[:, 7].clone()  # push_robot_counter | push_interval_s << 16 (drawn at construction)
         ts.env_f32.zero_()
+        ts.env_f32[:, 7] = push_word
         ts.env_f32[:, 0].copy_(h["motion_start_times"])
         ts.env_f32[:, 1].copy_(h["motion_len"])
         ts._kp_scale.copy_(h["kp_scale"])
