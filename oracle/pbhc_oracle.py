@@ -309,6 +309,22 @@ def body_angular_velocity(quat_xyzw, dt):
     return torch.from_numpy(_gauss_filter_time(av.numpy(), -3))
 
 
+def rebase_heading(pose_aa, trans, target_heading):
+    """motion_lib_base.py:447-460 (load_motion_with_skeleton, target_heading given): rotate the clip about z so that its first
+    frame heads along target_heading (xyzw).  fp64 through scipy like the reference; calc_heading_quat_inv is the reference's
+    torch function (rotations.py:296-306) evaluated on the fp64 start quaternion.  Returns (pose_aa fp32, trans fp64) - the
+    reference then runs its FK with the fp64 translations."""
+    from scipy.spatial.transform import Rotation as sRot
+    pose_aa = torch.as_tensor(np.asarray(pose_aa)).float().clone()
+    trans = torch.as_tensor(np.asarray(trans)).float().clone()
+    start_root_rot = sRot.from_rotvec(pose_aa[0, 0])
+    heading_inv_rot = sRot.from_quat(calc_heading_quat_inv(torch.from_numpy(start_root_rot.as_quat()[None,])))
+    heading_delta = sRot.from_quat(target_heading) * heading_inv_rot
+    pose_aa[:, 0] = torch.tensor((heading_delta * sRot.from_rotvec(pose_aa[:, 0])).as_rotvec())
+    trans = torch.matmul(trans.to(torch.float64), torch.from_numpy(heading_delta.as_matrix().squeeze().T))
+    return pose_aa, trans
+
+
 def load_clip(tree, pose_aa, trans, fps, contact_mask=None):
     """What load_motion_with_skeleton + fk_batch(return_full=True) produce for one clip
     (motion_lib_base.py:403-472, torch_humanoid_batch.py:168-226).  Returns per-frame arrays

@@ -78,7 +78,25 @@ class MotionLibRobot:
         self._sampling_prob = torch.ones(self._num_unique_motions, device=dev) / self._num_unique_motions
 
     # ---- motion_lib_base.py:261-391, 403-472 --------------------------------------------------
-    def _clip_arrays(self, entry, max_len):
+    @staticmethod
+    def _rebase_heading(pose_aa, trans, target_heading):
+        """load_motion_with_skeleton with target_heading (motion_lib_base.py:447-460): the whole clip is rotated about z so that
+        its FIRST frame heads along `target_heading` (xyzw).  Host-side fp64 file preprocessing like the reference's (scipy
+        Rotation); the rotated root axis-angles and translations then take the usual device FK.
+        heading_inv = calc_heading_quat_inv(start root rotation) (rotations.py:256-268, 296-306): the x axis rotated by the
+        root, its atan2 heading, the rotation by -heading about z."""
+        from scipy.spatial.transform import Rotation as sRot
+        start = sRot.from_rotvec(np.asarray(pose_aa[0, 0], dtype=np.float64))
+        d = start.apply(np.array([1.0, 0.0, 0.0]))
+        heading = np.arctan2(d[1], d[0])
+        heading_inv = sRot.from_rotvec(np.array([0.0, 0.0, -heading]))
+        delta = sRot.from_quat(np.asarray(target_heading, dtype=np.float64)) * heading_inv
+        pose_aa = np.array(pose_aa, dtype=np.float32, copy=True)
+        pose_aa[:, 0] = (delta * sRot.from_rotvec(pose_aa[:, 0].astype(np.float64))).as_rotvec().astype(np.float32)
+        trans = np.asarray(trans, dtype=np.float64) @ delta.as_matrix().squeeze().T
+        return pose_aa, trans.astype(np.float32)
+
+    def _clip_arrays(self, entry, max_len, target_heading=None):
         if not isinstance(entry, dict):
             key = entry.split("/")[-1].split(".")[0]
             import joblib
@@ -101,11 +119,11 @@ class MotionLibRobot:
             self._contact_size = cm.shape[1]
             self.has_contact_mask = "point"
             out["contact"] = cm[start:end]
+        if target_heading is not None:
+            out["pose_aa"], out["trans"] = self._rebase_heading(out["pose_aa"], out["trans"], target_heading)
         return out
 
     def load_motions(self, random_sample=True, start_idx=0, max_len=-1, target_heading=None, sampling_prob=None):
-        if target_heading is not None:
-            raise NotImplementedError("target_heading re-basing is not part of the B200 path")
         dev = self._device
         n_load = self.num_envs
         if random_sample:
@@ -121,7 +139,7 @@ class MotionLibRobot:
             uniq, clip_of_motion = np.unique(idx_host, return_inverse=True)
         else:
             uniq, clip_of_motion = idx_host, np.arange(n_load)
-        clips = [self._clip_arrays(self._motion_data_list[u], max_len) for u in uniq]
+        clips = [self._clip_arrays(self._motion_data_list[u], max_len, target_heading) for u in uniq]
         self._build_table(clips)
         com = torch.as_tensor(clip_of_motion, dtype=torch.int64, device=dev)
         self._clip_of_motion = com.to(torch.int32).contiguous()

@@ -157,6 +157,25 @@ def test_lookup_on_product_built_table_matches_reference_golden(case, tag, name,
         assert_close(out[k].cpu(), g["out_" + k], what=k, allow=SLERP_FLIP if "rot" in k else None, **tol)
 
 
+def test_lookup_on_a_library_rebased_to_a_target_heading_matches_reference_golden(tmp_path):
+    """load_motions(target_heading=...) (motion_lib_base.py:447-460): root axis-angles / translations re-based on the host in fp64
+    like the reference, table built on the device, K1 against the reference's own get_motion_state on its re-based library.
+    (The reference runs this one FK with fp64 root translations; the device FK is fp32: positions within 1 ulp of the +-8 m they
+    reach with the query offsets, velocities inside the product-table bound.)"""
+    from pbhc_b200.motion_lib import MotionLibRobot
+    g = gold("ref_lookup_23_heading.npz")
+    ml = MotionLibRobot(product_cfg("23", str(tmp_path), ["Horse-stance_pose"]), 3, DEV)
+    ml.load_motions(random_sample=False, target_heading=g["target_heading"])
+    ids, t, off = (torch.from_numpy(g[k]).to(DEV) for k in ("motion_ids", "motion_times", "offset"))
+    out = ml.get_motion_state(ids, t, off, with_indices=True)
+    for k in KEYS + ["contact_mask"]:
+        tol = PRODUCT_TABLE_TOL["ang"] if "ang_vel" in k else PRODUCT_TABLE_TOL["vel"] if ("vel" in k and k != "dof_vel") else {}
+        assert_close(out[k].cpu(), g["out_" + k], what=k, allow=SLERP_FLIP if "rot" in k else None, **tol)
+    plain = MotionLibRobot(product_cfg("23", str(tmp_path / "plain"), ["Horse-stance_pose"]), 3, DEV)
+    plain.load_motions(random_sample=False)
+    assert not torch.allclose(plain.get_motion_state(ids, t, off)["root_rot"], out["root_rot"], atol=1e-3)  # (it did turn the clip)
+
+
 def test_lookup_multiclip_large_vs_oracle(tmp_path):
     names = ["Horse-stance_pose", "Bruce_Lee_pose", "Charleston_dance", "Hooks_punch", "Horse-stance_punch",
              "Roundhouse_kick", "Side_kick"]

@@ -123,6 +123,20 @@ def stage_lookup(ns):
                         offset=_np(off), **{"out_" + k: _np(v) for k, v in res.items()})
 
 
+def stage_heading(ns):
+    """load_motions(target_heading=...) (motion_lib_base.py:447-460): the clip re-based so that its first frame heads along the
+    target heading - root axis-angles and root translations rotated in fp64 (scipy) before FK"""
+    gen = torch.Generator().manual_seed(4321)
+    th = np.array([0.0, 0.0, np.sin(np.pi / 8), np.cos(np.pi / 8)])  # xyzw: 45 degrees of yaw
+    cfg = R.motion_cfg(R.G1_23, R.example_motion("Horse-stance_pose"))
+    ml = ns.motion_lib_robot.MotionLibRobot(cfg, num_envs=3, device="cpu")
+    ml.load_motions(random_sample=False, target_heading=th)
+    ids, t, off = _queries(ml, 48, gen)
+    res = ml.get_motion_state(ids, t.clone(), offset=off)
+    np.savez_compressed(os.path.join(GOLD, "ref_lookup_23_heading.npz"), target_heading=th, motion_ids=_np(ids), motion_times=_np(t),
+                        offset=_np(off), **{"out_" + k: _np(v) for k, v in res.items()})
+
+
 def stage_fk(ns):
     gen = torch.Generator().manual_seed(4321)
     for tag, robot in (("23", R.G1_23), ("29", R.G1_29)):
@@ -152,6 +166,8 @@ def main():
         stage_assets(ns)
     if "lookup" in stages:
         stage_lookup(ns)
+    if "heading" in stages:
+        stage_heading(ns)
     if "fk" in stages:
         stage_fk(ns)
     if "env" in stages or "gae" in stages:
