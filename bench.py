@@ -143,8 +143,8 @@ def cpu_reference(n_envs, steps, warmup, seconds=None, with_fk=True, seed=0, wor
     """Times `steps` env steps (or as many as fit in `seconds`, at least 3) of the CPU oracle on n_envs envs."""
     import torch
     from oracle import pbhc_oracle as O, pbhc_oracle_env as OE
-    from pbhc_b200 import synth
-    from pbhc_b200.fixtures import env_config, tree_json, motion_npz
+    from benchkit import synth
+    from benchkit.fixtures import env_config, tree_json, motion_npz
 
     def oracle_tree(tag):
         t = tree_json(tag)
@@ -154,8 +154,8 @@ def cpu_reference(n_envs, steps, warmup, seconds=None, with_fk=True, seed=0, wor
         m = motion_npz(name)
         return O.load_clip(oracle_tree(tag), m["pose_aa"], m["root_trans_offset"], int(m["fps"]), m.get("contact_mask"))
     from pbhc_b200.spec import TrackSpec
-    from pbhc_b200.fixtures import CLIPS29
-    from pbhc_b200.workload import CASE, CASE_C, CLIP
+    from benchkit.fixtures import CLIPS29
+    from benchkit.workload import CASE, CASE_C, CLIP
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
     spec = TrackSpec.from_config(env_config(CASE_C if workload == "C" else CASE, push_robots=True))
@@ -236,7 +236,7 @@ def run_b200_arm(a):
     import torch
     import torch.distributed as dist
     from pbhc_b200 import _lib
-    from pbhc_b200.workload import Workload, step_bytes, fk_bytes
+    from benchkit.workload import Workload, step_bytes, fk_bytes
     _lib.lib()  # fails loudly when the CUDA library is missing: there is no CPU fallback
     rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -247,8 +247,9 @@ def run_b200_arm(a):
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     N, K, W, with_fk = a.envs, a.steps, max(a.warmup, 3), not a.no_fk
-    from pbhc_b200.workload import CASE, CASE_C
-    wl = Workload(N, dev, tempfile.mkdtemp(prefix=f"pbhc_bench_r{rank}_"), seed=1000 + rank, case=CASE_C if a.workload == "C" else CASE, push_robots=True)
+    from benchkit.workload import CASE, CASE_C
+    wl = Workload(N, dev, tempfile.mkdtemp(prefix=f"pbhc_bench_r{rank}_"), seed=1000 + rank, case=CASE_C if a.workload == "C" else CASE, push_robots=True,
+                  env_offset=rank * N)  # (the in-kernel random streams are keyed by the global env id)
     ts = wl.ts
     sampler = ClockSampler(torch.cuda.current_device() if os.environ.get("CUDA_VISIBLE_DEVICES") is None else local)
     sampler.start()
@@ -377,7 +378,7 @@ def config_c_pass(torch, a, dev, peak):
     that the motion table (~0.75 GB at 1024 clips) is served from HBM.  Same timing rules as the headline: CUDA-graph
     replay of the whole step, CUDA events, K steps after warm-up; roofline against SURVEY 8d's 36 165 B / env-step."""
     import time as _t
-    from pbhc_b200.workload import Workload, CASE_C, fk_bytes
+    from benchkit.workload import Workload, CASE_C, fk_bytes
     t0 = _t.perf_counter()
     wl = Workload(a.envs, dev, tempfile.mkdtemp(prefix="pbhc_bench_C_"), seed=2000, case=CASE_C, library_clips=a.library_clips, push_robots=True)
     load_s = _t.perf_counter() - t0

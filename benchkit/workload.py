@@ -9,7 +9,7 @@ import torch
 
 from . import synth
 from .fixtures import env_config, product_cfg
-from .spec import TrackSpec
+from pbhc_b200.spec import TrackSpec
 
 CLIP = "Horse-stance_pose"
 CASE = "mt23_main"  # obs=motion_tracking/main with the four observation-noise scales set to 0 (= benchmark.yaml's choice)
@@ -45,12 +45,12 @@ def fk_bytes(J):
 class Workload:
     """Everything one rank needs to run env steps on `device` for `n_envs` environments."""
 
-    def __init__(self, n_envs, device, tmpdir, seed=0, case=CASE, clip=CLIP, noise=None, library_clips=0, push_robots=None):
+    def __init__(self, n_envs, device, tmpdir, seed=0, case=CASE, clip=CLIP, noise=None, library_clips=0, push_robots=None, env_offset=0):
         """library_clips > 0 (config C only): the SURVEY 8d motion library of that many 29-DoF clips (fixtures.library29)
         instead of the 3-clip one, so that the table is served from HBM."""
         from .fixtures import CLIPS29, library29
-        from .motion_lib import MotionLibRobot
-        from .tracking_step import TrackingStep
+        from pbhc_b200.motion_lib import MotionLibRobot
+        from pbhc_b200.tracking_step import TrackingStep
         self.N, self.device = int(n_envs), torch.device(device)
         self.spec = spec = TrackSpec.from_config(env_config(case, noise, push_robots))
         self.tag = "29" if spec.general else "23"
@@ -62,7 +62,7 @@ class Workload:
             self.clips = list(data)
         self.lib = MotionLibRobot(product_cfg(self.tag, tmpdir, self.clips, motion_data=data), self.N, self.device)
         self.lib.load_motions(random_sample=False)
-        self.ts = TrackingStep(spec, self.lib, self.N, self.device, seed=seed)
+        self.ts = TrackingStep(spec, self.lib, self.N, self.device, seed=seed, env_offset=env_offset)  # env_offset: this rank's first global env (dist.shard_range)
         self.host = self.make_inputs(seed)
         dev = self.device
         h = self.host

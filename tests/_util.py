@@ -7,7 +7,7 @@ import torch
 
 from oracle import pbhc_oracle as O
 
-from pbhc_b200.fixtures import GOLD, gold, tree_json, motion_npz, write_mjcf, product_cfg, EXTEND, env_config  # noqa: F401
+from benchkit.fixtures import GOLD, gold, tree_json, motion_npz, write_mjcf, product_cfg, EXTEND, env_config  # noqa: F401
 
 # north_star tolerance: fp32 within 1e-5 relative / 1e-6 absolute
 RTOL, ATOL = 1e-5, 1e-6
@@ -82,7 +82,7 @@ def install_exact_table(ml, clips):
 
 
 def oracle_env_from_workload(wl):
-    """(tab, S, inp) for oracle.pbhc_oracle_env.step holding the same bits as a pbhc_b200.workload.Workload."""
+    """(tab, S, inp) for oracle.pbhc_oracle_env.step holding the same bits as a benchkit.workload.Workload."""
     from oracle import pbhc_oracle_env as OE
     spec, h, N = wl.spec, wl.host, wl.N
     nc = len(wl.clips)

@@ -152,8 +152,8 @@ def test_rfi_stream_advances_under_graph_replay_and_follows_the_global_env_id():
 
 def test_shares_randomisation_tensors_with_tracking_step(tmp_path):
     from pbhc_b200.actuation import Actuation
-    from pbhc_b200.fixtures import env_config
-    from pbhc_b200.workload import Workload
+    from benchkit.fixtures import env_config
+    from benchkit.workload import Workload
     wl = Workload(64, DEV, str(tmp_path), seed=1)
     a = Actuation(env_config(), 64, DEV, tracking_step=wl.ts)
     assert a._kp_scale.data_ptr() == wl.ts._kp_scale.data_ptr() and a.action_delay_idx.data_ptr() == wl.ts.action_delay_idx.data_ptr()

@@ -58,7 +58,7 @@ def make_env(case, tmp_path, resample=False, interval=1 << 30):
     cfg["resample_motion_when_training"] = resample
     spec = TrackSpec.from_config(cfg)
     N = int(g["meta_n_envs"])
-    from pbhc_b200.fixtures import clips_of_case
+    from benchkit.fixtures import clips_of_case
     _, ml = make_step(spec, N, tmp_path, clip_names=clips_of_case(cfg)[1], exact=True)
     sim = make_sim(N, spec.Jb, spec.D, spec.L)
     sim = RecordingSim(**vars(sim), calls=[])

@@ -182,7 +182,7 @@ def test_tracking_step_writes_observations_into_storage(tmp_path):
     """zero-copy store: the fused step writes its observation rows straight into the storage slot and update_key sees
     them in place; the rows equal those of an identical step writing its own buffers."""
     from pbhc_b200.rollout import RolloutStorage
-    from pbhc_b200.workload import Workload
+    from benchkit.workload import Workload
     dev = torch.device("cuda:0")
     a, b = (Workload(257, dev, str(tmp_path / f"w{i}"), seed=11) for i in range(2))
     st = RolloutStorage(257, 3, device=dev)

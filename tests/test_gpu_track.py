@@ -9,7 +9,7 @@ import pytest
 import torch
 
 from oracle import pbhc_oracle as O, pbhc_oracle_env as OE
-from pbhc_b200 import synth
+from benchkit import synth
 from pbhc_b200 import _lib
 from pbhc_b200.spec import TrackSpec, SIGMA_IDS
 from tests._util import gold, oracle_clip, product_cfg, assert_close, SLERP_FLIP, ATOL
@@ -24,7 +24,7 @@ VEL_OBS = {"next_step_ref_motion", "future_motion_base_lin_vel", "future_motion_
 
 
 def make_step(spec, N, tmp_path, clip_names=None, exact=True):
-    from pbhc_b200.fixtures import CLIPS29
+    from benchkit.fixtures import CLIPS29
     from pbhc_b200.motion_lib import MotionLibRobot
     from pbhc_b200.tracking_step import TrackingStep
     from tests.test_gpu_parity import _install_exact_table
@@ -106,7 +106,7 @@ def _run_golden_case(case, tmp_path, exact, loose=None):
     g = gold(f"ref_env_{case}.npz")
     spec = TrackSpec.from_config(json.loads(str(g["meta_config_json"])))
     N = int(g["meta_n_envs"])
-    from pbhc_b200.fixtures import clips_of_case
+    from benchkit.fixtures import clips_of_case
     ts, ml = make_step(spec, N, tmp_path, clip_names=clips_of_case(json.loads(str(g["meta_config_json"])))[1], exact=exact)
     sim = make_sim(N, spec.Jb, spec.D, spec.L)
     init = {k[5:]: g[k] for k in g if k.startswith("init_")}
@@ -220,7 +220,7 @@ def test_track_step_on_product_built_table_matches_reference_golden(case, tmp_pa
 @pytest.mark.parametrize("n_envs", [1, 37, 4096])
 def test_workload_step_vs_oracle(n_envs, tmp_path):
     """the bench workload itself (ragged and default-training sizes) against the CPU oracle, incl. resets."""
-    from pbhc_b200.workload import Workload
+    from benchkit.workload import Workload
     from tests._util import check_workload_step_against_oracle
     wl = Workload(n_envs, DEV, str(tmp_path), seed=3)
     n_reset = check_workload_step_against_oracle(wl, n_steps=3)
@@ -232,7 +232,7 @@ def test_workload_step_vs_oracle(n_envs, tmp_path):
 def test_workload_step_vs_oracle_general_tracking(n_envs, tmp_path):
     """config C (general_tracking, G1 29-DoF, 3-clip library with per-env motion ids and random start times) against the
     CPU oracle at ragged and training sizes, incl. resets and the 20-step future window."""
-    from pbhc_b200.workload import Workload, CASE_C
+    from benchkit.workload import Workload, CASE_C
     from tests._util import check_workload_step_against_oracle
     wl = Workload(n_envs, DEV, str(tmp_path), seed=4, case=CASE_C)
     n_reset = check_workload_step_against_oracle(wl, n_steps=3)
@@ -244,7 +244,7 @@ def test_workload_step_vs_oracle_general_tracking_large_library(tmp_path):
     """config C on the SURVEY 8d style library (fixtures.library29: the 29-DoF clip + the zero-padded, time-warped 23-DoF
     clips; 96 clips here so that the CPU oracle builds it in seconds - bench.py runs 1024): per-env motion ids over all
     clips, the table built by ONE batched FK + pbhc_clips_prepare launch"""
-    from pbhc_b200.workload import Workload, CASE_C
+    from benchkit.workload import Workload, CASE_C
     from tests._util import check_workload_step_against_oracle
     wl = Workload(4096, DEV, str(tmp_path), seed=6, case=CASE_C, library_clips=96)
     assert wl.lib._desc.num_clips == 96
@@ -255,7 +255,7 @@ def test_workload_step_vs_oracle_general_tracking_large_library(tmp_path):
 def test_host_step_chunked_pipeline_equals_single_launch(tmp_path):
     """HostStep (host buffers, 5 ragged env chunks on 3 streams) gives bit-identical per-env results to one launch;
     in-kernel reset draws are keyed by the global env id, so they do not depend on the chunking either."""
-    from pbhc_b200.workload import Workload
+    from benchkit.workload import Workload
     from pbhc_b200.tracking_step import HostStep
     n = 1003
     a = Workload(n, DEV, str(tmp_path / "a"), seed=7)
@@ -288,8 +288,8 @@ def test_observation_noise_statistics(tmp_path):
     per observation group and for the pushed history element (helpers.py:128-152).  torch.rand_like cannot be replayed,
     so parity here is distributional: bounds, mean 0, variance 1/3, independence between groups, exact equality of the
     noise-free columns and of everything that is not an observation, reproducibility under the seed."""
-    from pbhc_b200.fixtures import MAIN_NOISE
-    from pbhc_b200.workload import Workload
+    from benchkit.fixtures import MAIN_NOISE
+    from benchkit.workload import Workload
     n = 8192
     clean = Workload(n, DEV, str(tmp_path / "c"), seed=5)
     noisy = Workload(n, DEV, str(tmp_path / "n"), seed=5, noise=MAIN_NOISE)
@@ -352,7 +352,7 @@ def test_push_robots_in_kernel_draws(case, tmp_path):
     cfg = json.loads(str(g["meta_config_json"]))
     spec = TrackSpec.from_config(cfg)
     N = 2048
-    from pbhc_b200.fixtures import clips_of_case
+    from benchkit.fixtures import clips_of_case
     ts, ml = make_step(spec, N, tmp_path, clip_names=clips_of_case(cfg)[1], exact=False)
     sim = make_sim(N, spec.Jb, spec.D, spec.L)
     mids = torch.zeros(N, device=DEV, dtype=torch.int64)

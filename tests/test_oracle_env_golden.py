@@ -19,7 +19,7 @@ def load_case(name):
     g = gold(f"ref_env_{name}.npz")
     spec = TrackSpec.from_config(json.loads(str(g["meta_config_json"])))
     N = int(g["meta_n_envs"])
-    from pbhc_b200.fixtures import clips_of_case
+    from benchkit.fixtures import clips_of_case
     tag, names = clips_of_case(json.loads(str(g["meta_config_json"])))
     clips = [oracle_clip(tag, nm) for nm in names]
     tab = O.MotionTable(clips, spec.Jb, motion_to_clip=[i % len(clips) for i in range(N)])  # load_motions(random_sample=False)

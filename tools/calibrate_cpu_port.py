@@ -16,7 +16,7 @@ import torch
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 from oracle import ref_env as E, ref_loader as R  # noqa: E402
-from pbhc_b200 import synth  # noqa: E402
+from benchkit import synth  # noqa: E402
 
 
 def time_reference(n_envs, steps, warmup=2, seed=3):

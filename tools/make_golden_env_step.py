@@ -8,7 +8,7 @@ import numpy as np
 import torch
 
 from oracle import ref_env as E, ref_loader as R
-from pbhc_b200 import synth
+from benchkit import synth
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 GOLD = os.path.join(ROOT, "tests", "golden")
@@ -53,9 +53,9 @@ def env_state(env):
 
 
 def _library29(tmp="/tmp/pbhc_golden"):
-    """the 3-clip 29-DoF library of pbhc_b200.fixtures.CLIPS29 as a joblib file the reference loads."""
+    """the 3-clip 29-DoF library of benchkit.fixtures.CLIPS29 as a joblib file the reference loads."""
     import joblib
-    from pbhc_b200.fixtures import CLIPS29, motion_npz
+    from benchkit.fixtures import CLIPS29, motion_npz
     os.makedirs(tmp, exist_ok=True)
     data = {}
     for nm in CLIPS29:

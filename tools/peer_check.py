@@ -83,7 +83,7 @@ def main():
     out["peer_us"] = timed(lambda z: pd.all_reduce_sum_(z))
     out["nccl_us"] = timed(lambda z: dist.all_reduce(z))
     # ---- 4. sharded finalize == single-process finalize
-    from pbhc_b200.workload import Workload
+    from benchkit.workload import Workload
     N = 64 * world
     full = Workload(N, dev, tempfile.mkdtemp(prefix=f"pc_full{rank}_"), seed=5)
     lo, hi = pd.shard_range(N, rank, world)

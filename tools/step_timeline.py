@@ -15,7 +15,7 @@ import torch.distributed as dist
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from pbhc_b200 import _lib, dist as pd  # noqa: E402
-from pbhc_b200.workload import Workload  # noqa: E402
+from benchkit.workload import Workload  # noqa: E402
 
 
 def main():

@@ -14,7 +14,7 @@ import torch
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
-from pbhc_b200.fixtures import gold, product_cfg  # noqa: E402
+from benchkit.fixtures import gold, product_cfg  # noqa: E402
 from pbhc_b200.motion_lib import MotionLibRobot  # noqa: E402
 
 

@@ -9,7 +9,7 @@ import tempfile
 os.environ["PBHC_TILE_PROF"] = "1"
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch  # noqa: E402
-from pbhc_b200.workload import Workload  # noqa: E402
+from benchkit.workload import Workload  # noqa: E402
 
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 65536
 wl = Workload(n, "cuda:0", tempfile.mkdtemp(), seed=1)
