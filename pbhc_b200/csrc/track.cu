@@ -1320,6 +1320,9 @@ constexpr int kReduceGroups = 1024 / PBHC_ACC;
 __global__ void __launch_bounds__(1024) track_reduce_kernel(const double* __restrict__ partials, int n_blocks, double* __restrict__ acc) {
   __shared__ double part[kReduceGroups][PBHC_ACC + 1];
   const int a = threadIdx.x & (PBHC_ACC - 1), g = threadIdx.x / PBHC_ACC;  // blockDim = kReduceGroups * PBHC_ACC
+  // launched with programmatic stream serialization (launch_reduce): the block is resident while the step kernel drains;
+  // the step kernel's writes are visible after this returns
+  cudaGridDependencySynchronize();
   double v = 0.0;
 #pragma unroll 4
   for (int b = g; b < n_blocks; b += kReduceGroups) v += partials[(int64_t)b * PBHC_ACC + a];
@@ -1434,6 +1437,23 @@ __global__ void track_finalize_kernel(const __grid_constant__ PbhcTrackCfg c, co
 
 
 static int g_track_blocks_per_sm = 0;
+
+// the deterministic reduction behind the step kernel, as a programmatic dependent launch: its launch latency overlaps the
+// step kernel's tail instead of following its full drain (PBHC_REDUCE_PDL=0: a plain dependent launch)
+static void launch_reduce(const double* partials, int blocks, double* acc, cudaStream_t stream) {
+  static const bool pdl = [] { const char* e = getenv("PBHC_REDUCE_PDL"); return !(e && e[0] == '0'); }();
+  if (!pdl) { track_reduce_kernel<<<1, kReduceGroups * PBHC_ACC, 0, stream>>>(partials, blocks, acc); return; }
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(1); cfg.blockDim = dim3(kReduceGroups * PBHC_ACC); cfg.dynamicSmemBytes = 0; cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr; cfg.numAttrs = 1;
+  if (cudaLaunchKernelEx(&cfg, track_reduce_kernel, partials, blocks, acc) != cudaSuccess) {
+    (void)cudaGetLastError();
+    track_reduce_kernel<<<1, kReduceGroups * PBHC_ACC, 0, stream>>>(partials, blocks, acc);
+  }
+}
 int jit_get(const char* what, const std::string& spec_header, bool noise, const void** kernel);   // jit.cu
 
 // "track_spec.h" of the warp-per-env kernel: the env config as a constant byte image (seed zeroed: it stays a launch parameter)
@@ -1655,7 +1675,7 @@ extern "C" int pbhc_track_step(const PbhcTrackCfg* cfg, const PbhcTableDesc* tab
       const int rc = track_tile_launch(c, *tab, *io, n, (cudaStream_t)stream, &blocks);
       if (rc < 0) return rc;
       if (rc == PBHC_OK) {
-        track_reduce_kernel<<<1, kReduceGroups * PBHC_ACC, 0, (cudaStream_t)stream>>>(io->partials, blocks, io->acc);
+        launch_reduce(io->partials, blocks, io->acc, (cudaStream_t)stream);
         return check_launch("pbhc_track_step");
       }  // (rc > 0: tensors the tile kernel does not take, e.g. not 16-byte aligned - the kernel below runs)
     }
@@ -1724,7 +1744,7 @@ extern "C" int pbhc_track_step(const PbhcTrackCfg* cfg, const PbhcTableDesc* tab
       g_track_info[0] = 3; g_track_info[1] = (int)blocks; g_track_info[2] = (int)shmem; g_track_info[3] = jk_per_sm;
       void* args[] = {(void*)&P};
       if (cudaLaunchKernel(jk, dim3((unsigned)blocks), dim3(kTW * 32), args, shmem, (cudaStream_t)stream) != cudaSuccess) return check_launch("pbhc_track_step(spec)");
-      track_reduce_kernel<<<1, kReduceGroups * PBHC_ACC, 0, (cudaStream_t)stream>>>(io->partials, (int)blocks, io->acc);
+      launch_reduce(io->partials, (int)blocks, io->acc, (cudaStream_t)stream);
       return check_launch("pbhc_track_step");
     }
   }
@@ -1746,7 +1766,7 @@ extern "C" int pbhc_track_step(const PbhcTrackCfg* cfg, const PbhcTableDesc* tab
     void* args[] = {(void*)&P};
     if (cudaLaunchKernel(kern, dim3((unsigned)blocks), dim3(kTW * 32), args, shmem, (cudaStream_t)stream) != cudaSuccess) return check_launch("pbhc_track_step(launch)");
   }
-  track_reduce_kernel<<<1, kReduceGroups * PBHC_ACC, 0, (cudaStream_t)stream>>>(io->partials, (int)blocks, io->acc);
+  launch_reduce(io->partials, (int)blocks, io->acc, (cudaStream_t)stream);
   return check_launch("pbhc_track_step");
 }
 
