@@ -35,6 +35,7 @@ namespace pbhc {
 constexpr int kTW = F_TW;
 constexpr int kTrackMaxBlocks = 148 * 8;
 constexpr int kChunk = 16;                  // envs per pre phase (lanes used by it)
+constexpr int kFutChunk = 3;                // future steps whose dof / key-body rows are fetched together (general_tracking window)
 
 struct TrackParams {
   PbhcTrackCfg c;
@@ -59,6 +60,7 @@ struct TrackParams {
   int n_hdst_max;                        // max destinations of one history element
   int rew_extra;                         // bit (id - R_RADIAL_BODY_VEL): that R15 reward term is active
   int need_rootq;                        // relyaw sources or the feet-heading rewards are in use: the loop reads the root quaternion
+  int fut_win;                           // the staging buffer has room for kFutChunk steps of future-window rows behind the per-step table
 };
 
 // block-level tables (built once per block from the launch parameters)
@@ -1023,6 +1025,70 @@ __device__ __forceinline__ void track_body(const TrackParams& P) {
           }
           __syncwarp();
           const FDst d_dof = fdst(S_FUT_DOF), d_key = fdst(S_FUT_KEY);
+          // In a compact record the dof positions and the key-body positions of a frame are ONE contiguous run of D + 3K floats
+          // (56 for the teacher config).  Reading them straight from the table makes every step of the two loops below a
+          // dependent global load (ncu: 19 % of the kernel's stall samples sit on these two loops).  With the compact table the
+          // runs of kFutChunk steps x 2 frames are fetched together by cp.async into the idle part of the staging buffer: the
+          // table latency is exposed once per chunk instead of once per step, and the loops read shared memory.  Copy width:
+          // 16 bytes when the run is a multiple of 4 floats, 8 bytes when it is even (the teacher config: 29 + 3 x 11 = 62 floats
+          // = 31 pieces; the run starts 80 bytes into a 16-byte aligned record and the staged rows are 248 bytes apart).
+          const int row_f = D + 3 * K;
+          const int wf = (row_f & 3) == 0 ? 4 : ((row_f & 1) == 0 ? 2 : 0);  // floats per copy
+          // Which pair of loops runs is decided on the host from the launch itself (fut_staged_ok: compact table bound, even run,
+          // staging on).  The specialised kernel gets it as a constant and so carries ONE pair: with both compiled in, this
+          // instruction-fetch-bound kernel is slower on either path (B200, one box, 1.283 ms without the staged loops at all,
+          // 1.297 staged / 1.344 direct with both, 1.257 with the staged pair alone).
+#ifdef PBHC_SPEC
+          const bool staged = spec::fut_staged != 0;
+#else
+          const bool staged = ft && wf != 0 && P.fut_win;
+#endif
+          if (staged) {
+            float* win = fut + kFut * 32;
+            const uint32_t win_s = (uint32_t)__cvta_generic_to_shared(win);
+            const int pieces = row_f / wf;
+#pragma unroll 1
+            for (int c0 = 0; c0 < F; c0 += kFutChunk) {
+              const int ns = F - c0 < kFutChunk ? F - c0 : kFutChunk;
+              __syncwarp();  // (the previous chunk has been read)
+              for (int i = lane; i < 2 * ns * pieces; i += 32) {
+                const int r = i / pieces, pc = i - r * pieces, st = c0 + (r >> 1);
+                const int fr = __float_as_int(fut[((r & 1) ? F_F1 : F_F0) * 32 + st]);
+                const uint32_t dsts = win_s + 4 * (r * row_f + wf * pc);
+                const float* srcg = f_rec + (int64_t)fr * f_stride + o_dp + wf * pc;
+                if (wf == 4) cp_async16(dsts, srcg); else cp_async8(dsts, srcg);
+              }
+              cp_async_wait();
+              __syncwarp();
+#pragma unroll 1
+              for (int sl = 0; sl < ns; ++sl) {  // dof_pos: lane = dof
+                const int st = c0 + sl;
+                const float bb = fut[F_BLEND * 32 + st], ob = 1.0f - bb;
+                if (ld) {
+                  const float v = ob * win[(2 * sl) * row_f + lane] + bb * win[(2 * sl + 1) * row_f + lane];
+                  fput(d_dof, st * D + lane, v);
+                  if (st == 0) emit1<kNoise>(T, rows, S_NEXT_STEP, 7 + lane, v, nk);
+                }
+              }
+#pragma unroll 1
+              for (int sl0 = 0; sl0 < ns; sl0 += 2) {  // key bodies in the reference anchor frame: lane = (step, key)
+                const int sl = sl0 + (lane >> 4), k = lane & 15, st = c0 + sl;
+                if (sl < ns && k < K) {
+                  const float* w0 = win + (2 * sl) * row_f + D + 3 * k;
+                  const float* w1 = w0 + row_f;
+                  const float bb = fut[F_BLEND * 32 + st], ob = 1.0f - bb;
+                  const V3 d = {((ob * w0[0] + bb * w1[0]) + org[0]) - fut[F_APX * 32 + st],
+                                ((ob * w0[1] + bb * w1[1]) + org[1]) - fut[F_APY * 32 + st],
+                                ((ob * w0[2] + bb * w1[2]) + org[2]) - fut[F_APZ * 32 + st]};
+                  const Q4 aq = {fut[F_AQX * 32 + st], fut[F_AQY * 32 + st], fut[F_AQZ * 32 + st], fut[F_AQW * 32 + st]};
+                  const V3 lp = quat_apply(quat_conj(aq), d);
+                  const int el = st * 3 * K + 3 * k;
+                  fput(d_key, el, lp.x); fput(d_key, el + 1, lp.y); fput(d_key, el + 2, lp.z);
+                  if (st == 0) emit3<kNoise>(T, rows, S_NEXT_STEP, 7 + D + 3 * k, lp.x, lp.y, lp.z, nk);
+                }
+              }
+            }
+          } else {
 #pragma unroll 1
           for (int s = 0; s < F; ++s) {  // dof_pos of every future step: lane = dof (not unrolled: the specialised kernel knows F, and 20 copies of the body only cost instruction-cache misses)
             const float* q0 = f_rec + (int64_t)__float_as_int(fut[F_F0 * 32 + s]) * f_stride;
@@ -1051,6 +1117,7 @@ __device__ __forceinline__ void track_body(const TrackParams& P) {
               fput(d_key, el, lp.x); fput(d_key, el + 1, lp.y); fput(d_key, el + 2, lp.z);
               if (s == 0) emit3<kNoise>(T, rows, S_NEXT_STEP, 7 + D + 3 * k, lp.x, lp.y, lp.z, nk);
             }
+          }
           }
           __syncwarp();
         }
@@ -1456,8 +1523,18 @@ static void launch_reduce(const double* partials, int blocks, double* acc, cudaS
 }
 int jit_get(const char* what, const std::string& spec_header, bool noise, const void** kernel);   // jit.cu
 
+// the future window of this launch can take the staged loops: compact table bound, its dof + key-body run copyable in 8- or
+// 16-byte pieces, staging not switched off (PBHC_FUT_STAGE=0).  Used by pbhc_track_step AND pbhc_track_specialize, so the
+// kernel that is warmed up is the kernel that is launched; a launch without the compact table gets the direct-read variant
+// (forcing the staged loops onto the packed table is a misaligned cp.async - measured, it kills the context).
+static bool fut_staged_ok(const PbhcTrackCfg& c, const PbhcTrackIO& io) {
+  static const bool on = [] { const char* e = getenv("PBHC_FUT_STAGE"); return !(e && e[0] == '0'); }();
+  return on && c.general && c.n_future > 0 && io.fut_table != nullptr && ((c.D + 3 * c.n_key) & 1) == 0;
+}
+
 // "track_spec.h" of the warp-per-env kernel: the env config as a constant byte image (seed zeroed: it stays a launch parameter)
-static std::string track_spec_header(const PbhcTrackCfg& c) {
+// plus the launch facts the kernel is specialised on
+static std::string track_spec_header(const PbhcTrackCfg& c, bool fut_staged) {
   PbhcTrackCfg z = c;
   z.seed = 0;
   const unsigned char* b = reinterpret_cast<const unsigned char*>(&z);
@@ -1465,22 +1542,24 @@ static std::string track_spec_header(const PbhcTrackCfg& c) {
                   "__device__ const unsigned char __align__(16) cfg_bytes[" + std::to_string(sizeof(z)) + "] = {";
   char buf[8];
   for (size_t i = 0; i < sizeof(z); ++i) { snprintf(buf, sizeof(buf), "%u,", (unsigned)b[i]); h += buf; if ((i & 63) == 63) h += "\n"; }
-  h += "};\n}  // namespace spec\n";
+  h += "};\n";
+  h += std::string("constexpr int fut_staged = ") + (fut_staged ? "1" : "0") + ";  // future window: staged loops (1) or direct table reads (0)\n";
+  h += "}  // namespace spec\n";
   return h;
 }
 
 // the kernel specialised for this config (kernel == nullptr: compile into the on-disk cache only); cached per thread
-static int jit_track(const PbhcTrackCfg& c, bool noise, const void** kernel) {
+static int jit_track(const PbhcTrackCfg& c, bool noise, bool fut_staged, const void** kernel) {
   static thread_local PbhcTrackCfg last;
-  static thread_local bool last_noise = false, have = false;
+  static thread_local bool last_noise = false, last_staged = false, have = false;
   static thread_local const void* last_fn = nullptr;
   static thread_local int last_rc = 0;
   PbhcTrackCfg z = c;
   z.seed = 0;
-  if (kernel && have && last_noise == noise && !memcmp(&last, &z, sizeof(z))) { *kernel = last_fn; return last_rc; }
+  if (kernel && have && last_noise == noise && last_staged == fut_staged && !memcmp(&last, &z, sizeof(z))) { *kernel = last_fn; return last_rc; }
   const void* fn = nullptr;
-  const int rc = jit_get("track", track_spec_header(c), noise, kernel ? &fn : nullptr);
-  if (kernel) { last = z; last_noise = noise; have = true; last_fn = fn; last_rc = rc; *kernel = fn; }
+  const int rc = jit_get("track", track_spec_header(c, fut_staged), noise, kernel ? &fn : nullptr);
+  if (kernel) { last = z; last_noise = noise; last_staged = fut_staged; have = true; last_fn = fn; last_rc = rc; *kernel = fn; }
   return rc;
 }
 int track_tile_launch(const PbhcTrackCfg& c, const PbhcTableDesc& tab, const PbhcTrackIO& io, int64_t n, cudaStream_t stream, int* blocks_out);  // track_tile.cu
@@ -1548,7 +1627,7 @@ extern "C" int pbhc_track_specialize(const PbhcTrackCfg* cfg, const PbhcTableDes
   if (cfg->general) {  // LeggedRobotGeneralTracking: the warp-per-env kernel, specialised for the config
     bool noise = false;
     for (int k = 0; k < PBHC_NUM_OBS_SRC; ++k) noise |= cfg->obs_noise[k] != 0.0f;
-    return pbhc::jit_track(*cfg, noise, nullptr) == 0 ? PBHC_OK : PBHC_E_CUDA;
+    return pbhc::jit_track(*cfg, noise, pbhc::fut_staged_ok(*cfg, *io), nullptr) == 0 ? PBHC_OK : PBHC_E_CUDA;
   }
   if (pbhc::needs_warp_kernel(*cfg)) return PBHC_OK;  // served by the generic warp-per-env kernel
   return pbhc::track_tile_prepare(*cfg, *tab, *io);
@@ -1696,6 +1775,25 @@ extern "C" int pbhc_track_step(const PbhcTrackCfg* cfg, const PbhcTableDesc* tab
   // general_tracking runs two blocks per SM (register-bound): there is shared memory to spare, so the staging buffer is
   // widened to also take the (longer) history ring
   if (c.general && c.hist_row > stage_len && c.hist_row <= 1024) stage_len = up4h(c.hist_row);
+  // ... and to take kFutChunk steps x 2 frames of the future window's dof / key-body rows behind its per-step table
+  // (PBHC_FUT_STAGE=0: the window reads the table directly, for A/B runs)
+  P.fut_win = 0;
+  if (fut_staged_ok(c, *io)) {
+    const int need = kFut * 32 + kFutChunk * 2 * (c.D + 3 * c.n_key);
+    if (need > stage_len) stage_len = up4h(need);
+    P.fut_win = 1;
+  }
+  {  // PBHC_TRACK_VERBOSE=1: which path the future window of this launch takes (once per process)
+    static bool told = false;
+    const char* v = getenv("PBHC_TRACK_VERBOSE");
+    if (!told && v && v[0] == '1' && c.general && c.n_future > 0) {
+      told = true;
+      const int row_f = c.D + 3 * c.n_key, wf = (row_f & 3) == 0 ? 4 : ((row_f & 1) == 0 ? 2 : 0);
+      fprintf(stderr, "[pbhc track] future window: run of %d floats per frame, compact table %s, staging %s -> %s\n", row_f,
+              io->fut_table ? "yes" : "no", P.fut_win ? "on" : "off",
+              (io->fut_table && wf && P.fut_win) ? (wf == 4 ? "staged, 16-byte copies" : "staged, 8-byte copies") : "direct table reads");
+    }
+  }
   P.sm_rows = P.sm_body + stage_len;
   P.sm_per_warp = P.sm_rows + up4h(P.rows_len) + dump_len;
   P.o_hmap = (int)((sizeof(BlockTables) + 15) & ~size_t(15));
@@ -1727,7 +1825,7 @@ extern "C" int pbhc_track_step(const PbhcTrackCfg* cfg, const PbhcTableDesc* tab
   int which = 0;
   if (c.general) {  // the kernel specialised for this env config, when it can be had (NVRTC, cached on disk; PBHC_JIT=0 turns it off)
     const void* jk = nullptr;
-    if (jit_track(c, noise, &jk) == 0 && jk) {
+    if (jit_track(c, noise, P.fut_win != 0, &jk) == 0 && jk) {
       static thread_local const void* jk_configured = nullptr;
       static thread_local size_t jk_shmem = 0;
       static thread_local int jk_per_sm = 0;

@@ -346,6 +346,7 @@ class TrackingStep:
         io = _lib.TrackIO()
         io.default_dof_stride = spec.D
         io.ref_body_pos_extend, io.ref_body_rot_extend = 16, 16  # (only their NULL-ness is read)
+        io.fut_table = 16 if self._uses_future_table() else None    # (likewise: selects the staged or the direct-read future window)
         return _lib.lib().pbhc_track_specialize(C.byref(self._cfg), C.byref(desc), C.byref(io)) == 0
 
     def launch_info(self):
@@ -404,10 +405,15 @@ class TrackingStep:
         io.inject_push_interval, io.inject_push_vel = p(inj.get("push_interval_s"), torch.int64), p(inj.get("push_vel"), torch.float32)
         self._keep = (sim, actions, torques, env_origins, motion_ids, inj)
 
+    def _uses_future_table(self):
+        """a compact future-window table is bound to the launches of this step (one predicate for _future_table() and for the
+        warm-up in specialize(): the kernel is specialised on it, csrc/track.cu fut_staged_ok)"""
+        return bool(self.spec.general and self.spec.future_num_steps > 0 and os.environ.get("PBHC_FUTURE_TABLE", "1") != "0")
+
     def _future_table(self):
         """general_tracking: compact per-frame records for the 20-step future window (pbhc_future_table_build), rebuilt when
         the motion library's table changes (load_motions / resample_motion); None when the config has no future window."""
-        if not (self.spec.general and self.spec.future_num_steps > 0) or os.environ.get("PBHC_FUTURE_TABLE", "1") == "0":
+        if not self._uses_future_table():
             return None  # (PBHC_FUTURE_TABLE=0: the window reads the packed table itself - same results, for A/B runs)
         ver = (getattr(self.lib, "_table_version", 0), self.lib._records.data_ptr())
         if getattr(self, "_fut_ver", None) != ver:
