@@ -46,6 +46,7 @@ def parse_args():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-graph", action="store_true", help="launch eagerly instead of replaying a CUDA graph")
     ap.add_argument("--no-fk", action="store_true", help="leave the K2 launch out of the step")
+    ap.add_argument("--no-push-robots", action="store_true", help="domain_rand.push_robots off (the shipped domain_rand/main.yaml has it on; the fixtures and round 1 ran without)")
     ap.add_argument("--cpu-envs", type=int, default=4096, help="envs in the CPU baseline's bounded sample")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="CPU baseline time budget")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -57,6 +58,9 @@ def parse_args():
                     help="A: BASELINE configs[0..1] (23-DoF motion_tracking, the headline); C: configs[2] (29-DoF general_tracking)")
     a = ap.parse_args()
     global WORKLOAD
+    if a.no_push_robots:  # the labels say what ran
+        for k in WORKLOADS:
+            WORKLOADS[k] = WORKLOADS[k].replace("domain_rand=main incl. push_robots", "domain_rand=main with push_robots off")
     WORKLOAD = WORKLOADS[a.workload]
     return a
 
@@ -139,7 +143,7 @@ class ClockSampler(threading.Thread):
 # CPU arm: the oracle port of the reference's torch implementation, on the host cores (the one place outside tests/
 # and smoke() that executes oracle/).
 # ---------------------------------------------------------------------------------------------------------------
-def cpu_reference(n_envs, steps, warmup, seconds=None, with_fk=True, seed=0, workload="A"):
+def cpu_reference(n_envs, steps, warmup, seconds=None, with_fk=True, seed=0, workload="A", push_robots=True):
     """Times `steps` env steps (or as many as fit in `seconds`, at least 3) of the CPU oracle on n_envs envs."""
     import torch
     from oracle import pbhc_oracle as O, pbhc_oracle_env as OE
@@ -158,7 +162,7 @@ def cpu_reference(n_envs, steps, warmup, seconds=None, with_fk=True, seed=0, wor
     from benchkit.workload import CASE, CASE_C, CLIP
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
-    spec = TrackSpec.from_config(env_config(CASE_C if workload == "C" else CASE, push_robots=True))
+    spec = TrackSpec.from_config(env_config(CASE_C if workload == "C" else CASE, push_robots=push_robots))
     tag, clips = ("29", list(CLIPS29)) if spec.general else ("23", [CLIP])
     tree = oracle_tree(tag)
     N, D, Jb, J = n_envs, spec.D, spec.Jb, spec.J
@@ -213,7 +217,7 @@ def run_reference_arm(a):
         return 0
     # the arm runs the GPU arm's config: all a.envs envs per step (the oracle port steps 65536 envs in about a second on the
     # host cores); the time budget only guards against a very slow host
-    r = cpu_reference(a.envs, a.steps, a.warmup, seconds=240.0, with_fk=not a.no_fk, workload=a.workload)
+    r = cpu_reference(a.envs, a.steps, a.warmup, seconds=240.0, with_fk=not a.no_fk, workload=a.workload, push_robots=not a.no_push_robots)
     sample = (f"{r['n_envs']} envs per step (the whole {a.envs}-env workload), {r['steps']} timed steps after {a.warmup} warm-up; "
               "CPU oracle port of the reference torch path (oracle/pbhc_oracle_env.py, pinned bit-exact to the reference env), "
               f"torch {r['torch']} with {r['cores']} threads")
@@ -248,7 +252,7 @@ def run_b200_arm(a):
         dist.init_process_group("nccl", device_id=dev)
     N, K, W, with_fk = a.envs, a.steps, max(a.warmup, 3), not a.no_fk
     from benchkit.workload import CASE, CASE_C
-    wl = Workload(N, dev, tempfile.mkdtemp(prefix=f"pbhc_bench_r{rank}_"), seed=1000 + rank, case=CASE_C if a.workload == "C" else CASE, push_robots=True,
+    wl = Workload(N, dev, tempfile.mkdtemp(prefix=f"pbhc_bench_r{rank}_"), seed=1000 + rank, case=CASE_C if a.workload == "C" else CASE, push_robots=not a.no_push_robots,
                   env_offset=rank * N)  # (the in-kernel random streams are keyed by the global env id)
     ts = wl.ts
     sampler = ClockSampler(torch.cuda.current_device() if os.environ.get("CUDA_VISIBLE_DEVICES") is None else local)
@@ -363,7 +367,7 @@ def run_b200_arm(a):
     if cfg_c is not None:
         line["config_C"] = cfg_c
     if not a.no_cpu_baseline:
-        r = cpu_reference(a.cpu_envs, 10 ** 9, 2, seconds=a.cpu_seconds, with_fk=with_fk, workload=a.workload)
+        r = cpu_reference(a.cpu_envs, 10 ** 9, 2, seconds=a.cpu_seconds, with_fk=with_fk, workload=a.workload, push_robots=not a.no_push_robots)
         line["cpu_baseline"] = {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "port",
                                 "sample": f"{r['n_envs']} envs per step, {r['steps']} steps in ~{a.cpu_seconds:.0f} s, CPU oracle port of the "
                                           f"reference torch path (torch {r['torch']}, {r['cores']} threads), FK {'in' if with_fk else 'not in'} step",
@@ -380,7 +384,7 @@ def config_c_pass(torch, a, dev, peak):
     import time as _t
     from benchkit.workload import Workload, CASE_C, fk_bytes
     t0 = _t.perf_counter()
-    wl = Workload(a.envs, dev, tempfile.mkdtemp(prefix="pbhc_bench_C_"), seed=2000, case=CASE_C, library_clips=a.library_clips, push_robots=True)
+    wl = Workload(a.envs, dev, tempfile.mkdtemp(prefix="pbhc_bench_C_"), seed=2000, case=CASE_C, library_clips=a.library_clips, push_robots=not a.no_push_robots)
     load_s = _t.perf_counter() - t0
     for _ in range(3):
         wl.step(True)

@@ -46,7 +46,7 @@ def time_reference(n_envs, steps, warmup=2, seed=3):
 def time_port(n_envs, steps, warmup=2):
     sys.argv = [sys.argv[0]]
     import bench
-    r = bench.cpu_reference(n_envs, steps, warmup, with_fk=False)
+    r = bench.cpu_reference(n_envs, steps, warmup, with_fk=False, push_robots=False)  # (like the reference env above: domain_rand.push_robots off on both sides)
     return r["ms_per_step"], r["cores"]
 
 
